@@ -1,0 +1,180 @@
+/*
+ * gdk_b200.h — C-ABI of the B200-native GDK column-at-a-time hot path.
+ *
+ * One entry point per reference GDK operator on the path, with the same name
+ * (prefixed b200_), the same argument order, meaning and error behaviour.  The
+ * only change is that the reference's `BAT *` (gdk.h:778-804) is replaced by a
+ * plain descriptor `b200_bat` holding exactly the BAT/COLrec fields the path
+ * reads: no reference struct layout, no torch types, plain pointers and sizes.
+ * The reference-side binding (a patched libbat entry point that converts
+ * BAT* <-> b200_bat and tail-calls these functions) is shown in INTEGRATION.md
+ * and built in shim/.
+ *
+ * Conventions (all cited files are relative to the MonetDB reference tree):
+ *  - oid / BUN are 64-bit unsigned (gdk.h:460-461,507); oid_nil = 1<<63.
+ *  - fixed-width atoms only; nil is in-band (gdk_atoms.h:149-218): integer nil
+ *    = type minimum, flt/dbl nil = NaN.  date is stored as int, timestamp and
+ *    daytime as lng (ATOMbasetype, gdk_atoms.h:285-289).
+ *  - BAT-returning functions return NULL after recording a message retrievable
+ *    with b200_errbuf() (GDKerror/GDKerrbuf, gdk.h:1710-1717); gdk_return
+ *    functions return B200_FAIL likewise.  Messages carry the reference's
+ *    SQLSTATE-prefixed texts.
+ *  - inputs are borrowed; every returned BAT is new, device-resident and owned
+ *    by the caller (release with b200_BATfree = BBPreclaim).
+ *  - there is NO CPU fallback: if no CUDA device is usable every entry point
+ *    fails loudly.
+ */
+#ifndef GDK_B200_H
+#define GDK_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef uint64_t b200_oid;
+#define B200_OID_NIL ((b200_oid) 1 << 63)
+#define B200_BUN_NONE ((uint64_t) INT64_MAX)
+
+/* GDK type ids, gdk.h:429-451 (HAVE_HGE build) */
+enum {
+	B200_void = 0, B200_msk = 1, B200_bit = 2, B200_bte = 3, B200_sht = 4,
+	B200_int = 5, B200_oid = 6, B200_ptr = 7, B200_flt = 8, B200_dbl = 9,
+	B200_lng = 10, B200_hge = 11, B200_date = 12, B200_daytime = 13,
+	B200_timestamp = 14
+};
+
+typedef enum { B200_FAIL = 0, B200_SUCCEED = 1 } b200_return;	/* gdk.h:348-350 */
+
+/* candidate-list encodings beyond dense/oid[] (gdk_cand.h:16-45) */
+enum { B200_CAND_NONE = 0, B200_CAND_NEGOID = 1, B200_CAND_MSK = 2 };
+
+/* The slice of BAT + COLrec (gdk.h:712-804) the hot path uses. */
+typedef struct b200_bat {
+	int32_t  ttype;		/* tail type id; B200_void => virtual dense oids from tseqbase */
+	int32_t  device;	/* CUDA ordinal owning base/vheap; -1 = host memory */
+	uint64_t hseqbase;	/* oid of row 0 */
+	uint64_t count;		/* batCount */
+	uint64_t tseqbase;	/* void/dense-oid tail start, else oid_nil */
+	void    *base;		/* Tloc(b,0); NULL for void */
+	uint64_t capacity;	/* allocated items behind base */
+	int32_t  ccand;		/* B200_CAND_*: complex candidate list in vheap */
+	uint32_t firstbit;	/* CAND_MSK: first valid bit in word 0 */
+	void    *vheap;		/* NEGOID: sorted exception oids; MSK: uint32 words */
+	uint64_t nvheap;	/* number of exceptions / mask words */
+	uint8_t  tsorted, trevsorted, tkey, tnonil, tnil;
+	uint8_t  owns;		/* descriptor owns base/vheap (freed by b200_BATfree) */
+	uint8_t  pad[2];
+} b200_bat;
+
+/* ---- runtime / device heap tier (the tier added next to gdk_heap.c:141-225) ---- */
+int  b200_init(int device);			/* bind calling thread to a device; 0 on success */
+int  b200_device_count(void);
+const char *b200_errbuf(void);			/* GDKerrbuf analogue (thread-local) */
+void b200_clrerr(void);
+const char *b200_algorithm(void);		/* MT_thread_setalgorithm tag of the last call */
+uint64_t b200_kernel_launches(void);		/* kernels launched by this library so far */
+void b200_sync(void);				/* wait for the calling thread's stream */
+void *b200_stream(void);			/* cudaStream_t of the calling thread */
+
+void *b200_pinned_alloc(size_t bytes);		/* page-locked host staging memory */
+void  b200_pinned_free(void *p);
+
+b200_bat *b200_COLnew(uint64_t hseq, int tt, uint64_t cap);			/* gdk_bat.c:292 */
+b200_bat *b200_BATdense(uint64_t hseq, uint64_t tseq, uint64_t cnt);		/* gdk_bat.c:298 */
+b200_bat *b200_BATfromhost(const void *src, int tt, uint64_t cnt, uint64_t hseq);	/* upload a tail heap */
+b200_bat *b200_BATwrap(void *devptr, int tt, uint64_t cnt, uint64_t hseq);	/* borrow device memory */
+b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc); /* gdk_cand.c:1296 */
+b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows, const uint32_t *words, bool selected); /* gdk_cand.c:1366 */
+void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil);
+int  b200_BATtohost(const b200_bat *b, void *dst);	/* logical tail -> host (void/cands materialised as oids) */
+void b200_BATfree(b200_bat *b);				/* BBPreclaim */
+
+/* ---- selection: gdk_select.c:1342 (BATselect), :2102 (BATthetaselect) ---- */
+b200_bat *b200_BATselect(const b200_bat *b, const b200_bat *s, const void *tl, const void *th,
+			 bool li, bool hi, bool anti, bool nil_matches);
+b200_bat *b200_BATthetaselect(const b200_bat *b, const b200_bat *s, const void *val, const char *op);
+
+/* ---- candidate set algebra: gdk_cand.c:46,184,259 ---- */
+b200_bat *b200_BATmergecand(const b200_bat *a, const b200_bat *b);
+b200_bat *b200_BATintersectcand(const b200_bat *a, const b200_bat *b);
+b200_bat *b200_BATdiffcand(const b200_bat *a, const b200_bat *b);
+
+/* ---- projection: gdk_project.c:857 (BATproject), :590 (BATproject2) ---- */
+b200_bat *b200_BATproject(const b200_bat *l, const b200_bat *r);
+b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, const b200_bat *r2);
+
+/* ---- calc: gdk_calc_addsub.c:1480-1664,3166-3280; gdk_calc_mul.c:2085-2113;
+ *      gdk_calc_div.c:1945; compares gdk_calc_compare_*.c; BATconvert gdk_calc_convert.c:1415.
+ *      A ValRecord constant (gdk.h:567-600) is passed as (pointer, type id). ---- */
+b200_bat *b200_BATcalcadd(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
+b200_bat *b200_BATcalcsub(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
+b200_bat *b200_BATcalcmul(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
+b200_bat *b200_BATcalcdiv(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
+b200_bat *b200_BATcalcaddcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
+b200_bat *b200_BATcalcsubcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
+b200_bat *b200_BATcalcmulcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
+b200_bat *b200_BATcalcdivcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
+b200_bat *b200_BATcalccstadd(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+b200_bat *b200_BATcalccstsub(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+b200_bat *b200_BATcalccstmul(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+b200_bat *b200_BATcalccstdiv(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+b200_bat *b200_BATcalclt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcle(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcgt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcge(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalceq(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, bool nil_matches);
+b200_bat *b200_BATcalcne(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, bool nil_matches);
+b200_bat *b200_BATcalcltcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalclecst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcgtcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcgecst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalceqcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, bool nil_matches);
+b200_bat *b200_BATcalcnecst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, bool nil_matches);
+b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int tp, uint8_t scale1, uint8_t scale2, uint8_t precision);
+
+/* ---- grouping: gdk_group.c:1347 ---- */
+b200_return b200_BATgroup(b200_bat **groups, b200_bat **extents, b200_bat **histo,
+			  const b200_bat *b, const b200_bat *s, const b200_bat *g,
+			  const b200_bat *e, const b200_bat *h);
+
+/* ---- grouped / scalar aggregates: gdk_aggr.c:900,1018,1801,3069,3561,3720 ---- */
+b200_bat *b200_BATgroupsum(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+b200_bat *b200_BATgroupmin(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+b200_bat *b200_BATgroupmax(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const b200_bat *b, const b200_bat *g,
+			     const b200_bat *e, const b200_bat *s, int tp, bool skip_nils, int scale);
+b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
+
+/* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */
+b200_return b200_BAThash(const b200_bat *b);
+b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+			 const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate);
+
+/* ---- window frames and analytic aggregates: gdk_analytic.h:21-42.
+ *      As in the reference the CALLER allocates r (b200_COLnew of the result type,
+ *      capacity >= BATcount(b)); the callee fills it and sets count/tnil/tnonil. ---- */
+b200_return b200_GDKanalyticaldiff(b200_bat *r, const b200_bat *b, const b200_bat *p, const int8_t *npbit, int tpe);
+b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_bat *b, const b200_bat *p, const b200_bat *l,
+					   const void *bound, int tp1, int tp2, int unit,
+					   bool preceding, b200_oid first_half);
+b200_return b200_GDKanalyticalsum(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+				  const b200_bat *s, const b200_bat *e, int tp1, int tp2, int frame_type);
+b200_return b200_GDKanalyticalavg(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+				  const b200_bat *s, const b200_bat *e, int tpe, int frame_type);
+b200_return b200_GDKanalyticalcount(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+				    const b200_bat *s, const b200_bat *e, int8_t ignore_nils, int tpe, int frame_type);
+b200_return b200_GDKanalyticalmin(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+				  const b200_bat *s, const b200_bat *e, int tpe, int frame_type);
+b200_return b200_GDKanalyticalmax(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+				  const b200_bat *s, const b200_bat *e, int tpe, int frame_type);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GDK_B200_H */

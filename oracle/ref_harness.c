@@ -1,0 +1,230 @@
+/*
+ * ref_harness.c — TEST INFRASTRUCTURE ONLY (never linked into the product).
+ *
+ * Thin helper layer compiled against the reference's own headers where they lie
+ * under /root/reference and linked with the reference's GDK built by
+ * oracle/Makefile into oracle/_ref/libbat_ref.so.  It lets the Python tests and
+ * bench.py's CPU-baseline leg create in-memory BATs from raw arrays, inspect
+ * result BATs, and drive the reference's real entry points (BATselect,
+ * BATproject, BATgroup, BATgroupsum, BATjoin, GDKanalytical*, ...) which are
+ * called directly through ctypes with the BAT* handles made here.
+ *
+ * Initialisation follows the embedded in-memory start-up of the reference
+ * (tools/monetdbe/monetdbe.c:646,742; gdk_utils.c:933).
+ */
+#include "monetdb_config.h"
+#include "gdk.h"
+#include "gdk_analytic.h"
+#include "monet_options.h"
+#include <pthread.h>
+
+static int refh_ready = 0;
+
+int
+refh_init(int nthreads)
+{
+	if (refh_ready)
+		return 0;
+	opt *set = NULL;
+	int setlen = mo_builtin_settings(&set);
+	if (setlen == 0)
+		return -1;
+	if (nthreads > 0) {
+		char buf[32];
+		snprintf(buf, sizeof(buf), "%d", nthreads);
+		setlen = mo_add_option(&set, setlen, opt_cmdline, "gdk_nr_threads", buf);
+	}
+	if (BBPaddfarm(NULL, (1U << PERSISTENT) | (1U << TRANSIENT), false) != GDK_SUCCEED)
+		return -2;
+	if (GDKinit(set, setlen, true, NULL) != GDK_SUCCEED)
+		return -3;
+	refh_ready = 1;
+	return 0;
+}
+
+/* a worker thread that wants to call GDK must be known to it (for GDKerrbuf etc.) */
+int
+refh_thread_attach(const char *name)
+{
+	return MT_thread_register() ? 0 : -1;
+}
+
+void
+refh_thread_detach(void)
+{
+	MT_thread_deregister();
+}
+
+const char *
+refh_errbuf(void)
+{
+	char *e = GDKerrbuf;
+	return e ? e : "";
+}
+
+void
+refh_clrerr(void)
+{
+	GDKclrerr();
+}
+
+BAT *
+refh_bat_new(int type, uint64_t count, uint64_t hseq, const void *data,
+	     int sorted, int revsorted, int key, int nonil, int nil)
+{
+	BAT *b = COLnew((oid) hseq, type, (BUN) count, TRANSIENT);
+	if (b == NULL)
+		return NULL;
+	if (count > 0 && data != NULL)
+		memcpy(Tloc(b, 0), data, (size_t) count << b->tshift);
+	BATsetcount(b, (BUN) count);
+	b->tsorted = sorted != 0;
+	b->trevsorted = revsorted != 0;
+	b->tkey = key != 0;
+	b->tnonil = nonil != 0;
+	b->tnil = nil != 0;
+	b->tseqbase = oid_nil;
+	if (count <= 1) {
+		/* BATsetcount has already set the trivial properties */
+		b->tsorted = b->trevsorted = true;
+		b->tkey = true;
+	}
+	return b;
+}
+
+/* a msk BAT from uint32 words holding `nbits` bits */
+BAT *
+refh_msk_new(uint64_t hseq, uint64_t nbits, const uint32_t *words)
+{
+	BAT *b = COLnew((oid) hseq, TYPE_msk, (BUN) nbits, TRANSIENT);
+	if (b == NULL)
+		return NULL;
+	memcpy(Tloc(b, 0), words, ((nbits + 31) / 32) * 4);
+	BATsetcount(b, (BUN) nbits);
+	return b;
+}
+
+BAT *
+refh_dense(uint64_t hseq, uint64_t tseq, uint64_t cnt)
+{
+	return BATdense((oid) hseq, (oid) tseq, (BUN) cnt);
+}
+
+void *
+refh_tloc(BAT *b)
+{
+	return b->ttype == TYPE_void ? NULL : Tloc(b, 0);
+}
+
+struct refh_info {
+	int32_t i_type;
+	int32_t i_ccand;		/* 0 none, 1 negative oids, 2 mask */
+	uint64_t i_hseq;
+	uint64_t i_count;
+	uint64_t i_tseq;
+	uint8_t p_sorted, p_revsorted, p_key, p_nonil, p_nil, pad[3];
+};
+
+void
+refh_info(BAT *b, struct refh_info *out)
+{
+	out->i_type = b->ttype;
+	out->i_ccand = 0;
+	if (b->ttype == TYPE_void && b->tvheap != NULL)
+		out->i_ccand = ((ccand_t *) b->tvheap->base)->type == CAND_NEGOID ? 1 : 2;
+	out->i_hseq = b->hseqbase;
+	out->i_count = BATcount(b);
+	out->i_tseq = b->tseqbase;
+	out->p_sorted = b->tsorted;
+	out->p_revsorted = b->trevsorted;
+	out->p_key = b->tkey;
+	out->p_nonil = b->tnonil;
+	out->p_nil = b->tnil;
+}
+
+int
+refh_width(BAT *b)
+{
+	return b->ttype == TYPE_void ? 8 : b->twidth;
+}
+
+/* logical tail: void / candidate lists are materialised as oids */
+int
+refh_tail(BAT *b, void *dst)
+{
+	BUN n = BATcount(b);
+	if (b->ttype == TYPE_void) {
+		oid *o = dst;
+		if (b->tvheap != NULL || !is_oid_nil(b->tseqbase)) {
+			if (b->tvheap != NULL) {
+				struct canditer ci;
+				canditer_init(&ci, NULL, b);
+				for (BUN i = 0; i < ci.ncand; i++)
+					o[i] = canditer_next(&ci);
+			} else {
+				for (BUN i = 0; i < n; i++)
+					o[i] = b->tseqbase + i;
+			}
+		} else {
+			for (BUN i = 0; i < n; i++)
+				o[i] = oid_nil;
+		}
+		return 0;
+	}
+	if (b->ttype == TYPE_msk) {
+		memcpy(dst, Tloc(b, 0), ((n + 31) / 32) * 4);
+		return 0;
+	}
+	memcpy(dst, Tloc(b, 0), (size_t) n << b->tshift);
+	return 0;
+}
+
+void
+refh_free(BAT *b)
+{
+	BBPreclaim(b);
+}
+
+/* run the reference's own property checker on a result (gdk_bat.c:2699) */
+void
+refh_assert_props(BAT *b)
+{
+	BATassertProps(b);
+}
+
+/* --- bounded multi-core CPU baseline (mitosis-style slicing, opt_mitosis.c:188-214):
+ * the caller supplies a per-slice worker; threads are registered with GDK. --- */
+typedef void (*refh_slice_fn)(void *arg, int slice);
+struct refh_job { refh_slice_fn fn; void *arg; int next, nslices; pthread_mutex_t mu; };
+
+static void *
+refh_worker(void *p)
+{
+	struct refh_job *j = p;
+	MT_thread_register();
+	for (;;) {
+		pthread_mutex_lock(&j->mu);
+		int s = j->next < j->nslices ? j->next++ : -1;
+		pthread_mutex_unlock(&j->mu);
+		if (s < 0)
+			break;
+		j->fn(j->arg, s);
+	}
+	MT_thread_deregister();
+	return NULL;
+}
+
+int
+refh_parallel(refh_slice_fn fn, void *arg, int nslices, int nthreads)
+{
+	struct refh_job j = { fn, arg, 0, nslices, PTHREAD_MUTEX_INITIALIZER };
+	pthread_t th[256];
+	if (nthreads > 256)
+		nthreads = 256;
+	for (int i = 0; i < nthreads; i++)
+		if (pthread_create(&th[i], NULL, refh_worker, &j) != 0)
+			return -1;
+	for (int i = 0; i < nthreads; i++)
+		pthread_join(th[i], NULL);
+	return 0;
+}
