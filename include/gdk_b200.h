@@ -67,7 +67,9 @@ typedef struct b200_bat {
 	uint64_t nvheap;	/* number of exceptions / mask words */
 	uint8_t  tsorted, trevsorted, tkey, tnonil, tnil;
 	uint8_t  owns;		/* descriptor owns base/vheap (freed by b200_BATfree) */
-	uint8_t  pad[2];
+	uint8_t  oidrange_known;	/* first_oid/last_oid valid (sorted oid tails we produced) */
+	uint8_t  pad;
+	uint64_t first_oid, last_oid;	/* smallest / largest oid of a sorted oid tail (cf. tminpos/tmaxpos) */
 } b200_bat;
 
 /* ---- runtime / device heap tier (the tier added next to gdk_heap.c:141-225) ---- */

@@ -1,0 +1,158 @@
+// common.cuh — runtime plumbing shared by every operator of the B200 GDK path:
+// per-thread CUDA context (stream, mapped result slots, error buffer), the
+// device heap tier (stream-ordered pool), BAT descriptor helpers, candidate
+// views (gdk_cand.h:47-70 analogue) and the nil encodings (gdk_atoms.h:149-218).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+#include <atomic>
+#include "../../include/gdk_b200.h"
+
+typedef uint64_t oid;
+typedef int8_t bte;
+typedef int16_t sht;
+typedef int64_t lng;
+typedef __int128 hge;
+typedef unsigned __int128 uhge;
+typedef float flt;
+typedef double dbl;
+
+#define OID_NIL ((oid) 1 << 63)
+#define NSM 148			/* B200: 148 SMs */
+
+// ---------------------------------------------------------------- nil / limits
+template <typename T> struct Atom;
+#define INT_ATOM(T, U, BITS)                                                              \
+	template <> struct Atom<T> {                                                      \
+		static constexpr bool is_float = false;                                   \
+		__host__ __device__ static inline T nil() { return (T) ((U) 1 << (BITS - 1)); } \
+		__host__ __device__ static inline T minval() { return nil() + 1; }        \
+		__host__ __device__ static inline T maxval() { return (T) ~((U) 1 << (BITS - 1)); } \
+		__host__ __device__ static inline bool is_nil(T v) { return v == nil(); } \
+		__host__ __device__ static inline T prev(T v) { return v - 1; }           \
+		__host__ __device__ static inline T next(T v) { return v + 1; }           \
+	};
+INT_ATOM(bte, uint8_t, 8)
+INT_ATOM(sht, uint16_t, 16)
+INT_ATOM(int, uint32_t, 32)
+INT_ATOM(lng, uint64_t, 64)
+INT_ATOM(hge, uhge, 128)
+template <> struct Atom<flt> {
+	static constexpr bool is_float = true;
+	__host__ __device__ static inline flt nil() { return NAN; }
+	__host__ __device__ static inline flt minval() { return -3.402823466e+38F; }
+	__host__ __device__ static inline flt maxval() { return 3.402823466e+38F; }
+	__host__ __device__ static inline bool is_nil(flt v) { return v != v; }
+	__host__ __device__ static inline flt prev(flt v) { return nextafterf(v, -3.402823466e+38F); }
+	__host__ __device__ static inline flt next(flt v) { return nextafterf(v, 3.402823466e+38F); }
+};
+template <> struct Atom<dbl> {
+	static constexpr bool is_float = true;
+	__host__ __device__ static inline dbl nil() { return NAN; }
+	__host__ __device__ static inline dbl minval() { return -1.7976931348623157e+308; }
+	__host__ __device__ static inline dbl maxval() { return 1.7976931348623157e+308; }
+	__host__ __device__ static inline bool is_nil(dbl v) { return v != v; }
+	__host__ __device__ static inline dbl prev(dbl v) { return nextafter(v, -1.7976931348623157e+308); }
+	__host__ __device__ static inline dbl next(dbl v) { return nextafter(v, 1.7976931348623157e+308); }
+};
+
+// storage ("base") type of an atom, ATOMbasetype gdk_atoms.h:285-289
+static inline int basetype(int t)
+{
+	switch (t) {
+	case B200_bit: return B200_bte;
+	case B200_date: return B200_int;
+	case B200_oid: case B200_daytime: case B200_timestamp: case B200_ptr: return B200_lng;
+	default: return t;
+	}
+}
+static inline int atomsize(int t)
+{
+	switch (basetype(t)) {
+	case B200_void: return 0;
+	case B200_bte: return 1;
+	case B200_sht: return 2;
+	case B200_int: case B200_flt: return 4;
+	case B200_lng: case B200_dbl: return 8;
+	case B200_hge: return 16;
+	default: return -1;
+	}
+}
+static inline const char *atomname(int t)
+{
+	static const char *n[] = {"void", "msk", "bit", "bte", "sht", "int", "oid", "ptr", "flt", "dbl",
+				  "lng", "hge", "date", "daytime", "timestamp"};
+	return (t >= 0 && t <= 14) ? n[t] : "?";
+}
+
+// ---------------------------------------------------------------- thread context
+struct ResultSlot {		/* mapped pinned memory the finishing kernels write into */
+	unsigned long long v[16];
+};
+struct Ctx {
+	int device = -1;
+	cudaStream_t stream = nullptr;
+	ResultSlot *slot_h = nullptr, *slot_d = nullptr;	/* host / device view of the same page */
+	void *scratch = nullptr;	/* small device scratch (tile state, counters) */
+	size_t scratch_bytes = 0;
+	char err[1024] = {0};
+	const char *algo = "";
+};
+Ctx *ctx();				/* lazily initialises device 0 if b200_init was not called */
+extern std::atomic<unsigned long long> g_launches;
+#define COUNT_LAUNCH() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+void set_err(const char *fmt, ...);	/* GDKerror analogue */
+bool cuda_ok(cudaError_t e, const char *what);
+#define CK(x) do { if (!cuda_ok((x), #x)) goto bailout; } while (0)
+#define CKN(x) do { if (!cuda_ok((x), #x)) return nullptr; } while (0)
+
+void *dev_alloc(size_t bytes);		/* stream-ordered pool allocation, NULL + error on failure */
+void dev_free(void *p);
+void *scratch_get(size_t bytes);	/* per-thread reusable device scratch */
+bool stream_sync();			/* sync + error check */
+
+// ---------------------------------------------------------------- BAT helpers
+b200_bat *bat_alloc_desc();
+b200_bat *bat_new(uint64_t hseq, int tt, uint64_t cap);		/* device tail, count 0 */
+b200_bat *bat_dense(uint64_t hseq, uint64_t tseq, uint64_t cnt);
+static inline bool bat_is_dense(const b200_bat *b)
+{
+	return b->ccand == B200_CAND_NONE && (b->ttype == B200_void || b->count == 0) && b->tseqbase != OID_NIL;
+}
+// make sure b is usable by a kernel on the current device: device BATs are returned
+// as is; host BATs (device == -1) are staged through the heap tier (tmp owns the copy)
+struct Staged {
+	const b200_bat *b = nullptr;
+	b200_bat *tmp = nullptr;
+	~Staged() { if (tmp) b200_BATfree(tmp); }
+};
+bool stage(const b200_bat *in, Staged &out);
+
+// ---------------------------------------------------------------- candidates
+// canditer_init (gdk_cand.c:407-712) restated for the device: after clipping to
+// b's oid range a candidate list is either dense [seq, seq+ncand) or a device
+// array of ascending oids.  Negative and mask encodings are expanded on device.
+struct Cand {
+	bool dense = true;
+	oid seq = 0;			/* first candidate oid (dense) */
+	const oid *oids = nullptr;	/* device array (non-dense) */
+	uint64_t ncand = 0;
+	oid hseq = 0;			/* b->hseqbase: row index = oid - hseq */
+	void *owned = nullptr;		/* temp expansion to free */
+	~Cand() { if (owned) dev_free(owned); }
+};
+bool cand_init(Cand &ci, const b200_bat *b, const b200_bat *s);	/* b may be NULL (no clipping) */
+// result of slicing the whole candidate iterator (canditer_slice(&ci,0,ncand), gdk_cand.c:1102)
+b200_bat *cand_to_bat(const Cand &ci);
+
+static inline unsigned grid_for(uint64_t n, unsigned per_block, unsigned max_blocks = NSM * 16)
+{
+	uint64_t g = (n + per_block - 1) / per_block;
+	if (g < 1) g = 1;
+	return (unsigned) (g > max_blocks ? max_blocks : g);
+}

@@ -1,0 +1,395 @@
+// heap.cu — runtime of the B200 GDK path: per-thread CUDA context, the
+// device-resident BAT heap tier (the tier the north star adds beside
+// HEAPalloc/HEAPfree, gdk_heap.c:141-225,626), BAT descriptor life cycle
+// (COLnew gdk_bat.c:238-298, BATdense :298, BBPreclaim gdk_bbp.c:3161), and the
+// candidate iterator set-up (canditer_init, gdk_cand.c:407-712).
+#include "common.cuh"
+#include "scan.cuh"
+#include <mutex>
+#include <stdlib.h>
+
+std::atomic<unsigned long long> g_launches{0};
+static thread_local Ctx *tl_ctx = nullptr;
+static std::mutex g_pool_mu;
+static bool g_pool_ready[64] = {false};
+
+void set_err(const char *fmt, ...)
+{
+	Ctx *c = tl_ctx;
+	va_list ap;
+	va_start(ap, fmt);
+	if (c)
+		vsnprintf(c->err, sizeof(c->err), fmt, ap);
+	else
+		vfprintf(stderr, fmt, ap);
+	va_end(ap);
+}
+
+bool cuda_ok(cudaError_t e, const char *what)
+{
+	if (e == cudaSuccess)
+		return true;
+	set_err("CUDA error %s: %s (%s)\n", cudaGetErrorName(e), cudaGetErrorString(e), what);
+	return false;
+}
+
+static Ctx *ctx_create(int device)
+{
+	Ctx *c = new Ctx();
+	tl_ctx = c;
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) {
+		snprintf(c->err, sizeof(c->err),
+			 "b200: no usable CUDA device (%s); this library has no CPU fallback\n",
+			 e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+		c->device = -1;
+		return c;
+	}
+	if (device < 0 || device >= n) {
+		snprintf(c->err, sizeof(c->err), "b200: invalid device %d (have %d)\n", device, n);
+		c->device = -1;
+		return c;
+	}
+	if (!cuda_ok(cudaSetDevice(device), "cudaSetDevice")) {
+		c->device = -1;
+		return c;
+	}
+	c->device = device;
+	{
+		std::lock_guard<std::mutex> lk(g_pool_mu);
+		if (!g_pool_ready[device]) {
+			cudaMemPool_t pool;
+			if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+				uint64_t thr = UINT64_MAX;	/* keep freed heaps cached in the pool */
+				cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+			}
+			g_pool_ready[device] = true;
+		}
+	}
+	if (!cuda_ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream create") ||
+	    !cuda_ok(cudaHostAlloc((void **) &c->slot_h, sizeof(ResultSlot), cudaHostAllocMapped), "slot alloc") ||
+	    !cuda_ok(cudaHostGetDevicePointer((void **) &c->slot_d, c->slot_h, 0), "slot map")) {
+		c->device = -1;
+		return c;
+	}
+	memset(c->slot_h, 0, sizeof(ResultSlot));
+	return c;
+}
+
+Ctx *ctx()
+{
+	if (tl_ctx == nullptr)
+		ctx_create(0);
+	return tl_ctx;
+}
+
+static bool ctx_usable()
+{
+	Ctx *c = ctx();
+	if (c->device < 0) {
+		if (c->err[0] == 0)
+			snprintf(c->err, sizeof(c->err), "b200: no usable CUDA device; this library has no CPU fallback\n");
+		return false;
+	}
+	return true;
+}
+
+void *dev_alloc(size_t bytes)
+{
+	if (!ctx_usable())
+		return nullptr;
+	void *p = nullptr;
+	if (bytes == 0)
+		bytes = 16;
+	if (!cuda_ok(cudaMallocAsync(&p, bytes, ctx()->stream), "device heap alloc"))
+		return nullptr;
+	return p;
+}
+
+void dev_free(void *p)
+{
+	if (p && tl_ctx && tl_ctx->device >= 0)
+		cudaFreeAsync(p, tl_ctx->stream);
+}
+
+void *scratch_get(size_t bytes)
+{
+	Ctx *c = ctx();
+	if (c->device < 0)
+		return nullptr;
+	if (bytes > c->scratch_bytes) {
+		if (c->scratch)
+			cudaFreeAsync(c->scratch, c->stream);
+		size_t nb = bytes < (1u << 20) ? (1u << 20) : bytes * 2;
+		c->scratch = nullptr;
+		c->scratch_bytes = 0;
+		if (!cuda_ok(cudaMallocAsync(&c->scratch, nb, c->stream), "scratch alloc"))
+			return nullptr;
+		c->scratch_bytes = nb;
+	}
+	return c->scratch;
+}
+
+bool stream_sync()
+{
+	return cuda_ok(cudaStreamSynchronize(ctx()->stream), "stream sync");
+}
+
+// ---------------------------------------------------------------- C-ABI: runtime
+extern "C" int b200_init(int device)
+{
+	if (tl_ctx != nullptr && tl_ctx->device == device)
+		return 0;
+	if (tl_ctx != nullptr && tl_ctx->device >= 0) {
+		cudaSetDevice(tl_ctx->device);
+		cudaStreamSynchronize(tl_ctx->stream);
+	}
+	Ctx *c = ctx_create(device);
+	return c->device >= 0 ? 0 : -1;
+}
+
+extern "C" int b200_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess)
+		return 0;
+	return n;
+}
+
+extern "C" const char *b200_errbuf(void) { return tl_ctx ? tl_ctx->err : ""; }
+extern "C" void b200_clrerr(void) { if (tl_ctx) tl_ctx->err[0] = 0; }
+extern "C" const char *b200_algorithm(void) { return tl_ctx ? tl_ctx->algo : ""; }
+extern "C" uint64_t b200_kernel_launches(void) { return g_launches.load(); }
+extern "C" void b200_sync(void) { if (tl_ctx && tl_ctx->device >= 0) cudaStreamSynchronize(tl_ctx->stream); }
+extern "C" void *b200_stream(void) { return ctx()->stream; }
+
+extern "C" void *b200_pinned_alloc(size_t bytes)
+{
+	if (!ctx_usable())
+		return nullptr;
+	void *p = nullptr;
+	if (!cuda_ok(cudaHostAlloc(&p, bytes ? bytes : 16, cudaHostAllocDefault), "pinned alloc"))
+		return nullptr;
+	return p;
+}
+extern "C" void b200_pinned_free(void *p) { if (p) cudaFreeHost(p); }
+
+// ---------------------------------------------------------------- descriptors
+b200_bat *bat_alloc_desc()
+{
+	b200_bat *b = (b200_bat *) calloc(1, sizeof(b200_bat));
+	if (b == nullptr) {
+		set_err("b200: out of host memory for a BAT descriptor\n");
+		return nullptr;
+	}
+	b->tseqbase = OID_NIL;
+	b->device = tl_ctx ? tl_ctx->device : -1;
+	return b;
+}
+
+b200_bat *bat_new(uint64_t hseq, int tt, uint64_t cap)
+{
+	if (!ctx_usable())
+		return nullptr;
+	int w = atomsize(tt);
+	if (w < 0 && tt != B200_msk) {
+		set_err("b200: COLnew: unsupported tail type %d (fixed-width atoms only)\n", tt);
+		return nullptr;
+	}
+	b200_bat *b = bat_alloc_desc();
+	if (b == nullptr)
+		return nullptr;
+	b->ttype = tt;
+	b->hseqbase = hseq;
+	b->capacity = cap;
+	b->owns = 1;
+	if (tt == B200_void) {
+		b->tseqbase = 0;
+		b->tsorted = b->tkey = b->tnonil = 1;
+		return b;
+	}
+	size_t bytes = tt == B200_msk ? ((cap + 31) / 32) * 4 : (size_t) cap * w;
+	b->base = dev_alloc(bytes);
+	if (b->base == nullptr) {
+		free(b);
+		return nullptr;
+	}
+	/* an empty BAT is trivially sorted/key (BATsetcount, gdk_bat.c:2066) */
+	b->tsorted = b->trevsorted = b->tkey = b->tnonil = 1;
+	return b;
+}
+
+b200_bat *bat_dense(uint64_t hseq, uint64_t tseq, uint64_t cnt)
+{
+	if (!ctx_usable())
+		return nullptr;
+	b200_bat *b = bat_alloc_desc();
+	if (b == nullptr)
+		return nullptr;
+	b->ttype = B200_void;
+	b->hseqbase = hseq;
+	b->tseqbase = tseq;
+	b->count = cnt;
+	b->tsorted = b->tkey = b->tnonil = 1;
+	b->trevsorted = cnt <= 1;
+	b->owns = 1;
+	b->oidrange_known = cnt > 0;
+	b->first_oid = tseq;
+	b->last_oid = tseq + cnt - 1;
+	return b;
+}
+
+extern "C" b200_bat *b200_COLnew(uint64_t hseq, int tt, uint64_t cap) { b200_clrerr(); return bat_new(hseq, tt, cap); }
+extern "C" b200_bat *b200_BATdense(uint64_t hseq, uint64_t tseq, uint64_t cnt) { b200_clrerr(); return bat_dense(hseq, tseq, cnt); }
+
+extern "C" b200_bat *b200_BATfromhost(const void *src, int tt, uint64_t cnt, uint64_t hseq)
+{
+	b200_clrerr();
+	b200_bat *b = bat_new(hseq, tt, cnt);
+	if (b == nullptr)
+		return nullptr;
+	size_t bytes = tt == B200_msk ? ((cnt + 31) / 32) * 4 : (size_t) cnt * atomsize(tt);
+	if (bytes && !cuda_ok(cudaMemcpyAsync(b->base, src, bytes, cudaMemcpyHostToDevice, ctx()->stream), "upload")) {
+		b200_BATfree(b);
+		return nullptr;
+	}
+	b->count = cnt;
+	b->tsorted = b->trevsorted = b->tkey = cnt <= 1;
+	b->tnonil = cnt == 0;
+	b->tnil = 0;
+	if (basetype(tt) == B200_lng && tt == B200_oid && cnt > 0) {
+		/* callers that upload candidate lists tell us sortedness via BATsetprops */
+	}
+	/* the source buffer may be pageable: be done with it before returning */
+	if (!stream_sync()) {
+		b200_BATfree(b);
+		return nullptr;
+	}
+	return b;
+}
+
+extern "C" b200_bat *b200_BATwrap(void *devptr, int tt, uint64_t cnt, uint64_t hseq)
+{
+	b200_clrerr();
+	if (!ctx_usable())
+		return nullptr;
+	b200_bat *b = bat_alloc_desc();
+	if (b == nullptr)
+		return nullptr;
+	b->ttype = tt;
+	b->hseqbase = hseq;
+	b->count = b->capacity = cnt;
+	b->base = devptr;
+	b->owns = 0;
+	b->tsorted = b->trevsorted = b->tkey = cnt <= 1;
+	b->tnonil = cnt == 0;
+	return b;
+}
+
+extern "C" void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil)
+{
+	b->tsorted = sorted || b->count <= 1;
+	b->trevsorted = revsorted || b->count <= 1;
+	b->tkey = key || b->count <= 1;
+	b->tnonil = nonil;
+	b->tnil = nil;
+}
+
+extern "C" void b200_BATfree(b200_bat *b)
+{
+	if (b == nullptr)
+		return;
+	if (b->owns) {
+		if (b->device >= 0) {
+			if (tl_ctx && tl_ctx->device == b->device) {
+				dev_free(b->base);
+				dev_free(b->vheap);
+			} else {
+				/* freed from another thread/device context: synchronous path */
+				int cur = -1;
+				cudaGetDevice(&cur);
+				cudaSetDevice(b->device);
+				if (b->base) cudaFree(b->base);
+				if (b->vheap) cudaFree(b->vheap);
+				if (cur >= 0) cudaSetDevice(cur);
+			}
+		} else {
+			free(b->base);
+			free(b->vheap);
+		}
+	}
+	free(b);
+}
+
+extern "C" b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc)
+{
+	b200_clrerr();
+	/* BATnegcands (gdk_cand.c:1296): only exceptions inside [seq, seq+cnt) count */
+	uint64_t lo = 0, hi = nexc;
+	while (lo < nexc && exceptions[lo] < seq) lo++;
+	hi = lo;
+	while (hi < nexc && exceptions[hi] < seq + cnt) hi++;
+	b200_bat *b = bat_dense(0, seq, cnt);
+	if (b == nullptr || lo == hi)
+		return b;
+	if (hi - lo == cnt) {
+		b->count = 0;
+		return b;
+	}
+	b->vheap = dev_alloc((hi - lo) * sizeof(oid));
+	if (b->vheap == nullptr ||
+	    !cuda_ok(cudaMemcpyAsync(b->vheap, exceptions + lo, (hi - lo) * sizeof(oid), cudaMemcpyHostToDevice, ctx()->stream), "upload") ||
+	    !stream_sync()) {
+		b200_BATfree(b);
+		return nullptr;
+	}
+	b->ccand = B200_CAND_NEGOID;
+	b->nvheap = hi - lo;
+	b->count = cnt - (hi - lo);
+	b->oidrange_known = 0;
+	return b;
+}
+
+extern "C" b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows, const uint32_t *words, bool selected)
+{
+	b200_clrerr();
+	/* BATmaskedcands (gdk_cand.c:1366) for a mask of exactly nrows bits */
+	uint64_t nmask = (nrows + 31) / 32;
+	uint32_t *w = (uint32_t *) malloc(nmask * 4 + 4);
+	if (w == nullptr) {
+		set_err("b200: out of host memory\n");
+		return nullptr;
+	}
+	for (uint64_t i = 0; i < nmask; i++)
+		w[i] = selected ? words[i] : ~words[i];
+	if (nrows % 32)
+		w[nmask - 1] &= (1U << (nrows % 32)) - 1;
+	uint64_t cnt = 0, firstbit = 0;
+	for (uint64_t i = 0; i < nmask; i++) {
+		if (cnt == 0 && w[i] != 0)
+			firstbit = __builtin_ctz(w[i]) + i * 32;
+		cnt += __builtin_popcount(w[i]);
+	}
+	b200_bat *b = bat_dense(hseq, hseq, 0);
+	if (b == nullptr || cnt == 0) {
+		free(w);
+		return b;
+	}
+	b->vheap = dev_alloc(nmask * 4);
+	if (b->vheap == nullptr ||
+	    !cuda_ok(cudaMemcpyAsync(b->vheap, w, nmask * 4, cudaMemcpyHostToDevice, ctx()->stream), "upload") ||
+	    !stream_sync()) {
+		free(w);
+		b200_BATfree(b);
+		return nullptr;
+	}
+	free(w);
+	b->ccand = B200_CAND_MSK;
+	b->nvheap = nmask;
+	b->firstbit = (uint32_t) firstbit;
+	b->tseqbase = hseq + firstbit;
+	b->count = cnt;
+	b->oidrange_known = 0;
+	return b;
+}

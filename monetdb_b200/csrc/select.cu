@@ -1,0 +1,502 @@
+// select.cu — BATselect / BATthetaselect on the device.
+//
+// Host side: the reference's argument normalisation, verbatim in meaning
+// (gdk_select.c:1342-1560: lval/hval/lnil/equi/anti handling, anti-range swap,
+// the empty / everything shortcuts; scanfunc's closed-range normalisation
+// :300-446).  Device side: ONE streaming pass over the column (or a gather
+// through a materialised candidate list) evaluating the closed-range predicate,
+// with warp-scan + decoupled look-back compaction so the oids come out ascending,
+// exactly as scanloop's `dst[cnt] = o; cnt += TEST` (:239-245) produces them.
+// The result is virtualised to a dense void BAT when the hits are contiguous
+// (virtualize, :31-89).
+#include "common.cuh"
+#include "compact.cuh"
+
+// closed-range predicate after normalisation:
+//   nil(v) ? nilres : (anti ? (v <= vl || v >= vh) : (v >= vl && v <= vh))
+template <typename T> struct RangePred {
+	T vl, vh;
+	bool anti, nilres;
+	__device__ __forceinline__ bool operator()(T v) const
+	{
+		if (Atom<T>::is_nil(v))
+			return nilres;
+		return anti ? (v <= vl || v >= vh) : (v >= vl && v <= vh);
+	}
+};
+
+// ---------------------------------------------------------------- dense scan kernel
+// Tile = 256 threads x NV 16-byte vectors; warp w owns a contiguous slab of the
+// tile so each load instruction of a warp covers 512 contiguous bytes.
+template <typename T> struct DenseCfg {
+	static constexpr int VEC = 16 / sizeof(T);				/* values per 128-bit load */
+	static constexpr int NV = (sizeof(T) == 1) ? 1 : (sizeof(T) == 2 ? 2 : 4);	/* loads per thread */
+	static constexpr int TILE = CP_THREADS * NV * VEC;			/* rows per tile: 4096/4096/4096/2048/1024 */
+};
+
+template <typename T>
+__global__ void __launch_bounds__(CP_THREADS)
+select_dense_kernel(const T *__restrict__ src,	/* 16-byte aligned; row r of the scan = src[r] */
+		    uint64_t skip,		/* leading rows before the first candidate (alignment padding) */
+		    uint64_t n,			/* rows to scan including skip */
+		    oid seq,			/* oid of src[0] */
+		    RangePred<T> pred, oid *__restrict__ dst, TileScan ts, unsigned ntiles,
+		    unsigned long long *total_out)
+{
+	constexpr int VEC = DenseCfg<T>::VEC, NV = DenseCfg<T>::NV, TILE = DenseCfg<T>::TILE;
+	__shared__ oid stage[TILE];
+	__shared__ unsigned wtot[CP_THREADS / 32];
+	__shared__ unsigned long long slot;
+	__shared__ unsigned tslot;
+	const unsigned tile = tile_ticket(ts, &tslot);
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t wbase = (uint64_t) tile * TILE + (uint64_t) warp * (32 * NV * VEC);
+	unsigned masks[NV];
+#pragma unroll
+	for (int j = 0; j < NV; j++) {
+		const uint64_t r0 = wbase + (uint64_t) (j * 32 + lane) * VEC;
+		unsigned m = 0;
+		if (r0 + VEC <= n) {
+			union { int4 q; T v[VEC]; } u;
+			u.q = __ldcs(reinterpret_cast<const int4 *>(src + r0));
+#pragma unroll
+			for (int e = 0; e < VEC; e++)
+				m |= (unsigned) pred(u.v[e]) << e;
+			if (r0 < skip) {
+#pragma unroll
+				for (int e = 0; e < VEC; e++)
+					if (r0 + e < skip)
+						m &= ~(1u << e);
+			}
+		} else {
+			for (int e = 0; e < VEC; e++)
+				if (r0 + e < n && r0 + e >= skip)
+					m |= (unsigned) pred(src[r0 + e]) << e;
+		}
+		masks[j] = m;
+	}
+	/* rank of each thread's hits inside the warp, order = (j, lane, e) */
+	unsigned excl[NV];
+	unsigned wcount = 0;
+#pragma unroll
+	for (int j = 0; j < NV; j++) {
+		unsigned c = __popc(masks[j]);
+		unsigned inc = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+			if (lane >= o)
+				inc += t;
+		}
+		excl[j] = wcount + inc - c;
+		wcount += __shfl_sync(0xffffffffu, inc, 31);
+	}
+	if (lane == 0)
+		wtot[warp] = wcount;
+	__syncthreads();
+	unsigned wexcl = 0, ttot = 0;
+#pragma unroll
+	for (int w = 0; w < CP_THREADS / 32; w++) {
+		unsigned t = wtot[w];
+		wexcl += w < warp ? t : 0;
+		ttot += t;
+	}
+	unsigned long long gexcl = tile_exclusive_prefix(ts, tile, ttot, &slot);
+#pragma unroll
+	for (int j = 0; j < NV; j++) {
+		unsigned m = masks[j];
+		unsigned pos = wexcl + excl[j];
+		const oid o0 = seq + wbase + (uint64_t) (j * 32 + lane) * VEC;
+		while (m) {
+			int e = __ffs(m) - 1;
+			m &= m - 1;
+			stage[pos++] = o0 + e;
+		}
+	}
+	__syncthreads();
+	for (unsigned i = threadIdx.x; i < ttot; i += CP_THREADS)
+		dst[gexcl + i] = stage[i];
+	if (tile == ntiles - 1 && threadIdx.x == 0)
+		*total_out = gexcl + ttot;
+}
+
+template <typename T>
+static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, oid seq, RangePred<T> pred, oid *dst, CompactResult &res)
+{
+	Ctx *c = ctx();
+	const T *p = col + first_row;
+	uint64_t skip = ((uintptr_t) p & 15) / sizeof(T);
+	p -= skip;
+	uint64_t n = ncand + skip;
+	constexpr int TILE = DenseCfg<T>::TILE;
+	uint64_t ntiles = (n + TILE - 1) / TILE;
+	char *sp = (char *) scratch_get(16 + tilescan_bytes(ntiles));
+	if (sp == nullptr)
+		return false;
+	if (!cuda_ok(cudaMemsetAsync(sp, 0, 16 + tilescan_bytes(ntiles), c->stream), "memset tile state"))
+		return false;
+	unsigned long long *total = (unsigned long long *) sp;
+	TileScan ts;
+	ts.ticket = (unsigned int *) (sp + 16);
+	ts.status = (unsigned long long *) (sp + 32);
+	select_dense_kernel<T><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(p, skip, n, seq - skip, pred, dst, ts, (unsigned) ntiles, total);
+	COUNT_LAUNCH();
+	compact_finish_kernel<<<1, 1, 0, c->stream>>>(dst, total, c->slot_d->v);
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaGetLastError(), "select launch") || !stream_sync())
+		return false;
+	res.count = c->slot_h->v[0];
+	res.first = c->slot_h->v[1];
+	res.last = c->slot_h->v[2];
+	return true;
+}
+
+// ---------------------------------------------------------------- candidate-list scan
+template <typename T> struct GatherPredF {
+	const T *col;		/* col[o - hseq] */
+	const oid *cand;
+	oid hseq;
+	RangePred<T> pred;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &o) const
+	{
+		o = __ldcs(cand + idx);
+		return pred(col[o - hseq]);
+	}
+};
+
+// ---------------------------------------------------------------- typed driver
+struct SelArgs {
+	const b200_bat *b;
+	const Cand *ci;
+	const void *tl, *th;
+	bool li, hi, equi, anti, nil_matches, lval, hval, lnil;
+};
+
+// returns false on error; on success *out is the result (possibly empty dense)
+template <typename T>
+static bool select_typed(const SelArgs &a, b200_bat **out)
+{
+	/* scanfunc normalisation to closed ranges, gdk_select.c:300-446 */
+	T vl = *(const T *) a.tl, vh = *(const T *) a.th;
+	bool li = a.li, hi = a.hi, lval = a.lval, hval = a.hval, anti = a.anti;
+	const T minval = Atom<T>::minval(), maxval = Atom<T>::maxval();
+	const bool nonil = a.b->tnonil;
+	if (anti && li) {
+		if (vl == minval) {
+			anti = false;
+			vl = vh;
+			li = !hi;
+			hval = false;
+		} else {
+			vl = Atom<T>::prev(vl);
+			li = false;
+		}
+	}
+	if (anti && hi) {
+		if (vh == maxval) {
+			anti = false;
+			vh = vl;
+			hi = !li;
+			lval = false;
+		} else {
+			vh = Atom<T>::next(vh);
+			hi = false;
+		}
+	}
+	if (!anti) {
+		if (lval) {
+			if (!li) {
+				if (vl == maxval) { *out = bat_dense(0, 0, 0); return *out != nullptr; }
+				vl = Atom<T>::next(vl);
+				li = true;
+			}
+		} else {
+			vl = minval;
+			li = true;
+			lval = true;
+		}
+		if (hval) {
+			if (!hi) {
+				if (vh == minval) { *out = bat_dense(0, 0, 0); return *out != nullptr; }
+				vh = Atom<T>::prev(vh);
+				hi = true;
+			}
+		} else {
+			vh = maxval;
+			hi = true;
+			hval = true;
+		}
+		if (vl > vh) { *out = bat_dense(0, 0, 0); return *out != nullptr; }
+	}
+	RangePred<T> pred;
+	const char *algo;
+	if (a.equi) {
+		if (a.lnil) {
+			/* is_nil(v): empty range for non-nil values, nil matches */
+			pred.vl = maxval; pred.vh = minval; pred.anti = false; pred.nilres = true;
+			algo = "select: cuda scan is_nil(v)";
+		} else {
+			pred.vl = vl; pred.vh = vl; pred.anti = false; pred.nilres = false;
+			algo = "select: cuda scan v == vl";
+		}
+	} else if (anti) {
+		pred.vl = vl; pred.vh = vh; pred.anti = true;
+		pred.nilres = !nonil && a.nil_matches;
+		algo = "select: cuda scan (v <= vl || v >= vh)";
+	} else if (nonil && vl == minval) {
+		/* v <= vh (also accepts -inf for floating point, as the reference's test does) */
+		pred.vl = Atom<T>::is_float ? (T) -INFINITY : vl; pred.vh = vh; pred.anti = false; pred.nilres = false;
+		algo = "select: cuda scan v <= vh";
+	} else if (vh == maxval) {
+		/* v >= vl (also accepts +inf for floating point) */
+		pred.vl = vl; pred.vh = Atom<T>::is_float ? (T) INFINITY : vh; pred.anti = false; pred.nilres = false;
+		algo = "select: cuda scan v >= vl";
+	} else {
+		pred.vl = vl; pred.vh = vh; pred.anti = false; pred.nilres = false;
+		algo = "select: cuda scan v >= vl && v <= vh";
+	}
+	ctx()->algo = algo;
+	const Cand &ci = *a.ci;
+	oid *dst = (oid *) dev_alloc(ci.ncand * sizeof(oid));
+	if (dst == nullptr)
+		return false;
+	CompactResult r;
+	bool ok;
+	if (ci.dense) {
+		ok = run_select_dense<T>((const T *) a.b->base, ci.seq - ci.hseq, ci.ncand, ci.seq, pred, dst, r);
+	} else {
+		GatherPredF<T> f{(const T *) a.b->base, ci.oids, ci.hseq, pred};
+		ok = run_compact<8>(ci.ncand, f, dst, r);
+	}
+	if (!ok) {
+		dev_free(dst);
+		return false;
+	}
+	*out = oidlist_to_bat(dst, ci.ncand, r);
+	return *out != nullptr;
+}
+
+template <typename T> static int cmp_typed(const void *a, const void *b)
+{
+	/* ATOMcmp: nil is smaller than everything, nil == nil */
+	T x = *(const T *) a, y = *(const T *) b;
+	bool xn = Atom<T>::is_nil(x), yn = Atom<T>::is_nil(y);
+	if (xn || yn)
+		return xn && yn ? 0 : (xn ? -1 : 1);
+	return x < y ? -1 : (x > y ? 1 : 0);
+}
+static int atomcmp(int t, const void *a, const void *b)
+{
+	switch (t) {
+	case B200_bte: return cmp_typed<bte>(a, b);
+	case B200_sht: return cmp_typed<sht>(a, b);
+	case B200_int: return cmp_typed<int>(a, b);
+	case B200_lng: return cmp_typed<lng>(a, b);
+	case B200_hge: return cmp_typed<hge>(a, b);
+	case B200_flt: return cmp_typed<flt>(a, b);
+	case B200_dbl: return cmp_typed<dbl>(a, b);
+	}
+	return 0;
+}
+static const void *nilptr(int t)
+{
+	static const bte nb = Atom<bte>::nil();
+	static const sht ns = Atom<sht>::nil();
+	static const int ni = Atom<int>::nil();
+	static const lng nl = Atom<lng>::nil();
+	static const hge nh = Atom<hge>::nil();
+	static const flt nf = NAN;
+	static const dbl nd = NAN;
+	switch (t) {
+	case B200_bte: return &nb;
+	case B200_sht: return &ns;
+	case B200_int: return &ni;
+	case B200_lng: return &nl;
+	case B200_hge: return &nh;
+	case B200_flt: return &nf;
+	case B200_dbl: return &nd;
+	}
+	return nullptr;
+}
+
+static b200_bat *select_impl(const b200_bat *b, const b200_bat *s, const void *tl, const void *th,
+			     bool li, bool hi, bool anti, bool nil_matches)
+{
+	if (b == nullptr) {
+		set_err("BATselect: BAT required\n");
+		return nullptr;
+	}
+	if (tl == nullptr) {
+		set_err("BATselect: tl value required\n");
+		return nullptr;
+	}
+	if (s && s->ttype != B200_msk && !s->tsorted && s->ccand == B200_CAND_NONE && s->ttype != B200_void) {
+		set_err("BATselect: invalid argument: s must be sorted.\n");
+		return nullptr;
+	}
+	Staged sb, ss;
+	if (!stage(b, sb) || !stage(s, ss))
+		return nullptr;
+	b = sb.b;
+	s = ss.b;
+	Cand ci;
+	if (!cand_init(ci, b, s))
+		return nullptr;
+	if (ci.ncand == 0) {
+		ctx()->algo = "select: trivially empty";
+		return bat_dense(0, 0, 0);
+	}
+	int t = basetype(b->ttype);
+	if (b->ttype == B200_void) {
+		set_err("BATselect: void/dense tail columns are not on the device path\n");
+		return nullptr;
+	}
+	const void *nil = nilptr(t);
+	if (nil == nullptr) {
+		set_err("BATselect: unsupported tail type %s (fixed-width atoms only)\n", atomname(b->ttype));
+		return nullptr;
+	}
+	/* gdk_select.c:1394-1409 */
+	bool lnil = atomcmp(t, tl, nil) == 0;
+	bool lval = !lnil || th == nullptr;
+	bool equi = th == nullptr || (lval && atomcmp(t, tl, th) == 0);
+	bool hval;
+	if (lnil && nil_matches && (th == nullptr || atomcmp(t, th, nil) == 0)) {
+		equi = true;
+		lval = true;
+	}
+	if (equi) {
+		if (th == nullptr)
+			hi = li;
+		th = tl;
+		hval = true;
+		if (!anti && (!li || !hi)) {
+			ctx()->algo = "select: empty interval";
+			return bat_dense(0, 0, 0);
+		}
+	} else {
+		nil_matches = false;
+		hval = atomcmp(t, th, nil) != 0;
+	}
+	bool notnil_select = false;	/* "everything except nil" (:1480-1514) */
+	if (anti) {
+		if (lval != hval) {
+			/* one end point is nil: swap sub-ranges (:1443-1465) */
+			const void *tv = tl;
+			bool ti = li;
+			li = !hi;
+			hi = !ti;
+			tl = th;
+			th = tv;
+			ti = lval;
+			lval = hval;
+			hval = ti;
+			lnil = atomcmp(t, tl, nil) == 0;
+			anti = false;
+		} else if (!lval && !hval) {
+			ctx()->algo = "select: anti: nil-nil range, nonil";
+			return bat_dense(0, 0, 0);
+		} else if ((equi && (lnil || !(li && hi))) || atomcmp(t, tl, th) > 0) {
+			if (equi && !lnil && nil_matches && !(li && hi)) {
+				ctx()->algo = "select: anti, equi, open, nil_matches";
+				return cand_to_bat(ci);
+			}
+			notnil_select = true;
+		} else {
+			/* antiequi handled by the anti predicate below */
+			equi = false;
+		}
+	}
+	if (!notnil_select) {
+		if (hval && (equi ? !li || !hi : atomcmp(t, tl, th) > 0)) {
+			ctx()->algo = "select: empty range";
+			return bat_dense(0, 0, 0);
+		}
+		if (equi && lnil && b->tnonil) {
+			ctx()->algo = "select: equi-nil, nonil";
+			return bat_dense(0, 0, 0);
+		}
+		if (!equi && !lval && !hval && lnil && b->tnonil) {
+			ctx()->algo = "select: everything, nonil";
+			return cand_to_bat(ci);
+		}
+	} else if (b->tnonil) {
+		ctx()->algo = "select: everything, nonil";
+		return cand_to_bat(ci);
+	}
+	SelArgs a;
+	a.b = b;
+	a.ci = &ci;
+	if (notnil_select) {
+		/* x != nil  ==  nil-nil range, non-anti (:1296 of the table) */
+		a.tl = nil; a.th = nil; a.li = a.hi = true;
+		a.equi = false; a.anti = false; a.nil_matches = false;
+		a.lval = a.hval = false; a.lnil = true;
+	} else {
+		a.tl = tl; a.th = th; a.li = li; a.hi = hi;
+		a.equi = equi; a.anti = anti; a.nil_matches = nil_matches;
+		a.lval = lval; a.hval = hval; a.lnil = lnil;
+	}
+	b200_bat *bn = nullptr;
+	bool ok = false;
+	switch (t) {
+	case B200_bte: ok = select_typed<bte>(a, &bn); break;
+	case B200_sht: ok = select_typed<sht>(a, &bn); break;
+	case B200_int: ok = select_typed<int>(a, &bn); break;
+	case B200_lng: ok = select_typed<lng>(a, &bn); break;
+	case B200_hge: ok = select_typed<hge>(a, &bn); break;
+	case B200_flt: ok = select_typed<flt>(a, &bn); break;
+	case B200_dbl: ok = select_typed<dbl>(a, &bn); break;
+	}
+	return ok ? bn : nullptr;
+}
+
+extern "C" b200_bat *b200_BATselect(const b200_bat *b, const b200_bat *s, const void *tl, const void *th,
+				    bool li, bool hi, bool anti, bool nil_matches)
+{
+	b200_clrerr();
+	return select_impl(b, s, tl, th, li, hi, anti, nil_matches);
+}
+
+// gdk_select.c:2102-2154
+extern "C" b200_bat *b200_BATthetaselect(const b200_bat *b, const b200_bat *s, const void *val, const char *op)
+{
+	b200_clrerr();
+	if (b == nullptr || val == nullptr || op == nullptr) {
+		set_err("BATthetaselect: BAT, value and operator required\n");
+		return nullptr;
+	}
+	int t = basetype(b->ttype);
+	const void *nil = nilptr(t);
+	if (nil == nullptr) {
+		set_err("BATthetaselect: unsupported tail type %s\n", atomname(b->ttype));
+		return nullptr;
+	}
+	/* eq/ne can be used for "is" nil-handling */
+	if (strcmp(op, "eq") == 0)
+		return select_impl(b, s, val, nullptr, true, true, false, true);
+	if (strcmp(op, "ne") == 0)
+		return select_impl(b, s, val, nullptr, true, true, true, true);
+	if (atomcmp(t, val, nil) == 0)
+		return bat_dense(0, 0, 0);
+	if (op[0] == '=' && ((op[1] == '=' && op[2] == 0) || op[1] == 0))
+		return select_impl(b, s, val, nullptr, true, true, false, false);
+	if (op[0] == '!' && op[1] == '=' && op[2] == 0)
+		return select_impl(b, s, val, nullptr, true, true, true, false);
+	if (op[0] == '<') {
+		if (op[1] == 0)
+			return select_impl(b, s, nil, val, false, false, false, false);
+		if (op[1] == '=' && op[2] == 0)
+			return select_impl(b, s, nil, val, false, true, false, false);
+		if (op[1] == '>' && op[2] == 0)
+			return select_impl(b, s, val, nullptr, true, true, true, false);
+	}
+	if (op[0] == '>') {
+		if (op[1] == 0)
+			return select_impl(b, s, val, nil, false, false, false, false);
+		if (op[1] == '=' && op[2] == 0)
+			return select_impl(b, s, val, nil, true, false, false, false);
+	}
+	set_err("BATthetaselect: unknown operator.\n");
+	return nullptr;
+}
