@@ -24,7 +24,7 @@ LIB = PKG / "libgdk_b200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-lineinfo", "-O3", "-std=c++17",
+    "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
     "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
     "--expt-relaxed-constexpr",
     "-I", str(ROOT / "include"),

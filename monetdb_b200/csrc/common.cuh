@@ -120,6 +120,9 @@ bool stream_sync();			/* sync + error check */
 b200_bat *bat_alloc_desc();
 b200_bat *bat_new(uint64_t hseq, int tt, uint64_t cap);		/* device tail, count 0 */
 b200_bat *bat_dense(uint64_t hseq, uint64_t tseq, uint64_t cnt);
+/* BATconstant (gdk_batop.c): n copies of *val (NULL = the type's nil); oid nil -> void */
+b200_bat *bat_constant(uint64_t hseq, int tt, const void *val, uint64_t n);
+void atom_nil_bits(int t, void *out);	/* nil bit pattern of a storage type */
 static inline bool bat_is_dense(const b200_bat *b)
 {
 	return b->ccand == B200_CAND_NONE && (b->ttype == B200_void || b->count == 0) && b->tseqbase != OID_NIL;
@@ -156,3 +159,36 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block, unsigned max_blo
 	if (g < 1) g = 1;
 	return (unsigned) (g > max_blocks ? max_blocks : g);
 }
+
+// streaming (evict-first) load of any fixed-width atom
+#ifdef __CUDACC__
+template <typename T> __device__ __forceinline__ T ld_stream(const T *p)
+{
+	if constexpr (sizeof(T) == 16) {
+		ulonglong2 q = __ldcs(reinterpret_cast<const ulonglong2 *>(p));
+		union { ulonglong2 q; T t; } u;
+		u.q = q;
+		return u.t;
+	} else if constexpr (sizeof(T) == 8) {
+		unsigned long long q = __ldcs(reinterpret_cast<const unsigned long long *>(p));
+		union { unsigned long long q; T t; } u;
+		u.q = q;
+		return u.t;
+	} else if constexpr (sizeof(T) == 4) {
+		unsigned q = __ldcs(reinterpret_cast<const unsigned *>(p));
+		union { unsigned q; T t; } u;
+		u.q = q;
+		return u.t;
+	} else if constexpr (sizeof(T) == 2) {
+		unsigned short q = __ldcs(reinterpret_cast<const unsigned short *>(p));
+		union { unsigned short q; T t; } u;
+		u.q = q;
+		return u.t;
+	} else {
+		unsigned char q = __ldcs(reinterpret_cast<const unsigned char *>(p));
+		union { unsigned char q; T t; } u;
+		u.q = q;
+		return u.t;
+	}
+}
+#endif

@@ -393,3 +393,72 @@ extern "C" b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows,
 	b->oidrange_known = 0;
 	return b;
 }
+
+// ---------------------------------------------------------------- BATconstant
+void atom_nil_bits(int t, void *out)
+{
+	switch (basetype(t)) {
+	case B200_bte: { bte v = Atom<bte>::nil(); memcpy(out, &v, 1); break; }
+	case B200_sht: { sht v = Atom<sht>::nil(); memcpy(out, &v, 2); break; }
+	case B200_int: { int v = Atom<int>::nil(); memcpy(out, &v, 4); break; }
+	case B200_lng: { lng v = Atom<lng>::nil(); memcpy(out, &v, 8); break; }
+	case B200_hge: { hge v = Atom<hge>::nil(); memcpy(out, &v, 16); break; }
+	case B200_flt: { flt v = NAN; memcpy(out, &v, 4); break; }
+	case B200_dbl: { dbl v = NAN; memcpy(out, &v, 8); break; }
+	}
+}
+
+__global__ void fill16_kernel(uint4 *dst, uint64_t n16, uint4 v)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t) gridDim.x * blockDim.x)
+		dst[i] = v;
+}
+
+b200_bat *bat_constant(uint64_t hseq, int tt, const void *val, uint64_t n)
+{
+	unsigned char pat[16];
+	int w = atomsize(tt == B200_void ? B200_oid : tt);
+	if (w <= 0) {
+		set_err("b200: BATconstant: unsupported type %d\n", tt);
+		return nullptr;
+	}
+	if (val)
+		memcpy(pat, val, w);
+	else
+		atom_nil_bits(tt == B200_void ? B200_oid : tt, pat);
+	unsigned char nilpat[16];
+	atom_nil_bits(tt == B200_void ? B200_oid : tt, nilpat);
+	bool isnil = memcmp(pat, nilpat, w) == 0;
+	if (tt == B200_flt) { flt f; memcpy(&f, pat, 4); isnil = f != f; }
+	if (tt == B200_dbl) { dbl d; memcpy(&d, pat, 8); isnil = d != d; }
+	if ((tt == B200_oid || tt == B200_void) && (n == 0 || isnil)) {
+		b200_bat *bn = bat_dense(hseq, n ? OID_NIL : 0, n);
+		if (bn && n) {
+			bn->tnonil = 0;
+			bn->tnil = 1;
+			bn->tkey = n <= 1;
+			bn->trevsorted = 1;
+			bn->oidrange_known = 0;
+		}
+		return bn;
+	}
+	b200_bat *bn = bat_new(hseq, tt, n);
+	if (bn == nullptr)
+		return nullptr;
+	for (int i = w; i < 16; i++)
+		pat[i] = pat[i % w];
+	uint4 v;
+	memcpy(&v, pat, 16);
+	uint64_t n16 = ((uint64_t) n * w + 15) / 16;
+	/* the pool hands out >= 16-byte granules, so rounding the fill up is safe */
+	if (n16) {
+		fill16_kernel<<<grid_for(n16, 256), 256, 0, ctx()->stream>>>((uint4 *) bn->base, n16, v);
+		COUNT_LAUNCH();
+	}
+	bn->count = n;
+	bn->tnonil = n == 0 || !isnil;
+	bn->tnil = n > 0 && isnil;
+	bn->tsorted = bn->trevsorted = 1;
+	bn->tkey = n <= 1;
+	return bn;
+}

@@ -125,61 +125,9 @@ static void launch_project(const oid *l, uint64_t n, const ProjSrc &src, const v
 	COUNT_LAUNCH();
 }
 
-static void nil_bits(int t, void *out)
-{
-	switch (basetype(t)) {
-	case B200_bte: { bte v = Atom<bte>::nil(); memcpy(out, &v, 1); break; }
-	case B200_sht: { sht v = Atom<sht>::nil(); memcpy(out, &v, 2); break; }
-	case B200_int: { int v = Atom<int>::nil(); memcpy(out, &v, 4); break; }
-	case B200_lng: { lng v = Atom<lng>::nil(); memcpy(out, &v, 8); break; }
-	case B200_hge: { hge v = Atom<hge>::nil(); memcpy(out, &v, 16); break; }
-	case B200_flt: { flt v = NAN; memcpy(out, &v, 4); break; }
-	case B200_dbl: { dbl v = NAN; memcpy(out, &v, 8); break; }
-	}
-}
-
-__global__ void fill_kernel16(uint4 *dst, uint64_t n16, uint4 v)
-{
-	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t) gridDim.x * blockDim.x)
-		dst[i] = v;
-}
-
-// BATconstant(hseq, type, nil, n) for the trivial all-nil outcomes
 static b200_bat *constant_nil(uint64_t hseq, int tt, uint64_t n)
 {
-	if (tt == B200_oid || tt == B200_void) {
-		b200_bat *bn = bat_dense(hseq, n ? OID_NIL : 0, n);
-		if (bn && n) {
-			bn->tnonil = 0;
-			bn->tnil = 1;
-			bn->tkey = n <= 1;
-			bn->trevsorted = 1;
-			bn->oidrange_known = 0;
-		}
-		return bn;
-	}
-	b200_bat *bn = bat_new(hseq, tt, n);
-	if (bn == nullptr)
-		return nullptr;
-	int w = atomsize(tt);
-	unsigned char pat[16];
-	nil_bits(tt, pat);
-	for (int i = w; i < 16; i++)
-		pat[i] = pat[i % w];
-	uint4 v;
-	memcpy(&v, pat, 16);
-	uint64_t n16 = ((uint64_t) n * w + 15) / 16;
-	/* the pool hands out >= 16-byte granules, so rounding the fill up is safe */
-	if (n16) {
-		fill_kernel16<<<grid_for(n16, 256), 256, 0, ctx()->stream>>>((uint4 *) bn->base, n16, v);
-		COUNT_LAUNCH();
-	}
-	bn->count = n;
-	bn->tnonil = n == 0;
-	bn->tnil = n > 0;
-	bn->tsorted = bn->trevsorted = 1;
-	bn->tkey = n <= 1;
-	return bn;
+	return bat_constant(hseq, tt, nullptr, n);
 }
 
 static b200_bat *slice_view(const b200_bat *r, uint64_t lo, uint64_t hi, uint64_t hseq)
@@ -326,7 +274,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		return nullptr;
 	}
 	unsigned char nilb[16];
-	nil_bits(tpe, nilb);
+	atom_nil_bits(tpe, nilb);
 	ctx()->algo = "project: cuda gather";
 	if (src.r1void || src.r2void) {
 		project_void_kernel<<<grid_for(lcount, 256, NSM * 32), 256, 0, c->stream>>>(loids, lcount, src, (oid *) bn->base, errflag);

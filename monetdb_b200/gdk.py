@@ -1,0 +1,390 @@
+"""ctypes mirror of include/gdk_b200.h — the host side of the drop-in boundary.
+
+Function names, argument order and error behaviour follow the reference's GDK
+entry points (gdk.h:2245-2274, gdk_calc.h:36-147, gdk_analytic.h:21-42): a
+BAT-returning function that fails raises :class:`GDKError` carrying the
+reference's message text (GDKerror/GDKerrbuf, gdk.h:1710-1717).
+
+There is no CPU fallback here: if ``libgdk_b200.so`` is missing the import
+fails, and if no CUDA device is usable every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+_PKG = Path(__file__).resolve().parent
+_LIB = _PKG / "libgdk_b200.so"
+if not _LIB.exists():
+    raise ImportError(
+        f"{_LIB} not found: build it with `python -m monetdb_b200.build` "
+        "(nvcc, sm_100a). There is no CPU fallback for this package.")
+lib = C.CDLL(str(_LIB))
+
+
+class GDKError(RuntimeError):
+    """GDK_FAIL / NULL result; the message is the GDKerrbuf text."""
+
+
+# GDK type ids (gdk.h:429-451, HAVE_HGE build)
+class TYPE:
+    void, msk, bit, bte, sht, int, oid, ptr, flt, dbl, lng, hge, date, daytime, timestamp = range(15)
+
+
+oid_nil = 1 << 63
+BUN_NONE = (1 << 63) - 1
+hge_dtype = np.dtype([("lo", "<u8"), ("hi", "<i8")])
+
+NP_OF = {
+    TYPE.bit: np.dtype(np.int8), TYPE.bte: np.dtype(np.int8), TYPE.sht: np.dtype(np.int16),
+    TYPE.int: np.dtype(np.int32), TYPE.oid: np.dtype(np.uint64), TYPE.flt: np.dtype(np.float32),
+    TYPE.dbl: np.dtype(np.float64), TYPE.lng: np.dtype(np.int64), TYPE.hge: hge_dtype,
+    TYPE.date: np.dtype(np.int32), TYPE.daytime: np.dtype(np.int64), TYPE.timestamp: np.dtype(np.int64),
+    TYPE.void: np.dtype(np.uint64), TYPE.msk: np.dtype(np.uint32),
+}
+TYPE_NAME = {v: k for k, v in vars(TYPE).items() if not k.startswith("_")}
+
+
+def nil_of(tt: int):
+    """in-band nil of a fixed-width atom (gdk_atoms.h:149-218)"""
+    if tt in (TYPE.flt, TYPE.dbl):
+        return float("nan")
+    if tt in (TYPE.oid, TYPE.void):
+        return oid_nil
+    if tt == TYPE.hge:
+        return -(1 << 127)
+    return int(np.iinfo(NP_OF[tt]).min)
+
+
+def hge_from_ints(vals) -> np.ndarray:
+    a = np.empty(len(vals), dtype=hge_dtype)
+    for i, v in enumerate(vals):
+        v = int(v)
+        a["lo"][i] = v & 0xFFFFFFFFFFFFFFFF
+        a["hi"][i] = v >> 64
+    return a
+
+
+def hge_to_ints(a: np.ndarray) -> list:
+    return [(int(h) << 64) | int(l) for l, h in zip(a["lo"], a["hi"])]
+
+
+def hge_from_i64(a: np.ndarray) -> np.ndarray:
+    a = np.asarray(a, dtype=np.int64)
+    r = np.empty(a.shape, dtype=hge_dtype)
+    r["lo"] = a.view(np.uint64)
+    r["hi"] = a >> 63
+    return r
+
+
+class _bat(C.Structure):
+    _fields_ = [
+        ("ttype", C.c_int32), ("device", C.c_int32),
+        ("hseqbase", C.c_uint64), ("count", C.c_uint64), ("tseqbase", C.c_uint64),
+        ("base", C.c_void_p), ("capacity", C.c_uint64),
+        ("ccand", C.c_int32), ("firstbit", C.c_uint32),
+        ("vheap", C.c_void_p), ("nvheap", C.c_uint64),
+        ("tsorted", C.c_uint8), ("trevsorted", C.c_uint8), ("tkey", C.c_uint8),
+        ("tnonil", C.c_uint8), ("tnil", C.c_uint8), ("owns", C.c_uint8),
+        ("oidrange_known", C.c_uint8), ("pad", C.c_uint8),
+        ("first_oid", C.c_uint64), ("last_oid", C.c_uint64),
+    ]
+
+
+_P = C.POINTER(_bat)
+_PP = C.POINTER(_P)
+
+
+def _sig(name, res, *args):
+    f = getattr(lib, name)
+    f.restype = res
+    f.argtypes = list(args)
+    return f
+
+
+_sig("b200_init", C.c_int, C.c_int)
+_sig("b200_device_count", C.c_int)
+_sig("b200_errbuf", C.c_char_p)
+_sig("b200_clrerr", None)
+_sig("b200_algorithm", C.c_char_p)
+_sig("b200_kernel_launches", C.c_uint64)
+_sig("b200_sync", None)
+_sig("b200_stream", C.c_void_p)
+_sig("b200_pinned_alloc", C.c_void_p, C.c_size_t)
+_sig("b200_pinned_free", None, C.c_void_p)
+_sig("b200_COLnew", _P, C.c_uint64, C.c_int, C.c_uint64)
+_sig("b200_BATdense", _P, C.c_uint64, C.c_uint64, C.c_uint64)
+_sig("b200_BATfromhost", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
+_sig("b200_BATwrap", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
+_sig("b200_BATnegcands_fromhost", _P, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64)
+_sig("b200_BATmaskedcands_fromhost", _P, C.c_uint64, C.c_uint64, C.c_void_p, C.c_bool)
+_sig("b200_BATsetprops", None, _P, C.c_bool, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
+_sig("b200_BATtohost", C.c_int, _P, C.c_void_p)
+_sig("b200_BATfree", None, _P)
+_sig("b200_BATselect", _P, _P, _P, C.c_void_p, C.c_void_p, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
+_sig("b200_BATthetaselect", _P, _P, _P, C.c_void_p, C.c_char_p)
+for _n in ("b200_BATmergecand", "b200_BATintersectcand", "b200_BATdiffcand", "b200_BATproject"):
+    _sig(_n, _P, _P, _P)
+_sig("b200_BATproject2", _P, _P, _P, _P)
+
+
+def errbuf() -> str:
+    return (lib.b200_errbuf() or b"").decode()
+
+
+def _fail(what: str):
+    msg = errbuf().strip()
+    raise GDKError(msg or f"{what}: GDK_FAIL")
+
+
+def init(device: int = 0) -> None:
+    if lib.b200_init(device) != 0:
+        _fail("b200_init")
+
+
+def sync() -> None:
+    lib.b200_sync()
+
+
+def kernel_launches() -> int:
+    return int(lib.b200_kernel_launches())
+
+
+def algorithm() -> str:
+    return (lib.b200_algorithm() or b"").decode()
+
+
+class BAT:
+    """Owner of one ``b200_bat`` descriptor (a device-resident column or candidate list)."""
+
+    __slots__ = ("_p", "_keep")
+
+    def __init__(self, p, keep=None):
+        if not p:
+            _fail("BAT")
+        self._p = p
+        self._keep = keep
+
+    # descriptor fields
+    def __getattr__(self, name):
+        if name in ("_p", "_keep"):
+            raise AttributeError(name)
+        return getattr(self._p.contents, name)
+
+    def __len__(self):
+        return int(self._p.contents.count)
+
+    @property
+    def ptr(self):
+        return self._p
+
+    def free(self):
+        if self._p:
+            lib.b200_BATfree(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def setprops(self, sorted=False, revsorted=False, key=False, nonil=False, nil=False):
+        lib.b200_BATsetprops(self._p, sorted, revsorted, key, nonil, nil)
+        return self
+
+    def is_dense(self) -> bool:
+        b = self._p.contents
+        return b.ccand == 0 and b.ttype == TYPE.void and b.tseqbase != oid_nil
+
+    def numpy(self) -> np.ndarray:
+        """logical tail on the host (void / candidate encodings materialised as oids)"""
+        b = self._p.contents
+        tt = b.ttype
+        if tt == TYPE.void or b.ccand != 0:
+            out = np.empty(b.count, dtype=np.uint64)
+        elif tt == TYPE.msk:
+            out = np.empty((b.count + 31) // 32, dtype=np.uint32)
+        else:
+            out = np.empty(b.count, dtype=NP_OF[tt])
+        if b.count and lib.b200_BATtohost(self._p, out.ctypes.data_as(C.c_void_p)) != 0:
+            _fail("BATtohost")
+        return out
+
+    def props(self) -> dict:
+        b = self._p.contents
+        return dict(type=b.ttype, hseq=b.hseqbase, count=b.count, tseq=b.tseqbase,
+                    sorted=bool(b.tsorted), revsorted=bool(b.trevsorted), key=bool(b.tkey),
+                    nonil=bool(b.tnonil), nil=bool(b.tnil), ccand=b.ccand)
+
+
+def _ptr(b):
+    return b._p if b is not None else None
+
+
+def _val(tt: int, v):
+    """a C buffer holding one atom value of storage type tt (None -> NULL)"""
+    if v is None:
+        return None
+    if tt == TYPE.hge:
+        a = hge_from_ints([v])
+    elif tt in (TYPE.flt, TYPE.dbl):
+        a = np.array([v], dtype=NP_OF[tt])
+    else:
+        a = np.array([int(v)], dtype=np.int64).astype(NP_OF[tt]) if tt not in (TYPE.oid, TYPE.void) \
+            else np.array([int(v)], dtype=np.uint64)
+    return a
+
+
+def _vp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+# ------------------------------------------------------------------ construction
+def BATfromhost(arr: np.ndarray, tt: int | None = None, hseq: int = 0, **props) -> BAT:
+    """upload a tail heap (the device heap tier's load path)"""
+    arr = np.ascontiguousarray(arr)
+    if tt is None:
+        tt = {np.dtype(np.int8): TYPE.bte, np.dtype(np.int16): TYPE.sht, np.dtype(np.int32): TYPE.int,
+              np.dtype(np.int64): TYPE.lng, np.dtype(np.uint64): TYPE.oid, np.dtype(np.float32): TYPE.flt,
+              np.dtype(np.float64): TYPE.dbl, hge_dtype: TYPE.hge}[arr.dtype]
+    assert arr.dtype.itemsize == NP_OF[tt].itemsize, (arr.dtype, tt)
+    b = BAT(lib.b200_BATfromhost(_vp(arr), tt, len(arr), hseq))
+    if props:
+        b.setprops(**props)
+    return b
+
+
+def BATdense(hseq: int, tseq: int, cnt: int) -> BAT:
+    return BAT(lib.b200_BATdense(hseq, tseq, cnt))
+
+
+def COLnew(hseq: int, tt: int, cap: int) -> BAT:
+    return BAT(lib.b200_COLnew(hseq, tt, cap))
+
+
+def BATwrap(devptr: int, tt: int, cnt: int, hseq: int = 0, keep=None, **props) -> BAT:
+    b = BAT(lib.b200_BATwrap(C.c_void_p(devptr), tt, cnt, hseq), keep=keep)
+    if props:
+        b.setprops(**props)
+    return b
+
+
+def BATnegcands(seq: int, cnt: int, exceptions) -> BAT:
+    e = np.ascontiguousarray(exceptions, dtype=np.uint64)
+    return BAT(lib.b200_BATnegcands_fromhost(seq, cnt, _vp(e), len(e)))
+
+
+def BATmaskedcands(hseq: int, nrows: int, words, selected: bool = True) -> BAT:
+    w = np.ascontiguousarray(words, dtype=np.uint32)
+    return BAT(lib.b200_BATmaskedcands_fromhost(hseq, nrows, _vp(w), selected))
+
+
+# ------------------------------------------------------------------ select / project / cands
+def _storage(tt: int) -> int:
+    return {TYPE.bit: TYPE.bte, TYPE.date: TYPE.int, TYPE.daytime: TYPE.lng, TYPE.timestamp: TYPE.lng}.get(tt, tt)
+
+
+def BATselect(b: BAT, s: BAT | None, tl, th, li: bool, hi: bool, anti: bool, nil_matches: bool = False) -> BAT:
+    st = _storage(b.ttype)
+    vl, vh = _val(st, tl), _val(st, th)
+    return BAT(lib.b200_BATselect(b._p, _ptr(s), _vp(vl), _vp(vh), li, hi, anti, nil_matches))
+
+
+def BATthetaselect(b: BAT, s: BAT | None, val, op: str) -> BAT:
+    v = _val(_storage(b.ttype), val)
+    return BAT(lib.b200_BATthetaselect(b._p, _ptr(s), _vp(v), op.encode()))
+
+
+def BATproject(l: BAT, r: BAT) -> BAT:
+    return BAT(lib.b200_BATproject(l._p, r._p))
+
+
+def BATproject2(l: BAT, r1: BAT, r2: BAT | None) -> BAT:
+    return BAT(lib.b200_BATproject2(l._p, r1._p, _ptr(r2)))
+
+
+def BATmergecand(a: BAT, b: BAT) -> BAT:
+    return BAT(lib.b200_BATmergecand(a._p, b._p))
+
+
+def BATintersectcand(a: BAT, b: BAT) -> BAT:
+    return BAT(lib.b200_BATintersectcand(a._p, b._p))
+
+
+def BATdiffcand(a: BAT, b: BAT) -> BAT:
+    return BAT(lib.b200_BATdiffcand(a._p, b._p))
+
+
+# ------------------------------------------------------------------ calc
+for _op in ("add", "sub", "mul", "div"):
+    _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P, C.c_int)
+    _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P, C.c_int)
+    _sig(f"b200_BATcalccst{_op}", _P, C.c_void_p, C.c_int, _P, _P, C.c_int)
+_sig("b200_BATconvert", _P, _P, _P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8)
+
+
+def BATcalc(op: str, b1: BAT, b2: BAT, s1: BAT | None, s2: BAT | None, tp: int) -> BAT:
+    """BATcalcadd/sub/mul/div (gdk_calc.h:36-47)"""
+    return BAT(getattr(lib, f"b200_BATcalc{op}")(b1._p, b2._p, _ptr(s1), _ptr(s2), tp))
+
+
+def BATcalccst(op: str, b: BAT, v, vtype: int, s: BAT | None, tp: int, cst_first: bool = False) -> BAT:
+    """BATcalc<op>cst (b OP v) or BATcalccst<op> (v OP b); the ValRecord is (value, type id)"""
+    a = _val(_storage(vtype), v)
+    if cst_first:
+        return BAT(getattr(lib, f"b200_BATcalccst{op}")(_vp(a), vtype, b._p, _ptr(s), tp))
+    return BAT(getattr(lib, f"b200_BATcalc{op}cst")(b._p, _vp(a), vtype, _ptr(s), tp))
+
+
+def BATcalcadd(b1, b2, s1, s2, tp): return BATcalc("add", b1, b2, s1, s2, tp)
+def BATcalcsub(b1, b2, s1, s2, tp): return BATcalc("sub", b1, b2, s1, s2, tp)
+def BATcalcmul(b1, b2, s1, s2, tp): return BATcalc("mul", b1, b2, s1, s2, tp)
+def BATcalcdiv(b1, b2, s1, s2, tp): return BATcalc("div", b1, b2, s1, s2, tp)
+
+
+def BATconvert(b: BAT, s: BAT | None, tp: int, scale1: int = 0, scale2: int = 0, precision: int = 0) -> BAT:
+    return BAT(lib.b200_BATconvert(b._p, _ptr(s), tp, scale1, scale2, precision))
+
+
+# ------------------------------------------------------------------ aggregates
+for _n in ("sum", "count", "min", "max"):
+    if hasattr(lib, f"b200_BATgroup{_n}"):
+        _sig(f"b200_BATgroup{_n}", _P, _P, _P, _P, _P, C.c_int, C.c_bool)
+_sig("b200_BATgroupavg", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_int, C.c_bool, C.c_int)
+_sig("b200_BATsum", C.c_int, C.c_void_p, C.c_int, _P, _P, C.c_bool, C.c_bool)
+
+
+def BATgroupsum(b, g, e, s, tp, skip_nils=True) -> BAT:
+    return BAT(lib.b200_BATgroupsum(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
+
+
+def BATgroupcount(b, g, e, s, tp=TYPE.lng, skip_nils=True) -> BAT:
+    return BAT(lib.b200_BATgroupcount(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
+
+
+def BATgroupmin(b, g, e, s, tp=TYPE.oid, skip_nils=True) -> BAT:
+    return BAT(lib.b200_BATgroupmin(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
+
+
+def BATgroupmax(b, g, e, s, tp=TYPE.oid, skip_nils=True) -> BAT:
+    return BAT(lib.b200_BATgroupmax(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
+
+
+def BATgroupavg(b, g, e, s, tp=TYPE.dbl, skip_nils=True, scale=0, want_counts=True):
+    pa, pc = _P(), _P()
+    rc = lib.b200_BATgroupavg(C.byref(pa), C.byref(pc) if want_counts else None, b._p, _ptr(g), _ptr(e), _ptr(s),
+                              tp, skip_nils, scale)
+    if rc != 1:
+        _fail("BATgroupavg")
+    return BAT(pa), (BAT(pc) if want_counts else None)
+
+
+def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if_empty: bool = True) -> np.ndarray:
+    """returns a 1-element array of the result type (hge as (lo,hi))"""
+    out = np.zeros(1, dtype=NP_OF[tp])
+    if lib.b200_BATsum(_vp(out), tp, b._p, _ptr(s), skip_nils, nil_if_empty) != 1:
+        _fail("BATsum")
+    return out

@@ -228,3 +228,63 @@ refh_parallel(refh_slice_fn fn, void *arg, int nslices, int nthreads)
 		pthread_join(th[i], NULL);
 	return 0;
 }
+
+/* --- constant-operand calc: the Python side passes (pointer, type id) and we build
+ * the ValRecord the reference wants (VALinit, gdk_value.c). op: 0 add 1 sub 2 mul 3 div;
+ * side: 0 = BAT op cst, 1 = cst op BAT --- */
+BAT *
+refh_calc_cst(int op, int side, BAT *b, const void *v, int vtype, BAT *s, int tp)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	switch (op * 2 + side) {
+	case 0: bn = BATcalcaddcst(b, &val, s, tp); break;
+	case 1: bn = BATcalccstadd(&val, b, s, tp); break;
+	case 2: bn = BATcalcsubcst(b, &val, s, tp); break;
+	case 3: bn = BATcalccstsub(&val, b, s, tp); break;
+	case 4: bn = BATcalcmulcst(b, &val, s, tp); break;
+	case 5: bn = BATcalccstmul(&val, b, s, tp); break;
+	case 6: bn = BATcalcdivcst(b, &val, s, tp); break;
+	case 7: bn = BATcalccstdiv(&val, b, s, tp); break;
+	}
+	VALclear(&val);
+	return bn;
+}
+
+/* cmp: 0 lt 1 le 2 gt 3 ge 4 eq 5 ne */
+BAT *
+refh_cmp_cst(int cmp, BAT *b, const void *v, int vtype, BAT *s, int nil_matches)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	switch (cmp) {
+	case 0: bn = BATcalcltcst(b, &val, s); break;
+	case 1: bn = BATcalclecst(b, &val, s); break;
+	case 2: bn = BATcalcgtcst(b, &val, s); break;
+	case 3: bn = BATcalcgecst(b, &val, s); break;
+	case 4: bn = BATcalceqcst(b, &val, s, nil_matches); break;
+	case 5: bn = BATcalcnecst(b, &val, s, nil_matches); break;
+	}
+	VALclear(&val);
+	return bn;
+}
+
+/* hashjoin is what BATjoin picks for unsorted inputs; expose the algorithm string of the
+ * last call so tests can assert which implementation the oracle exercised */
+const char *
+refh_algorithm(void)
+{
+	const char *a = MT_thread_getalgorithm();
+	return a ? a : "";
+}
+
+/* timing helper for the CPU baseline: microseconds, monotonic */
+int64_t
+refh_usec(void)
+{
+	return (int64_t) GDKusec();
+}

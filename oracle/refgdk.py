@@ -1,0 +1,419 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes driver of the REAL reference GDK.
+
+``oracle/_ref/libbat_ref.so`` is the reference's own gdk/*.c compiled by
+``oracle/Makefile`` (target ``ref``) from the sources under /root/reference;
+``libref_harness.so`` adds the few helpers of ``ref_harness.c``.  This module lets
+the tests, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs call the reference's entry points (BATselect,
+BATproject, BATgroup, BATgroupsum, BATjoin, GDKanalytical*, ...) on in-memory
+BATs built from numpy arrays.  Nothing in ``monetdb_b200/`` may import it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_DIR = Path(__file__).resolve().parent / "_ref"
+LIBBAT = _DIR / "libbat_ref.so"
+LIBH = _DIR / "libref_harness.so"
+
+
+def available() -> bool:
+    return LIBBAT.exists() and LIBH.exists()
+
+
+class T:
+    void, msk, bit, bte, sht, int, oid, ptr, flt, dbl, lng, hge, date, daytime, timestamp = range(15)
+
+
+hge_dtype = np.dtype([("lo", "<u8"), ("hi", "<i8")])
+NP_OF = {
+    T.bit: np.dtype(np.int8), T.bte: np.dtype(np.int8), T.sht: np.dtype(np.int16),
+    T.int: np.dtype(np.int32), T.oid: np.dtype(np.uint64), T.flt: np.dtype(np.float32),
+    T.dbl: np.dtype(np.float64), T.lng: np.dtype(np.int64), T.hge: hge_dtype,
+    T.date: np.dtype(np.int32), T.daytime: np.dtype(np.int64), T.timestamp: np.dtype(np.int64),
+    T.void: np.dtype(np.uint64), T.msk: np.dtype(np.uint32),
+}
+oid_nil = 1 << 63
+BUN_NONE = (1 << 63) - 1
+
+
+class _Info(C.Structure):
+    _fields_ = [("type", C.c_int32), ("ccand", C.c_int32), ("hseq", C.c_uint64), ("count", C.c_uint64),
+                ("tseq", C.c_uint64), ("sorted", C.c_uint8), ("revsorted", C.c_uint8), ("key", C.c_uint8),
+                ("nonil", C.c_uint8), ("nil", C.c_uint8), ("pad", C.c_uint8 * 3)]
+
+
+_bat = None
+_h = None
+
+
+class RefError(RuntimeError):
+    pass
+
+
+def _load(nthreads: int = 0):
+    global _bat, _h
+    if _h is not None:
+        return
+    if not available():
+        raise RefError(f"reference GDK not built: run `make -C oracle ref` (needs /root/reference); looked in {_DIR}")
+    _bat = C.CDLL(str(LIBBAT), mode=C.RTLD_GLOBAL)
+    _h = C.CDLL(str(LIBH), mode=C.RTLD_GLOBAL)
+    V, P = C.c_void_p, C.c_void_p
+    _h.refh_init.restype = C.c_int
+    _h.refh_init.argtypes = [C.c_int]
+    _h.refh_errbuf.restype = C.c_char_p
+    _h.refh_algorithm.restype = C.c_char_p
+    _h.refh_bat_new.restype = P
+    _h.refh_bat_new.argtypes = [C.c_int, C.c_uint64, C.c_uint64, V] + [C.c_int] * 5
+    _h.refh_msk_new.restype = P
+    _h.refh_msk_new.argtypes = [C.c_uint64, C.c_uint64, V]
+    _h.refh_dense.restype = P
+    _h.refh_dense.argtypes = [C.c_uint64] * 3
+    _h.refh_tloc.restype = V
+    _h.refh_tloc.argtypes = [P]
+    _h.refh_info.argtypes = [P, C.POINTER(_Info)]
+    _h.refh_tail.argtypes = [P, V]
+    _h.refh_free.argtypes = [P]
+    _h.refh_assert_props.argtypes = [P]
+    _h.refh_calc_cst.restype = P
+    _h.refh_calc_cst.argtypes = [C.c_int, C.c_int, P, V, C.c_int, P, C.c_int]
+    _h.refh_cmp_cst.restype = P
+    _h.refh_cmp_cst.argtypes = [C.c_int, P, V, C.c_int, P, C.c_int]
+    _h.refh_usec.restype = C.c_int64
+    rc = _h.refh_init(nthreads)
+    if rc != 0:
+        raise RefError(f"GDKinit failed ({rc})")
+    B = C.c_bool
+    sigs = {
+        "BATselect": (P, [P, P, V, V, B, B, B, B]),
+        "BATthetaselect": (P, [P, P, V, C.c_char_p]),
+        "BATproject": (P, [P, P]),
+        "BATproject2": (P, [P, P, P]),
+        "BATmergecand": (P, [P, P]),
+        "BATintersectcand": (P, [P, P]),
+        "BATdiffcand": (P, [P, P]),
+        "BATnegcands": (P, [C.c_uint64, C.c_uint64, P]),
+        "BATmaskedcands": (P, [C.c_uint64, C.c_uint64, P, B]),
+        "BATgroup": (C.c_int, [C.POINTER(P), C.POINTER(P), C.POINTER(P), P, P, P, P, P]),
+        "BATgroupsum": (P, [P, P, P, P, C.c_int, B]),
+        "BATgroupcount": (P, [P, P, P, P, C.c_int, B]),
+        "BATgroupmin": (P, [P, P, P, P, C.c_int, B]),
+        "BATgroupmax": (P, [P, P, P, P, C.c_int, B]),
+        "BATgroupavg": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, C.c_int, B, C.c_int]),
+        "BATsum": (C.c_int, [V, C.c_int, P, P, B, B]),
+        "BATjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
+        "BAThash": (C.c_int, [P]),
+        "BATconvert": (P, [P, P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8]),
+        "BATcalcisnil": (P, [P, P]),
+        "GDKanalyticaldiff": (C.c_int, [P, P, P, V, C.c_int]),
+        "GDKanalyticalwindowbounds": (C.c_int, [P, P, P, P, V, C.c_int, C.c_int, C.c_int, B, C.c_uint64]),
+        "GDKanalyticalsum": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int, C.c_int]),
+        "GDKanalyticalavg": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
+        "GDKanalyticalavginteger": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
+        "GDKanalyticalcount": (C.c_int, [P, P, P, P, P, P, C.c_int8, C.c_int, C.c_int]),
+        "GDKanalyticalmin": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
+        "GDKanalyticalmax": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
+        "COLnew": (P, [C.c_uint64, C.c_int, C.c_uint64, C.c_int]),
+    }
+    for op in ("add", "sub", "mul", "div"):
+        sigs["BATcalc" + op] = (P, [P, P, P, P, C.c_int])
+    for op in ("lt", "le", "gt", "ge"):
+        sigs["BATcalc" + op] = (P, [P, P, P, P])
+    for op in ("eq", "ne"):
+        sigs["BATcalc" + op] = (P, [P, P, P, P, B])
+    for name, (res, args) in sigs.items():
+        f = getattr(_bat, name)
+        f.restype = res
+        f.argtypes = args
+
+
+def init(nthreads: int = 0):
+    _load(nthreads)
+
+
+def errbuf() -> str:
+    return (_h.refh_errbuf() or b"").decode()
+
+
+def clrerr():
+    _h.refh_clrerr()
+
+
+def algorithm() -> str:
+    return (_h.refh_algorithm() or b"").decode()
+
+
+def usec() -> int:
+    return int(_h.refh_usec())
+
+
+class RBAT:
+    """a reference BAT* (owned)"""
+
+    def __init__(self, p, what="BAT"):
+        if not p:
+            msg = errbuf().strip()
+            clrerr()
+            raise RefError(msg or f"{what}: NULL")
+        self.p = p
+
+    def free(self):
+        if self.p:
+            _h.refh_free(self.p)
+            self.p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def info(self) -> _Info:
+        i = _Info()
+        _h.refh_info(self.p, C.byref(i))
+        return i
+
+    def props(self) -> dict:
+        i = self.info()
+        return dict(type=i.type, hseq=i.hseq, count=i.count, tseq=i.tseq, sorted=bool(i.sorted),
+                    revsorted=bool(i.revsorted), key=bool(i.key), nonil=bool(i.nonil), nil=bool(i.nil),
+                    ccand=i.ccand)
+
+    def __len__(self):
+        return int(self.info().count)
+
+    def numpy(self) -> np.ndarray:
+        i = self.info()
+        if i.type == T.void:
+            out = np.empty(i.count, dtype=np.uint64)
+        elif i.type == T.msk:
+            out = np.empty((i.count + 31) // 32, dtype=np.uint32)
+        else:
+            out = np.empty(i.count, dtype=NP_OF[i.type])
+        if i.count:
+            _h.refh_tail(self.p, out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def assert_props(self):
+        _h.refh_assert_props(self.p)
+
+
+def _p(b):
+    return b.p if b is not None else None
+
+
+def _vp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _val(tt, v):
+    if v is None:
+        return None
+    st = {T.bit: T.bte, T.date: T.int, T.daytime: T.lng, T.timestamp: T.lng}.get(tt, tt)
+    if st == T.hge:
+        a = np.empty(1, dtype=hge_dtype)
+        a["lo"][0] = int(v) & 0xFFFFFFFFFFFFFFFF
+        a["hi"][0] = int(v) >> 64
+        return a
+    if st in (T.flt, T.dbl):
+        return np.array([v], dtype=NP_OF[st])
+    if st in (T.oid, T.void):
+        return np.array([int(v)], dtype=np.uint64)
+    return np.array([int(v)], dtype=np.int64).astype(NP_OF[st])
+
+
+def bat(arr: np.ndarray, tt: int, hseq: int = 0, sorted=False, revsorted=False, key=False,
+        nonil=False, nil=False) -> RBAT:
+    _load()
+    arr = np.ascontiguousarray(arr)
+    assert arr.dtype.itemsize == NP_OF[tt].itemsize, (arr.dtype, tt)
+    return RBAT(_h.refh_bat_new(tt, len(arr), hseq, _vp(arr), sorted, revsorted, key, nonil, nil))
+
+
+def dense(hseq, tseq, cnt) -> RBAT:
+    _load()
+    return RBAT(_h.refh_dense(hseq, tseq, cnt))
+
+
+def colnew(tt: int, cap: int, hseq: int = 0) -> RBAT:
+    """caller-allocated result BAT for the GDKanalytical* functions (sql_rank.c:161)"""
+    _load()
+    return RBAT(_bat.COLnew(hseq, tt, cap, 1))
+
+
+def negcands(seq, cnt, exceptions) -> RBAT:
+    _load()
+    e = np.ascontiguousarray(exceptions, dtype=np.uint64)
+    eb = bat(e, T.oid, sorted=True, key=True, nonil=True)
+    return RBAT(_bat.BATnegcands(seq, cnt, eb.p))
+
+
+def maskedcands(hseq, nrows, words, selected=True) -> RBAT:
+    _load()
+    w = np.ascontiguousarray(words, dtype=np.uint32)
+    m = RBAT(_h.refh_msk_new(hseq, nrows, _vp(w)))
+    return RBAT(_bat.BATmaskedcands(hseq, nrows, m.p, selected))
+
+
+def BATselect(b, s, tl, th, li, hi, anti, nil_matches=False) -> RBAT:
+    tt = b.info().type
+    vl, vh = _val(tt, tl), _val(tt, th)
+    return RBAT(_bat.BATselect(b.p, _p(s), _vp(vl), _vp(vh), li, hi, anti, nil_matches), "BATselect")
+
+
+def BATthetaselect(b, s, val, op) -> RBAT:
+    v = _val(b.info().type, val)
+    return RBAT(_bat.BATthetaselect(b.p, _p(s), _vp(v), op.encode()), "BATthetaselect")
+
+
+def BATproject(l, r) -> RBAT:
+    return RBAT(_bat.BATproject(l.p, r.p), "BATproject")
+
+
+def BATproject2(l, r1, r2) -> RBAT:
+    return RBAT(_bat.BATproject2(l.p, r1.p, _p(r2)), "BATproject2")
+
+
+def BATmergecand(a, b) -> RBAT:
+    return RBAT(_bat.BATmergecand(a.p, b.p))
+
+
+def BATintersectcand(a, b) -> RBAT:
+    return RBAT(_bat.BATintersectcand(a.p, b.p))
+
+
+def BATdiffcand(a, b) -> RBAT:
+    return RBAT(_bat.BATdiffcand(a.p, b.p))
+
+
+_OPS = {"add": 0, "sub": 1, "mul": 2, "div": 3}
+_CMPS = {"lt": 0, "le": 1, "gt": 2, "ge": 3, "eq": 4, "ne": 5}
+
+
+def BATcalc(op, b1, b2, s1, s2, tp) -> RBAT:
+    return RBAT(getattr(_bat, "BATcalc" + op)(b1.p, b2.p, _p(s1), _p(s2), tp), "BATcalc" + op)
+
+
+def BATcalccst(op, b, v, vtype, s, tp, cst_first=False) -> RBAT:
+    a = _val(vtype, v)
+    return RBAT(_h.refh_calc_cst(_OPS[op], 1 if cst_first else 0, b.p, _vp(a), vtype, _p(s), tp), "BATcalc" + op + "cst")
+
+
+def BATcalccmp(op, b1, b2, s1=None, s2=None, nil_matches=False) -> RBAT:
+    f = getattr(_bat, "BATcalc" + op)
+    if op in ("eq", "ne"):
+        return RBAT(f(b1.p, b2.p, _p(s1), _p(s2), nil_matches), "BATcalc" + op)
+    return RBAT(f(b1.p, b2.p, _p(s1), _p(s2)), "BATcalc" + op)
+
+
+def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False) -> RBAT:
+    a = _val(vtype, v)
+    return RBAT(_h.refh_cmp_cst(_CMPS[op], b.p, _vp(a), vtype, _p(s), nil_matches), "BATcalc" + op + "cst")
+
+
+def BATcalcisnil(b, s=None) -> RBAT:
+    return RBAT(_bat.BATcalcisnil(b.p, _p(s)))
+
+
+def BATconvert(b, s, tp, scale1=0, scale2=0, precision=0) -> RBAT:
+    return RBAT(_bat.BATconvert(b.p, _p(s), tp, scale1, scale2, precision), "BATconvert")
+
+
+def BATgroup(b, s=None, g=None, e=None, h=None):
+    pg, pe, ph = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    rc = _bat.BATgroup(C.byref(pg), C.byref(pe), C.byref(ph), b.p, _p(s), _p(g), _p(e), _p(h))
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATgroup failed")
+    return RBAT(pg.value), RBAT(pe.value), RBAT(ph.value)
+
+
+def _grp(name, b, g, e, s, tp, skip_nils) -> RBAT:
+    return RBAT(getattr(_bat, name)(b.p, _p(g), _p(e), _p(s), tp, skip_nils), name)
+
+
+def BATgroupsum(b, g, e, s, tp, skip_nils=True) -> RBAT:
+    return _grp("BATgroupsum", b, g, e, s, tp, skip_nils)
+
+
+def BATgroupcount(b, g, e, s, tp=T.lng, skip_nils=True) -> RBAT:
+    return _grp("BATgroupcount", b, g, e, s, tp, skip_nils)
+
+
+def BATgroupmin(b, g, e, s, tp=T.oid, skip_nils=True) -> RBAT:
+    return _grp("BATgroupmin", b, g, e, s, tp, skip_nils)
+
+
+def BATgroupmax(b, g, e, s, tp=T.oid, skip_nils=True) -> RBAT:
+    return _grp("BATgroupmax", b, g, e, s, tp, skip_nils)
+
+
+def BATgroupavg(b, g, e, s, tp=T.dbl, skip_nils=True, scale=0, want_counts=True):
+    pa, pc = C.c_void_p(), C.c_void_p()
+    rc = _bat.BATgroupavg(C.byref(pa), C.byref(pc) if want_counts else None, b.p, _p(g), _p(e), _p(s), tp, skip_nils, scale)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATgroupavg failed")
+    return RBAT(pa.value), (RBAT(pc.value) if want_counts else None)
+
+
+def BATsum(tp, b, s=None, skip_nils=True, nil_if_empty=True):
+    out = np.zeros(1, dtype=NP_OF[tp])
+    rc = _bat.BATsum(_vp(out), tp, b.p, _p(s), skip_nils, nil_if_empty)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATsum failed")
+    return out
+
+
+def BATjoin(l, r, sl=None, sr=None, nil_matches=False, estimate=BUN_NONE):
+    p1, p2 = C.c_void_p(), C.c_void_p()
+    rc = _bat.BATjoin(C.byref(p1), C.byref(p2), l.p, r.p, _p(sl), _p(sr), nil_matches, estimate)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATjoin failed")
+    return RBAT(p1.value), RBAT(p2.value)
+
+
+def _ok(rc, what):
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or what + " failed")
+
+
+def GDKanalyticaldiff(r, b, p, npbit, tpe):
+    nb = np.array([npbit], dtype=np.int8) if npbit is not None else None
+    _ok(_bat.GDKanalyticaldiff(r.p, b.p, _p(p), _vp(nb), tpe), "GDKanalyticaldiff")
+    return r
+
+
+def GDKanalyticalwindowbounds(r, b, p, l, bound, tp1, tp2, unit, preceding, first_half):
+    bv = _val(tp2, bound) if bound is not None else None
+    _ok(_bat.GDKanalyticalwindowbounds(r.p, _p(b), _p(p), _p(l), _vp(bv), tp1, tp2, unit, preceding, first_half),
+        "GDKanalyticalwindowbounds")
+    return r
+
+
+def GDKanalyticalsum(r, p, o, b, s, e, tp1, tp2, frame_type):
+    _ok(_bat.GDKanalyticalsum(r.p, _p(p), _p(o), b.p, _p(s), _p(e), tp1, tp2, frame_type), "GDKanalyticalsum")
+    return r
+
+
+def GDKanalyticalfn(name, r, p, o, b, s, e, tpe, frame_type):
+    _ok(getattr(_bat, "GDKanalytical" + name)(r.p, _p(p), _p(o), b.p, _p(s), _p(e), tpe, frame_type), name)
+    return r
+
+
+def GDKanalyticalcount(r, p, o, b, s, e, ignore_nils, tpe, frame_type):
+    _ok(_bat.GDKanalyticalcount(r.p, _p(p), _p(o), b.p, _p(s), _p(e), 1 if ignore_nils else 0, tpe, frame_type), "count")
+    return r
