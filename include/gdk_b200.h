@@ -82,6 +82,11 @@ uint64_t b200_kernel_launches(void);		/* kernels launched by this library so far
 void b200_sync(void);				/* wait for the calling thread's stream */
 void *b200_stream(void);			/* cudaStream_t of the calling thread */
 
+/* per-kernel timing for bench.py: CUDA events on the launching stream around the dominant
+ * kernels.  b200_timing_read syncs and writes lines "name launches total_ms algorithmic_bytes\n". */
+void b200_timing_enable(int on);
+int  b200_timing_read(char *buf, size_t bufsize);
+
 void *b200_pinned_alloc(size_t bytes);		/* page-locked host staging memory */
 void  b200_pinned_free(void *p);
 
@@ -89,6 +94,8 @@ b200_bat *b200_COLnew(uint64_t hseq, int tt, uint64_t cap);			/* gdk_bat.c:292 *
 b200_bat *b200_BATdense(uint64_t hseq, uint64_t tseq, uint64_t cnt);		/* gdk_bat.c:298 */
 b200_bat *b200_BATfromhost(const void *src, int tt, uint64_t cnt, uint64_t hseq);	/* upload a tail heap */
 b200_bat *b200_BATwrap(void *devptr, int tt, uint64_t cnt, uint64_t hseq);	/* borrow device memory */
+b200_bat *b200_BAThostwrap(const void *hostptr, int tt, uint64_t cnt, uint64_t hseq);	/* borrow HOST memory (device = -1):
+							   every operator stages it to the device on use */
 b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc); /* gdk_cand.c:1296 */
 b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows, const uint32_t *words, bool selected); /* gdk_cand.c:1366 */
 void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil);

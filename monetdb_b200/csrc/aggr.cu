@@ -172,6 +172,7 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, bool check
 		acc.fexp = in.fexp = (be ? be : 1) - 1023;
 	}
 	const unsigned grid = grid_for(in.n, AGGR_THREADS * 4, NSM * 8);
+	KTimer kt("aggr", in.n * (sizeof(T1) + (in.gids ? 8 : 0) + (in.cand ? 8 : 0)));
 	if (!acc.niltrack && ngrp <= 8) {
 #define REG_CASE(NG)                                                                                       \
 	if (check)                                                                                         \

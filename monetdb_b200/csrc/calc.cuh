@@ -392,6 +392,7 @@ static bool calc_run(const CalcOperand &o1, const CalcOperand &o2, void *dst, ui
 		(!a.incr1 || ((uintptr_t) a.lft % VecIO<T1, K>::CHUNK) == 0) &&
 		(!a.incr2 || ((uintptr_t) a.rgt % VecIO<T2, K>::CHUNK) == 0) &&
 		((uintptr_t) a.dst % VecIO<T3, K>::CHUNK) == 0;
+	KTimer kt("calc", n * ((a.incr1 ? sizeof(T1) : 0) + (a.incr2 ? sizeof(T2) : 0) + sizeof(T3)));
 	if (aligned) {
 		unsigned grid = grid_for(n / K + 256, 256, NSM * 32);
 		calc_vec_kernel<OP, T1, T2, T3><<<grid, 256, 0, c->stream>>>(a);
@@ -400,6 +401,8 @@ static bool calc_run(const CalcOperand &o1, const CalcOperand &o2, void *dst, ui
 		calc_gen_kernel<OP, T1, T2, T3><<<grid, 256, 0, c->stream>>>(a);
 	}
 	COUNT_LAUNCH();
+	kt.~KTimer();
+	kt.idx = -1;
 	if (!cuda_ok(cudaGetLastError(), "calc launch") ||
 	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 16, cudaMemcpyDeviceToHost, c->stream), "calc state read") ||
 	    !stream_sync())

@@ -106,6 +106,14 @@ Ctx *ctx();				/* lazily initialises device 0 if b200_init was not called */
 extern std::atomic<unsigned long long> g_launches;
 #define COUNT_LAUNCH() (g_launches.fetch_add(1, std::memory_order_relaxed))
 
+// optional per-kernel timing (b200_timing_enable): CUDA events on the launching stream
+// around the kernels that dominate an operator; read back with b200_timing_read.
+struct KTimer {
+	int idx = -1;
+	KTimer(const char *name, uint64_t bytes);	/* bytes = algorithmic bytes of this launch */
+	~KTimer();
+};
+
 void set_err(const char *fmt, ...);	/* GDKerror analogue */
 bool cuda_ok(cudaError_t e, const char *what);
 #define CK(x) do { if (!cuda_ok((x), #x)) goto bailout; } while (0)

@@ -92,7 +92,10 @@ static bool run_compact(uint64_t n, F f, oid *dst, CompactResult &res)
 	TileScan ts;
 	ts.ticket = (unsigned int *) (p + 16);
 	ts.status = (unsigned long long *) (p + 32);
-	compact_kernel<ITEMS, F><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(n, f, dst, ts, (unsigned) ntiles, total);
+	{
+		KTimer kt("compact", n * 8);
+		compact_kernel<ITEMS, F><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(n, f, dst, ts, (unsigned) ntiles, total);
+	}
 	COUNT_LAUNCH();
 	compact_finish_kernel<<<1, 1, 0, c->stream>>>(dst, total, c->slot_d->v);
 	COUNT_LAUNCH();

@@ -462,3 +462,91 @@ b200_bat *bat_constant(uint64_t hseq, int tt, const void *val, uint64_t n)
 	bn->tkey = n <= 1;
 	return bn;
 }
+
+// ---------------------------------------------------------------- kernel timing
+#include <vector>
+#include <string>
+struct KRec { const char *name; uint64_t bytes; cudaEvent_t a, b; };
+static thread_local std::vector<KRec> *tl_krecs = nullptr;
+static std::atomic<int> g_timing{0};
+
+KTimer::KTimer(const char *name, uint64_t bytes)
+{
+	if (!g_timing.load(std::memory_order_relaxed) || tl_ctx == nullptr || tl_ctx->device < 0)
+		return;
+	if (tl_krecs == nullptr)
+		tl_krecs = new std::vector<KRec>();
+	KRec r{name, bytes, nullptr, nullptr};
+	if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess)
+		return;
+	cudaEventRecord(r.a, tl_ctx->stream);
+	tl_krecs->push_back(r);
+	idx = (int) tl_krecs->size() - 1;
+}
+KTimer::~KTimer()
+{
+	if (idx >= 0)
+		cudaEventRecord((*tl_krecs)[idx].b, tl_ctx->stream);
+}
+
+extern "C" void b200_timing_enable(int on)
+{
+	g_timing.store(on);
+}
+
+extern "C" int b200_timing_read(char *buf, size_t bufsize)
+{
+	if (buf == nullptr || bufsize == 0)
+		return -1;
+	buf[0] = 0;
+	if (tl_krecs == nullptr || tl_ctx == nullptr)
+		return 0;
+	cudaStreamSynchronize(tl_ctx->stream);
+	struct Tot { std::string name; uint64_t n = 0, bytes = 0; double ms = 0; };
+	std::vector<Tot> tots;
+	for (KRec &r : *tl_krecs) {
+		float ms = 0;
+		cudaEventElapsedTime(&ms, r.a, r.b);
+		cudaEventDestroy(r.a);
+		cudaEventDestroy(r.b);
+		Tot *t = nullptr;
+		for (Tot &x : tots)
+			if (x.name == r.name)
+				t = &x;
+		if (t == nullptr) {
+			tots.push_back(Tot());
+			t = &tots.back();
+			t->name = r.name;
+		}
+		t->n++;
+		t->bytes += r.bytes;
+		t->ms += ms;
+	}
+	tl_krecs->clear();
+	size_t off = 0;
+	for (Tot &t : tots) {
+		int w = snprintf(buf + off, bufsize - off, "%s %llu %.6f %llu\n", t.name.c_str(), (unsigned long long) t.n, t.ms,
+				 (unsigned long long) t.bytes);
+		if (w < 0 || (size_t) w >= bufsize - off)
+			break;
+		off += w;
+	}
+	return (int) tots.size();
+}
+
+extern "C" b200_bat *b200_BAThostwrap(const void *hostptr, int tt, uint64_t cnt, uint64_t hseq)
+{
+	b200_clrerr();
+	b200_bat *b = bat_alloc_desc();
+	if (b == nullptr)
+		return nullptr;
+	b->ttype = tt;
+	b->device = -1;
+	b->hseqbase = hseq;
+	b->count = b->capacity = cnt;
+	b->base = (void *) hostptr;
+	b->owns = 0;
+	b->tsorted = b->trevsorted = b->tkey = cnt <= 1;
+	b->tnonil = cnt == 0;
+	return b;
+}

@@ -118,6 +118,7 @@ static void launch_project(const oid *l, uint64_t n, const ProjSrc &src, const v
 	constexpr int K = 16 / W;
 	uint64_t nchunks = (n + K - 1) / K;
 	unsigned grid = grid_for(nchunks, 256, NSM * 32);
+	KTimer kt("project", n * (8 + 2 * W));
 	if (((uintptr_t) l & 15) == 0)
 		project_kernel<W, true><<<grid, 256, 0, ctx()->stream>>>(l, n, src, nilword, (word *) dst, errflag);
 	else
@@ -193,7 +194,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 			return slice_view(r1, lo - r1->hseqbase, hi - r1->hseqbase, l->hseqbase);
 		}
 		if (lo < r1->hseqbase || r2 == nullptr || hi > r2->hseqbase + r2->count) {
-			set_err("BATproject2: does not match always\n");
+			set_err("does not match always\n");
 			return nullptr;
 		}
 		if (lo >= r2->hseqbase) {
@@ -256,7 +257,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 	src.r2t = r2 ? r2->tseqbase : OID_NIL;
 	if (l_sorted_known && (lfirst < src.r1seq || llast >= src.r2end)) {
 		if (ltmp) dev_free(ltmp);
-		set_err("BATproject2: does not match always\n");
+		set_err("does not match always\n");
 		return nullptr;
 	}
 	b200_bat *bn = bat_new(l->hseqbase, tpe, lcount);
@@ -300,7 +301,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		}
 		if ((unsigned) c->slot_h->v[8] & 1u) {
 			b200_BATfree(bn);
-			set_err("BATproject2: does not match always\n");
+			set_err("does not match always\n");
 			return nullptr;
 		}
 	}

@@ -139,7 +139,10 @@ static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, o
 	TileScan ts;
 	ts.ticket = (unsigned int *) (sp + 16);
 	ts.status = (unsigned long long *) (sp + 32);
-	select_dense_kernel<T><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(p, skip, n, seq - skip, pred, dst, ts, (unsigned) ntiles, total);
+	{
+		KTimer kt("select_dense", n * sizeof(T));
+		select_dense_kernel<T><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(p, skip, n, seq - skip, pred, dst, ts, (unsigned) ntiles, total);
+	}
 	COUNT_LAUNCH();
 	compact_finish_kernel<<<1, 1, 0, c->stream>>>(dst, total, c->slot_d->v);
 	COUNT_LAUNCH();

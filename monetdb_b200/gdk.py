@@ -388,3 +388,43 @@ def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if
     if lib.b200_BATsum(_vp(out), tp, b._p, _ptr(s), skip_nils, nil_if_empty) != 1:
         _fail("BATsum")
     return out
+
+
+# ------------------------------------------------------------------ bench support
+_sig("b200_timing_enable", None, C.c_int)
+_sig("b200_timing_read", C.c_int, C.c_char_p, C.c_size_t)
+_sig("b200_BAThostwrap", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
+
+
+def timing_enable(on: bool = True) -> None:
+    lib.b200_timing_enable(1 if on else 0)
+
+
+def timing_read() -> dict:
+    """{kernel name: (launches, total_ms, input_bytes)} since the last read"""
+    buf = C.create_string_buffer(1 << 16)
+    lib.b200_timing_read(buf, len(buf))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, n, ms, by = line.split()
+        out[name] = (int(n), float(ms), int(by))
+    return out
+
+
+def pinned_empty(n: int, dtype) -> np.ndarray:
+    """numpy array over page-locked host memory (freed with the process)"""
+    dt = np.dtype(dtype)
+    p = lib.b200_pinned_alloc(max(1, n * dt.itemsize))
+    if not p:
+        _fail("pinned_alloc")
+    buf = (C.c_char * (n * dt.itemsize)).from_address(p)
+    return np.frombuffer(buf, dtype=dt, count=n)
+
+
+def BAThostwrap(arr: np.ndarray, tt: int, hseq: int = 0, **props) -> BAT:
+    """a BAT whose heap lives in HOST memory: operators stage it to the device on every use"""
+    arr = np.ascontiguousarray(arr)
+    b = BAT(lib.b200_BAThostwrap(_vp(arr), tt, len(arr), hseq), keep=arr)
+    if props:
+        b.setprops(**props)
+    return b

@@ -1,0 +1,89 @@
+"""Synthetic TPC-H-shaped columns: splitmix64, one stream per
+column, seed = 0x5EED0000 + column index, value = f(z of row i) so that any row
+range can be generated independently on any GPU or host."""
+from __future__ import annotations
+
+import numpy as np
+
+M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def splitmix64(seed: int, lo: int, hi: int) -> np.ndarray:
+    """z values of rows [lo, hi) of the stream with the given seed"""
+    with np.errstate(over="ignore"):
+        i = np.arange(lo + 1, hi + 1, dtype=np.uint64)
+        z = np.uint64(seed) + i * np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return z
+
+
+def col_seed(idx: int) -> int:
+    return 0x5EED0000 + idx
+
+
+def todate(year: int, month: int, day: int) -> int:
+    """MonetDB's packed date (gdk_time.c:17-28): ((y+4712)*12 + m-1) << 5 | d"""
+    return (((year + 4712) * 12 + (month - 1)) << 5) | day
+
+
+_MDAYS = [31, 28, 31, 30, 31, 30, 31, 31, 30, 31, 30, 31]
+
+
+def _date_table(ndays: int = 2526) -> np.ndarray:
+    """packed dates of the ndays days starting 1992-01-02"""
+    out = np.empty(ndays, dtype=np.int32)
+    y, m, d = 1992, 1, 2
+    for i in range(ndays):
+        out[i] = todate(y, m, d)
+        d += 1
+        leap = y % 4 == 0 and (y % 100 != 0 or y % 400 == 0)
+        md = _MDAYS[m - 1] + (1 if (m == 2 and leap) else 0)
+        if d > md:
+            d = 1
+            m += 1
+            if m > 12:
+                m = 1
+                y += 1
+    return out
+
+
+DATES = _date_table()
+# column indices (seed offsets)
+C_SHIPDATE, C_DISCOUNT, C_QUANTITY, C_EXTPRICE, C_TAX, C_RETFLAG, C_K, C_V, C_LKEY, C_OKEY = range(10)
+
+
+def lineitem(lo: int, hi: int, cols=("shipdate", "discount", "quantity", "extprice")) -> dict:
+    """rows [lo,hi) of the synthetic lineitem table (configs 2 and 3)"""
+    out = {}
+    if "shipdate" in cols or "returnflag" in cols or "linestatus" in cols:
+        z = splitmix64(col_seed(C_SHIPDATE), lo, hi)
+        day = (z % np.uint64(2526)).astype(np.int64)
+        ship = DATES[day]
+        if "shipdate" in cols:
+            out["shipdate"] = ship
+        if "returnflag" in cols or "linestatus" in cols:
+            ls = (ship > todate(1995, 6, 17)).astype(np.int8)
+            z2 = splitmix64(col_seed(C_RETFLAG), lo, hi)
+            # A/F (0,0), R/F (2,0) before the cut; N/O (1,1) after; a thin N/F band (1,0) just before it
+            band = (ship > todate(1995, 6, 10)) & (ls == 0)
+            rf = np.where(ls == 1, 1, np.where(band, 1, np.where(z2 % np.uint64(2) == 1, 0, 2))).astype(np.int8)
+            out["returnflag"] = rf
+            out["linestatus"] = ls
+    if "discount" in cols:
+        out["discount"] = (splitmix64(col_seed(C_DISCOUNT), lo, hi) % np.uint64(11)).astype(np.int64)
+    if "quantity" in cols:
+        out["quantity"] = ((splitmix64(col_seed(C_QUANTITY), lo, hi) % np.uint64(50) + np.uint64(1)) * np.uint64(100)).astype(np.int64)
+    if "extprice" in cols:
+        out["extprice"] = (splitmix64(col_seed(C_EXTPRICE), lo, hi) % np.uint64(10400001) + np.uint64(90000)).astype(np.int64)
+    if "tax" in cols:
+        out["tax"] = (splitmix64(col_seed(C_TAX), lo, hi) % np.uint64(9)).astype(np.int64)
+    return out
+
+
+def config1(lo: int, hi: int):
+    """config 1: k:int = z%1000, v:lng = (z>>32)%100000"""
+    zk = splitmix64(col_seed(C_K), lo, hi)
+    zv = splitmix64(col_seed(C_V), lo, hi)
+    return (zk % np.uint64(1000)).astype(np.int32), ((zv >> np.uint64(32)) % np.uint64(100000)).astype(np.int64)

@@ -38,6 +38,9 @@ refh_init(int nthreads)
 		return -2;
 	if (GDKinit(set, setlen, true, NULL) != GDK_SUCCEED)
 		return -3;
+	/* GDKerror only records its text when the thread has an error buffer (gdk_tracer.c:586-597) */
+	if (GDKerrbuf == NULL)
+		GDKsetbuf(calloc(1, GDKMAXERRLEN));
 	refh_ready = 1;
 	return 0;
 }
@@ -46,7 +49,11 @@ refh_init(int nthreads)
 int
 refh_thread_attach(const char *name)
 {
-	return MT_thread_register() ? 0 : -1;
+	if (!MT_thread_register())
+		return -1;
+	if (GDKerrbuf == NULL)
+		GDKsetbuf(calloc(1, GDKMAXERRLEN));
+	return 0;
 }
 
 void

@@ -137,7 +137,18 @@ def init(nthreads: int = 0):
 
 
 def errbuf() -> str:
-    return (_h.refh_errbuf() or b"").decode()
+    """the GDKerror text of the last failure, without the tracer's "!ERROR: function: " prefix"""
+    raw = (_h.refh_errbuf() or b"").decode()
+    lines = [ln for ln in raw.splitlines() if ln.strip()]
+    if not lines:
+        return ""
+    msg = lines[-1]
+    if msg.startswith("!ERROR: "):
+        msg = msg[len("!ERROR: "):]
+        head, sep, tail = msg.partition(": ")
+        if sep and " " not in head:
+            msg = tail
+    return msg
 
 
 def clrerr():

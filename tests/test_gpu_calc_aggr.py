@@ -1,0 +1,228 @@
+"""BATcalc arithmetic, BATconvert, BATsum, BATgroupsum/avg/count: CUDA path vs
+the real reference GDK.  Integer results bit-exact, error texts identical;
+flt/dbl sums within 1e-12 (dbl) / 1e-5 (flt) relative as BASELINE.json states."""
+import numpy as np
+import pytest
+
+from tests.util import ALL_TYPES, INT_TYPES, assert_same, both, random_col, same_bits
+from monetdb_b200 import gdk as G
+
+pytestmark = pytest.mark.gpu
+T = G.TYPE
+RANK = {T.bte: 0, T.sht: 1, T.int: 2, T.lng: 3, T.hge: 4, T.flt: 5, T.dbl: 6}
+
+
+def _int_triples():
+    for t1 in INT_TYPES:
+        for t2 in INT_TYPES:
+            for t3 in INT_TYPES:
+                if RANK[t3] >= max(RANK[t1], RANK[t2]):
+                    yield t1, t2, t3
+
+
+def _cmp_or_err(gdk, ref, fo, fr):
+    """run both sides; either both succeed with identical bits or both fail with the same text"""
+    try:
+        r = fr()
+    except ref.RefError as e:
+        with pytest.raises(G.GDKError) as ei:
+            fo()
+        assert str(ei.value).strip() == str(e).strip(), (str(ei.value), str(e))
+        return None
+    o = fo()
+    assert_same(o, r)
+    return o
+
+
+@pytest.mark.parametrize("op", ["add", "sub", "mul", "div"])
+def test_calc_int_matrix(gdk, ref, op):
+    rng = np.random.default_rng(42)
+    n = 4099
+    for t1, t2, t3 in _int_triples():
+        a1 = random_col(rng, t1, n, nilfrac=0.03, lo=-11, hi=11)
+        a2 = random_col(rng, t2, n, nilfrac=0.03, lo=1 if op == "div" else -11, hi=11)
+        b1, r1 = both(gdk, ref, a1, t1)
+        b2, r2 = both(gdk, ref, a2, t2)
+        _cmp_or_err(gdk, ref, lambda: gdk.BATcalc(op, b1, b2, None, None, t3), lambda: ref.BATcalc(op, r1, r2, None, None, t3))
+
+
+@pytest.mark.parametrize("op", ["add", "sub", "mul"])
+@pytest.mark.parametrize("tt", INT_TYPES)
+def test_calc_overflow_message(gdk, ref, op, tt):
+    """first overflowing row aborts with the reference's text"""
+    rng = np.random.default_rng(1)
+    n = 10007
+    mx = (1 << (8 * G.NP_OF[tt].itemsize - 1)) - 1
+    if tt == T.hge:
+        a1 = [int(x) for x in rng.integers(-5, 5, n)]
+        a2 = [int(x) for x in rng.integers(-5, 5, n)]
+        a1[5003], a2[5003] = mx - 1, (-mx if op == "sub" else mx)
+        a1[7001], a2[7001] = mx, mx
+        a1, a2 = G.hge_from_ints(a1), G.hge_from_ints(a2)
+    else:
+        a1 = rng.integers(-5, 5, n).astype(G.NP_OF[tt])
+        a2 = rng.integers(-5, 5, n).astype(G.NP_OF[tt])
+        a1[5003], a2[5003] = mx - 1, (-mx if op == "sub" else mx)
+        a1[7001], a2[7001] = mx, mx
+    b1, r1 = both(gdk, ref, a1, tt)
+    b2, r2 = both(gdk, ref, a2, tt)
+    with pytest.raises(ref.RefError) as er:
+        ref.BATcalc(op, r1, r2, None, None, tt)
+    with pytest.raises(G.GDKError) as eo:
+        gdk.BATcalc(op, b1, b2, None, None, tt)
+    assert "22003!overflow in calculation" in str(eo.value)
+    assert str(eo.value).strip() == str(er.value).strip()
+
+
+def test_calc_div_by_zero(gdk, ref):
+    a1 = np.array([4, 5, 6], dtype=np.int64)
+    a2 = np.array([2, 0, 3], dtype=np.int64)
+    b1, r1 = both(gdk, ref, a1, T.lng)
+    b2, r2 = both(gdk, ref, a2, T.lng)
+    with pytest.raises(G.GDKError, match="22012!division by zero"):
+        gdk.BATcalc("div", b1, b2, None, None, T.lng)
+    with pytest.raises(ref.RefError, match="22012!division by zero"):
+        ref.BATcalc("div", r1, r2, None, None, T.lng)
+
+
+@pytest.mark.parametrize("op", ["add", "sub", "mul", "div"])
+def test_calc_float(gdk, ref, op):
+    rng = np.random.default_rng(7)
+    n = 5003
+    combos = [(T.flt, T.flt, T.flt), (T.flt, T.flt, T.dbl), (T.dbl, T.dbl, T.dbl), (T.flt, T.dbl, T.dbl), (T.dbl, T.flt, T.dbl),
+              (T.int, T.flt, T.flt), (T.lng, T.dbl, T.dbl), (T.dbl, T.int, T.dbl), (T.int, T.int, T.dbl), (T.lng, T.lng, T.flt),
+              (T.hge, T.dbl, T.dbl), (T.bte, T.sht, T.flt)]
+    for t1, t2, t3 in combos:
+        a1 = random_col(rng, t1, n, nilfrac=0.03, lo=-100, hi=100)
+        a2 = random_col(rng, t2, n, nilfrac=0.03, lo=1, hi=100)
+        b1, r1 = both(gdk, ref, a1, t1)
+        b2, r2 = both(gdk, ref, a2, t2)
+        _cmp_or_err(gdk, ref, lambda: gdk.BATcalc(op, b1, b2, None, None, t3), lambda: ref.BATcalc(op, r1, r2, None, None, t3))
+
+
+@pytest.mark.parametrize("op", ["add", "sub", "mul", "div"])
+def test_calc_cst_and_candidates(gdk, ref, op):
+    rng = np.random.default_rng(9)
+    n = 30011
+    a = random_col(rng, T.lng, n, nilfrac=0.02, lo=-1000, hi=1000)
+    b, rb = both(gdk, ref, a, T.lng, hseq=4)
+    o = np.sort(rng.choice(n, n // 3, replace=False)).astype(np.uint64) + np.uint64(4)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    for cand, rcand in ((None, None), (s, rs), (gdk.BATdense(0, 104, 999), ref.dense(0, 104, 999))):
+        for first in (False, True):
+            for tp in (T.lng, T.hge):
+                _cmp_or_err(gdk, ref, lambda: gdk.BATcalccst(op, b, 100, T.lng, cand, tp, cst_first=first),
+                            lambda: ref.BATcalccst(op, rb, 100, T.lng, rcand, tp, cst_first=first))
+    # two BATs through different candidate lists of equal size
+    a2 = random_col(rng, T.int, n, lo=1, hi=50)
+    b2, rb2 = both(gdk, ref, a2, T.int, hseq=4)
+    _cmp_or_err(gdk, ref, lambda: gdk.BATcalc(op, b, b2, s, s, T.hge), lambda: ref.BATcalc(op, rb, rb2, rs, rs, T.hge))
+    with pytest.raises(G.GDKError, match="inputs not the same size"):
+        gdk.BATcalc(op, b, b2, s, None, T.hge)
+
+
+@pytest.mark.parametrize("t1", ALL_TYPES)
+@pytest.mark.parametrize("t2", ALL_TYPES)
+def test_convert(gdk, ref, t1, t2):
+    rng = np.random.default_rng(t1 * 16 + t2)
+    a = random_col(rng, t1, 10007, nilfrac=0.03, lo=-120, hi=120)
+    b, rb = both(gdk, ref, a, t1)
+    _cmp_or_err(gdk, ref, lambda: gdk.BATconvert(b, None, t2), lambda: ref.BATconvert(rb, None, t2))
+    a = random_col(rng, t1, 1009, nilfrac=0.0, lo=-30000, hi=30000) if RANK[t1] >= 1 else a
+    b, rb = both(gdk, ref, a, t1)
+    s, rs = gdk.BATdense(0, 10, 500), ref.dense(0, 10, 500)
+    _cmp_or_err(gdk, ref, lambda: gdk.BATconvert(b, s, t2), lambda: ref.BATconvert(rb, rs, t2))
+
+
+def _sum_types(t1):
+    if t1 in INT_TYPES:
+        return [t for t in INT_TYPES if RANK[t] >= RANK[t1]] + [T.dbl]
+    return [T.flt, T.dbl] if t1 == T.flt else [T.dbl]
+
+
+def _close(a, b, tt):
+    tol = 1e-5 if tt == T.flt else 1e-12
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    m = ~np.isnan(a)
+    assert np.all(np.abs(a[m] - b[m]) <= tol * np.maximum(np.abs(b[m]), 1e-300)), (a[m][:5], b[m][:5])
+
+
+@pytest.mark.parametrize("t1", ALL_TYPES)
+def test_batsum(gdk, ref, t1):
+    rng = np.random.default_rng(t1)
+    for n in (0, 1, 1000, 200003):
+        for nilfrac in (0.0, 0.1):
+            a = random_col(rng, t1, n, nilfrac=nilfrac, lo=-100, hi=100)
+            b, rb = both(gdk, ref, a, t1)
+            for tp in _sum_types(t1):
+                for skip in (True, False):
+                    try:
+                        r = ref.BATsum(tp, rb, None, skip, True)
+                    except ref.RefError as e:
+                        with pytest.raises(G.GDKError) as ei:
+                            gdk.BATsum(tp, b, None, skip, True)
+                        assert str(ei.value).strip() == str(e).strip()
+                        continue
+                    o = gdk.BATsum(tp, b, None, skip, True)
+                    if tp in (T.flt, T.dbl):
+                        _close(o, r, tp)
+                    else:
+                        assert same_bits(o, r), (t1, tp, n, nilfrac, skip, o, r)
+
+
+def test_batsum_overflow_and_transient(gdk, ref):
+    """running-prefix overflow semantics of AGGR_SUM: a transient overflow errors even if the total fits"""
+    mx = (1 << 63) - 1
+    cases = [np.array([mx, 1, -5], dtype=np.int64),          # prefix overflows, total fits -> error
+             np.array([mx - 10, -20, 15], dtype=np.int64),   # P > max but no prefix overflows -> ok
+             np.array([-mx, -1, 5], dtype=np.int64),
+             np.array([mx, -mx, mx, -mx, 3], dtype=np.int64)]
+    for a in cases:
+        b, rb = both(gdk, ref, a, T.lng)
+        try:
+            r = ref.BATsum(T.lng, rb)
+        except ref.RefError as e:
+            with pytest.raises(G.GDKError, match="22003!overflow in sum aggregate"):
+                gdk.BATsum(T.lng, b)
+            continue
+        assert same_bits(gdk.BATsum(T.lng, b), r), a
+
+
+@pytest.mark.parametrize("ngrp", [1, 3, 4, 8, 9, 500, 7000, 100000])
+@pytest.mark.parametrize("t1", [T.bte, T.int, T.lng, T.hge, T.dbl])
+def test_groupsum_avg_count(gdk, ref, ngrp, t1):
+    rng = np.random.default_rng(ngrp + t1)
+    n = 120011
+    a = random_col(rng, t1, n, nilfrac=0.05, lo=-1000 if t1 != T.bte else -100, hi=1000 if t1 != T.bte else 100)
+    gids = rng.integers(0, ngrp, n, dtype=np.uint64)
+    b, rb = both(gdk, ref, a, t1, hseq=2)
+    g, rg = both(gdk, ref, gids, T.oid, hseq=2)
+    e, re_ = gdk.BATdense(0, 0, ngrp), ref.dense(0, 0, ngrp)   # extents: only count/hseqbase are used
+    for skip in (True, False):
+        for tp in _sum_types(t1):
+            if tp == T.dbl and t1 in INT_TYPES:
+                continue
+            try:
+                r = ref.BATgroupsum(rb, rg, re_, None, tp, skip)
+            except ref.RefError as ex:
+                with pytest.raises(G.GDKError) as ei:
+                    gdk.BATgroupsum(b, g, e, None, tp, skip)
+                assert str(ei.value).strip() == str(ex).strip()
+                continue
+            o = gdk.BATgroupsum(b, g, e, None, tp, skip)
+            if tp in (T.flt, T.dbl):
+                _close(o.numpy(), r.numpy(), tp)
+            else:
+                assert_same(o, r)
+        r, rc = ref.BATgroupavg(rb, rg, re_, None, T.dbl, skip, 2)
+        o, oc = gdk.BATgroupavg(b, g, e, None, T.dbl, skip, 2)
+        if t1 in INT_TYPES:
+            assert same_bits(o.numpy(), r.numpy())
+        else:
+            _close(o.numpy(), r.numpy(), T.dbl)
+        assert same_bits(oc.numpy(), rc.numpy())
+        assert_same(gdk.BATgroupcount(b, g, e, None, T.lng, skip), ref.BATgroupcount(rb, rg, re_, None, T.lng, skip))
+    # without extents: the group range comes from scanning g
+    assert_same(gdk.BATgroupsum(b, g, None, None, T.hge if t1 in INT_TYPES else T.dbl, True),
+                ref.BATgroupsum(rb, rg, None, None, T.hge if t1 in INT_TYPES else T.dbl, True)) if t1 in INT_TYPES else None

@@ -1,0 +1,139 @@
+"""BATselect / BATthetaselect / BATproject / candidate algebra: CUDA path vs the
+real reference GDK (oracle/_ref) on identical inputs, bit-exact oid lists.
+Matrix follows monetdb5/modules/kernel/Tests/select.maltest (li/hi/anti/nil)."""
+import itertools
+
+import numpy as np
+import pytest
+
+from tests.util import ALL_TYPES, assert_same, both, random_col, same_bits
+from monetdb_b200 import gdk as G
+
+pytestmark = pytest.mark.gpu
+
+
+def test_select_maltest_matrix(gdk, ref):
+    """values {7,6,8,nil,9,5,0,3,2,1,4} as in select.maltest, all li/hi/anti/nil_matches, bounds incl. nil"""
+    nil = G.nil_of(G.TYPE.int)
+    vals = np.array([7, 6, 8, nil, 9, 5, 0, 3, 2, 1, 4], dtype=np.int32)
+    for arr, pr in ((vals, {}), (np.sort(vals), dict(sorted=True)), (np.sort(vals)[::-1].copy(), dict(revsorted=True))):
+        b, rb = both(gdk, ref, arr, G.TYPE.int, **pr)
+        for tl, th in itertools.product([nil, 0, 3, 7, 9], [None, nil, 0, 3, 7, 9]):
+            for li, hi, anti, nm in itertools.product([False, True], repeat=4):
+                r = ref.BATselect(rb, None, tl, th, li, hi, anti, nm)
+                o = gdk.BATselect(b, None, tl, th, li, hi, anti, nm)
+                assert same_bits(o.numpy(), r.numpy()), (tl, th, li, hi, anti, nm, o.numpy(), r.numpy())
+
+
+@pytest.mark.parametrize("tt", ALL_TYPES)
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 32, 33, 4097, 65535, 65537, 300001])
+def test_select_random(gdk, ref, tt, n):
+    rng = np.random.default_rng(n * 31 + tt)
+    arr = random_col(rng, tt, n, nilfrac=0.05 if n > 2 else 0.0, lo=-100, hi=100)
+    b, rb = both(gdk, ref, arr, tt, hseq=7)
+    for (tl, th, li, hi, anti) in [(-50, 50, True, True, False), (-50, 50, False, False, True), (10, None, True, True, False),
+                                   (10, None, True, True, True), (G.nil_of(tt), 20, False, True, False),
+                                   (-20, G.nil_of(tt), True, False, False), (G.nil_of(tt), None, True, True, False)]:
+        r = ref.BATselect(rb, None, tl, th, li, hi, anti, False)
+        o = gdk.BATselect(b, None, tl, th, li, hi, anti, False)
+        assert_same(o, r, props=("count", "hseq"), exact_props=())
+
+
+@pytest.mark.parametrize("op", ["=", "==", "!=", "<>", "<", "<=", ">", ">=", "eq", "ne"])
+def test_thetaselect(gdk, ref, op):
+    rng = np.random.default_rng(5)
+    arr = random_col(rng, G.TYPE.lng, 100003, nilfrac=0.02, lo=-20, hi=20)
+    b, rb = both(gdk, ref, arr, G.TYPE.lng)
+    for v in (3, G.nil_of(G.TYPE.lng)):
+        assert same_bits(gdk.BATthetaselect(b, None, v, op).numpy(), ref.BATthetaselect(rb, None, v, op).numpy())
+
+
+def _cands(gdk, ref, kind, n, rng, hseq=0):
+    if kind == "dense":
+        lo, cnt = hseq + n // 7, n // 2
+        return gdk.BATdense(0, lo, cnt), ref.dense(0, lo, cnt)
+    if kind == "oids":
+        o = np.sort(rng.choice(n, size=max(1, n // 3), replace=False)).astype(np.uint64) + np.uint64(hseq)
+        return (gdk.BATfromhost(o, G.TYPE.oid, sorted=True, key=True, nonil=True),
+                ref.bat(o, G.TYPE.oid, sorted=True, key=True, nonil=True))
+    if kind == "neg":
+        e = np.sort(rng.choice(n, size=max(1, n // 10), replace=False)).astype(np.uint64) + np.uint64(hseq)
+        return gdk.BATnegcands(hseq, n, e), ref.negcands(hseq, n, e)
+    if kind == "mask":
+        w = rng.integers(0, 1 << 32, (n + 31) // 32, dtype=np.uint64).astype(np.uint32)
+        return gdk.BATmaskedcands(hseq, n, w, True), ref.maskedcands(hseq, n, w, True)
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("kind", ["dense", "oids", "neg", "mask"])
+@pytest.mark.parametrize("tt", [G.TYPE.bte, G.TYPE.int, G.TYPE.lng, G.TYPE.hge, G.TYPE.dbl])
+def test_select_with_candidates(gdk, ref, kind, tt):
+    rng = np.random.default_rng(11)
+    n = 50021
+    arr = random_col(rng, tt, n, nilfrac=0.03, lo=-100, hi=100)
+    b, rb = both(gdk, ref, arr, tt, hseq=3)
+    s, rs = _cands(gdk, ref, kind, n, rng, hseq=3)
+    for (tl, th, li, hi, anti) in [(-30, 30, True, False, False), (-30, 30, True, True, True), (5, None, True, True, False)]:
+        o = gdk.BATselect(b, s, tl, th, li, hi, anti, False)
+        r = ref.BATselect(rb, rs, tl, th, li, hi, anti, False)
+        assert same_bits(o.numpy(), r.numpy()), (kind, tl, th)
+    # chained selection: the result of one select is the candidate list of the next
+    o1, r1 = gdk.BATselect(b, s, -50, 50, True, True, False), ref.BATselect(rb, rs, -50, 50, True, True, False)
+    o2, r2 = gdk.BATthetaselect(b, o1, 0, ">="), ref.BATthetaselect(rb, r1, 0, ">=")
+    assert same_bits(o2.numpy(), r2.numpy())
+
+
+def test_select_dense_result_is_void(gdk, ref):
+    arr = np.arange(1000, dtype=np.int32)
+    b, rb = both(gdk, ref, arr, G.TYPE.int, sorted=True, key=True)
+    o, r = gdk.BATselect(b, None, 100, 199, True, True, False), ref.BATselect(rb, None, 100, 199, True, True, False)
+    assert o.props()["type"] == G.TYPE.void and o.props()["tseq"] == r.props()["tseq"] == 100
+    assert len(o) == len(r) == 100
+
+
+@pytest.mark.parametrize("tt", ALL_TYPES)
+def test_project(gdk, ref, tt):
+    rng = np.random.default_rng(tt)
+    n = 70001
+    arr = random_col(rng, tt, n, nilfrac=0.02)
+    r_, rr = both(gdk, ref, arr, tt, hseq=5)
+    for kind in ("dense", "oids", "neg", "mask"):
+        l, rl = _cands(gdk, ref, kind, n, rng, hseq=5)
+        assert_same(gdk.BATproject(l, r_), ref.BATproject(rl, rr), exact_props=("nonil",))
+    # unsorted oids with nils
+    o = rng.integers(5, 5 + n, 1000, dtype=np.uint64)
+    o[::17] = G.oid_nil
+    l, rl = both(gdk, ref, o, G.TYPE.oid)
+    assert same_bits(gdk.BATproject(l, r_).numpy(), ref.BATproject(rl, rr).numpy())
+
+
+def test_project_out_of_range(gdk, ref):
+    arr = np.arange(10, dtype=np.int32)
+    r_, rr = both(gdk, ref, arr, G.TYPE.int)
+    o = np.array([1, 2, 30], dtype=np.uint64)
+    l, rl = both(gdk, ref, o, G.TYPE.oid)
+    with pytest.raises(G.GDKError, match="does not match always"):
+        gdk.BATproject(l, r_)
+    with pytest.raises(ref.RefError, match="does not match always"):
+        ref.BATproject(rl, rr)
+
+
+def test_project2(gdk, ref):
+    a1, a2 = np.arange(100, dtype=np.int64), np.arange(1000, 1050, dtype=np.int64)
+    r1, rr1 = both(gdk, ref, a1, G.TYPE.lng)
+    r2, rr2 = both(gdk, ref, a2, G.TYPE.lng, hseq=100)
+    o = np.array([0, 149, 99, 100, 5], dtype=np.uint64)
+    l, rl = both(gdk, ref, o, G.TYPE.oid)
+    assert same_bits(gdk.BATproject2(l, r1, r2).numpy(), ref.BATproject2(rl, rr1, rr2).numpy())
+
+
+@pytest.mark.parametrize("ka", ["dense", "oids", "neg", "mask"])
+@pytest.mark.parametrize("kb", ["dense", "oids", "neg"])
+def test_cand_algebra(gdk, ref, ka, kb):
+    rng = np.random.default_rng(3)
+    n = 20011
+    a, ra = _cands(gdk, ref, ka, n, rng)
+    b, rb = _cands(gdk, ref, kb, n, rng)
+    assert same_bits(gdk.BATmergecand(a, b).numpy(), ref.BATmergecand(ra, rb).numpy())
+    assert same_bits(gdk.BATintersectcand(a, b).numpy(), ref.BATintersectcand(ra, rb).numpy())
+    assert same_bits(gdk.BATdiffcand(a, b).numpy(), ref.BATdiffcand(ra, rb).numpy())
