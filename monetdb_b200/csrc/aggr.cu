@@ -334,7 +334,7 @@ static void agg_props(b200_bat *bn, uint64_t nils)
 static bool singleton_groups(const AggrSetup &a)
 {
 	/* every candidate row is its own group (gdk_aggr.c:929-935) */
-	return (a.e == nullptr || (a.e->count == a.ci.ncand && a.e->hseqbase == a.ci.hseq)) &&
+	return (a.e == nullptr || (a.e->count == a.ci.ncand && a.e->hseqbase == a.ci.rhseq)) &&
 	       (bat_is_dense(a.g) || (a.g->tkey && a.g->tnonil));
 }
 

@@ -42,7 +42,7 @@ static b200_bat *calc_binary(int op, int mode, const b200_bat *b1, const b200_ba
 	if (mode == 0) {
 		if (!cand_init(ci2, b2, ss2.b))
 			return nullptr;
-		if (ci1.ncand != ci2.ncand || ci1.hseq != ci2.hseq) {
+		if (ci1.ncand != ci2.ncand || ci1.rhseq != ci2.rhseq) {
 			/* gdk_calc_addsub.c:1494, gdk_calc_mul.c:2041 */
 			if (op >= OP_MUL)
 				set_err("%s: inputs not the same size.\n", func);
@@ -57,7 +57,7 @@ static b200_bat *calc_binary(int op, int mode, const b200_bat *b1, const b200_ba
 			atomname(b1->ttype), atomname(mode == 0 ? b2->ttype : csttype), atomname(tp));
 		return nullptr;
 	}
-	b200_bat *bn = bat_new(ci1.hseq, tp, ci1.ncand);
+	b200_bat *bn = bat_new(ci1.rhseq, tp, ci1.ncand);
 	if (bn == nullptr)
 		return nullptr;
 	if (ci1.ncand == 0)

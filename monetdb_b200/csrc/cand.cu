@@ -103,6 +103,7 @@ bool cand_init(Cand &ci, const b200_bat *b, const b200_bat *s)
 	const oid blo = b ? b->hseqbase : 0;
 	const oid bhi = b ? b->hseqbase + b->count : ~(oid) 0;
 	ci.hseq = blo;
+	ci.rhseq = blo;
 	ci.dense = true;
 	ci.oids = nullptr;
 	if (s == nullptr) {
@@ -110,7 +111,10 @@ bool cand_init(Cand &ci, const b200_bat *b, const b200_bat *s)
 		ci.ncand = b ? b->count : 0;
 		return true;
 	}
-	if (s->count == 0) {
+	/* ci->hseq of the reference: s->hseqbase + leading candidates clipped away
+	 * (gdk_cand.c:440-457,711); 0 when nothing overlaps (:603-611) */
+	ci.rhseq = s->hseqbase;
+	if (s->count == 0 || (b != nullptr && b->count == 0)) {
 		ci.seq = blo;
 		ci.ncand = 0;
 		return true;
@@ -151,6 +155,11 @@ bool cand_init(Cand &ci, const b200_bat *b, const b200_bat *s)
 		oid hi = s->tseqbase + n < bhi ? s->tseqbase + n : bhi;
 		ci.seq = lo;
 		ci.ncand = hi > lo ? hi - lo : 0;
+		if (ci.ncand == 0) {
+			ci.seq = blo;
+			ci.rhseq = 0;
+		} else
+			ci.rhseq = s->hseqbase + (lo - s->tseqbase);
 		return true;
 	} else {
 		if (basetype(s->ttype) != B200_lng) {
@@ -179,10 +188,13 @@ bool cand_init(Cand &ci, const b200_bat *b, const b200_bat *s)
 		last = c->slot_h->v[3];
 		oids += lo;
 		n = hi - lo;
+		if (s->ccand != B200_CAND_MSK)
+			ci.rhseq = s->hseqbase + lo;
 	}
 	if (n == 0) {
 		ci.seq = blo;
 		ci.ncand = 0;
+		ci.rhseq = 0;
 		return true;
 	}
 	ci.ncand = n;

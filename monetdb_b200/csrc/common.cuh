@@ -154,6 +154,7 @@ struct Cand {
 	const oid *oids = nullptr;	/* device array (non-dense) */
 	uint64_t ncand = 0;
 	oid hseq = 0;			/* b->hseqbase: row index = oid - hseq */
+	oid rhseq = 0;			/* the reference's ci->hseq: hseqbase of a result aligned with the candidates */
 	void *owned = nullptr;		/* temp expansion to free */
 	~Cand() { if (owned) dev_free(owned); }
 };

@@ -154,7 +154,7 @@ extern "C" b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int t
 	if (!cand_init(ci, b, ss.b))
 		return nullptr;
 	if (ci.ncand == 0 || (b->ttype == B200_void && b->tseqbase == OID_NIL))
-		return bat_constant(ci.hseq, tp, nullptr, ci.ncand);
+		return bat_constant(ci.rhseq, tp, nullptr, ci.ncand);
 	if (scale1 != 0 || scale2 != 0 || precision != 0 || tp == B200_bit || tp == B200_oid || tp == B200_msk ||
 	    b->ttype == B200_void || b->ttype == B200_msk || b->ttype == B200_oid) {
 		set_err("BATconvert: decimal rescaling and bit/oid/msk conversions are not on the device path "
@@ -166,7 +166,7 @@ extern "C" b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int t
 		set_err("type combination (convert(%s)->%s) not supported.\n", atomname(b->ttype), atomname(tp));
 		return nullptr;
 	}
-	b200_bat *bn = bat_new(ci.hseq, tp, ci.ncand);
+	b200_bat *bn = bat_new(ci.rhseq, tp, ci.ncand);
 	if (bn == nullptr)
 		return nullptr;
 	uint64_t nils = 0;
