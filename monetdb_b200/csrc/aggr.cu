@@ -45,16 +45,8 @@ __global__ void fexp_kernel(AggrIn in, int *__restrict__ out)
 		atomicMax(out, best);
 }
 
-struct AggrSetup {
-	Staged sb, sg, se, ss;
-	Cand ci;
-	const b200_bat *b = nullptr, *g = nullptr, *e = nullptr;
-	oid min = 0, max = 0;
-	uint64_t ngrp = 0;
-};
-
 // BATgroupaggrinit.  g == NULL: one group (BATsum).  Returns false with the error set.
-static bool aggr_init(AggrSetup &a, const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s)
+bool aggr_init(AggrSetup &a, const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s)
 {
 	if (b == nullptr) {
 		set_err("b must exist\n");
@@ -391,11 +383,11 @@ extern "C" b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b
 				return B200_FAIL;
 			lng *cn = (lng *) (out + 1);
 			switch (t1) {
-			case B200_bte: aggr_finish_avg_kernel<bte><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state); break;
-			case B200_sht: aggr_finish_avg_kernel<sht><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state); break;
-			case B200_int: aggr_finish_avg_kernel<int><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state); break;
-			case B200_lng: aggr_finish_avg_kernel<lng><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state); break;
-			case B200_hge: aggr_finish_avg_kernel<hge><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state); break;
+			case B200_bte: aggr_finish_avg_kernel<bte><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state, true); break;
+			case B200_sht: aggr_finish_avg_kernel<sht><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state, true); break;
+			case B200_int: aggr_finish_avg_kernel<int><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state, true); break;
+			case B200_lng: aggr_finish_avg_kernel<lng><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state, true); break;
+			case B200_hge: aggr_finish_avg_kernel<hge><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, 0, 1.0, out, cn, acc.state, true); break;
 			}
 			COUNT_LAUNCH();
 			bool ok = cuda_ok(cudaMemcpyAsync(&c->slot_h->v[8], out, 16, cudaMemcpyDeviceToHost, c->stream), "read") && stream_sync();

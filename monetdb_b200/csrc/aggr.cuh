@@ -23,6 +23,7 @@
 //   GLB   otherwise     global REDs straight into the cell table
 #pragma once
 #include "common.cuh"
+#include "aggr_init.cuh"
 #include <type_traits>
 
 typedef unsigned long long u64;
@@ -426,7 +427,8 @@ __global__ void aggr_finish_sum_kernel(const u64 *__restrict__ cells, unsigned n
 		/* single group: any nil; several groups: a nil after the group's first value
 		 * (AGGR_SUM resets sums[gid] when it sees the first value, gdk_aggr.c:516-520) */
 		if (lastnil != 0)
-			isnil = ngrp == 1 || cnt == 0 || lastnil - 1 > first;
+			isnil = float_in /* dofsum: any nil ends the group, gdk_aggr.c:253-264 */ ||
+				ngrp == 1 || cnt == 0 || lastnil - 1 > first;
 		if (lastnil != 0)
 			atomicAdd(&state[3], 1ULL);	/* the reference counts nils as it meets them */
 	}
@@ -436,24 +438,28 @@ __global__ void aggr_finish_sum_kernel(const u64 *__restrict__ cells, unsigned n
 			res = 0;
 		else
 			isnil = true;
-	} else if (!isnil) {
+	} else {
 		const I192 S = i192_from_cells(cells + g, ngrp, nd);
 		if constexpr (Atom<T2>::is_float) {
-			double r = i192_to_double(S, fexp - 125);
-			if constexpr (sizeof(T2) == 4) {
-				res = (flt) r;
-				if (isinf(res) || isnan(res))
-					atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
-			} else {
-				res = r;
-				if (isinf(r) || isnan(r))
-					atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
+			if (!isnil) {
+				double r = i192_to_double(S, fexp - 125);
+				if constexpr (sizeof(T2) == 4) {
+					res = (flt) r;
+					if (isinf(res) || isnan(res))
+						atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
+				} else {
+					res = r;
+					if (isinf(r) || isnan(r))
+						atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
+				}
 			}
 		} else {
 			constexpr int bits = OutBits<T2>::bits;
-			if (!i192_fits(S, bits)) {
+			if (!isnil && !i192_fits(S, bits)) {
 				atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
 			} else if (check) {
+				/* also for groups that end up nil: the reference adds (and checks) the
+				 * values it meets before the nil that ends the group */
 				const I192 P = i192_from_cells(cells + (size_t) nd * ngrp + g, ngrp, nd);
 				const I192 M = i192_sub(P, S);
 				if (!i192_fits(P, bits) || !i192_fits(M, bits)) {
@@ -461,10 +467,12 @@ __global__ void aggr_finish_sum_kernel(const u64 *__restrict__ cells, unsigned n
 					exactlist[slot] = g;
 				}
 			}
-			if constexpr (sizeof(T2) == 16)
-				res = i192_to_hge(S);
-			else
-				res = (T2) (i64) S.w[0];
+			if (!isnil) {
+				if constexpr (sizeof(T2) == 16)
+					res = i192_to_hge(S);
+				else
+					res = (T2) (i64) S.w[0];
+			}
 		}
 	}
 	if (isnil) {
@@ -477,7 +485,8 @@ __global__ void aggr_finish_sum_kernel(const u64 *__restrict__ cells, unsigned n
 // integer / float average as dbl, plus counts (gdk_aggr.c:1717-1787, 1952-1957)
 template <typename T1>
 __global__ void aggr_finish_avg_kernel(const u64 *__restrict__ cells, unsigned ngrp, bool niltrack, int fexp, double fac,
-				       dbl *__restrict__ out, lng *__restrict__ cnts, u64 *__restrict__ state)
+				       dbl *__restrict__ out, lng *__restrict__ cnts, u64 *__restrict__ state,
+				       bool plain = false /* BATcalcavg: (dbl) sum / n while the sum fits a hge (gdk_aggr.c:2924) */)
 {
 	const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= ngrp)
@@ -499,6 +508,10 @@ __global__ void aggr_finish_avg_kernel(const u64 *__restrict__ cells, unsigned n
 	if constexpr (Atom<T1>::is_float) {
 		r = i192_to_double(S, fexp - 125) / (double) n;
 	} else {
+		if (plain && i192_fits(S, 128)) {
+			out[g] = (double) i192_to_hge(S) / (double) (lng) n;
+			return;
+		}
 		/* a = floor(S / n), rem = S - a * n  (0 <= rem < n), n < 2^32 */
 		const bool neg = S.neg();
 		I192 m = neg ? i192_neg(S) : S;
@@ -579,42 +592,79 @@ __device__ static inline Pfx pfx_compose(const Pfx &a, const Pfx &b)
 	r.mn = i192_less(t, a.mn) ? t : a.mn;
 	return r;
 }
+// With skip_nils == false a nil ends a group's summation: in the single-group loops
+// the first nil (gdk_aggr.c:447-452,481-486), in the grouped loops the first nil
+// that follows the group's first value (:506-525); only the values met before
+// that point are added and checked.  seen / lead / stopped carry that through the
+// ordered reduction.
+struct PfxN {
+	Pfx p;
+	unsigned char seen, lead, stopped;
+};
+__device__ static inline PfxN pfxn_compose(const PfxN &a, const PfxN &b, bool single)
+{
+	if (a.stopped)
+		return a;
+	if (b.lead && (a.seen || single)) {
+		PfxN r = a;
+		r.stopped = 1;
+		return r;
+	}
+	PfxN r;
+	r.p = pfx_compose(a.p, b.p);
+	r.seen = a.seen | b.seen;
+	r.lead = a.lead | (!a.seen && b.lead);
+	r.stopped = b.stopped;
+	return r;
+}
 template <typename T1>
 __global__ void __launch_bounds__(256)
 aggr_exact_check_kernel(AggrIn in, const unsigned *__restrict__ exactlist, int bits, u64 *__restrict__ state)
 {
 	constexpr int R = 8;
-	__shared__ Pfx sh[256];
+	__shared__ PfxN sh[256];
 	const oid want = in.gmin + exactlist[blockIdx.x];
-	Pfx run = {{{0, 0, 0}}, {{0, 0, 0}}, {{0, 0, 0}}};
+	const bool single = in.gmin == in.gmax, stop_on_nil = !in.skip_nils;
+	const PfxN zero = {{{{0, 0, 0}}, {{0, 0, 0}}, {{0, 0, 0}}}, 0, 0, 0};
+	PfxN run = zero;
 	for (uint64_t base = 0; base < in.n; base += 256 * R) {
-		Pfx p = {{{0, 0, 0}}, {{0, 0, 0}}, {{0, 0, 0}}};
+		PfxN q = zero;
 		for (int r = 0; r < R; r++) {
 			const uint64_t k = base + (uint64_t) threadIdx.x * R + r;
 			T1 x;
 			oid gid;
-			if (k >= in.n || !aggr_fetch<T1>(in, k, x, gid) || gid != want || Atom<T1>::is_nil(x))
+			if (k >= in.n || !aggr_fetch<T1>(in, k, x, gid) || gid != want || q.stopped)
 				continue;
+			if (Atom<T1>::is_nil(x)) {
+				if (stop_on_nil) {
+					if (q.seen || single)
+						q.stopped = 1;
+					if (!q.seen)
+						q.lead = 1;
+				}
+				continue;
+			}
 			I192 v;
 			hge hx = (hge) x;
 			v.w[0] = (u64) hx;
 			v.w[1] = (u64) (hx >> 64);
 			v.w[2] = hx < 0 ? ~0ULL : 0;
-			p.s = i192_add(p.s, v);
-			if (i192_less(p.mx, p.s)) p.mx = p.s;
-			if (i192_less(p.s, p.mn)) p.mn = p.s;
+			q.p.s = i192_add(q.p.s, v);
+			if (i192_less(q.p.mx, q.p.s)) q.p.mx = q.p.s;
+			if (i192_less(q.p.s, q.p.mn)) q.p.mn = q.p.s;
+			q.seen = 1;
 		}
-		sh[threadIdx.x] = p;
+		sh[threadIdx.x] = q;
 		__syncthreads();
 		for (int st = 1; st < 256; st <<= 1) {
 			if ((threadIdx.x % (2 * st)) == 0)
-				sh[threadIdx.x] = pfx_compose(sh[threadIdx.x], sh[threadIdx.x + st]);
+				sh[threadIdx.x] = pfxn_compose(sh[threadIdx.x], sh[threadIdx.x + st], single);
 			__syncthreads();
 		}
 		if (threadIdx.x == 0)
-			run = pfx_compose(run, sh[0]);
+			run = pfxn_compose(run, sh[0], single);
 		__syncthreads();
 	}
-	if (threadIdx.x == 0 && (!i192_fits(run.mx, bits) || !i192_fits(run.mn, bits)))
+	if (threadIdx.x == 0 && (!i192_fits(run.p.mx, bits) || !i192_fits(run.p.mn, bits)))
 		atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
 }

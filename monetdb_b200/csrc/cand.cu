@@ -73,6 +73,7 @@ struct MaskBitF {
 		o = base + idx;
 		return (words[idx >> 5] >> (idx & 31)) & 1u;
 	}
+	__device__ oid at(uint64_t idx) const { return base + idx; }
 };
 
 // first index with oids[idx] >= lo, first index with oids[idx] >= hi, plus the
@@ -316,6 +317,7 @@ struct SetOpF {
 		o = a.at(idx);
 		return b.contains(o) == want;
 	}
+	__device__ oid at(uint64_t idx) const { return a.at(idx); }
 };
 static Lookup lookup_of(const Cand &c) { return Lookup{c.dense, c.seq, c.oids, c.ncand}; }
 

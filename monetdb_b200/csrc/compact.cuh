@@ -1,71 +1,180 @@
 // compact.cuh — ordered stream compaction into oid lists: the building block
 // behind every operator that emits a candidate list (scanselect's
 // `dst[cnt] = o; cnt += TEST` loop, gdk_select.c:219-248; candidate set algebra,
-// gdk_cand.c:46-400; mask expansion, gdk_cand.c:1464).  One pass over the input,
-// results in input order, output staged through shared memory so the global
-// writes are contiguous.
+// gdk_cand.c:46-400; mask expansion, gdk_cand.c:1464).
+//
+// Three dependency-free steps (a first version used a single-pass decoupled
+// look-back; ncu showed 60 % of its warp samples parked on the look-back barrier,
+// see profiles/r1_select_dense_v0.md):
+//   1. MASK    one streaming pass evaluates the predicate and leaves ONE BIT per
+//              input index (32 indexes per word, LSB first — the layout of the
+//              reference's msk candidates, gdk.h:835-860) plus a hit count per
+//              chunk of CP_CHUNK indexes;
+//   2. SCAN    a single CTA turns the chunk counts into output offsets;
+//   3. EXPAND  one warp per 32 mask words writes the oids of the set bits,
+//              256 contiguous bytes per store instruction.
+// The input column is read once; the only extra traffic is the bitmask (n/8 bytes
+// written and read back, L2-resident for all but the largest inputs).
 #pragma once
 #include "common.cuh"
-#include "scan.cuh"
 
 #define CP_THREADS 256
+#define CP_CHUNK 8192			/* indexes per CTA: 256 mask words, 32 per warp */
+#define CP_WORDS (CP_CHUNK / 32)
 
-// Generic form: F is a functor `bool f(uint64_t idx, oid &out)` evaluated once per
-// input index; hits are written to dst in index order.
-template <int ITEMS, typename F>
-__global__ void __launch_bounds__(CP_THREADS)
-compact_kernel(uint64_t n, F f, oid *__restrict__ dst, TileScan ts, unsigned ntiles, unsigned long long *total_out)
+struct CompactScratch {
+	uint32_t *words;		/* nchunks * CP_WORDS */
+	uint32_t *counts;		/* nchunks */
+	unsigned long long *offs;	/* nchunks + 1: exclusive offsets, then the total */
+	uint64_t nchunks;
+};
+
+static inline bool compact_scratch(uint64_t n, CompactScratch &s)
 {
-	__shared__ oid stage[CP_THREADS * ITEMS];
-	__shared__ unsigned wtot[CP_THREADS / 32];
-	__shared__ unsigned long long slot;
-	__shared__ unsigned tslot;
-	const unsigned tile = tile_ticket(ts, &tslot);
-	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint64_t wbase = (uint64_t) tile * (CP_THREADS * ITEMS) + (uint64_t) warp * (32 * ITEMS);
-	oid vals[ITEMS];
-	unsigned rank[ITEMS];
-	unsigned hitmask = 0, wcount = 0;
-#pragma unroll
-	for (int j = 0; j < ITEMS; j++) {
-		uint64_t idx = wbase + j * 32 + lane;
-		oid o = 0;
-		bool h = idx < n && f(idx, o);
-		vals[j] = o;
-		unsigned bal = __ballot_sync(0xffffffffu, h);
-		rank[j] = wcount + __popc(bal & ((1u << lane) - 1));
-		wcount += __popc(bal);
-		hitmask |= (unsigned) h << j;
-	}
-	if (lane == 0)
-		wtot[warp] = wcount;
-	__syncthreads();
-	unsigned wexcl = 0, ttot = 0;
-#pragma unroll
-	for (int w = 0; w < CP_THREADS / 32; w++) {
-		unsigned t = wtot[w];
-		wexcl += w < warp ? t : 0;
-		ttot += t;
-	}
-	unsigned long long excl = tile_exclusive_prefix(ts, tile, ttot, &slot);
-#pragma unroll
-	for (int j = 0; j < ITEMS; j++)
-		if (hitmask & (1u << j))
-			stage[wexcl + rank[j]] = vals[j];
-	__syncthreads();
-	for (unsigned i = threadIdx.x; i < ttot; i += CP_THREADS)
-		dst[excl + i] = stage[i];
-	if (tile == ntiles - 1 && threadIdx.x == 0)
-		*total_out = excl + ttot;
+	s.nchunks = (n + CP_CHUNK - 1) / CP_CHUNK;
+	size_t wbytes = s.nchunks * CP_WORDS * 4, cbytes = (s.nchunks * 4 + 15) & ~(size_t) 15;
+	char *p = (char *) scratch_get(wbytes + cbytes + (s.nchunks + 1) * 8);
+	if (p == nullptr)
+		return false;
+	s.words = (uint32_t *) p;
+	s.counts = (uint32_t *) (p + wbytes);
+	s.offs = (unsigned long long *) (p + wbytes + cbytes);
+	return true;
 }
 
-// count / first / last of a freshly compacted oid list -> mapped host slot
-static __global__ void compact_finish_kernel(const oid *dst, const unsigned long long *total, unsigned long long *slot)
+// ---- step 1 (generic form): F is a functor with
+//        bool operator()(uint64_t idx, oid &o)   the test
+//        oid  at(uint64_t idx)                   the oid to emit for a hit
+template <typename F>
+__global__ void __launch_bounds__(CP_THREADS)
+compact_mask_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
 {
-	unsigned long long c = *total;
-	slot[0] = c;
-	slot[1] = c ? dst[0] : 0;
-	slot[2] = c ? dst[c - 1] : 0;
+	__shared__ unsigned total;
+	if (threadIdx.x == 0)
+		total = 0;
+	__syncthreads();
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t cbase = (uint64_t) blockIdx.x * CP_CHUNK;
+	unsigned cnt = 0;
+#pragma unroll 8
+	for (int j = 0; j < CP_CHUNK / CP_THREADS; j++) {
+		/* warp w evaluates 32 consecutive indexes per step: the ballot IS the mask word */
+		const uint64_t idx = cbase + (uint64_t) (j * (CP_THREADS / 32) + warp) * 32 + lane;
+		oid o;
+		const bool h = idx < n && f(idx, o);
+		const unsigned bal = __ballot_sync(0xffffffffu, h);
+		if (lane == 0) {
+			words[idx >> 5] = bal;
+			cnt += __popc(bal);
+		}
+	}
+	if (lane == 0 && cnt)
+		atomicAdd(&total, cnt);
+	__syncthreads();
+	if (threadIdx.x == 0)
+		counts[blockIdx.x] = total;
+}
+
+// ---- step 2: exclusive scan of the chunk counts by one CTA; total -> slot[0]
+static __global__ void __launch_bounds__(1024)
+compact_scan_kernel(const uint32_t *__restrict__ counts, uint64_t nchunks, unsigned long long *__restrict__ offs,
+		    unsigned long long *__restrict__ slot)
+{
+	__shared__ unsigned long long wsum[32];
+	__shared__ unsigned long long itertotal;
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	unsigned long long carry = 0;		/* uniform across the CTA */
+	for (uint64_t base = 0; base < nchunks; base += 1024) {
+		const uint64_t i = base + threadIdx.x;
+		const unsigned long long c = i < nchunks ? counts[i] : 0;
+		unsigned long long inc = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+			if (lane >= o)
+				inc += t;
+		}
+		if (lane == 31)
+			wsum[warp] = inc;
+		__syncthreads();
+		if (warp == 0) {
+			const unsigned long long w = wsum[lane];
+			unsigned long long winc = w;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				unsigned long long t = __shfl_up_sync(0xffffffffu, winc, o);
+				if (lane >= o)
+					winc += t;
+			}
+			wsum[lane] = winc - w;		/* exclusive over warps */
+			if (lane == 31)
+				itertotal = winc;
+		}
+		__syncthreads();
+		if (i < nchunks)
+			offs[i] = carry + wsum[warp] + inc - c;
+		carry += itertotal;
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		offs[nchunks] = carry;
+		slot[0] = carry;
+		slot[1] = 0;
+		slot[2] = 0;
+	}
+}
+
+// ---- step 3: mask words -> oids.  OidOf gives the oid of input index idx.
+struct DenseOid {
+	oid seq;	/* oid of index 0 */
+	__device__ __forceinline__ oid at(uint64_t idx) const { return seq + idx; }
+};
+
+template <typename OidOf>
+__global__ void __launch_bounds__(CP_THREADS)
+compact_expand_kernel(const uint32_t *__restrict__ words, const uint32_t *__restrict__ counts,
+		      const unsigned long long *__restrict__ offs, OidOf of, oid *__restrict__ dst,
+		      unsigned long long *__restrict__ slot)
+{
+	if (counts[blockIdx.x] == 0)
+		return;
+	__shared__ unsigned wtot[CP_THREADS / 32];
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t wbase = (uint64_t) blockIdx.x * CP_WORDS + warp * 32;
+	const unsigned w = words[wbase + lane];
+	const unsigned c = __popc(w);
+	unsigned inc = c;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o)
+			inc += t;
+	}
+	if (lane == 31)
+		wtot[warp] = inc;
+	__syncthreads();
+	unsigned long long base = offs[blockIdx.x];
+#pragma unroll
+	for (int k = 0; k < CP_THREADS / 32; k++)
+		base += k < warp ? wtot[k] : 0;
+	const unsigned long long total = offs[gridDim.x];
+	const unsigned excl = inc - c;
+	unsigned nonempty = __ballot_sync(0xffffffffu, c != 0);
+	while (nonempty) {
+		const int k = __ffs(nonempty) - 1;
+		nonempty &= nonempty - 1;
+		const unsigned wk = __shfl_sync(0xffffffffu, w, k);
+		const unsigned ek = __shfl_sync(0xffffffffu, excl, k);
+		if ((wk >> lane) & 1u) {
+			const unsigned long long pos = base + ek + __popc(wk & ((1u << lane) - 1));
+			const oid o = of.at((wbase + k) * 32 + lane);
+			dst[pos] = o;
+			if (pos == 0)
+				slot[1] = o;
+			if (pos == total - 1)
+				slot[2] = o;
+		}
+	}
 }
 
 struct CompactResult {
@@ -73,31 +182,17 @@ struct CompactResult {
 	oid first = 0, last = 0;
 };
 
-// device scratch: [total (16 B)][tile scan state]
-template <int ITEMS, typename F>
-static bool run_compact(uint64_t n, F f, oid *dst, CompactResult &res)
+// steps 2 + 3 and the read-back of (count, first oid, last oid)
+template <typename OidOf>
+static bool compact_finish(const CompactScratch &s, OidOf of, oid *dst, CompactResult &res)
 {
 	Ctx *c = ctx();
-	uint64_t ntiles = (n + CP_THREADS * ITEMS - 1) / (CP_THREADS * ITEMS);
-	if (ntiles == 0) {
-		res = CompactResult();
-		return true;
-	}
-	char *p = (char *) scratch_get(16 + tilescan_bytes(ntiles));
-	if (p == nullptr)
-		return false;
-	if (!cuda_ok(cudaMemsetAsync(p, 0, 16 + tilescan_bytes(ntiles), c->stream), "memset tile state"))
-		return false;
-	unsigned long long *total = (unsigned long long *) p;
-	TileScan ts;
-	ts.ticket = (unsigned int *) (p + 16);
-	ts.status = (unsigned long long *) (p + 32);
-	{
-		KTimer kt("compact", n * 8);
-		compact_kernel<ITEMS, F><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(n, f, dst, ts, (unsigned) ntiles, total);
-	}
+	compact_scan_kernel<<<1, 1024, 0, c->stream>>>(s.counts, s.nchunks, s.offs, c->slot_d->v);
 	COUNT_LAUNCH();
-	compact_finish_kernel<<<1, 1, 0, c->stream>>>(dst, total, c->slot_d->v);
+	{
+		KTimer kt("compact_expand", s.nchunks * CP_WORDS * 4);
+		compact_expand_kernel<OidOf><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(s.words, s.counts, s.offs, of, dst, c->slot_d->v);
+	}
 	COUNT_LAUNCH();
 	if (!cuda_ok(cudaGetLastError(), "compact launch") || !stream_sync())
 		return false;
@@ -105,6 +200,31 @@ static bool run_compact(uint64_t n, F f, oid *dst, CompactResult &res)
 	res.first = c->slot_h->v[1];
 	res.last = c->slot_h->v[2];
 	return true;
+}
+
+template <typename F> struct FunctorOid {
+	F f;
+	__device__ __forceinline__ oid at(uint64_t idx) const { return f.at(idx); }
+};
+
+// generic driver (the ITEMS parameter of the first version is kept for the call sites)
+template <int ITEMS, typename F>
+static bool run_compact(uint64_t n, F f, oid *dst, CompactResult &res)
+{
+	Ctx *c = ctx();
+	if (n == 0) {
+		res = CompactResult();
+		return true;
+	}
+	CompactScratch s;
+	if (!compact_scratch(n, s))
+		return false;
+	{
+		KTimer kt("compact", n * 8);
+		compact_mask_kernel<F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+	}
+	COUNT_LAUNCH();
+	return compact_finish(s, FunctorOid<F>{f}, dst, res);
 }
 
 // Turn a compacted oid array into a candidate-list BAT with the reference's result

@@ -1,0 +1,658 @@
+// group.cu — BATgroup on the device (gdk_group.c:657-1351).
+//
+// Semantics (gdk_group.c:21-72): candidate rows are partitioned by equal
+// (prior group id, value); group ids are handed out in order of FIRST OCCURRENCE
+// (GRPnotfound, :74-100), extents = oid of each group's first row (ascending),
+// histo = rows per group.  nil is an ordinary value (flt/dbl: nil == nil).
+//
+// The reference walks the rows serially and numbers groups as it meets them.
+// Here the numbering is derived without any serial step:
+//   A  one streaming pass records, per distinct key, the smallest candidate
+//      position holding it ("first row"), in a DIRECT table when the key domain
+//      is small (1-byte values, optionally x <= 256 prior groups; 2-byte values —
+//      the cases the reference serves with GRP_small_values, :607-654,921-939)
+//      or in an open-addressing HASH table whose slots hold that first row
+//      itself (keys are compared by reading the column at the slot's row, as the
+//      reference's link-array hash does, so any key width works lock-free);
+//   B  the first rows are marked in a bitmap over candidate positions and a
+//      popcount prefix over the bitmap turns "first row" into "rank among first
+//      rows" = the reference's group id; extents fall out in ascending order;
+//   C  a second streaming pass maps every row to its group id, builds the
+//      histogram (privatised in shared memory for few groups) and checks
+//      whether the ids are non-decreasing (gn->tsorted).
+#include "common.cuh"
+#include "scan.cuh"
+#include "keys.cuh"
+
+#define GRP_EMPTY (~0ULL)
+#define GRP_THREADS 256
+#define GRP_SHM_DOMAIN 4096	/* direct tables up to this many entries are privatised per CTA */
+#define GRP_SHM_HISTO 2048
+
+template <typename T> struct GrpSrc {
+	const T *vals;		/* dense: value of candidate position r is vals[r]; else vals[cand[r] - hseq] */
+	const oid *cand;	/* materialised candidates or NULL */
+	oid hseq;
+	oid seq;		/* dense: oid of candidate position 0 */
+	const oid *g;		/* prior group ids per candidate position, or NULL */
+	uint64_t n;
+	__device__ __forceinline__ T value(uint64_t r) const { return cand ? vals[cand[r] - hseq] : vals[r]; }
+	__device__ __forceinline__ oid rowoid(uint64_t r) const { return cand ? cand[r] : seq + r; }
+};
+
+// ---------------------------------------------------------------- pass A, direct table
+// entry index = value | prior gid << (8 * sizeof(T))   (the GV expressions at gdk_group.c:921-939)
+template <typename T, bool HASG> __device__ __forceinline__ unsigned direct_index(const GrpSrc<T> &src, uint64_t r)
+{
+	typedef typename KeyBits<T>::type U;
+	unsigned k = (unsigned) (U) src.value(r);
+	if (HASG)
+		k |= (unsigned) src.g[r] << (8 * sizeof(T));
+	return k;
+}
+
+template <typename T, bool HASG, bool SHM>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_direct_first_kernel(GrpSrc<T> src, u64 *__restrict__ first, unsigned domain)
+{
+	extern __shared__ u64 sfirst[];
+	if (SHM) {
+		for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS)
+			sfirst[i] = GRP_EMPTY;
+		__syncthreads();
+	}
+	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
+	constexpr int U4 = 4;
+	for (uint64_t r0 = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r0 < src.n; r0 += stride * U4) {
+		unsigned k[U4];
+#pragma unroll
+		for (int u = 0; u < U4; u++) {
+			const uint64_t r = r0 + u * stride;
+			k[u] = r < src.n ? direct_index<T, HASG>(src, r) : 0xffffffffu;
+		}
+#pragma unroll
+		for (int u = 0; u < U4; u++) {
+			const uint64_t r = r0 + u * stride;
+			if (k[u] == 0xffffffffu)
+				continue;
+			if (SHM) {
+				/* rows arrive in ascending order per thread: after the first few
+				 * iterations the plain read filters out every atomic */
+				if (r < sfirst[k[u]])
+					atomicMin(&sfirst[k[u]], (u64) r);
+			} else {
+				if (r < __ldcg(first + k[u]))
+					atomicMin(first + k[u], (u64) r);
+			}
+		}
+	}
+	if (SHM) {
+		__syncthreads();
+		for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS) {
+			u64 v = sfirst[i];
+			if (v != GRP_EMPTY && v < __ldcg(first + i))
+				atomicMin(first + i, v);
+		}
+	}
+}
+
+// ---------------------------------------------------------------- pass A, hash table
+// slots[h] = smallest candidate position seen so far of the key that owns slot h.
+// A slot's value only ever changes to another row with the SAME key, so comparing
+// against the key of whatever row is read from the slot is always valid.
+template <typename T, bool HASG>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t *__restrict__ slotof,
+		      unsigned *__restrict__ state /* [0] overflow flag, [1] inserted keys */)
+{
+	typedef typename KeyBits<T>::type U;
+	__shared__ unsigned sins;
+	if (threadIdx.x == 0)
+		sins = 0;
+	__syncthreads();
+	unsigned inserted = 0;
+	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
+	for (uint64_t r = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r < src.n; r += stride) {
+		const U v = KeyBits<T>::get(src.value(r));
+		const u64 gv = HASG ? src.g[r] : 0;
+		u64 h = hash_key<U>(v, gv) & mask;
+		unsigned probes = 0;
+		for (;;) {
+			u64 cur = __ldcg(slots + h);
+			if (cur == GRP_EMPTY) {
+				cur = atomicCAS(slots + h, GRP_EMPTY, (u64) r);
+				if (cur == GRP_EMPTY) {
+					inserted++;
+					break;
+				}
+			}
+			if (cur == r)
+				break;
+			if (KeyBits<T>::get(src.value(cur)) == v && (!HASG || src.g[cur] == gv)) {
+				if (r < cur)
+					atomicMin(slots + h, (u64) r);
+				break;
+			}
+			h = (h + 1) & mask;
+			if (++probes > 8192) {
+				state[0] = 1;	/* table too full: the host retries with a larger one */
+				break;
+			}
+		}
+		slotof[r] = (uint32_t) h;
+	}
+	if (inserted)
+		atomicAdd(&sins, inserted);
+	__syncthreads();
+	if (threadIdx.x == 0 && sins)
+		atomicAdd(&state[1], sins);
+}
+
+// ---------------------------------------------------------------- pass B: first rows -> ranks
+__global__ void grp_mark_kernel(const u64 *__restrict__ table, uint64_t nentries, u64 *__restrict__ bits)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nentries; i += (uint64_t) gridDim.x * blockDim.x) {
+		u64 r = __ldcs(table + i);
+		if (r != GRP_EMPTY)
+			atomicOr(bits + (r >> 6), 1ULL << (r & 63));
+	}
+}
+
+// exclusive popcount prefix per 64-bit word; total -> *total_out.  Tile = 256 x 8 words.
+#define BP_ITEMS 8
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_bitprefix_kernel(const u64 *__restrict__ bits, uint64_t nwords, u64 *__restrict__ pref, TileScan ts,
+		     unsigned ntiles, unsigned long long *total_out)
+{
+	__shared__ unsigned wtot[GRP_THREADS / 32];
+	__shared__ unsigned long long slot;
+	__shared__ unsigned tslot;
+	const unsigned tile = tile_ticket(ts, &tslot);
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t base = (uint64_t) tile * (GRP_THREADS * BP_ITEMS) + (uint64_t) threadIdx.x * BP_ITEMS;
+	unsigned c[BP_ITEMS], tsum = 0;
+#pragma unroll
+	for (int j = 0; j < BP_ITEMS; j++) {
+		c[j] = base + j < nwords ? __popcll(bits[base + j]) : 0;
+		tsum += c[j];
+	}
+	unsigned inc = tsum;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o)
+			inc += t;
+	}
+	if (lane == 31)
+		wtot[warp] = inc;
+	__syncthreads();
+	unsigned wexcl = 0, ttot = 0;
+#pragma unroll
+	for (int w = 0; w < GRP_THREADS / 32; w++) {
+		unsigned t = wtot[w];
+		wexcl += w < warp ? t : 0;
+		ttot += t;
+	}
+	const unsigned long long texcl = tile_exclusive_prefix(ts, tile, ttot, &slot);
+	unsigned long long run = texcl + wexcl + inc - tsum;
+#pragma unroll
+	for (int j = 0; j < BP_ITEMS; j++) {
+		if (base + j < nwords)
+			pref[base + j] = run;
+		run += c[j];
+	}
+	if (tile == ntiles - 1 && threadIdx.x == 0)
+		*total_out = texcl + ttot;
+}
+
+// table entry (first row) -> group id; extents[gid] = oid of that row
+template <typename T>
+__global__ void grp_rank_kernel(const u64 *__restrict__ table, uint64_t nentries, const u64 *__restrict__ bits,
+				const u64 *__restrict__ pref, GrpSrc<T> src, uint32_t *__restrict__ gidtab,
+				oid *__restrict__ exts)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nentries; i += (uint64_t) gridDim.x * blockDim.x) {
+		u64 r = __ldcs(table + i);
+		if (r == GRP_EMPTY)
+			continue;
+		u64 w = bits[r >> 6];
+		u64 gid = pref[r >> 6] + __popcll(w & ((1ULL << (r & 63)) - 1));
+		gidtab[i] = (uint32_t) gid;
+		if (exts)
+			exts[gid] = src.rowoid(r);
+	}
+}
+
+// ---------------------------------------------------------------- pass C: rows -> group ids
+// MODE 0: direct table, gidtab copied to shared memory (domain <= GRP_SHM_DOMAIN)
+// MODE 1: direct table in global memory
+// MODE 2: hash table, entry of row r saved in slotof[r] by pass A
+template <typename T, bool HASG, int MODE>
+__device__ __forceinline__ uint32_t grp_entry(const GrpSrc<T> &src, const uint32_t *slotof, uint64_t r)
+{
+	if constexpr (MODE == 2)
+		return __ldcs(slotof + r);
+	else
+		return direct_index<T, HASG>(src, r);
+}
+
+template <typename T, bool HASG, int MODE, bool SHISTO>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint32_t *__restrict__ gidtab, unsigned domain,
+		  oid *__restrict__ gids, u64 *__restrict__ cnts, unsigned ngrp, unsigned *__restrict__ unsorted)
+{
+	extern __shared__ uint32_t sh[];
+	uint32_t *sgid = sh;					/* MODE 0: domain entries */
+	uint32_t *shist = sh + (MODE == 0 ? domain : 0);	/* SHISTO: ngrp counters */
+	if (MODE == 0)
+		for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS)
+			sgid[i] = gidtab[i];
+	if (SHISTO)
+		for (unsigned i = threadIdx.x; i < ngrp; i += GRP_THREADS)
+			shist[i] = 0;
+	if (MODE == 0 || SHISTO)
+		__syncthreads();
+	bool bad = false;
+	/* a thread handles two consecutive rows per step so the id stores are 16 bytes wide */
+	const uint64_t npairs = (src.n + 1) / 2;
+	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
+	for (uint64_t p = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; p < npairs; p += stride) {
+		const uint64_t r = 2 * p;
+		const bool two = r + 1 < src.n;
+		uint32_t e0 = grp_entry<T, HASG, MODE>(src, slotof, r);
+		uint32_t e1 = two ? grp_entry<T, HASG, MODE>(src, slotof, r + 1) : e0;
+		uint32_t ep = r ? grp_entry<T, HASG, MODE>(src, slotof, r - 1) : e0;
+		uint32_t g0, g1, gp;
+		if (MODE == 0) {
+			g0 = sgid[e0];
+			g1 = sgid[e1];
+			gp = sgid[ep];
+		} else {
+			g0 = __ldg(gidtab + e0);
+			g1 = __ldg(gidtab + e1);
+			gp = __ldg(gidtab + ep);
+		}
+		bad |= (r && g0 < gp) || (two && g1 < g0);
+		if (two) {
+			ulonglong2 v;
+			v.x = g0;
+			v.y = g1;
+			__stcs(reinterpret_cast<ulonglong2 *>(gids + r), v);
+		} else {
+			gids[r] = g0;
+		}
+		if (cnts) {
+			if (SHISTO) {
+				/* warp-aggregated: one shared atomic per distinct id per warp */
+				const unsigned act = __activemask();
+				unsigned m0 = __match_any_sync(act, g0);
+				if ((unsigned) (__ffs(m0) - 1) == (threadIdx.x & 31))
+					atomicAdd(&shist[g0], (unsigned) __popc(m0));
+				unsigned m1 = __match_any_sync(act, two ? g1 : 0xffffffffu);
+				if (two && (unsigned) (__ffs(m1) - 1) == (threadIdx.x & 31))
+					atomicAdd(&shist[g1], (unsigned) __popc(m1));
+			} else {
+				atomicAdd(cnts + g0, 1ULL);
+				if (two)
+					atomicAdd(cnts + g1, 1ULL);
+			}
+		}
+	}
+	if (__syncthreads_or(bad) && threadIdx.x == 0)
+		*unsorted = 1;
+	if (SHISTO && cnts) {
+		for (unsigned i = threadIdx.x; i < ngrp; i += GRP_THREADS)
+			if (shist[i])
+				atomicAdd(cnts + i, (u64) shist[i]);
+	}
+}
+
+// ---------------------------------------------------------------- host side
+__global__ void grp_max_kernel(const oid *__restrict__ g, uint64_t n, u64 *__restrict__ out)
+{
+	u64 mx = 0;
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
+		oid v = __ldcs(g + i);
+		if (v != OID_NIL && v > mx)
+			mx = v;
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		u64 t = __shfl_down_sync(0xffffffffu, mx, o);
+		mx = t > mx ? t : mx;
+	}
+	if ((threadIdx.x & 31) == 0 && mx)
+		atomicMax(out, mx);
+}
+
+__global__ void grp_finish_kernel(const oid *exts, u64 ngrp, const unsigned *unsorted, unsigned long long *slot)
+{
+	slot[0] = *unsorted;
+	slot[1] = exts && ngrp ? exts[0] : 0;
+	slot[2] = exts && ngrp ? exts[ngrp - 1] : 0;
+}
+
+struct GrpTemps {
+	u64 *table = nullptr, *bits = nullptr, *pref = nullptr;
+	uint32_t *slotof = nullptr, *gidtab = nullptr;
+	unsigned *state = nullptr;
+	~GrpTemps()
+	{
+		dev_free(table);
+		dev_free(bits);
+		dev_free(pref);
+		dev_free(slotof);
+		dev_free(gidtab);
+		dev_free(state);
+	}
+};
+
+static inline u64 next_pow2(u64 x)
+{
+	u64 p = 1;
+	while (p < x)
+		p <<= 1;
+	return p;
+}
+
+template <typename T, bool HASG>
+static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat **enp, b200_bat **hnp, bool want_e, bool want_h)
+{
+	Ctx *c = ctx();
+	const uint64_t n = src.n;
+	const unsigned sgrid = grid_for(n, GRP_THREADS * 4, NSM * 8);
+	GrpTemps t;
+	int mode;		/* 0 direct/shared, 1 direct/global, 2 hash */
+	u64 nentries;
+	if (sizeof(T) == 1 && (!HASG || maxgrp < 256)) {
+		nentries = HASG ? 256 * (maxgrp + 1) : 256;
+		mode = nentries <= GRP_SHM_DOMAIN ? 0 : 1;
+	} else if (sizeof(T) == 2 && !HASG) {
+		nentries = 65536;
+		mode = 1;
+	} else {
+		mode = 2;
+		nentries = 0;
+	}
+	t.state = (unsigned *) dev_alloc(16);
+	if (t.state == nullptr)
+		return false;
+	if (mode != 2) {
+		t.table = (u64 *) dev_alloc(nentries * 8);
+		if (t.table == nullptr || !cuda_ok(cudaMemsetAsync(t.table, 0xff, nentries * 8, c->stream), "memset group table"))
+			return false;
+		if constexpr (sizeof(T) <= 2) {
+			KTimer kt("group_first", n * (sizeof(T) + (HASG ? 8 : 0)));
+			if (mode == 0)
+				grp_direct_first_kernel<T, HASG, true><<<sgrid, GRP_THREADS, nentries * 8, c->stream>>>(src, t.table, (unsigned) nentries);
+			else
+				grp_direct_first_kernel<T, HASG, false><<<sgrid, GRP_THREADS, 0, c->stream>>>(src, t.table, (unsigned) nentries);
+		}
+		COUNT_LAUNCH();
+		ctx()->algo = mode == 0 ? "group: cuda direct table (shared)" : "group: cuda direct table";
+	} else {
+		t.slotof = (uint32_t *) dev_alloc(n * 4);
+		if (t.slotof == nullptr)
+			return false;
+		const u64 capmax = next_pow2(2 * n);
+		u64 cap = next_pow2(n / 4);
+		if (cap < (1u << 16))
+			cap = 1u << 16;
+		if (cap > (1u << 22))
+			cap = 1u << 22;
+		if (cap > capmax)
+			cap = capmax;
+		for (;;) {
+			t.table = (u64 *) dev_alloc(cap * 8);
+			if (t.table == nullptr || !cuda_ok(cudaMemsetAsync(t.table, 0xff, cap * 8, c->stream), "memset group hash") ||
+			    !cuda_ok(cudaMemsetAsync(t.state, 0, 16, c->stream), "memset state"))
+				return false;
+			{
+				KTimer kt("group_hash", n * (sizeof(T) + (HASG ? 8 : 0) + 4));
+				grp_hash_first_kernel<T, HASG><<<grid_for(n, GRP_THREADS, NSM * 8), GRP_THREADS, 0, c->stream>>>(src, t.table, cap - 1, t.slotof, t.state);
+			}
+			COUNT_LAUNCH();
+			if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, t.state, 8, cudaMemcpyDeviceToHost, c->stream), "read state") || !stream_sync())
+				return false;
+			const unsigned *st = (const unsigned *) c->slot_h->v;
+			if (cap >= capmax || (st[0] == 0 && (u64) st[1] * 2 <= cap))
+				break;
+			/* too full for comfortable probing: retry with a table sized for the worst case seen */
+			dev_free(t.table);
+			t.table = nullptr;
+			cap = cap * 16 > capmax ? capmax : cap * 16;
+		}
+		nentries = cap;
+		ctx()->algo = "group: cuda hash table";
+	}
+	/* pass B */
+	const u64 nwords = (n + 63) / 64;
+	t.bits = (u64 *) dev_alloc(nwords * 8);
+	t.pref = (u64 *) dev_alloc(nwords * 8);
+	t.gidtab = (uint32_t *) dev_alloc(nentries * 4);
+	if (t.bits == nullptr || t.pref == nullptr || t.gidtab == nullptr ||
+	    !cuda_ok(cudaMemsetAsync(t.bits, 0, nwords * 8, c->stream), "memset bits") ||
+	    !cuda_ok(cudaMemsetAsync(t.state, 0, 16, c->stream), "memset state"))
+		return false;
+	grp_mark_kernel<<<grid_for(nentries, 256, NSM * 8), 256, 0, c->stream>>>(t.table, nentries, t.bits);
+	COUNT_LAUNCH();
+	const u64 ntiles = (nwords + GRP_THREADS * BP_ITEMS - 1) / (GRP_THREADS * BP_ITEMS);
+	char *sp = (char *) scratch_get(16 + tilescan_bytes(ntiles));
+	if (sp == nullptr || !cuda_ok(cudaMemsetAsync(sp, 0, 16 + tilescan_bytes(ntiles), c->stream), "memset tile state"))
+		return false;
+	TileScan ts;
+	ts.ticket = (unsigned int *) (sp + 16);
+	ts.status = (unsigned long long *) (sp + 32);
+	grp_bitprefix_kernel<<<(unsigned) ntiles, GRP_THREADS, 0, c->stream>>>(t.bits, nwords, t.pref, ts, (unsigned) ntiles, (unsigned long long *) sp);
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, sp, 8, cudaMemcpyDeviceToHost, c->stream), "read ngrp") || !stream_sync())
+		return false;
+	const u64 ngrp = c->slot_h->v[0];
+	b200_bat *en = nullptr, *hn = nullptr;
+	if (want_e) {
+		en = bat_new(0, B200_oid, ngrp);
+		if (en == nullptr)
+			return false;
+		*enp = en;
+	}
+	if (want_h) {
+		hn = bat_new(0, B200_lng, ngrp);
+		if (hn == nullptr || !cuda_ok(cudaMemsetAsync(hn->base, 0, ngrp * 8, c->stream), "memset histo"))
+			return false;
+		*hnp = hn;
+	}
+	grp_rank_kernel<T><<<grid_for(nentries, 256, NSM * 8), 256, 0, c->stream>>>(t.table, nentries, t.bits, t.pref, src, t.gidtab,
+										       en ? (oid *) en->base : nullptr);
+	COUNT_LAUNCH();
+	/* pass C */
+	const bool shisto = ngrp <= GRP_SHM_HISTO;
+	oid *gids = (oid *) gn->base;
+	u64 *cnts = hn ? (u64 *) hn->base : nullptr;
+	const unsigned agrid = grid_for((n + 1) / 2, GRP_THREADS * 4, NSM * 8);
+	const size_t shm = (mode == 0 ? nentries * 4 : 0) + (shisto ? ngrp * 4 : 0);
+	{
+		KTimer kt("group_assign", n * ((mode == 2 ? 4 : sizeof(T) + (HASG ? 8 : 0)) + 8));
+#define ASSIGN(MODE, SH) grp_assign_kernel<T, HASG, MODE, SH><<<agrid, GRP_THREADS, shm, c->stream>>>( \
+		src, t.slotof, t.gidtab, (unsigned) nentries, gids, cnts, (unsigned) ngrp, t.state)
+		if (mode == 2) {
+			if (shisto) ASSIGN(2, true); else ASSIGN(2, false);
+		} else if constexpr (sizeof(T) <= 2) {
+			if (mode == 0) {
+				if (shisto) ASSIGN(0, true); else ASSIGN(0, false);
+			} else {
+				if (shisto) ASSIGN(1, true); else ASSIGN(1, false);
+			}
+		}
+#undef ASSIGN
+	}
+	COUNT_LAUNCH();
+	grp_finish_kernel<<<1, 1, 0, c->stream>>>(en ? (const oid *) en->base : nullptr, ngrp, t.state, c->slot_d->v);
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaGetLastError(), "group launch") || !stream_sync())
+		return false;
+	const bool unsorted = c->slot_h->v[0] != 0;
+	const oid efirst = c->slot_h->v[1], elast = c->slot_h->v[2];
+	/* result properties, gdk_group.c:1283-1315 */
+	gn->count = n;
+	gn->tsorted = !unsorted;
+	gn->trevsorted = ngrp == 1 || n <= 1;
+	gn->tkey = ngrp == n;
+	gn->tnonil = 1;
+	gn->tnil = 0;
+	gn->tseqbase = OID_NIL;
+	if (en) {
+		en->count = ngrp;
+		en->tkey = en->tsorted = en->tnonil = 1;
+		en->trevsorted = ngrp == 1;
+		en->tnil = 0;
+		en->tseqbase = OID_NIL;
+		en->oidrange_known = 1;
+		en->first_oid = efirst;
+		en->last_oid = elast;
+		if (ngrp > 0 && elast - efirst + 1 == ngrp) {	/* virtualize (gdk_select.c:31-89) */
+			b200_bat *d = bat_dense(0, efirst, ngrp);
+			if (d == nullptr)
+				return false;
+			b200_BATfree(en);
+			*enp = d;
+		}
+	}
+	if (hn) {
+		hn->count = ngrp;
+		const bool triv = ngrp == n || ngrp == 1;
+		hn->tkey = ngrp == 1;
+		hn->tsorted = hn->trevsorted = triv;
+		hn->tnonil = 1;
+		hn->tnil = 0;
+	}
+	return true;
+}
+
+template <typename T>
+static bool group_typed(const b200_bat *b, const Cand &ci, const b200_bat *g, u64 maxgrp, b200_bat *gn,
+			b200_bat **enp, b200_bat **hnp, bool want_e, bool want_h)
+{
+	GrpSrc<T> src;
+	src.hseq = ci.hseq;
+	src.seq = ci.seq;
+	src.n = ci.ncand;
+	if (ci.dense) {
+		src.vals = (const T *) b->base + (ci.seq - ci.hseq);
+		src.cand = nullptr;
+	} else {
+		src.vals = (const T *) b->base;
+		src.cand = ci.oids;
+	}
+	src.g = g ? (const oid *) g->base : nullptr;
+	if (g)
+		return group_run<T, true>(src, maxgrp, gn, enp, hnp, want_e, want_h);
+	return group_run<T, false>(src, maxgrp, gn, enp, hnp, want_e, want_h);
+}
+
+extern "C" b200_return b200_BATgroup(b200_bat **groups, b200_bat **extents, b200_bat **histo,
+				     const b200_bat *b, const b200_bat *s, const b200_bat *g,
+				     const b200_bat *e, const b200_bat *h)
+{
+	b200_clrerr();
+	if (groups)
+		*groups = nullptr;
+	if (extents)
+		*extents = nullptr;
+	if (histo)
+		*histo = nullptr;
+	if (b == nullptr) {
+		set_err("b must exist\n");
+		return B200_FAIL;
+	}
+	if (groups == nullptr) {
+		set_err("BATgroup: groups output required\n");
+		return B200_FAIL;
+	}
+	Staged sb, ss, sg;
+	if (!stage(b, sb) || !stage(s, ss) || !stage(g, sg))
+		return B200_FAIL;
+	b = sb.b;
+	g = sg.b;
+	Cand ci;
+	if (!cand_init(ci, b, ss.b))
+		return B200_FAIL;
+	if (g && g->count != ci.ncand) {
+		set_err("BATgroup: g must be aligned with b and s\n");
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	const oid hseqb = ci.ncand == 0 ? 0 : ci.seq;
+	b200_bat *gn = nullptr, *en = nullptr, *hn = nullptr;
+	const bool bkey = b->tkey || (b->ttype == B200_void && b->tseqbase != OID_NIL);
+	if (bkey || ci.ncand <= 1 || (g && (g->tkey || bat_is_dense(g)))) {
+		/* grouping is trivial: 1 element per group (gdk_group.c:712-727) */
+		c->algo = "group: 1 element per group";
+		gn = bat_dense(hseqb, 0, b->count);
+		if (gn == nullptr)
+			goto bailout;
+		if (extents && (en = cand_to_bat(ci)) == nullptr)
+			goto bailout;
+		if (histo) {
+			const lng one = 1;
+			if ((hn = bat_constant(0, B200_lng, &one, ci.ncand)) == nullptr)
+				goto bailout;
+		}
+	} else {
+		u64 maxgrp = 0;
+		if (g) {
+			if (g->ttype == B200_void) {	/* void-nil: every row in group nil; not a valid grouping */
+				set_err("BATgroup: g must be a materialised oid column\n");
+				goto bailout;
+			}
+			if (e != nullptr && e->count > 0) {
+				maxgrp = e->count - 1;
+			} else {
+				u64 *st = (u64 *) scratch_get(64);
+				if (st == nullptr || !cuda_ok(cudaMemsetAsync(st, 0, 8, c->stream), "memset"))
+					goto bailout;
+				grp_max_kernel<<<grid_for(g->count, 256, NSM * 8), 256, 0, c->stream>>>((const oid *) g->base, g->count, st);
+				COUNT_LAUNCH();
+				if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, st, 8, cudaMemcpyDeviceToHost, c->stream), "read") || !stream_sync())
+					goto bailout;
+				maxgrp = c->slot_h->v[0];
+			}
+			if (maxgrp == 0)
+				g = nullptr;	/* single group (gdk_group.c:761-762) */
+		}
+		if (ci.ncand >= (1ULL << 32)) {
+			set_err("BATgroup: more than 2^32 candidate rows in one device call\n");
+			goto bailout;
+		}
+		gn = bat_new(hseqb, B200_oid, ci.ncand);
+		if (gn == nullptr)
+			goto bailout;
+		bool ok = false;
+		switch (basetype(b->ttype)) {
+		case B200_bte: ok = group_typed<bte>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_sht: ok = group_typed<sht>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_int: ok = group_typed<int>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_lng: ok = group_typed<lng>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_hge: ok = group_typed<hge>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_flt: ok = group_typed<flt>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		case B200_dbl: ok = group_typed<dbl>(b, ci, g, maxgrp, gn, &en, &hn, extents != nullptr, histo != nullptr); break;
+		default:
+			set_err("BATgroup: unsupported tail type %s (fixed-width atoms only)\n", atomname(b->ttype));
+		}
+		if (!ok)
+			goto bailout;
+	}
+	*groups = gn;
+	if (extents)
+		*extents = en;
+	if (histo)
+		*histo = hn;
+	return B200_SUCCEED;
+bailout:
+	if (gn)
+		b200_BATfree(gn);
+	if (en)
+		b200_BATfree(en);
+	if (hn)
+		b200_BATfree(hn);
+	return B200_FAIL;
+}

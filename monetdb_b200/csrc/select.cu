@@ -26,98 +26,74 @@ template <typename T> struct RangePred {
 };
 
 // ---------------------------------------------------------------- dense scan kernel
-// Tile = 256 threads x NV 16-byte vectors; warp w owns a contiguous slab of the
-// tile so each load instruction of a warp covers 512 contiguous bytes.
-template <typename T> struct DenseCfg {
-	static constexpr int VEC = 16 / sizeof(T);				/* values per 128-bit load */
-	static constexpr int NV = (sizeof(T) == 1) ? 1 : (sizeof(T) == 2 ? 2 : 4);	/* loads per thread */
-	static constexpr int TILE = CP_THREADS * NV * VEC;			/* rows per tile: 4096/4096/4096/2048/1024 */
-};
-
+// Step 1 of the compaction (compact.cuh) specialised for a dense candidate range:
+// 128-bit streaming loads, VEC predicate bits per thread, and the 32-row mask
+// words assembled from G = 32/VEC neighbouring lanes with one warp-level OR
+// reduction.  A CTA covers one CP_CHUNK of rows; all of a thread's loads are
+// independent, so 32/VEC of them are in flight per thread.
 template <typename T>
 __global__ void __launch_bounds__(CP_THREADS)
 select_dense_kernel(const T *__restrict__ src,	/* 16-byte aligned; row r of the scan = src[r] */
 		    uint64_t skip,		/* leading rows before the first candidate (alignment padding) */
 		    uint64_t n,			/* rows to scan including skip */
-		    oid seq,			/* oid of src[0] */
-		    RangePred<T> pred, oid *__restrict__ dst, TileScan ts, unsigned ntiles,
-		    unsigned long long *total_out)
+		    RangePred<T> pred, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
 {
-	constexpr int VEC = DenseCfg<T>::VEC, NV = DenseCfg<T>::NV, TILE = DenseCfg<T>::TILE;
-	__shared__ oid stage[TILE];
-	__shared__ unsigned wtot[CP_THREADS / 32];
-	__shared__ unsigned long long slot;
-	__shared__ unsigned tslot;
-	const unsigned tile = tile_ticket(ts, &tslot);
-	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint64_t wbase = (uint64_t) tile * TILE + (uint64_t) warp * (32 * NV * VEC);
-	unsigned masks[NV];
+	constexpr int VEC = 16 / sizeof(T);		/* values per 128-bit load */
+	constexpr int G = 32 / VEC;			/* lanes that share one mask word */
+	constexpr int NV = CP_CHUNK / (CP_THREADS * VEC);	/* loads per thread: 2/4/8/16/32 */
+	__shared__ unsigned total;
+	if (threadIdx.x == 0)
+		total = 0;
+	__syncthreads();
+	const unsigned lane = threadIdx.x & 31;
+	const uint64_t cbase = (uint64_t) blockIdx.x * CP_CHUNK;
+	unsigned cnt = 0;
+	constexpr int NB = NV > 8 ? 8 : NV;		/* loads issued back to back before any is consumed */
+	for (int jb = 0; jb < NV; jb += NB) {
+		int4 q[NB];
 #pragma unroll
-	for (int j = 0; j < NV; j++) {
-		const uint64_t r0 = wbase + (uint64_t) (j * 32 + lane) * VEC;
-		unsigned m = 0;
-		if (r0 + VEC <= n) {
-			union { int4 q; T v[VEC]; } u;
-			u.q = __ldcs(reinterpret_cast<const int4 *>(src + r0));
+		for (int j = 0; j < NB; j++) {
+			const uint64_t r0 = cbase + ((uint64_t) (jb + j) * CP_THREADS + threadIdx.x) * VEC;
+			if (r0 + VEC <= n)
+				q[j] = __ldcs(reinterpret_cast<const int4 *>(src + r0));
+		}
 #pragma unroll
-			for (int e = 0; e < VEC; e++)
-				m |= (unsigned) pred(u.v[e]) << e;
+		for (int j = 0; j < NB; j++) {
+			const uint64_t r0 = cbase + ((uint64_t) (jb + j) * CP_THREADS + threadIdx.x) * VEC;
+			unsigned m = 0;
+			if (r0 + VEC <= n) {
+				union { int4 q; T v[VEC]; } u;
+				u.q = q[j];
+#pragma unroll
+				for (int e = 0; e < VEC; e++)
+					m |= (unsigned) pred(u.v[e]) << e;
+			} else {
+				for (int e = 0; e < VEC; e++)
+					if (r0 + e < n)
+						m |= (unsigned) pred(src[r0 + e]) << e;
+			}
 			if (r0 < skip) {
 #pragma unroll
 				for (int e = 0; e < VEC; e++)
 					if (r0 + e < skip)
 						m &= ~(1u << e);
 			}
-		} else {
-			for (int e = 0; e < VEC; e++)
-				if (r0 + e < n && r0 + e >= skip)
-					m |= (unsigned) pred(src[r0 + e]) << e;
+			const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << (G & 31)) - 1)) << (lane & ~(G - 1));
+			const unsigned word = __reduce_or_sync(gmask, m << (VEC * (lane & (G - 1))));
+			if ((lane & (G - 1)) == 0) {
+				words[r0 >> 5] = word;
+				cnt += __popc(word);
+			}
 		}
-		masks[j] = m;
 	}
-	/* rank of each thread's hits inside the warp, order = (j, lane, e) */
-	unsigned excl[NV];
-	unsigned wcount = 0;
 #pragma unroll
-	for (int j = 0; j < NV; j++) {
-		unsigned c = __popc(masks[j]);
-		unsigned inc = c;
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
-			if (lane >= o)
-				inc += t;
-		}
-		excl[j] = wcount + inc - c;
-		wcount += __shfl_sync(0xffffffffu, inc, 31);
-	}
-	if (lane == 0)
-		wtot[warp] = wcount;
+	for (int o = 16; o > 0; o >>= 1)
+		cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+	if (lane == 0 && cnt)
+		atomicAdd(&total, cnt);
 	__syncthreads();
-	unsigned wexcl = 0, ttot = 0;
-#pragma unroll
-	for (int w = 0; w < CP_THREADS / 32; w++) {
-		unsigned t = wtot[w];
-		wexcl += w < warp ? t : 0;
-		ttot += t;
-	}
-	unsigned long long gexcl = tile_exclusive_prefix(ts, tile, ttot, &slot);
-#pragma unroll
-	for (int j = 0; j < NV; j++) {
-		unsigned m = masks[j];
-		unsigned pos = wexcl + excl[j];
-		const oid o0 = seq + wbase + (uint64_t) (j * 32 + lane) * VEC;
-		while (m) {
-			int e = __ffs(m) - 1;
-			m &= m - 1;
-			stage[pos++] = o0 + e;
-		}
-	}
-	__syncthreads();
-	for (unsigned i = threadIdx.x; i < ttot; i += CP_THREADS)
-		dst[gexcl + i] = stage[i];
-	if (tile == ntiles - 1 && threadIdx.x == 0)
-		*total_out = gexcl + ttot;
+	if (threadIdx.x == 0)
+		counts[blockIdx.x] = total;
 }
 
 template <typename T>
@@ -128,30 +104,15 @@ static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, o
 	uint64_t skip = ((uintptr_t) p & 15) / sizeof(T);
 	p -= skip;
 	uint64_t n = ncand + skip;
-	constexpr int TILE = DenseCfg<T>::TILE;
-	uint64_t ntiles = (n + TILE - 1) / TILE;
-	char *sp = (char *) scratch_get(16 + tilescan_bytes(ntiles));
-	if (sp == nullptr)
+	CompactScratch s;
+	if (!compact_scratch(n, s))
 		return false;
-	if (!cuda_ok(cudaMemsetAsync(sp, 0, 16 + tilescan_bytes(ntiles), c->stream), "memset tile state"))
-		return false;
-	unsigned long long *total = (unsigned long long *) sp;
-	TileScan ts;
-	ts.ticket = (unsigned int *) (sp + 16);
-	ts.status = (unsigned long long *) (sp + 32);
 	{
 		KTimer kt("select_dense", n * sizeof(T));
-		select_dense_kernel<T><<<(unsigned) ntiles, CP_THREADS, 0, c->stream>>>(p, skip, n, seq - skip, pred, dst, ts, (unsigned) ntiles, total);
+		select_dense_kernel<T><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, skip, n, pred, s.words, s.counts);
 	}
 	COUNT_LAUNCH();
-	compact_finish_kernel<<<1, 1, 0, c->stream>>>(dst, total, c->slot_d->v);
-	COUNT_LAUNCH();
-	if (!cuda_ok(cudaGetLastError(), "select launch") || !stream_sync())
-		return false;
-	res.count = c->slot_h->v[0];
-	res.first = c->slot_h->v[1];
-	res.last = c->slot_h->v[2];
-	return true;
+	return compact_finish(s, DenseOid{seq - skip}, dst, res);
 }
 
 // ---------------------------------------------------------------- candidate-list scan
@@ -165,6 +126,7 @@ template <typename T> struct GatherPredF {
 		o = __ldcs(cand + idx);
 		return pred(col[o - hseq]);
 	}
+	__device__ __forceinline__ oid at(uint64_t idx) const { return cand[idx]; }
 };
 
 // ---------------------------------------------------------------- typed driver

@@ -349,6 +349,51 @@ def BATconvert(b: BAT, s: BAT | None, tp: int, scale1: int = 0, scale2: int = 0,
     return BAT(lib.b200_BATconvert(b._p, _ptr(s), tp, scale1, scale2, precision))
 
 
+# ------------------------------------------------------------------ compares (gdk_calc.h:66-83)
+for _op in ("lt", "le", "gt", "ge"):
+    _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P)
+    _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P)
+for _op in ("eq", "ne"):
+    _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P, C.c_bool)
+    _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P, C.c_bool)
+_sig("b200_BATcalcisnil", _P, _P, _P)
+
+
+def BATcalccmp(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None, nil_matches: bool = False) -> BAT:
+    """BATcalclt/le/gt/ge/eq/ne -> bit column"""
+    f = getattr(lib, f"b200_BATcalc{op}")
+    if op in ("eq", "ne"):
+        return BAT(f(b1._p, b2._p, _ptr(s1), _ptr(s2), nil_matches))
+    return BAT(f(b1._p, b2._p, _ptr(s1), _ptr(s2)))
+
+
+def BATcalccmpcst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, nil_matches: bool = False) -> BAT:
+    a = _val(_storage(vtype), v)
+    f = getattr(lib, f"b200_BATcalc{op}cst")
+    if op in ("eq", "ne"):
+        return BAT(f(b._p, _vp(a), vtype, _ptr(s), nil_matches))
+    return BAT(f(b._p, _vp(a), vtype, _ptr(s)))
+
+
+def BATcalcisnil(b: BAT, s: BAT | None = None) -> BAT:
+    return BAT(lib.b200_BATcalcisnil(b._p, _ptr(s)))
+
+
+# ------------------------------------------------------------------ grouping
+_sig("b200_BATgroup", C.c_int, _PP, _PP, _PP, _P, _P, _P, _P, _P)
+
+
+def BATgroup(b: BAT, s: BAT | None = None, g: BAT | None = None, e: BAT | None = None, h: BAT | None = None,
+             want_extents: bool = True, want_histo: bool = True):
+    """BATgroup (gdk.h:1447) -> (groups, extents, histo)"""
+    pg, pe, ph = _P(), _P(), _P()
+    rc = lib.b200_BATgroup(C.byref(pg), C.byref(pe) if want_extents else None, C.byref(ph) if want_histo else None,
+                           b._p, _ptr(s), _ptr(g), _ptr(e), _ptr(h))
+    if rc != 1:
+        _fail("BATgroup")
+    return BAT(pg), (BAT(pe) if want_extents else None), (BAT(ph) if want_histo else None)
+
+
 # ------------------------------------------------------------------ aggregates
 for _n in ("sum", "count", "min", "max"):
     if hasattr(lib, f"b200_BATgroup{_n}"):

