@@ -121,6 +121,7 @@ bool cuda_ok(cudaError_t e, const char *what);
 
 void *dev_alloc(size_t bytes);		/* stream-ordered pool allocation, NULL + error on failure */
 void dev_free(void *p);
+void hash_cache_drop(const void *base);	/* join.cu: forget a cached BAThash index */
 void *scratch_get(size_t bytes);	/* per-thread reusable device scratch */
 bool stream_sync();			/* sync + error check */
 

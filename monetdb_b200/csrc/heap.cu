@@ -300,6 +300,8 @@ extern "C" void b200_BATfree(b200_bat *b)
 {
 	if (b == nullptr)
 		return;
+	if (b->device >= 0 && b->base != nullptr)
+		hash_cache_drop(b->base);	/* a BAThash index dies with its BAT */
 	if (b->owns) {
 		if (b->device >= 0) {
 			if (tl_ctx && tl_ctx->device == b->device) {

@@ -394,6 +394,26 @@ def BATgroup(b: BAT, s: BAT | None = None, g: BAT | None = None, e: BAT | None =
     return BAT(pg), (BAT(pe) if want_extents else None), (BAT(ph) if want_histo else None)
 
 
+# ------------------------------------------------------------------ hash + join (gdk_hash.h:36, gdk.h:2266)
+_sig("b200_BAThash", C.c_int, _P)
+_sig("b200_BATjoin", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_bool, C.c_uint64)
+
+
+def BAThash(b: BAT) -> None:
+    if lib.b200_BAThash(b._p) != 1:
+        _fail("BAThash")
+
+
+def BATjoin(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+            estimate: int = BUN_NONE, want_r2: bool = True):
+    """BATjoin -> (r1, r2): aligned oid lists of matching rows of l and r"""
+    p1, p2 = _P(), _P()
+    rc = lib.b200_BATjoin(C.byref(p1), C.byref(p2) if want_r2 else None, l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, estimate)
+    if rc != 1:
+        _fail("BATjoin")
+    return BAT(p1), (BAT(p2) if want_r2 else None)
+
+
 # ------------------------------------------------------------------ aggregates
 for _n in ("sum", "count", "min", "max"):
     if hasattr(lib, f"b200_BATgroup{_n}"):
