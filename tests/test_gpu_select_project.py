@@ -135,13 +135,15 @@ def test_cand_algebra(gdk, ref, ka, kb):
     a, ra = _cands(gdk, ref, ka, n, rng)
     b, rb = _cands(gdk, ref, kb, n, rng)
     if (ka, kb) == ("mask", "dense"):
-        # reference quirk: with a bitmask list and a dense list the reference's merge loses the first
-        # mask candidates after the dense range (canditer_setidx/canditer_search on cand_mask,
-        # gdk_cand.c:131-133).  The definition of the operator (set union) is the judge here.
-        want = np.union1d(ra.numpy(), rb.numpy())
-        assert same_bits(gdk.BATmergecand(a, b).numpy(), want)
-        assert len(ref.BATmergecand(ra, rb).numpy()) <= len(want)
-    else:
-        assert same_bits(gdk.BATmergecand(a, b).numpy(), ref.BATmergecand(ra, rb).numpy())
+        # reference quirk: with a bitmask list against a dense list the reference's set operations lose
+        # mask candidates at the edges of the dense range (canditer_setidx/canditer_search/canditer_peek on
+        # cand_mask, gdk_cand.c:131-133,216-240).  The definition of the operators (set algebra on the
+        # logical oid sets, which the reference's own expansion of both lists agrees with) is the judge here.
+        sa, sb = ra.numpy(), rb.numpy()
+        assert same_bits(gdk.BATmergecand(a, b).numpy(), np.union1d(sa, sb))
+        assert same_bits(gdk.BATintersectcand(a, b).numpy(), np.intersect1d(sa, sb))
+        assert same_bits(gdk.BATdiffcand(a, b).numpy(), np.setdiff1d(sa, sb))
+        return
+    assert same_bits(gdk.BATmergecand(a, b).numpy(), ref.BATmergecand(ra, rb).numpy())
     assert same_bits(gdk.BATintersectcand(a, b).numpy(), ref.BATintersectcand(ra, rb).numpy())
     assert same_bits(gdk.BATdiffcand(a, b).numpy(), ref.BATdiffcand(ra, rb).numpy())
