@@ -1,0 +1,183 @@
+// analytic.cuh — shared machinery of the window-function kernels
+// (gdk_analytic_bounds.c, gdk_analytic_func.c, gdk_analytic_statistics.c).
+//
+// The reference walks every partition sequentially (`for (; i < cnt; i++) if (np[i]) {...}`,
+// e.g. gdk_analytic_bounds.c:201-215).  On the device a partitioning is a SEGMENT
+// LIST: the ascending row positions where a new partition (or peer group) starts,
+// produced by the ordered compaction of compact.cuh, closed by a sentinel equal to
+// the row count.  Every kernel processes tiles of AN_TILE rows; a tile stages the
+// (usually one or two) segment boundaries that intersect it in shared memory, so a
+// row finds its partition [start, end) and partition number without touching
+// global memory again.
+//
+// Framed aggregates use the reference's fan-out-16 segment tree
+// (gdk_analytic.h:52-130), built per partition and aligned to the partition start
+// exactly as populate_segment_tree does, so that the order of floating-point
+// additions — and the reference's "average of node averages" behaviour for framed
+// integer averages (gdk_analytic_statistics.c:163-185) — are reproduced bit for bit.
+// Level 0 is the input column itself (never materialised); level l >= 1 of
+// partition q lives at slot  (S[q] >> 4l) + q + t  of one array per level.
+#pragma once
+#include "common.cuh"
+#include "compact.cuh"
+
+#define AN_TILE 1024
+#define AN_THREADS 256
+#define AN_FANOUT 16
+#define AN_MAXLEV 16
+
+enum { AN_ERR_OVERFLOW = 1, AN_ERR_BOUND = 2 };
+
+struct SegList {
+	oid *S = nullptr;	/* cnt starts + sentinel S[cnt] = n */
+	uint64_t cnt = 0, n = 0;
+	~SegList() { if (S) dev_free(S); }
+};
+
+static __global__ void an_set_u64(oid *p, oid v)
+{
+	*p = v;
+}
+
+// ordered compaction of the row positions for which f(idx) holds into an exactly
+// sized list (mask -> scan -> read the total -> allocate -> expand)
+template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
+{
+	Ctx *c = ctx();
+	out.n = n;
+	out.cnt = 0;
+	if (n == 0) {
+		out.S = (oid *) dev_alloc(8);
+		if (out.S == nullptr)
+			return false;
+		an_set_u64<<<1, 1, 0, c->stream>>>(out.S, 0);
+		COUNT_LAUNCH();
+		return true;
+	}
+	CompactScratch s;
+	if (!compact_scratch(n, s))
+		return false;
+	{
+		KTimer kt("an_seg_mask", n);
+		compact_mask_kernel<F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+	}
+	COUNT_LAUNCH();
+	compact_scan_kernel<<<1, 1024, 0, c->stream>>>(s.counts, s.nchunks, s.offs, c->slot_d->v);
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaGetLastError(), "seglist launch") || !stream_sync())
+		return false;
+	out.cnt = c->slot_h->v[0];
+	out.S = (oid *) dev_alloc((out.cnt + 1) * 8);
+	if (out.S == nullptr)
+		return false;
+	if (out.cnt) {
+		compact_expand_kernel<FunctorOid<F>><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(
+			s.words, s.counts, s.offs, FunctorOid<F>{f}, out.S, c->slot_d->v);
+		COUNT_LAUNCH();
+	}
+	an_set_u64<<<1, 1, 0, c->stream>>>(out.S + out.cnt, n);
+	COUNT_LAUNCH();
+	return cuda_ok(cudaGetLastError(), "seglist expand");
+}
+
+// partition starts: row 0 and every row whose p (or o) flag is set
+struct FlagStart {
+	const bte *p, *o;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const
+	{
+		return idx == 0 || (p && p[idx]) || (o && o[idx]);
+	}
+	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
+};
+// plain set bits of a bit column (peer-group starts for GROUPS frames)
+struct FlagBits {
+	const bte *b;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const { return b[idx] != 0; }
+	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
+};
+
+#ifdef __CUDACC__
+// number of entries of S[0..cnt) that are <= k
+__device__ __forceinline__ uint64_t seg_upper(const oid *__restrict__ S, uint64_t cnt, oid k)
+{
+	uint64_t lo = 0, hi = cnt;
+	while (lo < hi) {
+		uint64_t mid = (lo + hi) >> 1;
+		if (S[mid] <= k)
+			lo = mid + 1;
+		else
+			hi = mid;
+	}
+	return lo;
+}
+
+// The slice of a segment list that intersects one tile, staged in shared memory.
+struct TileSegs {
+	oid sm[AN_TILE + 2];
+	uint64_t q0;		/* index in S of sm[0] */
+	unsigned m;		/* sm[0..m] valid; sm[m] > last row of the tile */
+
+	// all threads of the CTA must call this
+	__device__ __forceinline__ void load(const oid *__restrict__ S, uint64_t cnt, uint64_t first, uint64_t last)
+	{
+		if (threadIdx.x == 0) {
+			uint64_t u0 = seg_upper(S, cnt, first), u1 = seg_upper(S, cnt, last);
+			q0 = u0 ? u0 - 1 : 0;
+			m = (unsigned) (u1 - q0);
+		}
+		__syncthreads();
+		for (unsigned i = threadIdx.x; i <= m; i += blockDim.x)
+			sm[i] = S[q0 + i];
+		__syncthreads();
+	}
+	// number of list entries <= k (global count); start/end of the segment holding k
+	__device__ __forceinline__ uint64_t locate(oid k, oid &start, oid &end) const
+	{
+		unsigned lo = 0, hi = m;
+		while (lo < hi) {
+			unsigned mid = (lo + hi) >> 1;
+			if (sm[mid] <= k)
+				lo = mid + 1;
+			else
+				hi = mid;
+		}
+		start = lo ? sm[lo - 1] : 0;
+		end = sm[lo];
+		return q0 + lo;
+	}
+};
+
+// ADD_WITH_CHECK / SUB_WITH_CHECK (gdk_calc_private.h:53-102), usable for every atom
+template <typename T> __device__ __forceinline__ bool add_with_check(T lft, T rgt, T &dst)
+{
+	const T mx = Atom<T>::maxval();
+	if (rgt < 1) {
+		if (-mx - rgt > lft)
+			return false;
+	} else {
+		if (mx - rgt < lft)
+			return false;
+	}
+	dst = lft + rgt;
+	return true;
+}
+template <typename T> __device__ __forceinline__ bool sub_with_check(T lft, T rgt, T &dst)
+{
+	const T mx = Atom<T>::maxval();
+	if (rgt < 1) {
+		if (mx + rgt < lft)
+			return false;
+	} else {
+		if (-mx + rgt > lft)
+			return false;
+	}
+	dst = lft - rgt;
+	return true;
+}
+#endif
+
+// shared host helpers (analytic_bounds.cu)
+bool an_partitions(const b200_bat *p, const b200_bat *o, uint64_t n, SegList &out);
+bool an_check_bit(const b200_bat *x, const char *what, uint64_t n);
+bool an_read_state(unsigned long long *state, unsigned long long out[2]);
+unsigned long long *an_state_init();

@@ -1,0 +1,661 @@
+// analytic_bounds.cu — GDKanalyticaldiff and GDKanalyticalwindowbounds
+// (gdk_analytic_bounds.c:95-175 and :1440-1456; ROWS :855-991, RANGE :994-1291,
+// GROUPS :1295-1437, UNBOUNDED :614-651, peers :654-852).
+//
+// The reference processes one partition after the other and one row after the other;
+// here every row is independent once it knows its partition [start, end), which it
+// gets from the staged segment list of analytic.cuh.
+#include "analytic.cuh"
+
+// ---------------------------------------------------------------- shared helpers
+unsigned long long *an_state_init()
+{
+	unsigned long long *st = (unsigned long long *) dev_alloc(16);
+	if (st == nullptr)
+		return nullptr;
+	if (!cuda_ok(cudaMemsetAsync(st, 0, 16, ctx()->stream), "state init")) {
+		dev_free(st);
+		return nullptr;
+	}
+	return st;
+}
+
+// reads {error bits, nil count}, frees the state
+bool an_read_state(unsigned long long *state, unsigned long long out[2])
+{
+	Ctx *c = ctx();
+	bool ok = cuda_ok(cudaGetLastError(), "analytic launch") &&
+		  cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 16, cudaMemcpyDeviceToHost, c->stream), "state read") &&
+		  stream_sync();
+	dev_free(state);
+	if (!ok)
+		return false;
+	out[0] = c->slot_h->v[0];
+	out[1] = c->slot_h->v[1];
+	return true;
+}
+
+bool an_check_bit(const b200_bat *x, const char *what, uint64_t n)
+{
+	if (x == nullptr)
+		return true;
+	if (basetype(x->ttype) != B200_bte || x->base == nullptr || x->count < n) {
+		set_err("analytic: %s must be a bit column aligned with the input\n", what);
+		return false;
+	}
+	return true;
+}
+
+bool an_partitions(const b200_bat *p, const b200_bat *o, uint64_t n, SegList &out)
+{
+	FlagStart f{p ? (const bte *) p->base : nullptr, o ? (const bte *) o->base : nullptr};
+	return build_seglist(n, f, out);
+}
+
+// ---------------------------------------------------------------- GDKanalyticaldiff
+template <typename T> __device__ __forceinline__ bool an_differs(T a, T b)
+{
+	if constexpr (Atom<T>::is_float)
+		return a != b && !(Atom<T>::is_nil(a) && Atom<T>::is_nil(b));	/* nil == nil */
+	else
+		return a != b;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+an_diff_kernel(const T *__restrict__ b, const bte *__restrict__ np, int mode /* 0 none, 1 np, 2 npbit */, bte npb,
+	       uint64_t n, bte *__restrict__ r)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
+		const bte keep = mode == 1 ? np[i] : mode == 2 ? npb : 0;
+		r[i] = (i > 0 && an_differs<T>(b[i], b[i - 1])) ? (bte) 1 : keep;
+	}
+}
+
+template <typename T>
+static void diff_launch(const b200_bat *b, const b200_bat *p, const int8_t *npbit, uint64_t n, bte *r)
+{
+	Ctx *c = ctx();
+	KTimer kt("an_diff", n * (sizeof(T) + 1 + (p ? 1 : 0)));
+	an_diff_kernel<T><<<grid_for(n, 256, NSM * 32), 256, 0, c->stream>>>(
+		(const T *) b->base, p ? (const bte *) p->base : nullptr, p ? 1 : npbit ? 2 : 0, npbit ? *npbit : 0, n, r);
+	COUNT_LAUNCH();
+}
+
+extern "C" b200_return b200_GDKanalyticaldiff(b200_bat *r, const b200_bat *b, const b200_bat *p, const int8_t *npbit, int tpe)
+{
+	b200_clrerr();
+	if (r == nullptr || b == nullptr) {
+		set_err("GDKanalyticaldiff: BAT required\n");
+		return B200_FAIL;
+	}
+	Staged sb, sp;
+	if (!stage(b, sb) || !stage(p, sp))
+		return B200_FAIL;
+	b = sb.b;
+	p = sp.b;
+	const uint64_t n = b->count;
+	if (r->device < 0 || basetype(r->ttype) != B200_bte || r->capacity < n) {
+		set_err("GDKanalyticaldiff: result must be a device bit BAT with capacity >= BATcount(b)\n");
+		return B200_FAIL;
+	}
+	if (!an_check_bit(p, "p", n))
+		return B200_FAIL;
+	if (n > 0) {
+		ctx()->algo = "analyticaldiff: cuda streaming";
+		switch (basetype(tpe)) {
+		case B200_bte: diff_launch<bte>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_sht: diff_launch<sht>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_int: diff_launch<int>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_lng: diff_launch<lng>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_hge: diff_launch<hge>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_flt: diff_launch<flt>(b, p, npbit, n, (bte *) r->base); break;
+		case B200_dbl: diff_launch<dbl>(b, p, npbit, n, (bte *) r->base); break;
+		default:
+			set_err("GDKanalyticaldiff: type %s is not on the device path (fixed-width atoms only)\n", atomname(tpe));
+			return B200_FAIL;
+		}
+		if (!cuda_ok(cudaGetLastError(), "diff launch"))
+			return B200_FAIL;
+	}
+	r->count = n;
+	r->tnonil = 1;
+	r->tnil = 0;
+	r->tsorted = r->trevsorted = n <= 1;
+	r->tkey = n <= 1;
+	return B200_SUCCEED;
+}
+
+// ---------------------------------------------------------------- window bounds
+#define OID_MAX (OID_NIL - 1)	/* GDK_oid_max */
+
+// limit of row k as the kernel's compute type LT, from a dynamic column of DT or the static value
+template <typename LT, typename DT>
+__device__ __forceinline__ bool an_limit(const DT *__restrict__ lim, LT slim, uint64_t k, LT &out)
+{
+	if (lim) {
+		const DT v = lim[k];
+		if (Atom<DT>::is_nil(v) || v < 0)
+			return false;
+		out = (LT) v;
+	} else {
+		out = slim;
+	}
+	return true;
+}
+template <typename LT> __device__ __forceinline__ oid an_limit_oid(LT v)
+{
+	if constexpr (sizeof(LT) == 16)
+		return v > (LT) OID_MAX ? OID_MAX : (oid) v;
+	else
+		return (oid) v;
+}
+
+// UNBOUNDED PRECEDING / FOLLOWING (allbounds) and peer bounds: start or end of the segment
+__global__ void __launch_bounds__(AN_THREADS)
+an_segbound_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, bool preceding, oid *__restrict__ rb)
+{
+	__shared__ TileSegs ts;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid s, e;
+		ts.locate(k, s, e);
+		rb[k] = preceding ? s : e;
+	}
+}
+
+// ROWS (gdk_analytic_bounds.c:177-198)
+template <typename DT>
+__global__ void __launch_bounds__(AN_THREADS)
+an_rows_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const DT *__restrict__ lim, DT slim, bool preceding,
+	       oid second_half, oid *__restrict__ rb, unsigned long long *__restrict__ state)
+{
+	__shared__ TileSegs ts;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	bool bad = false;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid j, e;
+		ts.locate(k, j, e);
+		DT ol;
+		if (!an_limit<DT, DT>(lim, slim, k, ol)) {
+			bad = true;
+			rb[k] = k;
+			continue;
+		}
+		oid rl = an_limit_oid<DT>(ol);
+		if (preceding) {
+			rb[k] = rl > k - j ? j : k - rl + second_half;
+		} else {
+			rl += second_half;
+			rb[k] = rl > e - k ? e : k + rl;
+		}
+	}
+	if (bad)
+		atomicOr(&state[0], (unsigned long long) AN_ERR_BOUND);
+}
+
+// GROUPS (gdk_analytic_bounds.c:217-254): G = positions of the set bits of the peer column
+template <typename DT>
+__global__ void __launch_bounds__(AN_THREADS)
+an_groups_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__ G, uint64_t gcnt, uint64_t n,
+		 const DT *__restrict__ lim, DT slim, bool preceding, oid *__restrict__ rb, unsigned long long *__restrict__ state)
+{
+	__shared__ TileSegs ts, tg;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	tg.load(G, gcnt, base, last);
+	bool bad = false;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid m, e, gs, ge;
+		ts.locate(k, m, e);
+		const uint64_t c = tg.locate(k, gs, ge);	/* set bits at positions <= k */
+		DT ol;
+		if (!an_limit<DT, DT>(lim, slim, k, ol)) {
+			bad = true;
+			rb[k] = k;
+			continue;
+		}
+		const oid rl = an_limit_oid<DT>(ol);
+		if (preceding) {
+			oid pos = m;
+			if (c >= 1 && rl <= c - 1) {
+				const oid g = G[c - 1 - rl];
+				pos = g > m ? g : m;
+			}
+			rb[k] = pos;
+		} else {
+			oid pos = e;
+			if (rl < gcnt - c) {
+				const oid g = G[c + rl];
+				pos = g < e ? g : e;
+			}
+			rb[k] = pos;
+		}
+	}
+	if (bad)
+		atomicOr(&state[0], (unsigned long long) AN_ERR_BOUND);
+}
+
+// RANGE (gdk_analytic_bounds.c:273-369): nearest position whose order value differs from
+// b[k] by more than the limit; nils form their own peer run; the subtraction is overflow-checked
+template <typename T, typename DT>
+__global__ void __launch_bounds__(AN_THREADS)
+an_range_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__restrict__ bp, bool nonil,
+		const DT *__restrict__ lim, DT slim, bool preceding, oid *__restrict__ rb, unsigned long long *__restrict__ state)
+{
+	typedef typename std::conditional<Atom<T>::is_float, T, hge>::type LT;
+	__shared__ TileSegs ts;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	unsigned err = 0;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid m, e;
+		ts.locate(k, m, e);
+		LT ol;
+		if (!an_limit<LT, DT>(lim, (LT) slim, k, ol)) {
+			err |= AN_ERR_BOUND;
+			rb[k] = k;
+			continue;
+		}
+		const T v = bp[k];
+		const bool vnil = !nonil && Atom<T>::is_nil(v);
+		oid j;
+		if (preceding) {
+			for (j = k;; j--) {
+				const T w = bp[j];
+				if (vnil) {
+					if (!Atom<T>::is_nil(w)) {
+						j++;
+						break;
+					}
+				} else {
+					if (!nonil && Atom<T>::is_nil(w)) {
+						j++;
+						break;
+					}
+					T calc;
+					if (!sub_with_check<T>(v, w, calc)) {
+						err |= AN_ERR_OVERFLOW;
+						break;
+					}
+					if ((LT) (calc < 0 ? -calc : calc) > ol) {
+						j++;
+						break;
+					}
+				}
+				if (j == m)
+					break;
+			}
+		} else {
+			for (j = k + 1; j < e; j++) {
+				const T w = bp[j];
+				if (vnil) {
+					if (!Atom<T>::is_nil(w))
+						break;
+				} else {
+					if (!nonil && Atom<T>::is_nil(w))
+						break;
+					T calc;
+					if (!sub_with_check<T>(v, w, calc)) {
+						err |= AN_ERR_OVERFLOW;
+						break;
+					}
+					if ((LT) (calc < 0 ? -calc : calc) > ol)
+						break;
+				}
+			}
+		}
+		rb[k] = j;
+	}
+	if (err)
+		atomicOr(&state[0], (unsigned long long) err);
+}
+
+// ---------------------------------------------------------------- host side
+// peer-run starts: row 0, partition starts and every row whose order value differs
+// from its predecessor (nil == nil), gdk_analytic_bounds.c:654-852
+template <typename T> struct PeerStart {
+	const bte *p;
+	const T *b;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const
+	{
+		return idx == 0 || (p && p[idx]) || an_differs<T>(b[idx], b[idx - 1]);
+	}
+	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
+};
+
+static inline unsigned an_tiles(uint64_t n)
+{
+	return (unsigned) ((n + AN_TILE - 1) / AN_TILE);
+}
+
+static bool segbound_run(const SegList &sl, uint64_t n, bool preceding, oid *rb)
+{
+	Ctx *c = ctx();
+	if (n == 0)
+		return true;
+	KTimer kt("an_segbound", n * 9);
+	an_segbound_kernel<<<an_tiles(n), AN_THREADS, 0, c->stream>>>(sl.S, sl.cnt, n, preceding, rb);
+	COUNT_LAUNCH();
+	return cuda_ok(cudaGetLastError(), "segbound launch");
+}
+
+template <typename T>
+static bool peers_run(const b200_bat *b, const b200_bat *p, uint64_t n, bool preceding, oid *rb)
+{
+	SegList pl;
+	PeerStart<T> f{p ? (const bte *) p->base : nullptr, (const T *) b->base};
+	return build_seglist(n, f, pl) && segbound_run(pl, n, preceding, rb);
+}
+
+static bool peers_dispatch(const b200_bat *b, const b200_bat *p, uint64_t n, bool preceding, oid *rb)
+{
+	ctx()->algo = "windowbounds: peers, cuda segment list";
+	switch (basetype(b->ttype)) {
+	case B200_bte: return peers_run<bte>(b, p, n, preceding, rb);
+	case B200_sht: return peers_run<sht>(b, p, n, preceding, rb);
+	case B200_int: return peers_run<int>(b, p, n, preceding, rb);
+	case B200_lng: return peers_run<lng>(b, p, n, preceding, rb);
+	case B200_hge: return peers_run<hge>(b, p, n, preceding, rb);
+	case B200_flt: return peers_run<flt>(b, p, n, preceding, rb);
+	case B200_dbl: return peers_run<dbl>(b, p, n, preceding, rb);
+	}
+	set_err("windowbounds: type %s is not on the device path (fixed-width atoms only)\n", atomname(b->ttype));
+	return false;
+}
+
+// value of a static integer bound as lng per the reference's casts (:936-968): nil -> lng_nil,
+// hge above lng max -> lng max
+static bool static_limit_lng(const void *bound, int tp2, lng &limit)
+{
+	switch (tp2) {
+	case B200_bte: limit = Atom<bte>::is_nil(*(const bte *) bound) ? Atom<lng>::nil() : (lng) *(const bte *) bound; return true;
+	case B200_sht: limit = Atom<sht>::is_nil(*(const sht *) bound) ? Atom<lng>::nil() : (lng) *(const sht *) bound; return true;
+	case B200_int: limit = Atom<int>::is_nil(*(const int *) bound) ? Atom<lng>::nil() : (lng) *(const int *) bound; return true;
+	case B200_lng: limit = *(const lng *) bound; return true;
+	case B200_hge: {
+		hge v;
+		memcpy(&v, bound, 16);
+		limit = Atom<hge>::is_nil(v) ? Atom<lng>::nil() : v > (hge) Atom<lng>::maxval() ? Atom<lng>::maxval() : (lng) v;
+		return true;
+	}
+	}
+	return false;
+}
+
+template <typename DT>
+static void rows_launch(const SegList &sl, uint64_t n, const void *lim, DT slim, bool preceding, oid second_half, oid *rb,
+			unsigned long long *state)
+{
+	KTimer kt("an_rows", n * (9 + (lim ? sizeof(DT) : 0)));
+	an_rows_kernel<DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, n, (const DT *) lim, slim, preceding, second_half, rb, state);
+	COUNT_LAUNCH();
+}
+template <typename DT>
+static void groups_launch(const SegList &sl, const SegList &gl, uint64_t n, const void *lim, DT slim, bool preceding, oid *rb,
+			  unsigned long long *state)
+{
+	KTimer kt("an_groups", n * (10 + (lim ? sizeof(DT) : 0)));
+	an_groups_kernel<DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, gl.S, gl.cnt, n, (const DT *) lim, slim, preceding, rb, state);
+	COUNT_LAUNCH();
+}
+template <typename T, typename DT>
+static void range_launch(const SegList &sl, uint64_t n, const b200_bat *b, const void *lim, DT slim, bool preceding, oid *rb,
+			 unsigned long long *state)
+{
+	KTimer kt("an_range", n * (9 + sizeof(T) + (lim ? sizeof(DT) : 0)));
+	an_range_kernel<T, DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, n, (const T *) b->base, b->tnonil != 0,
+									       (const DT *) lim, slim, preceding, rb, state);
+	COUNT_LAUNCH();
+}
+// dynamic limit column type x order column type
+template <typename T>
+static bool range_dyn(int tp2, const SegList &sl, uint64_t n, const b200_bat *b, const void *lim, bool preceding, oid *rb,
+		      unsigned long long *state)
+{
+	if constexpr (Atom<T>::is_float) {
+		return false;
+	} else {
+		switch (tp2) {
+		case B200_bte: if (sizeof(T) <= 8) { range_launch<T, bte>(sl, n, b, lim, 0, preceding, rb, state); return true; } break;
+		case B200_sht: if (sizeof(T) <= 8) { range_launch<T, sht>(sl, n, b, lim, 0, preceding, rb, state); return true; } break;
+		case B200_int: if (sizeof(T) <= 8) { range_launch<T, int>(sl, n, b, lim, 0, preceding, rb, state); return true; } break;
+		case B200_lng: if (sizeof(T) <= 8) { range_launch<T, lng>(sl, n, b, lim, 0, preceding, rb, state); return true; } break;
+		case B200_hge: range_launch<T, hge>(sl, n, b, lim, 0, preceding, rb, state); return true;
+		}
+		return false;
+	}
+}
+
+static b200_return bounds_done(b200_bat *r, uint64_t n, bool nonil)
+{
+	r->count = n;
+	r->tnonil = nonil;
+	r->tnil = 0;
+	r->tsorted = r->trevsorted = r->tkey = n <= 1;
+	r->tseqbase = OID_NIL;
+	return B200_SUCCEED;
+}
+
+extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_bat *b, const b200_bat *p, const b200_bat *l,
+						      const void *bound, int tp1, int tp2, int unit, bool preceding,
+						      b200_oid second_half)
+{
+	static const char *unitname[] = {"row", "range", "groups"};
+	b200_clrerr();
+	if (r == nullptr || b == nullptr || (l == nullptr) == (bound == nullptr) || unit < 0 || unit > 2) {
+		set_err("GDKanalyticalwindowbounds: needs r, b and exactly one of l / bound; unit 0..2\n");
+		return B200_FAIL;
+	}
+	Staged sb, sp, sl_;
+	if (!stage(b, sb) || !stage(p, sp) || !stage(l, sl_))
+		return B200_FAIL;
+	b = sb.b;
+	p = sp.b;
+	l = sl_.b;
+	const uint64_t n = b->count;
+	if (r->device < 0 || basetype(r->ttype) != B200_lng || r->capacity < n) {
+		set_err("GDKanalyticalwindowbounds: result must be a device oid BAT with capacity >= BATcount(b)\n");
+		return B200_FAIL;
+	}
+	if (!an_check_bit(p, "p", n))
+		return B200_FAIL;
+	oid *rb = (oid *) r->base;
+	const int t2 = tp2;	/* bound types are plain numeric atoms */
+	if (l != nullptr) {
+		if (l->tnil) {
+			set_err("42000!%s frame bound must be non negative and non null.\n", unitname[unit]);
+			return B200_FAIL;
+		}
+		if (l->base == nullptr || l->count < n || atomsize(l->ttype) != atomsize(t2)) {
+			set_err("GDKanalyticalwindowbounds: bound column must be a materialised %s column aligned with b\n", atomname(t2));
+			return B200_FAIL;
+		}
+	}
+	SegList S;
+	if (!an_partitions(p, nullptr, n, S))
+		return B200_FAIL;
+
+	if (unit == 1) {
+		/* ---- RANGE ---- */
+		if (tp1 == B200_date || tp1 == B200_daytime || tp1 == B200_timestamp) {
+			if (t2 != B200_int && t2 != B200_lng)
+				set_err("42000!range frame bound type %s not supported.\n", atomname(t2));
+			else
+				set_err("windowbounds: temporal RANGE frames (month/second intervals, gdk_analytic_bounds.c:440-611) "
+					"are not on the device path\n");
+			return B200_FAIL;
+		}
+		const int t1 = basetype(tp1);
+		if (b->base == nullptr || atomsize(b->ttype) != atomsize(t1) || atomsize(t1) <= 0) {
+			set_err("42000!type %s not supported for %s frame bound type.\n", atomname(tp1), atomname(t2));
+			return B200_FAIL;
+		}
+		bool type_ok = false;
+		switch (t2) {
+		case B200_bte: case B200_sht: case B200_int: case B200_lng:
+			type_ok = t1 == B200_bte || t1 == B200_sht || t1 == B200_int || t1 == B200_lng;
+			break;
+		case B200_hge:
+			type_ok = t1 == B200_bte || t1 == B200_sht || t1 == B200_int || t1 == B200_lng || t1 == B200_hge;
+			break;
+		case B200_flt: type_ok = t1 == B200_flt; break;
+		case B200_dbl: type_ok = t1 == B200_dbl; break;
+		default:
+			set_err("42000!range frame bound type %s not supported.\n", atomname(t2));
+			return B200_FAIL;
+		}
+		hge ilim = 0;
+		flt flim = 0;
+		dbl dlim = 0;
+		if (l == nullptr) {
+			/* static bound: max -> UNBOUNDED, 0 -> peers, nil / negative -> error (:1094-1262) */
+			bool unbounded = false, zero = false, invalid = false;
+			switch (t2) {
+			case B200_bte: { bte v = *(const bte *) bound; unbounded = v == Atom<bte>::maxval(); zero = v == 0; invalid = Atom<bte>::is_nil(v) || v < 0; ilim = v; break; }
+			case B200_sht: { sht v = *(const sht *) bound; unbounded = v == Atom<sht>::maxval(); zero = v == 0; invalid = Atom<sht>::is_nil(v) || v < 0; ilim = v; break; }
+			case B200_int: { int v = *(const int *) bound; unbounded = v == Atom<int>::maxval(); zero = v == 0; invalid = Atom<int>::is_nil(v) || v < 0; ilim = v; break; }
+			case B200_lng: { lng v = *(const lng *) bound; unbounded = v == Atom<lng>::maxval(); zero = v == 0; invalid = Atom<lng>::is_nil(v) || v < 0; ilim = v; break; }
+			case B200_hge: { hge v; memcpy(&v, bound, 16); invalid = Atom<hge>::is_nil(v) || v < 0; unbounded = !invalid && v == Atom<hge>::maxval(); zero = v == 0; ilim = v; break; }
+			case B200_flt: { flt v = *(const flt *) bound; invalid = Atom<flt>::is_nil(v) || v < 0; unbounded = !invalid && v == Atom<flt>::maxval(); zero = v == 0; flim = v; break; }
+			case B200_dbl: { dbl v = *(const dbl *) bound; invalid = Atom<dbl>::is_nil(v) || v < 0; unbounded = !invalid && v == Atom<dbl>::maxval(); zero = v == 0; dlim = v; break; }
+			}
+			if (unbounded) {
+				ctx()->algo = "windowbounds: unbounded, cuda segment list";
+				return segbound_run(S, n, preceding, rb) ? bounds_done(r, n, false) : B200_FAIL;
+			}
+			if (zero)
+				return peers_dispatch(b, p, n, preceding, rb) ? bounds_done(r, n, false) : B200_FAIL;
+			if (invalid) {
+				set_err("42000!range frame bound must be non negative and non null.\n");
+				return B200_FAIL;
+			}
+		}
+		if (!type_ok) {
+			set_err("42000!type %s not supported for %s frame bound type.\n", atomname(tp1), atomname(t2));
+			return B200_FAIL;
+		}
+		if (n == 0)
+			return bounds_done(r, n, true);
+		unsigned long long *state = an_state_init();
+		if (state == nullptr)
+			return B200_FAIL;
+		ctx()->algo = "windowbounds: range, cuda per-row walk";
+		bool launched = true;
+		if (l != nullptr) {
+			const void *lim = l->base;
+			switch (t1) {
+			case B200_bte: launched = range_dyn<bte>(t2, S, n, b, lim, preceding, rb, state); break;
+			case B200_sht: launched = range_dyn<sht>(t2, S, n, b, lim, preceding, rb, state); break;
+			case B200_int: launched = range_dyn<int>(t2, S, n, b, lim, preceding, rb, state); break;
+			case B200_lng: launched = range_dyn<lng>(t2, S, n, b, lim, preceding, rb, state); break;
+			case B200_hge: launched = range_dyn<hge>(t2, S, n, b, lim, preceding, rb, state); break;
+			case B200_flt: range_launch<flt, flt>(S, n, b, lim, 0, preceding, rb, state); break;
+			case B200_dbl: range_launch<dbl, dbl>(S, n, b, lim, 0, preceding, rb, state); break;
+			}
+		} else {
+			switch (t1) {
+			case B200_bte: range_launch<bte, hge>(S, n, b, nullptr, ilim, preceding, rb, state); break;
+			case B200_sht: range_launch<sht, hge>(S, n, b, nullptr, ilim, preceding, rb, state); break;
+			case B200_int: range_launch<int, hge>(S, n, b, nullptr, ilim, preceding, rb, state); break;
+			case B200_lng: range_launch<lng, hge>(S, n, b, nullptr, ilim, preceding, rb, state); break;
+			case B200_hge: range_launch<hge, hge>(S, n, b, nullptr, ilim, preceding, rb, state); break;
+			case B200_flt: range_launch<flt, flt>(S, n, b, nullptr, flim, preceding, rb, state); break;
+			case B200_dbl: range_launch<dbl, dbl>(S, n, b, nullptr, dlim, preceding, rb, state); break;
+			}
+		}
+		unsigned long long st[2];
+		if (!an_read_state(state, st))
+			return B200_FAIL;
+		if (!launched) {
+			set_err("42000!type %s not supported for %s frame bound type.\n", atomname(tp1), atomname(t2));
+			return B200_FAIL;
+		}
+		if (st[0] & AN_ERR_BOUND) {
+			set_err("42000!range frame bound must be non negative and non null.\n");
+			return B200_FAIL;
+		}
+		if (st[0] & AN_ERR_OVERFLOW) {
+			set_err("22003!overflow in calculation.\n");
+			return B200_FAIL;
+		}
+		return bounds_done(r, n, true);
+	}
+
+	/* ---- ROWS (unit 0) and GROUPS (unit 2) ---- */
+	if (t2 != B200_bte && t2 != B200_sht && t2 != B200_int && t2 != B200_lng && t2 != B200_hge) {
+		set_err("42000!%s frame bound type %s not supported.\n", unit == 0 ? "rows" : "groups", atomname(t2));
+		return B200_FAIL;
+	}
+	lng limit = 0;
+	if (l == nullptr) {
+		static_limit_lng(bound, t2, limit);
+		if (limit == Atom<lng>::maxval()) {
+			ctx()->algo = "windowbounds: unbounded, cuda segment list";
+			return segbound_run(S, n, preceding, rb) ? bounds_done(r, n, false) : B200_FAIL;
+		}
+		if (Atom<lng>::is_nil(limit) || limit < 0) {
+			set_err("42000!%s frame bound must be non negative and non null.\n", unitname[unit]);
+			return B200_FAIL;
+		}
+	}
+	if (n == 0)
+		return bounds_done(r, n, true);
+	SegList G;
+	if (unit == 2) {
+		if (basetype(b->ttype) != B200_bte || b->base == nullptr) {
+			set_err("GDKanalyticalwindowbounds: GROUPS frames take the peer-start bit column as b\n");
+			return B200_FAIL;
+		}
+		FlagBits fb{(const bte *) b->base};
+		if (!build_seglist(n, fb, G))
+			return B200_FAIL;
+	}
+	unsigned long long *state = an_state_init();
+	if (state == nullptr)
+		return B200_FAIL;
+	ctx()->algo = unit == 0 ? "windowbounds: rows, cuda segment list" : "windowbounds: groups, cuda segment list";
+	const void *lim = l ? l->base : nullptr;
+	const int dt = l ? t2 : B200_lng;
+#define AN_RG(DT, SL)                                                                          \
+	do {                                                                                   \
+		if (unit == 0)                                                                 \
+			rows_launch<DT>(S, n, lim, (DT) (SL), preceding, second_half, rb, state);   \
+		else                                                                           \
+			groups_launch<DT>(S, G, n, lim, (DT) (SL), preceding, rb, state);        \
+	} while (0)
+	switch (dt) {
+	case B200_bte: AN_RG(bte, 0); break;
+	case B200_sht: AN_RG(sht, 0); break;
+	case B200_int: AN_RG(int, 0); break;
+	case B200_lng: AN_RG(lng, limit); break;
+	case B200_hge: AN_RG(hge, 0); break;
+	}
+#undef AN_RG
+	unsigned long long st[2];
+	if (!an_read_state(state, st))
+		return B200_FAIL;
+	if (st[0] & AN_ERR_BOUND) {
+		set_err("42000!%s frame bound must be non negative and non null.\n", unitname[unit]);
+		return B200_FAIL;
+	}
+	return bounds_done(r, n, true);
+}
