@@ -1,0 +1,344 @@
+// analytic_aggr.cuh — aggregate definitions for the window functions and the host
+// driver that builds the per-partition segment trees and runs the frame kernel.
+#pragma once
+#include "analytic_tree.cuh"
+
+// ---- sum (gdk_analytic_func.c:1762-1796)
+template <typename T1, typename T2> struct SumOp {
+	typedef T1 In;
+	typedef T2 Node;
+	typedef T2 Acc;
+	typedef T2 Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v) { return Atom<T1>::is_nil(v) ? Atom<T2>::nil() : (T2) v; }
+	__device__ static __forceinline__ void init(Acc &a) { a = Atom<T2>::nil(); }
+	__device__ static __forceinline__ void add(Acc &a, Node v, unsigned &err)
+	{
+		if (!Atom<T2>::is_nil(v)) {
+			if (Atom<T2>::is_nil(a))
+				a = v;
+			else if (!add_with_check<T2>(v, a, a))
+				err |= AN_ERR_OVERFLOW;
+		}
+	}
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = Atom<T2>::is_nil(a);
+		return a;
+	}
+};
+
+// ---- min / max (gdk_analytic_func.c:971-992)
+template <typename T, bool ISMIN> struct MinMaxOp {
+	typedef T In;
+	typedef T Node;
+	typedef T Acc;
+	typedef T Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v) { return v; }
+	__device__ static __forceinline__ void init(Acc &a) { a = Atom<T>::nil(); }
+	__device__ static __forceinline__ void add(Acc &a, Node v, unsigned &err)
+	{
+		if (!Atom<T>::is_nil(v)) {
+			if (Atom<T>::is_nil(a))
+				a = v;
+			else if (ISMIN)
+				a = a < v ? a : v;
+			else
+				a = a > v ? a : v;
+		}
+	}
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = Atom<T>::is_nil(a);
+		return a;
+	}
+};
+
+// ---- count of non-nil values (gdk_analytic_func.c:1413-1428); count(*) is `direct`
+template <typename T> struct CountOp {
+	typedef T In;
+	typedef lng Node;
+	typedef lng Acc;
+	typedef lng Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v) { return Atom<T>::is_nil(v) ? 0 : 1; }
+	__device__ static __forceinline__ void init(Acc &a) { a = 0; }
+	__device__ static __forceinline__ void add(Acc &a, Node v, unsigned &err) { a += v; }
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = false;
+		return a;
+	}
+};
+struct CountAllOp {
+	typedef bte In;
+	typedef lng Node;
+	typedef lng Acc;
+	typedef lng Out;
+	static constexpr bool direct = true;
+	__device__ static __forceinline__ Node leaf(In v) { return 1; }
+	__device__ static __forceinline__ void init(Acc &a) { a = 0; }
+	__device__ static __forceinline__ void add(Acc &a, Node v, unsigned &err) { a += v; }
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = false;
+		return a;
+	}
+};
+
+// ---- average, frame types 3-6: (dbl) sum / n with the sum kept exactly in a hge
+// (gdk_analytic_statistics.c:28-147); floats: sum of doubles / n
+template <typename T> struct AvgExactOp {
+	typedef typename std::conditional<Atom<T>::is_float, dbl, hge>::type SumT;
+	struct NodeT {
+		SumT sum;
+		lng n;
+	};
+	typedef T In;
+	typedef NodeT Node;
+	typedef NodeT Acc;
+	typedef dbl Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v)
+	{
+		Node x;
+		if (Atom<T>::is_nil(v)) {
+			x.sum = 0;
+			x.n = 0;
+		} else {
+			x.sum = (SumT) v;
+			x.n = 1;
+		}
+		return x;
+	}
+	__device__ static __forceinline__ void init(Acc &a)
+	{
+		a.sum = 0;
+		a.n = 0;
+	}
+	__device__ static __forceinline__ void add(Acc &a, const Node &v, unsigned &err)
+	{
+		if (v.n == 0)
+			return;
+		if (a.n == 0)
+			a.sum = v.sum;		/* keeps the sign of a lone -0.0 */
+		else
+			a.sum += v.sum;
+		a.n += v.n;
+	}
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = a.n == 0;
+		if (isnil)
+			return NAN;
+		return (dbl) a.sum / (dbl) a.n;
+	}
+};
+
+// ---- average, frame types 0-2, integers: the reference's tree of avg_num_deltas
+// (gdk_analytic_statistics.c:158-193).  COMPUTE_LEVELN_AVG_NUM feeds a child's `a` to
+// AVERAGE_ITER as ONE value, so an inner node holds floor(mean of its children's a) and a
+// frame's result is the AVERAGE_ITER mean (a + rr/n) over the nodes the query touches.
+// AVERAGE_ITER keeps a*n + rr == sum(values) exactly, so (sum, count) in a hge gives
+// the identical a and rr whatever the order.
+template <typename T> struct AvgTreeIntOp {
+	struct NodeT {
+		T a;
+		bte has;
+	};
+	struct AccT {
+		hge sum;
+		lng n;
+	};
+	typedef T In;
+	typedef NodeT Node;
+	typedef AccT Acc;
+	typedef dbl Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v)
+	{
+		Node x;
+		x.has = !Atom<T>::is_nil(v);
+		x.a = x.has ? v : (T) 0;
+		return x;
+	}
+	__device__ static __forceinline__ void init(Acc &a)
+	{
+		a.sum = 0;
+		a.n = 0;
+	}
+	__device__ static __forceinline__ void add(Acc &a, const Node &v, unsigned &err)
+	{
+		if (v.has) {
+			a.sum += (hge) v.a;
+			a.n++;
+		}
+	}
+	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
+	{
+		q = a.sum / (hge) a.n;
+		hge r = a.sum - q * (hge) a.n;
+		if (r < 0) {
+			q--;
+			r += a.n;
+		}
+		rr = (lng) r;
+	}
+	__device__ static __forceinline__ Node node(const Acc &a)
+	{
+		Node x;
+		x.has = a.n != 0;
+		x.a = 0;
+		if (x.has) {
+			hge q;
+			lng rr;
+			floor_div(a, q, rr);
+			x.a = (T) q;
+		}
+		return x;
+	}
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = a.n == 0;
+		if (isnil)
+			return NAN;
+		hge q;
+		lng rr;
+		floor_div(a, q, rr);
+		return (dbl) (T) q + (dbl) rr / (dbl) a.n;
+	}
+};
+
+// ---- average, frame types 0-2, floats: running AVERAGE_ITER_FLOAT over the touched nodes
+// (gdk_analytic_statistics.c:268-303, gdk_calc_private.h:277-289), order-dependent and
+// therefore evaluated in the reference's order
+template <typename T> struct AvgTreeFltOp {
+	struct NodeT {
+		T a;
+		lng n;
+	};
+	typedef T In;
+	typedef NodeT Node;
+	typedef NodeT Acc;
+	typedef dbl Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v)
+	{
+		Node x;
+		x.n = Atom<T>::is_nil(v) ? 0 : 1;
+		x.a = x.n ? v : (T) 0;
+		return x;
+	}
+	__device__ static __forceinline__ void init(Acc &a)
+	{
+		a.a = 0;
+		a.n = 0;
+	}
+	__device__ static __forceinline__ void add(Acc &c, const Node &v, unsigned &err)
+	{
+		if (v.n) {
+			c.n++;
+			if ((c.a > 0) == (v.a > 0))
+				c.a += (v.a - c.a) / (T) c.n;
+			else
+				c.a = c.a - c.a / (T) c.n + v.a / (T) c.n;
+		}
+	}
+	__device__ static __forceinline__ Node node(const Acc &a) { return a; }
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = a.n == 0;
+		return isnil ? (dbl) NAN : (dbl) a.a;
+	}
+};
+
+// ---------------------------------------------------------------- host driver
+static __global__ void an_maxlen_kernel(const oid *__restrict__ S, uint64_t cnt, unsigned long long *__restrict__ out)
+{
+	unsigned long long m = 0;
+	for (uint64_t q = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; q < cnt; q += (uint64_t) gridDim.x * blockDim.x) {
+		const unsigned long long len = S[q + 1] - S[q];
+		m = len > m ? len : m;
+	}
+	if (m)
+		atomicMax(out, m);
+}
+
+struct FrameArgs {
+	const b200_bat *p, *o, *b, *s, *e;
+	int frame_type;
+	uint64_t n;
+};
+
+// runs Op over every row's frame into rb; st = {error bits, nil count}
+template <typename Op>
+static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long st[2], const char *kname)
+{
+	Ctx *c = ctx();
+	const uint64_t n = fa.n;
+	const bool peers = fa.frame_type == 3 || fa.frame_type == 4;
+	const bool framed = fa.frame_type < 3 || fa.frame_type > 6;
+	SegList S, O;
+	if (!an_partitions(fa.p, nullptr, n, S))
+		return false;
+	if (peers && !an_partitions(fa.p, fa.o, n, O))
+		return false;
+	unsigned long long *state = an_state_init();
+	if (state == nullptr)
+		return false;
+	Tree<typename Op::Node> tree;
+	if (!Op::direct && fa.frame_type != 6) {
+		an_maxlen_kernel<<<grid_for(S.cnt, 256, NSM * 8), 256, 0, c->stream>>>(S.S, S.cnt, state + 1);
+		COUNT_LAUNCH();
+		if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, state + 1, 8, cudaMemcpyDeviceToHost, c->stream), "maxlen") ||
+		    !stream_sync() || !cuda_ok(cudaMemsetAsync(state + 1, 0, 8, c->stream), "state reset")) {
+			dev_free(state);
+			return false;
+		}
+		const uint64_t maxlen = c->slot_h->v[0];
+		for (int level = 1; level < AN_MAXLEV; level++) {
+			const uint64_t below = (maxlen + ((uint64_t) 1 << (4 * (level - 1))) - 1) >> (4 * (level - 1));
+			if (below < AN_FANOUT)
+				break;
+			const uint64_t nslots = (n >> (4 * level)) + S.cnt + 1;
+			tree.lev[level] = (typename Op::Node *) dev_alloc(nslots * sizeof(typename Op::Node));
+			if (tree.lev[level] == nullptr) {
+				dev_free(state);
+				return false;
+			}
+			tree.size[level] = nslots;
+			tree.nlev = level;
+			KTimer kt("an_tree_build", level == 1 ? n * sizeof(typename Op::In) : nslots * sizeof(typename Op::Node) * 17);
+			an_tree_build_kernel<Op><<<(unsigned) ((nslots + 255) / 256), 256, 0, c->stream>>>(
+				S.S, S.cnt, (const typename Op::In *) fa.b->base, level, tree.lev[level - 1], tree.lev[level], nslots, state);
+			COUNT_LAUNCH();
+		}
+	}
+	{
+		KTimer kt(kname, n * (sizeof(typename Op::In) + sizeof(typename Op::Out) + (framed ? 16 : 0)));
+		const unsigned grid = (unsigned) ((n + AN_TILE - 1) / AN_TILE);
+		const oid *fs = framed ? (const oid *) fa.s->base : nullptr, *fe = framed ? (const oid *) fa.e->base : nullptr;
+		if (peers)
+			an_frame_kernel<Op, true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, O.S, O.cnt, n, (const typename Op::In *) fa.b->base,
+										   fs, fe, fa.frame_type, tree.dev(), rb, state);
+		else
+			an_frame_kernel<Op, false><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, nullptr, 0, n, (const typename Op::In *) fa.b->base,
+										    fs, fe, fa.frame_type, tree.dev(), rb, state);
+		COUNT_LAUNCH();
+	}
+	return an_read_state(state, st);
+}
+
+// argument checks shared by the five entry points; stages host BATs
+struct FrameStage {
+	Staged p, o, b, s, e;
+};
+bool an_frame_prepare(const char *fn, b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b, const b200_bat *s,
+		      const b200_bat *e, int rtype, int frame_type, FrameStage &fs, FrameArgs &fa);
+b200_return an_frame_done(b200_bat *r, uint64_t n, bool has_nils);

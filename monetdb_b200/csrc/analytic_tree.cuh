@@ -1,0 +1,195 @@
+// analytic_tree.cuh — the reference's fan-out-16 segment tree (gdk_analytic.h:52-130)
+// rebuilt for the device: all partitions' trees are built at once, one array per
+// level; level l >= 1 of partition q occupies slots (S[q] >> 4l) + q + t, t = 0 ..
+// ceil(len_q / 16^l) - 1 (slots of different partitions never collide because
+// floor(s/B) + ceil(len/B) <= floor((s+len)/B) + 1).  Nodes are aligned to the
+// partition start and children are combined left to right, as
+// populate_segment_tree does, and a query adds nodes in compute_on_segment_tree's
+// order, so floating-point results carry the reference's rounding.
+//
+// An aggregate is an `Op`:
+//   In, Node, Acc, Out          types
+//   leaf(In) -> Node            COMPUTE_LEVEL0_*
+//   init(Acc&)                  INIT_AGGREGATE_*
+//   add(Acc&, Node, err&)       COMPUTE_LEVELN_*
+//   node(Acc) -> Node           value stored for an inner node
+//   result(Acc, isnil&) -> Out  FINALIZE_AGGREGATE_*
+#pragma once
+#include "analytic.cuh"
+
+template <typename Node> struct TreeDev {
+	const Node *lev[AN_MAXLEV];	/* lev[0] unused */
+	int nlev;			/* highest built level */
+};
+
+template <typename Node> struct Tree {
+	Node *lev[AN_MAXLEV] = {nullptr};
+	uint64_t size[AN_MAXLEV] = {0};
+	int nlev = 0;
+	~Tree()
+	{
+		for (int i = 1; i <= nlev; i++)
+			if (lev[i])
+				dev_free(lev[i]);
+	}
+	TreeDev<Node> dev() const
+	{
+		TreeDev<Node> d;
+		for (int i = 0; i < AN_MAXLEV; i++)
+			d.lev[i] = lev[i];
+		d.nlev = nlev;
+		return d;
+	}
+};
+
+#ifdef __CUDACC__
+// build level `level` (>= 1): one thread per slot
+template <typename Op>
+__global__ void __launch_bounds__(256)
+an_tree_build_kernel(const oid *__restrict__ S, uint64_t cnt, const typename Op::In *__restrict__ bp, int level,
+		     const typename Op::Node *__restrict__ prev, typename Op::Node *__restrict__ out, uint64_t nslots,
+		     unsigned long long *__restrict__ state)
+{
+	const uint64_t c = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= nslots)
+		return;
+	const int sh = 4 * level;
+	/* partition q owning slot c: the last q with (S[q] >> sh) + q <= c */
+	uint64_t lo = 0, hi = cnt;
+	while (lo < hi) {
+		const uint64_t mid = (lo + hi) >> 1;
+		if ((S[mid] >> sh) + mid <= c)
+			lo = mid + 1;
+		else
+			hi = mid;
+	}
+	if (lo == 0)
+		return;
+	const uint64_t q = lo - 1;
+	const oid ps = S[q], len = S[q + 1] - ps;
+	const uint64_t t = c - ((ps >> sh) + q);
+	const uint64_t below = (len + ((oid) 1 << (sh - 4)) - 1) >> (sh - 4);	/* nodes of q one level down */
+	if (t * AN_FANOUT >= below)
+		return;		/* gap slot */
+	const uint64_t x0 = t * AN_FANOUT;
+	const uint64_t x1 = x0 + AN_FANOUT < below ? x0 + AN_FANOUT : below;
+	typename Op::Acc acc;
+	Op::init(acc);
+	unsigned err = 0;
+	if (level == 1) {
+		for (uint64_t x = x0; x < x1; x++)
+			Op::add(acc, Op::leaf(bp[ps + x]), err);
+	} else {
+		const uint64_t pbase = (ps >> (sh - 4)) + q;
+		for (uint64_t x = x0; x < x1; x++)
+			Op::add(acc, prev[pbase + x], err);
+	}
+	out[c] = Op::node(acc);
+	if (err)
+		atomicOr(&state[0], (unsigned long long) err);
+}
+
+template <typename Op>
+__device__ __forceinline__ typename Op::Node an_tree_node(const TreeDev<typename Op::Node> &t, const typename Op::In *__restrict__ bp,
+							  int level, oid ps, uint64_t q, uint64_t pos)
+{
+	if (level == 0)
+		return Op::leaf(bp[ps + pos]);
+	return t.lev[level][(ps >> (4 * level)) + q + pos];
+}
+
+// compute_on_segment_tree (gdk_analytic.h:93-128) for the frame [begin, tend) of partition q
+template <typename Op>
+__device__ __forceinline__ void an_tree_query(const TreeDev<typename Op::Node> &t, const typename Op::In *__restrict__ bp, oid ps,
+					      uint64_t q, uint64_t begin, uint64_t tend, typename Op::Acc &acc, unsigned &err)
+{
+	if (begin >= tend)
+		return;
+	for (int level = 0; level <= t.nlev; level++) {
+		uint64_t parent_begin = begin / AN_FANOUT, parent_end = tend / AN_FANOUT;
+		if (parent_begin == parent_end) {
+			for (uint64_t pos = begin; pos < tend; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			break;
+		}
+		const uint64_t group_begin = parent_begin * AN_FANOUT;
+		if (begin != group_begin) {
+			const uint64_t limit = group_begin + AN_FANOUT;
+			for (uint64_t pos = begin; pos < limit; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			parent_begin++;
+		}
+		const uint64_t group_end = parent_end * AN_FANOUT;
+		if (tend != group_end) {
+			for (uint64_t pos = group_end; pos < tend; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+		}
+		begin = parent_begin;
+		tend = parent_end;
+	}
+}
+
+// frame of row k (sql_catalog.h:104-113): 0-2 explicit start/end columns, 3 unbounded ->
+// current peer group, 4 current peer group -> unbounded, 5 whole partition, 6 current row.
+// DIRECT ops (count(*)) need no tree: the answer is the frame length.
+template <typename Op, bool PEERS>
+__global__ void __launch_bounds__(AN_THREADS)
+an_frame_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__ O, uint64_t ocnt, uint64_t n,
+		const typename Op::In *__restrict__ bp, const oid *__restrict__ fstart, const oid *__restrict__ fend,
+		int frame_type, TreeDev<typename Op::Node> tree, typename Op::Out *__restrict__ rb,
+		unsigned long long *__restrict__ state)
+{
+	__shared__ TileSegs ts;
+	__shared__ TileSegs to;		/* peer groups (frame types 3 and 4 only) */
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	if (PEERS)
+		to.load(O, ocnt, base, last);
+	unsigned err = 0, nils = 0;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid ps, pe;
+		const uint64_t q = ts.locate(k, ps, pe) - 1;
+		oid fs, fe;
+		switch (frame_type) {
+		case 3:
+		case 4: {
+			oid os = ps, oe = pe;
+			if (PEERS)
+				to.locate(k, os, oe);
+			fs = frame_type == 3 ? ps : os;
+			fe = frame_type == 3 ? oe : pe;
+			break;
+		}
+		case 5: fs = ps; fe = pe; break;
+		case 6: fs = k; fe = k + 1; break;
+		default: fs = fstart[k]; fe = fend[k]; break;
+		}
+		bool isnil = false;
+		typename Op::Out res;
+		if constexpr (Op::direct) {
+			res = fe > fs ? (typename Op::Out) (fe - fs) : 0;
+		} else {
+			if (fs < ps)
+				fs = ps;
+			if (fe > pe)
+				fe = pe;
+			typename Op::Acc acc;
+			Op::init(acc);
+			if (fs < fe)
+				an_tree_query<Op>(tree, bp, ps, q, fs - ps, fe - ps, acc, err);
+			res = Op::result(acc, isnil);
+		}
+		rb[k] = res;
+		nils += isnil;
+	}
+	if (err)
+		atomicOr(&state[0], (unsigned long long) err);
+	nils = __reduce_add_sync(0xffffffffu, nils);
+	if ((threadIdx.x & 31) == 0 && nils)
+		atomicAdd(&state[1], (unsigned long long) nils);
+}
+#endif

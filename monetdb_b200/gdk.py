@@ -455,6 +455,55 @@ def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if
     return out
 
 
+# ------------------------------------------------------------------ window functions (gdk_analytic.h:21-42)
+_sig("b200_GDKanalyticaldiff", C.c_int, _P, _P, _P, C.c_void_p, C.c_int)
+_sig("b200_GDKanalyticalwindowbounds", C.c_int, _P, _P, _P, _P, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_bool, C.c_uint64)
+_sig("b200_GDKanalyticalsum", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int)
+for _n in ("avg", "min", "max"):
+    _sig(f"b200_GDKanalytical{_n}", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int)
+_sig("b200_GDKanalyticalcount", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int8, C.c_int, C.c_int)
+
+
+def colnew(tt: int, cap: int, hseq: int = 0) -> BAT:
+    """caller-allocated result BAT for the GDKanalytical* functions (sql_rank.c:161)"""
+    return COLnew(hseq, tt, cap)
+
+
+def _ok(rc, what):
+    if rc != 1:
+        _fail(what)
+
+
+def GDKanalyticaldiff(r, b, p, npbit, tpe):
+    nb = np.array([npbit], dtype=np.int8) if npbit is not None else None
+    _ok(lib.b200_GDKanalyticaldiff(r._p, b._p, _ptr(p), _vp(nb), tpe), "GDKanalyticaldiff")
+    return r
+
+
+def GDKanalyticalwindowbounds(r, b, p, l, bound, tp1, tp2, unit, preceding, first_half):
+    bv = _val(_storage(tp2), bound) if bound is not None else None
+    _ok(lib.b200_GDKanalyticalwindowbounds(r._p, _ptr(b), _ptr(p), _ptr(l), _vp(bv), tp1, tp2, unit, preceding, first_half),
+        "GDKanalyticalwindowbounds")
+    return r
+
+
+def GDKanalyticalsum(r, p, o, b, s, e, tp1, tp2, frame_type):
+    _ok(lib.b200_GDKanalyticalsum(r._p, _ptr(p), _ptr(o), b._p, _ptr(s), _ptr(e), tp1, tp2, frame_type), "GDKanalyticalsum")
+    return r
+
+
+def GDKanalyticalfn(name, r, p, o, b, s, e, tpe, frame_type):
+    """GDKanalyticalavg / min / max"""
+    _ok(getattr(lib, "b200_GDKanalytical" + name)(r._p, _ptr(p), _ptr(o), b._p, _ptr(s), _ptr(e), tpe, frame_type), name)
+    return r
+
+
+def GDKanalyticalcount(r, p, o, b, s, e, ignore_nils, tpe, frame_type):
+    _ok(lib.b200_GDKanalyticalcount(r._p, _ptr(p), _ptr(o), b._p, _ptr(s), _ptr(e), 1 if ignore_nils else 0, tpe, frame_type),
+        "GDKanalyticalcount")
+    return r
+
+
 # ------------------------------------------------------------------ bench support
 _sig("b200_timing_enable", None, C.c_int)
 _sig("b200_timing_read", C.c_int, C.c_char_p, C.c_size_t)

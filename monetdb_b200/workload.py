@@ -87,3 +87,40 @@ def config1(lo: int, hi: int):
     zk = splitmix64(col_seed(C_K), lo, hi)
     zv = splitmix64(col_seed(C_V), lo, hi)
     return (zk % np.uint64(1000)).astype(np.int32), ((zv >> np.uint64(32)) % np.uint64(100000)).astype(np.int64)
+
+
+C_WPERM, C_WORD, C_WVAL = 10, 11, 12
+_PERMS = [(0, 1, 2), (0, 2, 1), (1, 0, 2), (1, 2, 0), (2, 0, 1), (2, 1, 0)]
+
+
+def window_layout(lens=(1000, 10000, 100000)):
+    """config 5 partitioning: rows come in blocks of sum(lens) rows; block k holds one partition of
+    each length, in the order given by permutation z(k) % 6 — so the partition of any row can be
+    computed without generating the rows before it"""
+    return sum(lens)
+
+
+def window(lo: int, hi: int, lens=(1000, 10000, 100000)) -> dict:
+    """rows [lo,hi) of the window-analytics table (config 5): pkey (lng, ascending), ord (lng,
+    ascending within a partition with duplicates: prev + z%3), val (lng = z%10000 - 5000).
+    lo must be a multiple of sum(lens) (shards start on block = partition boundaries)."""
+    blk = sum(lens)
+    assert lo % blk == 0, "window shards must start on a block boundary"
+    n = hi - lo
+    b0, b1 = lo // blk, (hi + blk - 1) // blk
+    zperm = splitmix64(col_seed(C_WPERM), b0, b1) % np.uint64(6)
+    starts = np.empty((b1 - b0) * 3, dtype=np.int64)     # partition start rows (absolute)
+    for i, zp in enumerate(zperm):
+        off = (b0 + i) * blk
+        for j, which in enumerate(_PERMS[int(zp)]):
+            starts[3 * i + j] = off
+            off += lens[which]
+    rows = np.arange(lo, hi, dtype=np.int64)
+    pidx = np.searchsorted(starts, rows, side="right") - 1
+    pkey = (3 * b0 + pidx).astype(np.int64)
+    inc = (splitmix64(col_seed(C_WORD), lo, hi) % np.uint64(3)).astype(np.int64)
+    c = np.cumsum(inc)
+    pstart = starts[pidx] - lo
+    ordv = c - c[pstart]
+    val = (splitmix64(col_seed(C_WVAL), lo, hi) % np.uint64(10000)).astype(np.int64) - 5000
+    return {"pkey": pkey, "ord": ordv, "val": val, "n": n}

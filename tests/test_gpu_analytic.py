@@ -1,0 +1,359 @@
+"""GDKanalyticaldiff / windowbounds / sum / avg / count / min / max: CUDA vs the real reference GDK
+(gdk_analytic_bounds.c, gdk_analytic_func.c, gdk_analytic_statistics.c).  Integer results, frame
+bounds and framed floating-point sums (same fan-out-16 tree order) are compared bit for bit;
+running floating-point sums/averages (frame types 3-5, sequential in the reference) within
+1e-12 (dbl) / 1e-5 (flt) relative."""
+import numpy as np
+import pytest
+
+from tests.util import both, has_nil, random_col, same_bits
+from monetdb_b200 import gdk as G
+
+pytestmark = pytest.mark.gpu
+T = G.TYPE
+
+
+def window(rng, n, nparts, tt=T.lng, nilfrac=0.0, step=3):
+    """sorted partitions with an ascending order column (duplicates) -> pkey, ord"""
+    cuts = np.sort(rng.choice(np.arange(1, n), size=min(nparts - 1, n - 1), replace=False)) if n > 1 and nparts > 1 else []
+    pkey = np.zeros(n, dtype=np.int32)
+    pkey[cuts] = 1
+    pkey = np.cumsum(pkey).astype(np.int32)
+    inc = rng.integers(0, step, n)
+    o = np.cumsum(inc)
+    start_of = np.zeros(n, dtype=np.int64)
+    if n:
+        # restart the order value in every partition
+        start_of = np.maximum.accumulate(np.where(np.r_[True, pkey[1:] != pkey[:-1]], np.arange(n), 0))
+        o = o - o[start_of]
+    if tt in (T.flt, T.dbl):
+        a = (o * 0.5).astype(G.NP_OF[tt])
+        if nilfrac:
+            # nils sort first within a partition: put them at the partition starts
+            m = (rng.random(n) < nilfrac) & (np.arange(n) == start_of)
+            a[m] = np.nan
+        return pkey, a
+    a = o.astype(G.NP_OF[tt]) if tt != T.hge else G.hge_from_i64(o)
+    if nilfrac and tt != T.hge:
+        m = (rng.random(n) < nilfrac * 20) & (np.arange(n) == start_of)
+        a[m] = np.iinfo(G.NP_OF[tt]).min
+    return pkey, a
+
+
+def flags(gdk, ref, col, tt, prior=None, rprior=None):
+    """partition / peer flags through GDKanalyticaldiff on both sides"""
+    n = len(col)
+    b, rb = both(gdk, ref, col, tt)
+    r = gdk.GDKanalyticaldiff(gdk.colnew(T.bit, n), b, prior, None, tt)
+    rr = ref.GDKanalyticaldiff(ref.colnew(T.bit, n), rb, rprior, None, tt)
+    assert same_bits(r.numpy(), rr.numpy())
+    return r, rr
+
+
+def check_oid(o, r):
+    a, b = o.numpy(), r.numpy()
+    assert len(a) == len(b)
+    assert same_bits(a, b), (a[:20], b[:20], np.flatnonzero(a != b)[:10])
+    po, pr = o.props(), r.props()
+    assert (po["nonil"], po["nil"]) == (pr["nonil"], pr["nil"])
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.hge, T.flt, T.dbl])
+@pytest.mark.parametrize("mode", ["none", "prior", "npbit"])
+def test_diff(gdk, ref, tt, mode):
+    rng = np.random.default_rng(tt * 7 + len(mode))
+    for n in (0, 1, 2, 33, 4097, 50021):
+        a = random_col(rng, tt, n, nilfrac=0.2, lo=0, hi=3)
+        b, rb = both(gdk, ref, a, tt)
+        prior = rprior = None
+        npbit = None
+        if mode == "prior":
+            pf = (rng.random(n) < 0.1).astype(np.int8)
+            prior, rprior = both(gdk, ref, pf, T.bit)
+        elif mode == "npbit":
+            npbit = 1
+        r = gdk.GDKanalyticaldiff(gdk.colnew(T.bit, n), b, prior, npbit, tt)
+        rr = ref.GDKanalyticaldiff(ref.colnew(T.bit, n), rb, rprior, npbit, tt)
+        assert same_bits(r.numpy(), rr.numpy()), (tt, mode, n)
+        assert r.props()["nonil"] and not r.props()["nil"]
+
+
+@pytest.mark.parametrize("n,nparts", [(0, 1), (1, 1), (2, 2), (31, 3), (1025, 1), (4099, 40), (70001, 9), (70001, 30000)])
+@pytest.mark.parametrize("preceding", [True, False])
+def test_rows_bounds(gdk, ref, n, nparts, preceding):
+    rng = np.random.default_rng(n + nparts)
+    pkey, o = window(rng, n, nparts)
+    p, rp = flags(gdk, ref, pkey, T.int) if n else both(gdk, ref, np.zeros(0, np.int8), T.bit)
+    b, rb = both(gdk, ref, o, T.lng)
+    for lim, tp2, half in ((0, T.lng, 1), (0, T.lng, 0), (3, T.int, 0), (100, T.lng, 1), (5, T.bte, 1), ((1 << 63) - 1, T.lng, 0),
+                           (7, T.hge, 0)):
+        r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, T.lng, tp2, 0, preceding, half)
+        rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, T.lng, tp2, 0, preceding, half)
+        check_oid(r, rr)
+    # no partition column at all
+    r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, None, None, 2, T.lng, T.lng, 0, preceding, 0)
+    rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, None, None, 2, T.lng, T.lng, 0, preceding, 0)
+    check_oid(r, rr)
+    # dynamic bounds
+    if n:
+        for dt in (T.bte, T.int, T.lng, T.hge):
+            lcol = random_col(rng, dt, n, lo=0, hi=9)
+            l, rl = both(gdk, ref, lcol, dt)
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, l, None, T.lng, dt, 0, preceding, 1)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, rl, None, T.lng, dt, 0, preceding, 1)
+            check_oid(r, rr)
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.hge, T.flt, T.dbl])
+@pytest.mark.parametrize("preceding", [True, False])
+def test_range_bounds(gdk, ref, tt, preceding):
+    rng = np.random.default_rng(tt)
+    for n, nparts, nilfrac in ((1, 1, 0), (40, 3, 0), (5003, 17, 0), (5003, 17, 0.5), (30011, 300, 0.5)):
+        step = 2 if tt == T.bte else 3
+        if tt == T.bte:
+            n, nparts = min(n, 90), min(nparts, 3)
+        pkey, o = window(rng, n, nparts, tt, nilfrac, step)
+        p, rp = flags(gdk, ref, pkey, T.int)
+        b, rb = both(gdk, ref, o, tt)
+        if tt in (T.flt, T.dbl):
+            cases = [(1.5, tt), (0.0, tt), (float(np.finfo(G.NP_OF[tt]).max), tt), (0.25, tt)]
+        elif tt == T.hge:
+            cases = [(5, T.hge), (0, T.hge), ((1 << 127) - 1, T.hge)]
+        else:
+            cases = [(5, T.lng), (0, T.lng), (1, T.int), (2, T.bte), (3, T.hge), ((1 << 63) - 1, T.lng), (127, T.bte)]
+        for lim, tp2 in cases:
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, tt, tp2, 1, preceding, 0)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, tt, tp2, 1, preceding, 0)
+            check_oid(r, rr)
+        if tt not in (T.flt, T.dbl, T.hge):
+            lcol = random_col(rng, T.int, n, lo=0, hi=6)
+            l, rl = both(gdk, ref, lcol, T.int)
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, l, None, tt, T.int, 1, preceding, 0)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, rl, None, tt, T.int, 1, preceding, 0)
+            check_oid(r, rr)
+
+
+@pytest.mark.parametrize("preceding", [True, False])
+def test_groups_bounds(gdk, ref, preceding):
+    rng = np.random.default_rng(5)
+    for n, nparts in ((1, 1), (50, 4), (6007, 23), (40009, 2000)):
+        pkey, o = window(rng, n, nparts)
+        p, rp = flags(gdk, ref, pkey, T.int)
+        op, rop = flags(gdk, ref, o, T.lng, p, rp)       # peer starts (includes partition starts)
+        for lim, tp2 in ((0, T.lng), (1, T.lng), (4, T.int), (1000, T.lng), ((1 << 63) - 1, T.lng)):
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), op, p, None, lim, T.bit, tp2, 2, preceding, 0)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rop, rp, None, lim, T.bit, tp2, 2, preceding, 0)
+            check_oid(r, rr)
+        lcol = random_col(rng, T.lng, n, lo=0, hi=5)
+        l, rl = both(gdk, ref, lcol, T.lng)
+        r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), op, p, l, None, T.bit, T.lng, 2, preceding, 0)
+        rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rop, rp, rl, None, T.bit, T.lng, 2, preceding, 0)
+        check_oid(r, rr)
+
+
+def test_bound_errors(gdk, ref):
+    rng = np.random.default_rng(1)
+    n = 100
+    pkey, o = window(rng, n, 3)
+    p, rp = flags(gdk, ref, pkey, T.int)
+    b, rb = both(gdk, ref, o, T.lng)
+    for unit, word in ((0, "row"), (1, "range"), (2, "groups")):
+        bb, rbb = (b, rb) if unit != 2 else (p, rp)
+        with pytest.raises(G.GDKError) as e1:
+            gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), bb, p, None, -1, T.lng, T.lng, unit, True, 0)
+        with pytest.raises(Exception) as e2:
+            ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rbb, rp, None, -1, T.lng, T.lng, unit, True, 0)
+        assert str(e1.value).strip() == str(e2.value).strip() == f"42000!{word} frame bound must be non negative and non null."
+    # dynamic bound with a negative entry
+    lcol = np.full(n, 2, dtype=np.int64)
+    lcol[37] = -4
+    l, rl = both(gdk, ref, lcol, T.lng)
+    with pytest.raises(G.GDKError) as e1:
+        gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, l, None, T.lng, T.lng, 0, True, 0)
+    with pytest.raises(Exception) as e2:
+        ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, rl, None, T.lng, T.lng, 0, True, 0)
+    assert str(e1.value).strip() == str(e2.value).strip()
+    # RANGE overflow of the checked subtraction
+    big = np.array([-(1 << 62) - 5, 0, (1 << 62) + 5], dtype=np.int64)
+    bb, rbb = both(gdk, ref, big, T.lng)
+    with pytest.raises(G.GDKError) as e1:
+        gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, 3), bb, None, None, (1 << 63) - 2, T.lng, T.lng, 1, True, 0)
+    with pytest.raises(Exception) as e2:
+        ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, 3), rbb, None, None, (1 << 63) - 2, T.lng, T.lng, 1, True, 0)
+    assert str(e1.value).strip() == str(e2.value).strip() == "22003!overflow in calculation."
+
+
+# ------------------------------------------------------------------ framed aggregates
+def frames(gdk, ref, n, nparts, rng, rows=(3, 2), nilfrac=0.0):
+    """partition flags, peer flags and ROWS start/end columns on both sides"""
+    pkey, o = window(rng, n, nparts)
+    p, rp = flags(gdk, ref, pkey, T.int)
+    op, rop = flags(gdk, ref, o, T.lng, p, rp)
+    b, rb = both(gdk, ref, o, T.lng)
+    s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, rows[0], T.lng, T.lng, 0, True, 0)
+    rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, rows[0], T.lng, T.lng, 0, True, 0)
+    e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, rows[1], T.lng, T.lng, 0, False, 1)
+    re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, rows[1], T.lng, T.lng, 0, False, 1)
+    return (p, op, s, e), (rp, rop, rs, re_)
+
+
+def close(a, b, tt_out, exact, mag=1.0):
+    """mag: magnitude of the input data — the reference's sequential flt running mean loses
+    accuracy relative to the data it has seen, not to the (possibly small) current mean"""
+    if exact:
+        assert same_bits(a, b), (a[:10], b[:10], np.flatnonzero(a.view(np.uint8).reshape(len(a), -1) != b.view(np.uint8).reshape(len(b), -1))[:10])
+        return
+    tol = 1e-5 if tt_out == T.flt else 1e-12
+    na, nb = np.isnan(a), np.isnan(b)
+    assert np.array_equal(na, nb)
+    scale = np.maximum(np.abs(b[~nb]), mag)
+    assert np.all(np.abs(a[~na] - b[~nb]) <= tol * scale), np.max(np.abs(a[~na] - b[~nb]) / scale)
+
+
+def _check_avg_suffix(got, v, pf, of):
+    """frame type 4: mean of the non-nil values from the start of the row's peer group to the end
+    of its partition"""
+    n = len(v)
+    pstart = [i for i in range(n) if i == 0 or pf[i]] + [n]
+    for a, z in zip(pstart[:-1], pstart[1:]):
+        ostart = [i for i in range(a, z) if i == a or of[i]]
+        for j, os_ in enumerate(ostart):
+            oe = ostart[j + 1] if j + 1 < len(ostart) else z
+            w = v[os_:z].astype(np.float64)
+            w = w[~np.isnan(w)]
+            want = w.mean() if len(w) else np.nan
+            for k in range(os_, oe):
+                assert (np.isnan(want) and np.isnan(got[k])) or abs(got[k] - want) <= 1e-9 * max(1.0, abs(want)), (k, got[k], want)
+
+
+SHAPES = [(1, 1, (3, 2)), (37, 3, (3, 2)), (5000, 7, (40, 25)), (70001, 11, (300, 0)), (70001, 11, (5000, 5000)), (30000, 9000, (2, 2))]
+
+
+@pytest.mark.parametrize("tp1,tp2", [(T.bte, T.bte), (T.bte, T.lng), (T.sht, T.int), (T.int, T.lng), (T.int, T.hge), (T.lng, T.lng),
+                                     (T.lng, T.hge), (T.hge, T.hge), (T.flt, T.flt), (T.flt, T.dbl), (T.dbl, T.dbl)])
+@pytest.mark.parametrize("frame_type", [0, 3, 4, 5, 6])
+def test_sum(gdk, ref, tp1, tp2, frame_type):
+    rng = np.random.default_rng(tp1 * 31 + tp2 + frame_type)
+    for n, nparts, rows in SHAPES:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        lo, hi = (-1, 1) if tp2 == T.bte else (-3, 3) if tp2 == T.int else (-1000, 1000)
+        if tp1 in (T.flt, T.dbl):
+            v = np.round(random_col(rng, tp1, n, nilfrac=0.1, lo=lo, hi=hi) * 8) / 8
+            v = v.astype(G.NP_OF[tp1])
+        else:
+            v = random_col(rng, tp1, n, nilfrac=0.1, lo=lo, hi=hi)
+        if tp2 == T.bte and n > 100:
+            continue
+        b, rb = both(gdk, ref, v, tp1)
+        r = gdk.GDKanalyticalsum(gdk.colnew(tp2, n), p, op, b, s, e, tp1, tp2, frame_type)
+        rr = ref.GDKanalyticalsum(ref.colnew(tp2, n), rp, rop, rb, rs, re_, tp1, tp2, frame_type)
+        exact = tp2 not in (T.flt, T.dbl) or frame_type in (0, 6)
+        close(r.numpy(), rr.numpy(), tp2, exact)
+        assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
+
+
+def test_sum_overflow(gdk, ref):
+    n = 40
+    v = np.full(n, (1 << 62), dtype=np.int64)
+    b, rb = both(gdk, ref, v, T.lng)
+    o, ro = both(gdk, ref, np.zeros(n, dtype=np.int8), T.bit)
+    for ft in (3, 5):
+        with pytest.raises(G.GDKError) as e1:
+            gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), None, o, b, None, None, T.lng, T.lng, ft)
+        with pytest.raises(Exception) as e2:
+            ref.GDKanalyticalsum(ref.colnew(T.lng, n), None, ro, rb, None, None, T.lng, T.lng, ft)
+        assert str(e1.value).strip() == str(e2.value).strip() == "22003!overflow in calculation."
+    with pytest.raises(G.GDKError) as e1:
+        gdk.GDKanalyticalsum(gdk.colnew(T.flt, n), None, None, b, None, None, T.lng, T.flt, 5)
+    assert "not supported" in str(e1.value)
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.flt, T.dbl])
+@pytest.mark.parametrize("frame_type", [0, 3, 4, 5, 6])
+def test_avg(gdk, ref, tt, frame_type):
+    rng = np.random.default_rng(tt * 31 + frame_type)
+    for n, nparts, rows in SHAPES:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        if tt in (T.flt, T.dbl):
+            v = (np.round(random_col(rng, tt, n, nilfrac=0.1, lo=-1000, hi=1000) * 8) / 8).astype(G.NP_OF[tt])
+        else:
+            v = random_col(rng, tt, n, nilfrac=0.1)
+        b, rb = both(gdk, ref, v, tt)
+        r = gdk.GDKanalyticalfn("avg", gdk.colnew(T.dbl, n), p, op, b, s, e, tt, frame_type)
+        if tt in (T.flt, T.dbl) and frame_type == 4:
+            # reference quirk: ANALYTICAL_AVG_IMP_FP_CURRENT_ROW_TILL_UNBOUNDED never assigns curval
+            # (gdk_analytic_statistics.c:228-250), so the reference returns nil for every row.  We
+            # return the mean the frame defines; check it against a direct evaluation instead.
+            if n <= 5000:
+                _check_avg_suffix(r.numpy(), v, p.numpy(), op.numpy())
+            continue
+        rr = ref.GDKanalyticalfn("avg", ref.colnew(T.dbl, n), rp, rop, rb, rs, re_, tt, frame_type)
+        # integers: exact formula on both sides; floats: framed = same tree order (bit-exact),
+        # running means are sequential in the reference -> tolerance
+        exact = tt not in (T.flt, T.dbl) or frame_type in (0, 6)
+        if tt == T.flt and not exact:
+            close(r.numpy(), rr.numpy(), T.flt, False, mag=1000.0)
+        else:
+            close(r.numpy(), rr.numpy(), T.dbl, exact)
+        assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.int, T.lng, T.hge, T.dbl])
+@pytest.mark.parametrize("frame_type", [0, 3, 4, 5, 6])
+@pytest.mark.parametrize("ignore_nils", [True, False])
+def test_count(gdk, ref, tt, frame_type, ignore_nils):
+    rng = np.random.default_rng(tt * 31 + frame_type)
+    for n, nparts, rows in SHAPES[:5]:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        v = random_col(rng, tt, n, nilfrac=0.3, lo=0, hi=9)
+        b, rb = both(gdk, ref, v, tt)
+        r = gdk.GDKanalyticalcount(gdk.colnew(T.lng, n), p, op, b, s, e, ignore_nils, tt, frame_type)
+        rr = ref.GDKanalyticalcount(ref.colnew(T.lng, n), rp, rop, rb, rs, re_, ignore_nils, tt, frame_type)
+        close(r.numpy(), rr.numpy(), T.lng, True)
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.hge, T.flt, T.dbl])
+@pytest.mark.parametrize("frame_type", [0, 3, 4, 5, 6])
+@pytest.mark.parametrize("fn", ["min", "max"])
+def test_minmax(gdk, ref, tt, frame_type, fn):
+    rng = np.random.default_rng(tt * 31 + frame_type)
+    for n, nparts, rows in SHAPES[:5]:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        v = random_col(rng, tt, n, nilfrac=0.3)
+        if tt in (T.flt, T.dbl):
+            v[v == 0] = 1      # keep away from -0/+0 ties
+        b, rb = both(gdk, ref, v, tt)
+        r = gdk.GDKanalyticalfn(fn, gdk.colnew(tt, n), p, op, b, s, e, tt, frame_type)
+        rr = ref.GDKanalyticalfn(fn, ref.colnew(tt, n), rp, rop, rb, rs, re_, tt, frame_type)
+        a, c = r.numpy(), rr.numpy()
+        if tt in (T.flt, T.dbl):
+            assert np.array_equal(np.isnan(a), np.isnan(c)) and np.array_equal(a[~np.isnan(a)], c[~np.isnan(c)])
+        else:
+            close(a, c, tt, True)
+        assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
+
+
+def test_config5_shape(gdk, ref):
+    """config 5 at a size the oracle finishes quickly: ROWS 100 PRECEDING..CURRENT ROW and
+    RANGE 50 PRECEDING..50 FOLLOWING, moving sum (lng -> hge) and avg"""
+    from monetdb_b200 import workload
+    n = 300_000
+    cols = workload.window(0, n, lens=(100, 1000, 20000))
+    pk, rpk = both(gdk, ref, cols["pkey"], T.lng)
+    p = gdk.GDKanalyticaldiff(gdk.colnew(T.bit, n), pk, None, None, T.lng)
+    rp = ref.GDKanalyticaldiff(ref.colnew(T.bit, n), rpk, None, None, T.lng)
+    o, ro = both(gdk, ref, cols["ord"], T.lng)
+    v, rv = both(gdk, ref, cols["val"], T.lng)
+    for unit, lo, hi, half in ((0, 100, 0, 1), (1, 50, 50, 0)):
+        s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, lo, T.lng, T.lng, unit, True, 0)
+        rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, lo, T.lng, T.lng, unit, True, 0)
+        e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, hi, T.lng, T.lng, unit, False, half)
+        re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, hi, T.lng, T.lng, unit, False, half)
+        check_oid(s, rs)
+        check_oid(e, re_)
+        r = gdk.GDKanalyticalsum(gdk.colnew(T.hge, n), p, None, v, s, e, T.lng, T.hge, unit)
+        rr = ref.GDKanalyticalsum(ref.colnew(T.hge, n), rp, None, rv, rs, re_, T.lng, T.hge, unit)
+        close(r.numpy(), rr.numpy(), T.hge, True)
+        r = gdk.GDKanalyticalfn("avg", gdk.colnew(T.dbl, n), p, None, v, s, e, T.lng, unit)
+        rr = ref.GDKanalyticalfn("avg", ref.colnew(T.dbl, n), rp, None, rv, rs, re_, T.lng, unit)
+        close(r.numpy(), rr.numpy(), T.dbl, True)
