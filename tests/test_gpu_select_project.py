@@ -147,3 +147,25 @@ def test_cand_algebra(gdk, ref, ka, kb):
     assert same_bits(gdk.BATmergecand(a, b).numpy(), ref.BATmergecand(ra, rb).numpy())
     assert same_bits(gdk.BATintersectcand(a, b).numpy(), ref.BATintersectcand(ra, rb).numpy())
     assert same_bits(gdk.BATdiffcand(a, b).numpy(), ref.BATdiffcand(ra, rb).numpy())
+
+
+def test_select_maltest_golden(gdk):
+    """the reference's own select matrix (monetdb5/modules/kernel/Tests/select.maltest, 192 cases,
+    fixture tests/golden/select_maltest.json) through the CUDA path"""
+    import json
+    from pathlib import Path
+    d = json.loads((Path(__file__).parent / "golden" / "select_maltest.json").read_text())
+    nil = np.iinfo(np.int32).min
+    b = np.array([nil if v is None else v for v in d["b"]], dtype=np.int32)
+    srt = np.sort(b)
+    vals = {"b": b, "s": srt, "r": srt[::-1].copy()}
+    cols = {"b": gdk.BATfromhost(b, G.TYPE.int, nil=True), "s": gdk.BATfromhost(srt, G.TYPE.int, sorted=True, nil=True),
+            "r": gdk.BATfromhost(vals["r"], G.TYPE.int, revsorted=True, nil=True)}
+    for c in d["cases"]:
+        lo = nil if c["lo"] is None else c["lo"]
+        hi = nil if c["hi"] is None else c["hi"]
+        if c["li"] and c["hi_incl"] and c["lo"] is None and c["hi"] is None:
+            hi = None           # algebra.c:298-305
+        x = gdk.BATselect(cols[c["col"]], None, lo, hi, c["li"], c["hi_incl"], c["anti"], False)
+        got = sorted(vals[c["col"]][x.numpy().astype(np.int64)].tolist())
+        assert got == sorted(nil if v is None else v for v in c["values"]), c
