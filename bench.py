@@ -218,8 +218,11 @@ def b200_arm(args):
 
     # ---- device-resident leg (value); per-kernel CUDA events on the launching stream are
     # recorded over the same timed region (the warm-up records are discarded inside timed())
-    G.timing_enable(True)
     ms, wall, res, launches, clocks = timed(dev, args.steps, args.warmup, sample_clocks=True)
+    # a second pass over the same region with the per-kernel CUDA events switched on (the events
+    # cost host time, so they stay out of the pass `value` comes from)
+    G.timing_enable(True)
+    timed(dev, args.steps, 1)
     ktimes = G.timing_read()
     G.timing_enable(False)
     # ---- e2e leg: host heaps through the C-ABI
@@ -232,10 +235,12 @@ def b200_arm(args):
     nsel = dict(counts)
     by = pipelines.q6_bytes(n, nsel["n1"], nsel["n2"], nsel["n3"])
     peak, peak_src = measured_hbm_peak()
-    # dominant kernel: the dense scan of l_shipdate (select 1)
+    # dominant operator: BATselect on l_shipdate (dense candidates) = mask scan + offset scan + expand;
+    # its first kernel (select_dense) is the dominant kernel of the step
     nl, kms, _ = ktimes.get("select_dense", (0, 0.0, 0))
     per_launch_ms = kms / nl if nl else None
-    achieved = by["select1"] / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms else None
+    mask_bytes = 4 * n + n // 8                         # column read once + one mask bit per row written
+    achieved = mask_bytes / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms else None
     total_rows = n * world
     value = total_rows * args.steps / (ms * 1e-3)
     h2d = 4 * n + 8 * n * 2 + 8 * n + 8 * n           # shipdate + discount (select, project) + quantity + extprice
@@ -257,7 +262,8 @@ def b200_arm(args):
                 "d2h_bytes_per_step": 16 + 7 * 32, "ms_per_step": ms_e / e2e_steps, "steps": e2e_steps},
         "roofline": {"bound": "hbm", "kernel": "select_dense_kernel<int> (BATselect on l_shipdate)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": by["select1"],
+                     "traffic": 245877248, "traffic_source": "ncu --set full, profiles/r1_q6_kernels_v1.md (dram read+write per launch)",
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": mask_bytes,
                      "launch_ms": per_launch_ms},
     }
     if world == 1 and not args.no_cpu:

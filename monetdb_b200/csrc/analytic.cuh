@@ -59,11 +59,9 @@ template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
 		return false;
 	{
 		KTimer kt("an_seg_mask", n);
-		compact_mask_kernel<F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+		compact_launch_mask(s, n, f);
 	}
-	COUNT_LAUNCH();
-	compact_scan_kernel<<<1, 1024, 0, c->stream>>>(s.counts, s.nchunks, s.offs, c->slot_d->v);
-	COUNT_LAUNCH();
+	compact_launch_scan(s);
 	if (!cuda_ok(cudaGetLastError(), "seglist launch") || !stream_sync())
 		return false;
 	out.cnt = c->slot_h->v[0];
@@ -71,9 +69,7 @@ template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
 	if (out.S == nullptr)
 		return false;
 	if (out.cnt) {
-		compact_expand_kernel<FunctorOid<F>><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(
-			s.words, s.counts, s.offs, FunctorOid<F>{f}, out.S, c->slot_d->v);
-		COUNT_LAUNCH();
+		compact_launch_expand(s, FunctorOid<F>{f}, out.S);
 	}
 	an_set_u64<<<1, 1, 0, c->stream>>>(out.S + out.cnt, n);
 	COUNT_LAUNCH();

@@ -19,20 +19,23 @@
 #include "common.cuh"
 
 #define CP_THREADS 256
-#define CP_CHUNK 8192			/* indexes per CTA: 256 mask words, 32 per warp */
+#define CP_CHUNK 8192			/* indexes per CTA for large inputs: 256 mask words */
+#define CP_CHUNK_SMALL 2048		/* ... and for inputs too small to fill the 148 SMs with 8192-index chunks */
 #define CP_WORDS (CP_CHUNK / 32)
 
 struct CompactScratch {
-	uint32_t *words;		/* nchunks * CP_WORDS */
+	uint32_t *words;		/* nchunks * chunk / 32 */
 	uint32_t *counts;		/* nchunks */
 	unsigned long long *offs;	/* nchunks + 1: exclusive offsets, then the total */
 	uint64_t nchunks;
+	unsigned chunk;			/* CP_CHUNK or CP_CHUNK_SMALL */
 };
 
-static inline bool compact_scratch(uint64_t n, CompactScratch &s)
+static inline bool compact_scratch(uint64_t n, CompactScratch &s, unsigned force_chunk = 0)
 {
-	s.nchunks = (n + CP_CHUNK - 1) / CP_CHUNK;
-	size_t wbytes = s.nchunks * CP_WORDS * 4, cbytes = (s.nchunks * 4 + 15) & ~(size_t) 15;
+	s.chunk = force_chunk ? force_chunk : (n < (uint64_t) NSM * 8 * CP_CHUNK ? CP_CHUNK_SMALL : CP_CHUNK);
+	s.nchunks = (n + s.chunk - 1) / s.chunk;
+	size_t wbytes = s.nchunks * (s.chunk / 32) * 4, cbytes = (s.nchunks * 4 + 15) & ~(size_t) 15;
 	char *p = (char *) scratch_get(wbytes + cbytes + (s.nchunks + 1) * 8);
 	if (p == nullptr)
 		return false;
@@ -45,7 +48,7 @@ static inline bool compact_scratch(uint64_t n, CompactScratch &s)
 // ---- step 1 (generic form): F is a functor with
 //        bool operator()(uint64_t idx, oid &o)   the test
 //        oid  at(uint64_t idx)                   the oid to emit for a hit
-template <typename F>
+template <int CHUNK, typename F>
 __global__ void __launch_bounds__(CP_THREADS)
 compact_mask_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
 {
@@ -54,19 +57,18 @@ compact_mask_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__r
 		total = 0;
 	__syncthreads();
 	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint64_t cbase = (uint64_t) blockIdx.x * CP_CHUNK;
-	unsigned cnt = 0;
+	const uint64_t cbase = (uint64_t) blockIdx.x * CHUNK;
+	unsigned cnt = 0;		/* warp-uniform */
 #pragma unroll 8
-	for (int j = 0; j < CP_CHUNK / CP_THREADS; j++) {
+	for (int j = 0; j < CHUNK / CP_THREADS; j++) {
 		/* warp w evaluates 32 consecutive indexes per step: the ballot IS the mask word */
 		const uint64_t idx = cbase + (uint64_t) (j * (CP_THREADS / 32) + warp) * 32 + lane;
 		oid o;
 		const bool h = idx < n && f(idx, o);
 		const unsigned bal = __ballot_sync(0xffffffffu, h);
-		if (lane == 0) {
+		if (lane == 0)
 			words[idx >> 5] = bal;
-			cnt += __popc(bal);
-		}
+		cnt += __popc(bal);
 	}
 	if (lane == 0 && cnt)
 		atomicAdd(&total, cnt);
@@ -75,73 +77,77 @@ compact_mask_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__r
 		counts[blockIdx.x] = total;
 }
 
-// ---- step 2: exclusive scan of the chunk counts by one CTA; total -> slot[0]
+// ---- step 2: exclusive scan of the chunk counts by one CTA; total -> slot[0].
+// Every thread owns a contiguous run of counts, so all its loads are independent.
 static __global__ void __launch_bounds__(1024)
 compact_scan_kernel(const uint32_t *__restrict__ counts, uint64_t nchunks, unsigned long long *__restrict__ offs,
 		    unsigned long long *__restrict__ slot)
 {
 	__shared__ unsigned long long wsum[32];
-	__shared__ unsigned long long itertotal;
 	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	unsigned long long carry = 0;		/* uniform across the CTA */
-	for (uint64_t base = 0; base < nchunks; base += 1024) {
-		const uint64_t i = base + threadIdx.x;
-		const unsigned long long c = i < nchunks ? counts[i] : 0;
-		unsigned long long inc = c;
+	const uint64_t items = (nchunks + 1023) / 1024;
+	const uint64_t lo = threadIdx.x * items, hi = lo + items < nchunks ? lo + items : nchunks;
+	unsigned long long mine = 0;
+#pragma unroll 8
+	for (uint64_t i = lo; i < hi; i++)
+		mine += counts[i];
+	unsigned long long inc = mine;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o)
+			inc += t;
+	}
+	if (lane == 31)
+		wsum[warp] = inc;
+	__syncthreads();
+	if (warp == 0) {
+		const unsigned long long w = wsum[lane];
+		unsigned long long winc = w;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
-			unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+			unsigned long long t = __shfl_up_sync(0xffffffffu, winc, o);
 			if (lane >= o)
-				inc += t;
+				winc += t;
 		}
-		if (lane == 31)
-			wsum[warp] = inc;
-		__syncthreads();
-		if (warp == 0) {
-			const unsigned long long w = wsum[lane];
-			unsigned long long winc = w;
-#pragma unroll
-			for (int o = 1; o < 32; o <<= 1) {
-				unsigned long long t = __shfl_up_sync(0xffffffffu, winc, o);
-				if (lane >= o)
-					winc += t;
-			}
-			wsum[lane] = winc - w;		/* exclusive over warps */
-			if (lane == 31)
-				itertotal = winc;
+		wsum[lane] = winc - w;		/* exclusive over warps */
+		if (lane == 31) {
+			offs[nchunks] = winc;
+			slot[0] = winc;
+			slot[1] = 0;
+			slot[2] = 0;
 		}
-		__syncthreads();
-		if (i < nchunks)
-			offs[i] = carry + wsum[warp] + inc - c;
-		carry += itertotal;
-		__syncthreads();
 	}
-	if (threadIdx.x == 0) {
-		offs[nchunks] = carry;
-		slot[0] = carry;
-		slot[1] = 0;
-		slot[2] = 0;
+	__syncthreads();
+	unsigned long long run = wsum[warp] + inc - mine;
+	for (uint64_t i = lo; i < hi; i++) {
+		offs[i] = run;
+		run += counts[i];
 	}
 }
 
 // ---- step 3: mask words -> oids.  OidOf gives the oid of input index idx.
+// One lane per mask word.  Each lane drops the positions of its set bits into a
+// per-warp shared-memory stage at its exclusive offset; the warp then streams the
+// stage out, 32 consecutive oids (256 contiguous bytes) per store instruction.
 struct DenseOid {
 	oid seq;	/* oid of index 0 */
 	__device__ __forceinline__ oid at(uint64_t idx) const { return seq + idx; }
 };
 
-template <typename OidOf>
-__global__ void __launch_bounds__(CP_THREADS)
+template <int WORDS, typename OidOf>
+__global__ void __launch_bounds__(WORDS)
 compact_expand_kernel(const uint32_t *__restrict__ words, const uint32_t *__restrict__ counts,
 		      const unsigned long long *__restrict__ offs, OidOf of, oid *__restrict__ dst,
 		      unsigned long long *__restrict__ slot)
 {
 	if (counts[blockIdx.x] == 0)
 		return;
-	__shared__ unsigned wtot[CP_THREADS / 32];
+	__shared__ unsigned short stage[WORDS * 32];
+	__shared__ unsigned wtot[WORDS / 32];
 	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint64_t wbase = (uint64_t) blockIdx.x * CP_WORDS + warp * 32;
-	const unsigned w = words[wbase + lane];
+	const uint64_t wbase = (uint64_t) blockIdx.x * WORDS + warp * 32;
+	unsigned w = words[wbase + lane];
 	const unsigned c = __popc(w);
 	unsigned inc = c;
 #pragma unroll
@@ -150,30 +156,31 @@ compact_expand_kernel(const uint32_t *__restrict__ words, const uint32_t *__rest
 		if (lane >= o)
 			inc += t;
 	}
+	const unsigned T = __shfl_sync(0xffffffffu, inc, 31);
 	if (lane == 31)
 		wtot[warp] = inc;
+	unsigned short *st = stage + warp * 1024;
+	unsigned pos = inc - c;
+	const unsigned short lbase = (unsigned short) (lane * 32);
+	while (w) {
+		const unsigned b = __ffs(w) - 1;
+		w &= w - 1;
+		st[pos++] = lbase + (unsigned short) b;
+	}
 	__syncthreads();
 	unsigned long long base = offs[blockIdx.x];
 #pragma unroll
-	for (int k = 0; k < CP_THREADS / 32; k++)
+	for (int k = 0; k < WORDS / 32; k++)
 		base += k < warp ? wtot[k] : 0;
 	const unsigned long long total = offs[gridDim.x];
-	const unsigned excl = inc - c;
-	unsigned nonempty = __ballot_sync(0xffffffffu, c != 0);
-	while (nonempty) {
-		const int k = __ffs(nonempty) - 1;
-		nonempty &= nonempty - 1;
-		const unsigned wk = __shfl_sync(0xffffffffu, w, k);
-		const unsigned ek = __shfl_sync(0xffffffffu, excl, k);
-		if ((wk >> lane) & 1u) {
-			const unsigned long long pos = base + ek + __popc(wk & ((1u << lane) - 1));
-			const oid o = of.at((wbase + k) * 32 + lane);
-			dst[pos] = o;
-			if (pos == 0)
-				slot[1] = o;
-			if (pos == total - 1)
-				slot[2] = o;
-		}
+	for (unsigned r = lane; r < T; r += 32) {
+		const unsigned long long p = base + r;
+		const oid o = of.at(wbase * 32 + st[r]);
+		dst[p] = o;
+		if (p == 0)
+			slot[1] = o;
+		if (p == total - 1)
+			slot[2] = o;
 	}
 }
 
@@ -182,18 +189,44 @@ struct CompactResult {
 	oid first = 0, last = 0;
 };
 
+template <typename OidOf>
+static inline void compact_launch_expand(const CompactScratch &s, OidOf of, oid *dst)
+{
+	Ctx *c = ctx();
+	KTimer kt("compact_expand", s.nchunks * (s.chunk / 32) * 4);
+	if (s.chunk == CP_CHUNK)
+		compact_expand_kernel<CP_CHUNK / 32, OidOf><<<(unsigned) s.nchunks, CP_CHUNK / 32, 0, c->stream>>>(
+			s.words, s.counts, s.offs, of, dst, c->slot_d->v);
+	else
+		compact_expand_kernel<CP_CHUNK_SMALL / 32, OidOf><<<(unsigned) s.nchunks, CP_CHUNK_SMALL / 32, 0, c->stream>>>(
+			s.words, s.counts, s.offs, of, dst, c->slot_d->v);
+	COUNT_LAUNCH();
+}
+
+template <typename F> static inline void compact_launch_mask(const CompactScratch &s, uint64_t n, F f)
+{
+	Ctx *c = ctx();
+	if (s.chunk == CP_CHUNK)
+		compact_mask_kernel<CP_CHUNK, F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+	else
+		compact_mask_kernel<CP_CHUNK_SMALL, F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+	COUNT_LAUNCH();
+}
+
+static inline void compact_launch_scan(const CompactScratch &s)
+{
+	Ctx *c = ctx();
+	compact_scan_kernel<<<1, 1024, 0, c->stream>>>(s.counts, s.nchunks, s.offs, c->slot_d->v);
+	COUNT_LAUNCH();
+}
+
 // steps 2 + 3 and the read-back of (count, first oid, last oid)
 template <typename OidOf>
 static bool compact_finish(const CompactScratch &s, OidOf of, oid *dst, CompactResult &res)
 {
 	Ctx *c = ctx();
-	compact_scan_kernel<<<1, 1024, 0, c->stream>>>(s.counts, s.nchunks, s.offs, c->slot_d->v);
-	COUNT_LAUNCH();
-	{
-		KTimer kt("compact_expand", s.nchunks * CP_WORDS * 4);
-		compact_expand_kernel<OidOf><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(s.words, s.counts, s.offs, of, dst, c->slot_d->v);
-	}
-	COUNT_LAUNCH();
+	compact_launch_scan(s);
+	compact_launch_expand(s, of, dst);
 	if (!cuda_ok(cudaGetLastError(), "compact launch") || !stream_sync())
 		return false;
 	res.count = c->slot_h->v[0];
@@ -221,9 +254,8 @@ static bool run_compact(uint64_t n, F f, oid *dst, CompactResult &res)
 		return false;
 	{
 		KTimer kt("compact", n * 8);
-		compact_mask_kernel<F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+		compact_launch_mask(s, n, f);
 	}
-	COUNT_LAUNCH();
 	return compact_finish(s, FunctorOid<F>{f}, dst, res);
 }
 

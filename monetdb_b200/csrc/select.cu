@@ -11,6 +11,7 @@
 // (virtualize, :31-89).
 #include "common.cuh"
 #include "compact.cuh"
+#include <type_traits>
 
 // closed-range predicate after normalisation:
 //   nil(v) ? nilres : (anti ? (v <= vl || v >= vh) : (v >= vl && v <= vh))
@@ -96,23 +97,101 @@ select_dense_kernel(const T *__restrict__ src,	/* 16-byte aligned; row r of the 
 		counts[blockIdx.x] = total;
 }
 
+// Dense scan for the 4/8/16-byte atoms: lane l of a warp tests row 32j + l, so the
+// ballot of step j IS mask word j — no cross-lane assembly, ~7 instructions per 32
+// rows.  A warp covers 32 words (1024 rows); all 32 loads of a thread are independent
+// and issued back to back (128-512 B in flight per thread).  Integer ranges without
+// nil matching use one unsigned compare: (U)(v - vl) <= (U)(vh - vl), which a nil
+// (the type minimum, below every valid vl) can never satisfy.
+template <typename T> struct FastRange {
+	typedef typename std::conditional<sizeof(T) == 4, uint32_t, typename std::conditional<sizeof(T) == 8, uint64_t, uhge>::type>::type U;
+	U lo, span;
+	__device__ __forceinline__ bool operator()(T v) const { return (U) ((U) v - lo) <= span; }
+};
+
+template <typename T, typename P>
+__global__ void __launch_bounds__(CP_THREADS)
+select_dense32_kernel(const T *__restrict__ src, uint64_t n, P pred, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
+{
+	__shared__ unsigned total;
+	if (threadIdx.x == 0)
+		total = 0;
+	__syncthreads();
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t wrow = (uint64_t) blockIdx.x * CP_CHUNK + warp * 1024;	/* first row of this warp */
+	constexpr int NB = sizeof(T) == 4 ? 32 : sizeof(T) == 8 ? 16 : 8;	/* loads in flight per thread */
+	unsigned cnt = 0, mine = 0;
+	if (wrow + 1024 <= n) {
+		const T *p = src + wrow + lane;
+#pragma unroll
+		for (int jb = 0; jb < 32; jb += NB) {
+			T v[NB];
+#pragma unroll
+			for (int j = 0; j < NB; j++)
+				v[j] = ld_stream(p + (jb + j) * 32);
+#pragma unroll
+			for (int j = 0; j < NB; j++) {
+				const unsigned bal = __ballot_sync(0xffffffffu, pred(v[j]));
+				cnt += __popc(bal);
+				mine = lane == jb + j ? bal : mine;
+			}
+		}
+	} else if (wrow < n) {
+		for (int j = 0; j < 32; j++) {
+			const uint64_t r = wrow + j * 32 + lane;
+			const bool h = r < n && pred(src[r]);
+			const unsigned bal = __ballot_sync(0xffffffffu, h);
+			cnt += __popc(bal);
+			mine = lane == j ? bal : mine;
+		}
+	}
+	words[(wrow >> 5) + lane] = mine;	/* the scratch covers whole chunks: rows past n get zero words */
+	if (lane == 0 && cnt)
+		atomicAdd(&total, cnt);
+	__syncthreads();
+	if (threadIdx.x == 0)
+		counts[blockIdx.x] = total;
+}
+
 template <typename T>
 static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, oid seq, RangePred<T> pred, oid *dst, CompactResult &res)
 {
 	Ctx *c = ctx();
-	const T *p = col + first_row;
-	uint64_t skip = ((uintptr_t) p & 15) / sizeof(T);
-	p -= skip;
-	uint64_t n = ncand + skip;
 	CompactScratch s;
-	if (!compact_scratch(n, s))
-		return false;
-	{
-		KTimer kt("select_dense", n * sizeof(T));
-		select_dense_kernel<T><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, skip, n, pred, s.words, s.counts);
+	if constexpr (sizeof(T) >= 4) {
+		const T *p = col + first_row;
+		if (!compact_scratch(ncand, s, CP_CHUNK))
+			return false;
+		{
+			KTimer kt("select_dense", ncand * sizeof(T));
+			bool fast = false;
+			if constexpr (!Atom<T>::is_float) {
+				if (!pred.anti && !pred.nilres && pred.vl <= pred.vh && pred.vl >= Atom<T>::minval()) {
+					typedef typename FastRange<T>::U U;
+					FastRange<T> fp{(U) pred.vl, (U) ((U) pred.vh - (U) pred.vl)};
+					select_dense32_kernel<T, FastRange<T>><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, ncand, fp, s.words, s.counts);
+					fast = true;
+				}
+			}
+			if (!fast)
+				select_dense32_kernel<T, RangePred<T>><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, ncand, pred, s.words, s.counts);
+		}
+		COUNT_LAUNCH();
+		return compact_finish(s, DenseOid{seq}, dst, res);
+	} else {
+		const T *p = col + first_row;
+		uint64_t skip = ((uintptr_t) p & 15) / sizeof(T);
+		p -= skip;
+		uint64_t n = ncand + skip;
+		if (!compact_scratch(n, s, CP_CHUNK))
+			return false;
+		{
+			KTimer kt("select_dense", n * sizeof(T));
+			select_dense_kernel<T><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, skip, n, pred, s.words, s.counts);
+		}
+		COUNT_LAUNCH();
+		return compact_finish(s, DenseOid{seq - skip}, dst, res);
 	}
-	COUNT_LAUNCH();
-	return compact_finish(s, DenseOid{seq - skip}, dst, res);
 }
 
 // ---------------------------------------------------------------- candidate-list scan
