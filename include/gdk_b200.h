@@ -8,7 +8,7 @@
  * reads: no reference struct layout, no torch types, plain pointers and sizes.
  * The reference-side binding (a patched libbat entry point that converts
  * BAT* <-> b200_bat and tail-calls these functions) is shown in INTEGRATION.md
- * and built in shim/.
+ *.
  *
  * Conventions (all cited files are relative to the MonetDB reference tree):
  *  - oid / BUN are 64-bit unsigned (gdk.h:460-461,507); oid_nil = 1<<63.
