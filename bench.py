@@ -189,7 +189,7 @@ def b200_arm(args):
     counts = {}
 
     def step(cols):
-        return merge(hge_int(pipelines.q6(G, cols, counts)))
+        return merge(hge_int(pipelines.q6(G, cols, counts)))      # merge == shard.allreduce_hge with a reused buffer
 
     def timed(cols, steps, warmup, sample_clocks=False):
         for _ in range(warmup):
@@ -277,6 +277,155 @@ def b200_arm(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------- other BASELINE configs
+def other_workload(args):
+    """--workload q1 | window | config1 | join: the other BASELINE configs on the B200 path (same
+    timing rules as the Q6 line: warm-up, CUDA events on the library's stream, max over ranks).
+    They are parity-test cases first; these lines record their throughput for profiles/."""
+    import torch
+    import torch.distributed as dist
+    from monetdb_b200 import gdk as G
+    from monetdb_b200 import pipelines, shard, workload
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available() or G.lib.b200_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    G.init(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    T = G.TYPE
+    n = args.rows
+    w = args.workload
+    info = {}
+
+    def upload(gen, types, lo, hi, chunk=50_000_000):
+        """generate rows [lo,hi) chunk by chunk on the host, one upload per column"""
+        bufs = {k: np.empty(hi - lo, dtype=G.NP_OF[t]) for k, t in types.items()}
+        for a in range(lo, hi, chunk):
+            b = min(hi, a + chunk)
+            part = gen(a, b)
+            for k in types:
+                bufs[k][a - lo:b - lo] = part[k]
+        return {k: G.BATfromhost(bufs[k], types[k], hseq=lo, nonil=True) for k in types}
+
+    if w == "q1":
+        types = {"shipdate": T.date, "discount": T.lng, "quantity": T.lng, "extprice": T.lng, "tax": T.lng,
+                 "returnflag": T.bte, "linestatus": T.bte}
+        lo, hi = rank * n, (rank + 1) * n
+        dev = upload(lambda a, b: workload.lineitem(a, b, cols=tuple(types)), types, lo, hi)
+
+        def step():
+            r = shard.q1_sharded(G, dev, dist if world > 1 else None)
+            info["nsel"] = sum(r["count_order"])
+            return r["sum_charge"]
+        metric = "GDK Q1 pipeline rows/s (TPC-H Q1 shape, synthetic lineitem)"
+        bytes_of = lambda: pipelines.q1_bytes(n * world, info["nsel"])
+        label = f"TPC-H Q1 shape: select + 6 project + 2-level group + 4 calc + 8 aggregates, {n} lineitem rows per GPU"
+    elif w == "config1":
+        k, v = workload.config1(0, n)
+        dev = {"k": G.BATfromhost(k, T.int, nonil=True), "v": G.BATfromhost(v, T.lng, nonil=True)}
+
+        def step():
+            out = {}
+            r = pipelines.config1(G, dev, out)
+            info["sel"] = len(out["s"])
+            return shard.hge_int(r.numpy())
+        metric = "GDK config-1 pipeline rows/s (select + 2 project + group + groupsum)"
+        bytes_of = lambda: 4 * n + 76 * info["sel"]
+        label = f"config 1: BATselect range + BATgroup + BATgroupsum on a {n}-row int/lng column pair"
+    elif w == "join":
+        nl, nr = n, max(1, n // 4)
+        rng = np.random.default_rng(0x5EED0009)
+        okey = (rng.permutation(nr) + 1).astype(np.int32)
+        lkey = (workload.splitmix64(workload.col_seed(workload.C_LKEY), 0, nl) % np.uint64(nr) + np.uint64(1)).astype(np.int32)
+        dev = {"l": G.BATfromhost(lkey, T.int, nonil=True), "r": G.BATfromhost(okey, T.int, nonil=True, key=True)}
+
+        def step():
+            r1, r2 = G.BATjoin(dev["l"], dev["r"], None, None, False)
+            info["pairs"] = len(r1)
+            return len(r1)
+        metric = "GDK hash join rows/s (lineitem JOIN orders shape, probe rows)"
+        bytes_of = lambda: (4 + 8 + 8) * nr + (4 + 2 * 8 + 16) * nl
+        label = f"config 4 shape on one GPU: {nl} int32 probe keys x {nr} unique build keys (BAThash + BATjoin)"
+    elif w == "window":
+        blk = workload.window_layout()
+        n = max(blk, n // blk * blk)
+        lo, hi = rank * n, (rank + 1) * n
+        types = {"pkey": T.lng, "ord": T.lng, "val": T.lng}
+        dev = upload(lambda a, b: workload.window(a, b), types, lo, hi, chunk=blk * 400)
+
+        def step():
+            p = G.GDKanalyticaldiff(G.colnew(T.bit, n), dev["pkey"], None, None, T.lng)
+            tot = 0
+            for unit, plo, phi, half in ((0, 100, 0, 1), (1, 50, 50, 0)):
+                s = G.GDKanalyticalwindowbounds(G.colnew(T.oid, n), dev["ord"], p, None, plo, T.lng, T.lng, unit, True, 0)
+                e = G.GDKanalyticalwindowbounds(G.colnew(T.oid, n), dev["ord"], p, None, phi, T.lng, T.lng, unit, False, half)
+                r = G.GDKanalyticalsum(G.colnew(T.hge, n), p, None, dev["val"], s, e, T.lng, T.hge, unit)
+                a = G.GDKanalyticalfn("avg", G.colnew(T.dbl, n), p, None, dev["val"], s, e, T.lng, unit)
+                tot += len(r) + len(a)
+            return tot
+        metric = "GDK window analytics rows/s (ROWS + RANGE frames, moving sum + avg)"
+        # diff 9; ROWS bounds 2 x 9; RANGE bounds 2 x 17; per frame kind sum 8+16+16 and avg 8+16+8
+        bytes_of = lambda: n * world * (9 + 18 + 34 + 2 * (40 + 32))
+        label = f"config 5: {n} rows per GPU, partitions of 1e3/1e4/1e5 rows, ROWS 100 PRECEDING..CURRENT and RANGE 50..50"
+    else:
+        raise SystemExit(f"unknown workload {w}")
+
+    stream = torch.cuda.ExternalStream(G.lib.b200_stream())
+
+    def barrier():
+        G.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(steps, warmup):
+        for _ in range(warmup):
+            res = step()
+        barrier()
+        G.timing_read()
+        l0 = G.kernel_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            res = step()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, res, G.kernel_launches() - l0
+
+    ms, res, launches = timed(args.steps, max(3, args.warmup))
+    G.timing_enable(True)
+    timed(min(args.steps, 3), 1)
+    kt = G.timing_read()
+    G.timing_enable(False)
+    if rank == 0:
+        peak, peak_src = measured_hbm_peak()
+        rows = n * world if w != "join" else n
+        by = bytes_of()
+        gbs = by * args.steps / (ms * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": metric, "value": rows * args.steps / (ms * 1e-3), "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int64/int128 integer", "data": "synthetic",
+            "config": {"workload": label, "info": info, "pipeline_algorithmic_bytes": by, "pipeline_gbs": gbs,
+                       "pipeline_frac_of_hbm_peak": gbs / (peak * world), "peak_source": peak_src,
+                       "kernel_ms": {k: round(v[1] / max(1, v[0]), 4) for k, v in kt.items()},
+                       "kernel_launch_counts": {k: v[0] for k, v in kt.items()},
+                       "kernel_gbs": {k: round(v[2] / (v[1] * 1e-3) / 1e9, 1) for k, v in kt.items() if v[1] > 0}},
+            "gpu_launches": int(launches), "result": str(res)[:200]}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -305,10 +454,14 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=N_SF10, help="lineitem rows per GPU (default SF10)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="q6", choices=["q6", "q1", "config1", "join", "window"],
+                    help="q6 (default) is the contract line; the others record the remaining BASELINE configs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
         reference_arm(args)
+    elif args.workload != "q6":
+        other_workload(args)
     else:
         if args.warmup < 3:
             args.warmup = 3

@@ -108,15 +108,96 @@ struct AggrAccum {
 	~AggrAccum() { if (cells) dev_free(cells); if (state) dev_free(state); }
 };
 
+// fast register accumulation (aggr_reg_fast_kernel).  On return `done` tells whether acc holds the
+// result; it is false when an overflow check was asked for and rows x max|x| does not fit
+// check_bits, in which case acc has been released for the exact form.
 template <typename T1>
-static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, bool check, bool need_values, AggrAccum &acc)
+static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &done)
 {
 	Ctx *c = ctx();
 	constexpr int ND = Digits<T1>::ND;
 	const unsigned ngrp = (unsigned) a.ngrp;
+	acc.check = false;
+	const AggrLayout L(ND, false, false);
+	acc.ncell = L.ncell;
+	const size_t bytes = (size_t) L.ncell * ngrp * 8;
+	acc.cells = (u64 *) dev_alloc(bytes);
+	acc.state = (u64 *) dev_alloc(64);
+	if (acc.cells == nullptr || acc.state == nullptr ||
+	    !cuda_ok(cudaMemsetAsync(acc.cells, 0, bytes, c->stream), "memset cells") ||
+	    !cuda_ok(cudaMemsetAsync(acc.state, 0, 64, c->stream), "memset state"))
+		return false;
+	AggrIn &in = acc.in;
+	memset(&in, 0, sizeof(in));
+	in.n = a.ci.ncand;
+	in.hseq = a.ci.hseq;
+	in.vals = (const T1 *) a.b->base + (a.ci.seq - a.ci.hseq);
+	in.gmin = a.min;
+	in.gmax = a.max;
+	in.gconst = a.g == nullptr;
+	in.gids = a.g ? (const oid *) a.g->base : nullptr;
+	in.nonil = a.b->tnonil;
+	in.skip_nils = true;
+	const unsigned grid = grid_for(in.n, AGGR_THREADS * 8, NSM * 8);
+	{
+		KTimer kt("aggr", in.n * (sizeof(T1) + (in.gids ? 8 : 0)));
+		const T1 *vals = (const T1 *) in.vals;
+		u64 *mx = acc.state + 5;
+#define FAST_CASE(NG)                                                                                                         \
+	do {                                                                                                                  \
+		if (in.gids)                                                                                                  \
+			aggr_reg_fast_kernel<T1, NG, true><<<grid, AGGR_THREADS, 0, c->stream>>>(vals, in.gids, in.gmin, in.gmax - in.gmin, in.n, in.nonil, acc.cells, ngrp, mx); \
+		else                                                                                                          \
+			aggr_reg_fast_kernel<T1, NG, false><<<grid, AGGR_THREADS, 0, c->stream>>>(vals, nullptr, in.gmin, in.gmax - in.gmin, in.n, in.nonil, acc.cells, ngrp, mx); \
+	} while (0)
+		if (ngrp <= 1) FAST_CASE(1);
+		else if (ngrp <= 2) FAST_CASE(2);
+		else if (ngrp <= 4) FAST_CASE(4);
+		else FAST_CASE(8);
+#undef FAST_CASE
+	}
+	COUNT_LAUNCH();
+	ctx()->algo = "aggr: cuda wide register accumulators";
+	if (!cuda_ok(cudaGetLastError(), "aggr launch"))
+		return false;
+	done = true;
+	if (check_bits != 0) {
+		if (!cuda_ok(cudaMemcpyAsync(&c->slot_h->v[5], acc.state + 5, 16, cudaMemcpyDeviceToHost, c->stream), "maxabs") || !stream_sync())
+			return false;
+		const uhge mx = ((uhge) c->slot_h->v[6] << 64) | c->slot_h->v[5];
+		const uhge lim = ((uhge) 1 << (check_bits - 1)) - 1;
+		if (mx != 0 && (uhge) in.n > lim / mx) {
+			dev_free(acc.cells);
+			dev_free(acc.state);
+			acc.cells = acc.state = nullptr;
+			done = false;
+		}
+	}
+	return true;
+}
+
+template <typename T1>
+static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_bits, bool need_values, AggrAccum &acc)
+{
+	Ctx *c = ctx();
+	constexpr int ND = Digits<T1>::ND;
+	const unsigned ngrp = (unsigned) a.ngrp;
+	bool check = check_bits != 0;
 	acc.nd = ND;
-	acc.check = check;
 	acc.niltrack = !skip_nils && !a.b->tnonil;
+	/* fast register form: integers, dense values, few groups; the overflow check becomes the
+	 * rows x max|x| bound, with the exact digit form as the fallback */
+	bool fast = false;
+	if constexpr (!Atom<T1>::is_float)
+		fast = !acc.niltrack && ngrp <= 8 && a.ci.dense && (a.g == nullptr || a.g->ttype != B200_void);
+	if (fast) {
+		if (!aggr_fast<T1>(a, check_bits, acc, fast))
+			return false;
+		if (fast)
+			return true;
+		/* bound failed: acc was reset, run the exact form */
+	}
+	acc.check = check;
 	const AggrLayout L(ND, check, acc.niltrack);
 	acc.ncell = L.ncell;
 	const size_t bytes = (size_t) L.ncell * ngrp * 8;
@@ -196,18 +277,18 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, bool check
 	return cuda_ok(cudaGetLastError(), "aggr launch");
 }
 
-static bool aggr_accumulate(const AggrSetup &a, bool skip_nils, bool check, AggrAccum &acc)
+static bool aggr_accumulate(const AggrSetup &a, bool skip_nils, int check_bits, AggrAccum &acc)
 {
 	if (a.ci.ncand >= (1ULL << 32)) {
 		set_err("b200: aggregates over 2^32 or more rows in one call are not supported\n");
 		return false;
 	}
 	switch (basetype(a.b->ttype)) {
-	case B200_bte: return aggr_accumulate_typed<bte>(a, skip_nils, check, true, acc);
-	case B200_sht: return aggr_accumulate_typed<sht>(a, skip_nils, check, true, acc);
-	case B200_int: return aggr_accumulate_typed<int>(a, skip_nils, check, true, acc);
-	case B200_lng: return aggr_accumulate_typed<lng>(a, skip_nils, check, true, acc);
-	case B200_hge: return aggr_accumulate_typed<hge>(a, skip_nils, check, true, acc);
+	case B200_bte: return aggr_accumulate_typed<bte>(a, skip_nils, check_bits, true, acc);
+	case B200_sht: return aggr_accumulate_typed<sht>(a, skip_nils, check_bits, true, acc);
+	case B200_int: return aggr_accumulate_typed<int>(a, skip_nils, check_bits, true, acc);
+	case B200_lng: return aggr_accumulate_typed<lng>(a, skip_nils, check_bits, true, acc);
+	case B200_hge: return aggr_accumulate_typed<hge>(a, skip_nils, check_bits, true, acc);
 	case B200_flt: return aggr_accumulate_typed<flt>(a, skip_nils, false, true, acc);
 	case B200_dbl: return aggr_accumulate_typed<dbl>(a, skip_nils, false, true, acc);
 	}
@@ -262,8 +343,9 @@ static uint64_t do_sum(const AggrSetup &a, int tp2, bool skip_nils, bool nil_if_
 		return B200_BUN_NONE;
 	}
 	AggrAccum acc;
-	if (!aggr_accumulate(a, skip_nils, check, acc))
+	if (!aggr_accumulate(a, skip_nils, check ? atomsize(t2) * 8 : 0, acc))
 		return B200_BUN_NONE;
+	check = acc.check;		/* the fast form proves "no overflow possible" with a bound instead */
 	const unsigned ngrp = (unsigned) a.ngrp;
 	unsigned *exactlist = nullptr;
 	if (check) {
@@ -376,7 +458,7 @@ extern "C" b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b
 		uint64_t cnt = 0;
 		if (a.ci.ncand > 0) {
 			AggrAccum acc;
-			if (!aggr_accumulate(a, true, false, acc))
+			if (!aggr_accumulate(a, true, 0, acc))
 				return B200_FAIL;
 			dbl *out = (dbl *) dev_alloc(16);
 			if (out == nullptr)
@@ -459,14 +541,22 @@ gid_count_kernel(const oid *__restrict__ gids, uint64_t n, oid gmin, oid gmax, u
 	const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
 	if (ngrp <= 8) {
 		unsigned c[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-		for (uint64_t k = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
-			oid g = __ldcs(gids + k);
-			if (g < gmin || g > gmax)
-				continue;
-			unsigned gi = (unsigned) (g - gmin);
+		constexpr int U = 8;	/* independent loads in flight per thread */
+		for (uint64_t k0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; k0 < n; k0 += stride * U) {
+			oid g[U];
 #pragma unroll
-			for (int j = 0; j < 8; j++)
-				c[j] += gi == j;
+			for (int u = 0; u < U; u++) {
+				const uint64_t k = k0 + u * stride;
+				g[u] = k < n ? __ldcs(gids + k) : OID_NIL;
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const u64 go = g[u] - gmin;
+				const unsigned gi = go <= gmax - gmin ? (unsigned) go : 0xffffffffu;
+#pragma unroll
+				for (int j = 0; j < 8; j++)
+					c[j] += gi == j;
+			}
 		}
 #pragma unroll
 		for (int j = 0; j < 8; j++) {
@@ -537,7 +627,7 @@ extern "C" b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, co
 			b200_BATfree(bn);
 			return nullptr;
 		}
-		const unsigned grid = grid_for(a.ci.ncand, 256 * 4, NSM * 8);
+		const unsigned grid = grid_for(a.ci.ncand, 256 * 8, NSM * 8);
 		if ((size_t) ngrp * 8 <= 48 * 1024)
 			gid_count_kernel<true><<<grid, 256, ngrp > 8 ? (size_t) ngrp * 8 : 0, c->stream>>>((const oid *) a.g->base, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
 		else
@@ -554,7 +644,7 @@ extern "C" b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, co
 	}
 	/* count the non-nil values per group */
 	AggrAccum acc;
-	if (!aggr_accumulate(a, true, false, acc))
+	if (!aggr_accumulate(a, true, 0, acc))
 		return nullptr;
 	b200_bat *bn = bat_new(a.min, B200_lng, a.ngrp);
 	if (bn == nullptr)
@@ -628,7 +718,7 @@ extern "C" b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const 
 		return B200_SUCCEED;
 	}
 	AggrAccum acc;
-	if (!aggr_accumulate(a, skip_nils, false, acc))
+	if (!aggr_accumulate(a, skip_nils, 0, acc))
 		return B200_FAIL;
 	const unsigned ngrp = (unsigned) a.ngrp;
 	bn = bat_new(a.min, B200_dbl, a.ngrp);

@@ -217,6 +217,164 @@ aggr_reg_kernel(AggrIn in, u64 *__restrict__ cells, unsigned ngrp, unsigned *__r
 	}
 }
 
+// ---------------------------------------------------------------- REG, fast form
+// Integer values, dense value column, ngrp <= NG <= 8, no nil tracking.  Each thread
+// keeps ONE wide two's-complement accumulator per group (64 bits for <= 4-byte
+// values, 128 for lng, 192 for hge) that a row updates with predicated adds — a third
+// of the instructions of the digit form above — plus the largest |x| it has seen:
+// if rows x max|x| fits the result type no prefix of any group can overflow, which
+// replaces the separate positive-part sums in all practical cases (otherwise the
+// host falls back to the exact form).  The wide sums are cut into the same 32-bit
+// digit cells at the end, so the finishing kernels are shared.
+template <typename T1> struct WideAcc {
+	static constexpr int NW = sizeof(T1) <= 4 ? 1 : sizeof(T1) == 8 ? 2 : 3;	/* 64-bit words */
+};
+
+template <typename T1, int NG, bool HASGID>
+__global__ void __launch_bounds__(AGGR_THREADS)
+aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, oid gmin, oid gspan /* gmax - gmin */,
+		     uint64_t n, bool nonil, u64 *__restrict__ cells, unsigned ngrp, u64 *__restrict__ maxabs_out)
+{
+	constexpr int NW = WideAcc<T1>::NW;
+	constexpr int ND = Digits<T1>::ND;
+	typedef typename std::conditional<sizeof(T1) == 16, uhge, u64>::type UA;
+	u64 acc[NG][NW];
+	unsigned cnt[NG];
+#pragma unroll
+	for (int g = 0; g < NG; g++) {
+		cnt[g] = 0;
+#pragma unroll
+		for (int w = 0; w < NW; w++)
+			acc[g][w] = 0;
+	}
+	UA maxabs = 0;
+	constexpr int U = sizeof(T1) == 16 ? 4 : 8;
+	const uint64_t stride = (uint64_t) gridDim.x * AGGR_THREADS;
+	for (uint64_t k0 = (uint64_t) blockIdx.x * AGGR_THREADS + threadIdx.x; k0 < n; k0 += stride * U) {
+		T1 x[U];
+		oid gid[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const uint64_t k = k0 + u * stride;
+			if (k < n) {
+				x[u] = ld_stream(vals + k);
+				gid[u] = HASGID ? __ldcs(gids + k) : gmin;
+			} else {
+				x[u] = Atom<T1>::nil();
+				gid[u] = gmin;
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const u64 go = gid[u] - gmin;
+			const bool ok = !Atom<T1>::is_nil(x[u]) && go <= gspan;		/* a tail slot holds nil */
+			const unsigned gi = ok ? (unsigned) go : 0xffffffffu;
+			const UA ax = x[u] < 0 ? (UA) 0 - (UA) x[u] : (UA) x[u];
+			if (ok && ax > maxabs)
+				maxabs = ax;
+			/* sign-extended words of x */
+			u64 xw[NW];
+			if constexpr (sizeof(T1) == 16) {
+				xw[0] = (u64) x[u];
+				xw[1] = (u64) ((uhge) x[u] >> 64);
+				xw[2] = (u64) ((i64) xw[1] >> 63);
+			} else if constexpr (sizeof(T1) == 8) {
+				xw[0] = (u64) x[u];
+				xw[1] = (u64) ((i64) x[u] >> 63);
+			} else {
+				xw[0] = (u64) (i64) x[u];
+			}
+#pragma unroll
+			for (int g = 0; g < NG; g++) {
+				if (gi == g) {
+					cnt[g]++;
+					if constexpr (NW == 1) {
+						acc[g][0] += xw[0];
+					} else if constexpr (NW == 2) {
+						const uhge t = (((uhge) acc[g][1] << 64) | acc[g][0]) + (((uhge) xw[1] << 64) | xw[0]);
+						acc[g][0] = (u64) t;
+						acc[g][1] = (u64) (t >> 64);
+					} else {
+						const uhge t = (uhge) acc[g][0] + xw[0];
+						acc[g][0] = (u64) t;
+						const uhge t2 = (((uhge) acc[g][2] << 64) | acc[g][1]) + (((uhge) xw[2] << 64) | xw[1]) + (u64) (t >> 64);
+						acc[g][1] = (u64) t2;
+						acc[g][2] = (u64) (t2 >> 64);
+					}
+				}
+			}
+		}
+	}
+	/* wide sum -> ND digit cells: digits 0..ND-2 are the low 32-bit pieces, the top
+	 * digit is the arithmetic remainder (fits 64 bits: |sum| < 2^(32 ND + 31)) */
+	__shared__ i64 wsum[AGGR_THREADS / 32][NG * (ND + 1)];
+	__shared__ u64 wmax[AGGR_THREADS / 32][2];
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+	for (int g = 0; g < NG; g++) {
+		i64 d[ND];
+		if constexpr (ND == 1) {
+			d[0] = (i64) acc[g][0];
+		} else if constexpr (ND == 2) {
+			d[0] = (i64) (uint32_t) acc[g][0];
+			d[1] = (i64) ((acc[g][0] >> 32) | (acc[g][1] << 32));
+		} else {
+			d[0] = (i64) (uint32_t) acc[g][0];
+			d[1] = (i64) (acc[g][0] >> 32);
+			d[2] = (i64) (uint32_t) acc[g][1];
+			d[3] = (i64) ((acc[g][1] >> 32) | (acc[g][2] << 32));
+		}
+#pragma unroll
+		for (int e = 0; e <= ND; e++) {
+			i64 v = e < ND ? d[e < ND ? e : 0] : (i64) cnt[g];
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1)
+				v += __shfl_down_sync(0xffffffffu, v, o);
+			if (lane == 0)
+				wsum[warp][g * (ND + 1) + e] = v;
+		}
+	}
+	{
+		u64 mlo = (u64) maxabs, mhi = sizeof(T1) == 16 ? (u64) ((uhge) maxabs >> 64) : 0;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			const u64 olo = __shfl_down_sync(0xffffffffu, mlo, o), ohi = __shfl_down_sync(0xffffffffu, mhi, o);
+			if (ohi > mhi || (ohi == mhi && olo > mlo)) {
+				mhi = ohi;
+				mlo = olo;
+			}
+		}
+		if (lane == 0) {
+			wmax[warp][0] = mlo;
+			wmax[warp][1] = mhi;
+		}
+	}
+	__syncthreads();
+	for (unsigned i = threadIdx.x; i < NG * (ND + 1); i += AGGR_THREADS) {
+		const unsigned g = i / (ND + 1), e = i % (ND + 1);
+		if (g >= ngrp)
+			continue;
+		i64 v = 0;
+#pragma unroll
+		for (int w = 0; w < AGGR_THREADS / 32; w++)
+			v += wsum[w][i];
+		if (v != 0)
+			atomicAdd(&cells[(size_t) e * ngrp + g], (u64) v);	/* cell order: S digits, count */
+	}
+	if (threadIdx.x == 0) {
+		u64 mlo = 0, mhi = 0;
+		for (int w = 0; w < AGGR_THREADS / 32; w++)
+			if (wmax[w][1] > mhi || (wmax[w][1] == mhi && wmax[w][0] > mlo)) {
+				mhi = wmax[w][1];
+				mlo = wmax[w][0];
+			}
+		/* (hi, lo) maximum with two ordered atomics; the bound only needs an upper estimate */
+		const u64 oldhi = atomicMax(&maxabs_out[1], mhi);
+		if (mhi >= oldhi)
+			atomicMax(&maxabs_out[0], mlo);		/* a stale larger lo only makes the bound more careful */
+	}
+}
+
 // ---------------------------------------------------------------- SHM / GLB: table of cells
 // USE_SHM: the block accumulates into a shared-memory copy of the table and flushes it
 // once; otherwise rows go straight to the global table with REDs.

@@ -81,7 +81,7 @@ def q1(X, col, out=None):
         "extents": e, "histo": h,
     }
     if out is not None:
-        out.update(nsel=len(c), groups=g)
+        out.update(nsel=len(c), groups=g, cand=c, rf=rf, ls=ls, disc=disc)
     return res
 
 
