@@ -189,6 +189,7 @@ def b200_arm(args):
     counts = {}
 
     def step(cols):
+        G.stage_cache_clear()       # e2e leg: every step uploads each host column again (once per step)
         return merge(hge_int(pipelines.q6(G, cols, counts)))      # merge == shard.allreduce_hge with a reused buffer
 
     def timed(cols, steps, warmup, sample_clocks=False):
@@ -227,6 +228,7 @@ def b200_arm(args):
     G.timing_enable(False)
     # ---- e2e leg: host heaps through the C-ABI
     e2e_steps = max(1, min(args.steps, 5))
+    G.stage_cache(True)             # a host column used by two operators of the plan (l_discount) is staged once per step
     ms_e, wall_e, res_e, _, _ = timed(hostbats, e2e_steps, 1)
     assert res_e == res, "e2e and device-resident results differ"
 
@@ -243,7 +245,7 @@ def b200_arm(args):
     achieved = mask_bytes / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms else None
     total_rows = n * world
     value = total_rows * args.steps / (ms * 1e-3)
-    h2d = 4 * n + 8 * n * 2 + 8 * n + 8 * n           # shipdate + discount (select, project) + quantity + extprice
+    h2d = 4 * n + 8 * n + 8 * n + 8 * n               # shipdate + discount + quantity + extprice, each staged once per step
     line = {
         "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

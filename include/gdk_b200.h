@@ -96,6 +96,9 @@ b200_bat *b200_BATfromhost(const void *src, int tt, uint64_t cnt, uint64_t hseq)
 b200_bat *b200_BATwrap(void *devptr, int tt, uint64_t cnt, uint64_t hseq);	/* borrow device memory */
 b200_bat *b200_BAThostwrap(const void *hostptr, int tt, uint64_t cnt, uint64_t hseq);	/* borrow HOST memory (device = -1):
 							   every operator stages it to the device on use */
+void b200_stage_cache(int on);		/* keep staged copies of HOST heaps (device = -1) until cleared: a host column used
+					   by several operators of one query is uploaded once */
+void b200_stage_cache_clear(void);	/* drop every staged copy (call when a host heap is written or freed) */
 b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc); /* gdk_cand.c:1296 */
 b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows, const uint32_t *words, bool selected); /* gdk_cand.c:1366 */
 void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil);

@@ -141,7 +141,8 @@ static inline bool bat_is_dense(const b200_bat *b)
 struct Staged {
 	const b200_bat *b = nullptr;
 	b200_bat *tmp = nullptr;
-	~Staged() { if (tmp) b200_BATfree(tmp); }
+	bool cached = false;	/* tmp belongs to the thread's stage cache (b200_stage_cache) */
+	~Staged() { if (tmp && !cached) b200_BATfree(tmp); }
 };
 bool stage(const b200_bat *in, Staged &out);
 

@@ -510,6 +510,20 @@ _sig("b200_timing_read", C.c_int, C.c_char_p, C.c_size_t)
 _sig("b200_BAThostwrap", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
 
 
+_sig("b200_stage_cache", None, C.c_int)
+_sig("b200_stage_cache_clear", None)
+
+
+def stage_cache(on: bool = True) -> None:
+    """keep staged copies of HOST heaps until stage_cache_clear(): a host column used by several
+    operators of one query crosses PCIe once"""
+    lib.b200_stage_cache(1 if on else 0)
+
+
+def stage_cache_clear() -> None:
+    lib.b200_stage_cache_clear()
+
+
 def timing_enable(on: bool = True) -> None:
     lib.b200_timing_enable(1 if on else 0)
 
