@@ -329,6 +329,147 @@ an_range_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__
 		atomicOr(&state[0], (unsigned long long) err);
 }
 
+// RANGE on an order column that is ascending (raw order, nil = smallest) inside every
+// partition — what ORDER BY produces: the reference's linear walk stops at the first row whose
+// distance exceeds the limit, and on sorted data that row is found by a galloping + binary
+// search from k (O(log frame) instead of O(frame) loads per row).  The overflow verdict is kept:
+// the walk only ever subtracts rows up to and including the first failing one, so the checked
+// subtraction can only fail there.
+template <typename T>
+__global__ void __launch_bounds__(256)
+an_sorted_check_kernel(const T *__restrict__ bp, const bte *__restrict__ np, uint64_t n, unsigned long long *__restrict__ state)
+{
+	bool bad = false;
+	for (uint64_t k = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x + 1; k < n; k += (uint64_t) gridDim.x * blockDim.x) {
+		if (np && np[k])
+			continue;
+		const T a = bp[k - 1], b = bp[k];
+		if constexpr (Atom<T>::is_float)
+			bad |= !(a <= b);	/* NaN anywhere -> not usable */
+		else
+			bad |= b < a;
+	}
+	if (bad)
+		atomicOr(&state[1], 1ULL);
+}
+
+template <typename T, typename DT>
+__global__ void __launch_bounds__(AN_THREADS)
+an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__restrict__ bp, bool nonil,
+		       const DT *__restrict__ lim, DT slim, bool preceding, oid *__restrict__ rb,
+		       unsigned long long *__restrict__ state)
+{
+	typedef typename std::conditional<Atom<T>::is_float, T, hge>::type LT;
+	__shared__ TileSegs ts;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	unsigned err = 0;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid m, e;
+		ts.locate(k, m, e);
+		LT ol;
+		if (!an_limit<LT, DT>(lim, (LT) slim, k, ol)) {
+			err |= AN_ERR_BOUND;
+			rb[k] = k;
+			continue;
+		}
+		const T v = bp[k];
+		const bool vnil = !nonil && Atom<T>::is_nil(v);
+		/* ok(j): row j is still inside the frame of row k */
+		auto ok = [&](oid j) -> bool {
+			const T w = bp[j];
+			if (vnil)
+				return Atom<T>::is_nil(w);
+			if (!nonil && Atom<T>::is_nil(w))
+				return false;
+			if constexpr (Atom<T>::is_float) {
+				const T d = v - w;
+				return (d < 0 ? -d : d) <= ol;
+			} else {
+				const hge d = (hge) v - (hge) w;
+				return (d < 0 ? -d : d) <= ol;
+			}
+		};
+		oid good = k, bad = 0;
+		bool have_bad = false;
+		if (preceding) {
+			for (oid step = 1;; step <<= 1) {
+				if (good - m < step) {
+					if (good != m) {
+						if (ok(m))
+							good = m;
+						else {
+							bad = m;
+							have_bad = true;
+						}
+					}
+					break;
+				}
+				const oid pos = good - step;
+				if (ok(pos))
+					good = pos;
+				else {
+					bad = pos;
+					have_bad = true;
+					break;
+				}
+			}
+			if (have_bad)
+				while (good - bad > 1) {
+					const oid mid = bad + (good - bad) / 2;
+					if (ok(mid))
+						good = mid;
+					else
+						bad = mid;
+				}
+			rb[k] = good;
+		} else {
+			for (oid step = 1;; step <<= 1) {
+				if (e - 1 - good < step) {
+					if (good != e - 1) {
+						if (ok(e - 1))
+							good = e - 1;
+						else {
+							bad = e - 1;
+							have_bad = true;
+						}
+					}
+					break;
+				}
+				const oid pos = good + step;
+				if (ok(pos))
+					good = pos;
+				else {
+					bad = pos;
+					have_bad = true;
+					break;
+				}
+			}
+			if (have_bad)
+				while (bad - good > 1) {
+					const oid mid = good + (bad - good) / 2;
+					if (ok(mid))
+						good = mid;
+					else
+						bad = mid;
+				}
+			rb[k] = good + 1;
+		}
+		if (have_bad && !vnil) {
+			const T w = bp[bad];
+			T calc;
+			if (!(!nonil && Atom<T>::is_nil(w)) && !sub_with_check<T>(v, w, calc))
+				err |= AN_ERR_OVERFLOW;
+		}
+	}
+	if (err)
+		atomicOr(&state[0], (unsigned long long) err);
+}
+
 // ---------------------------------------------------------------- host side
 // peer-run starts: row 0, partition starts and every row whose order value differs
 // from its predecessor (nil == nil), gdk_analytic_bounds.c:654-852
@@ -417,11 +558,21 @@ static void groups_launch(const SegList &sl, const SegList &gl, uint64_t n, cons
 	an_groups_kernel<DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, gl.S, gl.cnt, n, (const DT *) lim, slim, preceding, rb, state);
 	COUNT_LAUNCH();
 }
+static thread_local bool tl_range_sorted = false;
+
 template <typename T, typename DT>
 static void range_launch(const SegList &sl, uint64_t n, const b200_bat *b, const void *lim, DT slim, bool preceding, oid *rb,
 			 unsigned long long *state)
 {
 	KTimer kt("an_range", n * (9 + sizeof(T) + (lim ? sizeof(DT) : 0)));
+	if constexpr (sizeof(T) <= 8) {
+		if (tl_range_sorted) {
+			an_range_sorted_kernel<T, DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, n, (const T *) b->base, b->tnonil != 0,
+												 (const DT *) lim, slim, preceding, rb, state);
+			COUNT_LAUNCH();
+			return;
+		}
+	}
 	an_range_kernel<T, DT><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(sl.S, sl.cnt, n, (const T *) b->base, b->tnonil != 0,
 									       (const DT *) lim, slim, preceding, rb, state);
 	COUNT_LAUNCH();
@@ -558,7 +709,30 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 		unsigned long long *state = an_state_init();
 		if (state == nullptr)
 			return B200_FAIL;
-		ctx()->algo = "windowbounds: range, cuda per-row walk";
+		/* ascending inside every partition?  then search instead of walking */
+		tl_range_sorted = false;
+		if (atomsize(t1) <= 8) {
+			const bte *np = p ? (const bte *) p->base : nullptr;
+			const unsigned g = grid_for(n, 256, NSM * 16);
+			switch (t1) {
+			case B200_bte: an_sorted_check_kernel<bte><<<g, 256, 0, ctx()->stream>>>((const bte *) b->base, np, n, state); break;
+			case B200_sht: an_sorted_check_kernel<sht><<<g, 256, 0, ctx()->stream>>>((const sht *) b->base, np, n, state); break;
+			case B200_int: an_sorted_check_kernel<int><<<g, 256, 0, ctx()->stream>>>((const int *) b->base, np, n, state); break;
+			case B200_lng: an_sorted_check_kernel<lng><<<g, 256, 0, ctx()->stream>>>((const lng *) b->base, np, n, state); break;
+			case B200_flt: an_sorted_check_kernel<flt><<<g, 256, 0, ctx()->stream>>>((const flt *) b->base, np, n, state); break;
+			case B200_dbl: an_sorted_check_kernel<dbl><<<g, 256, 0, ctx()->stream>>>((const dbl *) b->base, np, n, state); break;
+			}
+			COUNT_LAUNCH();
+			Ctx *c = ctx();
+			if (!cuda_ok(cudaMemcpyAsync(&c->slot_h->v[8], state + 1, 8, cudaMemcpyDeviceToHost, c->stream), "sorted flag") ||
+			    !stream_sync() || !cuda_ok(cudaMemsetAsync(state + 1, 0, 8, c->stream), "state reset")) {
+				dev_free(state);
+				return B200_FAIL;
+			}
+			tl_range_sorted = c->slot_h->v[8] == 0;
+		}
+		ctx()->algo = tl_range_sorted ? "windowbounds: range, cuda galloping search (sorted partitions)"
+					      : "windowbounds: range, cuda per-row walk";
 		bool launched = true;
 		if (l != nullptr) {
 			const void *lim = l->base;

@@ -1,0 +1,223 @@
+// analytic_prefix.cuh — O(1)-per-row framed SUM for the integer -> hge case.
+//
+// When the result type is hge and the input at most 64 bits wide no sum of fewer than
+// 2^63 rows can overflow, so the reference's checked tree walk (gdk_analytic_func.c:1762-1796)
+// and a difference of two running totals give the same value:  sum[fs,fe) = P[fe] - P[fs],
+// with P the exclusive prefix sum of the non-nil values over the WHOLE column (partition
+// boundaries cancel in the difference) and C the matching prefix count of non-nil rows (only
+// built when the column may hold nils; an all-nil frame yields nil).
+// Three streaming kernels build P (tile sums, one-CTA scan of the tile sums, tile rescan);
+// the frame kernel then reads two prefix entries per row instead of walking ~40 tree nodes.
+#pragma once
+#include "analytic.cuh"
+
+#define AP_THREADS 256
+#define AP_ITEMS 8
+#define AP_TILE (AP_THREADS * AP_ITEMS)
+
+#ifdef __CUDACC__
+__device__ __forceinline__ uhge ap_shfl_up(uhge v, int d)
+{
+	const unsigned long long lo = __shfl_up_sync(0xffffffffu, (unsigned long long) v, d);
+	const unsigned long long hi = __shfl_up_sync(0xffffffffu, (unsigned long long) (v >> 64), d);
+	return ((uhge) hi << 64) | lo;
+}
+
+// CTA-wide exclusive scan of one (sum, count) pair per thread; returns the CTA totals too
+__device__ __forceinline__ void ap_block_scan(uhge &sum, unsigned &cnt, uhge &tot_sum, unsigned &tot_cnt)
+{
+	__shared__ uhge wsum[AP_THREADS / 32];
+	__shared__ unsigned wcnt[AP_THREADS / 32];
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uhge is = sum;
+	unsigned ic = cnt;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uhge ts = ap_shfl_up(is, o);
+		const unsigned tc = __shfl_up_sync(0xffffffffu, ic, o);
+		if (lane >= o) {
+			is += ts;
+			ic += tc;
+		}
+	}
+	if (lane == 31) {
+		wsum[warp] = is;
+		wcnt[warp] = ic;
+	}
+	__syncthreads();
+	uhge bs = 0, ts = 0;
+	unsigned bc = 0, tc = 0;
+#pragma unroll
+	for (int w = 0; w < AP_THREADS / 32; w++) {
+		if (w < (int) warp) {
+			bs += wsum[w];
+			bc += wcnt[w];
+		}
+		ts += wsum[w];
+		tc += wcnt[w];
+	}
+	sum = bs + is - sum;
+	cnt = bc + ic - cnt;
+	tot_sum = ts;
+	tot_cnt = tc;
+	__syncthreads();
+}
+
+template <typename T1>
+__global__ void __launch_bounds__(AP_THREADS)
+an_prefix_tile_kernel(const T1 *__restrict__ bp, uint64_t n, uhge *__restrict__ tsum, unsigned long long *__restrict__ tcnt)
+{
+	const uint64_t base = (uint64_t) blockIdx.x * AP_TILE;
+	uhge s = 0;
+	unsigned c = 0;
+#pragma unroll
+	for (int i = 0; i < AP_ITEMS; i++) {
+		const uint64_t k = base + (uint64_t) i * AP_THREADS + threadIdx.x;
+		if (k < n) {
+			const T1 v = ld_stream(bp + k);
+			if (!Atom<T1>::is_nil(v)) {
+				s += (uhge) (hge) v;
+				c++;
+			}
+		}
+	}
+	uhge ts;
+	unsigned tc;
+	ap_block_scan(s, c, ts, tc);
+	if (threadIdx.x == 0) {
+		tsum[blockIdx.x] = ts;
+		tcnt[blockIdx.x] = tc;
+	}
+}
+
+// exclusive scan of the tile totals by one CTA (each thread owns a contiguous run)
+static __global__ void __launch_bounds__(AP_THREADS)
+an_prefix_scan_kernel(uhge *__restrict__ tsum, unsigned long long *__restrict__ tcnt, uint64_t ntiles)
+{
+	const uint64_t items = (ntiles + AP_THREADS - 1) / AP_THREADS;
+	const uint64_t lo = threadIdx.x * items, hi = lo + items < ntiles ? lo + items : ntiles;
+	uhge s = 0;
+	unsigned long long c = 0;
+	for (uint64_t i = lo; i < hi; i++) {
+		s += tsum[i];
+		c += tcnt[i];
+	}
+	/* counts can exceed 32 bits across the column: scan them as the low half of a second uhge */
+	uhge cs = c, tots, totc;
+	unsigned dummy = 0, dt;
+	ap_block_scan(s, dummy, tots, dt);
+	dummy = 0;
+	ap_block_scan(cs, dummy, totc, dt);
+	unsigned long long cc = (unsigned long long) cs;
+	for (uint64_t i = lo; i < hi; i++) {
+		const uhge t = tsum[i];
+		const unsigned long long u = tcnt[i];
+		tsum[i] = s;
+		tcnt[i] = cc;
+		s += t;
+		cc += u;
+	}
+}
+
+// P[k] = sum of the non-nil values of rows [0, k), k = 0..n; C likewise (optional)
+template <typename T1>
+__global__ void __launch_bounds__(AP_THREADS)
+an_prefix_write_kernel(const T1 *__restrict__ bp, uint64_t n, const uhge *__restrict__ tsum,
+		       const unsigned long long *__restrict__ tcnt, uhge *__restrict__ P, unsigned long long *__restrict__ C)
+{
+	const uint64_t base = (uint64_t) blockIdx.x * AP_TILE + (uint64_t) threadIdx.x * AP_ITEMS;
+	T1 v[AP_ITEMS];
+	uhge s = 0;
+	unsigned c = 0;
+#pragma unroll
+	for (int i = 0; i < AP_ITEMS; i++) {
+		const uint64_t k = base + i;
+		v[i] = k < n ? bp[k] : Atom<T1>::nil();
+		if (!Atom<T1>::is_nil(v[i])) {
+			s += (uhge) (hge) v[i];
+			c++;
+		}
+	}
+	uhge ts;
+	unsigned tc;
+	ap_block_scan(s, c, ts, tc);
+	uhge run = tsum[blockIdx.x] + s;
+	unsigned long long rc = tcnt[blockIdx.x] + c;
+	if (base == 0 && n > 0) {
+		P[0] = 0;
+		if (C)
+			C[0] = 0;
+	}
+#pragma unroll
+	for (int i = 0; i < AP_ITEMS; i++) {
+		const uint64_t k = base + i;
+		if (k < n) {
+			if (!Atom<T1>::is_nil(v[i])) {
+				run += (uhge) (hge) v[i];
+				rc++;
+			}
+			P[k + 1] = run;
+			if (C)
+				C[k + 1] = rc;
+		}
+	}
+}
+
+// frames as in an_frame_kernel (analytic_tree.cuh); result hge, nil when the frame holds no value
+template <bool PEERS>
+__global__ void __launch_bounds__(AN_THREADS)
+an_frame_prefix_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__ O, uint64_t ocnt, uint64_t n,
+		       const oid *__restrict__ fstart, const oid *__restrict__ fend, int frame_type,
+		       const uhge *__restrict__ P, const unsigned long long *__restrict__ C, hge *__restrict__ rb,
+		       unsigned long long *__restrict__ state)
+{
+	__shared__ TileSegs ts;
+	__shared__ TileSegs to;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	const bool need_part = frame_type != 6;
+	if (need_part)
+		ts.load(S, cnt, base, last);
+	if (PEERS)
+		to.load(O, ocnt, base, last);
+	unsigned nils = 0;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid ps = 0, pe = n, fs, fe;
+		if (need_part)
+			ts.locate(k, ps, pe);
+		switch (frame_type) {
+		case 3:
+		case 4: {
+			oid os = ps, oe = pe;
+			if (PEERS)
+				to.locate(k, os, oe);
+			fs = frame_type == 3 ? ps : os;
+			fe = frame_type == 3 ? oe : pe;
+			break;
+		}
+		case 5: fs = ps; fe = pe; break;
+		case 6: fs = k; fe = k + 1; break;
+		default:
+			fs = fstart[k];
+			fe = fend[k];
+			if (fs < ps)
+				fs = ps;
+			if (fe > pe)
+				fe = pe;
+			break;
+		}
+		hge res = Atom<hge>::nil();
+		if (fs < fe && (C == nullptr || C[fe] != C[fs]))
+			res = (hge) (P[fe] - P[fs]);
+		else
+			nils++;
+		rb[k] = res;
+	}
+	nils = __reduce_add_sync(0xffffffffu, nils);
+	if ((threadIdx.x & 31) == 0 && nils)
+		atomicAdd(&state[1], (unsigned long long) nils);
+}
+#endif

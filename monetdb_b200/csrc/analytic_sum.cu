@@ -1,6 +1,7 @@
 // analytic_sum.cu — GDKanalyticalsum (gdk_analytic_func.c:1959-2022) and the argument
 // handling shared by the analytic aggregates.
 #include "analytic_aggr.cuh"
+#include "analytic_prefix.cuh"
 
 bool an_frame_prepare(const char *fn, b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b, const b200_bat *s,
 		      const b200_bat *e, int rtype, int frame_type, FrameStage &fs, FrameArgs &fa)
@@ -51,9 +52,62 @@ b200_return an_frame_done(b200_bat *r, uint64_t n, bool has_nils)
 	return B200_SUCCEED;
 }
 
+// integer -> hge: prefix sums (analytic_prefix.cuh)
+template <typename T1>
+static bool sum_prefix_run(const FrameArgs &fa, hge *rb, unsigned long long st[2])
+{
+	Ctx *c = ctx();
+	const uint64_t n = fa.n;
+	const uint64_t ntiles = (n + AP_TILE - 1) / AP_TILE;
+	const bool peers = fa.frame_type == 3 || fa.frame_type == 4;
+	const bool framed = fa.frame_type < 3 || fa.frame_type > 6;
+	SegList S, O;
+	if (fa.frame_type != 6 && !an_partitions(fa.p, nullptr, n, S))
+		return false;
+	if (peers && !an_partitions(fa.p, fa.o, n, O))
+		return false;
+	unsigned long long *state = an_state_init();
+	uhge *tsum = (uhge *) dev_alloc(ntiles * 16), *P = (uhge *) dev_alloc((n + 1) * 16);
+	unsigned long long *tcnt = (unsigned long long *) dev_alloc(ntiles * 8);
+	unsigned long long *C = fa.b->tnonil ? nullptr : (unsigned long long *) dev_alloc((n + 1) * 8);
+	bool ok = state && tsum && P && tcnt && (fa.b->tnonil || C);
+	if (ok) {
+		const T1 *bp = (const T1 *) fa.b->base;
+		{
+			KTimer kt("an_prefix", n * (2 * sizeof(T1) + 16 + (C ? 8 : 0)));
+			an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
+			COUNT_LAUNCH();
+			an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
+			COUNT_LAUNCH();
+			an_prefix_write_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt, P, C);
+			COUNT_LAUNCH();
+		}
+		KTimer kt("an_sum", n * ((framed ? 16 : 0) + 32 + 16));
+		const unsigned grid = (unsigned) ((n + AN_TILE - 1) / AN_TILE);
+		const oid *fs = framed ? (const oid *) fa.s->base : nullptr, *fe = framed ? (const oid *) fa.e->base : nullptr;
+		if (peers)
+			an_frame_prefix_kernel<true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, O.S, O.cnt, n, fs, fe, fa.frame_type, P, C, rb, state);
+		else
+			an_frame_prefix_kernel<false><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, nullptr, 0, n, fs, fe, fa.frame_type, P, C, rb, state);
+		COUNT_LAUNCH();
+		ctx()->algo = "analyticalsum: cuda prefix sums";
+	}
+	if (tsum) dev_free(tsum);
+	if (tcnt) dev_free(tcnt);
+	if (P) dev_free(P);
+	if (C) dev_free(C);
+	if (!ok) {
+		if (state) dev_free(state);
+		return false;
+	}
+	return an_read_state(state, st);
+}
+
 template <typename T1, typename T2>
 static bool sum_run(const FrameArgs &fa, void *rb, unsigned long long st[2])
 {
+	if constexpr (sizeof(T2) == 16 && sizeof(T1) <= 8 && !Atom<T1>::is_float)
+		return sum_prefix_run<T1>(fa, (hge *) rb, st);
 	ctx()->algo = "analyticalsum: cuda fan-out-16 segment tree";
 	return an_run<SumOp<T1, T2>>(fa, (T2 *) rb, st, "an_sum");
 }

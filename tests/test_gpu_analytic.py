@@ -357,3 +357,25 @@ def test_config5_shape(gdk, ref):
         r = gdk.GDKanalyticalfn("avg", gdk.colnew(T.dbl, n), p, None, v, s, e, T.lng, unit)
         rr = ref.GDKanalyticalfn("avg", ref.colnew(T.dbl, n), rp, None, rv, rs, re_, T.lng, unit)
         close(r.numpy(), rr.numpy(), T.dbl, True)
+
+
+@pytest.mark.parametrize("tt", [T.int, T.lng, T.dbl])
+@pytest.mark.parametrize("preceding", [True, False])
+@pytest.mark.parametrize("order", ["random", "desc"])
+def test_range_bounds_unsorted(gdk, ref, tt, preceding, order):
+    """order columns that are NOT ascending inside the partitions take the per-row walk
+    (the reference itself never requires sortedness)"""
+    rng = np.random.default_rng(tt + len(order))
+    for n, nparts, nilfrac in ((300, 4, 0.0), (20011, 40, 0.0), (20011, 40, 0.1)):
+        pkey, o = window(rng, n, nparts, tt)
+        if order == "random":
+            o = random_col(rng, tt, n, nilfrac=nilfrac, lo=0, hi=40)
+        else:
+            o = o[::-1].copy()
+        p, rp = flags(gdk, ref, pkey, T.int)
+        b, rb = both(gdk, ref, o, tt)
+        for lim in ((1.5, 7.0) if tt == T.dbl else (1, 7)):
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, tt, tt, 1, preceding, 0)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, tt, tt, 1, preceding, 0)
+            check_oid(r, rr)
+        assert "walk" in gdk.algorithm()
