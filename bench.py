@@ -339,19 +339,35 @@ def other_workload(args):
         bytes_of = lambda: 4 * n + 76 * info["sel"]
         label = f"config 1: BATselect range + BATgroup + BATgroupsum on a {n}-row int/lng column pair"
     elif w == "join":
+        # config 4 shape: l_orderkey = 1 + z % NR (about 4 matches per key), o_orderkey = a fixed bijection of
+        # 1..NR (unique, unsorted: forces hashjoin, gdk_join.c:4568).  Rank g holds rows [g*nl,(g+1)*nl) of
+        # lineitem and [g*nr,(g+1)*nr) of orders with global hseqbase; NR = world * nr.
         nl, nr = n, max(1, n // 4)
-        rng = np.random.default_rng(0x5EED0009)
-        okey = (rng.permutation(nr) + 1).astype(np.int32)
-        lkey = (workload.splitmix64(workload.col_seed(workload.C_LKEY), 0, nl) % np.uint64(nr) + np.uint64(1)).astype(np.int32)
-        dev = {"l": G.BATfromhost(lkey, T.int, nonil=True), "r": G.BATfromhost(okey, T.int, nonil=True, key=True)}
+        NR = nr * world
+        A = 2654435761                                  # odd and coprime to NR for the sizes used here
+        while np.gcd(A, NR) != 1:
+            A += 2
+        i = np.arange(rank * nr, (rank + 1) * nr, dtype=np.uint64)
+        okey = ((i * np.uint64(A) + np.uint64(12345)) % np.uint64(NR) + np.uint64(1)).astype(np.int32)
+        lkey = (workload.splitmix64(workload.col_seed(workload.C_LKEY), rank * nl, (rank + 1) * nl) % np.uint64(NR)
+                + np.uint64(1)).astype(np.int32)
+        dev = {"l": G.BATfromhost(lkey, T.int, hseq=rank * nl, nonil=True),
+               "r": G.BATfromhost(okey, T.int, hseq=rank * nr, nonil=True, key=True)}
+        phases = {}
 
         def step():
-            r1, r2 = G.BATjoin(dev["l"], dev["r"], None, None, False)
-            info["pairs"] = len(r1)
+            if world == 1:
+                r1, r2 = G.BATjoin(dev["l"], dev["r"], None, None, False)
+            else:
+                r1, r2 = shard.join_repartitioned(G, dev["l"], dev["r"], dist, torch, torch.device("cuda", local), phases)
+            info["pairs_rank0"] = len(r1)
             return len(r1)
         metric = "GDK hash join rows/s (lineitem JOIN orders shape, probe rows)"
-        bytes_of = lambda: (4 + 8 + 8) * nr + (4 + 2 * 8 + 16) * nl
-        label = f"config 4 shape on one GPU: {nl} int32 probe keys x {nr} unique build keys (BAThash + BATjoin)"
+        # per rank: partition pass 2*(4+8) per tuple of both sides + exchange + build 4+8+8 per build row + probe
+        bytes_of = lambda: world * ((4 + 8 + 8) * nr + (4 + 2 * 8 + 16) * nl + (0 if world == 1 else 2 * (4 + 8) * (nl + nr)))
+        label = (f"config 4 shape: {nl} int32 probe keys x {nr} unique build keys per GPU (BAThash + BATjoin)"
+                 + ("" if world == 1 else "; hash repartition of both sides + NCCL all-to-all of (key, oid) tuples"))
+        info["phases_ms_last_step"] = phases
     elif w == "window":
         blk = workload.window_layout()
         n = max(blk, n // blk * blk)
@@ -393,11 +409,15 @@ def other_workload(args):
         l0 = G.kernel_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        walls = []
         for _ in range(steps):
+            tw = time.perf_counter()
             res = step()
+            walls.append(round((time.perf_counter() - tw) * 1e3, 3))
         e1.record(stream)
         barrier()
         ms = e0.elapsed_time(e1)
+        info["host_ms_per_step"] = walls
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -411,7 +431,7 @@ def other_workload(args):
     G.timing_enable(False)
     if rank == 0:
         peak, peak_src = measured_hbm_peak()
-        rows = n * world if w != "join" else n
+        rows = n * world
         by = bytes_of()
         gbs = by * args.steps / (ms * 1e-3) / 1e9
         print(json.dumps({

@@ -168,6 +168,13 @@ b200_return b200_BAThash(const b200_bat *b);
 b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
 			 const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate);
 
+/* ---- the one exchange step of the multi-GPU path (no reference counterpart: mitosis only slices by row
+ *      range, opt_mitosis.c:188-214): split (key, oid) tuples by hash(key) mod nparts into nparts
+ *      contiguous send runs for an NCCL all-to-all.  counts[d] = tuples for destination d; pass
+ *      keys_out = oids_out = NULL to size the buffers first. ---- */
+b200_return b200_hash_partition(const b200_bat *b, const b200_bat *s, int nparts, bool keep_nil, void *keys_out,
+				b200_oid *oids_out, uint64_t *counts);
+
 /* ---- window frames and analytic aggregates: gdk_analytic.h:21-42.
  *      As in the reference the CALLER allocates r (b200_COLnew of the result type,
  *      capacity >= BATcount(b)); the callee fills it and sets count/tnil/tnonil. ---- */

@@ -504,6 +504,22 @@ def GDKanalyticalcount(r, p, o, b, s, e, ignore_nils, tpe, frame_type):
     return r
 
 
+# ------------------------------------------------------------------ multi-GPU exchange step
+_sig("b200_hash_partition", C.c_int, _P, _P, C.c_int, C.c_bool, C.c_void_p, C.c_void_p, C.c_void_p)
+
+
+def hash_partition(b: BAT, s: BAT | None, nparts: int, keys_ptr: int | None = None, oids_ptr: int | None = None,
+                   keep_nil: bool = False) -> np.ndarray:
+    """counts per destination of hash(key) mod nparts; with device pointers also scatters the (key, oid)
+    tuples into nparts contiguous runs (destination d at offset sum(counts[:d]))"""
+    counts = np.zeros(nparts, dtype=np.uint64)
+    rc = lib.b200_hash_partition(b._p, _ptr(s), nparts, keep_nil, C.c_void_p(keys_ptr) if keys_ptr else None,
+                                 C.c_void_p(oids_ptr) if oids_ptr else None, _vp(counts))
+    if rc != 1:
+        _fail("hash_partition")
+    return counts
+
+
 # ------------------------------------------------------------------ bench support
 _sig("b200_timing_enable", None, C.c_int)
 _sig("b200_timing_read", C.c_int, C.c_char_p, C.c_size_t)

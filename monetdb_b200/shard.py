@@ -138,3 +138,107 @@ def q1_sharded(X, cols, dist=None) -> dict:
     tables = [None] * dist.get_world_size()
     dist.all_gather_object(tables, mine)
     return q1_merge(tables)
+
+
+# ---------------------------------------------------------------------------- config 4: repartitioned hash join
+_TORCH_OF = {3: "int8", 4: "int16", 5: "int32", 10: "int64", 6: "int64", 8: "float32", 9: "float64"}
+
+
+def _partition_to_torch(X, col, world, torch, device):
+    """hash-partition one side into `world` contiguous send runs held in torch tensors"""
+    counts = X.hash_partition(col, None, world)
+    total = int(counts.sum())
+    tt = X._storage(col.ttype)
+    keys = torch.empty(max(total, 1), dtype=getattr(torch, _TORCH_OF[tt]), device=device)
+    oids = torch.empty(max(total, 1), dtype=torch.int64, device=device)
+    torch.cuda.current_stream().synchronize()
+    if total:
+        c2 = X.hash_partition(col, None, world, keys.data_ptr(), oids.data_ptr())
+        assert (c2 == counts).all()
+    X.sync()
+    return counts.astype("int64"), keys, oids, tt
+
+
+def join_repartitioned(X, l, r, dist, torch, device, timings=None):
+    """lineitem JOIN orders across the GPUs of one box: every rank hash-partitions its
+    shard of both key columns by hash(key) mod world (b200_hash_partition), one NCCL all-to-all per
+    side moves (key, global oid) tuples to the rank that owns the hash range, and each rank then
+    builds and probes locally (BAThash + BATjoin).  Returns this rank's slice of the result as two
+    aligned device BATs of GLOBAL oids (r1: rows of l, r2: rows of r); the concatenation over ranks is
+    the join, in no particular order (BATjoin promises none, gdk_join.c:56-61)."""
+    import time
+    world = dist.get_world_size()
+
+    def mark(name, t0):
+        if timings is not None:
+            torch.cuda.synchronize()
+            timings[name] = (time.perf_counter() - t0) * 1e3      # the latest call
+
+    t0 = time.perf_counter()
+    sides = [_partition_to_torch(X, c, world, torch, device) for c in (l, r)]
+    mark("partition_ms", t0)
+    t0 = time.perf_counter()
+    recv = []
+    for counts, keys, oids, tt in sides:
+        send_counts = torch.tensor(counts, dtype=torch.int64, device=device)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts)
+        rc = recv_counts.tolist()
+        sc = [int(x) for x in counts]
+        nrecv = sum(rc)
+        rk = torch.empty(max(nrecv, 1), dtype=keys.dtype, device=device)
+        ro = torch.empty(max(nrecv, 1), dtype=torch.int64, device=device)
+        dist.all_to_all_single(rk[:nrecv], keys[:sum(sc)], rc, sc)
+        dist.all_to_all_single(ro[:nrecv], oids[:sum(sc)], rc, sc)
+        recv.append((rk, ro, nrecv, tt))
+    mark("exchange_ms", t0)
+    t0 = time.perf_counter()
+    (lk, lo, nl, tt), (rk, ro, nr, _) = recv
+    res = _local_join(X, lk.data_ptr(), lo.data_ptr(), nl, rk.data_ptr(), ro.data_ptr(), nr, tt, keep=(lk, lo, rk, ro))
+    X.sync()
+    mark("join_ms", t0)
+    return res
+
+
+def _local_join(X, lk_ptr, lo_ptr, nl, rk_ptr, ro_ptr, nr, tt, keep=None):
+    """BATjoin of received (key, oid) runs; positions are mapped back to the global oids they carry"""
+    T = X.TYPE
+    lkb = X.BATwrap(lk_ptr, tt, nl, 0, keep=keep)
+    rkb = X.BATwrap(rk_ptr, tt, nr, 0, keep=keep)
+    r1, r2 = X.BATjoin(lkb, rkb, None, None, False)
+    g1 = X.BATproject(r1, X.BATwrap(lo_ptr, T.oid, nl, 0, keep=keep))
+    g2 = X.BATproject(r2, X.BATwrap(ro_ptr, T.oid, nr, 0, keep=keep))
+    return g1, g2
+
+
+def join_partitioned_single_gpu(X, l, r, nparts):
+    """the same plan on ONE GPU with the exchange replaced by slicing the send runs: partition both
+    sides into `nparts` hash ranges, join range d of l with range d of r, concatenate.  Used by the
+    parity tests (no NCCL needed) to pin the partitioning + local-join logic against BATjoin."""
+    import numpy as np
+    T = X.TYPE
+    out1, out2 = [], []
+    parts = []
+    for col in (l, r):
+        counts = X.hash_partition(col, None, nparts)
+        total = int(counts.sum())
+        tt = X._storage(col.ttype)
+        keys = X.COLnew(0, tt, max(total, 1))
+        oids = X.COLnew(0, T.oid, max(total, 1))
+        if total:
+            X.hash_partition(col, None, nparts, keys.base, oids.base)
+        parts.append((counts, keys, oids, tt))
+    (lc, lkeys, loids, tt), (rc, rkeys, roids, _) = parts
+    w = X.NP_OF[tt].itemsize
+    lo_off = ro_off = 0
+    for d in range(nparts):
+        nl, nr = int(lc[d]), int(rc[d])
+        if nl and nr:
+            g1, g2 = _local_join(X, lkeys.base + lo_off * w, loids.base + lo_off * 8, nl,
+                                 rkeys.base + ro_off * w, roids.base + ro_off * 8, nr, tt, keep=(lkeys, loids, rkeys, roids))
+            out1.append(g1.numpy())
+            out2.append(g2.numpy())
+        lo_off += nl
+        ro_off += nr
+    cat = lambda xs: np.concatenate(xs) if xs else np.zeros(0, dtype=np.uint64)
+    return cat(out1), cat(out2)
