@@ -36,6 +36,37 @@ extern "C" void b200_stage_cache(int on)
 		b200_stage_cache_clear();
 }
 
+// A host heap that an operator will only touch sparsely (a gather through a short candidate
+// list) is not staged at all when it lives in page-locked, device-mapped host memory: the
+// kernel dereferences it over PCIe and moves one 32-64 byte atom per touched row instead of the
+// whole column.  Falls back to stage() for pageable memory, dense access or a cached copy.
+bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows)
+{
+	if (in != nullptr && in->device < 0 && in->base != nullptr && in->ccand == B200_CAND_NONE && in->ttype != B200_void &&
+	    in->ttype != B200_msk && touch_rows < in->count / 16 && ctx()->device >= 0) {
+		bool cached = false;
+		if (tl_stage_on && tl_stage)
+			for (StageEntry &e : *tl_stage)
+				cached |= e.host == in->base;
+		cudaPointerAttributes at;
+		if (!cached && cudaPointerGetAttributes(&at, in->base) == cudaSuccess && at.type == cudaMemoryTypeHost &&
+		    at.devicePointer != nullptr) {
+			b200_bat *t = bat_alloc_desc();
+			if (t == nullptr)
+				return false;
+			*t = *in;
+			t->device = ctx()->device;
+			t->owns = 0;
+			t->base = at.devicePointer;
+			out.tmp = t;
+			out.b = t;
+			return true;
+		}
+		cudaGetLastError();	/* pageable memory: attributes query may have set an error */
+	}
+	return stage(in, out);
+}
+
 bool stage(const b200_bat *in, Staged &out)
 {
 	out.b = in;

@@ -145,6 +145,7 @@ struct Staged {
 	~Staged() { if (tmp && !cached) b200_BATfree(tmp); }
 };
 bool stage(const b200_bat *in, Staged &out);
+bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows);	/* zero-copy for sparse gathers */
 
 // ---------------------------------------------------------------- candidates
 // canditer_init (gdk_cand.c:407-712) restated for the device: after clipping to

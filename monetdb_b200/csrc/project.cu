@@ -168,7 +168,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		return nullptr;
 	}
 	Staged sl, s1, s2;
-	if (!stage(l, sl) || !stage(r1, s1) || !stage(r2, s2))
+	if (!stage(l, sl) || !stage_sparse(r1, s1, r2 == nullptr && l != nullptr ? l->count : UINT64_MAX) || !stage(r2, s2))
 		return nullptr;
 	l = sl.b;
 	r1 = s1.b;

@@ -379,7 +379,7 @@ static b200_bat *select_impl(const b200_bat *b, const b200_bat *s, const void *t
 		return nullptr;
 	}
 	Staged sb, ss;
-	if (!stage(b, sb) || !stage(s, ss))
+	if (!stage(s, ss) || !stage_sparse(b, sb, s != nullptr && s->ttype != B200_void && s->ccand == B200_CAND_NONE ? s->count : UINT64_MAX))
 		return nullptr;
 	b = sb.b;
 	s = ss.b;
