@@ -186,6 +186,8 @@ b200_return b200_GDKanalyticalsum(b200_bat *r, const b200_bat *p, const b200_bat
 				  const b200_bat *s, const b200_bat *e, int tp1, int tp2, int frame_type);
 b200_return b200_GDKanalyticalavg(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
 				  const b200_bat *s, const b200_bat *e, int tpe, int frame_type);
+b200_return b200_GDKanalyticalavginteger(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+					 const b200_bat *s, const b200_bat *e, int tpe, int frame_type);	/* gdk_analytic_statistics.c:631 */
 b200_return b200_GDKanalyticalcount(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
 				    const b200_bat *s, const b200_bat *e, int8_t ignore_nils, int tpe, int frame_type);
 b200_return b200_GDKanalyticalmin(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,

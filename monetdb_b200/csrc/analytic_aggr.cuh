@@ -215,6 +215,107 @@ template <typename T> struct AvgTreeIntOp {
 	}
 };
 
+// ---- integer-typed average (GDKanalyticalavginteger, gdk_analytic_statistics.c:449-700):
+// AVERAGE_ITER's (avg = floor(S/n), rem) followed by round-half-away-from... the reference's
+// ANALYTICAL_AVERAGE_INT_CALC_FINALIZE (:434-446): rem > 0 and (avg < 0 ? 2 rem > n : 2 rem >= n)
+// bumps avg by one.  EXACT = frame types 3-5 (plain running AVERAGE_ITER over the frame's values);
+// otherwise the fan-out-16 tree of avg_int_deltas, whose inner nodes hold their children's
+// UN-finalised floor averages and count as one value each (COMPUTE_LEVELN_AVG_INT, :538-542).
+template <typename T, bool EXACT> struct AvgIntegerOp {
+	struct NodeExact {
+		hge sum;
+		lng n;
+	};
+	struct NodeTree {
+		T a;
+		bte has;
+	};
+	struct AccT {
+		hge sum;
+		lng n;
+	};
+	typedef T In;
+	typedef typename std::conditional<EXACT, NodeExact, NodeTree>::type Node;
+	typedef AccT Acc;
+	typedef T Out;
+	static constexpr bool direct = false;
+	__device__ static __forceinline__ Node leaf(In v)
+	{
+		Node x;
+		const bool has = !Atom<T>::is_nil(v);
+		if constexpr (EXACT) {
+			x.sum = has ? (hge) v : (hge) 0;
+			x.n = has;
+		} else {
+			x.a = has ? v : (T) 0;
+			x.has = has;
+		}
+		return x;
+	}
+	__device__ static __forceinline__ void init(Acc &a)
+	{
+		a.sum = 0;
+		a.n = 0;
+	}
+	__device__ static __forceinline__ void add(Acc &a, const Node &v, unsigned &err)
+	{
+		if constexpr (EXACT) {
+			a.sum += v.sum;
+			a.n += v.n;
+		} else if (v.has) {
+			a.sum += (hge) v.a;
+			a.n++;
+		}
+	}
+	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
+	{
+		q = a.sum / (hge) a.n;
+		hge r = a.sum - q * (hge) a.n;
+		if (r < 0) {
+			q--;
+			r += a.n;
+		}
+		rr = (lng) r;
+	}
+	__device__ static __forceinline__ Node node(const Acc &a)
+	{
+		Node x;
+		if constexpr (EXACT) {
+			x.sum = a.sum;
+			x.n = a.n;
+		} else {
+			x.has = a.n != 0;
+			x.a = 0;
+			if (x.has) {
+				hge q;
+				lng rr;
+				floor_div(a, q, rr);
+				x.a = (T) q;
+			}
+		}
+		return x;
+	}
+	__device__ static __forceinline__ Out result(const Acc &a, bool &isnil)
+	{
+		isnil = a.n == 0;
+		if (isnil)
+			return Atom<T>::nil();
+		hge q;
+		lng rr;
+		floor_div(a, q, rr);
+		T avg = (T) q;
+		if (rr > 0) {
+			if (avg < 0) {
+				if (2 * rr > a.n)
+					avg++;
+			} else if (2 * rr >= a.n) {
+				avg++;
+			}
+		}
+		return avg;
+	}
+};
+
 // ---- average, frame types 0-2, floats: running AVERAGE_ITER_FLOAT over the touched nodes
 // (gdk_analytic_statistics.c:268-303, gdk_calc_private.h:277-289), order-dependent and
 // therefore evaluated in the reference's order

@@ -53,6 +53,48 @@ extern "C" b200_return b200_GDKanalyticalavg(b200_bat *r, const b200_bat *p, con
 	return an_frame_done(r, fa.n, st[1] != 0);
 }
 
+// ---------------------------------------------------------------- avg with an integer result
+template <typename T> static bool avgint_run(const FrameArgs &fa, T *rb, unsigned long long st[2])
+{
+	const bool framed = fa.frame_type < 3 || fa.frame_type > 6;
+	ctx()->algo = framed ? "analyticalavginteger: cuda fan-out-16 segment tree" : "analyticalavginteger: cuda exact sum/count";
+	if (framed)
+		return an_run<AvgIntegerOp<T, false>>(fa, rb, st, "an_avg");
+	return an_run<AvgIntegerOp<T, true>>(fa, rb, st, "an_avg");
+}
+
+extern "C" b200_return b200_GDKanalyticalavginteger(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
+						    const b200_bat *s, const b200_bat *e, int tpe, int frame_type)
+{
+	FrameStage fs;
+	FrameArgs fa;
+	if (!an_frame_prepare("GDKanalyticalavginteger", r, p, o, b, s, e, tpe, frame_type, fs, fa))
+		return B200_FAIL;
+	if (fa.n == 0)
+		return an_frame_done(r, 0, false);
+	if (atomsize(fa.b->ttype) != atomsize(tpe)) {
+		set_err("GDKanalyticalavginteger: tpe does not match the input column\n");
+		return B200_FAIL;
+	}
+	unsigned long long st[2] = {0, 0};
+	bool ok;
+	switch (tpe) {		/* the reference switches on tpe itself, not its base type (:674-690) */
+	case B200_bte: ok = avgint_run<bte>(fa, (bte *) r->base, st); break;
+	case B200_sht: ok = avgint_run<sht>(fa, (sht *) r->base, st); break;
+	case B200_int: ok = avgint_run<int>(fa, (int *) r->base, st); break;
+	case B200_lng: ok = avgint_run<lng>(fa, (lng *) r->base, st); break;
+	case B200_hge:
+		set_err("GDKanalyticalavginteger: hge input (sum may exceed 128 bits) is not on the device path\n");
+		return B200_FAIL;
+	default:
+		set_err("42000!average of type %s to %s unsupported.\n", atomname(tpe), atomname(tpe));
+		return B200_FAIL;
+	}
+	if (!ok)
+		return B200_FAIL;
+	return an_frame_done(r, fa.n, st[1] != 0);
+}
+
 // ---------------------------------------------------------------- count
 extern "C" b200_return b200_GDKanalyticalcount(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
 					       const b200_bat *s, const b200_bat *e, int8_t ignore_nils, int tpe, int frame_type)

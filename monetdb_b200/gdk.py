@@ -459,7 +459,7 @@ def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if
 _sig("b200_GDKanalyticaldiff", C.c_int, _P, _P, _P, C.c_void_p, C.c_int)
 _sig("b200_GDKanalyticalwindowbounds", C.c_int, _P, _P, _P, _P, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_bool, C.c_uint64)
 _sig("b200_GDKanalyticalsum", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int)
-for _n in ("avg", "min", "max"):
+for _n in ("avg", "avginteger", "min", "max"):
     _sig(f"b200_GDKanalytical{_n}", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int)
 _sig("b200_GDKanalyticalcount", C.c_int, _P, _P, _P, _P, _P, _P, C.c_int8, C.c_int, C.c_int)
 

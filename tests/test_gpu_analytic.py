@@ -379,3 +379,18 @@ def test_range_bounds_unsorted(gdk, ref, tt, preceding, order):
             rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, tt, tt, 1, preceding, 0)
             check_oid(r, rr)
         assert "walk" in gdk.algorithm()
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng])
+@pytest.mark.parametrize("frame_type", [0, 3, 4, 5, 6])
+def test_avginteger(gdk, ref, tt, frame_type):
+    """GDKanalyticalavginteger: integer-typed average with the reference's rounding, bit-exact"""
+    rng = np.random.default_rng(tt * 17 + frame_type)
+    for n, nparts, rows in SHAPES:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        v = random_col(rng, tt, n, nilfrac=0.1)
+        b, rb = both(gdk, ref, v, tt)
+        r = gdk.GDKanalyticalfn("avginteger", gdk.colnew(tt, n), p, op, b, s, e, tt, frame_type)
+        rr = ref.GDKanalyticalfn("avginteger", ref.colnew(tt, n), rp, rop, rb, rs, re_, tt, frame_type)
+        close(r.numpy(), rr.numpy(), tt, True)
+        assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
