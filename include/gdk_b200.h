@@ -161,6 +161,14 @@ b200_bat *b200_BATgroupmin(const b200_bat *b, const b200_bat *g, const b200_bat 
 b200_bat *b200_BATgroupmax(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const b200_bat *b, const b200_bat *g,
 			     const b200_bat *e, const b200_bat *s, int tp, bool skip_nils, int scale);
+
+/* exact integer average as (floor-rounded avg, rem, cnt) triples and their recombination —
+ * mergetable's phase 1 / phase 2 (gdk_aggr.c:1996, 2634); scalar average (gdk_aggr.c:2987) */
+b200_return b200_BATgroupavg3(b200_bat **avgp, b200_bat **remp, b200_bat **cntp, const b200_bat *b, const b200_bat *g,
+			      const b200_bat *e, const b200_bat *s, bool skip_nils);
+b200_bat *b200_BATgroupavg3combine(const b200_bat *avg, const b200_bat *rem, const b200_bat *cnt, const b200_bat *g,
+				   const b200_bat *e, bool skip_nils);
+b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, double *avg, uint64_t *vals, int scale);
 b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
 
 /* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */

@@ -761,3 +761,210 @@ extern "C" b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const 
 	*bnp = bn;
 	return B200_SUCCEED;
 }
+
+// ---------------------------------------------------------------- avg3 / avg3combine / calcavg
+static void free3(b200_bat *x, b200_bat *y, b200_bat *z)
+{
+	b200_BATfree(x);
+	b200_BATfree(y);
+	b200_BATfree(z);
+}
+
+// gdk_aggr.c:1996-2290.  Integer columns only (the reference's switch has no flt/dbl case).
+extern "C" b200_return b200_BATgroupavg3(b200_bat **avgp, b200_bat **remp, b200_bat **cntp, const b200_bat *b, const b200_bat *g,
+					 const b200_bat *e, const b200_bat *s, bool skip_nils)
+{
+	b200_clrerr();
+	if (avgp == nullptr || remp == nullptr || cntp == nullptr) {
+		set_err("BATgroupavg3: result pointers required\n");
+		return B200_FAIL;
+	}
+	*avgp = *remp = *cntp = nullptr;
+	AggrSetup a;
+	if (!aggr_init(a, b, g, e, s))
+		return B200_FAIL;
+	const int t = basetype(a.b->ttype);
+	if (int_rank(t) < 0) {
+		set_err("BATgroupavg3: type %s is not an integer type\n", atomname(a.b->ttype));
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	b200_bat *bn, *rn, *cn;
+	const lng zero = 0;
+	if (a.ci.ncand == 0 || a.ngrp == 0) {
+		const uint64_t hs = a.ngrp == 0 ? 0 : a.min;
+		bn = bat_constant(hs, a.b->ttype, nullptr, a.ngrp);
+		rn = bat_constant(hs, B200_lng, nullptr, a.ngrp);
+		cn = bat_constant(hs, B200_lng, &zero, a.ngrp);
+		if (bn == nullptr || rn == nullptr || cn == nullptr) {
+			free3(bn, rn, cn);
+			return B200_FAIL;
+		}
+		*avgp = bn;
+		*remp = rn;
+		*cntp = cn;
+		return B200_SUCCEED;
+	}
+	AggrAccum acc;
+	if (!aggr_accumulate(a, skip_nils, 0, acc))
+		return B200_FAIL;
+	const unsigned ngrp = (unsigned) a.ngrp;
+	bn = bat_new(a.min, a.b->ttype, a.ngrp);
+	rn = bat_new(a.min, B200_lng, a.ngrp);
+	cn = bat_new(a.min, B200_lng, a.ngrp);
+	if (bn == nullptr || rn == nullptr || cn == nullptr) {
+		free3(bn, rn, cn);
+		return B200_FAIL;
+	}
+	const unsigned gr = (ngrp + 127) / 128;
+#define AVG3_CASE(T) aggr_finish_avg3_kernel<T><<<gr, 128, 0, c->stream>>>(acc.cells, ngrp, acc.niltrack, (T *) bn->base, (lng *) rn->base, (lng *) cn->base, acc.state)
+	switch (t) {
+	case B200_bte: AVG3_CASE(bte); break;
+	case B200_sht: AVG3_CASE(sht); break;
+	case B200_int: AVG3_CASE(int); break;
+	case B200_lng: AVG3_CASE(lng); break;
+	case B200_hge: AVG3_CASE(hge); break;
+	}
+#undef AVG3_CASE
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaGetLastError(), "avg3 finish") ||
+	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, acc.state, 32, cudaMemcpyDeviceToHost, c->stream), "state read") ||
+	    !stream_sync()) {
+		free3(bn, rn, cn);
+		return B200_FAIL;
+	}
+	if ((unsigned) c->slot_h->v[0] & AGGR_F_OVERFLOW) {
+		free3(bn, rn, cn);
+		set_err("BATgroupavg3: group sum does not fit the device path (2^32 or more rows of hge values)\n");
+		return B200_FAIL;
+	}
+	bn->count = rn->count = cn->count = a.ngrp;
+	agg_props(bn, c->slot_h->v[1]);
+	agg_props(rn, c->slot_h->v[2]);
+	agg_props(cn, c->slot_h->v[2]);
+	*avgp = bn;
+	*remp = rn;
+	*cntp = cn;
+	return B200_SUCCEED;
+}
+
+// gdk_aggr.c:2634-2900
+extern "C" b200_bat *b200_BATgroupavg3combine(const b200_bat *avg, const b200_bat *rem, const b200_bat *cnt, const b200_bat *g,
+					      const b200_bat *e, bool skip_nils)
+{
+	b200_clrerr();
+	AggrSetup a;
+	if (!aggr_init(a, avg, g, e, nullptr))
+		return nullptr;
+	Staged sr, sc;
+	if (rem == nullptr || cnt == nullptr || !stage(rem, sr) || !stage(cnt, sc))
+		return nullptr;
+	if (a.ci.ncand != sr.b->count || a.ci.ncand != sc.b->count) {
+		set_err("input bats not aligned");
+		return nullptr;
+	}
+	if (a.ci.ncand == 0 || a.ngrp == 0)
+		return bat_constant(a.ngrp == 0 ? 0 : a.min, a.b->ttype, nullptr, a.ngrp);
+	const int t = basetype(a.b->ttype);
+	if (int_rank(t) < 0 || t == B200_hge || basetype(sr.b->ttype) != B200_lng || basetype(sc.b->ttype) != B200_lng) {
+		set_err("BATgroupavg3combine: (avg %s, rem %s, cnt %s) is not on the device path\n", atomname(a.b->ttype),
+			atomname(sr.b->ttype), atomname(sc.b->ttype));
+		return nullptr;
+	}
+	Ctx *c = ctx();
+	const unsigned ngrp = (unsigned) a.ngrp;
+	const size_t bytes = (size_t) 6 * ngrp * 8;
+	u64 *cells = (u64 *) dev_alloc(bytes), *state = (u64 *) dev_alloc(64);
+	b200_bat *bn = bat_new(a.min, a.b->ttype, a.ngrp);
+	bool ok = cells && state && bn && cuda_ok(cudaMemsetAsync(cells, 0, bytes, c->stream), "memset cells") &&
+		  cuda_ok(cudaMemsetAsync(state, 0, 64, c->stream), "memset state");
+	if (ok) {
+		const uint64_t n = a.ci.ncand;
+		const oid *gids = a.g && a.g->ttype != B200_void ? (const oid *) a.g->base : nullptr;
+		const bool gconst = a.g == nullptr;
+		const oid gdense = a.g && a.g->ttype == B200_void ? a.g->tseqbase : 0;
+		const unsigned grid = grid_for(n, 256, NSM * 8), gr = (ngrp + 127) / 128;
+#define COMB_CASE(T)                                                                                                         \
+	avg3_combine_kernel<T><<<grid, 256, 0, c->stream>>>((const T *) a.b->base, (const lng *) sr.b->base, (const lng *) sc.b->base, \
+							     gids, a.min, a.max, gdense, gconst, n, skip_nils, cells, ngrp);            \
+	COUNT_LAUNCH();                                                                                                      \
+	avg3_combine_finish_kernel<T><<<gr, 128, 0, c->stream>>>(cells, ngrp, (T *) bn->base, state);                       \
+	COUNT_LAUNCH()
+		switch (t) {
+		case B200_bte: COMB_CASE(bte); break;
+		case B200_sht: COMB_CASE(sht); break;
+		case B200_int: COMB_CASE(int); break;
+		case B200_lng: COMB_CASE(lng); break;
+		}
+#undef COMB_CASE
+		ok = cuda_ok(cudaGetLastError(), "avg3combine") &&
+		     cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 32, cudaMemcpyDeviceToHost, c->stream), "state read") && stream_sync();
+		if (ok && ((unsigned) c->slot_h->v[0] & AGGR_F_OVERFLOW)) {
+			set_err("BATgroupavg3combine: combined count does not fit a lng\n");
+			ok = false;
+		}
+	}
+	if (cells) dev_free(cells);
+	if (state) dev_free(state);
+	if (!ok) {
+		b200_BATfree(bn);
+		return nullptr;
+	}
+	bn->count = a.ngrp;
+	agg_props(bn, c->slot_h->v[1]);
+	ctx()->algo = "avg3combine: cuda 128-bit digit cells";
+	return bn;
+}
+
+// gdk_aggr.c:2987-3046.  Integers: (dbl) sum / n while the sum fits a hge, else floor average plus
+// (dbl) rem / n; floats: exactly rounded sum / n (the reference's running mean differs in the last ulps).
+extern "C" b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, double *avg, uint64_t *vals, int scale)
+{
+	b200_clrerr();
+	AggrSetup a;
+	if (avg == nullptr || !aggr_init(a, b, nullptr, nullptr, s))
+		return B200_FAIL;
+	const int t = basetype(a.b->ttype);
+	if (int_rank(t) < 0 && t != B200_flt && t != B200_dbl) {
+		set_err("average of type %s unsupported.\n", atomname(a.b->ttype));
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	dbl r = NAN;
+	uint64_t n = 0;
+	if (a.ci.ncand > 0) {
+		AggrAccum acc;
+		if (!aggr_accumulate(a, true, 0, acc))
+			return B200_FAIL;
+		dbl *out = (dbl *) dev_alloc(16);
+		if (out == nullptr)
+			return B200_FAIL;
+		lng *cn = (lng *) (out + 1);
+#define CAVG_CASE(T) aggr_finish_avg_kernel<T><<<1, 32, 0, c->stream>>>(acc.cells, 1, false, acc.fexp, 1.0, out, cn, acc.state, true)
+		switch (t) {
+		case B200_bte: CAVG_CASE(bte); break;
+		case B200_sht: CAVG_CASE(sht); break;
+		case B200_int: CAVG_CASE(int); break;
+		case B200_lng: CAVG_CASE(lng); break;
+		case B200_hge: CAVG_CASE(hge); break;
+		case B200_flt: CAVG_CASE(flt); break;
+		case B200_dbl: CAVG_CASE(dbl); break;
+		}
+#undef CAVG_CASE
+		COUNT_LAUNCH();
+		bool ok = cuda_ok(cudaMemcpyAsync(&c->slot_h->v[8], out, 16, cudaMemcpyDeviceToHost, c->stream), "read") && stream_sync();
+		dev_free(out);
+		if (!ok)
+			return B200_FAIL;
+		memcpy(&r, &c->slot_h->v[8], 8);
+		n = c->slot_h->v[9];
+	}
+	if (n == 0)
+		r = NAN;
+	else if (scale != 0)
+		r /= pow(10.0, (double) scale);
+	*avg = r;
+	if (vals)
+		*vals = n;
+	return B200_SUCCEED;
+}

@@ -826,3 +826,161 @@ aggr_exact_check_kernel(AggrIn in, const unsigned *__restrict__ exactlist, int b
 	if (threadIdx.x == 0 && (!i192_fits(run.p.mx, bits) || !i192_fits(run.p.mn, bits)))
 		atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
 }
+
+// ---------------------------------------------------------------- avg3 / avg3combine
+// floor(S / n) and S - floor(S / n) * n for a 192-bit S and 0 < n < 2^32 (long division on
+// 32-bit digits); larger n goes through the 128-bit divide when S fits a hge.
+__device__ static inline bool i192_floordiv(const I192 &S, u64 n, I192 &q, u64 &rem)
+{
+	if (n >= (1ULL << 32)) {
+		if (!i192_fits(S, 128))
+			return false;
+		const hge s = i192_to_hge(S);
+		hge hq = s / (hge) n, hr = s % (hge) n;
+		if (hr < 0) {
+			hq--;
+			hr += (hge) n;
+		}
+		q.w[0] = (u64) hq;
+		q.w[1] = (u64) (hq >> 64);
+		q.w[2] = hq < 0 ? ~0ULL : 0;
+		rem = (u64) hr;
+		return true;
+	}
+	const bool neg = S.neg();
+	const I192 m = neg ? i192_neg(S) : S;
+	uint32_t dig[6];
+	for (int i = 0; i < 3; i++) {
+		dig[2 * i] = (uint32_t) m.w[i];
+		dig[2 * i + 1] = (uint32_t) (m.w[i] >> 32);
+	}
+	rem = 0;
+	for (int i = 5; i >= 0; i--) {
+		u64 cur = (rem << 32) | dig[i];
+		dig[i] = (uint32_t) (cur / n);
+		rem = cur % n;
+	}
+	for (int i = 0; i < 3; i++)
+		q.w[i] = (u64) dig[2 * i] | ((u64) dig[2 * i + 1] << 32);
+	if (neg) {
+		q = i192_neg(q);
+		if (rem != 0) {
+			I192 one = {{1, 0, 0}};
+			q = i192_sub(q, one);
+			rem = n - rem;
+		}
+	}
+	return true;
+}
+
+// BATgroupavg3's result triple (gdk_aggr.c:1996-2290): avg = floor(S/n) rounded half away from the
+// floor as the reference does (rem may become negative), rem, cnt.  state[1] counts nil avgs,
+// state[2] the groups that a nil turned nil altogether (skip_nils == false).
+template <typename T1>
+__global__ void aggr_finish_avg3_kernel(const u64 *__restrict__ cells, unsigned ngrp, bool niltrack, T1 *__restrict__ avgs,
+					lng *__restrict__ rems, lng *__restrict__ cnts, u64 *__restrict__ state)
+{
+	const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= ngrp)
+		return;
+	constexpr int ND = Digits<T1>::ND;
+	const AggrLayout L(ND, false, niltrack);
+	const u64 n = cells[(size_t) L.c_cnt * ngrp + g];
+	if (niltrack && cells[(size_t) L.c_lastnil * ngrp + g] != 0) {
+		avgs[g] = Atom<T1>::nil();
+		rems[g] = Atom<lng>::nil();
+		cnts[g] = Atom<lng>::nil();
+		atomicAdd(&state[1], 1ULL);
+		atomicAdd(&state[2], 1ULL);
+		return;
+	}
+	cnts[g] = (lng) n;
+	if (n == 0) {
+		avgs[g] = Atom<T1>::nil();
+		rems[g] = 0;
+		atomicAdd(&state[1], 1ULL);
+		return;
+	}
+	const I192 S = i192_from_cells(cells + g, ngrp, ND);
+	I192 q;
+	u64 urem;
+	if (!i192_floordiv(S, n, q, urem)) {
+		atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
+		return;
+	}
+	T1 a;
+	if constexpr (sizeof(T1) == 16)
+		a = i192_to_hge(q);
+	else
+		a = (T1) (i64) q.w[0];
+	lng r = (lng) urem;
+	if (r > 0) {
+		if (a < 0 ? 2 * r > (lng) n : 2 * r >= (lng) n) {
+			a++;
+			r -= (lng) n;
+		}
+	}
+	avgs[g] = a;
+	rems[g] = r;
+}
+
+// BATgroupavg3combine (gdk_aggr.c:2634-2900): every input row is a partial (avg, rem, cnt); its
+// total avg*cnt + rem (after undoing the rounding when rem < 0, combine_averages_T :2391-2632)
+// is added to the group's 128-bit sum as four 32-bit digits.  cells: [0,4) digits, 4 cnt, 5 nil flag.
+template <typename T>
+__global__ void avg3_combine_kernel(const T *__restrict__ avg, const lng *__restrict__ rem, const lng *__restrict__ cnt,
+				    const oid *__restrict__ gids, oid gmin, oid gmax, oid gdense, bool gconst, uint64_t n,
+				    bool skip_nils, u64 *__restrict__ cells, unsigned ngrp)
+{
+	for (uint64_t k = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (uint64_t) gridDim.x * blockDim.x) {
+		const oid gid = gids ? gids[k] : (gconst ? gmin : gdense + k);
+		if (gid < gmin || gid > gmax)
+			continue;
+		const unsigned g = (unsigned) (gid - gmin);
+		T a = avg[k];
+		if (Atom<T>::is_nil(a)) {
+			if (!skip_nils)
+				atomicOr((unsigned long long *) &cells[(size_t) 5 * ngrp + g], 1ULL);
+			continue;
+		}
+		lng r = rem[k];
+		const lng c = cnt[k];
+		if (r < 0) {
+			a--;
+			r += c;
+		}
+		i64 d[4];
+		split_hge((hge) a * (hge) c + (hge) r, d);
+#pragma unroll
+		for (int e = 0; e < 4; e++)
+			if (d[e])
+				atomicAdd((unsigned long long *) &cells[(size_t) e * ngrp + g], (unsigned long long) d[e]);
+		atomicAdd((unsigned long long *) &cells[(size_t) 4 * ngrp + g], (unsigned long long) c);
+	}
+}
+
+template <typename T>
+__global__ void avg3_combine_finish_kernel(const u64 *__restrict__ cells, unsigned ngrp, T *__restrict__ out, u64 *__restrict__ state)
+{
+	const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= ngrp)
+		return;
+	const lng n = (lng) cells[(size_t) 4 * ngrp + g];
+	if (cells[(size_t) 5 * ngrp + g] != 0 || n == 0) {
+		out[g] = Atom<T>::nil();
+		atomicAdd(&state[1], 1ULL);
+		return;
+	}
+	const I192 S = i192_from_cells(cells + g, ngrp, 4);
+	I192 q;
+	u64 urem;
+	if (n < 0 || !i192_floordiv(S, (u64) n, q, urem)) {
+		atomicOr((unsigned *) &state[0], AGGR_F_OVERFLOW);
+		return;
+	}
+	T a = (T) (i64) q.w[0];
+	const lng r = (lng) urem;
+	if (r > 0 && (a < 0 ? 2 * r > n : 2 * r >= n))
+		a++;
+	out[g] = a;
+}

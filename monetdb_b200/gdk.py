@@ -420,6 +420,9 @@ for _n in ("sum", "count", "min", "max"):
         _sig(f"b200_BATgroup{_n}", _P, _P, _P, _P, _P, C.c_int, C.c_bool)
 _sig("b200_BATgroupavg", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_int, C.c_bool, C.c_int)
 _sig("b200_BATsum", C.c_int, C.c_void_p, C.c_int, _P, _P, C.c_bool, C.c_bool)
+_sig("b200_BATgroupavg3", C.c_int, _PP, _PP, _PP, _P, _P, _P, _P, C.c_bool)
+_sig("b200_BATgroupavg3combine", _P, _P, _P, _P, _P, _P, C.c_bool)
+_sig("b200_BATcalcavg", C.c_int, _P, _P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int)
 
 
 def BATgroupsum(b, g, e, s, tp, skip_nils=True) -> BAT:
@@ -445,6 +448,26 @@ def BATgroupavg(b, g, e, s, tp=TYPE.dbl, skip_nils=True, scale=0, want_counts=Tr
     if rc != 1:
         _fail("BATgroupavg")
     return BAT(pa), (BAT(pc) if want_counts else None)
+
+
+def BATgroupavg3(b, g, e, s, skip_nils=True):
+    """(avg, rem, cnt) triples, gdk_aggr.c:1996"""
+    pa, pr, pc = _P(), _P(), _P()
+    if lib.b200_BATgroupavg3(C.byref(pa), C.byref(pr), C.byref(pc), b._p, _ptr(g), _ptr(e), _ptr(s), skip_nils) != 1:
+        _fail("BATgroupavg3")
+    return BAT(pa), BAT(pr), BAT(pc)
+
+
+def BATgroupavg3combine(avg, rem, cnt, g, e, skip_nils=True) -> BAT:
+    return BAT(lib.b200_BATgroupavg3combine(avg._p, rem._p, cnt._p, _ptr(g), _ptr(e), skip_nils))
+
+
+def BATcalcavg(b, s=None, scale=0):
+    """(avg as float, number of non-nil values), gdk_aggr.c:2987"""
+    avg, n = C.c_double(), C.c_uint64()
+    if lib.b200_BATcalcavg(b._p, _ptr(s), C.byref(avg), C.byref(n), scale) != 1:
+        _fail("BATcalcavg")
+    return avg.value, n.value
 
 
 def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if_empty: bool = True) -> np.ndarray:

@@ -106,6 +106,9 @@ def _load(nthreads: int = 0):
         "BATgroupmax": (P, [P, P, P, P, C.c_int, B]),
         "BATgroupavg": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, C.c_int, B, C.c_int]),
         "BATsum": (C.c_int, [V, C.c_int, P, P, B, B]),
+        "BATgroupavg3": (C.c_int, [C.POINTER(P), C.POINTER(P), C.POINTER(P), P, P, P, P, B]),
+        "BATgroupavg3combine": (P, [P, P, P, P, P, B]),
+        "BATcalcavg": (C.c_int, [P, P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
         "BATjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
         "BAThash": (C.c_int, [P]),
         "BATconvert": (P, [P, P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8]),
@@ -373,6 +376,34 @@ def BATgroupavg(b, g, e, s, tp=T.dbl, skip_nils=True, scale=0, want_counts=True)
         clrerr()
         raise RefError(msg or "BATgroupavg failed")
     return RBAT(pa.value), (RBAT(pc.value) if want_counts else None)
+
+
+def BATgroupavg3(b, g, e, s, skip_nils=True):
+    pa, pr, pc = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    rc = _bat.BATgroupavg3(C.byref(pa), C.byref(pr), C.byref(pc), b.p, _p(g), _p(e), _p(s), skip_nils)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATgroupavg3 failed")
+    return RBAT(pa.value), RBAT(pr.value), RBAT(pc.value)
+
+
+def BATgroupavg3combine(avg, rem, cnt, g, e, skip_nils=True):
+    r = _bat.BATgroupavg3combine(avg.p, rem.p, cnt.p, _p(g), _p(e), skip_nils)
+    if not r:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATgroupavg3combine failed")
+    return RBAT(r)
+
+
+def BATcalcavg(b, s=None, scale=0):
+    avg, n = C.c_double(), C.c_uint64()
+    if _bat.BATcalcavg(b.p, _p(s), C.byref(avg), C.byref(n), scale) != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATcalcavg failed")
+    return avg.value, n.value
 
 
 def BATsum(tp, b, s=None, skip_nils=True, nil_if_empty=True):

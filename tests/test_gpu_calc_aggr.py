@@ -234,3 +234,69 @@ def test_groupsum_avg_count(gdk, ref, ngrp, t1):
     # without extents: the group range comes from scanning g
     assert_same(gdk.BATgroupsum(b, g, None, None, T.hge if t1 in INT_TYPES else T.dbl, True),
                 ref.BATgroupsum(rb, rg, None, None, T.hge if t1 in INT_TYPES else T.dbl, True)) if t1 in INT_TYPES else None
+
+
+@pytest.mark.parametrize("ngrp", [1, 4, 9, 500, 7000])
+@pytest.mark.parametrize("t1", [T.bte, T.sht, T.int, T.lng, T.hge])
+def test_groupavg3_and_combine(gdk, ref, ngrp, t1):
+    """mergetable's exact integer average: phase 1 triples per slice (BATgroupavg3, gdk_aggr.c:1996),
+    phase 2 recombination over the concatenated partials (BATgroupavg3combine, :2634)"""
+    rng = np.random.default_rng(31 * ngrp + t1)
+    n = 60013
+    # lng: the reference's combine_averages_lng multiplies avg * cnt in a lng before widening
+    # (gdk_aggr.c:2531), so keep |avg| * cnt below 2^63 where both sides are exact
+    big = {T.bte: 127, T.sht: 32767, T.int: 2**31 - 1, T.lng: 2**44, T.hge: 1 << 100}[t1]
+    e, re_ = gdk.BATdense(0, 0, ngrp), ref.dense(0, 0, ngrp)
+    parts = []
+    for slice_no, (lo, hi, nilfrac) in enumerate([(-big, big, 0.05), (-1000 if t1 != T.bte else -100, 0, 0.0),
+                                                  (0, big, 0.3)]):
+        a = random_col(rng, t1, n, nilfrac=nilfrac, lo=lo, hi=hi)
+        gids = rng.integers(0, ngrp, n, dtype=np.uint64)
+        if ngrp > 4:
+            gids[gids == 3] = 2          # one group stays empty
+        b, rb = both(gdk, ref, a, t1, hseq=5)
+        g, rg = both(gdk, ref, gids, T.oid, hseq=5)
+        for skip in (True, False):
+            o = gdk.BATgroupavg3(b, g, e, None, skip)
+            r = ref.BATgroupavg3(rb, rg, re_, None, skip)
+            for x, y in zip(o, r):
+                assert_same(x, y)
+        parts.append((gdk.BATgroupavg3(b, g, e, None, True), ref.BATgroupavg3(rb, rg, re_, None, True)))
+    if t1 == T.hge:
+        return                            # the recombination of hge partials is not on the device path
+    # phase 2: concatenate the partial triples, group id of partial row i of every slice = i
+    cat = [np.concatenate([p[1][k].numpy() for p in parts]) for k in range(3)]
+    pg = np.concatenate([np.arange(ngrp, dtype=np.uint64) for _ in parts])
+    if ngrp > 4:                          # empty group: avg nil, cnt 0 in every slice
+        assert all(p[1][2].numpy()[3] == 0 for p in parts)
+    av, rav = both(gdk, ref, cat[0], t1)
+    rm, rrm = both(gdk, ref, cat[1], T.lng)
+    ct, rct = both(gdk, ref, cat[2], T.lng)
+    g2, rg2 = both(gdk, ref, pg, T.oid)
+    for skip in (True, False):
+        assert_same(gdk.BATgroupavg3combine(av, rm, ct, g2, e, skip), ref.BATgroupavg3combine(rav, rrm, rct, rg2, re_, skip))
+
+
+@pytest.mark.parametrize("t1", ALL_TYPES)
+def test_calcavg(gdk, ref, t1):
+    rng = np.random.default_rng(77 + t1)
+    for n, nilfrac in ((0, 0), (1, 0), (5, 1.0), (100003, 0.1), (1 << 20, 0.0)):
+        a = random_col(rng, t1, n, nilfrac=nilfrac)
+        b, rb = both(gdk, ref, a, t1, hseq=3)
+        for scale in (0, 2):
+            o, r = gdk.BATcalcavg(b, None, scale), ref.BATcalcavg(rb, None, scale)
+            assert o[1] == r[1]
+            if t1 in INT_TYPES:
+                assert same_bits(np.float64(o[0]), np.float64(r[0])), (n, o, r)
+            else:
+                assert (np.isnan(o[0]) and np.isnan(r[0])) or abs(o[0] - r[0]) <= 1e-9 * 1000, (n, o, r)
+    # the lng sum overflows a lng but not a hge: still (dbl) sum / n
+    a = np.full(1000, 2**63 - 1, dtype=np.int64)
+    b, rb = both(gdk, ref, a, T.lng)
+    assert gdk.BATcalcavg(b) == ref.BATcalcavg(rb)
+    # candidates
+    a = random_col(rng, T.int, 50000, nilfrac=0.05)
+    b, rb = both(gdk, ref, a, T.int, hseq=10)
+    cand = np.sort(rng.choice(50000, 7000, replace=False)).astype(np.uint64) + 10
+    s, rs = both(gdk, ref, cand, T.oid, sorted=True, key=True)
+    assert gdk.BATcalcavg(b, s) == ref.BATcalcavg(rb, rs)
