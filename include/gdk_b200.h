@@ -101,6 +101,8 @@ void b200_stage_cache(int on);		/* keep staged copies of HOST heaps (device = -1
 void b200_stage_cache_clear(void);	/* drop every staged copy (call when a host heap is written or freed) */
 b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc); /* gdk_cand.c:1296 */
 b200_bat *b200_BATmaskedcands_fromhost(uint64_t hseq, uint64_t nrows, const uint32_t *words, bool selected); /* gdk_cand.c:1366 */
+b200_bat *b200_BATunmask(const b200_bat *b);	/* gdk_cand.c:1464: mask / negative candidates -> dense or oid[] */
+b200_return b200_BATextend(b200_bat *b, uint64_t newcap);	/* gdk_bat.c:529 / HEAPextend gdk_heap.c:246 */
 void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil);
 int  b200_BATtohost(const b200_bat *b, void *dst);	/* logical tail -> host (void/cands materialised as oids) */
 void b200_BATfree(b200_bat *b);				/* BBPreclaim */

@@ -104,6 +104,8 @@ struct AggrAccum {
 	u64 *state = nullptr;		/* device: [0] flags [1] nil groups [2] exact-check groups [3] nil rows seen */
 	int nd = 0, ncell = 0, fexp = 0;
 	bool check = false, niltrack = false;
+	int pending_bits = 0;		/* fast form launched without waiting: the caller checks state[5..7] against this width */
+	bool pending_narrow = false;
 	AggrIn in;
 	~AggrAccum() { if (cells) dev_free(cells); if (state) dev_free(state); }
 };
@@ -112,10 +114,13 @@ struct AggrAccum {
 // result; it is false when an overflow check was asked for and rows x max|x| does not fit
 // check_bits, in which case acc has been released for the exact form.
 template <typename T1>
-static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &done)
+static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &done, bool allow_narrow = true, bool defer = false)
 {
 	Ctx *c = ctx();
 	constexpr int ND = Digits<T1>::ND;
+	/* hge values that all fit 64 bits take the two-word accumulators; the host learns whether they
+	 * did from the readback it needs anyway for the overflow bound */
+	const bool narrow = sizeof(T1) == 16 && check_bits != 0 && allow_narrow;
 	const unsigned ngrp = (unsigned) a.ngrp;
 	acc.check = false;
 	const AggrLayout L(ND, false, false);
@@ -136,24 +141,43 @@ static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &
 	in.gmax = a.max;
 	in.gconst = a.g == nullptr;
 	in.gids = a.g ? (const oid *) a.g->base : nullptr;
+	Shadow gsh;
+	if (a.g && ((uintptr_t) in.vals & 15) == 0 && shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh))
+		in.g8 = (const unsigned char *) gsh.p;
 	in.nonil = a.b->tnonil;
 	in.skip_nils = true;
 	const unsigned grid = grid_for(in.n, AGGR_THREADS * 8, NSM * 8);
 	{
-		KTimer kt("aggr", in.n * (sizeof(T1) + (in.gids ? 8 : 0)));
+		KTimer kt("aggr", in.n * (sizeof(T1) + (in.gids ? 8 : 0)));	/* algorithmic: the API's 8-byte ids */
 		const T1 *vals = (const T1 *) in.vals;
 		u64 *mx = acc.state + 5;
-#define FAST_CASE(NG)                                                                                                         \
-	do {                                                                                                                  \
-		if (in.gids)                                                                                                  \
-			aggr_reg_fast_kernel<T1, NG, true><<<grid, AGGR_THREADS, 0, c->stream>>>(vals, in.gids, in.gmin, in.gmax - in.gmin, in.n, in.nonil, acc.cells, ngrp, mx); \
-		else                                                                                                          \
-			aggr_reg_fast_kernel<T1, NG, false><<<grid, AGGR_THREADS, 0, c->stream>>>(vals, nullptr, in.gmin, in.gmax - in.gmin, in.n, in.nonil, acc.cells, ngrp, mx); \
+#define FAST_LAUNCH(NG, HG, NRW, GT, GP) \
+	aggr_reg_fast_kernel<T1, NG, HG, NRW, GT><<<grid, AGGR_THREADS, 0, c->stream>>>(vals, GP, in.gmin, in.gmax - in.gmin, in.n, in.nonil, acc.cells, ngrp, mx)
+#define FAST_GID(NG, NRW)                                                                    \
+	do {                                                                                 \
+		if (in.g8)                                                                   \
+			FAST_LAUNCH(NG, true, NRW, unsigned char, in.g8);                    \
+		else if (in.gids)                                                            \
+			FAST_LAUNCH(NG, true, NRW, oid, in.gids);                            \
+		else                                                                         \
+			FAST_LAUNCH(NG, false, NRW, oid, (const oid *) nullptr);             \
+	} while (0)
+#define FAST_CASE(NG)                                                                        \
+	do {                                                                                 \
+		if constexpr (sizeof(T1) == 16) {                                            \
+			if (narrow) {                                                        \
+				FAST_GID(NG, true);                                          \
+				break;                                                       \
+			}                                                                    \
+		}                                                                            \
+		FAST_GID(NG, false);                                                         \
 	} while (0)
 		if (ngrp <= 1) FAST_CASE(1);
 		else if (ngrp <= 2) FAST_CASE(2);
 		else if (ngrp <= 4) FAST_CASE(4);
 		else FAST_CASE(8);
+#undef FAST_GID
+#undef FAST_LAUNCH
 #undef FAST_CASE
 	}
 	COUNT_LAUNCH();
@@ -161,9 +185,21 @@ static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &
 	if (!cuda_ok(cudaGetLastError(), "aggr launch"))
 		return false;
 	done = true;
+	if (check_bits != 0 && defer) {
+		acc.pending_bits = check_bits;
+		acc.pending_narrow = narrow;
+		return true;
+	}
 	if (check_bits != 0) {
-		if (!cuda_ok(cudaMemcpyAsync(&c->slot_h->v[5], acc.state + 5, 16, cudaMemcpyDeviceToHost, c->stream), "maxabs") || !stream_sync())
+		if (!cuda_ok(cudaMemcpyAsync(&c->slot_h->v[5], acc.state + 5, 24, cudaMemcpyDeviceToHost, c->stream), "maxabs") || !stream_sync())
 			return false;
+		if (narrow && c->slot_h->v[7] != 0) {
+			/* a value needs more than 64 bits: run the three-word form instead */
+			dev_free(acc.cells);
+			dev_free(acc.state);
+			acc.cells = acc.state = nullptr;
+			return aggr_fast<T1>(a, check_bits, acc, done, false);
+		}
 		const uhge mx = ((uhge) c->slot_h->v[6] << 64) | c->slot_h->v[5];
 		const uhge lim = ((uhge) 1 << (check_bits - 1)) - 1;
 		if (mx != 0 && (uhge) in.n > lim / mx) {
@@ -177,7 +213,7 @@ static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &
 }
 
 template <typename T1>
-static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_bits, bool need_values, AggrAccum &acc)
+static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_bits, bool defer, AggrAccum &acc)
 {
 	Ctx *c = ctx();
 	constexpr int ND = Digits<T1>::ND;
@@ -191,7 +227,7 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_
 	if constexpr (!Atom<T1>::is_float)
 		fast = !acc.niltrack && ngrp <= 8 && a.ci.dense && (a.g == nullptr || a.g->ttype != B200_void);
 	if (fast) {
-		if (!aggr_fast<T1>(a, check_bits, acc, fast))
+		if (!aggr_fast<T1>(a, check_bits, acc, fast, true, defer))
 			return false;
 		if (fast)
 			return true;
@@ -229,11 +265,13 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_
 		in.gdense = a.g->tseqbase;
 	} else {
 		in.gids = (const oid *) a.g->base;
+		Shadow gsh;
+		if (shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh))
+			in.g8 = (const unsigned char *) gsh.p;
 	}
 	in.nonil = a.b->tnonil;
 	in.skip_nils = skip_nils;
 	in.check = check;
-	(void) need_values;
 	unsigned *flags = (unsigned *) acc.state;
 	if constexpr (Atom<T1>::is_float) {
 		int *fe = (int *) (acc.state + 4);
@@ -277,20 +315,20 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_
 	return cuda_ok(cudaGetLastError(), "aggr launch");
 }
 
-static bool aggr_accumulate(const AggrSetup &a, bool skip_nils, int check_bits, AggrAccum &acc)
+static bool aggr_accumulate(const AggrSetup &a, bool skip_nils, int check_bits, AggrAccum &acc, bool defer = false)
 {
 	if (a.ci.ncand >= (1ULL << 32)) {
 		set_err("b200: aggregates over 2^32 or more rows in one call are not supported\n");
 		return false;
 	}
 	switch (basetype(a.b->ttype)) {
-	case B200_bte: return aggr_accumulate_typed<bte>(a, skip_nils, check_bits, true, acc);
-	case B200_sht: return aggr_accumulate_typed<sht>(a, skip_nils, check_bits, true, acc);
-	case B200_int: return aggr_accumulate_typed<int>(a, skip_nils, check_bits, true, acc);
-	case B200_lng: return aggr_accumulate_typed<lng>(a, skip_nils, check_bits, true, acc);
-	case B200_hge: return aggr_accumulate_typed<hge>(a, skip_nils, check_bits, true, acc);
-	case B200_flt: return aggr_accumulate_typed<flt>(a, skip_nils, false, true, acc);
-	case B200_dbl: return aggr_accumulate_typed<dbl>(a, skip_nils, false, true, acc);
+	case B200_bte: return aggr_accumulate_typed<bte>(a, skip_nils, check_bits, defer, acc);
+	case B200_sht: return aggr_accumulate_typed<sht>(a, skip_nils, check_bits, defer, acc);
+	case B200_int: return aggr_accumulate_typed<int>(a, skip_nils, check_bits, defer, acc);
+	case B200_lng: return aggr_accumulate_typed<lng>(a, skip_nils, check_bits, defer, acc);
+	case B200_hge: return aggr_accumulate_typed<hge>(a, skip_nils, check_bits, defer, acc);
+	case B200_flt: return aggr_accumulate_typed<flt>(a, skip_nils, 0, false, acc);
+	case B200_dbl: return aggr_accumulate_typed<dbl>(a, skip_nils, 0, false, acc);
 	}
 	set_err("b200: aggregate over type %s is not on the device path\n", atomname(a.b->ttype));
 	return false;
@@ -320,7 +358,7 @@ static void launch_finish_sum(const AggrAccum &acc, unsigned ngrp, bool nil_if_e
 
 // dosum (gdk_aggr.c:708-896): results (device, ngrp x tp2) must be allocated; returns
 // the number of nil results, or BUN_NONE with the error set
-static uint64_t do_sum(const AggrSetup &a, int tp2, bool skip_nils, bool nil_if_empty, void *results, const char *func)
+static uint64_t do_sum(const AggrSetup &a, int tp2, bool skip_nils, bool nil_if_empty, void *results, const char *func, bool defer = true)
 {
 	Ctx *c = ctx();
 	const int t1 = basetype(a.b->ttype), t2 = basetype(tp2);
@@ -343,7 +381,7 @@ static uint64_t do_sum(const AggrSetup &a, int tp2, bool skip_nils, bool nil_if_
 		return B200_BUN_NONE;
 	}
 	AggrAccum acc;
-	if (!aggr_accumulate(a, skip_nils, check ? atomsize(t2) * 8 : 0, acc))
+	if (!aggr_accumulate(a, skip_nils, check ? atomsize(t2) * 8 : 0, acc, defer))
 		return B200_BUN_NONE;
 	check = acc.check;		/* the fast form proves "no overflow possible" with a bound instead */
 	const unsigned ngrp = (unsigned) a.ngrp;
@@ -364,9 +402,20 @@ static uint64_t do_sum(const AggrSetup &a, int tp2, bool skip_nils, bool nil_if_
 	}
 	uint64_t ret = B200_BUN_NONE;
 	if (!cuda_ok(cudaGetLastError(), "finish launch") ||
-	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, acc.state, 32, cudaMemcpyDeviceToHost, c->stream), "state read") ||
+	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, acc.state, 64, cudaMemcpyDeviceToHost, c->stream), "state read") ||
 	    !stream_sync())
 		goto done;
+	if (acc.pending_bits != 0) {
+		/* the fast form ran unchecked: its rows x max|x| bound (and, for the two-word hge form,
+		 * "every value fits 64 bits") is verified here, after the one sync this call needs anyway */
+		const uhge mx = ((uhge) c->slot_h->v[6] << 64) | c->slot_h->v[5];
+		const uhge lim = ((uhge) 1 << (acc.pending_bits - 1)) - 1;
+		if ((acc.pending_narrow && c->slot_h->v[7] != 0) || (mx != 0 && (uhge) acc.in.n > lim / mx)) {
+			if (exactlist)
+				dev_free(exactlist);
+			return do_sum(a, tp2, skip_nils, nil_if_empty, results, func, false);
+		}
+	}
 	if (((unsigned) c->slot_h->v[0] & (AGGR_F_SPECIAL | AGGR_F_OVERFLOW)) == 0 && c->slot_h->v[2] != 0) {
 		/* some group's positive or negative part alone exceeds the result type:
 		 * decide exactly whether the running sum overflows */
@@ -533,9 +582,9 @@ extern "C" b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b
 
 // ---------------------------------------------------------------- count
 // histogram of group ids when the values need not be looked at (gdk_aggr.c:3118-3132)
-template <bool USE_SHM>
+template <bool USE_SHM, typename GT = oid>
 __global__ void __launch_bounds__(256)
-gid_count_kernel(const oid *__restrict__ gids, uint64_t n, oid gmin, oid gmax, unsigned ngrp, u64 *__restrict__ cnts)
+gid_count_kernel(const GT *__restrict__ gids, uint64_t n, oid gmin, oid gmax, unsigned ngrp, u64 *__restrict__ cnts)
 {
 	extern __shared__ u64 sh_cnt[];
 	const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
@@ -547,7 +596,7 @@ gid_count_kernel(const oid *__restrict__ gids, uint64_t n, oid gmin, oid gmax, u
 #pragma unroll
 			for (int u = 0; u < U; u++) {
 				const uint64_t k = k0 + u * stride;
-				g[u] = k < n ? __ldcs(gids + k) : OID_NIL;
+				g[u] = k < n ? (oid) __ldcs(gids + k) : OID_NIL;
 			}
 #pragma unroll
 			for (int u = 0; u < U; u++) {
@@ -628,7 +677,10 @@ extern "C" b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, co
 			return nullptr;
 		}
 		const unsigned grid = grid_for(a.ci.ncand, 256 * 8, NSM * 8);
-		if ((size_t) ngrp * 8 <= 48 * 1024)
+		Shadow gsh;
+		if (shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh) && (size_t) ngrp * 8 <= 48 * 1024)
+			gid_count_kernel<true, unsigned char><<<grid, 256, ngrp > 8 ? (size_t) ngrp * 8 : 0, c->stream>>>((const unsigned char *) gsh.p, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
+		else if ((size_t) ngrp * 8 <= 48 * 1024)
 			gid_count_kernel<true><<<grid, 256, ngrp > 8 ? (size_t) ngrp * 8 : 0, c->stream>>>((const oid *) a.g->base, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
 		else
 			gid_count_kernel<false><<<grid, 256, 0, c->stream>>>((const oid *) a.g->base, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);

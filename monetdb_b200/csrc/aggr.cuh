@@ -94,6 +94,7 @@ struct AggrIn {
 	const oid *cand;	/* candidate oids or NULL */
 	oid hseq;		/* subtracted from candidate oids */
 	const oid *gids;	/* group id per candidate row, or NULL */
+	const unsigned char *g8;	/* one-byte twin of gids (SHADOW_GID8), preferred when present */
 	oid gmin, gmax;		/* valid group-id range; cell index = gid - gmin */
 	oid gdense;		/* gids == NULL: gid of row k = gdense + k (ngrp == 1: gmin) */
 	bool gconst;		/* gids == NULL and every row is in group gmin */
@@ -125,7 +126,7 @@ __device__ __forceinline__ bool aggr_fetch(const AggrIn &in, uint64_t k, T1 &x, 
 {
 	const T1 *vals = (const T1 *) in.vals;
 	x = in.cand ? vals[__ldcs(in.cand + k) - in.hseq] : ld_stream(vals + k);
-	gid = in.gids ? __ldcs(in.gids + k) : (in.gconst ? in.gmin : in.gdense + k);
+	gid = in.g8 ? (oid) in.g8[k] : in.gids ? __ldcs(in.gids + k) : (in.gconst ? in.gmin : in.gdense + k);
 	return gid >= in.gmin && gid <= in.gmax;
 }
 
@@ -230,14 +231,19 @@ template <typename T1> struct WideAcc {
 	static constexpr int NW = sizeof(T1) <= 4 ? 1 : sizeof(T1) == 8 ? 2 : 3;	/* 64-bit words */
 };
 
-template <typename T1, int NG, bool HASGID>
+// NARROW (hge only): every value is expected to fit 64 bits (DECIMAL(38) columns holding ordinary
+// magnitudes): the accumulators are two words like the lng form's, and a value that does not fit
+// raises maxabs_out[2] so that the host reruns the three-word form.
+template <typename T1, int NG, bool HASGID, bool NARROW = false, typename GT = oid>
 __global__ void __launch_bounds__(AGGR_THREADS)
-aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, oid gmin, oid gspan /* gmax - gmin */,
+aggr_reg_fast_kernel(const T1 *__restrict__ vals, const GT *__restrict__ gids, oid gmin, oid gspan /* gmax - gmin */,
 		     uint64_t n, bool nonil, u64 *__restrict__ cells, unsigned ngrp, u64 *__restrict__ maxabs_out)
 {
-	constexpr int NW = WideAcc<T1>::NW;
+	static_assert(!NARROW || sizeof(T1) == 16, "NARROW is the hge form");
+	constexpr int NW = NARROW ? 2 : WideAcc<T1>::NW;
 	constexpr int ND = Digits<T1>::ND;
-	typedef typename std::conditional<sizeof(T1) == 16, uhge, u64>::type UA;
+	typedef typename std::conditional<sizeof(T1) == 16 && !NARROW, uhge, u64>::type UA;
+	bool anywide = false;
 	u64 acc[NG][NW];
 	unsigned cnt[NG];
 #pragma unroll
@@ -248,20 +254,56 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, 
 			acc[g][w] = 0;
 	}
 	UA maxabs = 0;
-	constexpr int U = sizeof(T1) == 16 ? 4 : 8;
+	/* one-byte ids: a thread takes 8 CONSECUTIVE rows, their ids are one 8-byte load and their
+	 * values 16-byte loads (vals must be 16-byte aligned; byte-wide LDGs measured far slower) */
+	constexpr bool G8 = HASGID && sizeof(GT) == 1;
+	constexpr int U = G8 ? 8 : (sizeof(T1) == 16 && !NARROW ? 4 : 8);
 	const uint64_t stride = (uint64_t) gridDim.x * AGGR_THREADS;
-	for (uint64_t k0 = (uint64_t) blockIdx.x * AGGR_THREADS + threadIdx.x; k0 < n; k0 += stride * U) {
+	const uint64_t kstep = G8 ? stride : stride * U;
+	const uint64_t kend = G8 ? (n + 7) / 8 : n;
+	for (uint64_t k0 = (uint64_t) blockIdx.x * AGGR_THREADS + threadIdx.x; k0 < kend; k0 += kstep) {
 		T1 x[U];
 		oid gid[U];
+		if constexpr (G8) {
+			const uint64_t r0 = k0 * 8;
+			if (r0 + 8 <= n) {
+				union {
+					T1 t[8];
+					uint4 q[sizeof(T1) >= 2 ? sizeof(T1) / 2 : 1];
+					u64 w;
+				} v;
+				if constexpr (sizeof(T1) == 1) {
+					v.w = __ldcs(reinterpret_cast<const u64 *>(vals + r0));
+				} else {
 #pragma unroll
-		for (int u = 0; u < U; u++) {
-			const uint64_t k = k0 + u * stride;
-			if (k < n) {
-				x[u] = ld_stream(vals + k);
-				gid[u] = HASGID ? __ldcs(gids + k) : gmin;
+					for (int i = 0; i < (int) sizeof(T1) / 2; i++)
+						v.q[i] = __ldg(reinterpret_cast<const uint4 *>(vals + r0) + i);
+				}
+				const u64 gw = __ldcs(reinterpret_cast<const u64 *>(gids + r0));
+#pragma unroll
+				for (int u = 0; u < 8; u++) {
+					x[u] = v.t[u];
+					gid[u] = (gw >> (8 * u)) & 0xff;
+				}
 			} else {
-				x[u] = Atom<T1>::nil();
-				gid[u] = gmin;
+#pragma unroll
+				for (int u = 0; u < 8; u++) {
+					const bool in = r0 + u < n;
+					x[u] = in ? vals[r0 + u] : Atom<T1>::nil();
+					gid[u] = in ? (oid) gids[r0 + u] : gmin;
+				}
+			}
+		} else {
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const uint64_t k = k0 + u * stride;
+				if (k < n) {
+					x[u] = ld_stream(vals + k);
+					gid[u] = HASGID ? (oid) __ldcs(gids + k) : gmin;
+				} else {
+					x[u] = Atom<T1>::nil();
+					gid[u] = gmin;
+				}
 			}
 		}
 #pragma unroll
@@ -269,12 +311,22 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, 
 			const u64 go = gid[u] - gmin;
 			const bool ok = !Atom<T1>::is_nil(x[u]) && go <= gspan;		/* a tail slot holds nil */
 			const unsigned gi = ok ? (unsigned) go : 0xffffffffu;
-			const UA ax = x[u] < 0 ? (UA) 0 - (UA) x[u] : (UA) x[u];
+			UA ax;
+			if constexpr (NARROW) {
+				const i64 lo = (i64) (u64) x[u];
+				anywide |= ok && (i64) ((uhge) x[u] >> 64) != (lo >> 63);
+				ax = lo < 0 ? (u64) 0 - (u64) lo : (u64) lo;
+			} else {
+				ax = x[u] < 0 ? (UA) 0 - (UA) x[u] : (UA) x[u];
+			}
 			if (ok && ax > maxabs)
 				maxabs = ax;
 			/* sign-extended words of x */
 			u64 xw[NW];
-			if constexpr (sizeof(T1) == 16) {
+			if constexpr (NARROW) {
+				xw[0] = (u64) x[u];
+				xw[1] = (u64) ((i64) xw[0] >> 63);
+			} else if constexpr (sizeof(T1) == 16) {
 				xw[0] = (u64) x[u];
 				xw[1] = (u64) ((uhge) x[u] >> 64);
 				xw[2] = (u64) ((i64) xw[1] >> 63);
@@ -319,10 +371,11 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, 
 			d[0] = (i64) (uint32_t) acc[g][0];
 			d[1] = (i64) ((acc[g][0] >> 32) | (acc[g][1] << 32));
 		} else {
+			const u64 top = NARROW ? (u64) ((i64) acc[g][1] >> 63) : acc[g][NW - 1];
 			d[0] = (i64) (uint32_t) acc[g][0];
 			d[1] = (i64) (acc[g][0] >> 32);
 			d[2] = (i64) (uint32_t) acc[g][1];
-			d[3] = (i64) ((acc[g][1] >> 32) | (acc[g][2] << 32));
+			d[3] = (i64) ((acc[g][1] >> 32) | (top << 32));
 		}
 #pragma unroll
 		for (int e = 0; e <= ND; e++) {
@@ -335,7 +388,9 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const oid *__restrict__ gids, 
 		}
 	}
 	{
-		u64 mlo = (u64) maxabs, mhi = sizeof(T1) == 16 ? (u64) ((uhge) maxabs >> 64) : 0;
+		u64 mlo = (u64) maxabs, mhi = sizeof(UA) == 16 ? (u64) ((uhge) maxabs >> 64) : 0;
+		if (NARROW && anywide)
+			maxabs_out[2] = 1;
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) {
 			const u64 olo = __shfl_down_sync(0xffffffffu, mlo, o), ohi = __shfl_down_sync(0xffffffffu, mhi, o);

@@ -246,43 +246,49 @@ __device__ __forceinline__ void calc_finish(unsigned long long fail, unsigned ni
 
 // dense / constant operands, aligned: K consecutive rows per thread
 template <int OP, typename T1, typename T2, typename T3>
-__global__ void __launch_bounds__(256) calc_vec_kernel(CalcArgs<T1, T2, T3> a)
+__global__ void __launch_bounds__(256, 4) calc_vec_kernel(CalcArgs<T1, T2, T3> a)
 {
 	constexpr int K = calc_k<T3>();
+	/* results of up to 8 bytes: four independent 16-byte chunks per operand in flight per thread
+	 * (one chunk leaves too few bytes in flight to saturate HBM); hge results already stream 32 bytes */
+	constexpr int UNR = sizeof(T3) <= 8 && sizeof(T1) <= 8 && sizeof(T2) <= 8 ? 4 : 1;
 	const uint64_t nchunks = a.n / K;
+	const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
 	unsigned long long fail = ~0ULL;
 	unsigned nils = 0;
-	for (uint64_t c = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += (uint64_t) gridDim.x * blockDim.x) {
-		const uint64_t k0 = c * K;
-		T1 x[K];
-		T2 y[K];
-		T3 z[K];
-		if (a.incr1)
-			VecIO<T1, K>::load(a.lft + k0, x);
-		else {
+	for (uint64_t c0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; c0 < nchunks; c0 += stride * UNR) {
+		T1 x[UNR][K];
+		T2 y[UNR][K];
 #pragma unroll
-			for (int e = 0; e < K; e++)
-				x[e] = a.cst1;
-		}
-		if (a.incr2)
-			VecIO<T2, K>::load(a.rgt + k0, y);
-		else {
-#pragma unroll
-			for (int e = 0; e < K; e++)
-				y[e] = a.cst2;
-		}
-#pragma unroll
-		for (int e = 0; e < K; e++) {
-			if (Atom<T1>::is_nil(x[e]) || Atom<T2>::is_nil(y[e])) {
-				z[e] = Atom<T3>::nil();
-				nils++;
-			} else {
-				z[e] = Atom<T3>::nil();
-				if (Calc<OP, T1, T2, T3>::apply(x[e], y[e], z[e]) != ST_OK && fail == ~0ULL)
-					fail = k0 + e;
+		for (int u = 0; u < UNR; u++) {
+			const uint64_t c = c0 + u * stride;
+			if (c < nchunks) {
+				if (a.incr1)
+					VecIO<T1, K>::load(a.lft + c * K, x[u]);
+				if (a.incr2)
+					VecIO<T2, K>::load(a.rgt + c * K, y[u]);
 			}
 		}
-		VecIO<T3, K>::store(a.dst + k0, z);
+#pragma unroll
+		for (int u = 0; u < UNR; u++) {
+			const uint64_t c = c0 + u * stride;
+			if (c >= nchunks)
+				break;
+			const uint64_t k0 = c * K;
+			T3 z[K];
+#pragma unroll
+			for (int e = 0; e < K; e++) {
+				const T1 xv = a.incr1 ? x[u][e] : a.cst1;
+				const T2 yv = a.incr2 ? y[u][e] : a.cst2;
+				z[e] = Atom<T3>::nil();
+				if (Atom<T1>::is_nil(xv) || Atom<T2>::is_nil(yv)) {
+					nils++;
+				} else if (Calc<OP, T1, T2, T3>::apply(xv, yv, z[e]) != ST_OK && fail == ~0ULL) {
+					fail = k0 + e;
+				}
+			}
+			VecIO<T3, K>::store(a.dst + k0, z);
+		}
 	}
 	/* tail rows */
 	const uint64_t k = nchunks * K + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;

@@ -40,10 +40,21 @@ extern "C" void b200_stage_cache(int on)
 // list) is not staged at all when it lives in page-locked, device-mapped host memory: the
 // kernel dereferences it over PCIe and moves one 32-64 byte atom per touched row instead of the
 // whole column.  Falls back to stage() for pageable memory, dense access or a cached copy.
+static unsigned sparse_div()
+{
+	/* a gather touching fewer than count / div rows reads the pinned host heap in place */
+	static const unsigned d = [] {
+		const char *e = getenv("B200_SPARSE_DIV");
+		const int v = e ? atoi(e) : 0;
+		return (unsigned) (v > 0 ? v : 16);
+	}();
+	return d;
+}
+
 bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows)
 {
 	if (in != nullptr && in->device < 0 && in->base != nullptr && in->ccand == B200_CAND_NONE && in->ttype != B200_void &&
-	    in->ttype != B200_msk && touch_rows < in->count / 16 && ctx()->device >= 0) {
+	    in->ttype != B200_msk && touch_rows < in->count / sparse_div() && ctx()->device >= 0) {
 		bool cached = false;
 		if (tl_stage_on && tl_stage)
 			for (StageEntry &e : *tl_stage)
@@ -317,6 +328,27 @@ b200_bat *cand_to_bat(const Cand &ci)
 	bn->owns = 1;
 	bn->tsorted = bn->tkey = bn->tnonil = 1;
 	bn->trevsorted = ci.ncand <= 1;
+	return bn;
+}
+
+// BATunmask (gdk_cand.c:1464): a mask (or negative) candidate list as its plain form — a dense
+// void BAT when the oids are consecutive, else a materialised ascending oid[] tail.
+extern "C" b200_bat *b200_BATunmask(const b200_bat *b)
+{
+	b200_clrerr();
+	if (b == nullptr) {
+		set_err("BATunmask: BAT required\n");
+		return nullptr;
+	}
+	Staged sb;
+	if (!stage(b, sb))
+		return nullptr;
+	Cand ci;
+	if (!cand_init(ci, nullptr, sb.b))
+		return nullptr;
+	b200_bat *bn = cand_to_bat(ci);
+	if (bn)
+		bn->hseqbase = b->hseqbase;
 	return bn;
 }
 

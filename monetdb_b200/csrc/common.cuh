@@ -122,6 +122,22 @@ bool cuda_ok(cudaError_t e, const char *what);
 void *dev_alloc(size_t bytes);		/* stream-ordered pool allocation, NULL + error on failure */
 void dev_free(void *p);
 void hash_cache_drop(const void *base);	/* join.cu: forget a cached BAThash index */
+
+// Narrow twins of columns this library produced itself, kept beside the descriptor and keyed by
+// the tail heap like the hash cache (heap.cu).  The oid[] tail the API mandates is always written
+// in full; a later operator that finds a twin reads it instead of the 8-byte form.
+enum { SHADOW_GID8 = 1 /* group ids < 256 as one byte per row */,
+       SHADOW_SELMASK = 2 /* select result: the scan's bitmask + chunk offsets */ };
+struct Shadow {
+	int kind = 0;
+	void *p = nullptr, *p2 = nullptr;	/* owned device buffers */
+	uint64_t n = 0;				/* rows of the BAT the twin describes */
+	uint64_t a0 = 0, a1 = 0, a2 = 0;	/* kind-specific */
+};
+void shadow_put(const void *base, const Shadow &s);
+bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out);
+void shadow_drop(const void *base);
+bool shadow_enabled();
 void *scratch_get(size_t bytes);	/* per-thread reusable device scratch */
 bool stream_sync();			/* sync + error check */
 

@@ -35,7 +35,9 @@ template <typename T> struct GrpSrc {
 	oid hseq;
 	oid seq;		/* dense: oid of candidate position 0 */
 	const oid *g;		/* prior group ids per candidate position, or NULL */
+	const unsigned char *g8;	/* their one-byte twin (SHADOW_GID8) when the prior BATgroup left one */
 	uint64_t n;
+	__device__ __forceinline__ oid gval(uint64_t r) const { return g8 ? (oid) g8[r] : g[r]; }
 	__device__ __forceinline__ T value(uint64_t r) const { return cand ? vals[cand[r] - hseq] : vals[r]; }
 	__device__ __forceinline__ oid rowoid(uint64_t r) const { return cand ? cand[r] : seq + r; }
 };
@@ -47,7 +49,7 @@ template <typename T, bool HASG> __device__ __forceinline__ unsigned direct_inde
 	typedef typename KeyBits<T>::type U;
 	unsigned k = (unsigned) (U) src.value(r);
 	if (HASG)
-		k |= (unsigned) src.g[r] << (8 * sizeof(T));
+		k |= (unsigned) src.gval(r) << (8 * sizeof(T));
 	return k;
 }
 
@@ -96,6 +98,54 @@ grp_direct_first_kernel(GrpSrc<T> src, u64 *__restrict__ first, unsigned domain)
 	}
 }
 
+// 1-byte values without a candidate list: 16 rows per thread from one 16-byte load (and eight
+// 16-byte loads of the prior group ids); the table lives in shared memory.
+template <bool HASG>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_byte_first_kernel(const unsigned char *__restrict__ vals, const unsigned char *__restrict__ g8, uint64_t n, u64 *__restrict__ first, unsigned domain)
+{
+	extern __shared__ u64 sfirst[];
+	for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS)
+		sfirst[i] = GRP_EMPTY;
+	__syncthreads();
+	const uint64_t nvec = n / 16;
+	for (uint64_t v = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; v < nvec; v += (uint64_t) gridDim.x * GRP_THREADS) {
+		const uint4 w = __ldcs(reinterpret_cast<const uint4 *>(vals) + v);
+		const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+		unsigned gw[4] = {0, 0, 0, 0};
+		if (HASG) {
+			const uint4 q = __ldcs(reinterpret_cast<const uint4 *>(g8) + v);
+			gw[0] = q.x;
+			gw[1] = q.y;
+			gw[2] = q.z;
+			gw[3] = q.w;
+		}
+#pragma unroll
+		for (int i = 0; i < 16; i++) {
+			unsigned k = (ww[i >> 2] >> (8 * (i & 3))) & 0xff;
+			if (HASG)
+				k |= ((gw[i >> 2] >> (8 * (i & 3))) & 0xff) << 8;
+			const u64 r = v * 16 + i;
+			if (r < sfirst[k])
+				atomicMin(&sfirst[k], r);
+		}
+	}
+	/* tail rows */
+	const uint64_t r = nvec * 16 + (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x;
+	if (r < n) {
+		unsigned k = vals[r];
+		if (HASG)
+			k |= (unsigned) g8[r] << 8;
+		atomicMin(&sfirst[k], (u64) r);
+	}
+	__syncthreads();
+	for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS) {
+		u64 v = sfirst[i];
+		if (v != GRP_EMPTY && v < __ldcg(first + i))
+			atomicMin(first + i, v);
+	}
+}
+
 // ---------------------------------------------------------------- pass A, hash table
 // slots[h] = smallest candidate position seen so far of the key that owns slot h.
 // A slot's value only ever changes to another row with the SAME key, so comparing
@@ -114,7 +164,7 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
 	for (uint64_t r = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r < src.n; r += stride) {
 		const U v = KeyBits<T>::get(src.value(r));
-		const u64 gv = HASG ? src.g[r] : 0;
+		const u64 gv = HASG ? src.gval(r) : 0;
 		u64 h = hash_key<U>(v, gv) & mask;
 		unsigned probes = 0;
 		for (;;) {
@@ -128,7 +178,7 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 			}
 			if (cur == r)
 				break;
-			if (KeyBits<T>::get(src.value(cur)) == v && (!HASG || src.g[cur] == gv)) {
+			if (KeyBits<T>::get(src.value(cur)) == v && (!HASG || src.gval(cur) == gv)) {
 				if (r < cur)
 					atomicMin(slots + h, (u64) r);
 				break;
@@ -239,7 +289,8 @@ __device__ __forceinline__ uint32_t grp_entry(const GrpSrc<T> &src, const uint32
 template <typename T, bool HASG, int MODE, bool SHISTO>
 __global__ void __launch_bounds__(GRP_THREADS)
 grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint32_t *__restrict__ gidtab, unsigned domain,
-		  oid *__restrict__ gids, u64 *__restrict__ cnts, unsigned ngrp, unsigned *__restrict__ unsorted)
+		  oid *__restrict__ gids, unsigned char *__restrict__ g8out, u64 *__restrict__ cnts, unsigned ngrp,
+		  unsigned *__restrict__ unsorted)
 {
 	extern __shared__ uint32_t sh[];
 	uint32_t *sgid = sh;					/* MODE 0: domain entries */
@@ -278,8 +329,12 @@ grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint
 			v.x = g0;
 			v.y = g1;
 			__stcs(reinterpret_cast<ulonglong2 *>(gids + r), v);
+			if (g8out)
+				*reinterpret_cast<unsigned short *>(g8out + r) = (unsigned short) (g0 | (g1 << 8));
 		} else {
 			gids[r] = g0;
+			if (g8out)
+				g8out[r] = (unsigned char) g0;
 		}
 		if (cnts) {
 			if (SHISTO) {
@@ -305,6 +360,103 @@ grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint
 			if (shist[i])
 				atomicAdd(cnts + i, (u64) shist[i]);
 	}
+}
+
+// 1-byte values without a candidate list, table in shared memory, at most 8 groups: a warp takes
+// 512 consecutive rows per step; lane l handles rows 2l, 2l+1 of each of eight 64-row slices, so
+// the value loads (2 bytes), prior-id loads and id stores (16 bytes) are all fully coalesced.  The
+// histogram is a packed 8 x 8-bit counter per thread, flushed every 8 steps (<= 128 rows).
+template <bool HASG>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_byte_assign_kernel(const unsigned char *__restrict__ vals, const unsigned char *__restrict__ g8, uint64_t n, const uint32_t *__restrict__ gidtab,
+		       unsigned domain, oid *__restrict__ gids, unsigned char *__restrict__ g8out, u64 *__restrict__ cnts, unsigned ngrp,
+		       unsigned *__restrict__ unsorted)
+{
+	extern __shared__ uint32_t sh[];
+	uint32_t *sgid = sh, *shist = sh + domain;
+	for (unsigned i = threadIdx.x; i < domain; i += GRP_THREADS)
+		sgid[i] = gidtab[i];
+	if (threadIdx.x < 8)
+		shist[threadIdx.x] = 0;
+	__syncthreads();
+	const unsigned lane = threadIdx.x & 31;
+	const uint64_t warp = ((uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x) >> 5;
+	const uint64_t nwarps = ((uint64_t) gridDim.x * GRP_THREADS) >> 5;
+	bool bad = false;
+	u64 packed = 0;
+	unsigned steps = 0;
+	for (uint64_t base = warp * 512; base < n; base += nwarps * 512) {
+		unsigned short v[8], pg[HASG ? 8 : 1];
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			const uint64_t r = base + j * 64 + 2 * lane;
+			v[j] = 0;
+			if (r + 1 < n)
+				v[j] = __ldcs(reinterpret_cast<const unsigned short *>(vals + r));
+			else if (r < n)
+				v[j] = vals[r];
+			if (HASG) {
+				pg[j] = 0;
+				if (r + 1 < n)
+					pg[j] = __ldcs(reinterpret_cast<const unsigned short *>(g8 + r));
+				else if (r < n)
+					pg[j] = g8[r];
+			}
+		}
+		/* id of the row just before this warp's 512 rows (sortedness check) */
+		uint32_t carry = 0;
+		if (lane == 0 && base > 0) {
+			unsigned k = vals[base - 1];
+			if (HASG)
+				k |= (unsigned) g8[base - 1] << 8;
+			carry = sgid[k];
+		}
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			const uint64_t r = base + j * 64 + 2 * lane;
+			unsigned k0 = v[j] & 0xff, k1 = v[j] >> 8;
+			if (HASG) {
+				k0 |= (unsigned) (pg[j] & 0xff) << 8;
+				k1 |= (unsigned) (pg[j] >> 8) << 8;
+			}
+			const bool in0 = r < n, in1 = r + 1 < n;
+			const uint32_t g0 = in0 ? sgid[k0] : 0, g1 = in1 ? sgid[k1] : g0;
+			uint32_t gp = __shfl_up_sync(0xffffffffu, g1, 1);
+			if (lane == 0)
+				gp = carry;
+			carry = __shfl_sync(0xffffffffu, g1, 31);
+			bad |= (in0 && r > 0 && g0 < gp) || (in1 && g1 < g0);
+			if (in1) {
+				ulonglong2 o;
+				o.x = g0;
+				o.y = g1;
+				__stcs(reinterpret_cast<ulonglong2 *>(gids + r), o);
+				if (g8out)
+					*reinterpret_cast<unsigned short *>(g8out + r) = (unsigned short) (g0 | (g1 << 8));
+			} else if (in0) {
+				gids[r] = g0;
+				if (g8out)
+					g8out[r] = (unsigned char) g0;
+			}
+			packed += (in0 ? 1ULL << (8 * g0) : 0) + (in1 ? 1ULL << (8 * g1) : 0);
+		}
+		if (++steps == 8) {
+#pragma unroll
+			for (int q = 0; q < 8; q++)
+				if ((packed >> (8 * q)) & 0xff)
+					atomicAdd(&shist[q], (unsigned) ((packed >> (8 * q)) & 0xff));
+			packed = 0;
+			steps = 0;
+		}
+	}
+#pragma unroll
+	for (int q = 0; q < 8; q++)
+		if ((packed >> (8 * q)) & 0xff)
+			atomicAdd(&shist[q], (unsigned) ((packed >> (8 * q)) & 0xff));
+	if (__syncthreads_or(bad) && threadIdx.x == 0)
+		*unsorted = 1;
+	if (cnts && threadIdx.x < ngrp && shist[threadIdx.x])
+		atomicAdd(cnts + threadIdx.x, (u64) shist[threadIdx.x]);
 }
 
 // ---------------------------------------------------------------- host side
@@ -382,8 +534,15 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 		if (t.table == nullptr || !cuda_ok(cudaMemsetAsync(t.table, 0xff, nentries * 8, c->stream), "memset group table"))
 			return false;
 		if constexpr (sizeof(T) <= 2) {
-			KTimer kt("group_first", n * (sizeof(T) + (HASG ? 8 : 0)));
-			if (mode == 0)
+			KTimer kt(HASG ? "group_first_g" : "group_first", n * (sizeof(T) + (HASG ? 8 : 0)));
+			bool fastb = false;
+			if constexpr (sizeof(T) == 1)
+				fastb = mode == 0 && src.cand == nullptr && ((uintptr_t) src.vals & 15) == 0 &&
+					(!HASG || (src.g8 != nullptr && ((uintptr_t) src.g8 & 15) == 0));	/* 8-byte prior ids: the row-per-lane form is already coalesced */
+			if (fastb)
+				grp_byte_first_kernel<HASG><<<grid_for(n / 16 + GRP_THREADS, GRP_THREADS, NSM * 8), GRP_THREADS, nentries * 8, c->stream>>>(
+					(const unsigned char *) src.vals, src.g8, n, t.table, (unsigned) nentries);
+			else if (mode == 0)
 				grp_direct_first_kernel<T, HASG, true><<<sgrid, GRP_THREADS, nentries * 8, c->stream>>>(src, t.table, (unsigned) nentries);
 			else
 				grp_direct_first_kernel<T, HASG, false><<<sgrid, GRP_THREADS, 0, c->stream>>>(src, t.table, (unsigned) nentries);
@@ -467,14 +626,23 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 	/* pass C */
 	const bool shisto = ngrp <= GRP_SHM_HISTO;
 	oid *gids = (oid *) gn->base;
+	/* few groups: leave a one-byte twin of the ids for the aggregates / the next BATgroup level */
+	unsigned char *g8out = shadow_enabled() && ngrp <= 256 && n >= (1u << 16) ? (unsigned char *) dev_alloc(n) : nullptr;
 	u64 *cnts = hn ? (u64 *) hn->base : nullptr;
 	const unsigned agrid = grid_for((n + 1) / 2, GRP_THREADS * 4, NSM * 8);
 	const size_t shm = (mode == 0 ? nentries * 4 : 0) + (shisto ? ngrp * 4 : 0);
 	{
-		KTimer kt("group_assign", n * ((mode == 2 ? 4 : sizeof(T) + (HASG ? 8 : 0)) + 8));
+		KTimer kt(HASG ? "group_assign_g" : "group_assign", n * ((mode == 2 ? 4 : sizeof(T) + (HASG ? 8 : 0)) + 8));
 #define ASSIGN(MODE, SH) grp_assign_kernel<T, HASG, MODE, SH><<<agrid, GRP_THREADS, shm, c->stream>>>( \
-		src, t.slotof, t.gidtab, (unsigned) nentries, gids, cnts, (unsigned) ngrp, t.state)
-		if (mode == 2) {
+		src, t.slotof, t.gidtab, (unsigned) nentries, gids, g8out, cnts, (unsigned) ngrp, t.state)
+		bool fastb = false;
+		if constexpr (sizeof(T) == 1)
+			fastb = mode == 0 && ngrp <= 8 && src.cand == nullptr && ((uintptr_t) src.vals & 1) == 0 &&
+				(!HASG || (src.g8 != nullptr && ((uintptr_t) src.g8 & 1) == 0));	/* 8-byte prior ids: measured no faster */
+		if (fastb) {
+			grp_byte_assign_kernel<HASG><<<grid_for(n, GRP_THREADS * 16, NSM * 8), GRP_THREADS, nentries * 4 + 32, c->stream>>>(
+				(const unsigned char *) src.vals, src.g8, n, t.gidtab, (unsigned) nentries, gids, g8out, cnts, (unsigned) ngrp, t.state);
+		} else if (mode == 2) {
 			if (shisto) ASSIGN(2, true); else ASSIGN(2, false);
 		} else if constexpr (sizeof(T) <= 2) {
 			if (mode == 0) {
@@ -488,8 +656,18 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 	COUNT_LAUNCH();
 	grp_finish_kernel<<<1, 1, 0, c->stream>>>(en ? (const oid *) en->base : nullptr, ngrp, t.state, c->slot_d->v);
 	COUNT_LAUNCH();
-	if (!cuda_ok(cudaGetLastError(), "group launch") || !stream_sync())
+	if (!cuda_ok(cudaGetLastError(), "group launch") || !stream_sync()) {
+		dev_free(g8out);
 		return false;
+	}
+	if (g8out) {
+		Shadow sh;
+		sh.kind = SHADOW_GID8;
+		sh.p = g8out;
+		sh.n = n;
+		sh.a0 = ngrp;
+		shadow_put(gn->base, sh);
+	}
 	const bool unsorted = c->slot_h->v[0] != 0;
 	const oid efirst = c->slot_h->v[1], elast = c->slot_h->v[2];
 	/* result properties, gdk_group.c:1283-1315 */
@@ -544,6 +722,10 @@ static bool group_typed(const b200_bat *b, const Cand &ci, const b200_bat *g, u6
 		src.cand = ci.oids;
 	}
 	src.g = g ? (const oid *) g->base : nullptr;
+	src.g8 = nullptr;
+	Shadow sh;
+	if (g && shadow_get(g->base, SHADOW_GID8, g->count, sh))
+		src.g8 = (const unsigned char *) sh.p;
 	if (g)
 		return group_run<T, true>(src, maxgrp, gn, enp, hnp, want_e, want_h);
 	return group_run<T, false>(src, maxgrp, gn, enp, hnp, want_e, want_h);
@@ -604,8 +786,11 @@ extern "C" b200_return b200_BATgroup(b200_bat **groups, b200_bat **extents, b200
 				set_err("BATgroup: g must be a materialised oid column\n");
 				goto bailout;
 			}
+			Shadow gsh;
 			if (e != nullptr && e->count > 0) {
 				maxgrp = e->count - 1;
+			} else if (shadow_get(g->base, SHADOW_GID8, g->count, gsh) && gsh.a0 > 0) {
+				maxgrp = gsh.a0 - 1;	/* the BATgroup call that made g left its group count */
 			} else {
 				u64 *st = (u64 *) scratch_get(64);
 				if (st == nullptr || !cuda_ok(cudaMemsetAsync(st, 0, 8, c->stream), "memset"))

@@ -4,6 +4,7 @@
 // (COLnew gdk_bat.c:238-298, BATdense :298, BBPreclaim gdk_bbp.c:3161), and the
 // candidate iterator set-up (canditer_init, gdk_cand.c:407-712).
 #include "common.cuh"
+#include <unordered_map>
 #include "scan.cuh"
 #include <mutex>
 #include <stdlib.h>
@@ -243,6 +244,39 @@ b200_bat *bat_dense(uint64_t hseq, uint64_t tseq, uint64_t cnt)
 extern "C" b200_bat *b200_COLnew(uint64_t hseq, int tt, uint64_t cap) { b200_clrerr(); return bat_new(hseq, tt, cap); }
 extern "C" b200_bat *b200_BATdense(uint64_t hseq, uint64_t tseq, uint64_t cnt) { b200_clrerr(); return bat_dense(hseq, tseq, cnt); }
 
+// BATextend / HEAPextend (gdk_bat.c:529, gdk_heap.c:246): grow the tail heap of a device BAT we own,
+// keeping the first count items; a capacity that is already large enough is left alone.
+extern "C" b200_return b200_BATextend(b200_bat *b, uint64_t newcap)
+{
+	b200_clrerr();
+	if (b == nullptr || !ctx_usable())
+		return B200_FAIL;
+	if (newcap <= b->capacity || b->ttype == B200_void)
+		return B200_SUCCEED;
+	if (!b->owns || b->device < 0 || b->device != tl_ctx->device) {
+		set_err("BATextend: only device heaps owned by the descriptor (on the calling thread's device) can grow\n");
+		return B200_FAIL;
+	}
+	const int w = atomsize(b->ttype);
+	const size_t nbytes = b->ttype == B200_msk ? ((newcap + 31) / 32) * 4 : (size_t) newcap * w;
+	const size_t obytes = b->ttype == B200_msk ? ((b->count + 31) / 32) * 4 : (size_t) b->count * w;
+	void *nb = dev_alloc(nbytes);
+	if (nb == nullptr)
+		return B200_FAIL;
+	if (obytes && !cuda_ok(cudaMemcpyAsync(nb, b->base, obytes, cudaMemcpyDeviceToDevice, tl_ctx->stream), "BATextend copy")) {
+		dev_free(nb);
+		return B200_FAIL;
+	}
+	if (b->base) {
+		hash_cache_drop(b->base);
+		shadow_drop(b->base);
+		dev_free(b->base);		/* stream-ordered: runs after the copy */
+	}
+	b->base = nb;
+	b->capacity = newcap;
+	return B200_SUCCEED;
+}
+
 extern "C" b200_bat *b200_BATfromhost(const void *src, int tt, uint64_t cnt, uint64_t hseq)
 {
 	b200_clrerr();
@@ -296,12 +330,63 @@ extern "C" void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool 
 	b->tnil = nil;
 }
 
+// ---------------------------------------------------------------- narrow twins (common.cuh)
+static std::mutex g_shadow_mu;
+static std::unordered_map<const void *, Shadow> g_shadows;
+
+bool shadow_enabled()
+{
+	static const bool on = [] {
+		const char *e = getenv("B200_NO_SHADOW");
+		return !(e && e[0] == '1');
+	}();
+	return on;
+}
+
+void shadow_put(const void *base, const Shadow &s)
+{
+	shadow_drop(base);
+	std::lock_guard<std::mutex> lk(g_shadow_mu);
+	g_shadows[base] = s;
+}
+
+bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out)
+{
+	if (base == nullptr)
+		return false;
+	std::lock_guard<std::mutex> lk(g_shadow_mu);
+	auto it = g_shadows.find(base);
+	if (it == g_shadows.end() || it->second.kind != kind || it->second.n != n)
+		return false;
+	out = it->second;
+	return true;
+}
+
+void shadow_drop(const void *base)
+{
+	if (base == nullptr)
+		return;
+	Shadow s;
+	{
+		std::lock_guard<std::mutex> lk(g_shadow_mu);
+		auto it = g_shadows.find(base);
+		if (it == g_shadows.end())
+			return;
+		s = it->second;
+		g_shadows.erase(it);
+	}
+	dev_free(s.p);
+	dev_free(s.p2);
+}
+
 extern "C" void b200_BATfree(b200_bat *b)
 {
 	if (b == nullptr)
 		return;
 	if (b->device >= 0 && b->base != nullptr)
 		hash_cache_drop(b->base);	/* a BAThash index dies with its BAT */
+	if (b->device >= 0 && b->base != nullptr && b->owns)
+		shadow_drop(b->base);
 	if (b->owns) {
 		if (b->device >= 0) {
 			if (tl_ctx && tl_ctx->device == b->device) {

@@ -120,6 +120,8 @@ _sig("b200_BATfromhost", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
 _sig("b200_BATwrap", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64)
 _sig("b200_BATnegcands_fromhost", _P, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64)
 _sig("b200_BATmaskedcands_fromhost", _P, C.c_uint64, C.c_uint64, C.c_void_p, C.c_bool)
+_sig("b200_BATunmask", _P, _P)
+_sig("b200_BATextend", C.c_int, _P, C.c_uint64)
 _sig("b200_BATsetprops", None, _P, C.c_bool, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
 _sig("b200_BATtohost", C.c_int, _P, C.c_void_p)
 _sig("b200_BATfree", None, _P)
@@ -280,6 +282,16 @@ def BATnegcands(seq: int, cnt: int, exceptions) -> BAT:
 def BATmaskedcands(hseq: int, nrows: int, words, selected: bool = True) -> BAT:
     w = np.ascontiguousarray(words, dtype=np.uint32)
     return BAT(lib.b200_BATmaskedcands_fromhost(hseq, nrows, _vp(w), selected))
+
+
+def BATunmask(b: BAT) -> BAT:
+    return BAT(lib.b200_BATunmask(b._p))
+
+
+def BATextend(b: BAT, newcap: int) -> BAT:
+    if lib.b200_BATextend(b._p, newcap) != 1:
+        _fail("BATextend")
+    return b
 
 
 # ------------------------------------------------------------------ select / project / cands

@@ -274,6 +274,15 @@ def maskedcands(hseq, nrows, words, selected=True) -> RBAT:
     return RBAT(_bat.BATmaskedcands(hseq, nrows, m.p, selected))
 
 
+def BATunmask(b) -> RBAT:
+    _load()
+    if not hasattr(_bat.BATunmask, "_set"):
+        _bat.BATunmask.restype = C.c_void_p
+        _bat.BATunmask.argtypes = [C.c_void_p]
+        _bat.BATunmask._set = True
+    return RBAT(_bat.BATunmask(b.p), "BATunmask")
+
+
 def BATselect(b, s, tl, th, li, hi, anti, nil_matches=False) -> RBAT:
     tt = b.info().type
     vl, vh = _val(tt, tl), _val(tt, th)

@@ -169,3 +169,20 @@ def test_select_maltest_golden(gdk):
         x = gdk.BATselect(cols[c["col"]], None, lo, hi, c["li"], c["hi_incl"], c["anti"], False)
         got = sorted(vals[c["col"]][x.numpy().astype(np.int64)].tolist())
         assert got == sorted(nil if v is None else v for v in c["values"]), c
+
+
+@pytest.mark.parametrize("kind", ["mask", "neg", "dense"])
+def test_unmask_and_extend(gdk, ref, kind):
+    """BATunmask (gdk_cand.c:1464) gives the same oid set; BATextend keeps the tail while growing it"""
+    rng = np.random.default_rng(99)
+    n = 40013
+    s, rs = _cands(gdk, ref, kind, n, rng, hseq=7)
+    o = gdk.BATunmask(s)
+    want = ref.BATunmask(rs).numpy() if kind == "mask" else rs.numpy()
+    assert same_bits(o.numpy(), want)
+    a = random_col(rng, G.TYPE.lng, n)
+    b = gdk.BATfromhost(a, G.TYPE.lng)
+    gdk.BATextend(b, 3 * n)
+    assert b.props()["count"] == n and same_bits(b.numpy(), a)
+    gdk.BATextend(b, 10)                 # never shrinks
+    assert same_bits(gdk.BATselect(b, None, 0, None, True, True, False).numpy(), np.flatnonzero(a == 0).astype(np.uint64))
