@@ -107,7 +107,15 @@ struct AggrAccum {
 	int pending_bits = 0;		/* fast form launched without waiting: the caller checks state[5..7] against this width */
 	bool pending_narrow = false;
 	AggrIn in;
-	~AggrAccum() { if (cells) dev_free(cells); if (state) dev_free(state); }
+	bool state_in_cells = false;	/* state is the tail of the cells allocation */
+	~AggrAccum() { release(); }
+	void release()
+	{
+		if (cells) dev_free(cells);
+		if (state && !state_in_cells) dev_free(state);
+		cells = state = nullptr;
+		state_in_cells = false;
+	}
 };
 
 // fast register accumulation (aggr_reg_fast_kernel).  On return `done` tells whether acc holds the
@@ -126,12 +134,12 @@ static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &
 	const AggrLayout L(ND, false, false);
 	acc.ncell = L.ncell;
 	const size_t bytes = (size_t) L.ncell * ngrp * 8;
-	acc.cells = (u64 *) dev_alloc(bytes);
-	acc.state = (u64 *) dev_alloc(64);
-	if (acc.cells == nullptr || acc.state == nullptr ||
-	    !cuda_ok(cudaMemsetAsync(acc.cells, 0, bytes, c->stream), "memset cells") ||
-	    !cuda_ok(cudaMemsetAsync(acc.state, 0, 64, c->stream), "memset state"))
+	/* cells and state in one allocation, cleared by one memset */
+	acc.cells = (u64 *) dev_alloc(bytes + 64);
+	if (acc.cells == nullptr || !cuda_ok(cudaMemsetAsync(acc.cells, 0, bytes + 64, c->stream), "memset cells"))
 		return false;
+	acc.state = acc.cells + bytes / 8;
+	acc.state_in_cells = true;
 	AggrIn &in = acc.in;
 	memset(&in, 0, sizeof(in));
 	in.n = a.ci.ncand;
@@ -195,17 +203,13 @@ static bool aggr_fast(const AggrSetup &a, int check_bits, AggrAccum &acc, bool &
 			return false;
 		if (narrow && c->slot_h->v[7] != 0) {
 			/* a value needs more than 64 bits: run the three-word form instead */
-			dev_free(acc.cells);
-			dev_free(acc.state);
-			acc.cells = acc.state = nullptr;
+			acc.release();
 			return aggr_fast<T1>(a, check_bits, acc, done, false);
 		}
 		const uhge mx = ((uhge) c->slot_h->v[6] << 64) | c->slot_h->v[5];
 		const uhge lim = ((uhge) 1 << (check_bits - 1)) - 1;
 		if (mx != 0 && (uhge) in.n > lim / mx) {
-			dev_free(acc.cells);
-			dev_free(acc.state);
-			acc.cells = acc.state = nullptr;
+			acc.release();
 			done = false;
 		}
 	}
@@ -567,14 +571,9 @@ extern "C" b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b
 		}
 		return B200_SUCCEED;
 	}
-	void *out = dev_alloc(16);
-	if (out == nullptr)
-		return B200_FAIL;
-	uint64_t nils = do_sum(a, tp, skip_nils, nil_if_empty, out, "BATsum");
-	bool ok = nils != B200_BUN_NONE &&
-		  cuda_ok(cudaMemcpyAsync(&c->slot_h->v[8], out, 16, cudaMemcpyDeviceToHost, c->stream), "read") && stream_sync();
-	dev_free(out);
-	if (!ok)
+	/* the finishing kernel stores the scalar straight into the mapped result slot; do_sum's own
+	 * sync makes it visible */
+	if (do_sum(a, tp, skip_nils, nil_if_empty, &c->slot_d->v[8], "BATsum") == B200_BUN_NONE)
 		return B200_FAIL;
 	memcpy(res, &c->slot_h->v[8], w2);
 	return B200_SUCCEED;

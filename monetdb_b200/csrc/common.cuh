@@ -132,8 +132,10 @@ struct Shadow {
 	int kind = 0;
 	void *p = nullptr, *p2 = nullptr;	/* owned device buffers */
 	uint64_t n = 0;				/* rows of the BAT the twin describes */
-	uint64_t a0 = 0, a1 = 0, a2 = 0;	/* kind-specific */
+	uint64_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;	/* kind-specific */
 };
+void *scratch_steal(size_t *bytes);	/* heap.cu */
+size_t scratch_size();
 void shadow_put(const void *base, const Shadow &s);
 bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out);
 void shadow_drop(const void *base);

@@ -184,6 +184,51 @@ compact_expand_kernel(const uint32_t *__restrict__ words, const uint32_t *__rest
 	}
 }
 
+// Expand-with-gather: the same per-chunk structure as compact_expand_kernel, but instead of the
+// oid of every set bit it emits src[bit index] — BATproject through a select result whose scan
+// bitmask is still at hand (SHADOW_SELMASK): the column is streamed once and no oid is read.
+template <int WORDS, typename VT>
+__global__ void __launch_bounds__(WORDS)
+compact_gather_kernel(const uint32_t *__restrict__ words, const unsigned long long *__restrict__ offs,
+		      const VT *__restrict__ src, VT *__restrict__ dst)
+{
+	const unsigned long long cbase = offs[blockIdx.x];
+	if (offs[blockIdx.x + 1] == cbase)
+		return;
+	__shared__ unsigned short stage[WORDS * 32];
+	__shared__ unsigned wtot[WORDS / 32];
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t wbase = (uint64_t) blockIdx.x * WORDS + warp * 32;
+	unsigned w = words[wbase + lane];
+	const unsigned c = __popc(w);
+	unsigned inc = c;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o)
+			inc += t;
+	}
+	const unsigned T = __shfl_sync(0xffffffffu, inc, 31);
+	if (lane == 31)
+		wtot[warp] = inc;
+	unsigned short *st = stage + warp * 1024;
+	unsigned pos = inc - c;
+	const unsigned short lbase = (unsigned short) (lane * 32);
+	while (w) {
+		const unsigned b = __ffs(w) - 1;
+		w &= w - 1;
+		st[pos++] = lbase + (unsigned short) b;
+	}
+	__syncthreads();
+	unsigned long long base = cbase;
+#pragma unroll
+	for (int k = 0; k < WORDS / 32; k++)
+		base += k < warp ? wtot[k] : 0;
+	const VT *sp = src + wbase * 32;
+	for (unsigned r = lane; r < T; r += 32)
+		dst[base + r] = sp[st[r]];
+}
+
 struct CompactResult {
 	uint64_t count = 0;
 	oid first = 0, last = 0;

@@ -132,6 +132,23 @@ void *scratch_get(size_t bytes)
 	return c->scratch;
 }
 
+// hand the scratch block over to the caller (who frees it with dev_free); the next scratch_get allocates afresh
+void *scratch_steal(size_t *bytes)
+{
+	Ctx *c = ctx();
+	void *p = c->scratch;
+	if (bytes)
+		*bytes = c->scratch_bytes;
+	c->scratch = nullptr;
+	c->scratch_bytes = 0;
+	return p;
+}
+
+size_t scratch_size()
+{
+	return ctx()->scratch_bytes;
+}
+
 bool stream_sync()
 {
 	return cuda_ok(cudaStreamSynchronize(ctx()->stream), "stream sync");

@@ -7,6 +7,7 @@
 // (16/w rows), reading its oids with 128-bit loads; the value reads are the
 // gather.
 #include "common.cuh"
+#include "compact.cuh"
 
 template <int W> struct WordOf;
 template <> struct WordOf<1> { typedef uint8_t type; };
@@ -123,6 +124,22 @@ static void launch_project(const oid *l, uint64_t n, const ProjSrc &src, const v
 		project_kernel<W, true><<<grid, 256, 0, ctx()->stream>>>(l, n, src, nilword, (word *) dst, errflag);
 	else
 		project_kernel<W, false><<<grid, 256, 0, ctx()->stream>>>(l, n, src, nilword, (word *) dst, errflag);
+	COUNT_LAUNCH();
+}
+
+// BATproject through a select result that still has its scan bitmask (SHADOW_SELMASK)
+template <int W>
+static void launch_project_mask(const Shadow &sh, const void *r1base, int64_t rowoff, void *dst, uint64_t n)
+{
+	typedef typename WordOf<W>::type word;
+	const word *src = (const word *) r1base + rowoff;	/* row of bit 0; only set bits are dereferenced */
+	KTimer kt("project", n * (8 + 2 * W));			/* algorithmic: the API's oid list + gather */
+	if (sh.a2 == CP_CHUNK)
+		compact_gather_kernel<CP_CHUNK / 32, word><<<(unsigned) sh.a1, CP_CHUNK / 32, 0, ctx()->stream>>>(
+			(const uint32_t *) sh.p, (const unsigned long long *) ((const char *) sh.p + sh.a3), src, (word *) dst);
+	else
+		compact_gather_kernel<CP_CHUNK_SMALL / 32, word><<<(unsigned) sh.a1, CP_CHUNK_SMALL / 32, 0, ctx()->stream>>>(
+			(const uint32_t *) sh.p, (const unsigned long long *) ((const char *) sh.p + sh.a3), src, (word *) dst);
 	COUNT_LAUNCH();
 }
 
@@ -277,7 +294,22 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 	unsigned char nilb[16];
 	atom_nil_bits(tpe, nilb);
 	ctx()->algo = "project: cuda gather";
-	if (src.r1void || src.r2void) {
+	Shadow msh;
+	const int w = atomsize(tpe);
+	/* dense enough for streaming the whole column to beat the gather (8-byte oid + 32-byte sector per row) */
+	if (r2 == nullptr && !src.r1void && l_sorted_known && loids == (const oid *) l->base &&
+	    shadow_get(l->base, SHADOW_SELMASK, lcount, msh) &&
+	    lcount * 4 >= msh.a1 * msh.a2) {
+		const int64_t rowoff = (int64_t) msh.a0 - (int64_t) r1->hseqbase;
+		switch (w) {
+		case 1: launch_project_mask<1>(msh, r1->base, rowoff, bn->base, lcount); break;
+		case 2: launch_project_mask<2>(msh, r1->base, rowoff, bn->base, lcount); break;
+		case 4: launch_project_mask<4>(msh, r1->base, rowoff, bn->base, lcount); break;
+		case 8: launch_project_mask<8>(msh, r1->base, rowoff, bn->base, lcount); break;
+		case 16: launch_project_mask<16>(msh, r1->base, rowoff, bn->base, lcount); break;
+		}
+		ctx()->algo = "project: cuda bitmask expand";
+	} else if (src.r1void || src.r2void) {
 		project_void_kernel<<<grid_for(lcount, 256, NSM * 32), 256, 0, c->stream>>>(loids, lcount, src, (oid *) bn->base, errflag);
 		COUNT_LAUNCH();
 	} else {

@@ -153,6 +153,40 @@ select_dense32_kernel(const T *__restrict__ src, uint64_t n, P pred, uint32_t *_
 		counts[blockIdx.x] = total;
 }
 
+// Keep the scan's bitmask and chunk offsets as a twin of the oid list about to be returned
+// (SHADOW_SELMASK): bit i <-> oid bit0 + i.  Only for large results keeping at least a quarter of the
+// scanned rows (below that a gather through the oid list moves fewer bytes than streaming the column).
+static void keep_selmask(const CompactScratch &s, uint64_t nbits, oid bit0, const oid *dst, const CompactResult &res)
+{
+	if (!shadow_enabled() || res.count < (1u << 16) || res.count * 4 < nbits || res.last - res.first + 1 == res.count)
+		return;
+	Ctx *c = ctx();
+	const size_t wbytes = s.nchunks * (s.chunk / 32) * 4, obytes = (s.nchunks + 1) * 8;
+	const size_t used = (size_t) ((const char *) s.offs - (const char *) s.words) + obytes;
+	Shadow sh;
+	sh.kind = SHADOW_SELMASK;
+	if ((const void *) s.words == scratch_get(0) && scratch_size() <= 4 * used) {
+		/* the mask lives at the start of the thread's scratch block: keep the block itself */
+		sh.p = scratch_steal(nullptr);
+		sh.a3 = (uint64_t) ((const char *) s.offs - (const char *) s.words);
+	} else {
+		sh.p = dev_alloc(wbytes + obytes);
+		sh.a3 = wbytes;
+		if (sh.p == nullptr ||
+		    !cuda_ok(cudaMemcpyAsync(sh.p, s.words, wbytes, cudaMemcpyDeviceToDevice, c->stream), "selmask words") ||
+		    !cuda_ok(cudaMemcpyAsync((char *) sh.p + wbytes, s.offs, obytes, cudaMemcpyDeviceToDevice, c->stream), "selmask offs")) {
+			dev_free(sh.p);
+			b200_clrerr();
+			return;
+		}
+	}
+	sh.n = res.count;
+	sh.a0 = bit0;
+	sh.a1 = s.nchunks;
+	sh.a2 = s.chunk;
+	shadow_put(dst, sh);
+}
+
 template <typename T>
 static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, oid seq, RangePred<T> pred, oid *dst, CompactResult &res)
 {
@@ -177,7 +211,10 @@ static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, o
 				select_dense32_kernel<T, RangePred<T>><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, ncand, pred, s.words, s.counts);
 		}
 		COUNT_LAUNCH();
-		return compact_finish(s, DenseOid{seq}, dst, res);
+		if (!compact_finish(s, DenseOid{seq}, dst, res))
+			return false;
+		keep_selmask(s, ncand, seq, dst, res);
+		return true;
 	} else {
 		const T *p = col + first_row;
 		uint64_t skip = ((uintptr_t) p & 15) / sizeof(T);
@@ -190,7 +227,10 @@ static bool run_select_dense(const T *col, uint64_t first_row, uint64_t ncand, o
 			select_dense_kernel<T><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(p, skip, n, pred, s.words, s.counts);
 		}
 		COUNT_LAUNCH();
-		return compact_finish(s, DenseOid{seq - skip}, dst, res);
+		if (!compact_finish(s, DenseOid{seq - skip}, dst, res))
+			return false;
+		keep_selmask(s, n, seq - skip, dst, res);
+		return true;
 	}
 }
 
@@ -317,6 +357,8 @@ static bool select_typed(const SelArgs &a, b200_bat **out)
 		return false;
 	}
 	*out = oidlist_to_bat(dst, ci.ncand, r);
+	if (*out == nullptr)
+		shadow_drop(dst);	/* the list was freed: its bitmask twin must not outlive it */
 	return *out != nullptr;
 }
 

@@ -244,6 +244,29 @@ def _vp(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
 
+_ATOMS: dict = {}
+_NOATOM = (None, None)
+
+
+def _valp(tt: int, v):
+    """(buffer, pointer) of one atom value, memoised: the per-call numpy/ctypes work of _val + _vp
+    is a measurable part of a short operator call"""
+    if v is None:
+        return _NOATOM
+    key = (tt, v)
+    try:
+        return _ATOMS[key]
+    except (KeyError, TypeError):
+        a = _val(tt, v)
+        r = (a, _vp(a))
+        try:
+            if len(_ATOMS) < 4096:
+                _ATOMS[key] = r
+        except TypeError:
+            pass
+        return r
+
+
 # ------------------------------------------------------------------ construction
 def BATfromhost(arr: np.ndarray, tt: int | None = None, hseq: int = 0, **props) -> BAT:
     """upload a tail heap (the device heap tier's load path)"""
@@ -299,15 +322,18 @@ def _storage(tt: int) -> int:
     return {TYPE.bit: TYPE.bte, TYPE.date: TYPE.int, TYPE.daytime: TYPE.lng, TYPE.timestamp: TYPE.lng}.get(tt, tt)
 
 
+_OPS = {o: o.encode() for o in ("=", "==", "!=", "<>", "<", "<=", ">", ">=", "eq", "ne")}
+
+
 def BATselect(b: BAT, s: BAT | None, tl, th, li: bool, hi: bool, anti: bool, nil_matches: bool = False) -> BAT:
     st = _storage(b.ttype)
-    vl, vh = _val(st, tl), _val(st, th)
-    return BAT(lib.b200_BATselect(b._p, _ptr(s), _vp(vl), _vp(vh), li, hi, anti, nil_matches))
+    vl, vh = _valp(st, tl), _valp(st, th)
+    return BAT(lib.b200_BATselect(b._p, _ptr(s), vl[1], vh[1], li, hi, anti, nil_matches))
 
 
 def BATthetaselect(b: BAT, s: BAT | None, val, op: str) -> BAT:
-    v = _val(_storage(b.ttype), val)
-    return BAT(lib.b200_BATthetaselect(b._p, _ptr(s), _vp(v), op.encode()))
+    v = _valp(_storage(b.ttype), val)
+    return BAT(lib.b200_BATthetaselect(b._p, _ptr(s), v[1], _OPS.get(op) or op.encode()))
 
 
 def BATproject(l: BAT, r: BAT) -> BAT:
@@ -345,10 +371,10 @@ def BATcalc(op: str, b1: BAT, b2: BAT, s1: BAT | None, s2: BAT | None, tp: int) 
 
 def BATcalccst(op: str, b: BAT, v, vtype: int, s: BAT | None, tp: int, cst_first: bool = False) -> BAT:
     """BATcalc<op>cst (b OP v) or BATcalccst<op> (v OP b); the ValRecord is (value, type id)"""
-    a = _val(_storage(vtype), v)
+    a = _valp(_storage(vtype), v)
     if cst_first:
-        return BAT(getattr(lib, f"b200_BATcalccst{op}")(_vp(a), vtype, b._p, _ptr(s), tp))
-    return BAT(getattr(lib, f"b200_BATcalc{op}cst")(b._p, _vp(a), vtype, _ptr(s), tp))
+        return BAT(getattr(lib, f"b200_BATcalccst{op}")(a[1], vtype, b._p, _ptr(s), tp))
+    return BAT(getattr(lib, f"b200_BATcalc{op}cst")(b._p, a[1], vtype, _ptr(s), tp))
 
 
 def BATcalcadd(b1, b2, s1, s2, tp): return BATcalc("add", b1, b2, s1, s2, tp)
