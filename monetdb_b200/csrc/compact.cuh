@@ -77,6 +77,56 @@ compact_mask_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__r
 		counts[blockIdx.x] = total;
 }
 
+// ---- step 1 for two-level functors (a candidate-list gather): F additionally has
+//        K    fetch(uint64_t idx)      first-level load (the candidate oid)
+//        V    gather(K k)              second-level load (the column value)
+//        bool test(V v)                the predicate
+// All first-level loads of a thread's U steps are issued before the second-level ones and those
+// before any ballot/store, so U dependent load chains are in flight per thread instead of one
+// (the store to words[] otherwise orders every iteration behind the previous one).
+template <int CHUNK, typename F>
+__global__ void __launch_bounds__(CP_THREADS)
+compact_mask2_kernel(uint64_t n, F f, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
+{
+	__shared__ unsigned total;
+	if (threadIdx.x == 0)
+		total = 0;
+	__syncthreads();
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t cbase = (uint64_t) blockIdx.x * CHUNK;
+	unsigned cnt = 0;		/* warp-uniform */
+	constexpr int U = 8;
+	static_assert((CHUNK / CP_THREADS) % U == 0, "chunk steps must be a multiple of the unroll");
+	for (int j0 = 0; j0 < CHUNK / CP_THREADS; j0 += U) {
+		decltype(f.fetch(0)) k[U];
+		decltype(f.gather(k[0])) v[U];
+		uint64_t idx[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			idx[u] = cbase + (uint64_t) ((j0 + u) * (CP_THREADS / 32) + warp) * 32 + lane;
+			if (idx[u] < n)
+				k[u] = f.fetch(idx[u]);
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++)
+			if (idx[u] < n)
+				v[u] = f.gather(k[u]);
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const bool h = idx[u] < n && f.test(v[u]);
+			const unsigned bal = __ballot_sync(0xffffffffu, h);
+			if (lane == 0)
+				words[idx[u] >> 5] = bal;
+			cnt += __popc(bal);
+		}
+	}
+	if (lane == 0 && cnt)
+		atomicAdd(&total, cnt);
+	__syncthreads();
+	if (threadIdx.x == 0)
+		counts[blockIdx.x] = total;
+}
+
 // ---- step 2: exclusive scan of the chunk counts by one CTA; total -> slot[0].
 // Every thread owns a contiguous run of counts, so all its loads are independent.
 static __global__ void __launch_bounds__(1024)
@@ -284,6 +334,29 @@ template <typename F> struct FunctorOid {
 	F f;
 	__device__ __forceinline__ oid at(uint64_t idx) const { return f.at(idx); }
 };
+
+// driver for two-level (gather) functors
+template <typename F>
+static bool run_compact_gather(uint64_t n, F f, oid *dst, CompactResult &res)
+{
+	Ctx *c = ctx();
+	if (n == 0) {
+		res = CompactResult();
+		return true;
+	}
+	CompactScratch s;
+	if (!compact_scratch(n, s))
+		return false;
+	{
+		KTimer kt("compact", n * 8);
+		if (s.chunk == CP_CHUNK)
+			compact_mask2_kernel<CP_CHUNK, F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+		else
+			compact_mask2_kernel<CP_CHUNK_SMALL, F><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f, s.words, s.counts);
+		COUNT_LAUNCH();
+	}
+	return compact_finish(s, FunctorOid<F>{f}, dst, res);
+}
 
 // generic driver (the ITEMS parameter of the first version is kept for the call sites)
 template <int ITEMS, typename F>

@@ -246,6 +246,10 @@ template <typename T> struct GatherPredF {
 		return pred(col[o - hseq]);
 	}
 	__device__ __forceinline__ oid at(uint64_t idx) const { return cand[idx]; }
+	/* two-level form (compact_mask2_kernel) */
+	__device__ __forceinline__ oid fetch(uint64_t idx) const { return __ldcs(cand + idx); }
+	__device__ __forceinline__ T gather(oid o) const { return col[o - hseq]; }
+	__device__ __forceinline__ bool test(T v) const { return pred(v); }
 };
 
 // ---------------------------------------------------------------- typed driver
@@ -350,7 +354,7 @@ static bool select_typed(const SelArgs &a, b200_bat **out)
 		ok = run_select_dense<T>((const T *) a.b->base, ci.seq - ci.hseq, ci.ncand, ci.seq, pred, dst, r);
 	} else {
 		GatherPredF<T> f{(const T *) a.b->base, ci.oids, ci.hseq, pred};
-		ok = run_compact<8>(ci.ncand, f, dst, r);
+		ok = run_compact_gather(ci.ncand, f, dst, r);
 	}
 	if (!ok) {
 		dev_free(dst);
