@@ -173,10 +173,27 @@ b200_bat *b200_BATgroupavg3combine(const b200_bat *avg, const b200_bat *rem, con
 b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, double *avg, uint64_t *vals, int scale);
 b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
 
+/* BATunique (gdk.h:2279, gdk_unique.c:30): candidate list of the first row of each distinct value of b within s */
+b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s);
+
 /* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */
 b200_return b200_BAThash(const b200_bat *b);
 b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
 			 const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate);
+/* the leftjoin family (gdk.h:2254-2265; gdk_join.c:4049 leftjoin and its flag wrappers :4320-4405).  r1 is
+ * always in l's candidate order.  semijoin/intersect/diff return r1 as a candidate list (dense when contiguous);
+ * outerjoin writes oid_nil into r2 for left rows without a match; match_one / max_one violations fail with
+ * "more than one match" / "not enough matches" like the reference's hashjoin (:2759-2762,2869-2871). */
+b200_return b200_BATleftjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+			     const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate);
+b200_return b200_BATouterjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+			      const b200_bat *sl, const b200_bat *sr, bool nil_matches, bool match_one, uint64_t estimate);
+b200_return b200_BATsemijoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+			     const b200_bat *sl, const b200_bat *sr, bool nil_matches, bool max_one, uint64_t estimate);
+b200_bat *b200_BATintersect(const b200_bat *l, const b200_bat *r, const b200_bat *sl, const b200_bat *sr,
+			    bool nil_matches, bool max_one, uint64_t estimate);
+b200_bat *b200_BATdiff(const b200_bat *l, const b200_bat *r, const b200_bat *sl, const b200_bat *sr,
+		       bool nil_matches, bool not_in, uint64_t estimate);
 
 /* ---- the one exchange step of the multi-GPU path (no reference counterpart: mitosis only slices by row
  *      range, opt_mitosis.c:188-214): split (key, oid) tuples by hash(key) mod nparts into nparts

@@ -841,3 +841,16 @@ bailout:
 		b200_BATfree(hn);
 	return B200_FAIL;
 }
+
+// BATunique (gdk_unique.c:30-): candidate list of the first row of every distinct tail value —
+// "essentially the same output as the extents output of BATgroup" (gdk_unique.c:19-22), so it is
+// the first-row table + bitmap passes of BATgroup; the ids are dropped.
+extern "C" b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s)
+{
+	b200_bat *g = nullptr, *e = nullptr;
+	if (b200_BATgroup(&g, &e, nullptr, b, s, nullptr, nullptr, nullptr) != B200_SUCCEED)
+		return nullptr;
+	b200_BATfree(g);
+	ctx()->algo = "unique: cuda first-row table (BATgroup extents)";
+	return e;
+}

@@ -33,11 +33,14 @@ struct HashIdx {
 
 template <typename T>
 __global__ void __launch_bounds__(JN_THREADS)
-join_build_kernel(ColSrc<T> r, bool skip_nil, uint32_t *__restrict__ head, uint32_t *__restrict__ next, u64 mask)
+join_build_kernel(ColSrc<T> r, bool skip_nil, uint32_t *__restrict__ head, uint32_t *__restrict__ next, u64 mask,
+		  unsigned *__restrict__ nilseen /* optional: set when r holds a nil (NOT IN, gdk_join.c:3027-3060) */)
 {
 	typedef typename KeyBits<T>::type U;
 	for (uint64_t i = (uint64_t) blockIdx.x * JN_THREADS + threadIdx.x; i < r.n; i += (uint64_t) gridDim.x * JN_THREADS) {
 		const T v = r.value(i);
+		if (nilseen && Atom<T>::is_nil(v))
+			*nilseen = 1;
 		if (skip_nil && Atom<T>::is_nil(v)) {
 			next[i] = JN_END;
 			continue;
@@ -47,19 +50,30 @@ join_build_kernel(ColSrc<T> r, bool skip_nil, uint32_t *__restrict__ head, uint3
 	}
 }
 
-// pass 1: matches per left row (+ the first one met), total per chunk
+// The flags of the reference's leftjoin (gdk_join.c:4033-4052) as one word.
+enum { JM_NIL_MATCHES = 1, JM_NIL_ON_MISS = 2, JM_SEMI = 4, JM_ONLY_MISSES = 8, JM_NOT_IN = 16, JM_MAX_ONE = 32, JM_MIN_ONE = 64 };
+/* flags[] words written by the kernels */
+enum { JF_MULTI = 0 /* a left row produced more than one pair */, JF_ERR = 1 /* 1: more than one match, 2: not enough matches */,
+       JF_MISS = 2 /* an outer-join row without match (r2 holds a nil) */, JF_RNIL = 3 /* build side holds a nil */ };
+
+// pass 1: result rows per left row (+ the first match met), total per chunk.  One row of l is
+// the body of the reference's HASHJOIN loop (gdk_join.c:2781-2895): nil handling, the walk of
+// the chain, then the semi / only_misses / nil_on_miss / max_one / min_one rules on the count.
 template <typename T>
 __global__ void __launch_bounds__(JN_THREADS)
-join_count_kernel(ColSrc<T> l, ColSrc<T> r, bool nil_matches, const uint32_t *__restrict__ head,
+join_count_kernel(ColSrc<T> l, ColSrc<T> r, unsigned mode, const uint32_t *__restrict__ head,
 		  const uint32_t *__restrict__ next, u64 mask, uint32_t *__restrict__ cnt, uint32_t *__restrict__ first,
-		  unsigned long long *__restrict__ chunktot)
+		  unsigned long long *__restrict__ chunktot, unsigned *__restrict__ flags)
 {
 	typedef typename KeyBits<T>::type U;
 	__shared__ unsigned long long total;
 	if (threadIdx.x == 0)
 		total = 0;
 	__syncthreads();
+	const bool stop_at_first = (mode & JM_ONLY_MISSES) || ((mode & JM_SEMI) && !(mode & JM_MAX_ONE));
 	unsigned long long mine = 0;
+	unsigned err = 0;
+	bool missed = false;
 #pragma unroll
 	for (int j = 0; j < JN_ROWS; j++) {
 		const uint64_t k = (uint64_t) blockIdx.x * JN_CHUNK + j * JN_THREADS + threadIdx.x;
@@ -67,20 +81,44 @@ join_count_kernel(ColSrc<T> l, ColSrc<T> r, bool nil_matches, const uint32_t *__
 			break;
 		const T v = l.value(k);
 		unsigned c = 0, f = JN_END;
-		if (nil_matches || !Atom<T>::is_nil(v)) {
+		const bool nilrow = (!(mode & JM_NIL_MATCHES) || (mode & JM_NOT_IN)) && Atom<T>::is_nil(v);
+		if (!nilrow) {
 			const U kv = KeyBits<T>::get(v);
 			for (uint32_t p = __ldg(head + (hash_key<U>(kv, 0) & mask)); p != JN_END; p = __ldg(next + p)) {
 				if (KeyBits<T>::get(r.value(p)) == kv) {
 					if (c == 0)
 						f = p;
 					c++;
+					if (stop_at_first)
+						break;
 				}
+			}
+		}
+		if (mode & (JM_NIL_ON_MISS | JM_SEMI | JM_ONLY_MISSES | JM_MAX_ONE | JM_MIN_ONE)) {
+			if (c > 1 && (mode & JM_MAX_ONE))
+				err |= 1;
+			if (mode & JM_ONLY_MISSES) {
+				c = (c == 0 && !(nilrow && (mode & JM_NOT_IN))) ? 1 : 0;
+				f = JN_END;
+			} else if (c == 0) {
+				if (mode & JM_NIL_ON_MISS) {
+					c = 1;
+					missed = true;
+				} else if (mode & JM_MIN_ONE) {
+					err |= 2;
+				}
+			} else if (mode & JM_SEMI) {
+				c = 1;
 			}
 		}
 		cnt[k] = c;
 		first[k] = f;
 		mine += c;
 	}
+	if (err)
+		atomicOr(flags + JF_ERR, err);
+	if (missed)
+		flags[JF_MISS] = 1;
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1)
 		mine += __shfl_xor_sync(0xffffffffu, mine, o);
@@ -94,7 +132,7 @@ join_count_kernel(ColSrc<T> l, ColSrc<T> r, bool nil_matches, const uint32_t *__
 // exclusive scan of the chunk totals by one CTA; grand total -> offs[nchunks] and slot[0]
 __global__ void __launch_bounds__(1024)
 join_scan_kernel(const unsigned long long *__restrict__ tot, uint64_t nchunks, unsigned long long *__restrict__ offs,
-		 unsigned long long *__restrict__ slot)
+		 unsigned long long *__restrict__ slot, const unsigned *__restrict__ flags)
 {
 	__shared__ unsigned long long wsum[32];
 	__shared__ unsigned long long itertotal;
@@ -135,6 +173,8 @@ join_scan_kernel(const unsigned long long *__restrict__ tot, uint64_t nchunks, u
 	if (threadIdx.x == 0) {
 		offs[nchunks] = carry;
 		slot[0] = carry;
+		slot[1] = flags[JF_ERR];
+		slot[2] = flags[JF_MISS];
 	}
 }
 
@@ -182,7 +222,7 @@ join_fill_kernel(ColSrc<T> l, ColSrc<T> r, const uint32_t *__restrict__ next, co
 		if (c[j] == 1) {
 			r1[pos] = lo;
 			if (r2)
-				r2[pos] = r.rowoid(p);
+				r2[pos] = p == JN_END ? OID_NIL : r.rowoid(p);	/* nil_on_miss */
 			pos++;
 			continue;
 		}
@@ -198,7 +238,7 @@ join_fill_kernel(ColSrc<T> l, ColSrc<T> r, const uint32_t *__restrict__ next, co
 		}
 	}
 	if (__syncthreads_or(multi) && threadIdx.x == 0)
-		flags[0] = 1;
+		flags[JF_MULTI] = 1;
 }
 
 // ---------------------------------------------------------------- hash index cache (BAThash)
@@ -228,7 +268,7 @@ static inline u64 hash_pow2(u64 x)
 	return p;
 }
 
-template <typename T> static bool hash_build(const ColSrc<T> &r, bool skip_nil, HashIdx &h)
+template <typename T> static bool hash_build(const ColSrc<T> &r, bool skip_nil, HashIdx &h, unsigned *nilseen = nullptr)
 {
 	Ctx *c = ctx();
 	h.n = r.n;
@@ -241,21 +281,21 @@ template <typename T> static bool hash_build(const ColSrc<T> &r, bool skip_nil, 
 	if (r.n == 0)
 		return true;
 	KTimer kt("hash_build", r.n * (sizeof(T) + 8));
-	join_build_kernel<T><<<grid_for(r.n, JN_THREADS, NSM * 16), JN_THREADS, 0, c->stream>>>(r, skip_nil, h.head, h.next, h.mask);
+	join_build_kernel<T><<<grid_for(r.n, JN_THREADS, NSM * 16), JN_THREADS, 0, c->stream>>>(r, skip_nil, h.head, h.next, h.mask, nilseen);
 	COUNT_LAUNCH();
 	return cuda_ok(cudaGetLastError(), "hash build launch");
 }
 
-static bool hash_build_any(int t, const b200_bat *b, const Cand &ci, bool skip_nil, HashIdx &h)
+static bool hash_build_any(int t, const b200_bat *b, const Cand &ci, bool skip_nil, HashIdx &h, unsigned *nilseen = nullptr)
 {
 	switch (t) {
-	case B200_bte: return hash_build<bte>(col_src<bte>(b, ci), skip_nil, h);
-	case B200_sht: return hash_build<sht>(col_src<sht>(b, ci), skip_nil, h);
-	case B200_int: return hash_build<int>(col_src<int>(b, ci), skip_nil, h);
-	case B200_lng: return hash_build<lng>(col_src<lng>(b, ci), skip_nil, h);
-	case B200_hge: return hash_build<hge>(col_src<hge>(b, ci), skip_nil, h);
-	case B200_flt: return hash_build<flt>(col_src<flt>(b, ci), skip_nil, h);
-	case B200_dbl: return hash_build<dbl>(col_src<dbl>(b, ci), skip_nil, h);
+	case B200_bte: return hash_build<bte>(col_src<bte>(b, ci), skip_nil, h, nilseen);
+	case B200_sht: return hash_build<sht>(col_src<sht>(b, ci), skip_nil, h, nilseen);
+	case B200_int: return hash_build<int>(col_src<int>(b, ci), skip_nil, h, nilseen);
+	case B200_lng: return hash_build<lng>(col_src<lng>(b, ci), skip_nil, h, nilseen);
+	case B200_hge: return hash_build<hge>(col_src<hge>(b, ci), skip_nil, h, nilseen);
+	case B200_flt: return hash_build<flt>(col_src<flt>(b, ci), skip_nil, h, nilseen);
+	case B200_dbl: return hash_build<dbl>(col_src<dbl>(b, ci), skip_nil, h, nilseen);
 	}
 	set_err("BAThash: unsupported tail type %s (fixed-width atoms only)\n", atomname(t));
 	return false;
@@ -299,10 +339,10 @@ extern "C" b200_return b200_BAThash(const b200_bat *b)
 	return B200_SUCCEED;
 }
 
-// ---------------------------------------------------------------- BATjoin
+// ---------------------------------------------------------------- BATjoin and the leftjoin family
 template <typename T>
-static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, const Cand &rci, bool nil_matches,
-		       const HashIdx &h, b200_bat **r1p, b200_bat **r2p)
+static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, const Cand &rci, unsigned mode,
+		       const HashIdx &h, unsigned *flags, b200_bat **r1p, b200_bat **r2p, const char *func)
 {
 	Ctx *c = ctx();
 	const ColSrc<T> ls = col_src<T>(l, lci), rs = col_src<T>(r, rci);
@@ -310,23 +350,30 @@ static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, co
 	uint32_t *cnt = (uint32_t *) dev_alloc(nl * 4), *first = (uint32_t *) dev_alloc(nl * 4);
 	unsigned long long *tot = (unsigned long long *) dev_alloc(nchunks * 8);
 	unsigned long long *offs = (unsigned long long *) dev_alloc((nchunks + 1) * 8);
-	unsigned *flags = (unsigned *) dev_alloc(16);
 	b200_bat *r1 = nullptr, *r2 = nullptr;
-	bool ok = false;
+	bool ok = false, missed = false;
 	uint64_t total = 0;
-	if (cnt == nullptr || first == nullptr || tot == nullptr || offs == nullptr || flags == nullptr ||
-	    !cuda_ok(cudaMemsetAsync(flags, 0, 16, c->stream), "memset flags"))
+	if (cnt == nullptr || first == nullptr || tot == nullptr || offs == nullptr)
 		goto done;
 	{
 		KTimer kt("join_probe", nl * (sizeof(T) + 4 + 4 + sizeof(T) + 8));
-		join_count_kernel<T><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, rs, nil_matches, h.head, h.next, h.mask, cnt, first, tot);
+		join_count_kernel<T><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, rs, mode, h.head, h.next, h.mask, cnt, first, tot, flags);
 	}
 	COUNT_LAUNCH();
-	join_scan_kernel<<<1, 1024, 0, c->stream>>>(tot, nchunks, offs, c->slot_d->v);
+	join_scan_kernel<<<1, 1024, 0, c->stream>>>(tot, nchunks, offs, c->slot_d->v, flags);
 	COUNT_LAUNCH();
 	if (!cuda_ok(cudaGetLastError(), "join probe launch") || !stream_sync())
 		goto done;
 	total = c->slot_h->v[0];
+	if (c->slot_h->v[1] & 1) {
+		set_err("%s: more than one match\n", func);	/* HASHLOOPBODY, gdk_join.c:2759-2762 */
+		goto done;
+	}
+	if (c->slot_h->v[1] & 2) {
+		set_err("%s: not enough matches\n", func);	/* gdk_join.c:2869-2871 */
+		goto done;
+	}
+	missed = c->slot_h->v[2] != 0;
 	r1 = bat_new(0, B200_oid, total);
 	if (r1 == nullptr)
 		goto done;
@@ -342,25 +389,42 @@ static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, co
 											      r2 ? (oid *) r2->base : nullptr, flags);
 		}
 		COUNT_LAUNCH();
-		if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, flags, 8, cudaMemcpyDeviceToHost, c->stream), "read flags") || !stream_sync())
+		if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, flags, 8, cudaMemcpyDeviceToHost, c->stream), "read flags") ||
+		    !cuda_ok(cudaMemcpyAsync(c->slot_h->v + 1, r1->base, 8, cudaMemcpyDeviceToHost, c->stream), "read first oid") ||
+		    !cuda_ok(cudaMemcpyAsync(c->slot_h->v + 2, (oid *) r1->base + (total - 1), 8, cudaMemcpyDeviceToHost, c->stream), "read last oid") ||
+		    !stream_sync())
 			goto done;
 	}
 	{
 		const bool multi = total > 0 && (unsigned) c->slot_h->v[0] != 0;
-		/* result properties (gdk_join.c:2877-2893,3260-3296): left-major output in candidate order */
-		r1->count = total;
-		r1->tsorted = 1;
-		r1->trevsorted = total <= 1;
-		r1->tkey = !multi;
-		r1->tnonil = 1;
-		r1->tnil = 0;
-		r1->tseqbase = total == 0 ? 0 : OID_NIL;
+		const oid lo = total ? c->slot_h->v[1] : 0, hi = total ? c->slot_h->v[2] : 0;
+		if (!multi && (mode & (JM_SEMI | JM_ONLY_MISSES)) && r2 == nullptr && (total == 0 || hi - lo + 1 == total)) {
+			/* virtualize(*r1p) for semi / only_misses results (gdk_join.c:4311-4312) */
+			b200_BATfree(r1);
+			r1 = bat_dense(0, lo, total);
+			if (r1 == nullptr)
+				goto done;
+		} else {
+			/* result properties (gdk_join.c:2877-2893,3260-3296): left-major output in candidate order */
+			r1->count = total;
+			r1->tsorted = 1;
+			r1->trevsorted = total <= 1;
+			r1->tkey = !multi;
+			r1->tnonil = 1;
+			r1->tnil = 0;
+			r1->tseqbase = total == 0 ? 0 : OID_NIL;
+			if (total > 0) {
+				r1->oidrange_known = 1;
+				r1->first_oid = lo;
+				r1->last_oid = hi;
+			}
+		}
 		if (r2) {
 			r2->count = total;
 			r2->tsorted = r2->trevsorted = total <= 1;
 			r2->tkey = total <= 1;
-			r2->tnonil = 1;
-			r2->tnil = 0;
+			r2->tnonil = !missed;
+			r2->tnil = missed;
 			r2->tseqbase = total == 0 ? 0 : OID_NIL;
 		}
 	}
@@ -370,7 +434,6 @@ done:
 	dev_free(first);
 	dev_free(tot);
 	dev_free(offs);
-	dev_free(flags);
 	if (!ok) {
 		if (r1)
 			b200_BATfree(r1);
@@ -384,17 +447,52 @@ done:
 	return true;
 }
 
-extern "C" b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
-				    const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate)
+// nomatch (gdk_join.c:302-360): nothing on one side.  Inner / semi joins are empty; an outer join
+// returns every candidate of l beside a nil, a difference returns every candidate of l.
+static b200_return join_nomatch(b200_bat **r1p, b200_bat **r2p, const Cand &lci, unsigned mode)
 {
-	(void) estimate;	/* a size hint for the reference's growing result; sizes are exact here */
+	ctx()->algo = "join: nomatch";
+	if (lci.ncand == 0 || !(mode & (JM_NIL_ON_MISS | JM_ONLY_MISSES))) {
+		*r1p = bat_dense(0, 0, 0);
+		if (r2p)
+			*r2p = bat_dense(0, 0, 0);
+	} else {
+		*r1p = cand_to_bat(lci);
+		if (r2p)
+			*r2p = bat_dense(0, OID_NIL, lci.ncand);	/* BATconstant(0, TYPE_void, &oid_nil, ncand) */
+		if (r2p && *r2p) {
+			(*r2p)->tsorted = (*r2p)->trevsorted = 1;
+			(*r2p)->tkey = lci.ncand <= 1;
+			(*r2p)->tnonil = 0;
+			(*r2p)->tnil = 1;
+			(*r2p)->oidrange_known = 0;
+		}
+	}
+	if (*r1p == nullptr || (r2p && *r2p == nullptr)) {
+		if (*r1p)
+			b200_BATfree(*r1p);
+		*r1p = nullptr;
+		if (r2p && *r2p) {
+			b200_BATfree(*r2p);
+			*r2p = nullptr;
+		}
+		return B200_FAIL;
+	}
+	return B200_SUCCEED;
+}
+
+// The shared driver: BATjoin (gdk_join.c:4451) and leftjoin (:4049) both end in hashjoin with a
+// flag set; on the device every flag combination runs the same build + count/scan/fill plan.
+static b200_return join_driver(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r, const b200_bat *sl,
+			       const b200_bat *sr, unsigned mode, const char *func)
+{
 	b200_clrerr();
 	if (r1p)
 		*r1p = nullptr;
 	if (r2p)
 		*r2p = nullptr;
 	if (r1p == nullptr || l == nullptr || r == nullptr) {
-		set_err("BATjoin: l, r and r1p required\n");
+		set_err("%s: l, r and r1p required\n", func);
 		return B200_FAIL;
 	}
 	Staged stl, str_, stsl, stsr;
@@ -403,35 +501,28 @@ extern "C" b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_b
 	const b200_bat *lb = stl.b, *rb = str_.b;
 	const int t = basetype(lb->ttype);
 	if (t != basetype(rb->ttype)) {
-		/* joininitresults / BATjoin: ATOMtype(l->ttype) == ATOMtype(r->ttype) asserted (gdk_join.c:3890) */
-		set_err("BATjoin: inputs not compatible (%s vs %s).\n", atomname(lb->ttype), atomname(rb->ttype));
+		/* joinparamcheck: ATOMtype(l->ttype) == ATOMtype(r->ttype) (gdk_join.c:3890) */
+		set_err("%s: inputs not compatible (%s vs %s).\n", func, atomname(lb->ttype), atomname(rb->ttype));
 		return B200_FAIL;
 	}
 	Cand lci, rci;
 	if (!cand_init(lci, lb, stsl.b) || !cand_init(rci, rb, stsr.b))
 		return B200_FAIL;
-	if (lci.ncand == 0 || rci.ncand == 0) {
-		/* nomatch (gdk_join.c:302-360) */
-		ctx()->algo = "join: nomatch";
-		*r1p = bat_dense(0, 0, 0);
-		if (r2p)
-			*r2p = bat_dense(0, 0, 0);
-		if (*r1p == nullptr || (r2p && *r2p == nullptr))
-			return B200_FAIL;
-		return B200_SUCCEED;
-	}
+	if (lci.ncand == 0 || rci.ncand == 0)
+		return join_nomatch(r1p, r2p, lci, mode);
 	if (lb->ttype == B200_void || rb->ttype == B200_void) {
-		set_err("BATjoin: void columns are not on the device path\n");
+		set_err("%s: void columns are not on the device path\n", func);
 		return B200_FAIL;
 	}
 	if (lci.ncand >= JN_END || rci.ncand >= JN_END) {
-		set_err("BATjoin: more than 2^32-1 rows in one device call\n");
+		set_err("%s: more than 2^32-1 rows in one device call\n", func);
 		return B200_FAIL;
 	}
+	const bool nil_matches = (mode & JM_NIL_MATCHES) != 0, not_in = (mode & JM_NOT_IN) != 0;
 	/* a cached whole-BAT hash (BAThash) can serve when r is used without candidates */
 	HashIdx h;
 	bool owned = true;
-	if (stsr.b == nullptr && rb == r) {
+	if (stsr.b == nullptr && rb == r && !not_in) {
 		std::lock_guard<std::mutex> lk(g_hash_mu);
 		auto it = g_hash_cache.find(rb->base);
 		if (it != g_hash_cache.end() && it->second.n == rb->count) {
@@ -440,24 +531,98 @@ extern "C" b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_b
 		}
 	}
 	ctx()->algo = owned ? "join: cuda hashjoin (build + probe)" : "join: cuda hashjoin (existing hash)";
-	bool ok = true;
-	if (owned)
-		ok = hash_build_any(t, rb, rci, !nil_matches, h);
-	if (ok) {
+	unsigned *flags = (unsigned *) dev_alloc(16);
+	bool ok = flags != nullptr && cuda_ok(cudaMemsetAsync(flags, 0, 16, ctx()->stream), "memset flags");
+	bool empty = false;
+	if (ok && owned)
+		ok = hash_build_any(t, rb, rci, !nil_matches || not_in, h, not_in ? flags + JF_RNIL : nullptr);
+	if (ok && not_in) {
+		/* NOT IN with a nil on the right: no row qualifies (gdk_join.c:3027-3060) */
+		Ctx *c = ctx();
+		ok = cuda_ok(cudaMemcpyAsync(c->slot_h->v, flags + JF_RNIL, 4, cudaMemcpyDeviceToHost, c->stream), "read nil flag") && stream_sync();
+		empty = ok && (unsigned) c->slot_h->v[0] != 0;
+	}
+	b200_return rc = B200_FAIL;
+	if (ok && empty) {
+		rc = join_nomatch(r1p, r2p, lci, 0);
+	} else if (ok) {
 		switch (t) {
-		case B200_bte: ok = join_typed<bte>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_sht: ok = join_typed<sht>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_int: ok = join_typed<int>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_lng: ok = join_typed<lng>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_hge: ok = join_typed<hge>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_flt: ok = join_typed<flt>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
-		case B200_dbl: ok = join_typed<dbl>(lb, rb, lci, rci, nil_matches, h, r1p, r2p); break;
+		case B200_bte: ok = join_typed<bte>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_sht: ok = join_typed<sht>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_int: ok = join_typed<int>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_lng: ok = join_typed<lng>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_hge: ok = join_typed<hge>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_flt: ok = join_typed<flt>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
+		case B200_dbl: ok = join_typed<dbl>(lb, rb, lci, rci, mode, h, flags, r1p, r2p, func); break;
 		default: ok = false;
 		}
+		rc = ok ? B200_SUCCEED : B200_FAIL;
 	}
+	dev_free(flags);
 	if (owned) {
 		dev_free(h.head);
 		dev_free(h.next);
 	}
-	return ok ? B200_SUCCEED : B200_FAIL;
+	return rc;
+}
+
+extern "C" b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+				    const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate)
+{
+	(void) estimate;	/* a size hint for the reference's growing result; sizes are exact here */
+	return join_driver(r1p, r2p, l, r, sl, sr, nil_matches ? JM_NIL_MATCHES : 0, "BATjoin");
+}
+
+/* gdk_join.c:4320: same pairs as BATjoin, r1 guaranteed in l's order (ours always is) */
+extern "C" b200_return b200_BATleftjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+					const b200_bat *sl, const b200_bat *sr, bool nil_matches, uint64_t estimate)
+{
+	(void) estimate;
+	return join_driver(r1p, r2p, l, r, sl, sr, nil_matches ? JM_NIL_MATCHES : 0, "BATleftjoin");
+}
+
+/* gdk_join.c:4334: nil_on_miss; match_one = exactly one match per left row or GDKerror */
+extern "C" b200_return b200_BATouterjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+					 const b200_bat *sl, const b200_bat *sr, bool nil_matches, bool match_one, uint64_t estimate)
+{
+	(void) estimate;
+	if (r2p == nullptr) {
+		set_err("BATouterjoin: r2p required\n");	/* assert(!nil_on_miss || r2p != NULL), gdk_join.c:4065 */
+		return B200_FAIL;
+	}
+	return join_driver(r1p, r2p, l, r, sl, sr,
+			   (nil_matches ? JM_NIL_MATCHES : 0) | JM_NIL_ON_MISS | (match_one ? JM_MAX_ONE | JM_MIN_ONE : 0), "BATouterjoin");
+}
+
+/* gdk_join.c:4347: at most one pair per left row */
+extern "C" b200_return b200_BATsemijoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,
+					const b200_bat *sl, const b200_bat *sr, bool nil_matches, bool max_one, uint64_t estimate)
+{
+	(void) estimate;
+	return join_driver(r1p, r2p, l, r, sl, sr, (nil_matches ? JM_NIL_MATCHES : 0) | JM_SEMI | (max_one ? JM_MAX_ONE : 0), "BATsemijoin");
+}
+
+/* gdk_join.c:4378: candidate list of the rows of l whose value occurs in r */
+extern "C" b200_bat *b200_BATintersect(const b200_bat *l, const b200_bat *r, const b200_bat *sl, const b200_bat *sr,
+				       bool nil_matches, bool max_one, uint64_t estimate)
+{
+	(void) estimate;
+	b200_bat *bn = nullptr;
+	if (join_driver(&bn, nullptr, l, r, sl, sr, (nil_matches ? JM_NIL_MATCHES : 0) | JM_SEMI | (max_one ? JM_MAX_ONE : 0),
+			"BATintersect") != B200_SUCCEED)
+		return nullptr;
+	return bn;
+}
+
+/* gdk_join.c:4395: candidate list of the rows of l whose value does not occur in r (anti-semi-join);
+ * not_in = SQL's NOT IN: a nil on either side never qualifies */
+extern "C" b200_bat *b200_BATdiff(const b200_bat *l, const b200_bat *r, const b200_bat *sl, const b200_bat *sr,
+				  bool nil_matches, bool not_in, uint64_t estimate)
+{
+	(void) estimate;
+	b200_bat *bn = nullptr;
+	if (join_driver(&bn, nullptr, l, r, sl, sr, (nil_matches ? JM_NIL_MATCHES : 0) | JM_ONLY_MISSES | (not_in ? JM_NOT_IN : 0),
+			"BATdiff") != B200_SUCCEED)
+		return nullptr;
+	return bn;
 }

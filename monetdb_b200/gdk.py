@@ -452,6 +452,71 @@ def BATjoin(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_ma
     return BAT(p1), (BAT(p2) if want_r2 else None)
 
 
+_sig("b200_BATleftjoin", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_bool, C.c_uint64)
+_sig("b200_BATouterjoin", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_bool, C.c_bool, C.c_uint64)
+_sig("b200_BATsemijoin", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_bool, C.c_bool, C.c_uint64)
+_sig("b200_BATintersect", _P, _P, _P, _P, _P, C.c_bool, C.c_bool, C.c_uint64)
+_sig("b200_BATdiff", _P, _P, _P, _P, _P, C.c_bool, C.c_bool, C.c_uint64)
+_sig("b200_BATunique", _P, _P, _P)
+
+
+def BATleftjoin(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+                estimate: int = BUN_NONE, want_r2: bool = True):
+    """BATleftjoin (gdk.h:2254) -> (r1, r2), r1 in l's order"""
+    p1, p2 = _P(), _P()
+    rc = lib.b200_BATleftjoin(C.byref(p1), C.byref(p2) if want_r2 else None, l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, estimate)
+    if rc != 1:
+        _fail("BATleftjoin")
+    return BAT(p1), (BAT(p2) if want_r2 else None)
+
+
+def BATouterjoin(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+                 match_one: bool = False, estimate: int = BUN_NONE):
+    """BATouterjoin (gdk.h:2258) -> (r1, r2); r2 holds oid_nil where a row of l has no match"""
+    p1, p2 = _P(), _P()
+    rc = lib.b200_BATouterjoin(C.byref(p1), C.byref(p2), l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, match_one, estimate)
+    if rc != 1:
+        _fail("BATouterjoin")
+    return BAT(p1), BAT(p2)
+
+
+def BATsemijoin(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+                max_one: bool = False, estimate: int = BUN_NONE, want_r2: bool = True):
+    """BATsemijoin (gdk.h:2262) -> (r1, r2): at most one pair per row of l"""
+    p1, p2 = _P(), _P()
+    rc = lib.b200_BATsemijoin(C.byref(p1), C.byref(p2) if want_r2 else None, l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, max_one,
+                              estimate)
+    if rc != 1:
+        _fail("BATsemijoin")
+    return BAT(p1), (BAT(p2) if want_r2 else None)
+
+
+def BATintersect(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+                 max_one: bool = False, estimate: int = BUN_NONE) -> BAT:
+    """BATintersect (gdk.h:2264) -> candidate list of the rows of l whose value occurs in r"""
+    p = lib.b200_BATintersect(l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, max_one, estimate)
+    if not p:
+        _fail("BATintersect")
+    return BAT(p)
+
+
+def BATdiff(l: BAT, r: BAT, sl: BAT | None = None, sr: BAT | None = None, nil_matches: bool = False,
+            not_in: bool = False, estimate: int = BUN_NONE) -> BAT:
+    """BATdiff (gdk.h:2265) -> candidate list of the rows of l whose value does not occur in r"""
+    p = lib.b200_BATdiff(l._p, r._p, _ptr(sl), _ptr(sr), nil_matches, not_in, estimate)
+    if not p:
+        _fail("BATdiff")
+    return BAT(p)
+
+
+def BATunique(b: BAT, s: BAT | None = None) -> BAT:
+    """BATunique (gdk.h:2279) -> candidate list of the first row of each distinct value"""
+    p = lib.b200_BATunique(b._p, _ptr(s))
+    if not p:
+        _fail("BATunique")
+    return BAT(p)
+
+
 # ------------------------------------------------------------------ aggregates
 for _n in ("sum", "count", "min", "max"):
     if hasattr(lib, f"b200_BATgroup{_n}"):

@@ -111,6 +111,12 @@ def _load(nthreads: int = 0):
         "BATcalcavg": (C.c_int, [P, P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
         "BATjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
         "BAThash": (C.c_int, [P]),
+        "BATleftjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
+        "BATouterjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, B, C.c_uint64]),
+        "BATsemijoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, B, C.c_uint64]),
+        "BATintersect": (P, [P, P, P, P, B, B, C.c_uint64]),
+        "BATdiff": (P, [P, P, P, P, B, B, C.c_uint64]),
+        "BATunique": (P, [P, P]),
         "BATconvert": (P, [P, P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8]),
         "BATcalcisnil": (P, [P, P]),
         "GDKanalyticaldiff": (C.c_int, [P, P, P, V, C.c_int]),
@@ -433,6 +439,48 @@ def BATjoin(l, r, sl=None, sr=None, nil_matches=False, estimate=BUN_NONE):
         clrerr()
         raise RefError(msg or "BATjoin failed")
     return RBAT(p1.value), RBAT(p2.value)
+
+
+def _join2(fn, what, l, r, sl, sr, *flags):
+    p1, p2 = C.c_void_p(), C.c_void_p()
+    rc = fn(C.byref(p1), C.byref(p2), l.p, r.p, _p(sl), _p(sr), *flags, BUN_NONE)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or what + " failed")
+    return RBAT(p1.value), RBAT(p2.value)
+
+
+def BATleftjoin(l, r, sl=None, sr=None, nil_matches=False):
+    return _join2(_bat.BATleftjoin, "BATleftjoin", l, r, sl, sr, nil_matches)
+
+
+def BATouterjoin(l, r, sl=None, sr=None, nil_matches=False, match_one=False):
+    return _join2(_bat.BATouterjoin, "BATouterjoin", l, r, sl, sr, nil_matches, match_one)
+
+
+def BATsemijoin(l, r, sl=None, sr=None, nil_matches=False, max_one=False):
+    return _join2(_bat.BATsemijoin, "BATsemijoin", l, r, sl, sr, nil_matches, max_one)
+
+
+def _cand1(p, what):
+    if not p:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or what + " failed")
+    return RBAT(p)
+
+
+def BATintersect(l, r, sl=None, sr=None, nil_matches=False, max_one=False):
+    return _cand1(_bat.BATintersect(l.p, r.p, _p(sl), _p(sr), nil_matches, max_one, BUN_NONE), "BATintersect")
+
+
+def BATdiff(l, r, sl=None, sr=None, nil_matches=False, not_in=False):
+    return _cand1(_bat.BATdiff(l.p, r.p, _p(sl), _p(sr), nil_matches, not_in, BUN_NONE), "BATdiff")
+
+
+def BATunique(b, s=None):
+    return _cand1(_bat.BATunique(b.p, _p(s)), "BATunique")
 
 
 def _ok(rc, what):
