@@ -173,6 +173,26 @@ b200_bat *b200_BATgroupavg3combine(const b200_bat *avg, const b200_bat *rem, con
 b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, double *avg, uint64_t *vals, int scale);
 b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
 
+/* ---- min/max, between, ifthenelse: gdk_calc.h:24-33,87-95 (gdk_calc.c:976-2300, 3968-4290, 4376-4800).
+ *      ValRecord arguments travel as (pointer to the atom, type id), as in the arithmetic cst forms. ---- */
+b200_bat *b200_BATcalcmin(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcmin_no_nil(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcmax(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcmax_no_nil(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcbetween(const b200_bat *b, const b200_bat *lo, const b200_bat *hi, const b200_bat *s,
+			      const b200_bat *slo, const b200_bat *shi, bool symmetric, bool linc, bool hinc,
+			      bool nils_false, bool anti);
+b200_bat *b200_BATcalcbetweencstcst(const b200_bat *b, const void *lo, int lotype, const void *hi, int hitype,
+				    const b200_bat *s, bool symmetric, bool linc, bool hinc, bool nils_false, bool anti);
+b200_bat *b200_BATcalcbetweenbatcst(const b200_bat *b, const b200_bat *lo, const void *hi, int hitype, const b200_bat *s,
+				    const b200_bat *slo, bool symmetric, bool linc, bool hinc, bool nils_false, bool anti);
+b200_bat *b200_BATcalcbetweencstbat(const b200_bat *b, const void *lo, int lotype, const b200_bat *hi, const b200_bat *s,
+				    const b200_bat *shi, bool symmetric, bool linc, bool hinc, bool nils_false, bool anti);
+b200_bat *b200_BATcalcifthenelse(const b200_bat *b, const b200_bat *b1, const b200_bat *b2);
+b200_bat *b200_BATcalcifthenelsecst(const b200_bat *b, const b200_bat *b1, const void *c2, int c2type);
+b200_bat *b200_BATcalcifthencstelse(const b200_bat *b, const void *c1, int c1type, const b200_bat *b2);
+b200_bat *b200_BATcalcifthencstelsecst(const b200_bat *b, const void *c1, int c1type, const void *c2, int c2type);
+
 /* BATunique (gdk.h:2279, gdk_unique.c:30): candidate list of the first row of each distinct value of b within s */
 b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s);
 

@@ -9,24 +9,11 @@
 // any flt -> flt, else the wider integer).  One streaming pass, 4 rows per
 // thread so the bit column is written 4 bytes at a time.
 #include "common.cuh"
+#include "operand.cuh"
 
 enum { CMP_LT = 0, CMP_LE, CMP_GT, CMP_GE, CMP_EQ, CMP_NE };
 #define BIT_NIL ((int8_t) -128)
 #define CMP_THREADS 256
-
-template <typename T> struct CmpOperand {
-	const T *vals;		/* dense: vals[k]; gather: vals[cand[k] - hseq]; constant: vals[0] (device copy) */
-	const oid *cand;
-	oid hseq;
-	bool cst;
-	T cval;
-	__device__ __forceinline__ T get(uint64_t k) const
-	{
-		if (cst)
-			return cval;
-		return cand ? vals[__ldcs(cand + k) - hseq] : ld_stream(vals + k);
-	}
-};
 
 template <typename A, typename B> struct Common {
 	typedef typename std::conditional<
@@ -112,33 +99,6 @@ isnil_kernel(CmpOperand<T> l, uint64_t n, int8_t *__restrict__ dst)
 	}
 }
 
-struct CmpSide {
-	const b200_bat *b;	/* NULL: constant */
-	const Cand *ci;
-	const void *cst;
-	int type;		/* storage type */
-};
-
-template <typename T> static CmpOperand<T> make_operand(const CmpSide &s)
-{
-	CmpOperand<T> o;
-	o.cand = nullptr;
-	o.hseq = 0;
-	o.cst = s.b == nullptr;
-	o.vals = nullptr;
-	o.cval = T();
-	if (o.cst) {
-		o.cval = *(const T *) s.cst;
-	} else if (s.ci->dense) {
-		o.vals = (const T *) s.b->base + (s.ci->seq - s.ci->hseq);
-	} else {
-		o.vals = (const T *) s.b->base;
-		o.cand = s.ci->oids;
-		o.hseq = s.ci->hseq;
-	}
-	return o;
-}
-
 template <typename T1, typename T2>
 static bool cmp_run(const CmpSide &s1, const CmpSide &s2, uint64_t n, int op, bool nonil, bool nil_matches, int8_t *dst,
 		    unsigned long long *nils_d)
@@ -181,20 +141,6 @@ static int cmp_dispatch(const CmpSide &s1, const CmpSide &s2, uint64_t n, int op
 	case B200_dbl: return cmp_dispatch2<dbl>(s1, s2, n, op, nonil, nil_matches, dst, nils_d);
 	}
 	return -1;
-}
-
-static bool cst_is_nil(int t, const void *v)
-{
-	switch (t) {
-	case B200_bte: return Atom<bte>::is_nil(*(const bte *) v);
-	case B200_sht: return Atom<sht>::is_nil(*(const sht *) v);
-	case B200_int: return Atom<int>::is_nil(*(const int *) v);
-	case B200_lng: return Atom<lng>::is_nil(*(const lng *) v);
-	case B200_hge: return Atom<hge>::is_nil(*(const hge *) v);
-	case B200_flt: return Atom<flt>::is_nil(*(const flt *) v);
-	case B200_dbl: return Atom<dbl>::is_nil(*(const dbl *) v);
-	}
-	return false;
 }
 
 // b2 == NULL: compare with the constant (cst, csttype)

@@ -417,6 +417,55 @@ def BATcalcisnil(b: BAT, s: BAT | None = None) -> BAT:
     return BAT(lib.b200_BATcalcisnil(b._p, _ptr(s)))
 
 
+# ------------------------------------------------------------------ min/max, between, ifthenelse (gdk_calc.h:24-33,87-95)
+for _n in ("min", "min_no_nil", "max", "max_no_nil"):
+    _sig(f"b200_BATcalc{_n}", _P, _P, _P, _P, _P)
+_B5 = (C.c_bool,) * 5
+_sig("b200_BATcalcbetween", _P, _P, _P, _P, _P, _P, _P, *_B5)
+_sig("b200_BATcalcbetweencstcst", _P, _P, C.c_void_p, C.c_int, C.c_void_p, C.c_int, _P, *_B5)
+_sig("b200_BATcalcbetweenbatcst", _P, _P, _P, C.c_void_p, C.c_int, _P, _P, *_B5)
+_sig("b200_BATcalcbetweencstbat", _P, _P, C.c_void_p, C.c_int, _P, _P, _P, *_B5)
+_sig("b200_BATcalcifthenelse", _P, _P, _P, _P)
+_sig("b200_BATcalcifthenelsecst", _P, _P, _P, C.c_void_p, C.c_int)
+_sig("b200_BATcalcifthencstelse", _P, _P, C.c_void_p, C.c_int, _P)
+_sig("b200_BATcalcifthencstelsecst", _P, _P, C.c_void_p, C.c_int, C.c_void_p, C.c_int)
+
+
+def BATcalcminmax(which: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
+    """BATcalcmin / min_no_nil / max / max_no_nil"""
+    return BAT(getattr(lib, f"b200_BATcalc{which}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))
+
+
+def BATcalcbetween(b: BAT, lo, hi, s: BAT | None = None, slo: BAT | None = None, shi: BAT | None = None,
+                   symmetric: bool = False, linc: bool = True, hinc: bool = True, nils_false: bool = False,
+                   anti: bool = False) -> BAT:
+    """BATcalcbetween and its batcst / cstbat / cstcst forms: lo and hi are BATs or plain values of b's type"""
+    fl = (symmetric, linc, hinc, nils_false, anti)
+    st = _storage(b.ttype)
+    lb, hb = isinstance(lo, BAT), isinstance(hi, BAT)
+    if lb and hb:
+        return BAT(lib.b200_BATcalcbetween(b._p, lo._p, hi._p, _ptr(s), _ptr(slo), _ptr(shi), *fl))
+    if lb:
+        return BAT(lib.b200_BATcalcbetweenbatcst(b._p, lo._p, _valp(st, hi)[1], b.ttype, _ptr(s), _ptr(slo), *fl))
+    if hb:
+        return BAT(lib.b200_BATcalcbetweencstbat(b._p, _valp(st, lo)[1], b.ttype, hi._p, _ptr(s), _ptr(shi), *fl))
+    return BAT(lib.b200_BATcalcbetweencstcst(b._p, _valp(st, lo)[1], b.ttype, _valp(st, hi)[1], b.ttype, _ptr(s), *fl))
+
+
+def BATcalcifthenelse(b: BAT, v1, v2, vtype: int | None = None) -> BAT:
+    """BATcalcifthenelse and its cst forms: v1 / v2 are BATs or plain values (of type vtype when both are values)"""
+    b1, b2 = isinstance(v1, BAT), isinstance(v2, BAT)
+    tt = v1.ttype if b1 else v2.ttype if b2 else vtype
+    st = _storage(tt)
+    if b1 and b2:
+        return BAT(lib.b200_BATcalcifthenelse(b._p, v1._p, v2._p))
+    if b1:
+        return BAT(lib.b200_BATcalcifthenelsecst(b._p, v1._p, _valp(st, v2)[1], tt))
+    if b2:
+        return BAT(lib.b200_BATcalcifthencstelse(b._p, _valp(st, v1)[1], tt, v2._p))
+    return BAT(lib.b200_BATcalcifthencstelsecst(b._p, _valp(st, v1)[1], tt, _valp(st, v2)[1], tt))
+
+
 # ------------------------------------------------------------------ grouping
 _sig("b200_BATgroup", C.c_int, _PP, _PP, _PP, _P, _P, _P, _P, _P)
 

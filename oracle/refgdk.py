@@ -111,6 +111,12 @@ def _load(nthreads: int = 0):
         "BATcalcavg": (C.c_int, [P, P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
         "BATjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
         "BAThash": (C.c_int, [P]),
+        "BATcalcmin": (P, [P, P, P, P]),
+        "BATcalcmin_no_nil": (P, [P, P, P, P]),
+        "BATcalcmax": (P, [P, P, P, P]),
+        "BATcalcmax_no_nil": (P, [P, P, P, P]),
+        "BATcalcbetween": (P, [P, P, P, P, P, P, B, B, B, B, B]),
+        "BATcalcifthenelse": (P, [P, P, P]),
         "BATleftjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
         "BATouterjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, B, C.c_uint64]),
         "BATsemijoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, B, C.c_uint64]),
@@ -343,6 +349,20 @@ def BATcalccmp(op, b1, b2, s1=None, s2=None, nil_matches=False) -> RBAT:
 def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False) -> RBAT:
     a = _val(vtype, v)
     return RBAT(_h.refh_cmp_cst(_CMPS[op], b.p, _vp(a), vtype, _p(s), nil_matches), "BATcalc" + op + "cst")
+
+
+def BATcalcminmax(which, b1, b2, s1=None, s2=None) -> RBAT:
+    return RBAT(getattr(_bat, "BATcalc" + which)(b1.p, b2.p, _p(s1), _p(s2)), "BATcalc" + which)
+
+
+def BATcalcbetween(b, lo, hi, s=None, slo=None, shi=None, symmetric=False, linc=True, hinc=True, nils_false=False,
+                   anti=False) -> RBAT:
+    return RBAT(_bat.BATcalcbetween(b.p, lo.p, hi.p, _p(s), _p(slo), _p(shi), symmetric, linc, hinc, nils_false, anti),
+                "BATcalcbetween")
+
+
+def BATcalcifthenelse(b, b1, b2) -> RBAT:
+    return RBAT(_bat.BATcalcifthenelse(b.p, b1.p, b2.p), "BATcalcifthenelse")
 
 
 def BATcalcisnil(b, s=None) -> RBAT:
