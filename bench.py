@@ -165,19 +165,25 @@ def b200_arm(args):
     hostbats = {k: G.BAThostwrap(pinned[k], types[k], hseq=lo, nonil=True) for k in types}
     stream = torch.cuda.ExternalStream(G.lib.b200_stream())
     red = torch.zeros(4, dtype=torch.int64, device="cuda")
+    red_in = torch.zeros(4, dtype=torch.int64).pin_memory()
+    red_out = torch.zeros(4, dtype=torch.int64).pin_memory()
+    red_in_np, red_out_np = red_in.numpy(), red_out.numpy()
 
     def merge(partial: int) -> int:
-        """global hge sum: all-reduce of the four 32-bit digits of each rank's partial"""
+        """global hge sum: all-reduce of the four 32-bit digits of each rank's partial (pinned staging
+        buffers, one synchronisation per step)"""
         if world == 1:
             return partial
         u = partial & ((1 << 128) - 1)
-        digs = [(u >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
+        for i in range(4):
+            red_in_np[i] = (u >> (32 * i)) & 0xFFFFFFFF
         if partial < 0:
-            digs[3] -= 1 << 32
-        red.copy_(torch.tensor(digs, dtype=torch.int64), non_blocking=False)
+            red_in_np[3] -= 1 << 32
+        red.copy_(red_in, non_blocking=True)
         dist.all_reduce(red)
-        d = red.tolist()
-        return sum(int(v) << (32 * i) for i, v in enumerate(d))
+        red_out.copy_(red, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return sum(int(v) << (32 * i) for i, v in enumerate(red_out_np))
 
     def barrier():
         G.sync()

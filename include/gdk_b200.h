@@ -193,6 +193,13 @@ b200_bat *b200_BATcalcifthenelsecst(const b200_bat *b, const b200_bat *b1, const
 b200_bat *b200_BATcalcifthencstelse(const b200_bat *b, const void *c1, int c1type, const b200_bat *b2);
 b200_bat *b200_BATcalcifthencstelsecst(const b200_bat *b, const void *c1, int c1type, const void *c2, int c2type);
 
+/* unary operators: gdk_calc.h:15-23 (gdk_calc.c:41 not, :233 negate, :371 absolute, :513 iszero -> bit, :652 sign -> bte) */
+b200_bat *b200_BATcalcnot(const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalcnegate(const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalcabsolute(const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalciszero(const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalcsign(const b200_bat *b, const b200_bat *s);
+
 /* BATunique (gdk.h:2279, gdk_unique.c:30): candidate list of the first row of each distinct value of b within s */
 b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s);
 

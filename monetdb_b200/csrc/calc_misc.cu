@@ -448,3 +448,181 @@ extern "C" b200_bat *b200_BATcalcifthencstelsecst(const b200_bat *b, const void 
 {
 	return ifthenelse_impl(b, nullptr, nullptr, c1, c1type, c2, c2type, "BATcalcifthencstelsecst");
 }
+
+// ---------------------------------------------------------------- unary operators
+// BATcalcnot / negate / absolute / iszero / sign (gdk_calc.c:41,233,371,513,652; loops UNARY_2TYPE_FUNC[_nilcheck],
+// gdk_calc_private.h:354-388): nil in, nil out; NOT on an integer fails when ~x is the nil pattern.
+enum { U_NOT = 0, U_NEGATE, U_ABSOLUTE, U_ISZERO, U_SIGN };
+
+template <int OP, typename TI, typename TO, bool ISBIT>
+__global__ void __launch_bounds__(MISC_THREADS)
+unary_kernel(CmpOperand<TI> src, uint64_t n, TO *__restrict__ dst, unsigned long long *__restrict__ state /* [0] nils, [1] overflow */)
+{
+	unsigned nils = 0;
+	bool ovf = false;
+	for (uint64_t k = (uint64_t) blockIdx.x * MISC_THREADS + threadIdx.x; k < n; k += (uint64_t) gridDim.x * MISC_THREADS) {
+		const TI x = src.get(k);
+		TO r;
+		if (Atom<TI>::is_nil(x)) {
+			r = Atom<TO>::nil();
+			nils++;
+		} else if constexpr (OP == U_NOT) {
+			if constexpr (ISBIT) {
+				r = (TO) !x;
+			} else {
+				r = (TO) ~x;
+				ovf |= Atom<TO>::is_nil(r);
+			}
+		} else if constexpr (OP == U_NEGATE) {
+			r = (TO) -x;
+		} else if constexpr (OP == U_ABSOLUTE) {
+			r = (TO) (x < 0 ? -x : x);
+		} else if constexpr (OP == U_ISZERO) {
+			r = (TO) (x == 0);
+		} else {
+			r = (TO) (x < 0 ? -1 : x > 0);
+		}
+		dst[k] = r;
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1)
+		nils += __shfl_down_sync(0xffffffffu, nils, o);
+	if ((threadIdx.x & 31) == 0 && nils)
+		atomicAdd(state, (unsigned long long) nils);
+	if (ovf)
+		state[1] = 1;
+}
+
+template <int OP, typename TI, typename TO, bool ISBIT = false>
+static bool unary_run(const CmpSide &s, uint64_t n, void *dst, unsigned long long *state)
+{
+	Ctx *c = ctx();
+	KTimer kt("calc_unary", n * (sizeof(TI) + sizeof(TO)));
+	unary_kernel<OP, TI, TO, ISBIT><<<grid_for(n, MISC_THREADS, NSM * 32), MISC_THREADS, 0, c->stream>>>(make_operand<TI>(s), n, (TO *) dst, state);
+	COUNT_LAUNCH();
+	return cuda_ok(cudaGetLastError(), "unary launch");
+}
+
+template <int OP> static int unary_dispatch(const CmpSide &s, int ttype, uint64_t n, void *dst, unsigned long long *state)
+{
+	if constexpr (OP == U_NOT) {
+		switch (s.type) {
+		case B200_bte: return ttype == B200_bit ? unary_run<OP, bte, bte, true>(s, n, dst, state) : unary_run<OP, bte, bte>(s, n, dst, state);
+		case B200_sht: return unary_run<OP, sht, sht>(s, n, dst, state);
+		case B200_int: return unary_run<OP, int, int>(s, n, dst, state);
+		case B200_lng: return unary_run<OP, lng, lng>(s, n, dst, state);
+		case B200_hge: return unary_run<OP, hge, hge>(s, n, dst, state);
+		}
+		return -1;
+	} else if constexpr (OP == U_NEGATE || OP == U_ABSOLUTE) {
+		switch (s.type) {
+		case B200_bte: return unary_run<OP, bte, bte>(s, n, dst, state);
+		case B200_sht: return unary_run<OP, sht, sht>(s, n, dst, state);
+		case B200_int: return unary_run<OP, int, int>(s, n, dst, state);
+		case B200_lng: return unary_run<OP, lng, lng>(s, n, dst, state);
+		case B200_hge: return unary_run<OP, hge, hge>(s, n, dst, state);
+		case B200_flt: return unary_run<OP, flt, flt>(s, n, dst, state);
+		case B200_dbl: return unary_run<OP, dbl, dbl>(s, n, dst, state);
+		}
+		return -1;
+	} else {
+		switch (s.type) {
+		case B200_bte: return unary_run<OP, bte, bte>(s, n, dst, state);
+		case B200_sht: return unary_run<OP, sht, bte>(s, n, dst, state);
+		case B200_int: return unary_run<OP, int, bte>(s, n, dst, state);
+		case B200_lng: return unary_run<OP, lng, bte>(s, n, dst, state);
+		case B200_hge: return unary_run<OP, hge, bte>(s, n, dst, state);
+		case B200_flt: return unary_run<OP, flt, bte>(s, n, dst, state);
+		case B200_dbl: return unary_run<OP, dbl, bte>(s, n, dst, state);
+		}
+		return -1;
+	}
+}
+
+static b200_bat *unary_impl(int op, const b200_bat *b, const b200_bat *s, const char *func)
+{
+	b200_clrerr();
+	if (b == nullptr) {
+		set_err("%s: BAT required\n", func);
+		return nullptr;
+	}
+	Staged sb, ss;
+	if (!stage(b, sb) || !stage(s, ss))
+		return nullptr;
+	b = sb.b;
+	Cand ci;
+	if (!cand_init(ci, b, ss.b))
+		return nullptr;
+	const uint64_t n = ci.ncand;
+	const int st = basetype(b->ttype);
+	const int rt = op == U_ISZERO ? B200_bit : op == U_SIGN ? B200_bte : (b->ttype == B200_void ? B200_oid : b->ttype);
+	b200_bat *bn = bat_new(ci.rhseq, rt, n);
+	if (bn == nullptr || n == 0)
+		return bn;
+	if (b->ttype == B200_void) {
+		b200_BATfree(bn);
+		set_err("%s: void columns are not on the device path\n", func);
+		return nullptr;
+	}
+	Ctx *c = ctx();
+	CmpSide side{b, &ci, nullptr, st};
+	unsigned long long *state = (unsigned long long *) dev_alloc(16);
+	bool ok = state != nullptr && cuda_ok(cudaMemsetAsync(state, 0, 16, c->stream), "memset state");
+	if (ok) {
+		c->algo = "calc: cuda streaming unary";
+		int rc;
+		switch (op) {
+		case U_NOT: rc = unary_dispatch<U_NOT>(side, b->ttype, n, bn->base, state); break;
+		case U_NEGATE: rc = unary_dispatch<U_NEGATE>(side, b->ttype, n, bn->base, state); break;
+		case U_ABSOLUTE: rc = unary_dispatch<U_ABSOLUTE>(side, b->ttype, n, bn->base, state); break;
+		case U_ISZERO: rc = unary_dispatch<U_ISZERO>(side, b->ttype, n, bn->base, state); break;
+		default: rc = unary_dispatch<U_SIGN>(side, b->ttype, n, bn->base, state);
+		}
+		if (rc < 0) {
+			if (op == U_ISZERO || op == U_SIGN)
+				set_err("bad input type %s.\n", atomname(b->ttype));	/* gdk_calc.c:563,702 */
+			else
+				set_err("type %s not supported.\n", atomname(b->ttype));	/* gdk_calc.c:118,284 */
+			ok = false;
+		} else {
+			ok = rc != 0 && cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 16, cudaMemcpyDeviceToHost, c->stream), "read state") &&
+			     stream_sync();
+		}
+	}
+	dev_free(state);
+	if (ok && c->slot_h->v[1] != 0) {
+		/* ON_OVERFLOW1(TYPE, "NOT"): ~x is the nil pattern only for x = the type's maximum */
+		static const char *maxs[] = {"127", "32767", "2147483647", "9223372036854775807", "170141183460469231731687303715884105727"};
+		const int w = atomsize(st);
+		set_err("22003!overflow in calculation NOT(%s).\n", maxs[w == 1 ? 0 : w == 2 ? 1 : w == 4 ? 2 : w == 8 ? 3 : 4]);
+		ok = false;
+	}
+	if (!ok) {
+		b200_BATfree(bn);
+		return nullptr;
+	}
+	const uint64_t nils = c->slot_h->v[0];
+	bn->count = n;
+	bn->tnil = nils != 0;
+	bn->tnonil = nils == 0;
+	if (op == U_NOT || op == U_NEGATE) {
+		/* reverses the order, but nils mess it up (gdk_calc.c:124-130, 290-296) */
+		bn->tsorted = nils == 0 && b->trevsorted;
+		bn->trevsorted = nils == 0 && b->tsorted;
+		bn->tkey = b->tkey && nils <= 1;
+	} else if (op == U_SIGN) {
+		bn->tsorted = b->tsorted || n <= 1 || nils == n;	/* gdk_calc.c:711-713 */
+		bn->trevsorted = b->trevsorted || n <= 1 || nils == n;
+		bn->tkey = n <= 1;
+	} else {
+		bn->tsorted = bn->trevsorted = n <= 1 || nils == n;	/* gdk_calc.c:433-435, 569-571 */
+		bn->tkey = n <= 1;
+	}
+	return bn;
+}
+
+extern "C" b200_bat *b200_BATcalcnot(const b200_bat *b, const b200_bat *s) { return unary_impl(U_NOT, b, s, "BATcalcnot"); }
+extern "C" b200_bat *b200_BATcalcnegate(const b200_bat *b, const b200_bat *s) { return unary_impl(U_NEGATE, b, s, "BATcalcnegate"); }
+extern "C" b200_bat *b200_BATcalcabsolute(const b200_bat *b, const b200_bat *s) { return unary_impl(U_ABSOLUTE, b, s, "BATcalcabsolute"); }
+extern "C" b200_bat *b200_BATcalciszero(const b200_bat *b, const b200_bat *s) { return unary_impl(U_ISZERO, b, s, "BATcalciszero"); }
+extern "C" b200_bat *b200_BATcalcsign(const b200_bat *b, const b200_bat *s) { return unary_impl(U_SIGN, b, s, "BATcalcsign"); }

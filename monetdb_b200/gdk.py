@@ -431,6 +431,15 @@ _sig("b200_BATcalcifthencstelse", _P, _P, C.c_void_p, C.c_int, _P)
 _sig("b200_BATcalcifthencstelsecst", _P, _P, C.c_void_p, C.c_int, C.c_void_p, C.c_int)
 
 
+for _n in ("not", "negate", "absolute", "iszero", "sign"):
+    _sig(f"b200_BATcalc{_n}", _P, _P, _P)
+
+
+def BATcalcunary(which: str, b: BAT, s: BAT | None = None) -> BAT:
+    """BATcalcnot / negate / absolute / iszero / sign"""
+    return BAT(getattr(lib, f"b200_BATcalc{which}")(b._p, _ptr(s)))
+
+
 def BATcalcminmax(which: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
     """BATcalcmin / min_no_nil / max / max_no_nil"""
     return BAT(getattr(lib, f"b200_BATcalc{which}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))

@@ -111,6 +111,11 @@ def _load(nthreads: int = 0):
         "BATcalcavg": (C.c_int, [P, P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
         "BATjoin": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, B, C.c_uint64]),
         "BAThash": (C.c_int, [P]),
+        "BATcalcnot": (P, [P, P]),
+        "BATcalcnegate": (P, [P, P]),
+        "BATcalcabsolute": (P, [P, P]),
+        "BATcalciszero": (P, [P, P]),
+        "BATcalcsign": (P, [P, P]),
         "BATcalcmin": (P, [P, P, P, P]),
         "BATcalcmin_no_nil": (P, [P, P, P, P]),
         "BATcalcmax": (P, [P, P, P, P]),
@@ -349,6 +354,10 @@ def BATcalccmp(op, b1, b2, s1=None, s2=None, nil_matches=False) -> RBAT:
 def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False) -> RBAT:
     a = _val(vtype, v)
     return RBAT(_h.refh_cmp_cst(_CMPS[op], b.p, _vp(a), vtype, _p(s), nil_matches), "BATcalc" + op + "cst")
+
+
+def BATcalcunary(which, b, s=None) -> RBAT:
+    return RBAT(getattr(_bat, "BATcalc" + which)(b.p, _p(s)), "BATcalc" + which)
 
 
 def BATcalcminmax(which, b1, b2, s1=None, s2=None) -> RBAT:

@@ -142,3 +142,39 @@ def test_ifthenelse_errors(gdk, ref):
         gdk.BATcalcifthenelse(c, x, z)
     with pytest.raises(G.GDKError, match="different types"):
         gdk.BATcalcifthenelse(x, x, x)                        # condition must be a bit column
+
+
+@pytest.mark.parametrize("tt", ALL_TYPES)
+@pytest.mark.parametrize("which", ["negate", "absolute", "iszero", "sign", "not"])
+def test_unary(gdk, ref, tt, which):
+    if which == "not" and tt in (T.flt, T.dbl):
+        b, rb = both(gdk, ref, np.ones(3, dtype=G.NP_OF[tt]), tt)
+        with pytest.raises(G.GDKError, match="not supported"):
+            gdk.BATcalcunary("not", b)
+        return
+    rng = np.random.default_rng(80 + tt)
+    n = 30011
+    a = _col(rng, tt, n)
+    b, rb = both(gdk, ref, a, tt, hseq=4)
+    assert_same(gdk.BATcalcunary(which, b), ref.BATcalcunary(which, rb))
+    o = np.sort(rng.choice(n, 6000, replace=False)).astype(np.uint64) + np.uint64(4)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    assert_same(gdk.BATcalcunary(which, b, s), ref.BATcalcunary(which, rb, rs))
+    # sorted input: the order properties the reference derives
+    srt = np.sort(a[:1000]) if tt != T.hge else a[:1]
+    if tt != T.hge:
+        sb, rsb = both(gdk, ref, srt, tt, sorted=True)
+        got, want = gdk.BATcalcunary(which, sb), ref.BATcalcunary(which, rsb)
+        assert_same(got, want)
+        assert got.props()["sorted"] == want.props()["sorted"] and got.props()["revsorted"] == want.props()["revsorted"]
+
+
+def test_not_bit_and_overflow(gdk, ref):
+    c = np.array([0, 1, -128, 1, 0], dtype=np.int8)
+    b, rb = both(gdk, ref, c, T.bit)
+    assert_same(gdk.BATcalcunary("not", b), ref.BATcalcunary("not", rb))
+    x, rx = both(gdk, ref, np.array([1, 2, 2147483647], dtype=np.int32), T.int)
+    with pytest.raises(G.GDKError, match=r"overflow in calculation NOT\(2147483647\)"):
+        gdk.BATcalcunary("not", x)
+    with pytest.raises(Exception, match=r"overflow in calculation NOT\(2147483647\)"):
+        ref.BATcalcunary("not", rx)
