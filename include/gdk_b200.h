@@ -122,20 +122,23 @@ b200_bat *b200_BATproject(const b200_bat *l, const b200_bat *r);
 b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, const b200_bat *r2);
 
 /* ---- calc: gdk_calc_addsub.c:1480-1664,3166-3280; gdk_calc_mul.c:2085-2113;
- *      gdk_calc_div.c:1945; compares gdk_calc_compare_*.c; BATconvert gdk_calc_convert.c:1415.
+ *      gdk_calc_div.c:1945; gdk_calc_mod.c:1179,1186,1236; compares gdk_calc_compare_*.c; BATconvert gdk_calc_convert.c:1415.
  *      A ValRecord constant (gdk.h:567-600) is passed as (pointer, type id). ---- */
 b200_bat *b200_BATcalcadd(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
 b200_bat *b200_BATcalcsub(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
 b200_bat *b200_BATcalcmul(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
 b200_bat *b200_BATcalcdiv(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
+b200_bat *b200_BATcalcmod(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, int tp);
 b200_bat *b200_BATcalcaddcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
 b200_bat *b200_BATcalcsubcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
 b200_bat *b200_BATcalcmulcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
 b200_bat *b200_BATcalcdivcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
+b200_bat *b200_BATcalcmodcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstadd(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstsub(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstmul(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstdiv(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+b200_bat *b200_BATcalccstmod(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalclt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcle(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcgt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);

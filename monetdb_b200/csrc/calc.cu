@@ -1,12 +1,12 @@
-// calc.cu — host drivers of BATcalcadd/sub/mul/div and their constant-operand
+// calc.cu — host drivers of BATcalcadd/sub/mul/div/mod and their constant-operand
 // forms (gdk_calc_addsub.c:1480-1664,3166-3330; gdk_calc_mul.c:2020-2210;
-// gdk_calc_div.c:1945-2060): candidate set-up, result allocation, error text and
+// gdk_calc_div.c:1945-2060; gdk_calc_mod.c:1179-1290): candidate set-up, result allocation, error text and
 // result properties.  The kernels live in calc.cuh / calc_<op>.cu.
 #include "calc.cuh"
 
-static const char *opsym[] = {"+", "-", "*", "/"};
-static const char *opname[] = {"add", "sub", "mul", "div"};
-static calc_fn opentry[] = {calc_add_entry, calc_sub_entry, calc_mul_entry, calc_div_entry};
+static const char *opsym[] = {"+", "-", "*", "/", "%"};
+static const char *opname[] = {"add", "sub", "mul", "div", "mod"};
+static calc_fn opentry[] = {calc_add_entry, calc_sub_entry, calc_mul_entry, calc_div_entry, calc_mod_entry};
 
 // sign of a constant (VARcalcsign) for the mul/div sortedness rules
 static int cst_sign(int t, const void *v)
@@ -166,3 +166,4 @@ BINOP(add, OP_ADD)
 BINOP(sub, OP_SUB)
 BINOP(mul, OP_MUL)
 BINOP(div, OP_DIV)
+BINOP(mod, OP_MOD)

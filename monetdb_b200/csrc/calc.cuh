@@ -17,7 +17,7 @@
 #include "common.cuh"
 #include <type_traits>
 
-enum { OP_ADD = 0, OP_SUB = 1, OP_MUL = 2, OP_DIV = 3 };
+enum { OP_ADD = 0, OP_SUB = 1, OP_MUL = 2, OP_DIV = 3, OP_MOD = 4 };
 enum { ST_OK = 0, ST_OVERFLOW = 1, ST_DIVZERO = 2, ST_DIVRANGE = 3 };
 
 template <typename T> struct Rank;
@@ -37,6 +37,13 @@ template <int OP, typename T1, typename T2, typename T3> constexpr bool calc_sup
 {
 	constexpr int r1 = Rank<T1>::v, r2 = Rank<T2>::v, r3 = Rank<T3>::v;
 	constexpr int rm = r1 > r2 ? r1 : r2;
+	if (OP == OP_MOD) {
+		/* gdk_calc_mod.c:121-290: an integer result holds the narrower input; a
+		 * floating-point one exists only in the widest input type */
+		if (!is_fl<T1> && !is_fl<T2>)
+			return !is_fl<T3> && r3 >= (r1 < r2 ? r1 : r2);
+		return r3 == rm;
+	}
 	if (!is_fl<T3>) {
 		if (is_fl<T1> || is_fl<T2>)
 			return false;
@@ -92,7 +99,26 @@ template <int OP, typename T1, typename T2, typename T3> struct Calc {
 	__host__ __device__ static inline int apply(T1 a, T2 b, T3 &dst)
 	{
 		const T3 max = Atom<T3>::maxval();
-		if constexpr (!is_fl<T3>) {
+		if constexpr (OP == OP_MOD) {
+			if (b == 0)
+				return ST_DIVZERO;
+			if constexpr (is_fl<T3>) {
+				/* FMOD_3TYPE: fmodf / fmod on both operands converted to the result type */
+				if constexpr (std::is_same<T3, flt>::value)
+					dst = fmodf((flt) a, (flt) b);
+				else
+					dst = fmod((dbl) a, (dbl) b);
+			} else {
+				/* MOD_3TYPE: `(TYPE3) lft % rgt` — the cast binds to lft alone, so a
+				 * result type narrower than lft truncates it first, as the reference does */
+				const T3 l = (T3) a;
+				if (b == (T2) -1)
+					dst = 0;	/* the remainder is 0; avoids min % -1 after a truncating cast */
+				else
+					dst = (T3) (l % b);
+			}
+			return ST_OK;
+		} else if constexpr (!is_fl<T3>) {
 			/* integer result */
 			if constexpr (OP == OP_DIV) {
 				if (b == 0)
@@ -507,4 +533,5 @@ typedef int (*calc_fn)(int, int, int, const CalcOperand &, const CalcOperand &, 
 int calc_add_entry(int, int, int, const CalcOperand &, const CalcOperand &, void *, uint64_t, CalcOut &);
 int calc_sub_entry(int, int, int, const CalcOperand &, const CalcOperand &, void *, uint64_t, CalcOut &);
 int calc_mul_entry(int, int, int, const CalcOperand &, const CalcOperand &, void *, uint64_t, CalcOut &);
+int calc_mod_entry(int, int, int, const CalcOperand &, const CalcOperand &, void *, uint64_t, CalcOut &);
 int calc_div_entry(int, int, int, const CalcOperand &, const CalcOperand &, void *, uint64_t, CalcOut &);

@@ -357,7 +357,7 @@ def BATdiffcand(a: BAT, b: BAT) -> BAT:
 
 
 # ------------------------------------------------------------------ calc
-for _op in ("add", "sub", "mul", "div"):
+for _op in ("add", "sub", "mul", "div", "mod"):
     _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P, C.c_int)
     _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P, C.c_int)
     _sig(f"b200_BATcalccst{_op}", _P, C.c_void_p, C.c_int, _P, _P, C.c_int)
@@ -365,7 +365,7 @@ _sig("b200_BATconvert", _P, _P, _P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8)
 
 
 def BATcalc(op: str, b1: BAT, b2: BAT, s1: BAT | None, s2: BAT | None, tp: int) -> BAT:
-    """BATcalcadd/sub/mul/div (gdk_calc.h:36-47)"""
+    """BATcalcadd/sub/mul/div/mod (gdk_calc.h:36-50)"""
     return BAT(getattr(lib, f"b200_BATcalc{op}")(b1._p, b2._p, _ptr(s1), _ptr(s2), tp))
 
 
@@ -381,6 +381,7 @@ def BATcalcadd(b1, b2, s1, s2, tp): return BATcalc("add", b1, b2, s1, s2, tp)
 def BATcalcsub(b1, b2, s1, s2, tp): return BATcalc("sub", b1, b2, s1, s2, tp)
 def BATcalcmul(b1, b2, s1, s2, tp): return BATcalc("mul", b1, b2, s1, s2, tp)
 def BATcalcdiv(b1, b2, s1, s2, tp): return BATcalc("div", b1, b2, s1, s2, tp)
+def BATcalcmod(b1, b2, s1, s2, tp): return BATcalc("mod", b1, b2, s1, s2, tp)
 
 
 def BATconvert(b: BAT, s: BAT | None, tp: int, scale1: int = 0, scale2: int = 0, precision: int = 0) -> BAT:

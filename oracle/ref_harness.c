@@ -237,7 +237,7 @@ refh_parallel(refh_slice_fn fn, void *arg, int nslices, int nthreads)
 }
 
 /* --- constant-operand calc: the Python side passes (pointer, type id) and we build
- * the ValRecord the reference wants (VALinit, gdk_value.c). op: 0 add 1 sub 2 mul 3 div;
+ * the ValRecord the reference wants (VALinit, gdk_value.c). op: 0 add 1 sub 2 mul 3 div 4 mod;
  * side: 0 = BAT op cst, 1 = cst op BAT --- */
 BAT *
 refh_calc_cst(int op, int side, BAT *b, const void *v, int vtype, BAT *s, int tp)
@@ -255,6 +255,8 @@ refh_calc_cst(int op, int side, BAT *b, const void *v, int vtype, BAT *s, int tp
 	case 5: bn = BATcalccstmul(&val, b, s, tp); break;
 	case 6: bn = BATcalcdivcst(b, &val, s, tp); break;
 	case 7: bn = BATcalccstdiv(&val, b, s, tp); break;
+	case 8: bn = BATcalcmodcst(b, &val, s, tp); break;
+	case 9: bn = BATcalccstmod(&val, b, s, tp); break;
 	}
 	VALclear(&val);
 	return bn;

@@ -140,7 +140,7 @@ def _load(nthreads: int = 0):
         "GDKanalyticalmax": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
         "COLnew": (P, [C.c_uint64, C.c_int, C.c_uint64, C.c_int]),
     }
-    for op in ("add", "sub", "mul", "div"):
+    for op in ("add", "sub", "mul", "div", "mod"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, C.c_int])
     for op in ("lt", "le", "gt", "ge"):
         sigs["BATcalc" + op] = (P, [P, P, P, P])
@@ -331,7 +331,7 @@ def BATdiffcand(a, b) -> RBAT:
     return RBAT(_bat.BATdiffcand(a.p, b.p))
 
 
-_OPS = {"add": 0, "sub": 1, "mul": 2, "div": 3}
+_OPS = {"add": 0, "sub": 1, "mul": 2, "div": 3, "mod": 4}
 _CMPS = {"lt": 0, "le": 1, "gt": 2, "ge": 3, "eq": 4, "ne": 5}
 
 

@@ -178,3 +178,84 @@ def test_not_bit_and_overflow(gdk, ref):
         gdk.BATcalcunary("not", x)
     with pytest.raises(Exception, match=r"overflow in calculation NOT\(2147483647\)"):
         ref.BATcalcunary("not", rx)
+
+
+# ------------------------------------------------------------------ BATcalcmod (gdk_calc_mod.c)
+_RANK = {T.bte: 0, T.sht: 1, T.int: 2, T.lng: 3, T.hge: 4, T.flt: 5, T.dbl: 6}
+
+
+def _mod_cmp(gdk, ref, fo, fr):
+    try:
+        r = fr()
+    except ref.RefError as e:
+        with pytest.raises(G.GDKError) as ei:
+            fo()
+        assert str(ei.value).strip() == str(e).strip(), (str(ei.value), str(e))
+        return
+    assert_same(fo(), r)
+
+
+def test_mod_int_matrix(gdk, ref):
+    """every (t1, t2) -> t3 of MOD_3TYPE, including result types narrower than the left operand"""
+    rng = np.random.default_rng(77)
+    n = 4099
+    ints = [T.bte, T.sht, T.int, T.lng, T.hge]
+    for t1 in ints:
+        for t2 in ints:
+            a1 = random_col(rng, t1, n, nilfrac=0.03, lo=-120 if t1 == T.bte else -30000, hi=120 if t1 == T.bte else 30000)
+            a2 = random_col(rng, t2, n, nilfrac=0.03, lo=1, hi=97)
+            if t2 != T.hge:
+                a2[::3] = -a2[::3]                      # negative divisors: C's sign-of-dividend rule
+            b1, r1 = both(gdk, ref, a1, t1)
+            b2, r2 = both(gdk, ref, a2, t2)
+            for t3 in ints:
+                _mod_cmp(gdk, ref, lambda: gdk.BATcalc("mod", b1, b2, None, None, t3),
+                         lambda: ref.BATcalc("mod", r1, r2, None, None, t3))
+
+
+def test_mod_float_matrix(gdk, ref):
+    """FMOD_3TYPE: fmodf / fmod are exact, so the bits match the host libm's"""
+    rng = np.random.default_rng(78)
+    n = 4099
+    for t1 in ALL_TYPES:
+        for t2 in ALL_TYPES:
+            if t1 not in (T.flt, T.dbl) and t2 not in (T.flt, T.dbl):
+                continue
+            a1 = random_col(rng, t1, n, nilfrac=0.03, lo=-120, hi=120)
+            a2 = random_col(rng, t2, n, nilfrac=0.03, lo=1, hi=97)
+            b1, r1 = both(gdk, ref, a1, t1)
+            b2, r2 = both(gdk, ref, a2, t2)
+            for t3 in (T.lng, T.flt, T.dbl):
+                _mod_cmp(gdk, ref, lambda: gdk.BATcalc("mod", b1, b2, None, None, t3),
+                         lambda: ref.BATcalc("mod", r1, r2, None, None, t3))
+
+
+def test_mod_cst_candidates_and_zero(gdk, ref):
+    rng = np.random.default_rng(79)
+    n = 30011
+    a = random_col(rng, T.lng, n, nilfrac=0.02, lo=-100000, hi=100000)
+    b, rb = both(gdk, ref, a, T.lng, hseq=4)
+    o = np.sort(rng.choice(n, n // 3, replace=False)).astype(np.uint64) + np.uint64(4)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    for cand, rcand in ((None, None), (s, rs), (gdk.BATdense(0, 104, 999), ref.dense(0, 104, 999))):
+        for first in (False, True):
+            for cst, ct in ((100, T.lng), (-7, T.int), (0, T.int)):
+                if first and cst == 0:
+                    continue
+                for tp in (T.int, T.lng, T.hge):
+                    if first:
+                        bb, rbb = both(gdk, ref, np.where(a == 0, 1, a), T.lng, hseq=4)
+                    else:
+                        bb, rbb = b, rb
+                    _mod_cmp(gdk, ref, lambda: gdk.BATcalccst("mod", bb, cst, ct, cand, tp, cst_first=first),
+                             lambda: ref.BATcalccst("mod", rbb, cst, ct, rcand, tp, cst_first=first))
+    # a zero divisor anywhere aborts with the reference's text
+    z = random_col(rng, T.int, n, lo=1, hi=50)
+    z[20000] = 0
+    b2, rb2 = both(gdk, ref, z, T.int, hseq=4)
+    with pytest.raises(G.GDKError, match="22012!division by zero"):
+        gdk.BATcalc("mod", b, b2, None, None, T.lng)
+    with pytest.raises(Exception, match="22012!division by zero"):
+        ref.BATcalc("mod", rb, rb2, None, None, T.lng)
+    with pytest.raises(G.GDKError, match="inputs not the same size"):
+        gdk.BATcalc("mod", b, b2, s, None, T.lng)
