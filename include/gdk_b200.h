@@ -139,6 +139,16 @@ b200_bat *b200_BATcalccstsub(const void *v, int vtype, const b200_bat *b, const 
 b200_bat *b200_BATcalccstmul(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstdiv(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstmod(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+/* and / or / xor: gdk_calc.c:2901,2967,3030 / 2670,2736,2799 / 2439,2506,2563 (three-valued on bit, bitwise on integers) */
+b200_bat *b200_BATcalcand(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcor(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcxor(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcandcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcorcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcxorcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalccstand(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstor(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstxor(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
 b200_bat *b200_BATcalclt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcle(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcgt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);

@@ -436,6 +436,25 @@ for _n in ("not", "negate", "absolute", "iszero", "sign"):
     _sig(f"b200_BATcalc{_n}", _P, _P, _P)
 
 
+for _n in ("and", "or", "xor"):
+    _sig(f"b200_BATcalc{_n}", _P, _P, _P, _P, _P)
+    _sig(f"b200_BATcalc{_n}cst", _P, _P, C.c_void_p, C.c_int, _P)
+    _sig(f"b200_BATcalccst{_n}", _P, C.c_void_p, C.c_int, _P, _P)
+
+
+def BATcalclogic(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
+    """BATcalcand / or / xor (gdk_calc.h:51-58): three-valued on bit, bitwise on the integer atoms"""
+    return BAT(getattr(lib, f"b200_BATcalc{op}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))
+
+
+def BATcalclogiccst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, cst_first: bool = False) -> BAT:
+    """BATcalc<op>cst / BATcalccst<op> for and / or / xor"""
+    a = _valp(_storage(vtype), v)
+    if cst_first:
+        return BAT(getattr(lib, f"b200_BATcalccst{op}")(a[1], vtype, b._p, _ptr(s)))
+    return BAT(getattr(lib, f"b200_BATcalc{op}cst")(b._p, a[1], vtype, _ptr(s)))
+
+
 def BATcalcunary(which: str, b: BAT, s: BAT | None = None) -> BAT:
     """BATcalcnot / negate / absolute / iszero / sign"""
     return BAT(getattr(lib, f"b200_BATcalc{which}")(b._p, _ptr(s)))

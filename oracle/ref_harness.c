@@ -262,6 +262,23 @@ refh_calc_cst(int op, int side, BAT *b, const void *v, int vtype, BAT *s, int tp
 	return bn;
 }
 
+/* op: 0 and 1 or 2 xor (BATcalc<op>cst, gdk_calc.c:2967,2736,2506) */
+BAT *
+refh_logic_cst(int op, BAT *b, const void *v, int vtype, BAT *s)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	switch (op) {
+	case 0: bn = BATcalcandcst(b, &val, s); break;
+	case 1: bn = BATcalcorcst(b, &val, s); break;
+	case 2: bn = BATcalcxorcst(b, &val, s); break;
+	}
+	VALclear(&val);
+	return bn;
+}
+
 /* cmp: 0 lt 1 le 2 gt 3 ge 4 eq 5 ne */
 BAT *
 refh_cmp_cst(int cmp, BAT *b, const void *v, int vtype, BAT *s, int nil_matches)

@@ -82,6 +82,8 @@ def _load(nthreads: int = 0):
     _h.refh_assert_props.argtypes = [P]
     _h.refh_calc_cst.restype = P
     _h.refh_calc_cst.argtypes = [C.c_int, C.c_int, P, V, C.c_int, P, C.c_int]
+    _h.refh_logic_cst.restype = P
+    _h.refh_logic_cst.argtypes = [C.c_int, P, V, C.c_int, P]
     _h.refh_cmp_cst.restype = P
     _h.refh_cmp_cst.argtypes = [C.c_int, P, V, C.c_int, P, C.c_int]
     _h.refh_usec.restype = C.c_int64
@@ -142,7 +144,7 @@ def _load(nthreads: int = 0):
     }
     for op in ("add", "sub", "mul", "div", "mod"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, C.c_int])
-    for op in ("lt", "le", "gt", "ge"):
+    for op in ("lt", "le", "gt", "ge", "and", "or", "xor"):
         sigs["BATcalc" + op] = (P, [P, P, P, P])
     for op in ("eq", "ne"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, B])
@@ -354,6 +356,15 @@ def BATcalccmp(op, b1, b2, s1=None, s2=None, nil_matches=False) -> RBAT:
 def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False) -> RBAT:
     a = _val(vtype, v)
     return RBAT(_h.refh_cmp_cst(_CMPS[op], b.p, _vp(a), vtype, _p(s), nil_matches), "BATcalc" + op + "cst")
+
+
+def BATcalclogic(op, b1, b2, s1=None, s2=None) -> RBAT:
+    return RBAT(getattr(_bat, "BATcalc" + op)(b1.p, b2.p, _p(s1), _p(s2)), "BATcalc" + op)
+
+
+def BATcalclogiccst(op, b, v, vtype, s=None) -> RBAT:
+    a = _val(vtype, v)
+    return RBAT(_h.refh_logic_cst({"and": 0, "or": 1, "xor": 2}[op], b.p, _vp(a), vtype, _p(s)), "BATcalc" + op + "cst")
 
 
 def BATcalcunary(which, b, s=None) -> RBAT:

@@ -259,3 +259,74 @@ def test_mod_cst_candidates_and_zero(gdk, ref):
         ref.BATcalc("mod", rb, rb2, None, None, T.lng)
     with pytest.raises(G.GDKError, match="inputs not the same size"):
         gdk.BATcalc("mod", b, b2, s, None, T.lng)
+
+
+# ------------------------------------------------------------------ BATcalcand / or / xor (gdk_calc.c:2376-3032)
+@pytest.mark.parametrize("op", ["and", "or", "xor"])
+def test_logic_bit_three_valued(gdk, ref, op):
+    vals = np.array([0, 1, -128], dtype=np.int8)
+    a = np.repeat(vals, 3)
+    b = np.tile(vals, 3)
+    ba, ra = both(gdk, ref, a, T.bit)
+    bb, rb = both(gdk, ref, b, T.bit)
+    assert_same(gdk.BATcalclogic(op, ba, bb), ref.BATcalclogic(op, ra, rb))
+    rng = np.random.default_rng(5)
+    n = 100003
+    a = rng.choice(vals, n)
+    b = rng.choice(vals, n)
+    ba, ra = both(gdk, ref, a, T.bit, hseq=7)
+    bb, rb = both(gdk, ref, b, T.bit, hseq=7)
+    assert_same(gdk.BATcalclogic(op, ba, bb), ref.BATcalclogic(op, ra, rb))
+    o = np.sort(rng.choice(n, 20000, replace=False)).astype(np.uint64) + np.uint64(7)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    assert_same(gdk.BATcalclogic(op, ba, bb, s, s), ref.BATcalclogic(op, ra, rb, rs, rs))
+    for cst in (0, 1, -128):
+        for cand, rcand in ((None, None), (s, rs)):
+            got, want = gdk.BATcalclogiccst(op, ba, cst, T.bit, cand), ref.BATcalclogiccst(op, ra, cst, T.bit, rcand)
+            assert_same(got, want)
+            assert got.props()["sorted"] == want.props()["sorted"] and got.props()["revsorted"] == want.props()["revsorted"]
+            assert_same(gdk.BATcalclogiccst(op, ba, cst, T.bit, cand, cst_first=True), want)
+
+
+@pytest.mark.parametrize("op", ["and", "or", "xor"])
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.hge])
+def test_logic_bitwise(gdk, ref, op, tt):
+    rng = np.random.default_rng(90 + tt)
+    n = 30011
+    # non-negative operands cannot combine to the nil pattern
+    a = random_col(rng, tt, n, nilfrac=0.04, lo=0, hi=127)
+    b = random_col(rng, tt, n, nilfrac=0.04, lo=0, hi=127)
+    ba, ra = both(gdk, ref, a, tt, hseq=2)
+    bb, rb = both(gdk, ref, b, tt, hseq=2)
+    assert_same(gdk.BATcalclogic(op, ba, bb), ref.BATcalclogic(op, ra, rb))
+    o = np.sort(rng.choice(n, 7000, replace=False)).astype(np.uint64) + np.uint64(2)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    assert_same(gdk.BATcalclogic(op, ba, bb, s, s), ref.BATcalclogic(op, ra, rb, rs, rs))
+    assert_same(gdk.BATcalclogiccst(op, ba, 85, tt, s), ref.BATcalclogiccst(op, ra, 85, tt, rs))
+    with pytest.raises(G.GDKError, match="inputs not the same size"):
+        gdk.BATcalclogic(op, ba, bb, s, None)
+    other = T.int if tt != T.int else T.lng
+    c, _ = both(gdk, ref, np.ones(n, dtype=G.NP_OF[other]), other, hseq=2)
+    with pytest.raises(G.GDKError, match="incompatible input types"):
+        gdk.BATcalclogic(op, ba, c)
+
+
+@pytest.mark.parametrize("op", ["and", "xor"])
+def test_logic_overflow_text(gdk, ref, op):
+    """two non-nil operands that combine to the nil pattern abort with the reference's text"""
+    for tt, bits in ((T.bte, 8), (T.int, 32), (T.lng, 64)):
+        dt = G.NP_OF[tt]
+        top = -(1 << (bits - 1))
+        x = np.ones(5000, dtype=dt)
+        y = np.ones(5000, dtype=dt)
+        if op == "and":
+            x[3333], y[3333] = top + 1, top + (1 << (bits - 2))       # 10..01 & 110..0 = 10..0
+        else:
+            x[3333], y[3333] = top + 1, 1                             # 10..01 ^ 0..01 = 10..0
+        bx, rx = both(gdk, ref, x, tt)
+        by, ry = both(gdk, ref, y, tt)
+        with pytest.raises(ref.RefError) as want:
+            ref.BATcalclogic(op, rx, ry)
+        with pytest.raises(G.GDKError) as got:
+            gdk.BATcalclogic(op, bx, by)
+        assert str(got.value).strip() == str(want.value).strip()
