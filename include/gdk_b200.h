@@ -139,6 +139,12 @@ b200_bat *b200_BATcalccstsub(const void *v, int vtype, const b200_bat *b, const 
 b200_bat *b200_BATcalccstmul(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstdiv(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
 b200_bat *b200_BATcalccstmod(const void *v, int vtype, const b200_bat *b, const b200_bat *s, int tp);
+/* min / max against a constant: gdk_calc.c:1403 (mincst), 1563 (mincst_no_nil), 2086 (maxcst), 2219 (maxcst_no_nil);
+ * the reference's BATcalccstmin/max[_no_nil] forward to these (:1530,1708) */
+b200_bat *b200_BATcalcmincst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcmincst_no_nil(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcmaxcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcmaxcst_no_nil(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
 /* and / or / xor: gdk_calc.c:2901,2967,3030 / 2670,2736,2799 / 2439,2506,2563 (three-valued on bit, bitwise on integers) */
 b200_bat *b200_BATcalcand(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcor(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);

@@ -60,11 +60,13 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(lambda s: _compile(s, force, hdr_m, verbose), srcs))
     if force or not LIB.exists() or any(o.stat().st_mtime > LIB.stat().st_mtime for o in objs):
+        tmp = LIB.with_suffix(".so.tmp")
         cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
-               "-o", str(LIB), *map(str, objs), "-cudart", "static", "-lpthread"]
+               "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, LIB)  # atomic: a snapshot taken mid-build never sees a half-written library
     return LIB
 
 

@@ -62,11 +62,12 @@ static bool minmax_run(const CmpSide &s1, const CmpSide &s2, uint64_t n, bool ma
 	return cuda_ok(cudaGetLastError(), "min/max launch");
 }
 
+// cst != NULL: the BATcalc{min,max}cst[_no_nil] forms (gdk_calc.c:1403,1563,2086,2219), b2 unused
 static b200_bat *minmax_impl(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2, bool max,
-			     bool nonil, const char *func)
+			     bool nonil, const char *func, const void *cst = nullptr, int csttype = 0)
 {
 	b200_clrerr();
-	if (b1 == nullptr || b2 == nullptr) {
+	if (b1 == nullptr || (cst == nullptr && b2 == nullptr)) {
 		set_err("%s: BAT required\n", func);
 		return nullptr;
 	}
@@ -75,30 +76,33 @@ static b200_bat *minmax_impl(const b200_bat *b1, const b200_bat *b2, const b200_
 		return nullptr;
 	b1 = sb1.b;
 	b2 = sb2.b;
-	if (basetype(b1->ttype) != basetype(b2->ttype)) {
-		set_err("inputs have incompatible types\n");	/* gdk_calc.c:993 */
+	if (cst ? (b1->ttype == B200_void ? B200_oid : b1->ttype) != csttype : basetype(b1->ttype) != basetype(b2->ttype)) {
+		set_err("inputs have incompatible types\n");	/* gdk_calc.c:993,1423 */
 		return nullptr;
 	}
 	Cand ci1, ci2;
-	if (!cand_init(ci1, b1, ss1.b) || !cand_init(ci2, b2, ss2.b))
+	if (!cand_init(ci1, b1, ss1.b) || (!cst && !cand_init(ci2, b2, ss2.b)))
 		return nullptr;
-	if (ci1.ncand != ci2.ncand || ci1.rhseq != ci2.rhseq) {
+	if (!cst && (ci1.ncand != ci2.ncand || ci1.rhseq != ci2.rhseq)) {
 		set_err("inputs not the same size.\n");	/* gdk_calc.c:1000 */
 		return nullptr;
 	}
 	const uint64_t n = ci1.ncand;
+	if (cst && (n == 0 || (!nonil && cst_is_nil(basetype(csttype), cst))))
+		return bat_constant(ci1.rhseq, b1->ttype, nullptr, n);	/* BATconstantV(nil), gdk_calc.c:1429-1432 */
 	b200_bat *bn = bat_new(ci1.rhseq, b1->ttype == B200_void ? B200_oid : b1->ttype, n);
 	if (bn == nullptr)
 		return nullptr;
 	bool nils = false;
 	if (n > 0) {
-		if (b1->ttype == B200_void || b2->ttype == B200_void) {
+		if (b1->ttype == B200_void || (!cst && b2->ttype == B200_void)) {
 			b200_BATfree(bn);
 			set_err("%s: void columns are not on the device path\n", func);
 			return nullptr;
 		}
 		Ctx *c = ctx();
-		CmpSide l{b1, &ci1, nullptr, basetype(b1->ttype)}, r{b2, &ci2, nullptr, basetype(b2->ttype)};
+		CmpSide l{b1, &ci1, nullptr, basetype(b1->ttype)};
+		CmpSide r = cst ? CmpSide{nullptr, nullptr, cst, basetype(csttype)} : CmpSide{b2, &ci2, nullptr, basetype(b2->ttype)};
 		unsigned *flag = (unsigned *) dev_alloc(4);
 		bool ok = flag != nullptr && cuda_ok(cudaMemsetAsync(flag, 0, 4, c->stream), "memset flag");
 		if (ok) {
@@ -149,6 +153,21 @@ extern "C" b200_bat *b200_BATcalcmax_no_nil(const b200_bat *b1, const b200_bat *
 {
 	return minmax_impl(b1, b2, s1, s2, true, true, "BATcalcmax_no_nil");
 }
+
+#define MINMAXCST(NAME, MAX, NONIL)                                                                                   \
+	extern "C" b200_bat *b200_BATcalc##NAME(const b200_bat *b, const void *v, int vtype, const b200_bat *s)       \
+	{                                                                                                             \
+		if (v == nullptr) {                                                                                   \
+			b200_clrerr();                                                                                \
+			set_err("BATcalc" #NAME ": value required\n");                                                \
+			return nullptr;                                                                               \
+		}                                                                                                     \
+		return minmax_impl(b, nullptr, s, nullptr, MAX, NONIL, "BATcalc" #NAME, v, vtype);                    \
+	}
+MINMAXCST(mincst, false, false)
+MINMAXCST(mincst_no_nil, false, true)
+MINMAXCST(maxcst, true, false)
+MINMAXCST(maxcst_no_nil, true, true)
 
 // ---------------------------------------------------------------- between
 // three-valued logic on bit {0, 1, bit_nil} (gdk_calc.c:2590 or3, :2826 and3, :3795 not3)
@@ -476,7 +495,13 @@ unary_kernel(CmpOperand<TI> src, uint64_t n, TO *__restrict__ dst, unsigned long
 		} else if constexpr (OP == U_NEGATE) {
 			r = (TO) -x;
 		} else if constexpr (OP == U_ABSOLUTE) {
-			r = (TO) (x < 0 ? -x : x);
+			/* abs / llabs / ABSOLUTE on integers, fabsf / fabs on floats: -0.0 becomes +0.0 (gdk_calc.c:400-420) */
+			if constexpr (std::is_same<TI, flt>::value)
+				r = (TO) fabsf(x);
+			else if constexpr (std::is_same<TI, dbl>::value)
+				r = (TO) fabs(x);
+			else
+				r = (TO) (x < 0 ? -x : x);
 		} else if constexpr (OP == U_ISZERO) {
 			r = (TO) (x == 0);
 		} else {

@@ -460,6 +460,17 @@ def BATcalcunary(which: str, b: BAT, s: BAT | None = None) -> BAT:
     return BAT(getattr(lib, f"b200_BATcalc{which}")(b._p, _ptr(s)))
 
 
+for _n in ("mincst", "mincst_no_nil", "maxcst", "maxcst_no_nil"):
+    _sig(f"b200_BATcalc{_n}", _P, _P, C.c_void_p, C.c_int, _P)
+
+
+def BATcalcminmaxcst(which: str, b: BAT, v, vtype: int, s: BAT | None = None) -> BAT:
+    """BATcalcmincst / mincst_no_nil / maxcst / maxcst_no_nil (gdk_calc.c:1403,1563,2086,2219); which = "min", "max_no_nil", ..."""
+    a = _valp(_storage(vtype), v)
+    name = which.replace("min", "mincst", 1) if which.startswith("min") else which.replace("max", "maxcst", 1)
+    return BAT(getattr(lib, f"b200_BATcalc{name}")(b._p, a[1], vtype, _ptr(s)))
+
+
 def BATcalcminmax(which: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
     """BATcalcmin / min_no_nil / max / max_no_nil"""
     return BAT(getattr(lib, f"b200_BATcalc{which}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))

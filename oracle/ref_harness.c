@@ -279,6 +279,24 @@ refh_logic_cst(int op, BAT *b, const void *v, int vtype, BAT *s)
 	return bn;
 }
 
+/* which: 0 min 1 min_no_nil 2 max 3 max_no_nil (gdk_calc.c:1403,1563,2086,2219) */
+BAT *
+refh_minmax_cst(int which, BAT *b, const void *v, int vtype, BAT *s)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	switch (which) {
+	case 0: bn = BATcalcmincst(b, &val, s); break;
+	case 1: bn = BATcalcmincst_no_nil(b, &val, s); break;
+	case 2: bn = BATcalcmaxcst(b, &val, s); break;
+	case 3: bn = BATcalcmaxcst_no_nil(b, &val, s); break;
+	}
+	VALclear(&val);
+	return bn;
+}
+
 /* cmp: 0 lt 1 le 2 gt 3 ge 4 eq 5 ne */
 BAT *
 refh_cmp_cst(int cmp, BAT *b, const void *v, int vtype, BAT *s, int nil_matches)

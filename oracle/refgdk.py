@@ -84,6 +84,8 @@ def _load(nthreads: int = 0):
     _h.refh_calc_cst.argtypes = [C.c_int, C.c_int, P, V, C.c_int, P, C.c_int]
     _h.refh_logic_cst.restype = P
     _h.refh_logic_cst.argtypes = [C.c_int, P, V, C.c_int, P]
+    _h.refh_minmax_cst.restype = P
+    _h.refh_minmax_cst.argtypes = [C.c_int, P, V, C.c_int, P]
     _h.refh_cmp_cst.restype = P
     _h.refh_cmp_cst.argtypes = [C.c_int, P, V, C.c_int, P, C.c_int]
     _h.refh_usec.restype = C.c_int64
@@ -369,6 +371,12 @@ def BATcalclogiccst(op, b, v, vtype, s=None) -> RBAT:
 
 def BATcalcunary(which, b, s=None) -> RBAT:
     return RBAT(getattr(_bat, "BATcalc" + which)(b.p, _p(s)), "BATcalc" + which)
+
+
+def BATcalcminmaxcst(which, b, v, vtype, s=None) -> RBAT:
+    a = _val(vtype, v)
+    w = {"min": 0, "min_no_nil": 1, "max": 2, "max_no_nil": 3}[which]
+    return RBAT(_h.refh_minmax_cst(w, b.p, _vp(a), vtype, _p(s)), "BATcalc" + which + "cst")
 
 
 def BATcalcminmax(which, b1, b2, s1=None, s2=None) -> RBAT:

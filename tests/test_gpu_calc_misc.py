@@ -330,3 +330,22 @@ def test_logic_overflow_text(gdk, ref, op):
         with pytest.raises(G.GDKError) as got:
             gdk.BATcalclogic(op, bx, by)
         assert str(got.value).strip() == str(want.value).strip()
+
+
+# ------------------------------------------------------------------ BATcalc{min,max}cst[_no_nil] (gdk_calc.c:1403-2330)
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.flt, T.dbl])
+@pytest.mark.parametrize("which", ["min", "min_no_nil", "max", "max_no_nil"])
+def test_minmax_cst(gdk, ref, tt, which):
+    rng = np.random.default_rng(120 + tt)
+    n = 30011
+    a = _col(rng, tt, n)
+    b, rb = both(gdk, ref, a, tt, hseq=3)
+    o = np.sort(rng.choice(n, 6000, replace=False)).astype(np.uint64) + np.uint64(3)
+    s, rs = both(gdk, ref, o, T.oid, sorted=True, key=True)
+    nilv = float("nan") if tt in (T.flt, T.dbl) else int(np.iinfo(G.NP_OF[tt]).min)
+    for cst in (7, -3, nilv):
+        for cand, rcand in ((None, None), (s, rs)):
+            assert_same(gdk.BATcalcminmaxcst(which, b, cst, tt, cand), ref.BATcalcminmaxcst(which, rb, cst, tt, rcand))
+    other = T.int if tt != T.int else T.lng
+    with pytest.raises(G.GDKError, match="inputs have incompatible types"):
+        gdk.BATcalcminmaxcst(which, b, 1, other)
