@@ -82,7 +82,7 @@ cmp_kernel(CmpOperand<T1> l, CmpOperand<T2> r, uint64_t n, int op, bool nonil, b
 
 template <typename T>
 __global__ void __launch_bounds__(CMP_THREADS)
-isnil_kernel(CmpOperand<T> l, uint64_t n, int8_t *__restrict__ dst)
+isnil_kernel(CmpOperand<T> l, uint64_t n, int8_t *__restrict__ dst, int8_t notnil)
 {
 	const uint64_t nquads = (n + 3) / 4;
 	for (uint64_t q = (uint64_t) blockIdx.x * CMP_THREADS + threadIdx.x; q < nquads; q += (uint64_t) gridDim.x * CMP_THREADS) {
@@ -90,7 +90,7 @@ isnil_kernel(CmpOperand<T> l, uint64_t n, int8_t *__restrict__ dst)
 #pragma unroll
 		for (int e = 0; e < 4; e++)
 			if (4 * q + e < n)
-				res[e] = Atom<T>::is_nil(l.get(4 * q + e));
+				res[e] = (int8_t) Atom<T>::is_nil(l.get(4 * q + e)) ^ notnil;
 		if (4 * q + 3 < n)
 			*reinterpret_cast<char4 *>(dst + 4 * q) = make_char4(res[0], res[1], res[2], res[3]);
 		else
@@ -242,21 +242,22 @@ CMPOP_NM(eq, CMP_EQ)
 CMPOP_NM(ne, CMP_NE)
 
 // ---------------------------------------------------------------- BATcalcisnil (gdk_calc.c:802-913)
-template <typename T> static bool isnil_run(const CmpSide &s, uint64_t n, int8_t *dst)
+template <typename T> static bool isnil_run(const CmpSide &s, uint64_t n, int8_t *dst, bool notnil)
 {
 	Ctx *c = ctx();
 	CmpOperand<T> l = make_operand<T>(s);
 	KTimer kt("isnil", n * (sizeof(T) + 1));
-	isnil_kernel<T><<<grid_for((n + 3) / 4, CMP_THREADS, NSM * 16), CMP_THREADS, 0, c->stream>>>(l, n, dst);
+	isnil_kernel<T><<<grid_for((n + 3) / 4, CMP_THREADS, NSM * 16), CMP_THREADS, 0, c->stream>>>(l, n, dst, notnil ? 1 : 0);
 	COUNT_LAUNCH();
 	return cuda_ok(cudaGetLastError(), "isnil launch");
 }
 
-extern "C" b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s)
+// BATcalcisnil_implementation(b, s, notnil), gdk_calc.c:802-913
+static b200_bat *isnil_impl(const b200_bat *b, const b200_bat *s, bool notnil)
 {
 	b200_clrerr();
 	if (b == nullptr) {
-		set_err("BATcalcisnil: BAT required\n");
+		set_err("%s: BAT required\n", notnil ? "BATcalcisnotnil" : "BATcalcisnil");
 		return nullptr;
 	}
 	Staged sb, ss;
@@ -266,7 +267,7 @@ extern "C" b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s)
 	Cand ci;
 	if (!cand_init(ci, b, ss.b))
 		return nullptr;
-	const int8_t zero = 0, one = 1;
+	const int8_t zero = notnil ? 1 : 0, one = notnil ? 0 : 1;
 	if (b->tnonil || (b->ttype == B200_void && b->tseqbase != OID_NIL))
 		return bat_constant(ci.rhseq, B200_bit, &zero, ci.ncand);
 	if (b->ttype == B200_void)
@@ -280,13 +281,13 @@ extern "C" b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s)
 		ok = true;
 	else
 		switch (l.type) {
-		case B200_bte: ok = isnil_run<bte>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_sht: ok = isnil_run<sht>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_int: ok = isnil_run<int>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_lng: ok = isnil_run<lng>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_hge: ok = isnil_run<hge>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_flt: ok = isnil_run<flt>(l, ci.ncand, (int8_t *) bn->base); break;
-		case B200_dbl: ok = isnil_run<dbl>(l, ci.ncand, (int8_t *) bn->base); break;
+		case B200_bte: ok = isnil_run<bte>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_sht: ok = isnil_run<sht>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_int: ok = isnil_run<int>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_lng: ok = isnil_run<lng>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_hge: ok = isnil_run<hge>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_flt: ok = isnil_run<flt>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
+		case B200_dbl: ok = isnil_run<dbl>(l, ci.ncand, (int8_t *) bn->base, notnil); break;
 		default: set_err("BATcalcisnil: unsupported tail type %s\n", atomname(b->ttype));
 		}
 	if (!ok) {
@@ -295,10 +296,14 @@ extern "C" b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s)
 	}
 	ctx()->algo = "isnil: cuda streaming";
 	bn->count = ci.ncand;
-	bn->tsorted = b->trevsorted;	/* nils sort first: sorted input gives 1...0 (gdk_calc.c:886-896) */
-	bn->trevsorted = b->tsorted;
+	/* nils sort first: sorted input gives 1...0 for isnil, 0...1 for isnotnil (gdk_calc.c:886-896) */
+	bn->tsorted = notnil ? b->tsorted : b->trevsorted;
+	bn->trevsorted = notnil ? b->trevsorted : b->tsorted;
 	bn->tnil = 0;
 	bn->tnonil = 1;
 	bn->tkey = ci.ncand <= 1;
 	return bn;
 }
+
+extern "C" b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s) { return isnil_impl(b, s, false); }
+extern "C" b200_bat *b200_BATcalcisnotnil(const b200_bat *b, const b200_bat *s) { return isnil_impl(b, s, true); }

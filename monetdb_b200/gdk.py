@@ -396,6 +396,7 @@ for _op in ("eq", "ne"):
     _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P, C.c_bool)
     _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P, C.c_bool)
 _sig("b200_BATcalcisnil", _P, _P, _P)
+_sig("b200_BATcalcisnotnil", _P, _P, _P)
 
 
 def BATcalccmp(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None, nil_matches: bool = False) -> BAT:
@@ -416,6 +417,10 @@ def BATcalccmpcst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, nil_matc
 
 def BATcalcisnil(b: BAT, s: BAT | None = None) -> BAT:
     return BAT(lib.b200_BATcalcisnil(b._p, _ptr(s)))
+
+
+def BATcalcisnotnil(b: BAT, s: BAT | None = None) -> BAT:
+    return BAT(lib.b200_BATcalcisnotnil(b._p, _ptr(s)))
 
 
 # ------------------------------------------------------------------ min/max, between, ifthenelse (gdk_calc.h:24-33,87-95)

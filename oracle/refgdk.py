@@ -134,6 +134,7 @@ def _load(nthreads: int = 0):
         "BATunique": (P, [P, P]),
         "BATconvert": (P, [P, P, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8]),
         "BATcalcisnil": (P, [P, P]),
+        "BATcalcisnotnil": (P, [P, P]),
         "GDKanalyticaldiff": (C.c_int, [P, P, P, V, C.c_int]),
         "GDKanalyticalwindowbounds": (C.c_int, [P, P, P, P, V, C.c_int, C.c_int, C.c_int, B, C.c_uint64]),
         "GDKanalyticalsum": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int, C.c_int]),
@@ -395,6 +396,10 @@ def BATcalcifthenelse(b, b1, b2) -> RBAT:
 
 def BATcalcisnil(b, s=None) -> RBAT:
     return RBAT(_bat.BATcalcisnil(b.p, _p(s)))
+
+
+def BATcalcisnotnil(b, s=None) -> RBAT:
+    return RBAT(_bat.BATcalcisnotnil(b.p, _p(s)))
 
 
 def BATconvert(b, s, tp, scale1=0, scale2=0, precision=0) -> RBAT:

@@ -63,3 +63,11 @@ def test_isnil(gdk, ref, tt):
         b, rb = both(gdk, ref, a, tt, hseq=2)
         assert_same(gdk.BATcalcisnil(b), ref.BATcalcisnil(rb))
         assert_same(gdk.BATcalcisnil(b, gdk.BATdense(0, 100, 50)), ref.BATcalcisnil(rb, ref.dense(0, 100, 50)))
+        assert_same(gdk.BATcalcisnotnil(b), ref.BATcalcisnotnil(rb))
+        assert_same(gdk.BATcalcisnotnil(b, gdk.BATdense(0, 100, 50)), ref.BATcalcisnotnil(rb, ref.dense(0, 100, 50)))
+        if tt not in (T.hge, T.flt, T.dbl):      # integer nils are the type minimum: np.sort puts them first, as GDK orders them
+            sb, rsb = both(gdk, ref, np.sort(a), tt, sorted=True)
+            for f in ("BATcalcisnil", "BATcalcisnotnil"):
+                got, want = getattr(gdk, f)(sb), getattr(ref, f)(rsb)
+                assert_same(got, want)
+                assert (got.props()["sorted"], got.props()["revsorted"]) == (want.props()["sorted"], want.props()["revsorted"])
