@@ -167,6 +167,13 @@ b200_bat *b200_BATcalcgtcst(const b200_bat *b, const void *v, int vtype, const b
 b200_bat *b200_BATcalcgecst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
 b200_bat *b200_BATcalceqcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, bool nil_matches);
 b200_bat *b200_BATcalcnecst(const b200_bat *b, const void *v, int vtype, const b200_bat *s, bool nil_matches);
+/* constant on the left: BATcalccstop, gdk_calc_compare.h:928 */
+b200_bat *b200_BATcalccstlt(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstle(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstgt(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstge(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccsteq(const void *v, int vtype, const b200_bat *b, const b200_bat *s, bool nil_matches);
+b200_bat *b200_BATcalccstne(const void *v, int vtype, const b200_bat *b, const b200_bat *s, bool nil_matches);
 b200_bat *b200_BATcalcisnil(const b200_bat *b, const b200_bat *s);
 b200_bat *b200_BATcalcisnotnil(const b200_bat *b, const b200_bat *s);	/* gdk_calc.c:916 */
 b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int tp, uint8_t scale1, uint8_t scale2, uint8_t precision);

@@ -241,6 +241,29 @@ CMPOP(ge, CMP_GE)
 CMPOP_NM(eq, CMP_EQ)
 CMPOP_NM(ne, CMP_NE)
 
+// BATcalccst<op>(v, b, s) (BATcalccstop, gdk_calc_compare.h:928): the constant on the left is the mirrored
+// operator with the constant on the right — the type matrix is symmetric and C converts both operands to
+// their common type either way, so the bits agree.
+#define CSTCMPOP(NAME, MIRROR)                                                                                       \
+	extern "C" b200_bat *b200_BATcalccst##NAME(const void *v, int vtype, const b200_bat *b, const b200_bat *s)   \
+	{                                                                                                            \
+		b200_clrerr();                                                                                       \
+		return compare_impl(MIRROR, b, nullptr, s, nullptr, v, vtype, false, "BATcalccst" #NAME);            \
+	}
+CSTCMPOP(lt, CMP_GT)
+CSTCMPOP(le, CMP_GE)
+CSTCMPOP(gt, CMP_LT)
+CSTCMPOP(ge, CMP_LE)
+#define CSTCMPOP_NM(NAME, OP)                                                                                        \
+	extern "C" b200_bat *b200_BATcalccst##NAME(const void *v, int vtype, const b200_bat *b, const b200_bat *s,   \
+						   bool nil_matches)                                                 \
+	{                                                                                                            \
+		b200_clrerr();                                                                                       \
+		return compare_impl(OP, b, nullptr, s, nullptr, v, vtype, nil_matches, "BATcalccst" #NAME);          \
+	}
+CSTCMPOP_NM(eq, CMP_EQ)
+CSTCMPOP_NM(ne, CMP_NE)
+
 // ---------------------------------------------------------------- BATcalcisnil (gdk_calc.c:802-913)
 template <typename T> static bool isnil_run(const CmpSide &s, uint64_t n, int8_t *dst, bool notnil)
 {

@@ -392,9 +392,11 @@ def BATconvert(b: BAT, s: BAT | None, tp: int, scale1: int = 0, scale2: int = 0,
 for _op in ("lt", "le", "gt", "ge"):
     _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P)
     _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P)
+    _sig(f"b200_BATcalccst{_op}", _P, C.c_void_p, C.c_int, _P, _P)
 for _op in ("eq", "ne"):
     _sig(f"b200_BATcalc{_op}", _P, _P, _P, _P, _P, C.c_bool)
     _sig(f"b200_BATcalc{_op}cst", _P, _P, C.c_void_p, C.c_int, _P, C.c_bool)
+    _sig(f"b200_BATcalccst{_op}", _P, C.c_void_p, C.c_int, _P, _P, C.c_bool)
 _sig("b200_BATcalcisnil", _P, _P, _P)
 _sig("b200_BATcalcisnotnil", _P, _P, _P)
 
@@ -407,8 +409,15 @@ def BATcalccmp(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None 
     return BAT(f(b1._p, b2._p, _ptr(s1), _ptr(s2)))
 
 
-def BATcalccmpcst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, nil_matches: bool = False) -> BAT:
+def BATcalccmpcst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, nil_matches: bool = False,
+                  cst_first: bool = False) -> BAT:
+    """BATcalc<op>cst (b OP v) or, with cst_first, BATcalccst<op> (v OP b; gdk_calc_compare.h:928)"""
     a = _val(_storage(vtype), v)
+    if cst_first:
+        f = getattr(lib, f"b200_BATcalccst{op}")
+        if op in ("eq", "ne"):
+            return BAT(f(_vp(a), vtype, b._p, _ptr(s), nil_matches))
+        return BAT(f(_vp(a), vtype, b._p, _ptr(s)))
     f = getattr(lib, f"b200_BATcalc{op}cst")
     if op in ("eq", "ne"):
         return BAT(f(b._p, _vp(a), vtype, _ptr(s), nil_matches))

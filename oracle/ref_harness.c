@@ -317,6 +317,26 @@ refh_cmp_cst(int cmp, BAT *b, const void *v, int vtype, BAT *s, int nil_matches)
 	return bn;
 }
 
+/* constant on the left: BATcalccst<op>(v, b, s) */
+BAT *
+refh_cst_cmp(int cmp, const void *v, int vtype, BAT *b, BAT *s, int nil_matches)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	switch (cmp) {
+	case 0: bn = BATcalccstlt(&val, b, s); break;
+	case 1: bn = BATcalccstle(&val, b, s); break;
+	case 2: bn = BATcalccstgt(&val, b, s); break;
+	case 3: bn = BATcalccstge(&val, b, s); break;
+	case 4: bn = BATcalccsteq(&val, b, s, nil_matches); break;
+	case 5: bn = BATcalccstne(&val, b, s, nil_matches); break;
+	}
+	VALclear(&val);
+	return bn;
+}
+
 /* hashjoin is what BATjoin picks for unsorted inputs; expose the algorithm string of the
  * last call so tests can assert which implementation the oracle exercised */
 const char *

@@ -86,6 +86,8 @@ def _load(nthreads: int = 0):
     _h.refh_logic_cst.argtypes = [C.c_int, P, V, C.c_int, P]
     _h.refh_minmax_cst.restype = P
     _h.refh_minmax_cst.argtypes = [C.c_int, P, V, C.c_int, P]
+    _h.refh_cst_cmp.restype = P
+    _h.refh_cst_cmp.argtypes = [C.c_int, V, C.c_int, P, P, C.c_int]
     _h.refh_cmp_cst.restype = P
     _h.refh_cmp_cst.argtypes = [C.c_int, P, V, C.c_int, P, C.c_int]
     _h.refh_usec.restype = C.c_int64
@@ -356,8 +358,10 @@ def BATcalccmp(op, b1, b2, s1=None, s2=None, nil_matches=False) -> RBAT:
     return RBAT(f(b1.p, b2.p, _p(s1), _p(s2)), "BATcalc" + op)
 
 
-def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False) -> RBAT:
+def BATcalccmpcst(op, b, v, vtype, s=None, nil_matches=False, cst_first=False) -> RBAT:
     a = _val(vtype, v)
+    if cst_first:
+        return RBAT(_h.refh_cst_cmp(_CMPS[op], _vp(a), vtype, b.p, _p(s), nil_matches), "BATcalccst" + op)
     return RBAT(_h.refh_cmp_cst(_CMPS[op], b.p, _vp(a), vtype, _p(s), nil_matches), "BATcalc" + op + "cst")
 
 

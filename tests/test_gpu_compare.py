@@ -43,6 +43,12 @@ def test_compare_cst_candidates(gdk, ref, op):
             assert_same(gdk.BATcalccmpcst(op, b, vv, vt, cand), ref.BATcalccmpcst(op, rb, vv, vt, rcand))
             if op in ("eq", "ne"):
                 assert_same(gdk.BATcalccmpcst(op, b, vv, vt, cand, True), ref.BATcalccmpcst(op, rb, vv, vt, rcand, True))
+            # constant on the left: BATcalccst<op>(v, b, s)
+            assert_same(gdk.BATcalccmpcst(op, b, vv, vt, cand, cst_first=True),
+                        ref.BATcalccmpcst(op, rb, vv, vt, rcand, cst_first=True))
+            if op in ("eq", "ne"):
+                assert_same(gdk.BATcalccmpcst(op, b, vv, vt, cand, True, cst_first=True),
+                            ref.BATcalccmpcst(op, rb, vv, vt, rcand, True, cst_first=True))
 
 
 def test_compare_size_mismatch(gdk, ref):
