@@ -70,6 +70,13 @@ typedef struct b200_bat {
 	uint8_t  oidrange_known;	/* first_oid/last_oid valid (sorted oid tails we produced) */
 	uint8_t  pad;
 	uint64_t first_oid, last_oid;	/* smallest / largest oid of a sorted oid tail (cf. tminpos/tmaxpos) */
+	void    *parent;	/* views (owns == 0 slices of a device BAT of ours): the tail heap they share.  The heap
+				   carries a share count like the reference's BBP share on a view's parent
+				   (theap->parentid, gdk_bat.c VIEWcreate): it is released when the owner AND every
+				   view have been freed, in either order */
+	uint32_t producer;	/* id of the thread context (stream) that produced this BAT, 0 = none: a consumer or
+				   b200_BATfree on another thread orders its own stream behind that stream first */
+	uint32_t pad2;
 } b200_bat;
 
 /* ---- runtime / device heap tier (the tier added next to gdk_heap.c:141-225) ---- */
@@ -106,6 +113,9 @@ b200_return b200_BATextend(b200_bat *b, uint64_t newcap);	/* gdk_bat.c:529 / HEA
 void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool key, bool nonil, bool nil);
 int  b200_BATtohost(const b200_bat *b, void *dst);	/* logical tail -> host (void/cands materialised as oids) */
 void b200_BATfree(b200_bat *b);				/* BBPreclaim */
+/* the owner of a WRAPPED heap (b200_BATwrap / b200_BAThostwrap) rewrote it in place: forget what the library
+ * cached about the old contents (BAThash index, staged device copy).  Heaps the library owns are immutable. */
+void b200_BATinvalidate(const b200_bat *b);
 
 /* ---- selection: gdk_select.c:1342 (BATselect), :2102 (BATthetaselect) ---- */
 b200_bat *b200_BATselect(const b200_bat *b, const b200_bat *s, const void *tl, const void *th,
@@ -198,6 +208,11 @@ b200_return b200_BATgroupavg3(b200_bat **avgp, b200_bat **remp, b200_bat **cntp,
 b200_bat *b200_BATgroupavg3combine(const b200_bat *avg, const b200_bat *rem, const b200_bat *cnt, const b200_bat *g,
 				   const b200_bat *e, bool skip_nils);
 b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, double *avg, uint64_t *vals, int scale);
+/* phase 2 of the two-phase average (mergetable splits avg into per-slice sum + count, opt_mergetable.c:1204-1215):
+ * dbl averages from merged lng/hge sums and lng counts with BATgroupavg's own closing formula
+ * floor(S/n) + (dbl) rem / n, then / 10^scale (gdk_aggr.c:1741-1748,1952-1957) — bit-identical to one
+ * BATgroupavg over all the rows */
+b200_bat *b200_BATcalcavgsum(const b200_bat *sum, const b200_bat *cnt, int scale);
 b200_return b200_BATsum(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
 
 /* ---- min/max, between, ifthenelse: gdk_calc.h:24-33,87-95 (gdk_calc.c:976-2300, 3968-4290, 4376-4800).
@@ -255,6 +270,31 @@ b200_bat *b200_BATdiff(const b200_bat *l, const b200_bat *r, const b200_bat *sl,
  *      keys_out = oids_out = NULL to size the buffers first. ---- */
 b200_return b200_hash_partition(const b200_bat *b, const b200_bat *s, int nparts, bool keep_nil, void *keys_out,
 				b200_oid *oids_out, uint64_t *counts);
+
+b200_return b200_BATpartition(b200_bat **keysp, b200_bat **oidsp, const b200_bat *b, const b200_bat *s, int nparts,
+			      bool keep_nil, uint64_t *counts);	/* one-call form: the send runs as two new BATs */
+
+/* ---- multi-GPU inside the library (one process per GPU, NCCL on the calling thread's stream).
+ *      rank 0 makes the 128-byte id (ncclGetUniqueId) and the launcher hands it to every rank (bench.py: one
+ *      torch.distributed broadcast).  Collective entry points must be called by every rank, in the same order,
+ *      from the thread that called b200_comm_init.  world == 1 needs no NCCL and no id.
+ *  b200_comm_pack     = mat.pack across the ranks (mergetable's packing step, opt_mergetable.c:1204-1215):
+ *      out[i] = rank-order concatenation of every rank's in[i] (k <= 16 small BATs of at most max_rows rows each,
+ *      the same k / types / max_rows on every rank).  One ncclAllGather, one sync.  Phase 2 of a two-phase
+ *      aggregate is then ordinary GDK calls on the packed BATs.
+ *  b200_comm_exchange = the all-to-all of the repartitioning plans: k parallel device columns, each laid out as
+ *      `world` contiguous runs of send_counts[d] rows (b200_BATpartition), are exchanged with one grouped
+ *      ncclSend/ncclRecv; out[i] = run `rank` of every rank in rank order; recv_counts[r] (may be NULL) = rows
+ *      received from rank r.  The outputs are ready in stream order (no sync after the data movement). ---- */
+int  b200_comm_unique_id(void *out128);
+int  b200_comm_init(int rank, int world, const void *id128);
+int  b200_comm_rank(void);
+int  b200_comm_world(void);
+int  b200_comm_nccl_version(void);
+void b200_comm_destroy(void);
+b200_return b200_comm_pack(int k, const b200_bat *const *in, b200_bat **out, uint64_t max_rows);
+b200_return b200_comm_exchange(int k, const b200_bat *const *in, const uint64_t *send_counts, b200_bat **out,
+			       uint64_t *recv_counts);
 
 /* ---- window frames and analytic aggregates: gdk_analytic.h:21-42.
  *      As in the reference the CALLER allocates r (b200_COLnew of the result type,

@@ -10,8 +10,15 @@ Attributes are resolved lazily from :mod:`monetdb_b200.gdk` so that
 """
 
 
+_SUBMODULES = ("gdk", "pipelines", "shard", "workload", "build")
+
+
 def __getattr__(name):
     import importlib
+    if name in _SUBMODULES:
+        # `from monetdb_b200 import workload` must not load libgdk_b200.so (the reference arm of
+        # bench.py uses workload / pipelines / shard and must never map the CUDA library)
+        return importlib.import_module("." + name, __name__)
     gdk = importlib.import_module(".gdk", __name__)
     try:
         return getattr(gdk, name)

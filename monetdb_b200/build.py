@@ -20,6 +20,7 @@ ROOT = PKG.parent
 CSRC = PKG / "csrc"
 OBJ = CSRC / "_obj"
 LIB = PKG / "libgdk_b200.so"
+WLIB = PKG / "libworkload.so"          # host-side synthetic data generator (plain C, no CUDA)
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
@@ -51,7 +52,20 @@ def _compile(src: Path, force: bool, hdr_m: float, verbose: bool) -> Path:
     return obj
 
 
+def build_workload(force: bool = False) -> Path:
+    src = PKG / "hostsrc" / "workload_host.c"
+    if force or not WLIB.exists() or WLIB.stat().st_mtime < src.stat().st_mtime:
+        tmp = WLIB.with_suffix(".so.tmp")
+        r = subprocess.run([os.environ.get("CC", "gcc"), "-O2", "-fPIC", "-shared", "-Wall", "-o", str(tmp), str(src), "-lpthread"],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"gcc failed for {src.name}:\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, WLIB)
+    return WLIB
+
+
 def build_library(force: bool = False, verbose: bool = False) -> Path:
+    build_workload(force)
     OBJ.mkdir(exist_ok=True)
     srcs = sorted(CSRC.glob("*.cu"))
     if not srcs:
@@ -62,7 +76,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     if force or not LIB.exists() or any(o.stat().st_mtime > LIB.stat().st_mtime for o in objs):
         tmp = LIB.with_suffix(".so.tmp")
         cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
-               "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread"]
+               "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -1019,3 +1019,92 @@ extern "C" b200_return b200_BATcalcavg(const b200_bat *b, const b200_bat *s, dou
 		*vals = n;
 	return B200_SUCCEED;
 }
+
+// ---------------------------------------------------------------- average from merged (sum, count)
+// Phase 2 of the two-phase average (mergetable splits avg into sum + count per slice and recombines,
+// opt_mergetable.c:1204-1215).  To be bit-identical with ONE BATgroupavg over all rows the recombination
+// uses that function's own closing formula (gdk_aggr.c:1741-1748, 1952-1957): with a = floor(S / n) and
+// rem = S - a * n (the invariant AVERAGE_ITER maintains, 0 <= rem < n),  avg = a + (dbl) rem / n, then
+// / 10^scale.  S: lng or hge sums, n: lng counts; n == 0 / nil or S nil gives nil.
+template <typename TS>
+__global__ void avg_from_sum_kernel(const TS *__restrict__ sum, const lng *__restrict__ cnt, uint64_t n, double fac,
+				    dbl *__restrict__ out, unsigned long long *__restrict__ nils)
+{
+	const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	const TS S = sum[i];
+	const lng c = cnt[i];
+	if (Atom<TS>::is_nil(S) || Atom<lng>::is_nil(c) || c <= 0) {
+		out[i] = NAN;
+		atomicAdd(nils, 1ULL);
+		return;
+	}
+	const hge s = (hge) S;
+	hge a = s / c, rem = s % c;	/* C truncates towards zero */
+	if (rem < 0) {
+		a -= 1;
+		rem += c;
+	}
+	double r = (double) a + (double) (lng) rem / (double) c;
+	if (fac != 1.0)
+		r /= fac;
+	out[i] = r;
+}
+
+extern "C" b200_bat *b200_BATcalcavgsum(const b200_bat *sum, const b200_bat *cnt, int scale)
+{
+	b200_clrerr();
+	if (sum == nullptr || cnt == nullptr) {
+		set_err("BATcalcavgsum: sum and cnt required\n");
+		return nullptr;
+	}
+	Staged ss, sc;
+	if (!stage(sum, ss) || !stage(cnt, sc))
+		return nullptr;
+	sum = ss.b;
+	cnt = sc.b;
+	const int ts = basetype(sum->ttype);
+	if ((ts != B200_lng && ts != B200_hge) || basetype(cnt->ttype) != B200_lng || sum->ttype == B200_oid || cnt->ttype == B200_oid) {
+		set_err("BATcalcavgsum: sums must be lng or hge and counts lng\n");
+		return nullptr;
+	}
+	if (sum->count != cnt->count) {
+		set_err("inputs not the same size.\n");
+		return nullptr;
+	}
+	Ctx *c = ctx();
+	const uint64_t n = sum->count;
+	b200_bat *bn = bat_new(sum->hseqbase, B200_dbl, n);
+	if (bn == nullptr)
+		return nullptr;
+	unsigned long long nils = 0;
+	if (n > 0) {
+		unsigned long long *dn = (unsigned long long *) scratch_get(64);
+		const double fac = scale ? pow(10.0, (double) scale) : 1.0;
+		if (dn == nullptr || !cuda_ok(cudaMemsetAsync(dn, 0, 8, c->stream), "memset")) {
+			b200_BATfree(bn);
+			return nullptr;
+		}
+		const unsigned grid = (unsigned) ((n + 255) / 256);
+		if (ts == B200_hge)
+			avg_from_sum_kernel<hge><<<grid, 256, 0, c->stream>>>((const hge *) sum->base, (const lng *) cnt->base, n, fac,
+									    (dbl *) bn->base, dn);
+		else
+			avg_from_sum_kernel<lng><<<grid, 256, 0, c->stream>>>((const lng *) sum->base, (const lng *) cnt->base, n, fac,
+									    (dbl *) bn->base, dn);
+		COUNT_LAUNCH();
+		if (!cuda_ok(cudaGetLastError(), "avg launch") ||
+		    !cuda_ok(cudaMemcpyAsync(&c->slot_h->v[0], dn, 8, cudaMemcpyDeviceToHost, c->stream), "nil count") || !stream_sync()) {
+			b200_BATfree(bn);
+			return nullptr;
+		}
+		nils = c->slot_h->v[0];
+	}
+	ctx()->algo = "avg: from merged (sum, count)";
+	bn->count = n;
+	bn->tnil = nils != 0;
+	bn->tnonil = nils == 0;
+	bn->tsorted = bn->trevsorted = bn->tkey = n <= 1;
+	return bn;
+}

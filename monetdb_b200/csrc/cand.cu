@@ -29,6 +29,27 @@ extern "C" void b200_stage_cache_clear(void)
 	}
 }
 
+// the thread rebinds to another device (b200_init): the copies belong to the old one
+void stage_cache_retire(void)
+{
+	b200_stage_cache_clear();
+}
+
+// the owner rewrote one host heap (b200_BATinvalidate)
+void stage_cache_forget(const void *host)
+{
+	if (tl_stage == nullptr)
+		return;
+	for (size_t i = 0; i < tl_stage->size();) {
+		if ((*tl_stage)[i].host == host) {
+			dev_free((*tl_stage)[i].dev);
+			tl_stage->erase(tl_stage->begin() + i);
+		} else {
+			i++;
+		}
+	}
+}
+
 extern "C" void b200_stage_cache(int on)
 {
 	tl_stage_on = on != 0;
@@ -81,8 +102,12 @@ bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows)
 bool stage(const b200_bat *in, Staged &out)
 {
 	out.b = in;
-	if (in == nullptr || in->device >= 0)
+	if (in == nullptr)
 		return true;
+	if (in->device >= 0) {
+		order_after(in);	/* produced on another thread's stream without a sync? wait for it */
+		return true;
+	}
 	Ctx *c = ctx();
 	if (c->device < 0) {
 		set_err("b200: no usable CUDA device; this library has no CPU fallback\n");

@@ -1,0 +1,427 @@
+// comm.cu — the multi-GPU half of the path inside the library: one process per GPU, NCCL over
+// NVLink/NVSwitch on the calling thread's stream.
+//
+// Two primitives carry every plan that is not embarrassingly parallel:
+//
+//   b200_comm_pack      mat.pack across the ranks (the packing step of mergetable's two-phase plans,
+//                       opt_mergetable.c:1204-1215,1674-): out[i] = the rank-order concatenation of every
+//                       rank's in[i].  All k small BATs of a partial-aggregate table travel in ONE
+//                       fixed-size record per rank through ONE ncclAllGather; a single kernel unpacks
+//                       every record into the k result BATs and leaves their counts in the mapped result
+//                       slot, so the whole step costs two kernels, one collective and one sync.  Phase 2
+//                       is then ordinary GDK operators (BATgroup / BATgroupsum / BATsum) on the packed
+//                       BATs — which also reproduces BATgroup's first-occurrence numbering, because rank
+//                       r's rows all precede rank r+1's and each rank's partial table is in local
+//                       first-occurrence order.
+//   b200_comm_exchange  the one all-to-all of the repartitioning plans (hash join, high-cardinality
+//                       GROUP BY): k parallel arrays, each split into `world` contiguous runs by the same
+//                       per-destination counts (b200_BATpartition), are exchanged with one grouped
+//                       ncclSend/ncclRecv; the count matrix travels once through an ncclAllGather.
+//
+// NCCL is resolved at run time (dlopen "libnccl.so.2": the copy the process already maps — e.g. the one
+// bundled with torch in bench.py — or the system one), so a single-GPU user of the library needs no NCCL.
+#include "common.cuh"
+#include <dlfcn.h>
+#include <nccl.h>
+#include <mutex>
+#include <vector>
+#include <stdlib.h>
+
+#define PACK_MAXBATS 16
+#define PACK_HDR (PACK_MAXBATS * 2)	/* per BAT: count, flags (bit 0 = tnonil) */
+
+struct NcclApi {
+	void *h = nullptr;
+	ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+	ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+	ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*GroupStart)() = nullptr;
+	ncclResult_t (*GroupEnd)() = nullptr;
+	const char *(*GetErrorString)(ncclResult_t) = nullptr;
+	ncclResult_t (*GetVersion)(int *) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_comm_mu;
+static ncclComm_t g_comm = nullptr;
+static int g_rank = 0, g_world = 1, g_comm_device = -1;
+
+static bool nccl_load()
+{
+	if (g_nccl.h != nullptr)
+		return true;
+	const char *env = getenv("B200_NCCL_LIB");
+	const char *names[] = {env, "libnccl.so.2", "libnccl.so", nullptr};
+	void *h = nullptr;
+	for (int i = 0; i < 3 && h == nullptr; i++)
+		if (names[i] && names[i][0])
+			h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+	if (h == nullptr) {
+		set_err("b200_comm: cannot load NCCL (libnccl.so.2): %s\n", dlerror());
+		return false;
+	}
+#define SYM(field, name) \
+	do { *(void **) &g_nccl.field = dlsym(h, name); \
+	     if (g_nccl.field == nullptr) { set_err("b200_comm: NCCL lacks %s\n", name); return false; } } while (0)
+	SYM(GetUniqueId, "ncclGetUniqueId");
+	SYM(CommInitRank, "ncclCommInitRank");
+	SYM(CommDestroy, "ncclCommDestroy");
+	SYM(AllGather, "ncclAllGather");
+	SYM(Send, "ncclSend");
+	SYM(Recv, "ncclRecv");
+	SYM(GroupStart, "ncclGroupStart");
+	SYM(GroupEnd, "ncclGroupEnd");
+	SYM(GetErrorString, "ncclGetErrorString");
+	SYM(GetVersion, "ncclGetVersion");
+#undef SYM
+	g_nccl.h = h;
+	return true;
+}
+
+static bool nccl_ok(ncclResult_t r, const char *what)
+{
+	if (r == ncclSuccess)
+		return true;
+	set_err("NCCL error %s (%s)\n", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?", what);
+	return false;
+}
+#define NC(x) nccl_ok((x), #x)
+
+extern "C" int b200_comm_unique_id(void *out128)
+{
+	b200_clrerr();
+	if (out128 == nullptr || ctx()->device < 0 || !nccl_load())
+		return -1;
+	static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+	ncclUniqueId id;
+	if (!NC(g_nccl.GetUniqueId(&id)))
+		return -1;
+	memcpy(out128, &id, sizeof(id));
+	return 0;
+}
+
+extern "C" int b200_comm_init(int rank, int world, const void *id128)
+{
+	b200_clrerr();
+	Ctx *c = ctx();
+	if (c->device < 0) {
+		set_err("b200_comm_init: no usable CUDA device; this library has no CPU fallback\n");
+		return -1;
+	}
+	if (world < 1 || rank < 0 || rank >= world || (world > 1 && id128 == nullptr)) {
+		set_err("b200_comm_init: bad rank %d / world %d\n", rank, world);
+		return -1;
+	}
+	std::lock_guard<std::mutex> lk(g_comm_mu);
+	if (g_comm != nullptr) {
+		set_err("b200_comm_init: already initialised (rank %d of %d)\n", g_rank, g_world);
+		return -1;
+	}
+	g_rank = rank;
+	g_world = world;
+	g_comm_device = c->device;
+	if (world == 1)
+		return 0;
+	if (!nccl_load())
+		return -1;
+	ncclUniqueId id;
+	memcpy(&id, id128, sizeof(id));
+	if (!NC(g_nccl.CommInitRank(&g_comm, world, id, rank))) {
+		g_comm = nullptr;
+		g_world = 1;
+		g_rank = 0;
+		return -1;
+	}
+	return 0;
+}
+
+extern "C" int b200_comm_rank(void) { return g_rank; }
+extern "C" int b200_comm_world(void) { return g_world; }
+extern "C" int b200_comm_nccl_version(void)
+{
+	int v = 0;
+	if (g_nccl.h && g_nccl.GetVersion)
+		g_nccl.GetVersion(&v);
+	return v;
+}
+
+extern "C" void b200_comm_destroy(void)
+{
+	std::lock_guard<std::mutex> lk(g_comm_mu);
+	if (g_comm != nullptr) {
+		if (ctx()->device >= 0)
+			cudaStreamSynchronize(ctx()->stream);
+		g_nccl.CommDestroy(g_comm);
+		g_comm = nullptr;
+	}
+	g_world = 1;
+	g_rank = 0;
+}
+
+static bool comm_ready(const char *fn)
+{
+	Ctx *c = ctx();
+	if (c->device < 0) {
+		set_err("%s: no usable CUDA device; this library has no CPU fallback\n", fn);
+		return false;
+	}
+	if (g_world > 1 && (g_comm == nullptr || c->device != g_comm_device)) {
+		set_err("%s: call b200_comm_init on this device first\n", fn);
+		return false;
+	}
+	return true;
+}
+
+// ---------------------------------------------------------------- pack
+struct PackSrc {
+	const void *base[PACK_MAXBATS];		/* NULL: void tail, oids from tseq */
+	unsigned long long tseq[PACK_MAXBATS];
+	unsigned long long count[PACK_MAXBATS];
+	unsigned long long flags[PACK_MAXBATS];
+	unsigned width[PACK_MAXBATS];
+	unsigned long long off[PACK_MAXBATS];	/* byte offset of BAT i's region inside a record */
+	int k;
+};
+struct PackDst {
+	void *base[PACK_MAXBATS];
+	unsigned width[PACK_MAXBATS];
+	unsigned long long off[PACK_MAXBATS];
+	unsigned long long recbytes;
+	int k, world;
+};
+
+// one CTA per BAT: copy its tail into this rank's record (bytes; the tables are tiny)
+__global__ void pack_record_kernel(PackSrc s, unsigned char *__restrict__ rec)
+{
+	const int i = blockIdx.x;
+	unsigned long long *hdr = (unsigned long long *) rec;
+	if (threadIdx.x == 0) {
+		hdr[2 * i] = s.count[i];
+		hdr[2 * i + 1] = s.flags[i];
+	}
+	unsigned char *dst = rec + s.off[i];
+	if (s.base[i] != nullptr) {
+		const unsigned char *src = (const unsigned char *) s.base[i];
+		const unsigned long long nb = s.count[i] * s.width[i];
+		for (unsigned long long b = threadIdx.x; b < nb; b += blockDim.x)
+			dst[b] = src[b];
+	} else {
+		oid *d = (oid *) dst;
+		for (unsigned long long r = threadIdx.x; r < s.count[i]; r += blockDim.x)
+			d[r] = s.tseq[i] == OID_NIL ? OID_NIL : s.tseq[i] + r;
+	}
+}
+
+// one CTA per BAT: concatenate the ranks' regions in rank order; totals and the AND of the flags -> slot
+__global__ void pack_unpack_kernel(PackDst d, const unsigned char *__restrict__ recs, unsigned long long *__restrict__ slot)
+{
+	const int i = blockIdx.x;
+	unsigned long long run = 0, flags = ~0ULL;
+	unsigned char *dst = (unsigned char *) d.base[i];
+	for (int r = 0; r < d.world; r++) {
+		const unsigned char *rec = recs + (unsigned long long) r * d.recbytes;
+		const unsigned long long *hdr = (const unsigned long long *) rec;
+		const unsigned long long cnt = hdr[2 * i], nb = cnt * d.width[i];
+		flags &= hdr[2 * i + 1];
+		const unsigned char *src = rec + d.off[i];
+		for (unsigned long long b = threadIdx.x; b < nb; b += blockDim.x)
+			dst[run * d.width[i] + b] = src[b];
+		run += cnt;
+	}
+	if (threadIdx.x == 0) {
+		slot[i] = run;
+		slot[PACK_MAXBATS + i] = flags;
+	}
+}
+
+static_assert(sizeof(ResultSlot) >= 2 * PACK_MAXBATS * 8, "the result slot holds a count and a flag word per packed BAT");
+
+extern "C" b200_return b200_comm_pack(int k, const b200_bat *const *in, b200_bat **out, uint64_t max_rows)
+{
+	b200_clrerr();
+	if (!comm_ready("b200_comm_pack"))
+		return B200_FAIL;
+	if (k < 1 || k > PACK_MAXBATS || in == nullptr || out == nullptr || max_rows == 0) {
+		set_err("b200_comm_pack: 1 <= k <= %d BATs and max_rows > 0 required\n", PACK_MAXBATS);
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	Staged st[PACK_MAXBATS];
+	PackSrc s;
+	PackDst d;
+	memset(&s, 0, sizeof(s));
+	memset(&d, 0, sizeof(d));
+	unsigned long long off = PACK_HDR * 8;
+	int types[PACK_MAXBATS];
+	for (int i = 0; i < k; i++) {
+		out[i] = nullptr;
+		if (in[i] == nullptr || !stage(in[i], st[i]))
+			return B200_FAIL;
+		const b200_bat *b = st[i].b;
+		if (b->ccand != B200_CAND_NONE || b->ttype == B200_msk) {
+			set_err("b200_comm_pack: complex candidate lists / msk tails are not packed; BATunmask them first\n");
+			return B200_FAIL;
+		}
+		if (b->count > max_rows) {
+			set_err("b200_comm_pack: BAT %d has %llu rows, more than max_rows = %llu (a partial table this large "
+				"needs the repartition plan, b200_BATpartition + b200_comm_exchange)\n", i,
+				(unsigned long long) b->count, (unsigned long long) max_rows);
+			return B200_FAIL;
+		}
+		types[i] = b->ttype == B200_void ? B200_oid : b->ttype;
+		const int w = atomsize(types[i]);
+		s.base[i] = b->ttype == B200_void ? nullptr : b->base;
+		s.tseq[i] = b->tseqbase;
+		s.count[i] = b->count;
+		s.flags[i] = (b->tnonil || b->count == 0 || (b->ttype == B200_void && b->tseqbase != OID_NIL)) ? 1 : 0;
+		s.width[i] = d.width[i] = (unsigned) w;
+		s.off[i] = d.off[i] = off;
+		off += (max_rows * w + 15) & ~15ULL;
+	}
+	s.k = d.k = k;
+	d.world = g_world;
+	d.recbytes = off;
+	unsigned char *recs = (unsigned char *) dev_alloc((size_t) off * (g_world + 1));
+	if (recs == nullptr)
+		return B200_FAIL;
+	unsigned char *mine = recs + (size_t) off * g_world;	/* send record (allgather is not in place here) */
+	bool ok = true;
+	for (int i = 0; i < k && ok; i++) {
+		out[i] = bat_new(0, types[i], max_rows * g_world);
+		ok = out[i] != nullptr;
+		if (ok)
+			d.base[i] = out[i]->base;
+	}
+	if (ok) {
+		KTimer kt("comm_pack", off);
+		pack_record_kernel<<<k, 128, 0, c->stream>>>(s, g_world > 1 ? mine : recs);
+		COUNT_LAUNCH();
+		if (g_world > 1)
+			ok = NC(g_nccl.AllGather(mine, recs, off, ncclUint8, g_comm, c->stream));
+		if (ok) {
+			pack_unpack_kernel<<<k, 128, 0, c->stream>>>(d, recs, c->slot_d->v);
+			COUNT_LAUNCH();
+		}
+	}
+	ok = ok && cuda_ok(cudaGetLastError(), "comm_pack launch") && stream_sync();
+	dev_free(recs);
+	if (!ok) {
+		for (int i = 0; i < k; i++) {
+			b200_BATfree(out[i]);
+			out[i] = nullptr;
+		}
+		return B200_FAIL;
+	}
+	ctx()->algo = g_world > 1 ? "pack: nccl allgather of one record per rank" : "pack: single rank";
+	for (int i = 0; i < k; i++) {
+		b200_bat *bn = out[i];
+		bn->count = c->slot_h->v[i];
+		bn->tnonil = (c->slot_h->v[PACK_MAXBATS + i] & 1) != 0;
+		bn->tnil = 0;
+		bn->tsorted = bn->trevsorted = bn->tkey = bn->count <= 1;
+	}
+	return B200_SUCCEED;
+}
+
+// ---------------------------------------------------------------- exchange
+extern "C" b200_return b200_comm_exchange(int k, const b200_bat *const *in, const uint64_t *send_counts, b200_bat **out,
+					  uint64_t *recv_counts)
+{
+	b200_clrerr();
+	if (!comm_ready("b200_comm_exchange"))
+		return B200_FAIL;
+	if (k < 1 || k > PACK_MAXBATS || in == nullptr || out == nullptr || send_counts == nullptr) {
+		set_err("b200_comm_exchange: 1 <= k <= %d BATs and send_counts required\n", PACK_MAXBATS);
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	const int W = g_world;
+	uint64_t total_send = 0;
+	for (int r = 0; r < W; r++)
+		total_send += send_counts[r];
+	for (int i = 0; i < k; i++) {
+		out[i] = nullptr;
+		if (in[i] == nullptr || in[i]->device < 0 || in[i]->ttype == B200_void || in[i]->ccand != B200_CAND_NONE ||
+		    in[i]->count != total_send) {
+			set_err("b200_comm_exchange: BAT %d must be a materialised device column of sum(send_counts) rows\n", i);
+			return B200_FAIL;
+		}
+		order_after(in[i]);
+	}
+	// the count matrix: every rank learns how much every rank sends to everyone (one all-gather)
+	std::vector<uint64_t> mat((size_t) W * W, 0);
+	if (W == 1) {
+		mat[0] = send_counts[0];
+	} else {
+		unsigned long long *dev = (unsigned long long *) dev_alloc((size_t) (W + 1) * W * 8);
+		if (dev == nullptr)
+			return B200_FAIL;
+		bool ok = cuda_ok(cudaMemcpyAsync(dev + (size_t) W * W, send_counts, W * 8, cudaMemcpyHostToDevice, c->stream), "counts up") &&
+			  NC(g_nccl.AllGather(dev + (size_t) W * W, dev, W, ncclUint64, g_comm, c->stream)) &&
+			  cuda_ok(cudaMemcpyAsync(mat.data(), dev, (size_t) W * W * 8, cudaMemcpyDeviceToHost, c->stream), "counts down") &&
+			  stream_sync();
+		dev_free(dev);
+		if (!ok)
+			return B200_FAIL;
+	}
+	uint64_t total_recv = 0;
+	std::vector<uint64_t> roff(W + 1, 0), soff(W + 1, 0);
+	for (int r = 0; r < W; r++) {
+		const uint64_t n = mat[(size_t) r * W + g_rank];	/* what rank r sends to me */
+		if (recv_counts)
+			recv_counts[r] = n;
+		roff[r + 1] = roff[r] + n;
+		soff[r + 1] = soff[r] + send_counts[r];
+		total_recv += n;
+	}
+	bool ok = true;
+	for (int i = 0; i < k && ok; i++) {
+		out[i] = bat_new(0, in[i]->ttype, total_recv);
+		ok = out[i] != nullptr;
+	}
+	if (ok) {
+		uint64_t bytes = 0;
+		for (int i = 0; i < k; i++)
+			bytes += (total_send + total_recv) * atomsize(in[i]->ttype);
+		KTimer kt("comm_exchange", bytes);
+		if (W > 1)
+			ok = NC(g_nccl.GroupStart());
+		for (int i = 0; i < k && ok; i++) {
+			const int w = atomsize(in[i]->ttype);
+			for (int r = 0; r < W && ok; r++) {
+				const char *sp = (const char *) in[i]->base + soff[r] * w;
+				char *rp = (char *) out[i]->base + roff[r] * w;
+				const uint64_t ns = send_counts[r], nr = roff[r + 1] - roff[r];
+				if (r == g_rank) {
+					if (ns)
+						ok = cuda_ok(cudaMemcpyAsync(rp, sp, ns * w, cudaMemcpyDeviceToDevice, c->stream), "exchange self copy");
+					continue;
+				}
+				if (ns)
+					ok = NC(g_nccl.Send(sp, ns * w, ncclUint8, r, g_comm, c->stream));
+				if (ok && nr)
+					ok = NC(g_nccl.Recv(rp, nr * w, ncclUint8, r, g_comm, c->stream));
+			}
+		}
+		if (W > 1)
+			ok = NC(g_nccl.GroupEnd()) && ok;
+	}
+	if (!ok) {
+		for (int i = 0; i < k; i++) {
+			b200_BATfree(out[i]);
+			out[i] = nullptr;
+		}
+		return B200_FAIL;
+	}
+	ctx()->algo = W > 1 ? "exchange: nccl grouped send/recv" : "exchange: single rank";
+	for (int i = 0; i < k; i++) {
+		b200_bat *bn = out[i];
+		bn->count = total_recv;
+		bn->tnonil = in[i]->tnonil;
+		bn->tnil = 0;
+		bn->tsorted = bn->trevsorted = bn->tkey = total_recv <= 1;
+	}
+	return B200_SUCCEED;
+}

@@ -91,7 +91,7 @@ static inline const char *atomname(int t)
 
 // ---------------------------------------------------------------- thread context
 struct ResultSlot {		/* mapped pinned memory the finishing kernels write into */
-	unsigned long long v[16];
+	unsigned long long v[64];
 };
 struct Ctx {
 	int device = -1;
@@ -101,6 +101,8 @@ struct Ctx {
 	size_t scratch_bytes = 0;
 	char err[1024] = {0};
 	const char *algo = "";
+	uint32_t id = 0;		/* index + 1 in the context registry (b200_bat.producer) */
+	cudaEvent_t ev = nullptr;	/* scratch event for order_after() */
 };
 Ctx *ctx();				/* lazily initialises device 0 if b200_init was not called */
 extern std::atomic<unsigned long long> g_launches;
@@ -121,6 +123,15 @@ bool cuda_ok(cudaError_t e, const char *what);
 
 void *dev_alloc(size_t bytes);		/* stream-ordered pool allocation, NULL + error on failure */
 void dev_free(void *p);
+// Cross-thread ordering (every thread has its own non-blocking stream): each descriptor names the
+// context that made it; stage() — which every entry point runs on every input — and b200_BATfree()
+// order the calling thread's stream behind the producer stream's tail when the BAT comes from another
+// context of the same device.  Same-thread use needs nothing (stream order).
+void order_after(const b200_bat *b);
+// Share counts of heaps that have views (BATproject with dense candidates returns a slice view).
+void heap_share(const void *root);
+bool heap_unshare(const void *root);		/* true: the last view of an orphaned heap went away, free it */
+bool heap_owner_release(const void *root);	/* true: no views, free now; false: orphaned, the last view frees */
 void hash_cache_drop(const void *base);	/* join.cu: forget a cached BAThash index */
 
 // Narrow twins of columns this library produced itself, kept beside the descriptor and keyed by

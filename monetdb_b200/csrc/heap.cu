@@ -7,12 +7,15 @@
 #include <unordered_map>
 #include "scan.cuh"
 #include <mutex>
+#include <vector>
 #include <stdlib.h>
 
 std::atomic<unsigned long long> g_launches{0};
 static thread_local Ctx *tl_ctx = nullptr;
 static std::mutex g_pool_mu;
 static bool g_pool_ready[64] = {false};
+static std::mutex g_ctx_mu;
+static std::vector<Ctx *> g_ctxs;		/* every context ever created; index = id - 1 (kept for their events) */
 
 void set_err(const char *fmt, ...)
 {
@@ -75,7 +78,54 @@ static Ctx *ctx_create(int device)
 		return c;
 	}
 	memset(c->slot_h, 0, sizeof(ResultSlot));
+	if (!cuda_ok(cudaEventCreateWithFlags(&c->ev, cudaEventDisableTiming), "event create")) {
+		c->device = -1;
+		return c;
+	}
+	{
+		std::lock_guard<std::mutex> lk(g_ctx_mu);
+		g_ctxs.push_back(c);
+		c->id = (uint32_t) g_ctxs.size();
+	}
 	return c;
+}
+
+// the calling thread rebinds to another device: give back what the old context held.  The struct and its
+// event stay registered because BATs it produced may still name it as their producer.
+static void ctx_retire(Ctx *c)
+{
+	if (c == nullptr || c->device < 0)
+		return;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	if (c->scratch)
+		cudaFree(c->scratch);
+	c->scratch = nullptr;
+	c->scratch_bytes = 0;
+	if (c->slot_h)
+		cudaFreeHost(c->slot_h);
+	c->slot_h = c->slot_d = nullptr;
+	cudaStreamDestroy(c->stream);
+	c->stream = nullptr;
+	c->device = -1;
+}
+
+// Every descriptor is tagged with the context that made it (bat_alloc_desc).  A consumer on another
+// thread records an event at the producer stream's current tail — everything that wrote the BAT was
+// submitted before the BAT was handed over — and orders its own stream behind it.
+void order_after(const b200_bat *b)
+{
+	Ctx *c = tl_ctx;
+	if (b == nullptr || b->producer == 0 || c == nullptr || c->device < 0 || b->producer == c->id)
+		return;
+	std::lock_guard<std::mutex> lk(g_ctx_mu);
+	if (b->producer > g_ctxs.size())
+		return;
+	Ctx *p = g_ctxs[b->producer - 1];
+	if (p->stream == nullptr || p->device != c->device)
+		return;		/* retired (it synchronised on the way out) or another device */
+	if (cudaEventRecord(c->ev, p->stream) == cudaSuccess)
+		cudaStreamWaitEvent(c->stream, c->ev, 0);
 }
 
 Ctx *ctx()
@@ -110,8 +160,12 @@ void *dev_alloc(size_t bytes)
 
 void dev_free(void *p)
 {
-	if (p && tl_ctx && tl_ctx->device >= 0)
+	if (p == nullptr)
+		return;
+	if (tl_ctx && tl_ctx->device >= 0)
 		cudaFreeAsync(p, tl_ctx->stream);
+	else
+		cudaFree(p);		/* a thread without a context (or after ctx_retire): synchronous release */
 }
 
 void *scratch_get(size_t bytes)
@@ -159,9 +213,10 @@ extern "C" int b200_init(int device)
 {
 	if (tl_ctx != nullptr && tl_ctx->device == device)
 		return 0;
-	if (tl_ctx != nullptr && tl_ctx->device >= 0) {
-		cudaSetDevice(tl_ctx->device);
-		cudaStreamSynchronize(tl_ctx->stream);
+	if (tl_ctx != nullptr) {
+		extern void stage_cache_retire(void);
+		stage_cache_retire();
+		ctx_retire(tl_ctx);
 	}
 	Ctx *c = ctx_create(device);
 	return c->device >= 0 ? 0 : -1;
@@ -203,6 +258,7 @@ b200_bat *bat_alloc_desc()
 	}
 	b->tseqbase = OID_NIL;
 	b->device = tl_ctx ? tl_ctx->device : -1;
+	b->producer = tl_ctx ? tl_ctx->id : 0;
 	return b;
 }
 
@@ -396,34 +452,91 @@ void shadow_drop(const void *base)
 	dev_free(s.p2);
 }
 
+// ---------------------------------------------------------------- heap share counts (views)
+struct HeapShare { uint64_t views = 0; bool orphan = false; };
+static std::mutex g_share_mu;
+static std::unordered_map<const void *, HeapShare> g_shares;
+
+void heap_share(const void *root)
+{
+	std::lock_guard<std::mutex> lk(g_share_mu);
+	g_shares[root].views++;
+}
+
+bool heap_unshare(const void *root)
+{
+	std::lock_guard<std::mutex> lk(g_share_mu);
+	auto it = g_shares.find(root);
+	if (it == g_shares.end())
+		return false;
+	if (--it->second.views > 0)
+		return false;
+	const bool orphan = it->second.orphan;
+	g_shares.erase(it);
+	return orphan;
+}
+
+bool heap_owner_release(const void *root)
+{
+	std::lock_guard<std::mutex> lk(g_share_mu);
+	auto it = g_shares.find(root);
+	if (it == g_shares.end())
+		return true;
+	it->second.orphan = true;
+	return false;
+}
+
+static void heap_release(void *p, int device)
+{
+	if (p == nullptr)
+		return;
+	if (tl_ctx && tl_ctx->device == device) {
+		dev_free(p);
+	} else {
+		/* freed from a thread bound to another device (or to none): synchronous path */
+		cudaFree(p);
+	}
+}
+
 extern "C" void b200_BATfree(b200_bat *b)
 {
 	if (b == nullptr)
 		return;
-	if (b->device >= 0 && b->base != nullptr)
-		hash_cache_drop(b->base);	/* a BAThash index dies with its BAT */
-	if (b->device >= 0 && b->base != nullptr && b->owns)
+	if (b->device >= 0)
+		order_after(b);		/* a free on this thread's stream must not overtake the producer's kernels */
+	if (b->device >= 0 && b->base != nullptr && b->owns) {
+		/* what the library cached about this heap dies with its owner — never with a view or a
+		 * wrapped alias (owns == 0), which would discard the parent's BAThash index */
+		hash_cache_drop(b->base);
 		shadow_drop(b->base);
-	if (b->owns) {
+	}
+	if (b->parent != nullptr) {
+		if (heap_unshare(b->parent))
+			heap_release(b->parent, b->device);
+	} else if (b->owns) {
 		if (b->device >= 0) {
-			if (tl_ctx && tl_ctx->device == b->device) {
-				dev_free(b->base);
-				dev_free(b->vheap);
-			} else {
-				/* freed from another thread/device context: synchronous path */
-				int cur = -1;
-				cudaGetDevice(&cur);
-				cudaSetDevice(b->device);
-				if (b->base) cudaFree(b->base);
-				if (b->vheap) cudaFree(b->vheap);
-				if (cur >= 0) cudaSetDevice(cur);
-			}
+			if (b->base == nullptr || heap_owner_release(b->base))
+				heap_release(b->base, b->device);
+			heap_release(b->vheap, b->device);
 		} else {
 			free(b->base);
 			free(b->vheap);
 		}
 	}
 	free(b);
+}
+
+extern "C" void b200_BATinvalidate(const b200_bat *b)
+{
+	if (b == nullptr || b->base == nullptr)
+		return;
+	extern void stage_cache_forget(const void *host);
+	if (b->device >= 0) {
+		hash_cache_drop(b->base);
+		shadow_drop(b->base);
+	} else {
+		stage_cache_forget(b->base);
+	}
 }
 
 extern "C" b200_bat *b200_BATnegcands_fromhost(uint64_t seq, uint64_t cnt, const b200_oid *exceptions, uint64_t nexc)
@@ -568,7 +681,6 @@ b200_bat *bat_constant(uint64_t hseq, int tt, const void *val, uint64_t n)
 }
 
 // ---------------------------------------------------------------- kernel timing
-#include <vector>
 #include <string>
 struct KRec { const char *name; uint64_t bytes; cudaEvent_t a, b; };
 static thread_local std::vector<KRec> *tl_krecs = nullptr;

@@ -69,7 +69,7 @@ partition_scatter_kernel(ColSrc<T> src, unsigned nparts, bool keep_nil, unsigned
 
 template <typename T>
 static bool partition_typed(const b200_bat *b, const Cand &ci, unsigned nparts, bool keep_nil, void *keys_out, oid *oids_out,
-			    uint64_t *counts)
+			    uint64_t *counts, b200_bat **keysp = nullptr, b200_bat **oidsp = nullptr)
 {
 	Ctx *c = ctx();
 	ColSrc<T> src = col_src<T>(b, ci);
@@ -99,6 +99,22 @@ static bool partition_typed(const b200_bat *b, const Cand &ci, unsigned nparts, 
 			counts[i] = h[i];
 			off[i] = run;
 			run += h[i];
+		}
+		if (keysp != nullptr) {
+			/* b200_BATpartition: the send runs are BATs sized by the histogram just read */
+			*keysp = bat_new(0, b->ttype, run);
+			*oidsp = bat_new(0, B200_oid, run);
+			if (*keysp == nullptr || *oidsp == nullptr) {
+				dev_free(dev);
+				return false;
+			}
+			(*keysp)->count = (*oidsp)->count = run;
+			(*keysp)->tnonil = !keep_nil || b->tnonil;
+			(*oidsp)->tnonil = 1;
+			(*keysp)->tsorted = (*keysp)->trevsorted = (*keysp)->tkey = run <= 1;
+			(*oidsp)->tsorted = (*oidsp)->trevsorted = (*oidsp)->tkey = run <= 1;
+			keys_out = (*keysp)->base;
+			oids_out = (oid *) (*oidsp)->base;
 		}
 		if (keys_out != nullptr && run > 0) {
 			ok = cuda_ok(cudaMemcpyAsync(dev + PT_MAXPARTS, off, nparts * 8, cudaMemcpyHostToDevice, c->stream), "partition cursors");
@@ -155,6 +171,50 @@ extern "C" b200_return b200_hash_partition(const b200_bat *b, const b200_bat *s,
 	default:
 		set_err("b200_hash_partition: type %s is not on the device path (fixed-width atoms only)\n", atomname(b->ttype));
 		return B200_FAIL;
+	}
+	return ok ? B200_SUCCEED : B200_FAIL;
+}
+
+// One call form of the above for the library's own exchange step (b200_comm_exchange): *keysp / *oidsp are new
+// BATs (b's atom type / oid) holding the tuples of destination d at offset sum(counts[0..d)).
+extern "C" b200_return b200_BATpartition(b200_bat **keysp, b200_bat **oidsp, const b200_bat *b, const b200_bat *s, int nparts,
+					 bool keep_nil, uint64_t *counts)
+{
+	b200_clrerr();
+	if (b == nullptr || counts == nullptr || keysp == nullptr || oidsp == nullptr || nparts < 1 || nparts > PT_MAXPARTS) {
+		set_err("b200_BATpartition: needs b, outputs, counts and 1 <= nparts <= %d\n", PT_MAXPARTS);
+		return B200_FAIL;
+	}
+	*keysp = *oidsp = nullptr;
+	Staged sb, ss;
+	if (!stage(b, sb) || !stage(s, ss))
+		return B200_FAIL;
+	b = sb.b;
+	Cand ci;
+	if (!cand_init(ci, b, ss.b))
+		return B200_FAIL;
+	if (b->ttype == B200_void || b->base == nullptr) {
+		set_err("b200_BATpartition: key column must be materialised\n");
+		return B200_FAIL;
+	}
+	ctx()->algo = "partition: cuda hash scatter";
+	bool ok = false;
+	switch (basetype(b->ttype)) {
+	case B200_bte: ok = partition_typed<bte>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_sht: ok = partition_typed<sht>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_int: ok = partition_typed<int>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_lng: ok = partition_typed<lng>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_hge: ok = partition_typed<hge>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_flt: ok = partition_typed<flt>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	case B200_dbl: ok = partition_typed<dbl>(b, ci, nparts, keep_nil, nullptr, nullptr, counts, keysp, oidsp); break;
+	default:
+		set_err("b200_BATpartition: type %s is not on the device path (fixed-width atoms only)\n", atomname(b->ttype));
+		return B200_FAIL;
+	}
+	if (!ok) {
+		b200_BATfree(*keysp);
+		b200_BATfree(*oidsp);
+		*keysp = *oidsp = nullptr;
 	}
 	return ok ? B200_SUCCEED : B200_FAIL;
 }

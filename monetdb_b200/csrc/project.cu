@@ -7,6 +7,7 @@
 // (16/w rows), reading its oids with 128-bit loads; the value reads are the
 // gather.
 #include "common.cuh"
+#include <utility>
 #include "compact.cuh"
 
 template <int W> struct WordOf;
@@ -148,27 +149,68 @@ static b200_bat *constant_nil(uint64_t hseq, int tt, uint64_t n)
 	return bat_constant(hseq, tt, nullptr, n);
 }
 
-static b200_bat *slice_view(const b200_bat *r, uint64_t lo, uint64_t hi, uint64_t hseq)
+// BATslice (gdk_batop.c:1825) of a column for BATproject with dense candidates.  `r` is the staged
+// form of the caller's BAT and `st` says how it was staged:
+//  * device-resident column of ours: a view that shares the heap and holds a share on it
+//    (heap_share, the BBP share the reference's VIEWcreate takes on the parent), so owner and views
+//    can be freed in any order;
+//  * a wrapped device heap (b200_BATwrap): a plain alias, the wrapper's owner controls the lifetime
+//    exactly as it does for the wrapped BAT itself;
+//  * HOST column staged for this call: the staged device copy is a temporary, so the result takes
+//    the copy over when it is the whole column and uncached, and is copied out of it otherwise.
+static b200_bat *slice_view(const b200_bat *r, const Staged &st, uint64_t lo, uint64_t hi, uint64_t hseq)
 {
-	/* BATslice (gdk_batop.c:1825) of a device-resident column: a view sharing r's heap */
 	if (r->ttype == B200_void) {
 		b200_bat *bn = bat_dense(hseq, r->tseqbase == OID_NIL ? OID_NIL : r->tseqbase + lo, hi - lo);
 		return bn;
 	}
-	b200_bat *bn = bat_alloc_desc();
-	if (bn == nullptr)
-		return nullptr;
+	const int w = atomsize(r->ttype);
+	const bool from_host = st.tmp != nullptr;
+	b200_bat *bn = nullptr;
+	if (from_host) {
+		if (lo == 0 && st.tmp->owns) {	/* owns: a private staged copy (not the stage cache's, not mapped host memory) */
+			/* take the staged heap over */
+			bn = bat_alloc_desc();
+			if (bn == nullptr)
+				return nullptr;
+			bn->base = st.tmp->base;
+			bn->capacity = st.tmp->capacity;
+			bn->owns = 1;
+			st.tmp->base = nullptr;
+		} else {
+			bn = bat_new(hseq, r->ttype, hi - lo);
+			if (bn == nullptr)
+				return nullptr;
+			if (hi > lo && !cuda_ok(cudaMemcpyAsync(bn->base, (const char *) r->base + lo * w, (hi - lo) * w,
+								 cudaMemcpyDefault, ctx()->stream), "project: slice copy")) {
+				b200_BATfree(bn);
+				return nullptr;
+			}
+		}
+	} else {
+		bn = bat_alloc_desc();
+		if (bn == nullptr)
+			return nullptr;
+		bn->base = (char *) r->base + lo * w;
+		bn->capacity = hi - lo;
+		bn->owns = 0;
+		bn->producer = r->producer;	/* a view is as ready as the heap it shares */
+		const void *root = r->parent ? r->parent : (r->owns ? r->base : nullptr);
+		if (root) {
+			heap_share(root);
+			bn->parent = (void *) root;
+		}
+	}
 	bn->ttype = r->ttype;
 	bn->device = r->device;
 	bn->hseqbase = hseq;
-	bn->count = bn->capacity = hi - lo;
-	bn->base = (char *) r->base + lo * atomsize(r->ttype);
-	bn->owns = 0;
+	bn->count = hi - lo;
 	bn->tsorted = r->tsorted || hi - lo <= 1;
 	bn->trevsorted = r->trevsorted || hi - lo <= 1;
 	bn->tkey = r->tkey || hi - lo <= 1;
 	bn->tnonil = r->tnonil;
 	bn->tnil = 0;
+	bn->oidrange_known = 0;
 	if (r->oidrange_known && r->tsorted && lo == 0 && hi == r->count) {
 		bn->oidrange_known = 1;
 		bn->first_oid = r->first_oid;
@@ -193,6 +235,9 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 	if (r2 && r1->count == 0) {
 		r1 = r2;
 		r2 = nullptr;
+		std::swap(s1.b, s2.b);
+		std::swap(s1.tmp, s2.tmp);
+		std::swap(s1.cached, s2.cached);
 	}
 	if (r1->ccand != B200_CAND_NONE || (r2 && r2->ccand != B200_CAND_NONE) || r1->ttype == B200_msk) {
 		set_err("BATproject: complex candidate lists / msk on the right-hand side are not on the device path\n");
@@ -208,7 +253,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		oid lo = l->tseqbase, hi = l->tseqbase + lcount;
 		if (lo >= r1->hseqbase && hi <= r1->hseqbase + r1->count) {
 			ctx()->algo = "project: slice view";
-			return slice_view(r1, lo - r1->hseqbase, hi - r1->hseqbase, l->hseqbase);
+			return slice_view(r1, s1, lo - r1->hseqbase, hi - r1->hseqbase, l->hseqbase);
 		}
 		if (lo < r1->hseqbase || r2 == nullptr || hi > r2->hseqbase + r2->count) {
 			set_err("does not match always\n");
@@ -216,7 +261,7 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		}
 		if (lo >= r2->hseqbase) {
 			ctx()->algo = "project: slice2 view";
-			return slice_view(r2, lo - r2->hseqbase, hi - r2->hseqbase, l->hseqbase);
+			return slice_view(r2, s2, lo - r2->hseqbase, hi - r2->hseqbase, l->hseqbase);
 		}
 	}
 	/* normalise l to an oid array */

@@ -90,6 +90,7 @@ class _bat(C.Structure):
         ("tnonil", C.c_uint8), ("tnil", C.c_uint8), ("owns", C.c_uint8),
         ("oidrange_known", C.c_uint8), ("pad", C.c_uint8),
         ("first_oid", C.c_uint64), ("last_oid", C.c_uint64),
+        ("parent", C.c_void_p), ("producer", C.c_uint32), ("pad2", C.c_uint32),
     ]
 
 
@@ -125,6 +126,7 @@ _sig("b200_BATextend", C.c_int, _P, C.c_uint64)
 _sig("b200_BATsetprops", None, _P, C.c_bool, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
 _sig("b200_BATtohost", C.c_int, _P, C.c_void_p)
 _sig("b200_BATfree", None, _P)
+_sig("b200_BATinvalidate", None, _P)
 _sig("b200_BATselect", _P, _P, _P, C.c_void_p, C.c_void_p, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
 _sig("b200_BATthetaselect", _P, _P, _P, C.c_void_p, C.c_char_p)
 for _n in ("b200_BATmergecand", "b200_BATintersectcand", "b200_BATdiffcand", "b200_BATproject"):
@@ -676,6 +678,14 @@ def BATcalcavg(b, s=None, scale=0):
     return avg.value, n.value
 
 
+_sig("b200_BATcalcavgsum", _P, _P, _P, C.c_int)
+
+
+def BATcalcavgsum(sums: BAT, cnts: BAT, scale: int = 0) -> BAT:
+    """dbl averages from merged (sum, count) with BATgroupavg's closing formula (phase 2 of a two-phase avg)"""
+    return BAT(lib.b200_BATcalcavgsum(sums._p, cnts._p, scale))
+
+
 def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if_empty: bool = True) -> np.ndarray:
     """returns a 1-element array of the result type (hge as (lo,hi))"""
     out = np.zeros(1, dtype=NP_OF[tp])
@@ -747,6 +757,84 @@ def hash_partition(b: BAT, s: BAT | None, nparts: int, keys_ptr: int | None = No
     if rc != 1:
         _fail("hash_partition")
     return counts
+
+
+_sig("b200_BATpartition", C.c_int, _PP, _PP, _P, _P, C.c_int, C.c_bool, C.c_void_p)
+
+
+def BATpartition(b: BAT, s: BAT | None, nparts: int, keep_nil: bool = False):
+    """(keys, oids, counts): the (key, oid) tuples of b (restricted to s) as `nparts` contiguous send runs"""
+    counts = np.zeros(nparts, dtype=np.uint64)
+    pk, po = _P(), _P()
+    if lib.b200_BATpartition(C.byref(pk), C.byref(po), b._p, _ptr(s), nparts, keep_nil, _vp(counts)) != 1:
+        _fail("BATpartition")
+    return BAT(pk), BAT(po), counts
+
+
+# ------------------------------------------------------------------ multi-GPU: NCCL inside the library (comm.cu)
+_sig("b200_comm_unique_id", C.c_int, C.c_void_p)
+_sig("b200_comm_init", C.c_int, C.c_int, C.c_int, C.c_void_p)
+_sig("b200_comm_rank", C.c_int)
+_sig("b200_comm_world", C.c_int)
+_sig("b200_comm_nccl_version", C.c_int)
+_sig("b200_comm_destroy", None)
+_sig("b200_comm_pack", C.c_int, C.c_int, C.POINTER(_P), C.POINTER(_P), C.c_uint64)
+_sig("b200_comm_exchange", C.c_int, C.c_int, C.POINTER(_P), C.c_void_p, C.POINTER(_P), C.c_void_p)
+
+
+def comm_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    if lib.b200_comm_unique_id(buf) != 0:
+        _fail("comm_unique_id")
+    return buf.raw
+
+
+def comm_init(rank: int, world: int, uid: bytes | None) -> None:
+    if lib.b200_comm_init(rank, world, uid) != 0:
+        _fail("comm_init")
+
+
+def comm_init_torch(dist) -> None:
+    """bootstrap through an initialised torch.distributed group: rank 0's NCCL id is broadcast once"""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [comm_unique_id() if rank == 0 and world > 1 else None]
+    if world > 1:
+        dist.broadcast_object_list(box, src=0)
+    comm_init(rank, world, box[0])
+
+
+def comm_world() -> int:
+    return int(lib.b200_comm_world())
+
+
+def comm_rank() -> int:
+    return int(lib.b200_comm_rank())
+
+
+def comm_destroy() -> None:
+    lib.b200_comm_destroy()
+
+
+def comm_pack(bats, max_rows: int = 256):
+    """mat.pack across the ranks: list of small BATs -> list of their rank-order concatenations"""
+    k = len(bats)
+    inp = (_P * k)(*[b._p for b in bats])
+    out = (_P * k)()
+    if lib.b200_comm_pack(k, inp, out, max_rows) != 1:
+        _fail("comm_pack")
+    return [BAT(out[i]) for i in range(k)]
+
+
+def comm_exchange(bats, send_counts):
+    """all-to-all of parallel columns laid out as world runs -> (received columns, recv_counts)"""
+    k = len(bats)
+    inp = (_P * k)(*[b._p for b in bats])
+    out = (_P * k)()
+    sc = np.ascontiguousarray(send_counts, dtype=np.uint64)
+    rc = np.zeros(len(sc), dtype=np.uint64)
+    if lib.b200_comm_exchange(k, inp, _vp(sc), out, _vp(rc)) != 1:
+        _fail("comm_exchange")
+    return [BAT(out[i]) for i in range(k)], rc
 
 
 # ------------------------------------------------------------------ bench support

@@ -3,23 +3,31 @@
 Rank g of G holds rows [lo_g, hi_g) of every column of a table with ``hseqbase = lo_g``, so the
 candidate lists, extents and min/max oids each rank produces are GLOBAL oids and the
 concatenation of per-rank candidate lists in rank order is the global list.  select / project /
-calc / compare need no exchange.  What does:
+calc / compare need no exchange.  What does follows mergetable's two-phase plans
+(opt_mergetable.c:1204-1215): phase 1 runs the operator chain on the rank's own rows and ends in a
+small partial table; ``pack`` (mat.pack across the ranks: ``b200_comm_pack``, one ncclAllGather
+inside the library) concatenates the ranks' tables in rank order; phase 2 is ordinary GDK calls on
+the packed BATs, identical on every rank:
 
-* scalar aggregates (Q6): one all-reduce of the partial hge, carried as four 32-bit digits in
-  int64 lanes so the sum cannot overflow for any world size <= 2^31;
-* low-cardinality GROUP BY (Q1): mergetable's two-phase plan (opt_mergetable.c:1204-1215) — every
-  rank groups and aggregates its own rows, the <= ngrp-entry partial tables are all-gathered and
-  every rank performs the same deterministic merge.  The global group id of a key is the rank of
-  its smallest first-occurrence oid, which is exactly BATgroup's first-occurrence numbering
-  (gdk_group.c:74-100); averages are recomputed from the merged exact (sum, count) with the
-  reference's formula floor(S/n) + rem/n, then / 10^scale (gdk_aggr.c:1717-1753,1952-1957).
+* scalar aggregates (Q6): per-rank ``BATgroupsum(x, g=NULL)`` (one row), pack, ``BATsum``;
+* low-cardinality GROUP BY (Q1): per-rank keys / first-occurrence oid / partial sums / counts of
+  each local group, pack, ``BATgroup`` on the packed keys — which reproduces BATgroup's
+  first-occurrence numbering (gdk_group.c:74-100) because rank r's rows all precede rank r+1's and
+  every rank's table is in local first-occurrence order — then ``BATgroupsum`` of the partials and
+  the exact average from the merged (sum, count) with BATgroupavg's own closing formula
+  (``BATcalcavgsum``; gdk_aggr.c:1741-1748,1952-1957);
+* the non-broadcast hash join (config 4): ``BATpartition`` by hash(key) mod G, ``comm_exchange``
+  (grouped ncclSend/ncclRecv inside the library), local ``BATjoin``, positions mapped back to the
+  global oids the tuples carry.
 
-``X`` is any module with the GDK API mirror (monetdb_b200.gdk on the GPUs; the CPU tests pass the
-reference driver to exercise this logic under gloo).  ``dist`` is torch.distributed or None.
+``X`` is any module with the GDK API mirror: monetdb_b200.gdk on the GPUs; the CPU tests and the
+reference arm of bench.py pass the reference driver, with a host ``pack`` (gloo all-gather, or the
+in-process concatenation of mitosis slices).  Nothing here computes on column data itself.
 """
 from __future__ import annotations
 
 from . import pipelines
+from .pipelines import T_hge, T_lng
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
@@ -31,173 +39,155 @@ def hge_int(a, i: int = 0) -> int:
     return (int(a["hi"][i]) << 64) | int(a["lo"][i])
 
 
-def hge_digits(v: int) -> list[int]:
-    """signed 128-bit value -> four int64 lanes holding 32-bit digits (top digit signed)"""
-    u = v & ((1 << 128) - 1)
-    d = [(u >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
-    if v < 0:
-        d[3] -= 1 << 32
-    return d
+def device_pack(X, max_rows: int = 256):
+    """pack = b200_comm_pack on the calling rank's library communicator"""
+    return lambda bats: X.comm_pack(bats, max_rows)
 
 
-def hge_from_digits(d) -> int:
-    return sum(int(x) << (32 * i) for i, x in enumerate(d))
+def host_pack(R, gather=None):
+    """pack for the reference driver: `gather(list of numpy arrays) -> list over ranks of such lists`
+    (gloo all_gather_object in the CPU tests); the arrays are concatenated in rank order"""
+    import numpy as np
+
+    def pack(bats):
+        mine = [(b.numpy(), b.props()["type"]) for b in bats]
+        tables = gather(mine) if gather is not None else [mine]
+        out = []
+        for i in range(len(bats)):
+            tt = mine[i][1]
+            arr = np.concatenate([t[i][0] for t in tables])
+            out.append(R.bat(arr, tt if tt != 0 else R.T.oid))
+        return out
+    return pack
 
 
-def allreduce_hge(partial: int, dist=None, device=None) -> int:
-    """global sum of one hge per rank (the Q6 merge)"""
-    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        return partial
-    import torch
-    t = torch.tensor(hge_digits(partial), dtype=torch.int64, device=device)
-    dist.all_reduce(t)
-    return hge_from_digits(t.tolist())
+def pack_tables(R, tables):
+    """mat.pack of per-slice partial tables held in ONE process (the reference arm's mitosis slices)"""
+    import numpy as np
+    out = []
+    for i in range(len(tables[0])):
+        tt = tables[0][i].props()["type"]
+        out.append(R.bat(np.concatenate([t[i].numpy() for t in tables]), tt if tt != 0 else R.T.oid))
+    return out
 
 
-def q6_sharded(X, cols, dist=None, device=None, counts=None) -> int:
-    """config 2 on this rank's rows + the hge all-reduce"""
-    return allreduce_hge(hge_int(pipelines.q6(X, cols, counts)), dist, device)
+# ---------------------------------------------------------------------------- Q6
+def _scalar_bat(X, arr, tt):
+    """mat.pack's view of a scalar aggregate: a one-row BAT.  On the CUDA path the row stays in host memory
+    (BAThostwrap); comm_pack stages it with the record it builds anyway."""
+    return X.BAThostwrap(arr, tt) if hasattr(X, "BAThostwrap") else X.bat(arr, tt)
+
+
+def q6_phase1(X, cols, counts=None):
+    """config 2 on this rank's rows, ending in the one-row partial sum(hge) (nil when nothing qualified)"""
+    return [_scalar_bat(X, pipelines.q6(X, cols, counts), T_hge)]
+
+
+def q6_phase2(X, packed):
+    """BATsum over the ranks' partials -> 1-element hge array"""
+    return X.BATsum(T_hge, packed[0], None, True, True)
+
+
+def q6_sharded(X, cols, pack, counts=None) -> int:
+    return hge_int(q6_phase2(X, pack(q6_phase1(X, cols, counts))))
 
 
 # ---------------------------------------------------------------------------- Q1
 Q1_SUMS = ("sum_qty", "sum_base_price", "sum_disc_price", "sum_charge")
+Q1_PARTIAL = ("rf", "ls", "first", "histo", "sum_qty", "sum_base_price", "sum_disc_price", "sum_charge", "sum_disc",
+              "cnt_qty", "cnt_price", "cnt_disc")
 
 
-def q1_partial(X, cols) -> list[dict]:
-    """phase 1: this rank's partial group table, one dict per local group"""
-    out = {}
-    res = pipelines.q1(X, cols, out)
-    e = res["extents"]
-    if len(e) == 0:
-        return []
-    # key values and GLOBAL first-occurrence oid of each local group
-    rf = X.BATproject(e, out["rf"]).numpy()
-    ls = X.BATproject(e, out["ls"]).numpy()
-    first = X.BATproject(e, out["cand"]).numpy()
-    sum_disc = X.BATgroupsum(out["disc"], out["groups"], e, None, pipelines.T_hge, True).numpy()
-    cnt = res["count_order"].numpy()
-    sums = {k: res[k].numpy() for k in Q1_SUMS}
-    table = []
-    for i in range(len(e)):
-        row = {"rf": int(rf[i]), "ls": int(ls[i]), "first": int(first[i]), "n": int(cnt[i]),
-               "sum_disc": hge_int(sum_disc, i)}
-        for k in Q1_SUMS:
-            row[k] = hge_int(sums[k], i)
-        table.append(row)
+def q1_phase1(X, cols, out=None):
+    """phase 1: this rank's partial group table as len(Q1_PARTIAL) small BATs, one row per local group in
+    local first-occurrence order.  Averages are split into (sum, count of non-nil values) as mergetable
+    does; the three per-rank BATgroupavg passes of the unsharded plan are not needed."""
+    o = {}
+    pipelines.q1_groups_and_calcs(X, cols, o)
+    g, e, h = o["g"], o["e"], o["h"]
+    gsum = lambda b: X.BATgroupsum(b, g, e, None, T_hge, True)
+    gcnt = lambda b: X.BATgroupcount(b, g, e, None, T_lng, True)
+    table = [
+        X.BATproject(e, o["rf"]), X.BATproject(e, o["ls"]), X.BATproject(e, o["cand"]), h,
+        gsum(o["qty"]), gsum(o["price"]), gsum(o["dp"]), gsum(o["ch"]), gsum(o["disc"]),
+        gcnt(o["qty"]), gcnt(o["price"]), gcnt(o["disc"]),
+    ]
+    if out is not None:
+        out.update(nsel=len(o["cand"]))
     return table
 
 
-def exact_avg(total: int, n: int, scale: int) -> float:
-    """BATgroupavg on integers: floor(S/n) + rem/n as dbl, then / 10^scale"""
-    if n == 0:
-        return float("nan")
-    a, rem = divmod(total, n)          # Python floors, rem in [0, n)
-    r = float(a) + float(rem) / float(n)
-    if scale:
-        r /= float(10 ** scale)
-    return r
+def q1_phase2(X, packed) -> dict:
+    """phase 2, identical on every rank: the Q1 result (BATs, BATgroup's group order) from the packed tables"""
+    P = dict(zip(Q1_PARTIAL, packed))
+    g1, e1, h1 = X.BATgroup(P["rf"], None, None, None, None)
+    g, e, h = X.BATgroup(P["ls"], None, g1, e1, h1)
+    tot = lambda name, tp: X.BATgroupsum(P[name], g, e, None, tp, True)
+    res = {k: tot(k, T_hge) for k in Q1_SUMS}
+    n_qty, n_price, n_disc = tot("cnt_qty", T_lng), tot("cnt_price", T_lng), tot("cnt_disc", T_lng)
+    res.update(
+        avg_qty=X.BATcalcavgsum(res["sum_qty"], n_qty, 2),
+        avg_price=X.BATcalcavgsum(res["sum_base_price"], n_price, 2),
+        avg_disc=X.BATcalcavgsum(tot("sum_disc", T_hge), n_disc, 2),
+        count_order=n_qty,
+        extents=X.BATproject(e, P["first"]),
+        histo=tot("histo", T_lng),
+        rf=X.BATproject(e, P["rf"]), ls=X.BATproject(e, P["ls"]),
+    )
+    return res
 
 
-def q1_merge(tables: list[list[dict]]) -> dict:
-    """phase 2: identical on every rank.  Returns the Q1 result in BATgroup's group order."""
-    merged: dict[tuple[int, int], dict] = {}
-    for t in tables:
-        for row in t:
-            k = (row["rf"], row["ls"])
-            m = merged.get(k)
-            if m is None:
-                merged[k] = dict(row)
-                continue
-            m["first"] = min(m["first"], row["first"])
-            m["n"] += row["n"]
-            m["sum_disc"] += row["sum_disc"]
-            for s in Q1_SUMS:
-                m[s] += row[s]
-    groups = sorted(merged.values(), key=lambda r: r["first"])
-    lim = (1 << 127) - 1
-    for g in groups:
-        for s in Q1_SUMS:
-            if abs(g[s]) > lim:
-                raise OverflowError("22003!overflow in sum aggregate.")
-    return {
-        "keys": [(g["rf"], g["ls"]) for g in groups],
-        "extents": [g["first"] for g in groups],
-        "count_order": [g["n"] for g in groups],
-        **{s: [g[s] for g in groups] for s in Q1_SUMS},
-        "avg_qty": [exact_avg(g["sum_qty"], g["n"], 2) for g in groups],
-        "avg_price": [exact_avg(g["sum_base_price"], g["n"], 2) for g in groups],
-        "avg_disc": [exact_avg(g["sum_disc"], g["n"], 2) for g in groups],
-    }
+def q1_sharded(X, cols, pack, out=None) -> dict:
+    """config 3 on this rank's rows, pack, phase 2"""
+    return q1_phase2(X, pack(q1_phase1(X, cols, out)))
 
 
-def q1_sharded(X, cols, dist=None) -> dict:
-    """config 3 on this rank's rows, all-gather of the partial tables, merge"""
-    mine = q1_partial(X, cols)
-    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        return q1_merge([mine])
-    tables = [None] * dist.get_world_size()
-    dist.all_gather_object(tables, mine)
-    return q1_merge(tables)
+def q1_host(res: dict) -> dict:
+    """a Q1 result (sharded or not) as plain Python values, for comparisons"""
+    out = {}
+    for k, v in res.items():
+        a = v.numpy()
+        if a.dtype.names:                         # hge as (lo, hi)
+            out[k] = [hge_int(a, i) for i in range(len(a))]
+        else:
+            out[k] = a.tolist()
+    return out
 
 
 # ---------------------------------------------------------------------------- config 4: repartitioned hash join
-_TORCH_OF = {3: "int8", 4: "int16", 5: "int32", 10: "int64", 6: "int64", 8: "float32", 9: "float64"}
-
-
-def _partition_to_torch(X, col, world, torch, device):
-    """hash-partition one side into `world` contiguous send runs held in torch tensors"""
-    counts = X.hash_partition(col, None, world)
-    total = int(counts.sum())
-    tt = X._storage(col.ttype)
-    keys = torch.empty(max(total, 1), dtype=getattr(torch, _TORCH_OF[tt]), device=device)
-    oids = torch.empty(max(total, 1), dtype=torch.int64, device=device)
-    torch.cuda.current_stream().synchronize()
-    if total:
-        c2 = X.hash_partition(col, None, world, keys.data_ptr(), oids.data_ptr())
-        assert (c2 == counts).all()
-    X.sync()
-    return counts.astype("int64"), keys, oids, tt
-
-
-def join_repartitioned(X, l, r, dist, torch, device, timings=None):
+def join_repartitioned(X, l, r, timings=None):
     """lineitem JOIN orders across the GPUs of one box: every rank hash-partitions its
-    shard of both key columns by hash(key) mod world (b200_hash_partition), one NCCL all-to-all per
-    side moves (key, global oid) tuples to the rank that owns the hash range, and each rank then
-    builds and probes locally (BAThash + BATjoin).  Returns this rank's slice of the result as two
-    aligned device BATs of GLOBAL oids (r1: rows of l, r2: rows of r); the concatenation over ranks is
-    the join, in no particular order (BATjoin promises none, gdk_join.c:56-61)."""
+    shard of both key columns by hash(key) mod world (BATpartition), one grouped NCCL send/recv per side
+    (comm_exchange) moves the (key, global oid) tuples to the rank that owns the hash range, and each rank
+    builds and probes locally (BATjoin).  Returns this rank's slice of the result as two aligned device
+    BATs of GLOBAL oids (r1: rows of l, r2: rows of r); the concatenation over ranks is the join, in no
+    particular order (BATjoin promises none, gdk_join.c:56-61)."""
     import time
-    world = dist.get_world_size()
+    world = X.comm_world()
 
     def mark(name, t0):
         if timings is not None:
-            torch.cuda.synchronize()
+            X.sync()
             timings[name] = (time.perf_counter() - t0) * 1e3      # the latest call
 
     t0 = time.perf_counter()
-    sides = [_partition_to_torch(X, c, world, torch, device) for c in (l, r)]
+    lk, lo, lc = X.BATpartition(l, None, world)
+    rk, ro, rc = X.BATpartition(r, None, world)
     mark("partition_ms", t0)
     t0 = time.perf_counter()
-    recv = []
-    for counts, keys, oids, tt in sides:
-        send_counts = torch.tensor(counts, dtype=torch.int64, device=device)
-        recv_counts = torch.empty_like(send_counts)
-        dist.all_to_all_single(recv_counts, send_counts)
-        rc = recv_counts.tolist()
-        sc = [int(x) for x in counts]
-        nrecv = sum(rc)
-        rk = torch.empty(max(nrecv, 1), dtype=keys.dtype, device=device)
-        ro = torch.empty(max(nrecv, 1), dtype=torch.int64, device=device)
-        dist.all_to_all_single(rk[:nrecv], keys[:sum(sc)], rc, sc)
-        dist.all_to_all_single(ro[:nrecv], oids[:sum(sc)], rc, sc)
-        recv.append((rk, ro, nrecv, tt))
+    (lk2, lo2), _ = X.comm_exchange([lk, lo], lc)
+    (rk2, ro2), _ = X.comm_exchange([rk, ro], rc)
     mark("exchange_ms", t0)
+    if timings is not None:
+        w = X.NP_OF[X._storage(lk.ttype)].itemsize + 8
+        me = X.comm_rank()
+        timings["exchange_bytes_sent"] = int((lc.sum() - lc[me]) * w + (rc.sum() - rc[me]) * w)
     t0 = time.perf_counter()
-    (lk, lo, nl, tt), (rk, ro, nr, _) = recv
-    res = _local_join(X, lk.data_ptr(), lo.data_ptr(), nl, rk.data_ptr(), ro.data_ptr(), nr, tt, keep=(lk, lo, rk, ro))
-    X.sync()
+    r1, r2 = X.BATjoin(lk2, rk2, None, None, False)
+    g1 = X.BATproject(r1, lo2)
+    g2 = X.BATproject(r2, ro2)
     mark("join_ms", t0)
-    return res
+    return g1, g2
 
 
 def _local_join(X, lk_ptr, lo_ptr, nl, rk_ptr, ro_ptr, nr, tt, keep=None):

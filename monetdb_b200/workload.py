@@ -54,32 +54,97 @@ DATES = _date_table()
 C_SHIPDATE, C_DISCOUNT, C_QUANTITY, C_EXTPRICE, C_TAX, C_RETFLAG, C_K, C_V, C_LKEY, C_OKEY = range(10)
 
 
-def lineitem(lo: int, hi: int, cols=("shipdate", "discount", "quantity", "extprice")) -> dict:
-    """rows [lo,hi) of the synthetic lineitem table (configs 2 and 3)"""
+LINEITEM_DTYPES = {"shipdate": np.int32, "discount": np.int64, "quantity": np.int64, "extprice": np.int64,
+                   "tax": np.int64, "returnflag": np.int8, "linestatus": np.int8}
+CUT_LS = todate(1995, 6, 17)
+CUT_BAND = todate(1995, 6, 10)
+
+
+def _nil(z, vals, nils: bool, nil):
+    """the 1 %-nil variant of SURVEY.md §8(d): a value is nil where its own z % 100 == 0"""
+    if nils:
+        vals = vals.copy()
+        vals[z % np.uint64(100) == 0] = nil
+    return vals
+
+
+def lineitem(lo: int, hi: int, cols=("shipdate", "discount", "quantity", "extprice"), nils: bool = False) -> dict:
+    """rows [lo,hi) of the synthetic lineitem table (configs 2 and 3); numpy form = the definition"""
     out = {}
+    I64NIL, I32NIL = np.iinfo(np.int64).min, np.iinfo(np.int32).min
     if "shipdate" in cols or "returnflag" in cols or "linestatus" in cols:
         z = splitmix64(col_seed(C_SHIPDATE), lo, hi)
         day = (z % np.uint64(2526)).astype(np.int64)
         ship = DATES[day]
         if "shipdate" in cols:
-            out["shipdate"] = ship
+            out["shipdate"] = _nil(z, ship, nils, I32NIL)
         if "returnflag" in cols or "linestatus" in cols:
-            ls = (ship > todate(1995, 6, 17)).astype(np.int8)
+            ls = (ship > CUT_LS).astype(np.int8)
             z2 = splitmix64(col_seed(C_RETFLAG), lo, hi)
             # A/F (0,0), R/F (2,0) before the cut; N/O (1,1) after; a thin N/F band (1,0) just before it
-            band = (ship > todate(1995, 6, 10)) & (ls == 0)
+            band = (ship > CUT_BAND) & (ls == 0)
             rf = np.where(ls == 1, 1, np.where(band, 1, np.where(z2 % np.uint64(2) == 1, 0, 2))).astype(np.int8)
             out["returnflag"] = rf
             out["linestatus"] = ls
     if "discount" in cols:
-        out["discount"] = (splitmix64(col_seed(C_DISCOUNT), lo, hi) % np.uint64(11)).astype(np.int64)
+        z = splitmix64(col_seed(C_DISCOUNT), lo, hi)
+        out["discount"] = _nil(z, (z % np.uint64(11)).astype(np.int64), nils, I64NIL)
     if "quantity" in cols:
-        out["quantity"] = ((splitmix64(col_seed(C_QUANTITY), lo, hi) % np.uint64(50) + np.uint64(1)) * np.uint64(100)).astype(np.int64)
+        z = splitmix64(col_seed(C_QUANTITY), lo, hi)
+        out["quantity"] = _nil(z, ((z % np.uint64(50) + np.uint64(1)) * np.uint64(100)).astype(np.int64), nils, I64NIL)
     if "extprice" in cols:
-        out["extprice"] = (splitmix64(col_seed(C_EXTPRICE), lo, hi) % np.uint64(10400001) + np.uint64(90000)).astype(np.int64)
+        z = splitmix64(col_seed(C_EXTPRICE), lo, hi)
+        out["extprice"] = _nil(z, (z % np.uint64(10400001) + np.uint64(90000)).astype(np.int64), nils, I64NIL)
     if "tax" in cols:
-        out["tax"] = (splitmix64(col_seed(C_TAX), lo, hi) % np.uint64(9)).astype(np.int64)
+        z = splitmix64(col_seed(C_TAX), lo, hi)
+        out["tax"] = _nil(z, (z % np.uint64(9)).astype(np.int64), nils, I64NIL)
     return out
+
+
+_WL = None
+
+
+def _wl():
+    """libworkload.so (hostsrc/workload_host.c): the same generator in threaded C"""
+    global _WL
+    if _WL is None:
+        import ctypes as C
+        from pathlib import Path
+        so = Path(__file__).resolve().parent / "libworkload.so"
+        if not so.exists():
+            from .build import build_workload
+            build_workload()
+        lib = C.CDLL(str(so))
+        lib.wl_lineitem.restype = C.c_int
+        lib.wl_lineitem.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int32, C.c_int32] + \
+            [C.c_void_p] * 7
+        _WL = lib
+    return _WL
+
+
+def lineitem_into(lo: int, hi: int, out: dict, nils: bool = False, threads: int | None = None) -> dict:
+    """fill caller-provided arrays (e.g. page-locked staging memory) with rows [lo,hi); `out` maps
+    column name -> numpy array of hi-lo items of LINEITEM_DTYPES[name]"""
+    import os
+    order = ("shipdate", "discount", "quantity", "extprice", "tax", "returnflag", "linestatus")
+    ptrs = []
+    for k in order:
+        a = out.get(k)
+        if a is None:
+            ptrs.append(None)
+            continue
+        assert a.dtype == LINEITEM_DTYPES[k] and len(a) == hi - lo and a.flags.c_contiguous, k
+        ptrs.append(a.ctypes.data)
+    dates = np.ascontiguousarray(DATES, dtype=np.int32)
+    _wl().wl_lineitem(lo, hi, threads or min(64, os.cpu_count() or 1), 1 if nils else 0, dates.ctypes.data, len(dates),
+                      CUT_LS, CUT_BAND, *ptrs)
+    return out
+
+
+def lineitem_fast(lo: int, hi: int, cols=("shipdate", "discount", "quantity", "extprice"), nils: bool = False) -> dict:
+    """lineitem() through the threaded C generator (bit-identical; tests/test_cpu_oracle.py checks it)"""
+    out = {k: np.empty(hi - lo, dtype=LINEITEM_DTYPES[k]) for k in cols}
+    return lineitem_into(lo, hi, out, nils)
 
 
 def config1(lo: int, hi: int):

@@ -478,6 +478,26 @@ def BATcalcavg(b, s=None, scale=0):
     return avg.value, n.value
 
 
+def BATcalcavgsum(sums, cnts, scale=0) -> RBAT:
+    """phase 2 of the two-phase average: exact Python integers, then BATgroupavg's closing formula
+    floor(S/n) + (dbl) rem / n, / 10^scale (gdk_aggr.c:1741-1748,1952-1957).  The reference has no single
+    entry point for this (mergetable recombines in MAL); the CUDA path's b200_BATcalcavgsum is checked
+    against this and against one BATgroupavg over all rows."""
+    sa, ca = sums.numpy(), cnts.numpy()
+    out = np.empty(len(ca), dtype=np.float64)
+    for i in range(len(ca)):
+        S = ((int(sa["hi"][i]) << 64) | int(sa["lo"][i])) if sa.dtype.names else int(sa[i])
+        n = int(ca[i])
+        nil_s = S == -(1 << 127) if sa.dtype.names else S == -(1 << 63)
+        if n <= 0 or nil_s:
+            out[i] = np.nan
+            continue
+        a, rem = divmod(S, n)
+        r = float(a) + float(rem) / float(n)
+        out[i] = r / float(10.0 ** scale) if scale else r
+    return bat(out, T.dbl)
+
+
 def BATsum(tp, b, s=None, skip_nils=True, nil_if_empty=True):
     out = np.zeros(1, dtype=NP_OF[tp])
     rc = _bat.BATsum(_vp(out), tp, b.p, _p(s), skip_nils, nil_if_empty)
