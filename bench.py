@@ -1,19 +1,24 @@
 #!/usr/bin/env python
-"""bench.py — BASELINE.json's metric on the B200 GDK path.
+"""bench.py — BASELINE.json's metric ("GDK Q1/Q6 pipeline rows/s and % HBM peak at 1/2/4/8 B200 vs CPU GDK").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--rows TOTAL]
 
-A "step" is one pass of the TPC-H Q6 operator pipeline (config 2 of
-BASELINE.json: 3 selects -> 2 projects -> mul -> sum over a synthetic SF10
-lineitem, 59 986 052 rows) per GPU.  N > 1 (torchrun, one rank per GPU) shards
-lineitem by contiguous row range, SF10 rows per rank (weak scaling), and merges the
-per-rank hge partial sums with one NCCL all-reduce.  `value` = rows processed by
-all ranks / device time (columns resident in HBM); `e2e` = the same pipeline
-through the C-ABI with HOST (pinned) column heaps, so every operator's
-host->device staging and the result read-back are inside the timed region.
-`--impl reference` times the real reference GDK (oracle/_ref, built from
-/root/reference by oracle/Makefile) on the host cores with mitosis-style
-slicing on a bounded sample of the same workload.
+The contract line is BASELINE config 3: the TPC-H Q1 operator pipeline over a synthetic SF100 lineitem
+(600 037 902 rows), STRONG-scaled: N ranks (torchrun, one per GPU) each hold a contiguous 1/N row range of
+every column.  A "step" is one pass of the Q1 plan over the whole table:
+  N = 1   the §8(d) plan (select, 6 projects, 2-level group, 4 calcs, 4 sums, 3 avgs, count);
+  N > 1   mergetable's two-phase form of it (monetdb_b200/shard.py): phase 1 on the rank's rows ends in a
+          <= 4-row partial table, b200_comm_pack (one ncclAllGather inside the library) concatenates the
+          ranks' tables, phase 2 is ordinary GDK calls on the packed BATs.
+`value` = table rows / device time (columns resident in HBM, CUDA events on the library's stream, max over
+ranks).  `config.q6` carries the same measurement for the Q6 plan (config 2's shape) on the same table.
+`e2e` = the Q1 step through the C-ABI with HOST (page-locked) column heaps: every operator stages its inputs
+inside the timed region and the result tables are read back.
+`--impl reference` times the real reference GDK (oracle/_ref, compiled from /root/reference by
+oracle/Makefile) on the host cores with mitosis slicing + mergetable phase 2, on the same table (or, if K
+steps of that would take longer than the time budget, on the longest prefix of it that fits; the line says
+which).  The B200 arm's cpu_baseline leg runs the same reference once and asserts that the GPU results are
+identical (parity_checked).
 """
 from __future__ import annotations
 
@@ -31,9 +36,13 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+N_SF100 = 600_037_902
 N_SF10 = 59_986_052
-CPU_SAMPLE_ROWS = 6_000_000      # ~SF1: bounded sample for the CPU legs
-METRIC = "GDK Q6 pipeline rows/s (TPC-H Q6 shape, SF10 lineitem per GPU)"
+METRIC = "GDK Q1 pipeline rows/s (TPC-H Q1 shape, SF100 synthetic lineitem, strong scaling; Q6 in config.q6)"
+DTYPE = "int32/int64 compare, int64 x int64 -> int128 multiply-add, exact 192-bit sums"
+Q1_COLS = ("shipdate", "discount", "quantity", "extprice", "tax", "returnflag", "linestatus")
+Q6_COLS = ("shipdate", "discount", "quantity", "extprice")
+REF_BUDGET_S = 240.0           # wall budget of the reference arm's K + W steps
 
 
 def measured_hbm_peak():
@@ -44,6 +53,19 @@ def measured_hbm_peak():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def workload_label(total: int) -> str:
+    sf = "SF100" if total == N_SF100 else "SF10" if total == N_SF10 else f"{total} rows"
+    return (f"TPC-H Q1 shape, {sf} synthetic lineitem ({total} rows): select + 6 project + 2-level group + 4 calc + "
+            f"8 aggregates; Q6 shape (3-predicate select + 2 project + calc mul + sum) on the same table in config.q6")
 
 
 class ClockSampler:
@@ -91,56 +113,176 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons)}
 
 
-def hge_int(a) -> int:
-    return (int(a["hi"][0]) << 64) | int(a["lo"][0])
+def hge_int(a, i=0) -> int:
+    return (int(a["hi"][i]) << 64) | int(a["lo"][i])
+
+
+def q1_unsharded_host(X, res, cand) -> dict:
+    """the §8(d) Q1 plan's result as plain values, extents mapped through the candidate list to table oids
+    (the form shard.q1_host gives for the two-phase plan)"""
+    from monetdb_b200 import shard
+    out = {}
+    for k in shard.Q1_SUMS:
+        a = res[k].numpy()
+        out[k] = [hge_int(a, i) for i in range(len(a))]
+    for k in ("avg_qty", "avg_price", "avg_disc", "count_order", "histo"):
+        out[k] = res[k].numpy().tolist()
+    out["extents"] = X.BATproject(res["extents"], cand).numpy().tolist()
+    return out
+
+
+def same_q1(a: dict, b: dict) -> bool:
+    from monetdb_b200 import shard
+    keys = shard.Q1_SUMS + ("count_order", "histo", "extents")
+    if any(a[k] != b[k] for k in keys):
+        return False
+    for k in ("avg_qty", "avg_price", "avg_disc"):
+        if np.array(a[k], dtype=np.float64).tobytes() != np.array(b[k], dtype=np.float64).tobytes():
+            return False
+    return True
 
 
 # ---------------------------------------------------------------------------- reference (CPU) arm
-def reference_q6(rows: int, steps: int, warmup: int, threads: int):
-    """the real reference GDK on host cores, mitosis-style: the sample is cut into
-    min(4*T, rows/100000) contiguous slices (opt_mitosis.c:18-19,204-205) that run the
-    per-slice operator chain in T threads; partial sums are added (mergetable phase 2)."""
+class ReferenceTable:
+    """rows [0, rows) of lineitem as mitosis slices of reference BATs: P = min(4T, rows/100000) contiguous row
+    ranges (opt_mitosis.c:18-19,204-205); the generator writes straight into the GDK heaps"""
+
+    def __init__(self, rows: int, threads: int, nils: bool = False):
+        from oracle import refgdk as R
+        from monetdb_b200 import shard, workload
+        R.init(threads)
+        # the slices' operator chains are driven from Python threads; the calls into the reference release the
+        # GIL, but with the default 5 ms switch interval the hand-over between 16+ workers dominates short
+        # operators (measured: Q6 157 -> 434 M rows/s on 8 cores)
+        sys.setswitchinterval(1e-4)
+        self.R, self.rows, self.threads = R, rows, threads
+        self.nsl = max(1, min(4 * threads, rows // 100000))
+        T = R.T
+        types = {"shipdate": T.date, "discount": T.lng, "quantity": T.lng, "extprice": T.lng, "tax": T.lng,
+                 "returnflag": T.bte, "linestatus": T.bte}
+        self.slices = []
+        for i in range(self.nsl):
+            lo, hi = shard.shard_range(rows, i, self.nsl)
+            bats, views = {}, {}
+            for k, tt in types.items():
+                nonil = not nils or k in ("returnflag", "linestatus")
+                bats[k], views[k] = R.bat_uninit(tt, hi - lo, lo, nonil=nonil, nil=not nonil)
+            workload.lineitem_into(lo, hi, views, nils, threads)
+            self.slices.append(bats)
+        self._tl = threading.local()
+
+    def _attach(self):
+        if not getattr(self._tl, "ok", False):
+            self.R._h.refh_thread_attach(b"bench")
+            self._tl.ok = True
+
+    def run(self, ex, first: int | None = None):
+        """one pass of Q1 then Q6 over the first `first` slices (default all): per-slice operator chains in
+        the thread pool, mat.pack of the partial tables, phase 2 (mergetable).  -> (q1 dict, q6 int, t_q1, t_q6)"""
+        from monetdb_b200 import shard
+        R = self.R
+        sl = self.slices if first is None else self.slices[:first]
+
+        def p1(cols):
+            self._attach()
+            return shard.q1_phase1(R, cols)
+
+        def p6(cols):
+            self._attach()
+            return shard.q6_phase1(R, cols)
+
+        t0 = time.perf_counter()
+        tables = list(ex.map(p1, sl))
+        q1 = shard.q1_host(shard.q1_phase2(R, shard.pack_tables(R, tables)))
+        t1 = time.perf_counter()
+        del tables
+        sums = list(ex.map(p6, sl))
+        q6 = hge_int(shard.q6_phase2(R, shard.pack_tables(R, sums)))
+        t2 = time.perf_counter()
+        return q1, q6, t1 - t0, t2 - t1
+
+    def rows_of(self, first: int | None) -> int:
+        from monetdb_b200 import shard
+        return self.rows if first is None else shard.shard_range(self.rows, first - 1, self.nsl)[1]
+
+
+def host_mem_ok(table_bytes: int) -> bool:
+    try:
+        import psutil
+        return psutil.virtual_memory().available > 2.2 * table_bytes + (8 << 30)
+    except Exception:
+        return True
+
+
+def table_bytes(rows: int) -> int:
+    return rows * (4 + 4 * 8 + 2)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
     from concurrent.futures import ThreadPoolExecutor
-    from oracle import refgdk as R
-    from monetdb_b200 import pipelines, workload
-    R.init(threads)
-    nsl = max(1, min(4 * threads, rows // 100000))
-    bounds = [rows * i // nsl for i in range(nsl + 1)]
-    slices = []
-    for i in range(nsl):
-        lo, hi = bounds[i], bounds[i + 1]
-        c = workload.lineitem(lo, hi)
-        slices.append({
-            "shipdate": R.bat(c["shipdate"], R.T.date, hseq=lo, nonil=True),
-            "discount": R.bat(c["discount"], R.T.lng, hseq=lo, nonil=True),
-            "quantity": R.bat(c["quantity"], R.T.lng, hseq=lo, nonil=True),
-            "extprice": R.bat(c["extprice"], R.T.lng, hseq=lo, nonil=True),
-        })
-    registered = threading.local()
-
-    def run_slice(col):
-        if not getattr(registered, "ok", False):
-            R._h.refh_thread_attach(b"bench")
-            registered.ok = True
-        return hge_int(pipelines.q6(R, col))
-
-    times, total = [], 0
-    with ThreadPoolExecutor(max_workers=threads) as ex:
-        for it in range(warmup + steps):
-            t0 = time.perf_counter()
-            total = sum(ex.map(run_slice, slices))
-            dt = time.perf_counter() - t0
+    thr = host_threads()
+    total = args.rows
+    rows = total
+    while not host_mem_ok(table_bytes(rows)) and rows > 10_000_000:
+        rows //= 2
+    tab = ReferenceTable(rows, thr)
+    steps, warmup = args.steps, max(args.warmup, 1)
+    first = None
+    t_q1, t_q6 = [], []
+    with ThreadPoolExecutor(max_workers=thr) as ex:
+        q1, q6, a, b = tab.run(ex)                      # warm-up step 1, on everything that was generated
+        est = (a + b) * (steps + warmup - 1)
+        if est > REF_BUDGET_S:
+            first = max(1, int(tab.nsl * REF_BUDGET_S / est))
+        for it in range(1, warmup + steps):
+            q1, q6, a, b = tab.run(ex, first)
             if it >= warmup:
-                times.append(dt)
-    return sum(times), total, nsl
+                t_q1.append(a)
+                t_q6.append(b)
+    used = tab.rows_of(first)
+    v1 = used * steps / sum(t_q1)
+    v6 = used * steps / sum(t_q6)
+    sample = (f"rows [0, {used}) of the {total}-row table ({'the whole table' if used == total else 'bounded prefix'}), "
+              f"{tab.nsl if first is None else first} mitosis slices of {rows // tab.nsl} rows on {thr} threads, "
+              f"per-slice operator chains + mergetable phase 2")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v1, "unit": "rows/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+        "steps": steps, "warmup": warmup, "ms_per_step": sum(t_q1) / steps * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+        "config": {"workload": workload_label(total), "rows": total,
+                   "q6": {"value": v6, "unit": "rows/s", "ms_per_step": sum(t_q6) / steps * 1e3}},
+        "same_rows": used == total, "rows_per_step": used,
+        "cpu_baseline": {"value": v1, "unit": "rows/s", "cores": thr, "kind": "reference", "sample": sample},
+        "e2e": {"value": v1, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "result": {"q1_sum_charge": [str(x) for x in q1["sum_charge"]], "q1_count_order": q1["count_order"], "q6_hge": str(q6)},
+    }))
 
 
 # ---------------------------------------------------------------------------- B200 arm
+def load_dram_table(workload: str, rows_per_gpu: int):
+    """per-kernel dram__bytes (read + write) per launch from the committed ncu capture of the same plan at the
+    same per-GPU row count (profiles/r2_dram_bytes.json, written by scripts/ncu_dram_table.py); None otherwise"""
+    p = ROOT / "profiles" / "r2_dram_bytes.json"
+    if not p.exists():
+        return None, None
+    try:
+        d = json.loads(p.read_text())
+        for ent in d.get(workload, []):
+            if ent.get("rows_per_gpu") == rows_per_gpu:
+                return ent["kernels"], ent.get("source")
+    except Exception:
+        pass
+    return None, None
+
+
 def b200_arm(args):
     import torch
     import torch.distributed as dist
     from monetdb_b200 import gdk as G
-    from monetdb_b200 import pipelines, workload
+    from monetdb_b200 import pipelines, shard, workload
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -151,39 +293,50 @@ def b200_arm(args):
     G.init(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n = args.rows
-    lo, hi = rank * n, (rank + 1) * n                      # contiguous row range of this rank (weak scaling)
-    host = workload.lineitem(lo, hi)
-    types = {"shipdate": G.TYPE.date, "discount": G.TYPE.lng, "quantity": G.TYPE.lng, "extprice": G.TYPE.lng}
-    # pinned host copies (e2e leg) and device-resident BATs (device heap tier)
-    pinned = {}
-    for k, a in host.items():
-        p = G.pinned_empty(len(a), a.dtype)
-        p[:] = a
-        pinned[k] = p
-    dev = {k: G.BATfromhost(pinned[k], types[k], hseq=lo, nonil=True) for k in types}
-    hostbats = {k: G.BAThostwrap(pinned[k], types[k], hseq=lo, nonil=True) for k in types}
-    stream = torch.cuda.ExternalStream(G.lib.b200_stream())
-    red = torch.zeros(4, dtype=torch.int64, device="cuda")
-    red_in = torch.zeros(4, dtype=torch.int64).pin_memory()
-    red_out = torch.zeros(4, dtype=torch.int64).pin_memory()
-    red_in_np, red_out_np = red_in.numpy(), red_out.numpy()
+        G.comm_init_torch(dist)
+    else:
+        G.comm_init(0, 1, None)
+    total = args.rows
+    lo, hi = shard.shard_range(total, rank, world)           # contiguous row range of this rank (strong scaling)
+    n = hi - lo
+    T = G.TYPE
+    types = {"shipdate": T.date, "discount": T.lng, "quantity": T.lng, "extprice": T.lng, "tax": T.lng,
+             "returnflag": T.bte, "linestatus": T.bte}
+    thr = max(1, host_threads() // world)
+    t_setup = time.perf_counter()
+    pinned = {k: G.pinned_empty(n, workload.LINEITEM_DTYPES[k]) for k in types}
+    workload.lineitem_into(lo, hi, pinned, False, thr)
 
-    def merge(partial: int) -> int:
-        """global hge sum: all-reduce of the four 32-bit digits of each rank's partial (pinned staging
-        buffers, one synchronisation per step)"""
+    def upload(nils=False):
+        nonil = lambda k: not nils or k in ("returnflag", "linestatus")
+        dev = {k: G.BATfromhost(pinned[k], types[k], hseq=lo, nonil=nonil(k), nil=not nonil(k)) for k in types}
+        hostb = {k: G.BAThostwrap(pinned[k], types[k], hseq=lo, nonil=nonil(k), nil=not nonil(k)) for k in types}
+        return dev, hostb
+
+    dev, hostbats = upload()
+    setup_s = time.perf_counter() - t_setup
+    stream = torch.cuda.ExternalStream(G.lib.b200_stream())
+    pack = shard.device_pack(G)
+    info = {}
+
+    def q1_step(cols):
         if world == 1:
-            return partial
-        u = partial & ((1 << 128) - 1)
-        for i in range(4):
-            red_in_np[i] = (u >> (32 * i)) & 0xFFFFFFFF
-        if partial < 0:
-            red_in_np[3] -= 1 << 32
-        red.copy_(red_in, non_blocking=True)
-        dist.all_reduce(red)
-        red_out.copy_(red, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return sum(int(v) << (32 * i) for i, v in enumerate(red_out_np))
+            out = {}
+            res = pipelines.q1(G, cols, out)
+            info["nsel"] = out["nsel"]
+            info["cand"] = out["cand"]
+            return res
+        out = {}
+        res = shard.q1_sharded(G, cols, pack, out)
+        info["nsel"] = out["nsel"]
+        return res
+
+    counts = {}
+
+    def q6_step(cols):
+        if world == 1:
+            return hge_int(pipelines.q6(G, cols, counts))
+        return shard.q6_sharded(G, cols, pack, counts)
 
     def barrier():
         G.sync()
@@ -192,14 +345,11 @@ def b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    counts = {}
-
-    def step(cols):
-        G.stage_cache_clear()       # e2e leg: every step uploads each host column again (once per step)
-        return merge(hge_int(pipelines.q6(G, cols, counts)))      # merge == shard.allreduce_hge with a reused buffer
-
-    def timed(cols, steps, warmup, sample_clocks=False):
+    def timed(step, cols, steps, warmup, sample_clocks=False, e2e=False):
+        res = None
         for _ in range(warmup):
+            if e2e:
+                G.stage_cache_clear()
             res = step(cols)
         barrier()
         G.timing_read()          # drop the warm-up launches from the per-kernel event log
@@ -209,96 +359,197 @@ def b200_arm(args):
         l0 = G.kernel_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        t0 = time.perf_counter()
         for _ in range(steps):
+            if e2e:
+                G.stage_cache_clear()       # e2e leg: every step uploads each host column again (once per step)
             res = step(cols)
         e1.record(stream)
         barrier()
-        wall = time.perf_counter() - t0
         ms = e0.elapsed_time(e1)
         clocks = cs.stop() if cs else None
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, wall, res, G.kernel_launches() - l0, clocks
+        return ms, res, G.kernel_launches() - l0, clocks
 
-    # ---- device-resident leg (value); per-kernel CUDA events on the launching stream are
-    # recorded over the same timed region (the warm-up records are discarded inside timed())
-    ms, wall, res, launches, clocks = timed(dev, args.steps, args.warmup, sample_clocks=not args.device_only)
+    def ktable(step, cols, steps):
+        """a second pass over the same region with the per-kernel CUDA events switched on (the events cost
+        host time, so they stay out of the pass `value` comes from)"""
+        G.timing_enable(True)
+        timed(step, cols, steps, 1)
+        kt = G.timing_read()
+        G.timing_enable(False)
+        return {k: {"launches_per_step": v[0] / steps, "ms_per_launch": v[1] / max(1, v[0]),
+                    "ms_per_step": v[1] / steps, "algorithmic_bytes_per_launch": v[2] // max(1, v[0])} for k, v in kt.items()}
+
+    # ---- Q1: device-resident leg (value)
+    ms1, res1, launches1, clocks = timed(q1_step, dev, args.steps, args.warmup, sample_clocks=True)
     if args.device_only:
-        # profiling aid (ncu launch lists): only the device-resident steps run, so every launch the
-        # profiler sees belongs to the timed region's plan; the line printed is not a bench value
         if rank == 0:
-            print(json.dumps({"device_only": True, "ms_per_step": ms / args.steps, "gpu_launches": launches}))
+            print(json.dumps({"device_only": True, "q1_ms_per_step": ms1 / args.steps, "gpu_launches": launches1}))
         return
-    # a second pass over the same region with the per-kernel CUDA events switched on (the events
-    # cost host time, so they stay out of the pass `value` comes from)
-    G.timing_enable(True)
-    timed(dev, args.steps, 1)
-    ktimes = G.timing_read()
-    G.timing_enable(False)
-    # ---- e2e leg: host heaps through the C-ABI
-    e2e_steps = max(1, min(args.steps, 5))
-    G.stage_cache(True)             # a host column used by two operators of the plan (l_discount) is staged once per step
-    ms_e, wall_e, res_e, _, _ = timed(hostbats, e2e_steps, 1)
-    assert res_e == res, "e2e and device-resident results differ"
+    if world == 1:
+        q1_res = q1_unsharded_host(G, res1, info["cand"])
+    else:
+        q1_res = shard.q1_host(res1)
+    nsel_local = info["nsel"]
+    k1 = ktable(q1_step, dev, min(args.steps, 3))
+    # ---- Q6 on the same table
+    ms6, res6, launches6, _ = timed(q6_step, dev, args.steps, args.warmup)
+    k6 = ktable(q6_step, dev, min(args.steps, 5))
+    nsel6 = dict(counts)
+    info.clear()
+    # ---- e2e leg: host heaps through the C-ABI (Q1; then Q6)
+    for b in dev.values():
+        b.free()
+    e2e_steps = max(1, min(args.steps, 3))
+    G.stage_cache(True)             # a host column used by several operators of the plan is staged once per step
+    ms1e, res1e, _, _ = timed(q1_step, hostbats, e2e_steps, 1, e2e=True)
+    q1_res_e = q1_unsharded_host(G, res1e, info["cand"]) if world == 1 else shard.q1_host(res1e)
+    assert same_q1(q1_res_e, q1_res), "e2e and device-resident Q1 results differ"
+    info.clear()
+    ms6e, res6e, _, _ = timed(q6_step, hostbats, e2e_steps, 1, e2e=True)
+    assert res6e == res6, "e2e and device-resident Q6 results differ"
+    G.stage_cache_clear()
+    G.stage_cache(False)
+
+    # ---- totals over ranks
+    if world > 1:
+        t = torch.tensor([nsel_local, nsel6["n1"], nsel6["n2"], nsel6["n3"]], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        nsel_tot, n1, n2, n3 = (int(x) for x in t.tolist())
+    else:
+        nsel_tot, n1, n2, n3 = nsel_local, nsel6["n1"], nsel6["n2"], nsel6["n3"]
+
+    # ---- the 1 %-nil second run (SURVEY.md §8d): same plans, every value column nil where z % 100 == 0
+    nil_run = None
+    if not args.no_nil_run:
+        workload.lineitem_into(lo, hi, pinned, True, thr)
+        devn, _ = upload(nils=True)
+        nsteps = max(1, min(args.steps, 5))
+        msn1, resn1, _, _ = timed(q1_step, devn, nsteps, 1)
+        qn1 = q1_unsharded_host(G, resn1, info["cand"]) if world == 1 else shard.q1_host(resn1)
+        msn6, resn6, _, _ = timed(q6_step, devn, nsteps, 1)
+        nil_run = {"q1_ms_per_step": msn1 / nsteps, "q6_ms_per_step": msn6 / nsteps, "steps": nsteps,
+                   "q1_rows_per_s": total * nsteps / (msn1 * 1e-3), "q6_rows_per_s": total * nsteps / (msn6 * 1e-3)}
+        for b in devn.values():
+            b.free()
+        info.clear()
 
     if rank != 0:
+        if world > 1:
+            dist.barrier()
+            G.comm_destroy()
+            dist.destroy_process_group()
         return
-    nsel = dict(counts)
-    by = pipelines.q6_bytes(n, nsel["n1"], nsel["n2"], nsel["n3"])
+
     peak, peak_src = measured_hbm_peak()
-    # dominant operator: BATselect on l_shipdate (dense candidates) = mask scan + offset scan + expand;
-    # its first kernel (select_dense) is the dominant kernel of the step
-    nl, kms, _ = ktimes.get("select_dense", (0, 0.0, 0))
-    per_launch_ms = kms / nl if nl else None
-    mask_bytes = 4 * n + n // 8                         # column read once + one mask bit per row written
-    achieved = mask_bytes / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms else None
-    total_rows = n * world
-    value = total_rows * args.steps / (ms * 1e-3)
-    # e2e host->device bytes per step: l_shipdate and l_discount are staged whole (dense scan / 14 % candidate
-    # density); l_quantity and l_extprice are only touched through short candidate lists (3.9 % / 1.8 % of the
-    # rows) and are read in place from the pinned host heap, 8 useful bytes per touched row
-    h2d = 4 * n + 8 * n + 8 * nsel["n2"] + 8 * nsel["n3"]
+    by1 = pipelines.q1_bytes(total, nsel_tot) if world == 1 else pipelines.q1_bytes_sharded(total, nsel_tot)
+    by6 = sum(pipelines.q6_bytes(total, n1, n2, n3).values())
+    value = total * args.steps / (ms1 * 1e-3)
+    # dominant kernel of the Q1 step = the timed kernel with the largest share of the step (per-kernel CUDA events)
+    dom = max(k1.items(), key=lambda kv: kv[1]["ms_per_step"]) if k1 else (None, None)
+    dram1, dram_src = load_dram_table("q1", n)
+    dram6, _ = load_dram_table("q6", n)
+    roof = {"bound": "hbm", "kernel": None, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,
+            "peak_source": peak_src}
+    if dom[0]:
+        name, d = dom
+        ach = d["algorithmic_bytes_per_launch"] / (d["ms_per_launch"] * 1e-3) / 1e9
+        roof.update(kernel=name, achieved=ach, frac=ach / peak, launch_ms=d["ms_per_launch"],
+                    algorithmic_bytes_per_launch=d["algorithmic_bytes_per_launch"],
+                    share_of_step=d["ms_per_step"] / (ms1 / args.steps),
+                    traffic=(dram1 or {}).get(name), traffic_source=dram_src if dram1 and name in dram1 else None,
+                    note="kernel = the timed kernel with the largest share of the Q1 step; achieved = the operator's "
+                         "API-faithful algorithmic bytes (SURVEY.md §8d) / launch time; traffic = ncu dram bytes of the "
+                         "same launch where a capture at this row count is committed")
+    pipe_gbs = by1 * args.steps / (ms1 * 1e-3) / 1e9
+    dram_step = sum(v * k1[k]["launches_per_step"] for k, v in (dram1 or {}).items() if k in k1) if dram1 else None
     line = {
         "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int32/int64 compare, int64 x int64 -> int128 multiply-add", "data": "synthetic",
-        "config": {"workload": "TPC-H Q6 shape, SF10 synthetic lineitem (59986052 rows per GPU): 3-predicate select + "
-                               "2 project + calc mul + sum(hge)", "rows_per_gpu": n,
-                   "selected": nsel, "l2": "inputs (1.7 GB) larger than L2; no flush needed",
-                   "pipeline_algorithmic_bytes": sum(by.values()),
-                   "pipeline_gbs": sum(by.values()) * world * args.steps / (ms * 1e-3) / 1e9,
-                   "kernel_ms": {k: round(v[1] / max(1, v[0]), 4) for k, v in ktimes.items()},
-                   "kernel_launch_counts": {k: v[0] for k, v in ktimes.items()}},
-        "gpu_launches": int(launches),
-        "result_hge": str(res),
+        "ms_per_step": ms1 / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": DTYPE, "data": "synthetic",
+        "config": {
+            "workload": workload_label(total), "rows": total, "rows_per_gpu": n,
+            "plan": "SURVEY §8(d) config 3 plan" if world == 1 else
+                    "two-phase (mergetable): phase 1 per rank, b200_comm_pack (one ncclAllGather), phase 2 on the packed BATs",
+            "selected": nsel_tot, "l2": f"inputs ({table_bytes(n) / 1e9:.1f} GB per GPU) larger than L2; no flush needed",
+            "pipeline_algorithmic_bytes": by1, "pipeline_gbs": pipe_gbs,
+            "pipeline_frac_of_hbm_peak_algorithmic": pipe_gbs / (peak * world),
+            "pipeline_dram_bytes_per_gpu": dram_step,
+            "pipeline_frac_of_hbm_peak_dram": (dram_step / (ms1 / args.steps * 1e-3) / 1e9 / peak) if dram_step else None,
+            "kernels": {k: {kk: (round(vv, 5) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in k1.items()},
+            "timed_kernel_ms_per_step": round(sum(v["ms_per_step"] for v in k1.values()), 4),
+            "setup_s": round(setup_s, 1),
+            "q6": {
+                "value": total * args.steps / (ms6 * 1e-3), "unit": "rows/s", "ms_per_step": ms6 / args.steps,
+                "selected": {"n1": n1, "n2": n2, "n3": n3}, "pipeline_algorithmic_bytes": by6,
+                "pipeline_gbs": by6 * args.steps / (ms6 * 1e-3) / 1e9,
+                "pipeline_frac_of_hbm_peak_algorithmic": by6 * args.steps / (ms6 * 1e-3) / 1e9 / (peak * world),
+                "gpu_launches": int(launches6), "result_hge": str(res6),
+                "kernels": {k: {kk: (round(vv, 5) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in k6.items()},
+                "dram_bytes_per_launch": dram6,
+                "e2e": {"value": total * e2e_steps / (ms6e * 1e-3), "unit": "rows/s", "ms_per_step": ms6e / e2e_steps},
+            },
+            "nil_run": nil_run,
+        },
+        "gpu_launches": int(launches1),
+        "result": {"sum_charge": [str(x) for x in q1_res["sum_charge"]], "count_order": q1_res["count_order"],
+                   "extents": q1_res["extents"], "avg_disc": q1_res["avg_disc"]},
         "clocks": clocks,
-        "e2e": {"value": total_rows * e2e_steps / (ms_e * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 16 + 7 * 32, "ms_per_step": ms_e / e2e_steps, "steps": e2e_steps},
-        "roofline": {"bound": "hbm", "kernel": "select_dense_kernel<int> (BATselect on l_shipdate)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
-                     "traffic": 245877248, "traffic_source": "ncu --set full, profiles/r1_q6_kernels_v2.md (dram read+write per launch)",
-                     "peak_source": peak_src, "algorithmic_bytes_per_launch": mask_bytes,
-                     "launch_ms": per_launch_ms},
+        "e2e": {"value": total * e2e_steps / (ms1e * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": table_bytes(n) * world,
+                "d2h_bytes_per_step": 8 * 16 * 8 * world, "ms_per_step": ms1e / e2e_steps, "steps": e2e_steps},
+        "roofline": roof,
     }
+    # golden answers of the full SF100 table (written from the reference's own run, tests/golden/)
+    gold = ROOT / "tests" / "golden" / "lineitem_answers.json"
+    if gold.exists():
+        g = json.loads(gold.read_text()).get(str(total))
+        if g:
+            ok = ([str(x) for x in q1_res["sum_charge"]] == g["q1_sum_charge"] and q1_res["count_order"] == g["q1_count_order"]
+                  and str(res6) == g["q6_hge"])
+            assert ok, "results differ from the golden answers of the reference GDK"
+            line["golden_checked"] = True
     if world == 1 and not args.no_cpu:
-        thr = os.cpu_count() or 1
-        rows = min(CPU_SAMPLE_ROWS, n)
-        t, total, nsl = reference_q6(rows, 3, 1, thr)
-        line["cpu_baseline"] = {"value": rows * 3 / t, "unit": "rows/s", "cores": thr, "kind": "reference",
-                                "sample": f"first {rows} rows of the same lineitem, {nsl} mitosis slices, 3 passes"}
+        from concurrent.futures import ThreadPoolExecutor
+        cthr = host_threads()
+        rows = total
+        while not host_mem_ok(table_bytes(rows)) and rows > 10_000_000:
+            rows //= 2
+        tab = ReferenceTable(rows, cthr)
+        with ThreadPoolExecutor(max_workers=cthr) as ex:
+            rq1, rq6, ta, tb = tab.run(ex)
+        if rows == total:
+            gq1, gq6 = q1_res, res6
+        else:
+            # the reference could only hold a prefix of the table: run the GPU plans on the same prefix
+            workload.lineitem_into(lo, hi, pinned, False, thr)
+            sub = {k: G.BATfromhost(pinned[k][:rows], types[k], hseq=0, nonil=True) for k in types}
+            r = q1_step(sub)
+            gq1 = q1_unsharded_host(G, r, info["cand"])
+            gq6 = q6_step(sub)
+        assert same_q1(gq1, rq1), "Q1: the B200 result differs from the reference GDK"
+        assert gq6 == rq6, "Q6: the B200 result differs from the reference GDK"
+        line["parity_checked"] = True
+        line["parity_rows"] = rows
+        line["cpu_baseline"] = {
+            "value": rows / ta, "unit": "rows/s", "cores": cthr, "kind": "reference",
+            "sample": f"rows [0, {rows}) of the same table ({'the whole table' if rows == total else 'prefix: host memory'}), "
+                      f"{tab.nsl} mitosis slices on {cthr} threads, one pass; Q6 on the same rows: {rows / tb:.4g} rows/s",
+            "q6_value": rows / tb}
     print(json.dumps(line))
     if world > 1:
+        dist.barrier()
+        G.comm_destroy()
         dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------------------- other BASELINE configs
 def other_workload(args):
-    """--workload q1 | window | config1 | join: the other BASELINE configs on the B200 path (same
-    timing rules as the Q6 line: warm-up, CUDA events on the library's stream, max over ranks).
-    They are parity-test cases first; these lines record their throughput for profiles/."""
+    """--workload window | config1 | join: the other BASELINE configs on the B200 path (same timing rules as
+    the contract line: warm-up, CUDA events on the library's stream, max over ranks).  They are parity-test
+    cases first; these lines record their throughput for profiles/.  --rows is PER GPU here (weak scaling)."""
     import torch
     import torch.distributed as dist
     from monetdb_b200 import gdk as G
@@ -313,6 +564,9 @@ def other_workload(args):
     G.init(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        G.comm_init_torch(dist)
+    else:
+        G.comm_init(0, 1, None)
     T = G.TYPE
     n = args.rows
     w = args.workload
@@ -328,20 +582,7 @@ def other_workload(args):
                 bufs[k][a - lo:b - lo] = part[k]
         return {k: G.BATfromhost(bufs[k], types[k], hseq=lo, nonil=True) for k in types}
 
-    if w == "q1":
-        types = {"shipdate": T.date, "discount": T.lng, "quantity": T.lng, "extprice": T.lng, "tax": T.lng,
-                 "returnflag": T.bte, "linestatus": T.bte}
-        lo, hi = rank * n, (rank + 1) * n
-        dev = upload(lambda a, b: workload.lineitem(a, b, cols=tuple(types)), types, lo, hi)
-
-        def step():
-            r = shard.q1_sharded(G, dev, dist if world > 1 else None)
-            info["nsel"] = sum(r["count_order"])
-            return r["sum_charge"]
-        metric = "GDK Q1 pipeline rows/s (TPC-H Q1 shape, synthetic lineitem)"
-        bytes_of = lambda: pipelines.q1_bytes(n * world, info["nsel"])
-        label = f"TPC-H Q1 shape: select + 6 project + 2-level group + 4 calc + 8 aggregates, {n} lineitem rows per GPU"
-    elif w == "config1":
+    if w == "config1":
         k, v = workload.config1(0, n)
         dev = {"k": G.BATfromhost(k, T.int, nonil=True), "v": G.BATfromhost(v, T.lng, nonil=True)}
 
@@ -374,14 +615,15 @@ def other_workload(args):
             if world == 1:
                 r1, r2 = G.BATjoin(dev["l"], dev["r"], None, None, False)
             else:
-                r1, r2 = shard.join_repartitioned(G, dev["l"], dev["r"], dist, torch, torch.device("cuda", local), phases)
+                r1, r2 = shard.join_repartitioned(G, dev["l"], dev["r"], phases if args.phases else None)
             info["pairs_rank0"] = len(r1)
             return len(r1)
         metric = "GDK hash join rows/s (lineitem JOIN orders shape, probe rows)"
         # per rank: partition pass 2*(4+8) per tuple of both sides + exchange + build 4+8+8 per build row + probe
         bytes_of = lambda: world * ((4 + 8 + 8) * nr + (4 + 2 * 8 + 16) * nl + (0 if world == 1 else 2 * (4 + 8) * (nl + nr)))
         label = (f"config 4 shape: {nl} int32 probe keys x {nr} unique build keys per GPU (BAThash + BATjoin)"
-                 + ("" if world == 1 else "; hash repartition of both sides + NCCL all-to-all of (key, oid) tuples"))
+                 + ("" if world == 1 else "; hash repartition of both sides + grouped ncclSend/ncclRecv of (key, oid) tuples "
+                                          "inside the library"))
         info["phases_ms_last_step"] = phases
     elif w == "window":
         blk = workload.window_layout()
@@ -460,45 +702,32 @@ def other_workload(args):
                        "kernel_gbs": {k: round(v[2] / (v[1] * 1e-3) / 1e9, 1) for k, v in kt.items() if v[1] > 0}},
             "gpu_launches": int(launches), "result": str(res)[:200]}))
     if world > 1:
+        dist.barrier()
+        G.comm_destroy()
         dist.destroy_process_group()
-
-
-def reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    thr = os.cpu_count() or 1
-    rows = min(CPU_SAMPLE_ROWS, args.rows)
-    t, total, nsl = reference_q6(rows, args.steps, args.warmup, thr)
-    v = rows * args.steps / t
-    sample = f"first {rows} rows of the SF10 lineitem, {nsl} mitosis slices on {thr} threads"
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": "rows/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t / args.steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int32/int64 compare, int64 x int64 -> int128 multiply-add",
-        "data": "synthetic", "config": {"workload": "TPC-H Q6 shape, SF10 synthetic lineitem (bounded sample)", "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "rows/s", "cores": thr, "kind": "reference", "sample": sample},
-        "e2e": {"value": v, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "result_hge": str(total),
-    }))
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rows", type=int, default=N_SF10, help="lineitem rows per GPU (default SF10)")
-    ap.add_argument("--device-only", action="store_true", help="run only the device-resident steps (for ncu launch lists)")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--workload", default="q6", choices=["q6", "q1", "config1", "join", "window"],
-                    help="q6 (default) is the contract line; the others record the remaining BASELINE configs")
+    ap.add_argument("--rows", type=int, default=None,
+                    help="lineitem rows of the WHOLE table (default SF100 = 600037902); per GPU for --workload config1/join/window")
+    ap.add_argument("--device-only", action="store_true", help="run only the device-resident Q1 steps (for ncu launch lists)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    ap.add_argument("--no-nil-run", action="store_true", help="skip the 1 %%-nil second run")
+    ap.add_argument("--phases", action="store_true", help="join: time partition / exchange / join separately (adds syncs)")
+    ap.add_argument("--workload", default="q1", choices=["q1", "config1", "join", "window"],
+                    help="q1 (default) is the contract line (Q1 + Q6 on SF100); the others record the remaining BASELINE configs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    if args.rows is None:
+        args.rows = N_SF100 if args.workload == "q1" else N_SF10
     if args.impl == "reference":
         reference_arm(args)
-    elif args.workload != "q6":
+    elif args.workload != "q1":
         other_workload(args)
     else:
         if args.warmup < 3:

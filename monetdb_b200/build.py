@@ -76,7 +76,8 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     if force or not LIB.exists() or any(o.stat().st_mtime > LIB.stat().st_mtime for o in objs):
         tmp = LIB.with_suffix(".so.tmp")
         cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
-               "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread", "-ldl"]
+               "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread", "-ldl", "-lrt",
+               "-Xlinker", "--no-undefined"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

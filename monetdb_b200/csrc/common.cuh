@@ -128,6 +128,8 @@ void dev_free(void *p);
 // order the calling thread's stream behind the producer stream's tail when the BAT comes from another
 // context of the same device.  Same-thread use needs nothing (stream order).
 void order_after(const b200_bat *b);
+void stage_cache_retire(void);			/* cand.cu: the thread rebinds to another device */
+void stage_cache_forget(const void *host);	/* cand.cu: one host heap was rewritten (b200_BATinvalidate) */
 // Share counts of heaps that have views (BATproject with dense candidates returns a slice view).
 void heap_share(const void *root);
 bool heap_unshare(const void *root);		/* true: the last view of an orphaned heap went away, free it */

@@ -214,7 +214,6 @@ extern "C" int b200_init(int device)
 	if (tl_ctx != nullptr && tl_ctx->device == device)
 		return 0;
 	if (tl_ctx != nullptr) {
-		extern void stage_cache_retire(void);
 		stage_cache_retire();
 		ctx_retire(tl_ctx);
 	}
@@ -530,7 +529,6 @@ extern "C" void b200_BATinvalidate(const b200_bat *b)
 {
 	if (b == nullptr || b->base == nullptr)
 		return;
-	extern void stage_cache_forget(const void *host);
 	if (b->device >= 0) {
 		hash_cache_drop(b->base);
 		shadow_drop(b->base);

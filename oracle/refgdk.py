@@ -273,6 +273,18 @@ def bat(arr: np.ndarray, tt: int, hseq: int = 0, sorted=False, revsorted=False, 
     return RBAT(_h.refh_bat_new(tt, len(arr), hseq, _vp(arr), sorted, revsorted, key, nonil, nil))
 
 
+def bat_uninit(tt: int, n: int, hseq: int = 0, nonil=False, nil=False):
+    """(BAT of n uninitialised items, numpy view of its tail heap): lets a generator write straight into the
+    GDK heap instead of going through a second host copy (bench.py's full-table reference arm)"""
+    _load()
+    b = RBAT(_h.refh_bat_new(tt, n, hseq, None, False, False, False, nonil, nil))
+    dt = NP_OF[tt]
+    _h.refh_tloc.restype = C.c_void_p
+    addr = _h.refh_tloc(b.p)
+    view = np.frombuffer((C.c_char * (n * dt.itemsize)).from_address(addr), dtype=dt, count=n) if n else np.empty(0, dt)
+    return b, view
+
+
 def dense(hseq, tseq, cnt) -> RBAT:
     _load()
     return RBAT(_h.refh_dense(hseq, tseq, cnt))
