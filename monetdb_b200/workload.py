@@ -142,7 +142,7 @@ def lineitem_into(lo: int, hi: int, out: dict, nils: bool = False, threads: int 
 
 
 def lineitem_fast(lo: int, hi: int, cols=("shipdate", "discount", "quantity", "extprice"), nils: bool = False) -> dict:
-    """lineitem() through the threaded C generator (bit-identical; tests/test_cpu_oracle.py checks it)"""
+    """lineitem() through the threaded C generator (bit-identical; tests/test_cpu_shard.py checks it)"""
     out = {k: np.empty(hi - lo, dtype=LINEITEM_DTYPES[k]) for k in cols}
     return lineitem_into(lo, hi, out, nils)
 
