@@ -69,48 +69,73 @@ def workload_label(total: int) -> str:
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled while the timed region runs"""
+    """SM clock and throttle reasons sampled through NVML from a thread WHILE the timed region runs.  (A
+    `nvidia-smi -lms 100` child process was used first; its polling slowed a 25-sync Q1 step from 39 to 66 ms
+    on the B200 box, so the sampler now makes two NVML calls every 50 ms in-process instead.)"""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index: int):
-        self.index = index
-        self.proc = None
-        self.lines = []
+    def __init__(self, index: int, period: float = 0.05):
+        self.index, self.period = index, period
+        self.sm, self.mx, self.reasons = [], None, set()
+        self._stop = threading.Event()
+        self._thr = None
+        self.err = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except Exception:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates all GPUs of the box, CUDA only the visible ones: map through the UUID order
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if vis:
+                ent = vis.split(",")[self.index].strip()
+                if ent.isdigit():
+                    idx = int(ent)
+                else:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(ent.encode() if hasattr(ent, "encode") else ent)
+                    idx = pynvml.nvmlDeviceGetIndex(h)
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nv = pynvml
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as ex:            # noqa: BLE001
+            self.err = repr(ex)
+            return
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+    def _sample(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:                  # noqa: BLE001
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for bit, name in self.REASONS.items():
+            if r & bit:
+                self.reasons.add(name)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._sample()
+            except Exception as ex:        # noqa: BLE001
+                self.err = repr(ex)
+                return
+            self._stop.wait(self.period)
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 6:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons)}
+        if self._thr is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"NVML unavailable: {self.err}"]}
+        try:
+            self._sample()                 # at least one sample inside the region's tail
+        except Exception:                  # noqa: BLE001
+            pass
+        self._stop.set()
+        self._thr.join(1.0)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "how": "NVML, in-process thread, 50 ms"}
 
 
 def hge_int(a, i=0) -> int:
@@ -384,11 +409,14 @@ def b200_arm(args):
                     "ms_per_step": v[1] / steps, "algorithmic_bytes_per_launch": v[2] // max(1, v[0])} for k, v in kt.items()}
 
     # ---- Q1: device-resident leg (value)
-    ms1, res1, launches1, clocks = timed(q1_step, dev, args.steps, args.warmup, sample_clocks=True)
     if args.device_only:
+        # profiling aid (ncu launch lists): only the device-resident steps of one plan run, so every launch the
+        # profiler sees belongs to that plan; the line printed is not a bench value
+        msd, _, ld, _ = timed(q6_step if args.device_only == "q6" else q1_step, dev, args.steps, args.warmup)
         if rank == 0:
-            print(json.dumps({"device_only": True, "q1_ms_per_step": ms1 / args.steps, "gpu_launches": launches1}))
+            print(json.dumps({"device_only": args.device_only, "ms_per_step": msd / args.steps, "gpu_launches": ld}))
         return
+    ms1, res1, launches1, clocks = timed(q1_step, dev, args.steps, args.warmup, sample_clocks=True)
     if world == 1:
         q1_res = q1_unsharded_host(G, res1, info["cand"])
     else:
@@ -715,7 +743,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=None,
                     help="lineitem rows of the WHOLE table (default SF100 = 600037902); per GPU for --workload config1/join/window")
-    ap.add_argument("--device-only", action="store_true", help="run only the device-resident Q1 steps (for ncu launch lists)")
+    ap.add_argument("--device-only", nargs="?", const="q1", default=None, choices=["q1", "q6"],
+                    help="run only the device-resident steps of one plan (for ncu launch lists)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     ap.add_argument("--no-nil-run", action="store_true", help="skip the 1 %%-nil second run")
     ap.add_argument("--phases", action="store_true", help="join: time partition / exchange / join separately (adds syncs)")
@@ -730,7 +759,7 @@ def main():
     elif args.workload != "q1":
         other_workload(args)
     else:
-        if args.warmup < 3:
+        if args.warmup < 3 and not args.device_only:
             args.warmup = 3
         b200_arm(args)
 

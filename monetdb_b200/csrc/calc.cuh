@@ -433,8 +433,7 @@ static bool calc_run(const CalcOperand &o1, const CalcOperand &o2, void *dst, ui
 		calc_gen_kernel<OP, T1, T2, T3><<<grid, 256, 0, c->stream>>>(a);
 	}
 	COUNT_LAUNCH();
-	kt.~KTimer();
-	kt.idx = -1;
+	kt.stop();
 	if (!cuda_ok(cudaGetLastError(), "calc launch") ||
 	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 16, cudaMemcpyDeviceToHost, c->stream), "calc state read") ||
 	    !stream_sync())

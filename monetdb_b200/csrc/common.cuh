@@ -112,8 +112,11 @@ extern std::atomic<unsigned long long> g_launches;
 // around the kernels that dominate an operator; read back with b200_timing_read.
 struct KTimer {
 	int idx = -1;
+	bool stopped = false;
 	KTimer(const char *name, uint64_t bytes);	/* bytes = algorithmic bytes of this launch */
-	~KTimer();
+	~KTimer() { stop(); }
+	void stop();				/* record the end event now (idempotent) */
+	void add_bytes(uint64_t more);		/* bytes only known after the result count was read */
 };
 
 void set_err(const char *fmt, ...);	/* GDKerror analogue */

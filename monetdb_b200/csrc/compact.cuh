@@ -285,10 +285,10 @@ struct CompactResult {
 };
 
 template <typename OidOf>
-static inline void compact_launch_expand(const CompactScratch &s, OidOf of, oid *dst)
+static inline void compact_launch_expand(const CompactScratch &s, OidOf of, oid *dst, KTimer *ktp = nullptr)
 {
 	Ctx *c = ctx();
-	KTimer kt("compact_expand", s.nchunks * (s.chunk / 32) * 4);
+	KTimer own(ktp ? nullptr : "compact_expand", s.nchunks * (s.chunk / 32) * 4);
 	if (s.chunk == CP_CHUNK)
 		compact_expand_kernel<CP_CHUNK / 32, OidOf><<<(unsigned) s.nchunks, CP_CHUNK / 32, 0, c->stream>>>(
 			s.words, s.counts, s.offs, of, dst, c->slot_d->v);
@@ -321,9 +321,12 @@ static bool compact_finish(const CompactScratch &s, OidOf of, oid *dst, CompactR
 {
 	Ctx *c = ctx();
 	compact_launch_scan(s);
-	compact_launch_expand(s, of, dst);
+	KTimer kt("compact_expand", s.nchunks * (s.chunk / 32) * 4);	/* mask words read ... */
+	compact_launch_expand(s, of, dst, &kt);
+	kt.stop();
 	if (!cuda_ok(cudaGetLastError(), "compact launch") || !stream_sync())
 		return false;
+	kt.add_bytes(c->slot_h->v[0] * sizeof(oid));			/* ... + the oids written */
 	res.count = c->slot_h->v[0];
 	res.first = c->slot_h->v[1];
 	res.last = c->slot_h->v[2];

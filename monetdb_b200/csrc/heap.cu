@@ -68,6 +68,13 @@ static Ctx *ctx_create(int device)
 				uint64_t thr = UINT64_MAX;	/* keep freed heaps cached in the pool */
 				cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
 			}
+			/* B200_L2_FETCH = 32 | 64 | 128: cudaLimitMaxL2FetchGranularity (a hint; the sparse gathers of
+			 * the candidate-list selects move one DRAM atom per touched row) */
+			if (const char *e = getenv("B200_L2_FETCH")) {
+				const int g = atoi(e);
+				if (g == 32 || g == 64 || g == 128)
+					cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t) g);
+			}
 			g_pool_ready[device] = true;
 		}
 	}
@@ -686,7 +693,7 @@ static std::atomic<int> g_timing{0};
 
 KTimer::KTimer(const char *name, uint64_t bytes)
 {
-	if (!g_timing.load(std::memory_order_relaxed) || tl_ctx == nullptr || tl_ctx->device < 0)
+	if (name == nullptr || !g_timing.load(std::memory_order_relaxed) || tl_ctx == nullptr || tl_ctx->device < 0)
 		return;
 	if (tl_krecs == nullptr)
 		tl_krecs = new std::vector<KRec>();
@@ -697,10 +704,16 @@ KTimer::KTimer(const char *name, uint64_t bytes)
 	tl_krecs->push_back(r);
 	idx = (int) tl_krecs->size() - 1;
 }
-KTimer::~KTimer()
+void KTimer::stop()
 {
-	if (idx >= 0)
+	if (idx >= 0 && !stopped)
 		cudaEventRecord((*tl_krecs)[idx].b, tl_ctx->stream);
+	stopped = true;
+}
+void KTimer::add_bytes(uint64_t more)
+{
+	if (idx >= 0 && tl_krecs && (size_t) idx < tl_krecs->size())
+		(*tl_krecs)[idx].bytes += more;
 }
 
 extern "C" void b200_timing_enable(int on)
