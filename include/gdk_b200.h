@@ -94,6 +94,11 @@ void *b200_stream(void);			/* cudaStream_t of the calling thread */
 void b200_timing_enable(int on);
 int  b200_timing_read(char *buf, size_t bufsize);
 
+/* freed device heaps are cached by size and reused without a driver call (cf. HEAPcache, gdk_heap.c:60-139);
+ * the cache is bounded by B200_HEAP_CACHE_GB (default 60 % of the device) and emptied on allocation failure */
+void b200_heap_cache_trim(void);		/* give every cached heap back to the driver */
+uint64_t b200_heap_cache_bytes(void);
+
 void *b200_pinned_alloc(size_t bytes);		/* page-locked host staging memory */
 void  b200_pinned_free(void *p);
 

@@ -8,12 +8,20 @@
 #include "scan.cuh"
 #include <mutex>
 #include <vector>
+#include <map>
+#include <iterator>
 #include <stdlib.h>
 
 std::atomic<unsigned long long> g_launches{0};
 static thread_local Ctx *tl_ctx = nullptr;
 static std::mutex g_pool_mu;
 static bool g_pool_ready[64] = {false};
+struct CachedBlock { void *p; uint32_t ctx; };
+static std::mutex g_cache_mu;
+static std::multimap<size_t, CachedBlock> g_cache[64];
+static std::unordered_map<const void *, size_t> g_block_size;	/* live + cached blocks handed out by dev_alloc */
+static size_t g_cached_bytes[64] = {0};
+static size_t g_cache_limit[64] = {0};	/* block cache bound per device (see dev_alloc) */
 static std::mutex g_ctx_mu;
 static std::vector<Ctx *> g_ctxs;		/* every context ever created; index = id - 1 (kept for their events) */
 
@@ -75,6 +83,11 @@ static Ctx *ctx_create(int device)
 				if (g == 32 || g == 64 || g == 128)
 					cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t) g);
 			}
+			size_t fr = 0, tot = 0;
+			cudaMemGetInfo(&fr, &tot);
+			g_cache_limit[device] = tot / 10 * 6;
+			if (const char *e = getenv("B200_HEAP_CACHE_GB"))
+				g_cache_limit[device] = (size_t) atoll(e) << 30;
 			g_pool_ready[device] = true;
 		}
 	}
@@ -105,8 +118,13 @@ static void ctx_retire(Ctx *c)
 		return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
-	if (c->scratch)
+	if (c->scratch) {
+		{
+			std::lock_guard<std::mutex> lk(g_cache_mu);
+			g_block_size.erase(c->scratch);
+		}
 		cudaFree(c->scratch);
+	}
 	c->scratch = nullptr;
 	c->scratch_bytes = 0;
 	if (c->slot_h)
@@ -120,19 +138,25 @@ static void ctx_retire(Ctx *c)
 // Every descriptor is tagged with the context that made it (bat_alloc_desc).  A consumer on another
 // thread records an event at the producer stream's current tail — everything that wrote the BAT was
 // submitted before the BAT was handed over — and orders its own stream behind it.
-void order_after(const b200_bat *b)
+static void order_after_ctx(uint32_t producer)
 {
 	Ctx *c = tl_ctx;
-	if (b == nullptr || b->producer == 0 || c == nullptr || c->device < 0 || b->producer == c->id)
+	if (producer == 0 || c == nullptr || c->device < 0 || producer == c->id)
 		return;
 	std::lock_guard<std::mutex> lk(g_ctx_mu);
-	if (b->producer > g_ctxs.size())
+	if (producer > g_ctxs.size())
 		return;
-	Ctx *p = g_ctxs[b->producer - 1];
+	Ctx *p = g_ctxs[producer - 1];
 	if (p->stream == nullptr || p->device != c->device)
 		return;		/* retired (it synchronised on the way out) or another device */
 	if (cudaEventRecord(c->ev, p->stream) == cudaSuccess)
 		cudaStreamWaitEvent(c->stream, c->ev, 0);
+}
+
+void order_after(const b200_bat *b)
+{
+	if (b != nullptr)
+		order_after_ctx(b->producer);
 }
 
 Ctx *ctx()
@@ -153,15 +177,81 @@ static bool ctx_usable()
 	return true;
 }
 
+// ---------------------------------------------------------------- the device heap tier's block cache
+// cudaMallocAsync keeps freed memory in its pool, but a query plan whose intermediates are multi-GB blocks of
+// several sizes makes the pool map and unmap physical memory again and again (measured on Q1 SF100: 8 ms of a
+// 40 ms step; single BATgroup / BATcalcmul calls stalled 20-30 ms in the allocator).  A plan allocates the same
+// sizes every time it runs, so freed heaps are kept in a size-keyed cache instead and handed out again without
+// a driver call — GDK's own HEAPcache idea (gdk_heap.c:60-139) applied to device heaps.  Reuse is safe in stream
+// order; a block freed by one thread context and reused by another orders the new owner's stream behind the
+// old one's tail first.  The cache is trimmed when it exceeds B200_HEAP_CACHE_GB (default: 60 % of the device)
+// and emptied when an allocation fails.
+
+static size_t round_block(size_t bytes)
+{
+	if (bytes < 512)
+		return 512;
+	if (bytes < ((size_t) 1 << 20))
+		return (bytes + 511) & ~(size_t) 511;
+	return (bytes + ((size_t) 2 << 20) - 1) & ~(((size_t) 2 << 20) - 1);
+}
+
+static void order_after_ctx(uint32_t producer);
+
+// give cached blocks back to the driver until at most `keep` bytes stay cached (caller holds no lock)
+static void cache_trim(int device, size_t keep)
+{
+	std::vector<void *> drop;
+	{
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		auto &m = g_cache[device];
+		while (g_cached_bytes[device] > keep && !m.empty()) {
+			auto it = std::prev(m.end());		/* largest first */
+			g_cached_bytes[device] -= it->first;
+			g_block_size.erase(it->second.p);
+			drop.push_back(it->second.p);
+			m.erase(it);
+		}
+	}
+	if (drop.empty())
+		return;
+	/* blocks may have been used last on any stream of the device: settle everything, then free */
+	cudaDeviceSynchronize();
+	for (void *p : drop)
+		cudaFree(p);
+}
+
 void *dev_alloc(size_t bytes)
 {
 	if (!ctx_usable())
 		return nullptr;
+	Ctx *c = ctx();
+	const size_t size = round_block(bytes ? bytes : 16);
+	{
+		std::unique_lock<std::mutex> lk(g_cache_mu);
+		auto &m = g_cache[c->device];
+		auto it = m.lower_bound(size);
+		if (it != m.end() && it->first <= size + size / 8) {
+			CachedBlock b = it->second;
+			g_cached_bytes[c->device] -= it->first;
+			m.erase(it);
+			lk.unlock();
+			if (b.ctx != c->id)
+				order_after_ctx(b.ctx);
+			return b.p;
+		}
+	}
 	void *p = nullptr;
-	if (bytes == 0)
-		bytes = 16;
-	if (!cuda_ok(cudaMallocAsync(&p, bytes, ctx()->stream), "device heap alloc"))
+	cudaError_t e = cudaMallocAsync(&p, size, c->stream);
+	if (e != cudaSuccess) {
+		cudaGetLastError();
+		cache_trim(c->device, 0);		/* out of memory: the cache gives everything back, then retry */
+		e = cudaMallocAsync(&p, size, c->stream);
+	}
+	if (!cuda_ok(e, "device heap alloc"))
 		return nullptr;
+	std::lock_guard<std::mutex> lk(g_cache_mu);
+	g_block_size[p] = size;
 	return p;
 }
 
@@ -169,10 +259,47 @@ void dev_free(void *p)
 {
 	if (p == nullptr)
 		return;
-	if (tl_ctx && tl_ctx->device >= 0)
-		cudaFreeAsync(p, tl_ctx->stream);
+	Ctx *c = tl_ctx;
+	const bool have_ctx = c && c->device >= 0;
+	size_t size = 0;
+	bool over = false;
+	if (have_ctx) {
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		auto it = g_block_size.find(p);
+		if (it != g_block_size.end()) {
+			size = it->second;
+			g_cache[c->device].insert({size, CachedBlock{p, c->id}});
+			g_cached_bytes[c->device] += size;
+			over = g_cached_bytes[c->device] > g_cache_limit[c->device];
+		}
+	}
+	if (size != 0) {
+		if (over)
+			cache_trim(c->device, g_cache_limit[c->device] / 2);
+		return;
+	}
+	{
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		g_block_size.erase(p);
+	}
+	if (have_ctx)
+		cudaFreeAsync(p, c->stream);
 	else
 		cudaFree(p);		/* a thread without a context (or after ctx_retire): synchronous release */
+}
+
+extern "C" void b200_heap_cache_trim(void)
+{
+	if (tl_ctx && tl_ctx->device >= 0)
+		cache_trim(tl_ctx->device, 0);
+}
+
+extern "C" uint64_t b200_heap_cache_bytes(void)
+{
+	if (tl_ctx == nullptr || tl_ctx->device < 0)
+		return 0;
+	std::lock_guard<std::mutex> lk(g_cache_mu);
+	return g_cached_bytes[tl_ctx->device];
 }
 
 void *scratch_get(size_t bytes)
@@ -182,11 +309,11 @@ void *scratch_get(size_t bytes)
 		return nullptr;
 	if (bytes > c->scratch_bytes) {
 		if (c->scratch)
-			cudaFreeAsync(c->scratch, c->stream);
+			dev_free(c->scratch);
 		size_t nb = bytes < (1u << 20) ? (1u << 20) : bytes * 2;
-		c->scratch = nullptr;
 		c->scratch_bytes = 0;
-		if (!cuda_ok(cudaMallocAsync(&c->scratch, nb, c->stream), "scratch alloc"))
+		c->scratch = dev_alloc(nb);
+		if (c->scratch == nullptr)
 			return nullptr;
 		c->scratch_bytes = nb;
 	}
@@ -500,6 +627,10 @@ static void heap_release(void *p, int device)
 		dev_free(p);
 	} else {
 		/* freed from a thread bound to another device (or to none): synchronous path */
+		{
+			std::lock_guard<std::mutex> lk(g_cache_mu);
+			g_block_size.erase(p);
+		}
 		cudaFree(p);
 	}
 }

@@ -113,6 +113,8 @@ _sig("b200_algorithm", C.c_char_p)
 _sig("b200_kernel_launches", C.c_uint64)
 _sig("b200_sync", None)
 _sig("b200_stream", C.c_void_p)
+_sig("b200_heap_cache_trim", None)
+_sig("b200_heap_cache_bytes", C.c_uint64)
 _sig("b200_pinned_alloc", C.c_void_p, C.c_size_t)
 _sig("b200_pinned_free", None, C.c_void_p)
 _sig("b200_COLnew", _P, C.c_uint64, C.c_int, C.c_uint64)
