@@ -55,13 +55,45 @@ class RefError(RuntimeError):
     pass
 
 
+class _Chain:
+    """attribute lookup through several CDLLs in order"""
+
+    def __init__(self, libs):
+        self._libs = libs
+
+    def __getattr__(self, name):
+        for lib in self._libs:
+            try:
+                f = getattr(lib, name)
+            except AttributeError:
+                continue
+            setattr(self, name, f)
+            return f
+        raise AttributeError(name)
+
+
+def shim_stats():
+    """(device calls, forwarded calls, inputs served by a device twin, inputs staged) of the loaded shim"""
+    out = (C.c_ulong * 4)()
+    _bat.b200shim_stats(out)
+    return tuple(out)
+
+
 def _load(nthreads: int = 0):
     global _bat, _h
     if _h is not None:
         return
     if not available():
         raise RefError(f"reference GDK not built: run `make -C oracle ref` (needs /root/reference); looked in {_DIR}")
-    _bat = C.CDLL(str(LIBBAT), mode=C.RTLD_GLOBAL)
+    shim = os.environ.get("REFGDK_SHIM")
+    if shim:
+        # boundary test (tests/test_gpu_shim.py): integration/_build/libbat_b200shim.so is loaded FIRST and
+        # globally, so the GDK entry points it exports interpose the reference's for the harness (PLT lookups)
+        # and for this driver (names are resolved in the shim first); everything else comes from libbat_ref
+        _shimlib = C.CDLL(shim, mode=C.RTLD_GLOBAL)
+        _bat = _Chain([_shimlib, C.CDLL(str(LIBBAT), mode=C.RTLD_GLOBAL)])
+    else:
+        _bat = C.CDLL(str(LIBBAT), mode=C.RTLD_GLOBAL)
     _h = C.CDLL(str(LIBH), mode=C.RTLD_GLOBAL)
     V, P = C.c_void_p, C.c_void_p
     _h.refh_init.restype = C.c_int
