@@ -637,6 +637,49 @@ gid_count_kernel(const GT *__restrict__ gids, uint64_t n, oid gmin, oid gmax, un
 	}
 }
 
+// one-byte id twin, at most 8 groups (Q1's count(*)): 16 ids per 16-byte load, one SIMD byte compare per
+// group and word; byte-wide loads ran this at 0.74 TB/s (profiles/r2_q1_sf100_launches.md)
+__global__ void __launch_bounds__(256)
+gid8_count_kernel(const unsigned char *__restrict__ gids, uint64_t n, unsigned gmin, unsigned ngrp, u64 *__restrict__ cnts)
+{
+	unsigned c[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+	const uint64_t nvec = n / 16, stride = (uint64_t) gridDim.x * blockDim.x;
+	const uint4 *v = reinterpret_cast<const uint4 *>(gids);
+	constexpr int U = 4;
+	for (uint64_t i0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+		uint4 q[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const uint64_t i = i0 + u * stride;
+			q[u] = i < nvec ? __ldcs(v + i) : make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				const unsigned pat = (gmin + j) * 0x01010101u;
+				c[j] += (__popc(__vcmpeq4(q[u].x, pat)) + __popc(__vcmpeq4(q[u].y, pat)) +
+					 __popc(__vcmpeq4(q[u].z, pat)) + __popc(__vcmpeq4(q[u].w, pat))) >> 3;
+			}
+		}
+	}
+	if (blockIdx.x == 0 && threadIdx.x < n % 16) {
+		const unsigned go = (unsigned) gids[nvec * 16 + threadIdx.x] - gmin;
+#pragma unroll
+		for (int j = 0; j < 8; j++)
+			c[j] += go == (unsigned) j;
+	}
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		unsigned x = c[j];
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1)
+			x += __shfl_down_sync(0xffffffffu, x, o);
+		if ((threadIdx.x & 31) == 0 && x && j < (int) ngrp)
+			atomicAdd(&cnts[j], (u64) x);
+	}
+}
+
 extern "C" b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils)
 {
 	b200_clrerr();
@@ -677,13 +720,18 @@ extern "C" b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, co
 		}
 		const unsigned grid = grid_for(a.ci.ncand, 256 * 8, NSM * 8);
 		Shadow gsh;
-		if (shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh) && (size_t) ngrp * 8 <= 48 * 1024)
+		KTimer kt("gid_count", a.ci.ncand * 8);		/* algorithmic: the API's 8-byte ids */
+		if (shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh) && ngrp <= 8 && a.min + 8 <= 255 && ((uintptr_t) gsh.p & 15) == 0)
+			gid8_count_kernel<<<grid_for(a.ci.ncand / 16 + 1, 256 * 4, NSM * 8), 256, 0, c->stream>>>(
+				(const unsigned char *) gsh.p, a.ci.ncand, (unsigned) a.min, ngrp, (u64 *) bn->base);
+		else if (shadow_get(a.g->base, SHADOW_GID8, a.g->count, gsh) && (size_t) ngrp * 8 <= 48 * 1024)
 			gid_count_kernel<true, unsigned char><<<grid, 256, ngrp > 8 ? (size_t) ngrp * 8 : 0, c->stream>>>((const unsigned char *) gsh.p, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
 		else if ((size_t) ngrp * 8 <= 48 * 1024)
 			gid_count_kernel<true><<<grid, 256, ngrp > 8 ? (size_t) ngrp * 8 : 0, c->stream>>>((const oid *) a.g->base, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
 		else
 			gid_count_kernel<false><<<grid, 256, 0, c->stream>>>((const oid *) a.g->base, a.ci.ncand, a.min, a.max, ngrp, (u64 *) bn->base);
 		COUNT_LAUNCH();
+		kt.stop();
 		ctx()->algo = "count: cuda gid histogram";
 		if (!cuda_ok(cudaGetLastError(), "count launch")) {
 			b200_BATfree(bn);

@@ -470,6 +470,282 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		atomicOr(&state[0], (unsigned long long) err);
 }
 
+// ---------------------------------------------------------------- temporal RANGE frames
+// gdk_analytic_bounds.c:458-611: the order column is a date / daytime / timestamp, the bound an interval in
+// months (int) or milliseconds (lng).  Per row vmin = SUB(v, limit), vmax = ADD(v, limit) with the calendar
+// arithmetic of gdk_time.c (a nil from an out-of-range result switches that side of the test off), then the
+// frame extends from k while vmin <= b[j] <= vmax.  The calendar functions are restated from gdk_time.c:
+// date = ((year + 4712) * 12 + month - 1) << 5 | day (:17-31), timestamp = date << 37 | usec of day (:42-50).
+namespace mtime {
+constexpr int YEAR_MIN = -4712, YEAR_OFFSET = 4712, MONTH_WIDTH = 21, DAY_WIDTH = 5;
+constexpr int YEAR_MAX = YEAR_MIN + (1 << MONTH_WIDTH) / 12 - 1;
+constexpr lng DAY_USEC = 24LL * 60 * 60 * 1000000;
+__device__ __forceinline__ bool leap(int y) { return y % 4 == 0 && (y % 100 != 0 || y % 400 == 0); }
+__device__ __forceinline__ int monthdays(int y, int m)
+{
+	const int l = (m == 2) ? 29 : ((m == 4 || m == 6 || m == 9 || m == 11) ? 30 : 31);
+	return l - (m == 2 && !leap(y));
+}
+__device__ __forceinline__ int d_day(int dt) { return (int) ((unsigned) dt & 31u); }
+__device__ __forceinline__ int d_month(int dt) { return (int) ((((unsigned) dt >> DAY_WIDTH) & ((1u << MONTH_WIDTH) - 1)) % 12 + 1); }
+__device__ __forceinline__ int d_year(int dt) { return (int) ((((unsigned) dt >> DAY_WIDTH) & ((1u << MONTH_WIDTH) - 1)) / 12) - YEAR_OFFSET; }
+__device__ __forceinline__ int mkdate(int y, int m, int d) { return (int) (((unsigned) ((y + YEAR_OFFSET) * 12 + m - 1) << DAY_WIDTH) | (unsigned) d); }
+
+// date_add_month, gdk_time.c:155-183
+__device__ inline int date_add_month(int dt, int months)
+{
+	if (Atom<int>::is_nil(dt) || Atom<int>::is_nil(months))
+		return Atom<int>::nil();
+	if ((months < 0 ? -(long long) months : (long long) months) >= (1LL << MONTH_WIDTH))
+		return Atom<int>::nil();
+	int y = d_year(dt), m = d_month(dt), d = d_day(dt);
+	m += months;
+	if (m <= 0) {
+		y -= (12 - m) / 12;
+		if (y < YEAR_MIN)
+			return Atom<int>::nil();
+		m = 12 - (-m % 12);
+	} else if (m > 12) {
+		y += (m - 1) / 12;
+		if (y > YEAR_MAX)
+			return Atom<int>::nil();
+		m = (m - 1) % 12 + 1;
+	}
+	const int md = monthdays(y, m);
+	if (d > md)
+		d = md;
+	return mkdate(y, m, d);
+}
+
+// days since 0000-03-01 of the proleptic Gregorian calendar and back (the closed forms of the month-by-month
+// walk in date_add_day, gdk_time.c:122-153: same calendar, same results, O(1) instead of O(months))
+__device__ inline long long days_from_civil(int y, int m, int d)
+{
+	y -= m <= 2;
+	const long long era = (y >= 0 ? y : y - 399) / 400;
+	const unsigned yoe = (unsigned) (y - era * 400);
+	const unsigned doy = (153u * (unsigned) (m + (m > 2 ? -3 : 9)) + 2) / 5 + (unsigned) d - 1;
+	const unsigned doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+	return era * 146097 + (long long) doe;
+}
+__device__ inline void civil_from_days(long long z, long long &y, int &m, int &d)
+{
+	const long long era = (z >= 0 ? z : z - 146096) / 146097;
+	const unsigned doe = (unsigned) (z - era * 146097);
+	const unsigned yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+	y = (long long) yoe + era * 400;
+	const unsigned doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+	const unsigned mp = (5 * doy + 2) / 153;
+	d = (int) (doy - (153 * mp + 2) / 5 + 1);
+	m = (int) (mp < 10 ? mp + 3 : mp - 9);
+	y += m <= 2;
+}
+__device__ inline int date_add_day(int dt, int days)
+{
+	if (Atom<int>::is_nil(dt) || Atom<int>::is_nil(days))
+		return Atom<int>::nil();
+	if ((days < 0 ? -(long long) days : (long long) days) >= (1LL << (DAY_WIDTH + MONTH_WIDTH)))
+		return Atom<int>::nil();
+	long long y;
+	int m, d;
+	civil_from_days(days_from_civil(d_year(dt), d_month(dt), d_day(dt)) + days, y, m, d);
+	if (y < YEAR_MIN || y > YEAR_MAX)
+		return Atom<int>::nil();
+	return mkdate((int) y, m, d);
+}
+__device__ __forceinline__ lng ts_time(lng ts) { return (lng) ((unsigned long long) ts & ((1ULL << 37) - 1)); }
+__device__ __forceinline__ int ts_date(lng ts) { return (int) (((unsigned long long) ts >> 37) & ((1u << (DAY_WIDTH + MONTH_WIDTH)) - 1)); }
+__device__ __forceinline__ lng mktimestamp(int d, lng t) { return (lng) (((unsigned long long) (unsigned) d << 37) | (unsigned long long) t); }
+// timestamp_add_usec, gdk_time.c:436-457
+__device__ inline lng timestamp_add_usec(lng t, lng usec)
+{
+	if (Atom<lng>::is_nil(t) || Atom<lng>::is_nil(usec))
+		return Atom<lng>::nil();
+	lng tm = ts_time(t);
+	int dt = ts_date(t);
+	tm = (lng) ((unsigned long long) tm + (unsigned long long) usec);
+	if (tm < 0) {
+		const int add = (int) ((DAY_USEC - 1 - tm) / DAY_USEC);
+		tm += add * DAY_USEC;
+		dt = date_add_day(dt, -add);
+	} else if (tm >= DAY_USEC) {
+		dt = date_add_day(dt, (int) (tm / DAY_USEC));
+		tm %= DAY_USEC;
+	}
+	if (Atom<int>::is_nil(dt))
+		return Atom<lng>::nil();
+	return mktimestamp(dt, tm);
+}
+__device__ inline lng timestamp_add_month(lng t, int m)
+{
+	if (Atom<lng>::is_nil(t) || Atom<int>::is_nil(m))
+		return Atom<lng>::nil();
+	const int dt = date_add_month(ts_date(t), m);
+	if (Atom<int>::is_nil(dt))
+		return Atom<lng>::nil();
+	return mktimestamp(dt, ts_time(t));
+}
+__device__ inline lng daytime_add_usec(lng t, lng usec)
+{
+	if (Atom<lng>::is_nil(t) || Atom<lng>::is_nil(usec))
+		return Atom<lng>::nil();
+	if ((usec < 0 ? -usec : usec) >= DAY_USEC)
+		return Atom<lng>::nil();
+	t += usec;
+	if (t < 0 || t >= DAY_USEC)
+		return Atom<lng>::nil();
+	return t;
+}
+enum { DATE_MONTH, TS_MONTH, DATE_MSEC, DAYTIME_MSEC, TS_MSEC };
+// SUB / ADD of gdk_analytic_bounds.c:455-466 for each (order type, interval unit)
+template <int KIND, typename T, typename DT> __device__ __forceinline__ void minmax(T v, DT lim, T &vmin, T &vmax)
+{
+	if constexpr (KIND == DATE_MONTH) {
+		vmin = date_add_month(v, -(int) lim);
+		vmax = date_add_month(v, (int) lim);
+	} else if constexpr (KIND == TS_MONTH) {
+		vmin = timestamp_add_month(v, -(int) lim);
+		vmax = timestamp_add_month(v, (int) lim);
+	} else if constexpr (KIND == DATE_MSEC) {
+		vmin = date_add_day(v, (int) (-(lng) lim / (24LL * 60 * 60 * 1000)));
+		vmax = date_add_day(v, (int) ((lng) lim / (24LL * 60 * 60 * 1000)));
+	} else if constexpr (KIND == DAYTIME_MSEC) {
+		vmin = daytime_add_usec(v, (lng) ((unsigned long long) -1000LL * (unsigned long long) (lng) lim));
+		vmax = daytime_add_usec(v, (lng) (1000ULL * (unsigned long long) (lng) lim));
+	} else {
+		vmin = timestamp_add_usec(v, (lng) ((unsigned long long) -(lng) lim * 1000ULL));
+		vmax = timestamp_add_usec(v, (lng) ((unsigned long long) (lng) lim * 1000ULL));
+	}
+}
+}	// namespace mtime
+
+template <typename T, typename DT, int KIND, bool SORTED>
+__global__ void __launch_bounds__(AN_THREADS)
+an_range_mtime_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__restrict__ bp, bool nonil,
+		      const DT *__restrict__ lim, DT slim, bool preceding, oid *__restrict__ rb, unsigned long long *__restrict__ state)
+{
+	__shared__ TileSegs ts;
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	unsigned err = 0;
+	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		oid m, e;
+		ts.locate(k, m, e);
+		const DT rl = lim ? lim[k] : slim;
+		if (Atom<DT>::is_nil(rl) || rl < 0) {
+			err |= AN_ERR_BOUND;
+			rb[k] = k;
+			continue;
+		}
+		const T v = bp[k];
+		const bool vnil = !nonil && Atom<T>::is_nil(v);
+		T vmin = 0, vmax = 0;
+		if (!vnil)
+			mtime::minmax<KIND, T, DT>(v, rl, vmin, vmax);
+		const bool usemin = !Atom<T>::is_nil(vmin), usemax = !Atom<T>::is_nil(vmax);
+		/* in(j): row j still belongs to the frame of row k */
+		auto in = [&](oid j) -> bool {
+			const T w = bp[j];
+			if (vnil)
+				return Atom<T>::is_nil(w);
+			if (!nonil && Atom<T>::is_nil(w))
+				return false;
+			return !((usemin && w < vmin) || (usemax && w > vmax));
+		};
+		if constexpr (!SORTED) {
+			oid j;
+			if (preceding) {
+				for (j = k;; j--) {
+					if (!in(j)) {
+						j++;
+						break;
+					}
+					if (j == m)
+						break;
+				}
+			} else {
+				for (j = k + 1; j < e; j++)
+					if (!in(j))
+						break;
+			}
+			rb[k] = j;
+		} else {
+			/* ascending inside the partition: membership is monotone along the walk -> gallop + bisect */
+			oid good = k, bad = 0;
+			bool have_bad = false;
+			if (preceding) {
+				for (oid step = 1;; step <<= 1) {
+					if (good - m < step) {
+						if (good != m) {
+							if (in(m))
+								good = m;
+							else {
+								bad = m;
+								have_bad = true;
+							}
+						}
+						break;
+					}
+					const oid pos = good - step;
+					if (in(pos))
+						good = pos;
+					else {
+						bad = pos;
+						have_bad = true;
+						break;
+					}
+				}
+				if (have_bad)
+					while (good - bad > 1) {
+						const oid mid = bad + (good - bad) / 2;
+						if (in(mid))
+							good = mid;
+						else
+							bad = mid;
+					}
+				rb[k] = good;
+			} else {
+				for (oid step = 1;; step <<= 1) {
+					if (e - 1 - good < step) {
+						if (good != e - 1) {
+							if (in(e - 1))
+								good = e - 1;
+							else {
+								bad = e - 1;
+								have_bad = true;
+							}
+						}
+						break;
+					}
+					const oid pos = good + step;
+					if (in(pos))
+						good = pos;
+					else {
+						bad = pos;
+						have_bad = true;
+						break;
+					}
+				}
+				if (have_bad)
+					while (bad - good > 1) {
+						const oid mid = good + (bad - good) / 2;
+						if (in(mid))
+							good = mid;
+						else
+							bad = mid;
+					}
+				rb[k] = good + 1;
+			}
+		}
+	}
+	if (err)
+		atomicOr(&state[0], (unsigned long long) err);
+}
+
 // ---------------------------------------------------------------- host side
 // peer-run starts: row 0, partition starts and every row whose order value differs
 // from its predecessor (nil == nil), gdk_analytic_bounds.c:654-852
@@ -486,6 +762,20 @@ template <typename T> struct PeerStart {
 static inline unsigned an_tiles(uint64_t n)
 {
 	return (unsigned) ((n + AN_TILE - 1) / AN_TILE);
+}
+
+template <typename T, typename DT, int KIND>
+static void range_mtime_launch(const SegList &sl, uint64_t n, const b200_bat *b, const void *lim, DT slim, bool preceding, bool sorted,
+			       oid *rb, unsigned long long *state)
+{
+	KTimer kt("an_range_mtime", n * (9 + sizeof(T) + (lim ? sizeof(DT) : 0)));
+	if (sorted)
+		an_range_mtime_kernel<T, DT, KIND, true><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(
+			sl.S, sl.cnt, n, (const T *) b->base, b->tnonil != 0, (const DT *) lim, slim, preceding, rb, state);
+	else
+		an_range_mtime_kernel<T, DT, KIND, false><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(
+			sl.S, sl.cnt, n, (const T *) b->base, b->tnonil != 0, (const DT *) lim, slim, preceding, rb, state);
+	COUNT_LAUNCH();
 }
 
 static bool segbound_run(const SegList &sl, uint64_t n, bool preceding, oid *rb)
@@ -647,12 +937,9 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 
 	if (unit == 1) {
 		/* ---- RANGE ---- */
-		if (tp1 == B200_date || tp1 == B200_daytime || tp1 == B200_timestamp) {
-			if (t2 != B200_int && t2 != B200_lng)
-				set_err("42000!range frame bound type %s not supported.\n", atomname(t2));
-			else
-				set_err("windowbounds: temporal RANGE frames (month/second intervals, gdk_analytic_bounds.c:440-611) "
-					"are not on the device path\n");
+		const bool temporal = tp1 == B200_date || tp1 == B200_daytime || tp1 == B200_timestamp;
+		if (temporal && t2 != B200_int && t2 != B200_lng) {
+			set_err("42000!range frame bound type %s not supported.\n", atomname(t2));	/* :1003-1004 */
 			return B200_FAIL;
 		}
 		const int t1 = basetype(tp1);
@@ -700,6 +987,8 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 				return B200_FAIL;
 			}
 		}
+		if (temporal)	/* month intervals: date / timestamp; msec intervals: date / daytime / timestamp (:578-611) */
+			type_ok = t2 == B200_lng || tp1 != B200_daytime;
 		if (!type_ok) {
 			set_err("42000!type %s not supported for %s frame bound type.\n", atomname(tp1), atomname(t2));
 			return B200_FAIL;
@@ -734,7 +1023,27 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 		ctx()->algo = tl_range_sorted ? "windowbounds: range, cuda galloping search (sorted partitions)"
 					      : "windowbounds: range, cuda per-row walk";
 		bool launched = true;
-		if (l != nullptr) {
+		if (temporal) {
+			const void *lim = l ? l->base : nullptr;
+			const bool so = tl_range_sorted;
+			ctx()->algo = so ? "windowbounds: temporal range, cuda galloping search (sorted partitions)"
+					 : "windowbounds: temporal range, cuda per-row walk";
+			if (t2 == B200_int) {
+				const int il = (int) ilim;
+				if (tp1 == B200_date)
+					range_mtime_launch<int, int, mtime::DATE_MONTH>(S, n, b, lim, il, preceding, so, rb, state);
+				else
+					range_mtime_launch<lng, int, mtime::TS_MONTH>(S, n, b, lim, il, preceding, so, rb, state);
+			} else {
+				const lng ll = (lng) ilim;
+				if (tp1 == B200_date)
+					range_mtime_launch<int, lng, mtime::DATE_MSEC>(S, n, b, lim, ll, preceding, so, rb, state);
+				else if (tp1 == B200_daytime)
+					range_mtime_launch<lng, lng, mtime::DAYTIME_MSEC>(S, n, b, lim, ll, preceding, so, rb, state);
+				else
+					range_mtime_launch<lng, lng, mtime::TS_MSEC>(S, n, b, lim, ll, preceding, so, rb, state);
+			}
+		} else if (l != nullptr) {
 			const void *lim = l->base;
 			switch (t1) {
 			case B200_bte: launched = range_dyn<bte>(t2, S, n, b, lim, preceding, rb, state); break;

@@ -24,6 +24,7 @@ KTIMER = OrderedDict([
     ("group_assign", r"grp_byte_assign_kernel|grp_assign_kernel"),
     ("group_first_g", r"grp_byte_first_kernel<.*true|grp_first_kernel<[^,]+, *\(bool\)1|grp_first_kernel<[^,]+, *true"),
     ("group_first", r"grp_byte_first_kernel|grp_first_kernel|grp_direct_first_kernel"),
+    ("gid_count", r"gid_count_kernel|gid8_count_kernel"),
     ("compact_expand", r"compact_expand_kernel"),
     ("compact", r"compact_mask2_kernel|compact_mask_kernel"),
     ("select_dense", r"select_dense32_kernel|select_dense_kernel"),

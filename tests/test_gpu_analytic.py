@@ -394,3 +394,98 @@ def test_avginteger(gdk, ref, tt, frame_type):
         rr = ref.GDKanalyticalfn("avginteger", ref.colnew(tt, n), rp, rop, rb, rs, re_, tt, frame_type)
         close(r.numpy(), rr.numpy(), tt, True)
         assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
+
+
+# ---------------------------------------------------------------------------- temporal RANGE frames (a20)
+def _dates(rng, n, span_days=4000):
+    """packed GDK dates (gdk_time.c:17-31) of random days after 1990-01-01, incl. month ends and leap days"""
+    import datetime as dt
+    base = dt.date(1990, 1, 1)
+    days = np.sort(rng.integers(0, span_days, n))
+    out = np.empty(n, dtype=np.int32)
+    for i, d in enumerate(days):
+        x = base + dt.timedelta(days=int(d))
+        out[i] = (((x.year + 4712) * 12 + x.month - 1) << 5) | x.day
+    return out
+
+
+def _timestamps(rng, n):
+    d = _dates(rng, n).astype(np.int64)
+    usec = rng.integers(0, 86_400_000_000, n).astype(np.int64)
+    ts = (d << 37) | usec
+    return np.sort(ts)
+
+
+@pytest.mark.parametrize("tp1", [T.date, T.timestamp, T.daytime])
+@pytest.mark.parametrize("preceding", [True, False])
+@pytest.mark.parametrize("order", ["sorted", "random"])
+def test_temporal_range_bounds(gdk, ref, tp1, preceding, order):
+    """RANGE frames on date / timestamp / daytime order columns with month (int) and millisecond (lng)
+    interval bounds (gdk_analytic_bounds.c:458-611), static and per-row bounds, with and without nils"""
+    rng = np.random.default_rng(tp1 * 7 + preceding)
+    for n, nparts, nilfrac in ((1, 1, 0.0), (300, 4, 0.0), (20011, 40, 0.0), (20011, 40, 0.15)):
+        pkey = np.sort(rng.integers(0, nparts, n)).astype(np.int32)
+        if tp1 == T.date:
+            o = _dates(rng, n)
+        elif tp1 == T.timestamp:
+            o = _timestamps(rng, n)
+        else:
+            o = np.sort(rng.integers(0, 86_400_000_000, n)).astype(np.int64)
+        # ascending inside every partition (what ORDER BY produces), or shuffled
+        if order == "sorted":
+            for k in range(nparts):
+                m = pkey == k
+                o[m] = np.sort(o[m])
+        else:
+            o = rng.permutation(o)
+        if nilfrac:
+            nil = np.iinfo(o.dtype).min
+            mask = rng.random(n) < nilfrac
+            o = o.copy()
+            o[mask] = nil
+            if order == "sorted":                       # nil sorts first inside a partition
+                for k in range(nparts):
+                    m = pkey == k
+                    o[m] = np.sort(o[m])
+        p, rp = flags(gdk, ref, pkey, T.int)
+        b, rb = both(gdk, ref, o, tp1)
+        cases = []
+        if tp1 != T.daytime:
+            cases += [(1, T.int), (3, T.int), (14, T.int), (0, T.int), (2**31 - 1, T.int), (400000, T.int)]
+        cases += [(86_400_000, T.lng), (3 * 86_400_000 + 5, T.lng), (3_600_000, T.lng), (1, T.lng), (0, T.lng), ((1 << 63) - 1, T.lng),
+                  (10**15, T.lng)]
+        for lim, tp2 in cases:
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, tp1, tp2, 1, preceding, 0)
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, tp1, tp2, 1, preceding, 0)
+            check_oid(r, rr)
+        if n > 1:
+            for tp2, hi in (((T.int, 20),) if tp1 != T.daytime else ()) + ((T.lng, 5 * 86_400_000),):
+                lcol = random_col(rng, tp2, n, lo=0, hi=hi)
+                l, rl = both(gdk, ref, lcol, tp2)
+                r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, l, None, tp1, tp2, 1, preceding, 0)
+                rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, rl, None, tp1, tp2, 1, preceding, 0)
+                check_oid(r, rr)
+            if order == "sorted" and not nilfrac:
+                assert "galloping" in gdk.algorithm()
+
+
+def test_temporal_range_bound_errors(gdk, ref):
+    rng = np.random.default_rng(3)
+    n = 200
+    o = _dates(rng, n)
+    pkey = np.zeros(n, dtype=np.int32)
+    p, rp = flags(gdk, ref, pkey, T.int)
+    b, rb = both(gdk, ref, o, T.date)
+    for lim, tp2 in ((-1, T.int), (-5, T.lng), (3, T.sht), (1.5, T.dbl)):
+        with pytest.raises(G.GDKError) as e1:
+            gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, T.date, tp2, 1, True, 0)
+        with pytest.raises(Exception) as e2:
+            ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, T.date, tp2, 1, True, 0)
+        assert str(e1.value).strip() == str(e2.value).strip(), (lim, tp2)
+    # daytime takes no month interval
+    d, rd = both(gdk, ref, np.sort(rng.integers(0, 86_400_000_000, n)).astype(np.int64), T.daytime)
+    with pytest.raises(G.GDKError) as e1:
+        gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), d, p, None, 2, T.daytime, T.int, 1, True, 0)
+    with pytest.raises(Exception) as e2:
+        ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rd, rp, None, 2, T.daytime, T.int, 1, True, 0)
+    assert str(e1.value).strip() == str(e2.value).strip()
