@@ -149,6 +149,19 @@ template <int OP, typename T1, typename T2, typename T3> struct Calc {
 			} else {
 				/* compute exactly in the next wider type, then range-check against [-max,max] */
 				typedef typename Rank<T3>::wider W;
+				if constexpr (sizeof(W) == 16 && sizeof(T3) == 8 && OP != OP_MUL) {
+					/* lng +- lng -> lng: the 128-bit detour made this kernel issue-bound (78 % SM,
+					 * 60 % DRAM, profiles/r2_q1_75m_full.md); the wrapped 64-bit result and the
+					 * sign rule give the same verdict: overflow iff the operands' signs allow it and
+					 * the result's sign differs, or the result is the nil pattern (-max - 1) */
+					const unsigned long long ua = (unsigned long long) (lng) a, ub = (unsigned long long) (lng) b;
+					const unsigned long long ur = OP == OP_ADD ? ua + ub : ua - ub;
+					const unsigned long long ov = OP == OP_ADD ? ((ua ^ ur) & (ub ^ ur)) : ((ua ^ ub) & (ua ^ ur));
+					if ((long long) ov < 0 || ur == 0x8000000000000000ULL)
+						return ST_OVERFLOW;
+					dst = (T3) (long long) ur;
+					return ST_OK;
+				}
 				W r = OP == OP_ADD ? (W) a + (W) b : OP == OP_SUB ? (W) a - (W) b : (W) a * (W) b;
 				if (r < -(W) max || r > (W) max)
 					return ST_OVERFLOW;

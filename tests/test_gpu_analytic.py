@@ -489,3 +489,62 @@ def test_temporal_range_bound_errors(gdk, ref):
     with pytest.raises(Exception) as e2:
         ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rd, rp, None, 2, T.daytime, T.int, 1, True, 0)
     assert str(e1.value).strip() == str(e2.value).strip()
+
+
+# ---------------------------------------------------------------------------- frame types 1 (RANGE) and 2 (GROUPS)
+def frames_unit(gdk, ref, n, nparts, rng, unit):
+    """partition / peer flags and start / end columns made by RANGE (unit 1) or GROUPS (unit 2) bounds"""
+    pkey, o = window(rng, n, nparts)
+    p, rp = flags(gdk, ref, pkey, T.int)
+    op, rop = flags(gdk, ref, o, T.lng, p, rp)
+    b, rb = both(gdk, ref, o, T.lng)
+    if unit == 1:
+        args, rargs, tp1 = (b, p, None), (rb, rp, None), T.lng
+    else:
+        args, rargs, tp1 = (op, p, None), (rop, rp, None), T.bit
+    s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), *args, 2, tp1, T.lng, unit, True, 0)
+    rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), *rargs, 2, tp1, T.lng, unit, True, 0)
+    e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), *args, 1, tp1, T.lng, unit, False, 0)
+    re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), *rargs, 1, tp1, T.lng, unit, False, 0)
+    check_oid(s, rs)
+    check_oid(e, re_)
+    return (p, op, s, e), (rp, rop, rs, re_)
+
+
+@pytest.mark.parametrize("frame_type", [1, 2])
+@pytest.mark.parametrize("tt", [T.int, T.lng, T.dbl])
+def test_aggregates_on_range_and_groups_frames(gdk, ref, frame_type, tt):
+    """sum / avg / avginteger / count / min / max with frame_type 1 (RANGE) and 2 (GROUPS): the start / end
+    columns come from the corresponding bounds (the reference evaluates them like ROWS frames, through its
+    segment tree: gdk_analytic_func.c:1959, gdk_analytic_statistics.c:364)"""
+    rng = np.random.default_rng(tt * 7 + frame_type)
+    for n, nparts in ((1, 1), (300, 4), (40001, 23)):
+        (p, op, s, e), (rp, rop, rs, re_) = frames_unit(gdk, ref, n, nparts, rng, frame_type)
+        if tt == T.dbl:
+            v = (np.round(random_col(rng, tt, n, nilfrac=0.1, lo=-1000, hi=1000) * 8) / 8).astype(np.float64)
+        else:
+            v = random_col(rng, tt, n, nilfrac=0.1)
+        b, rb = both(gdk, ref, v, tt)
+        tp2 = T.dbl if tt == T.dbl else T.hge
+        r = gdk.GDKanalyticalsum(gdk.colnew(tp2, n), p, op, b, s, e, tt, tp2, frame_type)
+        rr = ref.GDKanalyticalsum(ref.colnew(tp2, n), rp, rop, rb, rs, re_, tt, tp2, frame_type)
+        close(r.numpy(), rr.numpy(), tp2, True)
+        r = gdk.GDKanalyticalfn("avg", gdk.colnew(T.dbl, n), p, op, b, s, e, tt, frame_type)
+        rr = ref.GDKanalyticalfn("avg", ref.colnew(T.dbl, n), rp, rop, rb, rs, re_, tt, frame_type)
+        close(r.numpy(), rr.numpy(), T.dbl, True)
+        if tt != T.dbl:
+            r = gdk.GDKanalyticalfn("avginteger", gdk.colnew(tt, n), p, op, b, s, e, tt, frame_type)
+            rr = ref.GDKanalyticalfn("avginteger", ref.colnew(tt, n), rp, rop, rb, rs, re_, tt, frame_type)
+            close(r.numpy(), rr.numpy(), tt, True)
+        for ign in (True, False):
+            r = gdk.GDKanalyticalcount(gdk.colnew(T.lng, n), p, op, b, s, e, ign, tt, frame_type)
+            rr = ref.GDKanalyticalcount(ref.colnew(T.lng, n), rp, rop, rb, rs, re_, ign, tt, frame_type)
+            close(r.numpy(), rr.numpy(), T.lng, True)
+        for fn in ("min", "max"):
+            r = gdk.GDKanalyticalfn(fn, gdk.colnew(tt, n), p, op, b, s, e, tt, frame_type)
+            rr = ref.GDKanalyticalfn(fn, ref.colnew(tt, n), rp, rop, rb, rs, re_, tt, frame_type)
+            a, c = r.numpy(), rr.numpy()
+            if tt == T.dbl:
+                assert np.array_equal(np.isnan(a), np.isnan(c)) and np.array_equal(a[~np.isnan(a)], c[~np.isnan(c)])
+            else:
+                close(a, c, tt, True)
