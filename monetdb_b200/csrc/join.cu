@@ -2,19 +2,25 @@
 // (gdk_hash.c:717-1039 BAThash_impl/BAThash; gdk_join.c:4451-4623 BATjoin,
 // :2900-3332 hashjoin, probe loop HASHJOIN :2781-2895).
 //
-// Build: a chained hash over the candidate positions of r — `head[bucket]` and
-// `next[position]`, the device form of the reference's bucket + link arrays
-// (gdk_hash.h:16-28).  Rows are pushed with one atomicExch each, so the build is a
-// single streaming pass with no locks.
+// Build: an OPEN-ADDRESSING table over the candidate positions of r (load factor <= 1/2, linear
+// probing).  A slot holds the key's canonical bits AND the row position side by side — 8 bytes for
+// keys up to 4 bytes, 16 for 8-byte keys, 32 for hge — so a probe costs one aligned vector load per
+// slot visited and never touches r's column; the first version's chained index (head[] / next[] /
+// key in the column: three dependent random reads per probe) ran the 60 M x 15 M probe at 0.07 of
+// HBM peak.  Rows claim a slot with one atomicCAS on its row word and then store the key; probes run
+// in later launches, so they always see complete slots.
+// A table of up to OA_SMEM_BYTES is STAGED IN SHARED MEMORY by the probe kernel: one elected thread
+// arms an mbarrier with the byte count and issues cp.async.bulk (TMA, SASS UBLKCP) copies of the
+// table tiles; every probe of the CTA's chunks then stays on chip (dimension-table joins).
 // Probe: the reference appends (lo, ro) pairs while it walks l in candidate order
 // and grows the result BATs as it goes (maybeextend, gdk_join.c:257-292).  Here the
-// result size is computed first: pass 1 walks each left row's chain and records
+// result size is computed first: pass 1 probes each left row and records
 // its match count and first match, a scan turns the counts into output offsets,
 // pass 2 writes the pairs — rows with a single match (every row of a foreign-key
-// join) are written straight from pass 1's record without a second walk.
+// join) are written straight from pass 1's record without a second probe.
 // Output is left-major in candidate order, like the reference's unswapped
-// hashjoin; the order of several right matches of one left row follows the chain
-// and is not specified (BATjoin promises no order, gdk_join.c:56-61).
+// hashjoin; the order of several right matches of one left row follows the probe
+// sequence and is not specified (BATjoin promises no order, gdk_join.c:56-61).
 #include "common.cuh"
 #include "keys.cuh"
 #include <mutex>
@@ -24,16 +30,39 @@
 #define JN_ROWS 4				/* left rows per thread */
 #define JN_CHUNK (JN_THREADS * JN_ROWS)
 #define JN_END 0xffffffffu
+#define OA_SMEM_BYTES (160u * 1024u)		/* largest table staged in shared memory */
+#define OA_TILE (32u * 1024u)			/* bytes per cp.async.bulk */
+
+// one slot: key bits + row position, padded to a power of two so it never straddles a 32-byte sector
+template <int KW> struct OaSlot;
+template <> struct alignas(8) OaSlot<4> { uint32_t key; uint32_t row; };
+template <> struct alignas(16) OaSlot<8> { u64 key; uint32_t row; uint32_t pad; };
+template <> struct alignas(32) OaSlot<16> { uhge key; uint32_t row; uint32_t pad[3]; };
+template <typename T> struct OaOf {
+	typedef typename KeyBits<T>::type U;
+	static constexpr int KW = sizeof(U) <= 4 ? 4 : (int) sizeof(U);
+	typedef OaSlot<KW> slot;
+	typedef decltype(slot::key) K;		/* key bits widened to the slot's key word */
+	__device__ static inline K key(T v) { return (K) KeyBits<T>::get(v); }
+};
 
 struct HashIdx {
-	uint32_t *head = nullptr, *next = nullptr;
+	void *slots = nullptr;	/* OaSlot<KW>[mask + 1] */
 	u64 mask = 0;
 	uint64_t n = 0;
+	unsigned slot_bytes = 0;
 };
+
+__global__ void oa_clear_kernel(uint4 *__restrict__ p, uint64_t n16)
+{
+	const uint4 e = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t) gridDim.x * blockDim.x)
+		p[i] = e;
+}
 
 template <typename T>
 __global__ void __launch_bounds__(JN_THREADS)
-join_build_kernel(ColSrc<T> r, bool skip_nil, uint32_t *__restrict__ head, uint32_t *__restrict__ next, u64 mask,
+join_build_kernel(ColSrc<T> r, bool skip_nil, typename OaOf<T>::slot *__restrict__ slots, u64 mask,
 		  unsigned *__restrict__ nilseen /* optional: set when r holds a nil (NOT IN, gdk_join.c:3027-3060) */)
 {
 	typedef typename KeyBits<T>::type U;
@@ -41,13 +70,61 @@ join_build_kernel(ColSrc<T> r, bool skip_nil, uint32_t *__restrict__ head, uint3
 		const T v = r.value(i);
 		if (nilseen && Atom<T>::is_nil(v))
 			*nilseen = 1;
-		if (skip_nil && Atom<T>::is_nil(v)) {
-			next[i] = JN_END;
+		if (skip_nil && Atom<T>::is_nil(v))
 			continue;
+		const typename OaOf<T>::K kv = OaOf<T>::key(v);
+		for (u64 h = hash_key<U>(KeyBits<T>::get(v), 0) & mask;; h = (h + 1) & mask) {
+			if (atomicCAS(&slots[h].row, JN_END, (uint32_t) i) == JN_END) {
+				slots[h].key = kv;
+				break;
+			}
 		}
-		const u64 h = hash_key<U>(KeyBits<T>::get(v), 0) & mask;
-		next[i] = atomicExch(head + h, (uint32_t) i);
 	}
+}
+
+// one aligned vector load of a slot (global through the read-only path, or shared memory)
+template <int KW> __device__ __forceinline__ OaSlot<KW> oa_load(const OaSlot<KW> *p)
+{
+	OaSlot<KW> s;
+	if constexpr (KW == 4) {
+		const uint2 q = __ldg(reinterpret_cast<const uint2 *>(p));
+		s.key = q.x;
+		s.row = q.y;
+	} else if constexpr (KW == 8) {
+		const uint4 q = __ldg(reinterpret_cast<const uint4 *>(p));
+		s.key = (u64) q.x | ((u64) q.y << 32);
+		s.row = q.z;
+	} else {
+		const uint4 a = reinterpret_cast<const uint4 *>(p)[0];
+		s.key = (uhge) ((u64) a.x | ((u64) a.y << 32)) | ((uhge) ((u64) a.z | ((u64) a.w << 32)) << 64);
+		s.row = reinterpret_cast<const uint32_t *>(p)[4];
+	}
+	return s;
+}
+
+// ---- TMA bulk copy global -> shared with mbarrier completion (cp.async.bulk, SASS UBLKCP)
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, uint64_t *bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+		     ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned phase)
+{
+	unsigned done;
+	do {
+		asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+			     : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+	} while (!done);
 }
 
 // The flags of the reference's leftjoin (gdk_join.c:4033-4052) as one word.
@@ -59,74 +136,100 @@ enum { JF_MULTI = 0 /* a left row produced more than one pair */, JF_ERR = 1 /* 
 // pass 1: result rows per left row (+ the first match met), total per chunk.  One row of l is
 // the body of the reference's HASHJOIN loop (gdk_join.c:2781-2895): nil handling, the walk of
 // the chain, then the semi / only_misses / nil_on_miss / max_one / min_one rules on the count.
-template <typename T>
+template <typename T, bool SMEM>
 __global__ void __launch_bounds__(JN_THREADS)
-join_count_kernel(ColSrc<T> l, ColSrc<T> r, unsigned mode, const uint32_t *__restrict__ head,
-		  const uint32_t *__restrict__ next, u64 mask, uint32_t *__restrict__ cnt, uint32_t *__restrict__ first,
-		  unsigned long long *__restrict__ chunktot, unsigned *__restrict__ flags)
+join_count_kernel(ColSrc<T> l, unsigned mode, const typename OaOf<T>::slot *__restrict__ gslots, u64 mask,
+		  uint32_t *__restrict__ cnt, uint32_t *__restrict__ first, unsigned long long *__restrict__ chunktot,
+		  uint64_t nchunks, unsigned *__restrict__ flags)
 {
 	typedef typename KeyBits<T>::type U;
+	typedef typename OaOf<T>::slot Slot;
+	constexpr int KW = OaOf<T>::KW;
+	extern __shared__ __align__(128) unsigned char oa_smem[];
 	__shared__ unsigned long long total;
-	if (threadIdx.x == 0)
-		total = 0;
-	__syncthreads();
+	__shared__ __align__(8) uint64_t bar;
+	const Slot *slots = gslots;
+	if constexpr (SMEM) {
+		/* stage the whole table in shared memory: one thread arms the barrier with the byte count and
+		 * issues the bulk copies, everybody waits for the transaction count to drain */
+		const unsigned bytes = (unsigned) ((mask + 1) * sizeof(Slot));
+		if (threadIdx.x == 0)
+			mbar_init(&bar, 1);
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(&bar, bytes);
+			for (unsigned off = 0; off < bytes; off += OA_TILE)
+				bulk_g2s(oa_smem + off, (const unsigned char *) gslots + off, bytes - off < OA_TILE ? bytes - off : OA_TILE, &bar);
+		}
+		mbar_wait(&bar, 0);
+		slots = reinterpret_cast<const Slot *>(oa_smem);
+	}
 	const bool stop_at_first = (mode & JM_ONLY_MISSES) || ((mode & JM_SEMI) && !(mode & JM_MAX_ONE));
-	unsigned long long mine = 0;
 	unsigned err = 0;
 	bool missed = false;
+	for (uint64_t chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+		__syncthreads();
+		if (threadIdx.x == 0)
+			total = 0;
+		__syncthreads();
+		unsigned long long mine = 0;
 #pragma unroll
-	for (int j = 0; j < JN_ROWS; j++) {
-		const uint64_t k = (uint64_t) blockIdx.x * JN_CHUNK + j * JN_THREADS + threadIdx.x;
-		if (k >= l.n)
-			break;
-		const T v = l.value(k);
-		unsigned c = 0, f = JN_END;
-		const bool nilrow = (!(mode & JM_NIL_MATCHES) || (mode & JM_NOT_IN)) && Atom<T>::is_nil(v);
-		if (!nilrow) {
-			const U kv = KeyBits<T>::get(v);
-			for (uint32_t p = __ldg(head + (hash_key<U>(kv, 0) & mask)); p != JN_END; p = __ldg(next + p)) {
-				if (KeyBits<T>::get(r.value(p)) == kv) {
-					if (c == 0)
-						f = p;
-					c++;
-					if (stop_at_first)
+		for (int j = 0; j < JN_ROWS; j++) {
+			const uint64_t k = chunk * JN_CHUNK + j * JN_THREADS + threadIdx.x;
+			if (k >= l.n)
+				break;
+			const T v = l.value(k);
+			unsigned c = 0, f = JN_END;
+			const bool nilrow = (!(mode & JM_NIL_MATCHES) || (mode & JM_NOT_IN)) && Atom<T>::is_nil(v);
+			if (!nilrow) {
+				const typename OaOf<T>::K kv = OaOf<T>::key(v);
+				for (u64 h = hash_key<U>(KeyBits<T>::get(v), 0) & mask;; h = (h + 1) & mask) {
+					const Slot e = SMEM ? slots[h] : oa_load<KW>(slots + h);
+					if (e.row == JN_END)
 						break;
+					if (e.key == kv) {
+						if (c == 0)
+							f = e.row;
+						c++;
+						if (stop_at_first)
+							break;
+					}
 				}
 			}
-		}
-		if (mode & (JM_NIL_ON_MISS | JM_SEMI | JM_ONLY_MISSES | JM_MAX_ONE | JM_MIN_ONE)) {
-			if (c > 1 && (mode & JM_MAX_ONE))
-				err |= 1;
-			if (mode & JM_ONLY_MISSES) {
-				c = (c == 0 && !(nilrow && (mode & JM_NOT_IN))) ? 1 : 0;
-				f = JN_END;
-			} else if (c == 0) {
-				if (mode & JM_NIL_ON_MISS) {
+			if (mode & (JM_NIL_ON_MISS | JM_SEMI | JM_ONLY_MISSES | JM_MAX_ONE | JM_MIN_ONE)) {
+				if (c > 1 && (mode & JM_MAX_ONE))
+					err |= 1;
+				if (mode & JM_ONLY_MISSES) {
+					c = (c == 0 && !(nilrow && (mode & JM_NOT_IN))) ? 1 : 0;
+					f = JN_END;
+				} else if (c == 0) {
+					if (mode & JM_NIL_ON_MISS) {
+						c = 1;
+						missed = true;
+					} else if (mode & JM_MIN_ONE) {
+						err |= 2;
+					}
+				} else if (mode & JM_SEMI) {
 					c = 1;
-					missed = true;
-				} else if (mode & JM_MIN_ONE) {
-					err |= 2;
 				}
-			} else if (mode & JM_SEMI) {
-				c = 1;
 			}
+			cnt[k] = c;
+			first[k] = f;
+			mine += c;
 		}
-		cnt[k] = c;
-		first[k] = f;
-		mine += c;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1)
+			mine += __shfl_xor_sync(0xffffffffu, mine, o);
+		if ((threadIdx.x & 31) == 0 && mine)
+			atomicAdd(&total, mine);
+		__syncthreads();
+		if (threadIdx.x == 0)
+			chunktot[chunk] = total;
 	}
 	if (err)
 		atomicOr(flags + JF_ERR, err);
 	if (missed)
 		flags[JF_MISS] = 1;
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1)
-		mine += __shfl_xor_sync(0xffffffffu, mine, o);
-	if ((threadIdx.x & 31) == 0 && mine)
-		atomicAdd(&total, mine);
-	__syncthreads();
-	if (threadIdx.x == 0)
-		chunktot[blockIdx.x] = total;
 }
 
 // exclusive scan of the chunk totals by one CTA; grand total -> offs[nchunks] and slot[0]
@@ -181,7 +284,7 @@ join_scan_kernel(const unsigned long long *__restrict__ tot, uint64_t nchunks, u
 // pass 2: write the (left oid, right oid) pairs of a chunk at its output offset
 template <typename T>
 __global__ void __launch_bounds__(JN_THREADS)
-join_fill_kernel(ColSrc<T> l, ColSrc<T> r, const uint32_t *__restrict__ next, const uint32_t *__restrict__ cnt,
+join_fill_kernel(ColSrc<T> l, ColSrc<T> r, const typename OaOf<T>::slot *__restrict__ slots, u64 mask, const uint32_t *__restrict__ cnt,
 		 const uint32_t *__restrict__ first, const unsigned long long *__restrict__ offs, oid *__restrict__ r1,
 		 oid *__restrict__ r2, unsigned *__restrict__ flags /* [0] a left row matched more than once */)
 {
@@ -227,13 +330,20 @@ join_fill_kernel(ColSrc<T> l, ColSrc<T> r, const uint32_t *__restrict__ next, co
 			continue;
 		}
 		multi = true;
-		const U kv = KeyBits<T>::get(l.value(k));
-		for (; p != JN_END; p = __ldg(next + p)) {
-			if (KeyBits<T>::get(r.value(p)) == kv) {
+		/* several matches: probe again from the key's home slot and emit every equal key */
+		const T v = l.value(k);
+		const typename OaOf<T>::K kv = OaOf<T>::key(v);
+		unsigned left = c[j];
+		for (u64 h = hash_key<U>(KeyBits<T>::get(v), 0) & mask; left > 0; h = (h + 1) & mask) {
+			const typename OaOf<T>::slot e = oa_load<OaOf<T>::KW>(slots + h);
+			if (e.row == JN_END)
+				break;
+			if (e.key == kv) {
 				r1[pos] = lo;
 				if (r2)
-					r2[pos] = r.rowoid(p);
+					r2[pos] = r.rowoid(e.row);
 				pos++;
+				left--;
 			}
 		}
 	}
@@ -254,8 +364,7 @@ void hash_cache_drop(const void *base)
 	std::lock_guard<std::mutex> lk(g_hash_mu);
 	auto it = g_hash_cache.find(base);
 	if (it != g_hash_cache.end()) {
-		dev_free(it->second.head);
-		dev_free(it->second.next);
+		dev_free(it->second.slots);
 		g_hash_cache.erase(it);
 	}
 }
@@ -271,17 +380,20 @@ static inline u64 hash_pow2(u64 x)
 template <typename T> static bool hash_build(const ColSrc<T> &r, bool skip_nil, HashIdx &h, unsigned *nilseen = nullptr)
 {
 	Ctx *c = ctx();
+	typedef typename OaOf<T>::slot Slot;
 	h.n = r.n;
-	h.mask = hash_pow2(r.n) - 1;		/* load factor <= 1, like HASHmask (gdk_hash.c:42-55) */
-	h.head = (uint32_t *) dev_alloc((h.mask + 1) * 4);
-	h.next = (uint32_t *) dev_alloc((r.n ? r.n : 1) * 4);
-	if (h.head == nullptr || h.next == nullptr ||
-	    !cuda_ok(cudaMemsetAsync(h.head, 0xff, (h.mask + 1) * 4, c->stream), "memset hash heads"))
+	h.mask = hash_pow2(2 * r.n) - 1;		/* load factor <= 1/2 */
+	h.slot_bytes = sizeof(Slot);
+	const size_t bytes = (size_t) (h.mask + 1) * sizeof(Slot);
+	h.slots = dev_alloc(bytes);
+	if (h.slots == nullptr)
 		return false;
+	oa_clear_kernel<<<grid_for(bytes / 16, 256, NSM * 16), 256, 0, c->stream>>>((uint4 *) h.slots, bytes / 16);
+	COUNT_LAUNCH();
 	if (r.n == 0)
-		return true;
-	KTimer kt("hash_build", r.n * (sizeof(T) + 8));
-	join_build_kernel<T><<<grid_for(r.n, JN_THREADS, NSM * 16), JN_THREADS, 0, c->stream>>>(r, skip_nil, h.head, h.next, h.mask, nilseen);
+		return cuda_ok(cudaGetLastError(), "hash clear launch");
+	KTimer kt("hash_build", r.n * (sizeof(T) + sizeof(Slot)));
+	join_build_kernel<T><<<grid_for(r.n, JN_THREADS, NSM * 16), JN_THREADS, 0, c->stream>>>(r, skip_nil, (Slot *) h.slots, h.mask, nilseen);
 	COUNT_LAUNCH();
 	return cuda_ok(cudaGetLastError(), "hash build launch");
 }
@@ -327,11 +439,10 @@ extern "C" b200_return b200_BAThash(const b200_bat *b)
 	if (!cand_init(ci, b, nullptr))
 		return B200_FAIL;
 	HashIdx h;
-	ctx()->algo = "hash: cuda chained build";
+	ctx()->algo = "hash: cuda open-addressing build";
 	/* nils are indexed too (the reference hashes every BUN); probes skip them unless nil_matches */
 	if (!hash_build_any(basetype(b->ttype), b, ci, false, h) || !stream_sync()) {
-		dev_free(h.head);
-		dev_free(h.next);
+		dev_free(h.slots);
 		return B200_FAIL;
 	}
 	std::lock_guard<std::mutex> lk(g_hash_mu);
@@ -356,8 +467,24 @@ static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, co
 	if (cnt == nullptr || first == nullptr || tot == nullptr || offs == nullptr)
 		goto done;
 	{
-		KTimer kt("join_probe", nl * (sizeof(T) + 4 + 4 + sizeof(T) + 8));
-		join_count_kernel<T><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, rs, mode, h.head, h.next, h.mask, cnt, first, tot, flags);
+		typedef typename OaOf<T>::slot Slot;
+		const size_t tbytes = (size_t) (h.mask + 1) * sizeof(Slot);
+		KTimer kt("join_probe", nl * (sizeof(T) + sizeof(Slot) + 8));	/* key + about one slot + count/first per probe row */
+		if (tbytes <= OA_SMEM_BYTES && nchunks >= 4) {
+			/* small build side: every CTA stages the table in shared memory (cp.async.bulk) and probes on chip */
+			static bool attr_set = false;
+			if (!attr_set) {
+				cudaFuncSetAttribute(join_count_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) OA_SMEM_BYTES);
+				attr_set = true;
+			}
+			const unsigned grid = (unsigned) (nchunks < (uint64_t) NSM ? nchunks : NSM);
+			join_count_kernel<T, true><<<grid, JN_THREADS, tbytes, c->stream>>>(ls, mode, (const Slot *) h.slots, h.mask, cnt, first, tot,
+											 nchunks, flags);
+			c->algo = "join: cuda hashjoin, table staged in shared memory by cp.async.bulk";
+		} else {
+			join_count_kernel<T, false><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, mode, (const Slot *) h.slots, h.mask, cnt, first,
+												       tot, nchunks, flags);
+		}
 	}
 	COUNT_LAUNCH();
 	join_scan_kernel<<<1, 1024, 0, c->stream>>>(tot, nchunks, offs, c->slot_d->v, flags);
@@ -385,7 +512,7 @@ static bool join_typed(const b200_bat *l, const b200_bat *r, const Cand &lci, co
 	if (total > 0) {
 		{
 			KTimer kt("join_fill", nl * 8 + total * (r2 ? 16 : 8));
-			join_fill_kernel<T><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, rs, h.next, cnt, first, offs, (oid *) r1->base,
+			join_fill_kernel<T><<<(unsigned) nchunks, JN_THREADS, 0, c->stream>>>(ls, rs, (const typename OaOf<T>::slot *) h.slots, h.mask, cnt, first, offs, (oid *) r1->base,
 											      r2 ? (oid *) r2->base : nullptr, flags);
 		}
 		COUNT_LAUNCH();
@@ -559,10 +686,8 @@ static b200_return join_driver(b200_bat **r1p, b200_bat **r2p, const b200_bat *l
 		rc = ok ? B200_SUCCEED : B200_FAIL;
 	}
 	dev_free(flags);
-	if (owned) {
-		dev_free(h.head);
-		dev_free(h.next);
-	}
+	if (owned)
+		dev_free(h.slots);
 	return rc;
 }
 
