@@ -74,7 +74,12 @@ join_build_kernel(ColSrc<T> r, bool skip_nil, typename OaOf<T>::slot *__restrict
 			continue;
 		const typename OaOf<T>::K kv = OaOf<T>::key(v);
 		for (u64 h = hash_key<U>(KeyBits<T>::get(v), 0) & mask;; h = (h + 1) & mask) {
-			if (atomicCAS(&slots[h].row, JN_END, (uint32_t) i) == JN_END) {
+			if constexpr (OaOf<T>::KW == 4) {
+				/* key and row are one 64-bit word: a single CAS from the all-ones empty pattern fills the slot */
+				const unsigned long long want = (unsigned long long) kv | ((unsigned long long) (uint32_t) i << 32);
+				if (atomicCAS(reinterpret_cast<unsigned long long *>(slots + h), ~0ULL, want) == ~0ULL)
+					break;
+			} else if (atomicCAS(&slots[h].row, JN_END, (uint32_t) i) == JN_END) {
 				slots[h].key = kv;
 				break;
 			}
