@@ -250,6 +250,14 @@ b200_bat *b200_BATcalcsign(const b200_bat *b, const b200_bat *s);
 /* BATunique (gdk.h:2279, gdk_unique.c:30): candidate list of the first row of each distinct value of b within s */
 b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s);
 
+/* ---- sort / top-N: gdk_batop.c:2342 (BATsort: sorted copy, order oids, group ids; o / g chain
+ *      the calls of a multi-column ORDER BY), gdk_firstn.c:1280 (BATfirstn, plain form: g == NULL, gids == NULL,
+ *      !distinct).  One stable LSD radix sort serves stable and !stable alike. ---- */
+b200_return b200_BATsort(b200_bat **sorted, b200_bat **order, b200_bat **groups, const b200_bat *b, const b200_bat *o,
+			 const b200_bat *g, bool reverse, bool nilslast, bool stable);
+b200_return b200_BATfirstn(b200_bat **topn, b200_bat **gids, const b200_bat *b, const b200_bat *s, const b200_bat *g,
+			   uint64_t n, bool asc, bool nilslast, bool distinct);
+
 /* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */
 b200_return b200_BAThash(const b200_bat *b);
 b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,

@@ -327,6 +327,23 @@ extern "C" b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int t
 		set_err("type combination (convert(%s)->%s) not supported.\n", atomname(b->ttype), atomname(tp));
 		return nullptr;
 	}
+	{
+		/* the powers of ten must fit the types they are cast to (the reference divides by a wrapped 0 otherwise) */
+		auto fits = [](hge p, int t) {
+			switch (t) {
+			case B200_bte: return p <= 100;
+			case B200_sht: return p <= 10000;
+			case B200_int: return p <= 1000000000;
+			case B200_lng: return p <= (hge) 1000000000000000000LL;
+			default: return true;
+			}
+		};
+		if ((!f2 && (!fits(sc.mul, t2) || !fits(sc.prec, t2))) || (!f1 && !fits(sc.div, t1))) {
+			set_err("BATconvert: scale / precision does not fit the types (convert(%s)->%s, %d, %d, %d)\n", atomname(b->ttype),
+				atomname(tp), scale1, scale2, precision);
+			return nullptr;
+		}
+	}
 	b200_bat *bn = bat_new(ci.rhseq, tp, ci.ncand);
 	if (bn == nullptr)
 		return nullptr;

@@ -539,6 +539,30 @@ def BATgroup(b: BAT, s: BAT | None = None, g: BAT | None = None, e: BAT | None =
     return BAT(pg), (BAT(pe) if want_extents else None), (BAT(ph) if want_histo else None)
 
 
+# ------------------------------------------------------------------ sort / top-N (gdk.h BATsort, BATfirstn)
+_sig("b200_BATsort", C.c_int, _PP, _PP, _PP, _P, _P, _P, C.c_bool, C.c_bool, C.c_bool)
+_sig("b200_BATfirstn", C.c_int, _PP, _PP, _P, _P, _P, C.c_uint64, C.c_bool, C.c_bool, C.c_bool)
+
+
+def BATsort(b: BAT, o: BAT | None = None, g: BAT | None = None, reverse: bool = False, nilslast: bool = False,
+            stable: bool = False, want=(True, True, True)):
+    """BATsort (gdk_batop.c:2342) -> (sorted, order, groups); entries of `want` that are False come back None"""
+    ps, po, pg = _P(), _P(), _P()
+    rc = lib.b200_BATsort(C.byref(ps) if want[0] else None, C.byref(po) if want[1] else None, C.byref(pg) if want[2] else None,
+                          b._p, _ptr(o), _ptr(g), reverse, nilslast, stable)
+    if rc != 1:
+        _fail("BATsort")
+    return (BAT(ps) if want[0] else None), (BAT(po) if want[1] else None), (BAT(pg) if want[2] else None)
+
+
+def BATfirstn(b: BAT, s: BAT | None, n: int, asc: bool = True, nilslast: bool = False) -> BAT:
+    """BATfirstn, plain form (gdk_firstn.c:1280) -> candidate list of the n smallest / largest values"""
+    p = _P()
+    if lib.b200_BATfirstn(C.byref(p), None, b._p, _ptr(s), None, n, asc, nilslast, False) != 1:
+        _fail("BATfirstn")
+    return BAT(p)
+
+
 # ------------------------------------------------------------------ hash + join (gdk_hash.h:36, gdk.h:2266)
 _sig("b200_BAThash", C.c_int, _P)
 _sig("b200_BATjoin", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_bool, C.c_uint64)

@@ -178,6 +178,8 @@ def _load(nthreads: int = 0):
         "GDKanalyticalmin": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
         "GDKanalyticalmax": (C.c_int, [P, P, P, P, P, P, C.c_int, C.c_int]),
         "COLnew": (P, [C.c_uint64, C.c_int, C.c_uint64, C.c_int]),
+        "BATsort": (C.c_int, [C.POINTER(P), C.POINTER(P), C.POINTER(P), P, P, P, B, B, B]),
+        "BATfirstn": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, C.c_uint64, B, B, B]),
     }
     for op in ("add", "sub", "mul", "div", "mod"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, C.c_int])
@@ -550,6 +552,26 @@ def BATsum(tp, b, s=None, skip_nils=True, nil_if_empty=True):
         clrerr()
         raise RefError(msg or "BATsum failed")
     return out
+
+
+def BATsort(b, o=None, g=None, reverse=False, nilslast=False, stable=False, want=(True, True, True)):
+    ps, po, pg = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    rc = _bat.BATsort(C.byref(ps) if want[0] else None, C.byref(po) if want[1] else None, C.byref(pg) if want[2] else None,
+                      b.p, _p(o), _p(g), reverse, nilslast, stable)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATsort failed")
+    return (RBAT(ps.value) if want[0] else None), (RBAT(po.value) if want[1] else None), (RBAT(pg.value) if want[2] else None)
+
+
+def BATfirstn(b, s, n, asc=True, nilslast=False) -> RBAT:
+    p = C.c_void_p()
+    if _bat.BATfirstn(C.byref(p), None, b.p, _p(s), None, n, asc, nilslast, False) != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATfirstn failed")
+    return RBAT(p.value)
 
 
 def BATjoin(l, r, sl=None, sr=None, nil_matches=False, estimate=BUN_NONE):

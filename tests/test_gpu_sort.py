@@ -1,0 +1,131 @@
+"""BATsort / BATfirstn against the reference (gdk_batop.c:2342, gdk_firstn.c:1280):
+sorted copies and group ids bit-exact; order columns identical for stable sorts and valid permutations (the
+order of equal values is open) otherwise; multi-column ORDER BY through the (order, groups) chain."""
+import numpy as np
+import pytest
+
+from monetdb_b200 import gdk as G
+from tests.util import both, random_col, same_bits
+
+pytestmark = pytest.mark.gpu
+T = G.TYPE
+MODES = [(False, False, False), (True, True, False), (False, True, False), (True, False, False), (False, False, True), (True, True, True)]
+
+
+def check_sort(gdk, ref, b, rb, a, o=None, ro=None, g=None, rg=None, mode=(False, False, False), hseq=0):
+    rev, nl, st = mode
+    s, od, gr = gdk.BATsort(b, o, g, rev, nl, st)
+    rs, rod, rgr = ref.BATsort(rb, ro, rg, rev, nl, st)
+    sa, ra = s.numpy(), rs.numpy()
+    assert same_bits(sa, ra), (mode, sa[:8], ra[:8])
+    assert same_bits(gr.numpy(), rgr.numpy()), mode
+    oa, roa = od.numpy(), rod.numpy()
+    # a permutation of the input rows that reproduces the sorted column
+    assert np.array_equal(np.sort(oa), np.sort(roa))
+    assert same_bits(a[(oa - hseq).astype(np.int64)], sa)
+    if st:
+        assert np.array_equal(oa, roa), mode
+    for x, y in ((s, rs), (od, rod), (gr, rgr)):
+        px, py = x.props(), y.props()
+        assert (px["count"], px["hseq"]) == (py["count"], py["hseq"])
+        # order flags may be conservative but never falsely true
+        if px["sorted"] and len(sa) > 1 and x is s and a.dtype.names is None and not np.issubdtype(a.dtype, np.floating):
+            v = sa.astype(object)
+            assert all(v[i] <= v[i + 1] for i in range(min(len(v) - 1, 2000)))
+    return (s, od, gr), (rs, rod, rgr)
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng, T.hge, T.flt, T.dbl, T.date, T.timestamp, T.oid])
+@pytest.mark.parametrize("mode", MODES)
+def test_single_column(gdk, ref, tt, mode):
+    rng = np.random.default_rng(tt * 13 + sum(mode))
+    for n, distinct, nilfrac in ((1, 1, 0), (2, 2, 0.5), (33, 5, 0.2), (2049, 50, 0.1), (70_001, 1000, 0.05), (70_001, 10**9, 0.0)):
+        if tt == T.oid:
+            a = rng.integers(0, min(distinct, 10**9), n).astype(np.uint64)
+            if nilfrac:
+                a[rng.random(n) < nilfrac] = np.uint64(1 << 63)
+        elif tt in (T.flt, T.dbl):
+            a = np.round(rng.uniform(-distinct, distinct, n)).astype(G.NP_OF[tt])
+            a[rng.random(n) < 0.05] = -0.0
+            if nilfrac:
+                a[rng.random(n) < nilfrac] = np.nan
+        else:
+            hi = min(distinct, {T.bte: 120, T.sht: 30000}.get(tt, 10**9))
+            a = random_col(rng, tt, n, nilfrac=nilfrac, lo=-hi, hi=hi)
+        b, rb = both(gdk, ref, a, tt, hseq=7)
+        check_sort(gdk, ref, b, rb, a, mode=mode, hseq=7)
+
+
+@pytest.mark.parametrize("stable", [False, True])
+def test_multi_column_order_by(gdk, ref, stable):
+    """ORDER BY c1, c2 DESC, c3: each call refines the (order, groups) of the previous one"""
+    rng = np.random.default_rng(5 + stable)
+    n = 50_003
+    c1 = rng.integers(0, 20, n).astype(np.int32)
+    c2 = random_col(rng, T.lng, n, nilfrac=0.05, lo=-30, hi=30)
+    c3 = np.round(rng.uniform(-5, 5, n)).astype(np.float64)
+    b1, r1 = both(gdk, ref, c1, T.int)
+    b2, r2 = both(gdk, ref, c2, T.lng)
+    b3, r3 = both(gdk, ref, c3, T.dbl)
+    (s1, o1, g1), (rs1, ro1, rg1) = check_sort(gdk, ref, b1, r1, c1, mode=(False, False, stable))
+    # the second key is sorted inside the groups of the first, descending
+    m2 = (True, True, stable)
+    s2, o2, g2 = gdk.BATsort(b2, o1, g1, *m2)
+    rs2, ro2, rg2 = ref.BATsort(r2, ro1 if stable else ref.bat(o1.numpy(), ref.T.oid), rg1, *m2)
+    assert same_bits(s2.numpy(), rs2.numpy())
+    assert same_bits(g2.numpy(), rg2.numpy())
+    assert same_bits(c2[o2.numpy().astype(np.int64)], s2.numpy())
+    if stable:
+        assert np.array_equal(o2.numpy(), ro2.numpy())
+    s3, o3, g3 = gdk.BATsort(b3, o2, g2, False, False, stable)
+    rs3, ro3, rg3 = ref.BATsort(r3, ro2 if stable else ref.bat(o2.numpy(), ref.T.oid), rg2, False, False, stable)
+    assert same_bits(s3.numpy(), rs3.numpy())
+    assert same_bits(g3.numpy(), rg3.numpy())
+    # the final order is the lexicographic one
+    fo = o3.numpy().astype(np.int64)
+    k2 = np.where(c2 == np.iinfo(np.int64).min, np.iinfo(np.int64).min, c2)
+    ref_order = np.lexsort((c3, -k2.astype(np.float64), c1))
+    assert np.array_equal(c1[fo], c1[ref_order]) and same_bits(c2[fo], c2[ref_order]) and same_bits(c3[fo], c3[ref_order])
+    if stable:
+        assert np.array_equal(o3.numpy(), ro3.numpy())
+
+
+def test_sort_only_some_outputs_and_errors(gdk, ref):
+    a = np.array([5, 3, 9, 3, 1], dtype=np.int64)
+    b, rb = both(gdk, ref, a, T.lng)
+    s, o, g = gdk.BATsort(b, None, None, False, False, False, want=(True, False, False))
+    assert o is None and g is None and s.numpy().tolist() == [1, 3, 3, 5, 9]
+    s, o, g = gdk.BATsort(b, None, None, False, False, False, want=(False, True, False))
+    assert s is None and a[o.numpy().astype(np.int64)].tolist() == [1, 3, 3, 5, 9]
+    with pytest.raises(G.GDKError) as e1:
+        gdk.BATsort(b, None, None, True, False, True)
+    with pytest.raises(Exception) as e2:
+        ref.BATsort(rb, None, None, True, False, True)
+    assert str(e1.value).strip() == str(e2.value).strip() == "stable sort cannot have reverse != nilslast"
+
+
+@pytest.mark.parametrize("tt", [T.int, T.lng, T.dbl])
+@pytest.mark.parametrize("asc", [True, False])
+@pytest.mark.parametrize("nilslast", [True, False])
+def test_firstn(gdk, ref, tt, asc, nilslast):
+    rng = np.random.default_rng(tt + asc * 2 + nilslast)
+    for n, k in ((10, 3), (10, 20), (5000, 100), (60_000, 1000), (60_000, 1)):
+        if tt == T.dbl:
+            a = np.round(rng.uniform(-500, 500, n)).astype(np.float64)
+            a[rng.random(n) < 0.01] = np.nan
+        else:
+            a = random_col(rng, tt, n, nilfrac=0.01, lo=-500, hi=500)
+        b, rb = both(gdk, ref, a, tt, hseq=3)
+        got, want = gdk.BATfirstn(b, None, k, asc, nilslast), ref.BATfirstn(rb, None, k, asc, nilslast)
+        ga, wa = got.numpy(), want.numpy()
+        assert len(ga) == len(wa) == min(k, n)
+        assert np.all(np.diff(ga.astype(np.int64)) > 0)                # a candidate list
+        # the same VALUES are selected (which of several equal boundary rows is open)
+        gv, wv = np.sort(a[(ga - 3).astype(np.int64)]), np.sort(a[(wa - 3).astype(np.int64)])
+        assert same_bits(gv, wv)
+        # with a candidate list
+        cand = np.sort(rng.choice(n, max(1, n // 2), replace=False)).astype(np.uint64) + 3
+        s, rs = gdk.BATfromhost(cand, T.oid).setprops(sorted=True, key=True, nonil=True), ref.bat(cand, ref.T.oid, sorted=True, key=True, nonil=True)
+        ga, wa = gdk.BATfirstn(b, s, k, asc, nilslast).numpy(), ref.BATfirstn(rb, rs, k, asc, nilslast).numpy()
+        assert set(ga.tolist()) <= set(cand.tolist())
+        assert same_bits(np.sort(a[(ga - 3).astype(np.int64)]), np.sort(a[(wa - 3).astype(np.int64)]))
