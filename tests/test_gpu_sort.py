@@ -17,7 +17,11 @@ def check_sort(gdk, ref, b, rb, a, o=None, ro=None, g=None, rg=None, mode=(False
     s, od, gr = gdk.BATsort(b, o, g, rev, nl, st)
     rs, rod, rgr = ref.BATsort(rb, ro, rg, rev, nl, st)
     sa, ra = s.numpy(), rs.numpy()
-    assert same_bits(sa, ra), (mode, sa[:8], ra[:8])
+    if not st and sa.dtype.names is None and np.issubdtype(sa.dtype, np.floating):
+        # -0 == +0: an unstable sort may leave them in any order; compare with the zeros folded
+        assert same_bits(sa + 0.0, ra + 0.0), (mode, sa[:8], ra[:8])
+    else:
+        assert same_bits(sa, ra), (mode, sa[:8], ra[:8])
     assert same_bits(gr.numpy(), rgr.numpy()), mode
     oa, roa = od.numpy(), rod.numpy()
     # a permutation of the input rows that reproduces the sorted column
