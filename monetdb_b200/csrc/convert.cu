@@ -318,11 +318,7 @@ extern "C" b200_bat *b200_BATconvert(const b200_bat *b, const b200_bat *s, int t
 	} else if (f1 && !f2) {
 		sc.mul = pow10_hge(scale2);
 		sc.prec = precision ? pow10_hge(precision) : 0;
-	} else if (t1 == B200_dbl && t2 == B200_flt) {
-		sc.mul = pow10_hge(scale2 > 38 ? 38 : scale2);
-	} else {
-		sc.div = pow10_hge(scale1 > 38 ? 38 : scale1);
-	}
+	}	/* floating point -> floating point: the reference passes scale 0 (gdk_calc_convert.c:1346-1405) */
 	if (atomsize(t1) <= 0 || atomsize(t2) <= 0) {
 		set_err("type combination (convert(%s)->%s) not supported.\n", atomname(b->ttype), atomname(tp));
 		return nullptr;
