@@ -190,6 +190,25 @@ def join_repartitioned(X, l, r, timings=None):
     return g1, g2
 
 
+# ---------------------------------------------------------------------------- high-cardinality GROUP BY
+def groupby_sum_repartitioned(X, key, val, tp=T_hge):
+    """GROUP BY key, SUM(val) when the number of groups is too large for a packed partial table:
+    every rank hash-partitions its (key, global oid) tuples by hash(key) mod world (BATpartition), fetches the
+    values of those rows (BATproject through the oids), one grouped NCCL send/recv moves keys, oids and values to
+    the rank owning the hash range (comm_exchange), and that rank groups and aggregates locally.  Every key
+    lives on exactly one rank, so the ranks' results are disjoint and complete; they stay distributed:
+    returns (keys, first, sums, counts) of this rank's groups, where `first` is the smallest GLOBAL oid of the
+    group — BATgroup's first occurrence, so the concatenation over the ranks ordered by `first` is the
+    unsharded BATgroup numbering.  nil keys are kept (they form a group, gdk_group.c:56-60)."""
+    world = X.comm_world()
+    k, oids, counts = X.BATpartition(key, None, world, keep_nil=True)
+    v = X.BATproject(oids, val)
+    (k2, o2, v2), _ = X.comm_exchange([k, oids, v], counts)
+    g, e, h = X.BATgroup(k2, None, None, None, None)
+    return (X.BATproject(e, k2), X.BATproject(X.BATgroupmin(o2, g, e, None), o2), X.BATgroupsum(v2, g, e, None, tp, True),
+            X.BATgroupcount(v2, g, e, None, T_lng, True))
+
+
 def _local_join(X, lk_ptr, lo_ptr, nl, rk_ptr, ro_ptr, nr, tt, keep=None):
     """BATjoin of received (key, oid) runs; positions are mapped back to the global oids they carry"""
     T = X.TYPE

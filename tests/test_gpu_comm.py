@@ -153,6 +153,38 @@ def test_partition_exchange_join_single_rank(comm1, ref, tt):
     assert same_bits(a[(oo - 5000).astype(np.int64)], kk)          # every tuple carries its own row's key
 
 
+def _groupby_reference(ref, keys, vals):
+    """key -> (first oid, sum, count) from ONE reference BATgroup + BATgroupsum over all rows"""
+    rk, rv = ref.bat(keys, ref.T.lng), ref.bat(vals, ref.T.lng)
+    g, e, h = ref.BATgroup(rk, None, None, None, None)
+    sums = ref.BATgroupsum(rv, g, e, None, ref.T.hge, True).numpy()
+    cnts = ref.BATgroupcount(rv, g, e, None, ref.T.lng, True).numpy()
+    ext = e.numpy()
+    return {int(keys[int(x)]): (int(x), (int(sums["hi"][i]) << 64) | int(sums["lo"][i]), int(cnts[i])) for i, x in enumerate(ext)}
+
+
+def _groupby_collect(parts):
+    out = {}
+    for k, first, sums, cnts in parts:
+        for i in range(len(k)):
+            assert int(k[i]) not in out, "a key showed up on two ranks"
+            out[int(k[i])] = (int(first[i]), (int(sums["hi"][i]) << 64) | int(sums["lo"][i]), int(cnts[i]))
+    return out
+
+
+def test_high_cardinality_groupby_single_rank(comm1, ref):
+    """BATpartition + comm_exchange + local BATgroup/BATgroupsum == one reference GROUP BY (200 k groups)"""
+    from monetdb_b200 import shard
+    rng = np.random.default_rng(9)
+    n = 400_003
+    keys = rng.integers(0, 200_000, n).astype(np.int64)
+    keys[rng.random(n) < 0.01] = np.iinfo(np.int64).min          # nil keys form a group
+    vals = rng.integers(-10**9, 10**9, n).astype(np.int64)
+    kb, vb = comm1.BATfromhost(keys, T.lng), comm1.BATfromhost(vals, T.lng, nonil=True)
+    parts = [tuple(x.numpy() for x in shard.groupby_sum_repartitioned(comm1, kb, vb))]
+    assert _groupby_collect(parts) == _groupby_reference(ref, keys, vals)
+
+
 # ---------------------------------------------------------------------------- lifetimes (ADVICE r1)
 def test_project_dense_view_outlives_parent(gdk):
     """BATproject with dense candidates returns a view of r's heap; it must stay valid after r is freed and
@@ -294,6 +326,14 @@ def _nccl_worker(rank, world, port, n, q):
     r = g.BATfromhost(okey, g.TYPE.int, hseq=rank * nr, nonil=True)
     g1, g2 = shard.join_repartitioned(g, l, r)
     out["join"] = (g1.numpy(), g2.numpy())
+    # high-cardinality GROUP BY: rank r holds rows [r*ng, (r+1)*ng)
+    ng = 150_000
+    rng = np.random.default_rng(77)
+    allk = rng.integers(0, 90_000, ng * world).astype(np.int64)
+    allv = rng.integers(-10**9, 10**9, ng * world).astype(np.int64)
+    kb = g.BATfromhost(allk[rank * ng:(rank + 1) * ng], g.TYPE.lng, hseq=rank * ng, nonil=True)
+    vb = g.BATfromhost(allv[rank * ng:(rank + 1) * ng], g.TYPE.lng, hseq=rank * ng, nonil=True)
+    out["groupby"] = tuple(x.numpy() for x in shard.groupby_sum_repartitioned(g, kb, vb))
     q.put((rank, out))
     dist.barrier()
     g.comm_destroy()
@@ -335,3 +375,8 @@ def test_nccl_two_ranks_q1_q6_join(ref):
     x2 = np.concatenate([got[r]["join"][1] for r in range(world)])
     o, p = np.lexsort((x2, x1)), np.lexsort((e2.numpy(), e1.numpy()))
     assert np.array_equal(x1[o], e1.numpy()[p]) and np.array_equal(x2[o], e2.numpy()[p])
+    ng = 150_000
+    rng = np.random.default_rng(77)
+    allk = rng.integers(0, 90_000, ng * world).astype(np.int64)
+    allv = rng.integers(-10**9, 10**9, ng * world).astype(np.int64)
+    assert _groupby_collect([got[r]["groupby"] for r in range(world)]) == _groupby_reference(ref, allk, allv)
