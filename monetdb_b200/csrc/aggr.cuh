@@ -254,6 +254,7 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const GT *__restrict__ gids, o
 			acc[g][w] = 0;
 	}
 	UA maxabs = 0;
+	u64 ormax = 0;
 	/* one-byte ids: a thread takes 8 CONSECUTIVE rows, their ids are one 8-byte load and their
 	 * values 16-byte loads (vals must be 16-byte aligned; byte-wide LDGs measured far slower) */
 	constexpr bool G8 = HASGID && sizeof(GT) == 1;
@@ -311,16 +312,22 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const GT *__restrict__ gids, o
 			const u64 go = gid[u] - gmin;
 			const bool ok = !Atom<T1>::is_nil(x[u]) && go <= gspan;		/* a tail slot holds nil */
 			const unsigned gi = ok ? (unsigned) go : 0xffffffffu;
-			UA ax;
-			if constexpr (NARROW) {
-				const i64 lo = (i64) (u64) x[u];
-				anywide |= ok && (i64) ((uhge) x[u] >> 64) != (lo >> 63);
-				ax = lo < 0 ? (u64) 0 - (u64) lo : (u64) lo;
+			if constexpr (sizeof(UA) == 8) {
+				/* |x| (or |x| - 1) OR-ed together: at most twice max |x|, in 3 instructions instead of the
+				 * 9 of abs + compare + select — the bound check only needs an upper estimate */
+				i64 lo;
+				if constexpr (NARROW) {
+					lo = (i64) (u64) x[u];
+					anywide |= ok && (i64) ((uhge) x[u] >> 64) != (lo >> 63);
+				} else {
+					lo = (i64) x[u];
+				}
+				ormax |= ok ? (u64) (lo ^ (lo >> 63)) : 0;
 			} else {
-				ax = x[u] < 0 ? (UA) 0 - (UA) x[u] : (UA) x[u];
+				const UA ax = x[u] < 0 ? (UA) 0 - (UA) x[u] : (UA) x[u];
+				if (ok && ax > maxabs)
+					maxabs = ax;
 			}
-			if (ok && ax > maxabs)
-				maxabs = ax;
 			/* sign-extended words of x */
 			u64 xw[NW];
 			if constexpr (NARROW) {
@@ -357,6 +364,8 @@ aggr_reg_fast_kernel(const T1 *__restrict__ vals, const GT *__restrict__ gids, o
 			}
 		}
 	}
+	if constexpr (sizeof(UA) == 8)
+		maxabs = (UA) (ormax + (ormax != 0));	/* >= max |x|; 0 when no value was seen */
 	/* wide sum -> ND digit cells: digits 0..ND-2 are the low 32-bit pieces, the top
 	 * digit is the arithmetic remainder (fits 64 bits: |sum| < 2^(32 ND + 31)) */
 	__shared__ i64 wsum[AGGR_THREADS / 32][NG * (ND + 1)];
