@@ -162,34 +162,67 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 	__syncthreads();
 	unsigned inserted = 0;
 	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
-	for (uint64_t r = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r < src.n; r += stride) {
-		const U v = KeyBits<T>::get(src.value(r));
-		const u64 gv = HASG ? src.gval(r) : 0;
-		u64 h = hash_key<U>(v, gv) & mask;
-		unsigned probes = 0;
-		for (;;) {
-			u64 cur = __ldcg(slots + h);
-			if (cur == GRP_EMPTY) {
-				cur = atomicCAS(slots + h, GRP_EMPTY, (u64) r);
-				if (cur == GRP_EMPTY) {
-					inserted++;
-					break;
+	constexpr int B = 4;		/* rows in flight per thread */
+	for (uint64_t r0 = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r0 < src.n; r0 += stride * B) {
+		/* The common case of a low-cardinality key — the slot at the key's home position already holds an
+		 * EARLIER row with the same key — needs three dependent loads (key, slot, key of the slot's row) and
+		 * no atomic.  One row at a time that chain left the kernel latency-bound (37 % + 27 % of the stall
+		 * samples on the two loads, profiles/r2_cfg1_full.md); B rows' chains are issued together here and
+		 * only rows that miss this fast test enter the probing loop. */
+		U v[B];
+		u64 gv[B], h[B], cur[B];
+		bool live[B], done[B];
+#pragma unroll
+		for (int j = 0; j < B; j++) {
+			const uint64_t r = r0 + (uint64_t) j * stride;
+			live[j] = r < src.n;
+			v[j] = live[j] ? KeyBits<T>::get(src.value(r)) : (U) 0;
+			gv[j] = (HASG && live[j]) ? src.gval(r) : 0;
+			h[j] = hash_key<U>(v[j], gv[j]) & mask;
+		}
+#pragma unroll
+		for (int j = 0; j < B; j++)
+			cur[j] = live[j] ? __ldcg(slots + h[j]) : GRP_EMPTY;
+#pragma unroll
+		for (int j = 0; j < B; j++) {
+			const uint64_t r = r0 + (uint64_t) j * stride;
+			done[j] = false;
+			if (live[j] && cur[j] != GRP_EMPTY && cur[j] <= r)
+				done[j] = cur[j] == r || (KeyBits<T>::get(src.value(cur[j])) == v[j] && (!HASG || src.gval(cur[j]) == gv[j]));
+		}
+#pragma unroll
+		for (int j = 0; j < B; j++) {
+			const uint64_t r = r0 + (uint64_t) j * stride;
+			if (!live[j])
+				continue;
+			u64 hh = h[j];
+			if (!done[j]) {
+				unsigned probes = 0;
+				for (;;) {
+					u64 c = __ldcg(slots + hh);
+					if (c == GRP_EMPTY) {
+						c = atomicCAS(slots + hh, GRP_EMPTY, (u64) r);
+						if (c == GRP_EMPTY) {
+							inserted++;
+							break;
+						}
+					}
+					if (c == r)
+						break;
+					if (KeyBits<T>::get(src.value(c)) == v[j] && (!HASG || src.gval(c) == gv[j])) {
+						if (r < c)
+							atomicMin(slots + hh, (u64) r);
+						break;
+					}
+					hh = (hh + 1) & mask;
+					if (++probes > 8192) {
+						state[0] = 1;	/* table too full: the host retries with a larger one */
+						break;
+					}
 				}
 			}
-			if (cur == r)
-				break;
-			if (KeyBits<T>::get(src.value(cur)) == v && (!HASG || src.gval(cur) == gv)) {
-				if (r < cur)
-					atomicMin(slots + h, (u64) r);
-				break;
-			}
-			h = (h + 1) & mask;
-			if (++probes > 8192) {
-				state[0] = 1;	/* table too full: the host retries with a larger one */
-				break;
-			}
+			slotof[r] = (uint32_t) hh;
 		}
-		slotof[r] = (uint32_t) h;
 	}
 	if (inserted)
 		atomicAdd(&sins, inserted);
@@ -337,8 +370,8 @@ grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint
 				g8out[r] = (unsigned char) g0;
 		}
 		if (cnts) {
-			if (SHISTO) {
-				/* warp-aggregated: one shared atomic per distinct id per warp */
+			if (SHISTO && ngrp <= 32) {
+				/* few groups: warp-aggregated, one shared atomic per distinct id per warp */
 				const unsigned act = __activemask();
 				unsigned m0 = __match_any_sync(act, g0);
 				if ((unsigned) (__ffs(m0) - 1) == (threadIdx.x & 31))
@@ -346,6 +379,12 @@ grp_assign_kernel(GrpSrc<T> src, const uint32_t *__restrict__ slotof, const uint
 				unsigned m1 = __match_any_sync(act, two ? g1 : 0xffffffffu);
 				if (two && (unsigned) (__ffs(m1) - 1) == (threadIdx.x & 31))
 					atomicAdd(&shist[g1], (unsigned) __popc(m1));
+			} else if (SHISTO) {
+				/* many groups: lanes rarely collide, and MATCH.ANY cost a third of this kernel's issue slots
+				 * at 500 groups (profiles/r2_cfg1_full.md) — plain shared-memory atomics */
+				atomicAdd(&shist[g0], 1u);
+				if (two)
+					atomicAdd(&shist[g1], 1u);
 			} else {
 				atomicAdd(cnts + g0, 1ULL);
 				if (two)
