@@ -162,8 +162,24 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 	__syncthreads();
 	unsigned inserted = 0;
 	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
+	/* keys of up to 4 bytes: a direct-mapped shared-memory cache key -> global slot (one 64-bit word per entry,
+	 * so an entry is always consistent).  A CTA meets its rows in ascending order, so once it has settled a key
+	 * in the global table every later row with that key only needs the slot number: a hit costs one
+	 * shared-memory load instead of two scattered global loads (the kernel was L1TEX-bound on those: 69 % of
+	 * the L1 pipe, 70 % excess sectors). */
+	constexpr bool CACHED = !HASG && sizeof(U) <= 4;
+	constexpr unsigned CSZ = 2048;
+	__shared__ unsigned long long kcache[CACHED ? CSZ : 1];
+	if constexpr (CACHED) {
+		for (unsigned i = threadIdx.x; i < CSZ; i += GRP_THREADS)
+			kcache[i] = 0;
+		__syncthreads();
+	}
 	constexpr int B = 4;		/* rows in flight per thread */
-	for (uint64_t r0 = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r0 < src.n; r0 += stride * B) {
+	/* the trip count is uniform over the CTA (barriers inside): rows of iteration i+1 are all larger than the
+	 * rows of iteration i of this CTA */
+	for (uint64_t rb = (uint64_t) blockIdx.x * GRP_THREADS; rb < src.n; rb += stride * B) {
+		const uint64_t r0 = rb + threadIdx.x;
 		/* The common case of a low-cardinality key — the slot at the key's home position already holds an
 		 * EARLIER row with the same key — needs three dependent loads (key, slot, key of the slot's row) and
 		 * no atomic.  One row at a time that chain left the kernel latency-bound (37 % + 27 % of the stall
@@ -179,6 +195,22 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 			v[j] = live[j] ? KeyBits<T>::get(src.value(r)) : (U) 0;
 			gv[j] = (HASG && live[j]) ? src.gval(r) : 0;
 			h[j] = hash_key<U>(v[j], gv[j]) & mask;
+		}
+		if constexpr (CACHED) {
+#pragma unroll
+			for (int j = 0; j < B; j++) {
+				if (!live[j])
+					continue;
+				const unsigned long long e = kcache[(unsigned) (h[j] >> 7) & (CSZ - 1)];
+				if ((e >> 32) != 0 && (uint32_t) e == (uint32_t) v[j]) {
+					slotof[r0 + (uint64_t) j * stride] = (uint32_t) (e >> 32) - 1;
+					live[j] = false;	/* settled from the cache */
+				}
+			}
+			/* entries read above were installed by EARLIER iterations, i.e. by smaller rows whose
+			 * global update is done; this iteration's installs must not be seen by this iteration's
+			 * lookups (a smaller row of the same iteration would skip its atomicMin) */
+			__syncthreads();
 		}
 #pragma unroll
 		for (int j = 0; j < B; j++)
@@ -222,7 +254,11 @@ grp_hash_first_kernel(GrpSrc<T> src, u64 *__restrict__ slots, u64 mask, uint32_t
 				}
 			}
 			slotof[r] = (uint32_t) hh;
+			if constexpr (CACHED)
+				kcache[(unsigned) (h[j] >> 7) & (CSZ - 1)] = (unsigned long long) (uint32_t) v[j] | ((unsigned long long) ((uint32_t) hh + 1) << 32);
 		}
+		if constexpr (CACHED)
+			__syncthreads();
 	}
 	if (inserted)
 		atomicAdd(&sins, inserted);
