@@ -658,7 +658,7 @@ def other_workload(args):
         n = max(blk, n // blk * blk)
         lo, hi = rank * n, (rank + 1) * n
         types = {"pkey": T.lng, "ord": T.lng, "val": T.lng}
-        dev = upload(lambda a, b: workload.window(a, b), types, lo, hi, chunk=blk * 400)
+        dev = upload(lambda a, b: workload.window_fast(a, b, threads=max(1, host_threads() // world)), types, lo, hi, chunk=blk * 400)
 
         def step():
             p = G.GDKanalyticaldiff(G.colnew(T.bit, n), dev["pkey"], None, None, T.lng)

@@ -125,3 +125,84 @@ int wl_lineitem(uint64_t lo, uint64_t hi, int nthreads, int nils, const int32_t 
 		pthread_join(th[t], NULL);
 	return 0;
 }
+
+/* ---- config 5: the window-analytics table (workload.py: window()).  Rows come in blocks of sum(lens) rows;
+ * block k holds one partition of each length in the order of permutation z(k) % 6, so blocks are independent
+ * and the threads take whole blocks.  pkey ascends, ord ascends inside a partition with duplicates
+ * (0 at the partition start, then + z % 3), val = z % 10000 - 5000. */
+enum { C_WPERM = 10, C_WORD = 11, C_WVAL = 12 };
+static const int wperms[6][3] = {{0, 1, 2}, {0, 2, 1}, {1, 0, 2}, {1, 2, 0}, {2, 0, 1}, {2, 1, 0}};
+
+struct wjob {
+	uint64_t b0, b1, lo, hi, blk;
+	uint64_t lens[3];
+	int64_t *pkey, *ord, *val;
+};
+
+static void *wrun(void *arg)
+{
+	struct wjob *j = (struct wjob *) arg;
+	for (uint64_t k = j->b0; k < j->b1; k++) {
+		const int *perm = wperms[smix(SEED(C_WPERM), k) % 6];
+		uint64_t row = k * j->blk;
+		for (int p = 0; p < 3; p++) {
+			const uint64_t len = j->lens[perm[p]];
+			int64_t o = 0;
+			for (uint64_t t = 0; t < len; t++, row++) {
+				if (row < j->lo || row >= j->hi)
+					continue;
+				const uint64_t i = row - j->lo;
+				if (t > 0)
+					o += (int64_t) (smix(SEED(C_WORD), row) % 3);
+				j->pkey[i] = (int64_t) (3 * k + (uint64_t) p);
+				j->ord[i] = o;
+				j->val[i] = (int64_t) (smix(SEED(C_WVAL), row) % 10000) - 5000;
+			}
+		}
+	}
+	return NULL;
+}
+
+int wl_window(uint64_t lo, uint64_t hi, int nthreads, uint64_t len0, uint64_t len1, uint64_t len2, int64_t *pkey, int64_t *ord,
+	      int64_t *val)
+{
+	const uint64_t blk = len0 + len1 + len2;
+	if (blk == 0 || lo % blk != 0)
+		return -1;
+	const uint64_t b0 = lo / blk, b1 = (hi + blk - 1) / blk, nb = b1 - b0;
+	if (nthreads < 1)
+		nthreads = 1;
+	if (nthreads > 256)
+		nthreads = 256;
+	if ((uint64_t) nthreads > nb)
+		nthreads = (int) (nb ? nb : 1);
+	pthread_t th[256];
+	struct wjob jobs[256];
+	int started = 0;
+	for (int t = 0; t < nthreads; t++) {
+		struct wjob *j = &jobs[t];
+		j->b0 = b0 + nb * (uint64_t) t / (uint64_t) nthreads;
+		j->b1 = b0 + nb * (uint64_t) (t + 1) / (uint64_t) nthreads;
+		j->lo = lo;
+		j->hi = hi;
+		j->blk = blk;
+		j->lens[0] = len0;
+		j->lens[1] = len1;
+		j->lens[2] = len2;
+		j->pkey = pkey;
+		j->ord = ord;
+		j->val = val;
+		if (t == nthreads - 1 || pthread_create(&th[t], NULL, wrun, j) != 0) {
+			if (t != nthreads - 1)
+				j->b1 = b1;
+			wrun(j);
+			if (t != nthreads - 1)
+				break;
+		} else {
+			started++;
+		}
+	}
+	for (int t = 0; t < started; t++)
+		pthread_join(th[t], NULL);
+	return 0;
+}

@@ -115,6 +115,8 @@ def _wl():
             from .build import build_workload
             build_workload()
         lib = C.CDLL(str(so))
+        lib.wl_window.restype = C.c_int
+        lib.wl_window.argtypes = [C.c_uint64, C.c_uint64, C.c_int] + [C.c_uint64] * 3 + [C.c_void_p] * 3
         lib.wl_lineitem.restype = C.c_int
         lib.wl_lineitem.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int32, C.c_int32] + \
             [C.c_void_p] * 7
@@ -189,3 +191,15 @@ def window(lo: int, hi: int, lens=(1000, 10000, 100000)) -> dict:
     ordv = c - c[pstart]
     val = (splitmix64(col_seed(C_WVAL), lo, hi) % np.uint64(10000)).astype(np.int64) - 5000
     return {"pkey": pkey, "ord": ordv, "val": val, "n": n}
+
+
+def window_fast(lo: int, hi: int, lens=(1000, 10000, 100000), threads: int | None = None) -> dict:
+    """window() through the threaded C generator (bit-identical; tests/test_cpu_shard.py checks it)"""
+    import os
+    n = hi - lo
+    out = {k: np.empty(n, dtype=np.int64) for k in ("pkey", "ord", "val")}
+    rc = _wl().wl_window(lo, hi, threads or min(64, os.cpu_count() or 1), *lens, out["pkey"].ctypes.data, out["ord"].ctypes.data,
+                         out["val"].ctypes.data)
+    assert rc == 0, "window shards must start on a block boundary"
+    out["n"] = n
+    return out

@@ -113,6 +113,11 @@ def test_shard_range_and_workload_generator():
         b = workload.lineitem_fast(777, 777 + 200_000, Q1_COLS, nils)
         for k in Q1_COLS:
             assert a[k].dtype == b[k].dtype and (a[k] == b[k]).all(), k
+    blk = 6100
+    for lo, hi in ((0, 3 * blk), (2 * blk, 5 * blk + 777)):
+        a, b = workload.window(lo, hi, lens=(100, 1000, 5000)), workload.window_fast(lo, hi, lens=(100, 1000, 5000))
+        for k in ("pkey", "ord", "val"):
+            assert (a[k] == b[k]).all(), k
     if True:
         z = workload.lineitem(0, 100_000, ("discount",), nils=True)["discount"]
         assert 0.005 < (z == np.iinfo(np.int64).min).mean() < 0.02
