@@ -326,6 +326,133 @@ extern "C" b200_return b200_comm_pack(int k, const b200_bat *const *in, b200_bat
 }
 
 // ---------------------------------------------------------------- exchange
+// receive arenas for the peer-memory exchange
+struct PeerArena {
+	cudaIpcMemHandle_t handle;
+	uint64_t gen = 0;
+	void *mapped = nullptr;
+};
+struct ArenaRec {		/* what every rank publishes per exchange */
+	uint64_t gen;
+	uint64_t bytes;
+	cudaIpcMemHandle_t handle;
+};
+static void *g_arena = nullptr;
+static size_t g_arena_bytes = 0;
+static uint64_t g_arena_gen = 0;
+static cudaIpcMemHandle_t g_arena_handle;
+static std::vector<PeerArena> g_peer;
+static bool g_p2p_ok = true;
+static unsigned long long *g_token = nullptr;	/* [1 + world] device words for the completion all-gather */
+static ArenaRec *g_rec_dev = nullptr;		/* [1 + world] */
+
+// make sure my arena holds `need` bytes, publish (gen, handle), open the peers' current arenas.
+// Collective: every rank calls it once per exchange.  false -> fall back to ncclSend/ncclRecv (all ranks agree,
+// because the decision is taken from the gathered records).
+static bool arena_exchange_handles(size_t need)
+{
+	Ctx *c = ctx();
+	const int W = g_world;
+	static bool env_checked = false;
+	if (!env_checked) {
+		env_checked = true;
+		const char *e = getenv("B200_EXCHANGE");
+		if (e && strcmp(e, "nccl") == 0)
+			g_p2p_ok = false;
+	}
+	if ((int) g_peer.size() != W)
+		g_peer.assign(W, PeerArena());
+	bool mine_ok = g_p2p_ok;
+	if (mine_ok && need > g_arena_bytes) {
+		cudaStreamSynchronize(c->stream);
+		if (g_arena)
+			cudaFree(g_arena);
+		g_arena = nullptr;
+		g_arena_bytes = 0;
+		size_t nb = need + need / 2;
+		nb = (nb + ((size_t) 2 << 20) - 1) & ~(((size_t) 2 << 20) - 1);
+		if (cudaMalloc(&g_arena, nb) != cudaSuccess || cudaIpcGetMemHandle(&g_arena_handle, g_arena) != cudaSuccess) {
+			cudaGetLastError();
+			if (g_arena)
+				cudaFree(g_arena);
+			g_arena = nullptr;
+			mine_ok = false;
+		} else {
+			g_arena_bytes = nb;
+			g_arena_gen++;
+		}
+	}
+	if (g_token == nullptr) {
+		if (cudaMalloc(&g_token, (size_t) (W + 1) * 8) != cudaSuccess || cudaMalloc(&g_rec_dev, (size_t) (W + 1) * sizeof(ArenaRec)) != cudaSuccess) {
+			cudaGetLastError();
+			g_p2p_ok = false;
+			return false;	/* every rank fails the same allocation pattern or the next gather disagrees; be safe: */
+		}
+		cudaMemsetAsync(g_token, 0, (size_t) (W + 1) * 8, c->stream);
+	}
+	ArenaRec mine;
+	memset(&mine, 0, sizeof(mine));
+	mine.gen = mine_ok ? g_arena_gen : 0;	/* gen 0 = "I cannot take part" */
+	mine.bytes = g_arena_bytes;
+	if (mine_ok)
+		mine.handle = g_arena_handle;
+	std::vector<ArenaRec> all(W);
+	if (!cuda_ok(cudaMemcpyAsync(g_rec_dev, &mine, sizeof(mine), cudaMemcpyHostToDevice, c->stream), "arena rec up") ||
+	    !NC(g_nccl.AllGather(g_rec_dev, g_rec_dev + 1, sizeof(ArenaRec), ncclUint8, g_comm, c->stream)) ||
+	    !cuda_ok(cudaMemcpyAsync(all.data(), g_rec_dev + 1, (size_t) W * sizeof(ArenaRec), cudaMemcpyDeviceToHost, c->stream), "arena rec down") ||
+	    !stream_sync())
+		return false;
+	bool everyone = true;
+	for (int r = 0; r < W; r++)
+		everyone &= all[r].gen != 0;
+	if (!everyone) {
+		g_p2p_ok = false;	/* the same verdict on every rank: the records are identical everywhere */
+		return false;
+	}
+	/* (re)open the arenas whose generation changed; every rank sees the same set of changes (seen[] is kept for
+	 * all ranks, this one included), so every rank takes the confirmation round below or none does */
+	static std::vector<uint64_t> seen;
+	if ((int) seen.size() != W)
+		seen.assign(W, 0);
+	bool anychange = false, opened = true;
+	for (int r = 0; r < W; r++) {
+		if (seen[r] == all[r].gen)
+			continue;
+		anychange = true;
+		seen[r] = all[r].gen;
+		if (r == g_rank)
+			continue;
+		if (g_peer[r].mapped)
+			cudaIpcCloseMemHandle(g_peer[r].mapped);
+		g_peer[r].mapped = nullptr;
+		if (cudaIpcOpenMemHandle(&g_peer[r].mapped, all[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+			cudaGetLastError();
+			g_peer[r].mapped = nullptr;
+			opened = false;
+		}
+	}
+	if (anychange) {
+		/* confirmation: one word per rank — did it map every peer?  Any failure switches EVERY rank to the NCCL
+		 * path for good, in this very call */
+		unsigned long long okw = opened ? 1 : 0;
+		std::vector<unsigned long long> oks(W);
+		if (!cuda_ok(cudaMemcpyAsync(g_token, &okw, 8, cudaMemcpyHostToDevice, c->stream), "confirm up") ||
+		    !NC(g_nccl.AllGather(g_token, g_token + 1, 1, ncclUint64, g_comm, c->stream)) ||
+		    !cuda_ok(cudaMemcpyAsync(oks.data(), g_token + 1, (size_t) W * 8, cudaMemcpyDeviceToHost, c->stream), "confirm down") ||
+		    !stream_sync())
+			return false;
+		for (int r = 0; r < W; r++)
+			if (oks[r] == 0)
+				g_p2p_ok = false;
+		if (!g_p2p_ok) {
+			for (int r = 0; r < W; r++)
+				seen[r] = 0;
+			return false;
+		}
+	}
+	return true;
+}
+
 extern "C" b200_return b200_comm_exchange(int k, const b200_bat *const *in, const uint64_t *send_counts, b200_bat **out,
 					  uint64_t *recv_counts)
 {
@@ -381,7 +508,67 @@ extern "C" b200_return b200_comm_exchange(int k, const b200_bat *const *in, cons
 		out[i] = bat_new(0, in[i]->ttype, total_recv);
 		ok = out[i] != nullptr;
 	}
-	if (ok) {
+	bool pushed = false;
+	if (ok && W > 1 && g_p2p_ok) {
+		/* ---- direct peer-memory exchange: every rank owns a receive arena (cudaMalloc, exported with CUDA IPC);
+		 * the senders WRITE their runs straight into the destination arenas over NVLink (copy engines, no
+		 * staging through NCCL's channel buffers — grouped ncclSend/ncclRecv moved these runs at 120 GB/s per GPU
+		 * on NV18 links), a token all-gather tells every rank that its arena is complete, and each rank copies
+		 * its arena into the result BATs.  Stream order protects the arena: a peer can only start the next
+		 * exchange after this rank has contributed to that exchange's count gather, which is queued behind the
+		 * copies out of the arena. */
+		size_t colbase[PACK_MAXBATS + 1];
+		auto layout = [&](uint64_t rows, size_t *base) {
+			size_t off = 0;
+			for (int i = 0; i < k; i++) {
+				base[i] = off;
+				off += ((size_t) rows * atomsize(in[i]->ttype) + 255) & ~(size_t) 255;
+			}
+			base[k] = off;
+		};
+		layout(total_recv, colbase);
+		pushed = arena_exchange_handles(colbase[k]);
+		if (pushed) {
+			uint64_t bytes = 0;
+			for (int i = 0; i < k; i++)
+				bytes += (total_send + total_recv) * atomsize(in[i]->ttype);
+			KTimer kt("comm_exchange", bytes);
+			for (int r = 0; r < W && ok; r++) {
+				if (r == g_rank)
+					continue;
+				uint64_t peer_total = 0, my_off = 0;
+				for (int q = 0; q < W; q++) {
+					peer_total += mat[(size_t) q * W + r];
+					if (q < g_rank)
+						my_off += mat[(size_t) q * W + r];
+				}
+				size_t pbase[PACK_MAXBATS + 1];
+				layout(peer_total, pbase);
+				for (int i = 0; i < k && ok; i++) {
+					const int w = atomsize(in[i]->ttype);
+					if (send_counts[r])
+						ok = cuda_ok(cudaMemcpyAsync((char *) g_peer[r].mapped + pbase[i] + my_off * w,
+									     (const char *) in[i]->base + soff[r] * w, send_counts[r] * w,
+									     cudaMemcpyDefault, c->stream), "exchange peer write");
+				}
+			}
+			/* completion token: after this collective every peer's writes into my arena have finished */
+			ok = ok && NC(g_nccl.AllGather(g_token, g_token + 1, 1, ncclUint64, g_comm, c->stream));
+			for (int i = 0; i < k && ok; i++) {
+				const int w = atomsize(in[i]->ttype);
+				for (int r = 0; r < W && ok; r++) {
+					const uint64_t nr = roff[r + 1] - roff[r];
+					if (nr == 0)
+						continue;
+					const char *src = r == g_rank ? (const char *) in[i]->base + soff[r] * w
+								      : (const char *) g_arena + colbase[i] + roff[r] * w;
+					ok = cuda_ok(cudaMemcpyAsync((char *) out[i]->base + roff[r] * w, src, nr * w, cudaMemcpyDeviceToDevice, c->stream),
+						     "exchange arena copy");
+				}
+			}
+		}
+	}
+	if (ok && !pushed) {
 		uint64_t bytes = 0;
 		for (int i = 0; i < k; i++)
 			bytes += (total_send + total_recv) * atomsize(in[i]->ttype);
@@ -415,7 +602,7 @@ extern "C" b200_return b200_comm_exchange(int k, const b200_bat *const *in, cons
 		}
 		return B200_FAIL;
 	}
-	ctx()->algo = W > 1 ? "exchange: nccl grouped send/recv" : "exchange: single rank";
+	ctx()->algo = W == 1 ? "exchange: single rank" : pushed ? "exchange: peer-memory writes over NVLink (CUDA IPC arenas)" : "exchange: nccl grouped send/recv";
 	for (int i = 0; i < k; i++) {
 		b200_bat *bn = out[i];
 		bn->count = total_recv;
