@@ -170,6 +170,13 @@ b200_bat *b200_BATcalcxorcst(const b200_bat *b, const void *v, int vtype, const 
 b200_bat *b200_BATcalccstand(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
 b200_bat *b200_BATcalccstor(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
 b200_bat *b200_BATcalccstxor(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+/* shifts: gdk_calc.c:3246 (BATcalclsh), 3305 (lshcst), 3356 (cstlsh), 3596-3770 (rsh forms); result type = left operand */
+b200_bat *b200_BATcalclsh(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalcrsh(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
+b200_bat *b200_BATcalclshcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalcrshcst(const b200_bat *b, const void *v, int vtype, const b200_bat *s);
+b200_bat *b200_BATcalccstlsh(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
+b200_bat *b200_BATcalccstrsh(const void *v, int vtype, const b200_bat *b, const b200_bat *s);
 b200_bat *b200_BATcalclt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcle(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);
 b200_bat *b200_BATcalcgt(const b200_bat *b1, const b200_bat *b2, const b200_bat *s1, const b200_bat *s2);

@@ -460,6 +460,25 @@ for _n in ("and", "or", "xor"):
     _sig(f"b200_BATcalccst{_n}", _P, C.c_void_p, C.c_int, _P, _P)
 
 
+for _n in ("lsh", "rsh"):
+    _sig(f"b200_BATcalc{_n}", _P, _P, _P, _P, _P)
+    _sig(f"b200_BATcalc{_n}cst", _P, _P, C.c_void_p, C.c_int, _P)
+    _sig(f"b200_BATcalccst{_n}", _P, C.c_void_p, C.c_int, _P, _P)
+
+
+def BATcalcshift(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
+    """BATcalclsh / BATcalcrsh (gdk_calc.c:3246, 3596); op = "lsh" | "rsh" """
+    return BAT(getattr(lib, f"b200_BATcalc{op}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))
+
+
+def BATcalcshiftcst(op: str, b: BAT, v, vtype: int, s: BAT | None = None, cst_first: bool = False) -> BAT:
+    """b OP v, or with cst_first v OP b (b holds the shift counts)"""
+    a = _valp(_storage(vtype), v)
+    if cst_first:
+        return BAT(getattr(lib, f"b200_BATcalccst{op}")(a[1], vtype, b._p, _ptr(s)))
+    return BAT(getattr(lib, f"b200_BATcalc{op}cst")(b._p, a[1], vtype, _ptr(s)))
+
+
 def BATcalclogic(op: str, b1: BAT, b2: BAT, s1: BAT | None = None, s2: BAT | None = None) -> BAT:
     """BATcalcand / or / xor (gdk_calc.h:51-58): three-valued on bit, bitwise on the integer atoms"""
     return BAT(getattr(lib, f"b200_BATcalc{op}")(b1._p, b2._p, _ptr(s1), _ptr(s2)))
