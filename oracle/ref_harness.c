@@ -279,6 +279,22 @@ refh_logic_cst(int op, BAT *b, const void *v, int vtype, BAT *s)
 	return bn;
 }
 
+/* op: 0 lsh 1 rsh; side 0: b OP v, side 1: v OP b (gdk_calc.c:3305,3356,3655,3706) */
+BAT *
+refh_shift_cst(int op, int side, BAT *b, const void *v, int vtype, BAT *s)
+{
+	ValRecord val;
+	if (VALinit(&val, vtype, v) == NULL)
+		return NULL;
+	BAT *bn = NULL;
+	if (op == 0)
+		bn = side == 0 ? BATcalclshcst(b, &val, s) : BATcalccstlsh(&val, b, s);
+	else
+		bn = side == 0 ? BATcalcrshcst(b, &val, s) : BATcalccstrsh(&val, b, s);
+	VALclear(&val);
+	return bn;
+}
+
 /* which: 0 min 1 min_no_nil 2 max 3 max_no_nil (gdk_calc.c:1403,1563,2086,2219) */
 BAT *
 refh_minmax_cst(int which, BAT *b, const void *v, int vtype, BAT *s)

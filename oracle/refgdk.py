@@ -122,6 +122,8 @@ def _load(nthreads: int = 0):
     _h.refh_cst_cmp.argtypes = [C.c_int, V, C.c_int, P, P, C.c_int]
     _h.refh_cmp_cst.restype = P
     _h.refh_cmp_cst.argtypes = [C.c_int, P, V, C.c_int, P, C.c_int]
+    _h.refh_shift_cst.restype = P
+    _h.refh_shift_cst.argtypes = [C.c_int, C.c_int, P, V, C.c_int, P]
     _h.refh_usec.restype = C.c_int64
     rc = _h.refh_init(nthreads)
     if rc != 0:
@@ -183,7 +185,7 @@ def _load(nthreads: int = 0):
     }
     for op in ("add", "sub", "mul", "div", "mod"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, C.c_int])
-    for op in ("lt", "le", "gt", "ge", "and", "or", "xor"):
+    for op in ("lt", "le", "gt", "ge", "and", "or", "xor", "lsh", "rsh"):
         sigs["BATcalc" + op] = (P, [P, P, P, P])
     for op in ("eq", "ne"):
         sigs["BATcalc" + op] = (P, [P, P, P, P, B])
@@ -418,6 +420,15 @@ def BATcalclogic(op, b1, b2, s1=None, s2=None) -> RBAT:
 def BATcalclogiccst(op, b, v, vtype, s=None) -> RBAT:
     a = _val(vtype, v)
     return RBAT(_h.refh_logic_cst({"and": 0, "or": 1, "xor": 2}[op], b.p, _vp(a), vtype, _p(s)), "BATcalc" + op + "cst")
+
+
+def BATcalcshift(op, b1, b2, s1=None, s2=None) -> RBAT:
+    return RBAT(getattr(_bat, "BATcalc" + op)(b1.p, b2.p, _p(s1), _p(s2)), "BATcalc" + op)
+
+
+def BATcalcshiftcst(op, b, v, vtype, s=None, cst_first=False) -> RBAT:
+    a = _val(vtype, v)
+    return RBAT(_h.refh_shift_cst(0 if op == "lsh" else 1, 1 if cst_first else 0, b.p, _vp(a), vtype, _p(s)), "BATcalc" + op + "cst")
 
 
 def BATcalcunary(which, b, s=None) -> RBAT:

@@ -349,3 +349,62 @@ def test_minmax_cst(gdk, ref, tt, which):
     other = T.int if tt != T.int else T.lng
     with pytest.raises(G.GDKError, match="inputs have incompatible types"):
         gdk.BATcalcminmaxcst(which, b, 1, other)
+
+
+# ---------------------------------------------------------------------------- shifts (gdk_calc.c:3246-3770)
+@pytest.mark.parametrize("op", ["lsh", "rsh"])
+@pytest.mark.parametrize("t1", [T.bte, T.sht, T.int, T.lng, T.hge])
+@pytest.mark.parametrize("t2", [T.bte, T.int, T.lng, T.hge])
+def test_shifts(gdk, ref, op, t1, t2):
+    """BATcalclsh / BATcalcrsh and the cst forms: result type = left operand, nil in nil out, the reference's
+    three check variants (SHIFT_CHECK, LSH_CHECK, none for hge << bte) and its error text"""
+    rng = np.random.default_rng(t1 * 11 + t2 + (op == "rsh"))
+    bits = {T.bte: 8, T.sht: 16, T.int: 32, T.lng: 64, T.hge: 128}[t1]
+    n = 20_003
+    # small non-negative left values and small counts: everything passes for lsh as well
+    a = random_col(rng, t1, n, nilfrac=0.05, lo=0, hi=3)
+    cnt = random_col(rng, t2, n, nilfrac=0.05, lo=0, hi=bits - 4)
+    b1, r1 = both(gdk, ref, a, t1)
+    b2, r2 = both(gdk, ref, cnt, t2)
+    assert_same(gdk.BATcalcshift(op, b1, b2), ref.BATcalcshift(op, r1, r2))
+    assert_same(gdk.BATcalcshiftcst(op, b1, 2, t2), ref.BATcalcshiftcst(op, r1, 2, t2))
+    assert_same(gdk.BATcalcshiftcst(op, b2, 1, t1, cst_first=True), ref.BATcalcshiftcst(op, r2, 1, t1, cst_first=True))
+    # right shifts of negative values are fine; left shifts of negative / too large values are refused (except
+    # where the reference checks only the count)
+    neg = random_col(rng, t1, n, nilfrac=0.05, lo=-100, hi=100)
+    bn, rn = both(gdk, ref, neg, t1)
+    small = random_col(rng, t2, n, nilfrac=0.0, lo=0, hi=2)
+    bs, rs = both(gdk, ref, small, t2)
+    for x, rx, y, ry in ((bn, rn, bs, rs), (b1, r1, b2, r2)):
+        try:
+            want, err = ref.BATcalcshift(op, rx, ry), None
+        except Exception as ex:     # noqa: BLE001
+            want, err = None, str(ex).strip()
+        if err is None:
+            assert_same(gdk.BATcalcshift(op, x, y), want)
+        else:
+            with pytest.raises(G.GDKError) as e1:
+                gdk.BATcalcshift(op, x, y)
+            assert str(e1.value).strip() == err
+    # a count beyond the width is refused with the reference's text (first failing row)
+    if not (op == "lsh" and t1 == T.hge and t2 == T.bte):
+        big = cnt.copy()
+        if t2 == T.hge:
+            big["lo"][777] = bits
+            big["hi"][777] = 0
+        else:
+            big[777] = min(bits, 127) if t2 == T.bte else bits
+        if not (t2 == T.bte and bits > 127):
+            bb, rb = both(gdk, ref, big, t2)
+            a2 = a.copy()
+            if t1 == T.hge:
+                a2["lo"][777], a2["hi"][777] = 1, 0
+            else:
+                a2[777] = 1
+            ba, ra = both(gdk, ref, a2, t1)
+            with pytest.raises(G.GDKError) as e1:
+                gdk.BATcalcshift(op, ba, bb)
+            with pytest.raises(Exception) as e2:
+                ref.BATcalcshift(op, ra, rb)
+            assert str(e1.value).strip() == str(e2.value).strip()
+            assert "shift operand too large" in str(e1.value)
