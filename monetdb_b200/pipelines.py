@@ -104,6 +104,7 @@ def q1_bytes(n, s):
 
 def q1_bytes_sharded(n, s):
     """the sharded plan's phase 1 (shard.q1_phase1): the three BATgroupavg passes (3 x (8+8)) are replaced by
-    one more BATgroupsum (l_discount: 8+8) and two more BATgroupcount (8 each); the projections of the extents
-    and phase 2 touch a handful of rows"""
-    return q1_bytes(n, s) - 3 * 16 * s + 16 * s + 2 * 8 * s
+    one more BATgroupsum (l_discount: 8+8); the counts of the non-nil values are BATgroup's histogram when the
+    columns hold no nils (the headline tables), three BATgroupcount (8 each) otherwise; the projections of the
+    extents and phase 2 touch a handful of rows"""
+    return q1_bytes(n, s) - 3 * 16 * s + 16 * s - 8 * s

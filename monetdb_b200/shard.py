@@ -106,7 +106,8 @@ def q1_phase1(X, cols, out=None):
     pipelines.q1_groups_and_calcs(X, cols, o)
     g, e, h = o["g"], o["e"], o["h"]
     gsum = lambda b: X.BATgroupsum(b, g, e, None, T_hge, True)
-    gcnt = lambda b: X.BATgroupcount(b, g, e, None, T_lng, True)
+    # count(col) on a column without nils is count(*): the histogram BATgroup already produced
+    gcnt = lambda b: h if b.props()["nonil"] else X.BATgroupcount(b, g, e, None, T_lng, True)
     table = [
         X.BATproject(e, o["rf"]), X.BATproject(e, o["ls"]), X.BATproject(e, o["cand"]), h,
         gsum(o["qty"]), gsum(o["price"]), gsum(o["dp"]), gsum(o["ch"]), gsum(o["disc"]),

@@ -548,3 +548,31 @@ def test_aggregates_on_range_and_groups_frames(gdk, ref, frame_type, tt):
                 assert np.array_equal(np.isnan(a), np.isnan(c)) and np.array_equal(a[~np.isnan(a)], c[~np.isnan(c)])
             else:
                 close(a, c, tt, True)
+
+
+def test_window_sum_overflow_deviation_is_pinned(gdk, ref):
+    """BASELINE.md §5 deviation 2, kept on record: with lng sums of 2^60-sized values a level-1 node of the
+    reference's segment tree (16 consecutive rows) overflows although no FRAME does (ROWS 1 PRECEDING .. CURRENT
+    ROW adds two values).  The reference fails the whole call; the device path returns the frame sums, which are
+    checked against exact integers here.  If either side changes, this test says so."""
+    n = 64
+    v = np.full(n, 1 << 60, dtype=np.int64)
+    pkey = np.zeros(n, dtype=np.int32)
+    p, rp = flags(gdk, ref, pkey, T.int)
+    b, rb = both(gdk, ref, v, T.lng)
+    o, ro = both(gdk, ref, np.arange(n, dtype=np.int64), T.lng)
+    s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, 1, T.lng, T.lng, 0, True, 0)
+    e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, 0, T.lng, T.lng, 0, False, 1)
+    rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, 1, T.lng, T.lng, 0, True, 0)
+    re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, 0, T.lng, T.lng, 0, False, 1)
+    with pytest.raises(Exception) as e2:
+        ref.GDKanalyticalsum(ref.colnew(T.lng, n), rp, None, rb, rs, re_, T.lng, T.lng, 0)
+    assert str(e2.value).strip() == "22003!overflow in calculation."
+    r = gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), p, None, b, s, e, T.lng, T.lng, 0)
+    want = np.array([1 << 60] + [1 << 61] * (n - 1), dtype=np.int64)
+    assert np.array_equal(r.numpy(), want)
+    # a frame that really overflows fails on both sides with the same text
+    s4 = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, 9, T.lng, T.lng, 0, True, 0)
+    with pytest.raises(G.GDKError) as e1:
+        gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), p, None, b, s4, e, T.lng, T.lng, 0)
+    assert str(e1.value).strip() == "22003!overflow in calculation."
