@@ -44,7 +44,8 @@ enum {
 	B200_void = 0, B200_msk = 1, B200_bit = 2, B200_bte = 3, B200_sht = 4,
 	B200_int = 5, B200_oid = 6, B200_ptr = 7, B200_flt = 8, B200_dbl = 9,
 	B200_lng = 10, B200_hge = 11, B200_date = 12, B200_daytime = 13,
-	B200_timestamp = 14
+	B200_timestamp = 14,
+	B200_str = 16		/* dictionary-encoded: fixed-width offsets (width in b200_bat.pad) + string heap in vheap */
 };
 
 typedef enum { B200_FAIL = 0, B200_SUCCEED = 1 } b200_return;	/* gdk.h:348-350 */
@@ -264,6 +265,15 @@ b200_return b200_BATsort(b200_bat **sorted, b200_bat **order, b200_bat **groups,
 			 const b200_bat *g, bool reverse, bool nilslast, bool stable);
 b200_return b200_BATfirstn(b200_bat **topn, b200_bat **gids, const b200_bat *b, const b200_bat *s, const b200_bat *g,
 			   uint64_t n, bool asc, bool nilslast, bool distinct);
+
+/* ---- dictionary strings: a str tail as GDK stores it — offsets of `width` bytes (1/2: minus
+ * GDK_VAROFFSET, gdk_atoms.h:370-377) into a heap of NUL-terminated strings, nil = "\200"; elim_doubles = the heap is
+ * duplicate-free (GDK_ELIMDOUBLES, gdk.h).  On such columns BATgroup (gdk_group.c:897-919), the (anti-)equality forms of
+ * BATselect / BATthetaselect (gdk_select.c:608-656) and BATproject (gdk_project.c:681-695) run on the device. ---- */
+b200_bat *b200_BATstrfromhost(const void *offsets, int width, uint64_t cnt, uint64_t hseq, const void *heap,
+			      uint64_t heapbytes, bool elim_doubles);
+int b200_BATstrheap_tohost(const b200_bat *b, void *dst);	/* nvheap bytes; the offsets come with b200_BATtohost */
+int b200_BATstrwidth(const b200_bat *b);
 
 /* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */
 b200_return b200_BAThash(const b200_bat *b);

@@ -2,9 +2,18 @@
 // driver that builds the per-partition segment trees and runs the frame kernel.
 #pragma once
 #include "analytic_tree.cuh"
+#include <type_traits>
 
 // ---- sum (gdk_analytic_func.c:1762-1796)
+// Ops whose add() can raise an error (a checked sum) set `checked`: their tree is then built up to the single root
+// node, as GDKrebuild_segment_tree does (gdk_analytic_func.c:34-45), so that a node no frame uses — the partial
+// last node of a level, the root — fails the call on exactly the inputs the reference fails on.  For all other
+// ops a level is only built when some frame can use it (>= 16 nodes below).
+template <typename Op, typename = void> struct op_checked : std::false_type {};
+template <typename Op> struct op_checked<Op, std::void_t<decltype(Op::checked)>> : std::integral_constant<bool, Op::checked> {};
+
 template <typename T1, typename T2> struct SumOp {
+	static constexpr bool checked = true;
 	typedef T1 In;
 	typedef T2 Node;
 	typedef T2 Acc;
@@ -405,7 +414,7 @@ static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long
 		const uint64_t maxlen = c->slot_h->v[0];
 		for (int level = 1; level < AN_MAXLEV; level++) {
 			const uint64_t below = (maxlen + ((uint64_t) 1 << (4 * (level - 1))) - 1) >> (4 * (level - 1));
-			if (below < AN_FANOUT)
+			if (op_checked<Op>::value ? below <= 1 : below < AN_FANOUT)
 				break;
 			const uint64_t nslots = (n >> (4 * level)) + S.cnt + 1;
 			tree.lev[level] = (typename Op::Node *) dev_alloc(nslots * sizeof(typename Op::Node));

@@ -408,6 +408,8 @@ extern "C" int b200_BATtohost(const b200_bat *b, void *dst)
 		return 0;
 	}
 	size_t bytes = b->ttype == B200_msk ? ((b->count + 31) / 32) * 4 : (size_t) b->count * atomsize(b->ttype);
+	if (b->ttype == B200_STR_TYPE)
+		bytes = (size_t) b->count * b->pad;	/* the offsets, in their stored width (str.cu) */
 	if (b->device < 0) {
 		memcpy(dst, b->base, bytes);
 		return 0;

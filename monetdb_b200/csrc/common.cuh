@@ -181,6 +181,14 @@ struct Staged {
 bool stage(const b200_bat *in, Staged &out);
 bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows);	/* zero-copy for sparse gathers */
 
+// ---------------------------------------------------------------- dictionary strings (str.cu)
+#define B200_STR_TYPE B200_str
+b200_bat *str_select_entry(const b200_bat *b, const b200_bat *s, const void *tl, const void *th, bool li, bool hi, bool anti,
+			   bool nil_matches);
+b200_bat *str_thetaselect_entry(const b200_bat *b, const b200_bat *s, const void *val, const char *op);
+bool str_as_offsets(const b200_bat *b, b200_bat &view, bool need_elim, const char *func);
+bool str_adopt_heap(b200_bat *bn, const b200_bat *src);
+
 // ---------------------------------------------------------------- candidates
 // canditer_init (gdk_cand.c:407-712) restated for the device: after clipping to
 // b's oid range a candidate list is either dense [seq, seq+ncand) or a device

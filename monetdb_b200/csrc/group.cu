@@ -830,6 +830,13 @@ extern "C" b200_return b200_BATgroup(b200_bat **groups, b200_bat **extents, b200
 		return B200_FAIL;
 	b = sb.b;
 	g = sg.b;
+	b200_bat strview;
+	if (b->ttype == B200_STR_TYPE) {
+		/* a duplicate-free string heap is grouped by offset, as the reference does (gdk_group.c:897-919) */
+		if (!str_as_offsets(b, strview, true, "BATgroup"))
+			return B200_FAIL;
+		b = &strview;
+	}
 	Cand ci;
 	if (!cand_init(ci, b, ss.b))
 		return B200_FAIL;

@@ -650,6 +650,8 @@ extern "C" void b200_BATfree(b200_bat *b)
 	if (b->parent != nullptr) {
 		if (heap_unshare(b->parent))
 			heap_release(b->parent, b->device);
+		if (b->ttype == B200_STR_TYPE && b->device >= 0)
+			heap_release(b->vheap, b->device);	/* a str view shares the offsets, its string heap is its own copy */
 	} else if (b->owns) {
 		if (b->device >= 0) {
 			if (b->base == nullptr || heap_owner_release(b->base))

@@ -226,6 +226,33 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 		set_err("BATproject: BAT required\n");
 		return nullptr;
 	}
+	if (r1->ttype == B200_STR_TYPE) {
+		/* gdk_project.c:681-695: gather the offsets, the result refers to the same strings */
+		if (r2 != nullptr || r1->device < 0) {
+			set_err("BATproject: str columns must be device-resident and single (no r2) on the device path\n");
+			return nullptr;
+		}
+		if (l->ttype != B200_void && l->ccand == B200_CAND_NONE && !l->tnonil) {
+			set_err("BATproject: nil oids into a str column are not on the device path\n");
+			return nullptr;
+		}
+		b200_bat view;
+		if (!str_as_offsets(r1, view, false, "BATproject"))
+			return nullptr;
+		b200_bat *bn = b200_BATproject2(l, &view, nullptr);
+		if (bn == nullptr)
+			return nullptr;
+		if (bn->ttype == B200_void || !str_adopt_heap(bn, r1)) {
+			b200_BATfree(bn);
+			if (b200_errbuf()[0] == 0)
+				set_err("BATproject: unexpected result shape for a str column\n");
+			return nullptr;
+		}
+		bn->tnonil = r1->tnonil;
+		bn->tnil = 0;
+		bn->tsorted = bn->trevsorted = bn->tkey = bn->count <= 1;
+		return bn;
+	}
 	Staged sl, s1, s2;
 	if (!stage(l, sl) || !stage_sparse(r1, s1, r2 == nullptr && l != nullptr ? l->count : UINT64_MAX) || !stage(r2, s2))
 		return nullptr;

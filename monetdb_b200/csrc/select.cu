@@ -545,6 +545,8 @@ extern "C" b200_bat *b200_BATselect(const b200_bat *b, const b200_bat *s, const 
 				    bool li, bool hi, bool anti, bool nil_matches)
 {
 	b200_clrerr();
+	if (b != nullptr && b->ttype == B200_STR_TYPE)
+		return str_select_entry(b, s, tl, th, li, hi, anti, nil_matches);
 	return select_impl(b, s, tl, th, li, hi, anti, nil_matches);
 }
 
@@ -556,6 +558,8 @@ extern "C" b200_bat *b200_BATthetaselect(const b200_bat *b, const b200_bat *s, c
 		set_err("BATthetaselect: BAT, value and operator required\n");
 		return nullptr;
 	}
+	if (b->ttype == B200_STR_TYPE)
+		return str_thetaselect_entry(b, s, val, op);
 	int t = basetype(b->ttype);
 	const void *nil = nilptr(t);
 	if (nil == nullptr) {

@@ -31,6 +31,7 @@ class GDKError(RuntimeError):
 # GDK type ids (gdk.h:429-451, HAVE_HGE build)
 class TYPE:
     void, msk, bit, bte, sht, int, oid, ptr, flt, dbl, lng, hge, date, daytime, timestamp = range(15)
+    str = 16
 
 
 oid_nil = 1 << 63
@@ -129,6 +130,9 @@ _sig("b200_BATsetprops", None, _P, C.c_bool, C.c_bool, C.c_bool, C.c_bool, C.c_b
 _sig("b200_BATtohost", C.c_int, _P, C.c_void_p)
 _sig("b200_BATfree", None, _P)
 _sig("b200_BATinvalidate", None, _P)
+_sig("b200_BATstrfromhost", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_bool)
+_sig("b200_BATstrheap_tohost", C.c_int, _P, C.c_void_p)
+_sig("b200_BATstrwidth", C.c_int, _P)
 _sig("b200_BATselect", _P, _P, _P, C.c_void_p, C.c_void_p, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
 _sig("b200_BATthetaselect", _P, _P, _P, C.c_void_p, C.c_char_p)
 for _n in ("b200_BATmergecand", "b200_BATintersectcand", "b200_BATdiffcand", "b200_BATproject"):
@@ -329,13 +333,64 @@ def _storage(tt: int) -> int:
 _OPS = {o: o.encode() for o in ("=", "==", "!=", "<>", "<", "<=", ">", ">=", "eq", "ne")}
 
 
+str_nil = b"\x80"
+GDK_VAROFFSET = 8192
+_STR_OFF = {1: np.dtype(np.uint8), 2: np.dtype(np.uint16), 4: np.dtype(np.uint32), 8: np.dtype(np.uint64)}
+
+
+def _cstr(v):
+    """a str atom as the NUL-terminated bytes GDK passes around (None stays NULL, nil is "\\200")"""
+    if v is None:
+        return None
+    return C.c_char_p(v if isinstance(v, bytes) else v.encode())
+
+
+def BATstrfromhost(offsets: np.ndarray, heap: bytes, hseq: int = 0, elim_doubles: bool = True) -> BAT:
+    """a str column as GDK stores it: the tail of offsets (uint8/16/32/64; the two narrow forms are stored
+    minus GDK_VAROFFSET) and the string heap (gdk_atoms.h:370-377)"""
+    offsets = np.ascontiguousarray(offsets)
+    if offsets.dtype not in _STR_OFF.values():
+        raise TypeError("offsets must be uint8 / uint16 / uint32 / uint64")
+    hb = (C.c_char * len(heap)).from_buffer_copy(heap)
+    return BAT(lib.b200_BATstrfromhost(offsets.ctypes.data_as(C.c_void_p), offsets.dtype.itemsize, len(offsets), hseq,
+                                       C.cast(hb, C.c_void_p), len(heap), elim_doubles))
+
+
+def str_parts(b: BAT):
+    """(offsets as stored, heap bytes) of a device str column"""
+    w = lib.b200_BATstrwidth(b._p)
+    if w not in _STR_OFF:
+        raise GDKError("not a str column")
+    off = np.empty(len(b), dtype=_STR_OFF[w])
+    if len(b) and lib.b200_BATtohost(b._p, off.ctypes.data_as(C.c_void_p)) != 0:
+        _fail("BATtohost")
+    heap = C.create_string_buffer(int(b.nvheap) + 1)
+    if lib.b200_BATstrheap_tohost(b._p, C.cast(heap, C.c_void_p)) != 0:
+        _fail("BATstrheap_tohost")
+    return off, heap.raw[:int(b.nvheap)]
+
+
+def str_decode(offsets: np.ndarray, heap: bytes) -> list:
+    """the strings a tail of offsets names (bytes; nil = b"\\x80")"""
+    add = GDK_VAROFFSET if offsets.dtype.itemsize <= 2 else 0
+    out = []
+    for o in offsets.tolist():
+        o += add
+        out.append(heap[o:heap.index(b"\0", o)])
+    return out
+
+
 def BATselect(b: BAT, s: BAT | None, tl, th, li: bool, hi: bool, anti: bool, nil_matches: bool = False) -> BAT:
+    if b.ttype == TYPE.str:
+        return BAT(lib.b200_BATselect(b._p, _ptr(s), _cstr(tl), _cstr(th), li, hi, anti, nil_matches))
     st = _storage(b.ttype)
     vl, vh = _valp(st, tl), _valp(st, th)
     return BAT(lib.b200_BATselect(b._p, _ptr(s), vl[1], vh[1], li, hi, anti, nil_matches))
 
 
 def BATthetaselect(b: BAT, s: BAT | None, val, op: str) -> BAT:
+    if b.ttype == TYPE.str:
+        return BAT(lib.b200_BATthetaselect(b._p, _ptr(s), _cstr(val), _OPS.get(op) or op.encode()))
     v = _valp(_storage(b.ttype), val)
     return BAT(lib.b200_BATthetaselect(b._p, _ptr(s), v[1], _OPS.get(op) or op.encode()))
 

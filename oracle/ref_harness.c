@@ -99,6 +99,39 @@ refh_bat_new(int type, uint64_t count, uint64_t hseq, const void *data,
 	return b;
 }
 
+/* a str BAT: `n` NUL-terminated strings packed back to back in `packed` ("\200" = nil), appended one by one so
+ * the heap, its duplicate elimination and the offset width are whatever GDK makes of them */
+BAT *
+refh_str_new(uint64_t hseq, uint64_t n, const char *packed)
+{
+	BAT *b = COLnew((oid) hseq, TYPE_str, (BUN) n, TRANSIENT);
+	if (b == NULL)
+		return NULL;
+	for (uint64_t i = 0; i < n; i++) {
+		if (BUNappend(b, packed, false) != GDK_SUCCEED) {
+			BBPreclaim(b);
+			return NULL;
+		}
+		packed += strlen(packed) + 1;
+	}
+	return b;
+}
+
+/* how GDK stores it: offset width, used bytes of the string heap, whether the heap is duplicate-free */
+void
+refh_str_parts(BAT *b, int *width, uint64_t *heapfree, int *elim)
+{
+	*width = b->twidth;
+	*heapfree = b->tvheap->free;
+	*elim = GDK_ELIMDOUBLES(b->tvheap);
+}
+
+void
+refh_str_heap(BAT *b, void *dst)
+{
+	memcpy(dst, b->tvheap->base, b->tvheap->free);
+}
+
 /* a msk BAT from uint32 words holding `nbits` bits */
 BAT *
 refh_msk_new(uint64_t hseq, uint64_t nbits, const uint32_t *words)

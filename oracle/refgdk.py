@@ -355,13 +355,52 @@ def BATunmask(b) -> RBAT:
     return RBAT(_bat.BATunmask(b.p), "BATunmask")
 
 
+STR = 16
+str_nil = b"\x80"
+_STR_OFF = {1: np.dtype(np.uint8), 2: np.dtype(np.uint16), 4: np.dtype(np.uint32), 8: np.dtype(np.uint64)}
+
+
+def strbat(values, hseq: int = 0) -> RBAT:
+    """a TYPE_str BAT built with BUNappend from bytes values (b"\\x80" = nil)"""
+    _load()
+    packed = b"".join(v + b"\0" for v in values)
+    _h.refh_str_new.restype = C.c_void_p
+    _h.refh_str_new.argtypes = [C.c_uint64, C.c_uint64, C.c_char_p]
+    return RBAT(_h.refh_str_new(hseq, len(values), packed), "strbat")
+
+
+def str_parts(b: RBAT):
+    """(offsets as stored, heap bytes, heap is duplicate-free) of a str BAT"""
+    w, free, elim = C.c_int(), C.c_uint64(), C.c_int()
+    _h.refh_str_parts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _h.refh_str_parts(b.p, C.byref(w), C.byref(free), C.byref(elim))
+    n = len(b)
+    off = np.empty(n, dtype=_STR_OFF[w.value])
+    if n:
+        _h.refh_tail(b.p, off.ctypes.data_as(C.c_void_p))
+    heap = C.create_string_buffer(free.value + 1)
+    _h.refh_str_heap.argtypes = [C.c_void_p, C.c_void_p]
+    _h.refh_str_heap(b.p, heap)
+    return off, heap.raw[:free.value], bool(elim.value)
+
+
+def str_values(b: RBAT) -> list:
+    off, heap, _ = str_parts(b)
+    add = 8192 if off.dtype.itemsize <= 2 else 0
+    return [heap[o + add:heap.index(b"\0", o + add)] for o in off.tolist()]
+
+
 def BATselect(b, s, tl, th, li, hi, anti, nil_matches=False) -> RBAT:
     tt = b.info().type
+    if tt == STR:
+        return RBAT(_bat.BATselect(b.p, _p(s), tl, th, li, hi, anti, nil_matches), "BATselect")
     vl, vh = _val(tt, tl), _val(tt, th)
     return RBAT(_bat.BATselect(b.p, _p(s), _vp(vl), _vp(vh), li, hi, anti, nil_matches), "BATselect")
 
 
 def BATthetaselect(b, s, val, op) -> RBAT:
+    if b.info().type == STR:
+        return RBAT(_bat.BATthetaselect(b.p, _p(s), val, op.encode()), "BATthetaselect")
     v = _val(b.info().type, val)
     return RBAT(_bat.BATthetaselect(b.p, _p(s), _vp(v), op.encode()), "BATthetaselect")
 

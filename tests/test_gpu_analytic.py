@@ -550,11 +550,12 @@ def test_aggregates_on_range_and_groups_frames(gdk, ref, frame_type, tt):
                 close(a, c, tt, True)
 
 
-def test_window_sum_overflow_deviation_is_pinned(gdk, ref):
-    """BASELINE.md §5 deviation 2, kept on record: with lng sums of 2^60-sized values a level-1 node of the
-    reference's segment tree (16 consecutive rows) overflows although no FRAME does (ROWS 1 PRECEDING .. CURRENT
-    ROW adds two values).  The reference fails the whole call; the device path returns the frame sums, which are
-    checked against exact integers here.  If either side changes, this test says so."""
+def test_window_sum_node_overflow_matches_reference(gdk, ref):
+    """With lng sums of 2^60-sized values a level-1 node of the fan-out-16 segment tree (16 consecutive rows)
+    overflows although no FRAME does (ROWS 1 PRECEDING .. CURRENT ROW adds two values).  The reference fails the
+    whole call (gdk_analytic_func.c:1762-1796 builds every node with ADD_WITH_CHECK); the device path builds the
+    same nodes with the same check and must fail with the same text — an earlier note in BASELINE.md §5 claimed a
+    deviation here; this test is what settled that there is none."""
     n = 64
     v = np.full(n, 1 << 60, dtype=np.int64)
     pkey = np.zeros(n, dtype=np.int32)
@@ -567,12 +568,27 @@ def test_window_sum_overflow_deviation_is_pinned(gdk, ref):
     re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, 0, T.lng, T.lng, 0, False, 1)
     with pytest.raises(Exception) as e2:
         ref.GDKanalyticalsum(ref.colnew(T.lng, n), rp, None, rb, rs, re_, T.lng, T.lng, 0)
-    assert str(e2.value).strip() == "22003!overflow in calculation."
-    r = gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), p, None, b, s, e, T.lng, T.lng, 0)
-    want = np.array([1 << 60] + [1 << 61] * (n - 1), dtype=np.int64)
-    assert np.array_equal(r.numpy(), want)
-    # a frame that really overflows fails on both sides with the same text
-    s4 = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, 9, T.lng, T.lng, 0, True, 0)
     with pytest.raises(G.GDKError) as e1:
-        gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), p, None, b, s4, e, T.lng, T.lng, 0)
-    assert str(e1.value).strip() == "22003!overflow in calculation."
+        gdk.GDKanalyticalsum(gdk.colnew(T.lng, n), p, None, b, s, e, T.lng, T.lng, 0)
+    assert str(e1.value).strip() == str(e2.value).strip() == "22003!overflow in calculation."
+    # partial nodes count too: the reference builds every level up to a single root (GDKrebuild_segment_tree,
+    # gdk_analytic_func.c:34-45), so 15 rows make ONE level-1 node of 15 values that overflows; 7 rows do not
+    for m, fails in ((15, True), (7, False), (17, True)):
+        b, rb = both(gdk, ref, v[:m], T.lng)
+        p, rp = flags(gdk, ref, pkey[:m], T.int)
+        o, ro = both(gdk, ref, np.arange(m, dtype=np.int64), T.lng)
+        s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, m), o, p, None, 1, T.lng, T.lng, 0, True, 0)
+        e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, m), o, p, None, 0, T.lng, T.lng, 0, False, 1)
+        rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, m), ro, rp, None, 1, T.lng, T.lng, 0, True, 0)
+        re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, m), ro, rp, None, 0, T.lng, T.lng, 0, False, 1)
+        if fails:
+            with pytest.raises(Exception) as e2:
+                ref.GDKanalyticalsum(ref.colnew(T.lng, m), rp, None, rb, rs, re_, T.lng, T.lng, 0)
+            with pytest.raises(G.GDKError) as e1:
+                gdk.GDKanalyticalsum(gdk.colnew(T.lng, m), p, None, b, s, e, T.lng, T.lng, 0)
+            assert str(e1.value).strip() == str(e2.value).strip() == "22003!overflow in calculation."
+        else:
+            want = ref.GDKanalyticalsum(ref.colnew(T.lng, m), rp, None, rb, rs, re_, T.lng, T.lng, 0).numpy()
+            r = gdk.GDKanalyticalsum(gdk.colnew(T.lng, m), p, None, b, s, e, T.lng, T.lng, 0)
+            assert np.array_equal(r.numpy(), want)
+            assert want.tolist() == [1 << 60] + [1 << 61] * (m - 1)
