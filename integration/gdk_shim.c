@@ -314,6 +314,32 @@ in_open(inarg *a, BAT *b)
 	return true;
 }
 
+/* dictionary strings: a str tail travels as GDK stores it — offsets + string heap.  Only
+ * b of BATselect / BATthetaselect (equality forms) and BATgroup (duplicate-free heap) may be one. */
+static bool
+str_ok(BAT *b)
+{
+	return b != NULL && b->ttype == TYPE_str && b->tvheap != NULL && b->tvheap->base != NULL;
+}
+
+static bool
+in_open_str(inarg *a, BAT *b)
+{
+	memset(a, 0, sizeof(*a));
+	a->bi = bat_iterator(b);
+	a->iter = true;
+	a->d = b200_BATstrfromhost(a->bi.base, a->bi.width, a->bi.count, b->hseqbase, a->bi.vh->base, a->bi.vhfree,
+				   a->bi.vhfree < GDK_ELIMLIMIT);
+	n_staged++;
+	return a->d != NULL;
+}
+
+static inline bool
+in_open_any(inarg *a, BAT *b)
+{
+	return str_ok(b) ? in_open_str(a, b) : in_open(a, b);
+}
+
 static void
 in_close(inarg *a)
 {
@@ -442,11 +468,12 @@ static BAT *(*real_BATthetaselect)(BAT *, BAT *, const void *, const char *);
 BAT *
 BATselect(BAT *b, BAT *s, const void *tl, const void *th, bool li, bool hi, bool anti, bool nil_matches)
 {
-	if (b == NULL || !bat_ok(b) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))
+	const bool strsel = str_ok(b) && tl != NULL && li && hi && (th == NULL || strcmp((const char *) tl, (const char *) th) == 0);
+	if (b == NULL || !(strsel || bat_ok(b)) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(BATselect, b, s, tl, th, li, hi, anti, nil_matches);
-	inarg ab, as;
+	inarg ab = {0}, as = {0};
 	BAT *bn = NULL;
-	if (in_open(&ab, b) && in_open(&as, s)) {
+	if (in_open_any(&ab, b) && in_open(&as, s)) {
 		b200_bat *r = b200_BATselect(ab.d, as.d, tl, th, li, hi, anti, nil_matches);
 		bn = r ? out_bat(r) : fail(__func__);
 		n_device++;
@@ -460,11 +487,14 @@ BATselect(BAT *b, BAT *s, const void *tl, const void *th, bool li, bool hi, bool
 BAT *
 BATthetaselect(BAT *b, BAT *s, const void *val, const char *op)
 {
-	if (b == NULL || !bat_ok(b) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))
+	const bool strsel = str_ok(b) && val != NULL && op != NULL &&
+		(strcmp(op, "=") == 0 || strcmp(op, "==") == 0 || strcmp(op, "!=") == 0 || strcmp(op, "<>") == 0 ||
+		 strcmp(op, "eq") == 0 || strcmp(op, "ne") == 0);
+	if (b == NULL || !(strsel || bat_ok(b)) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(BATthetaselect, b, s, val, op);
-	inarg ab, as;
+	inarg ab = {0}, as = {0};
 	BAT *bn = NULL;
-	if (in_open(&ab, b) && in_open(&as, s)) {
+	if (in_open_any(&ab, b) && in_open(&as, s)) {
 		b200_bat *r = b200_BATthetaselect(ab.d, as.d, val, op);
 		bn = r ? out_bat(r) : fail(__func__);
 		n_device++;
@@ -486,7 +516,7 @@ BATproject2(BAT *restrict l, BAT *restrict r1, BAT *restrict r2)
 	if (l == NULL || r1 == NULL || !bat_ok(l) || !bat_ok(r1) || !bat_ok(r2) || BATtdense(l) || l->ttype == TYPE_void ||
 	    r1->ttype == TYPE_void || (r2 && r2->ttype == TYPE_void) || !enter(BATcount(l)))
 		FORWARD(BATproject2, l, r1, r2);
-	inarg al, a1, a2;
+	inarg al = {0}, a1 = {0}, a2 = {0};
 	BAT *bn = NULL;
 	if (in_open(&al, l) && in_open(&a1, r1) && in_open(&a2, r2)) {
 		b200_bat *r = b200_BATproject2(al.d, a1.d, a2.d);
@@ -512,10 +542,11 @@ static gdk_return (*real_BATgroup)(BAT **, BAT **, BAT **, BAT *, BAT *, BAT *, 
 gdk_return
 BATgroup(BAT **groups, BAT **extents, BAT **histo, BAT *b, BAT *s, BAT *g, BAT *e, BAT *h)
 {
-	if (b == NULL || groups == NULL || !bat_ok(b) || !bat_ok(s) || !bat_ok(g) || !bat_ok(e) || !bat_ok(h) ||
+	const bool strgrp = str_ok(b) && b->tvheap->free < GDK_ELIMLIMIT;	/* grouped by offset, gdk_group.c:897-919 */
+	if (b == NULL || groups == NULL || !(strgrp || bat_ok(b)) || !bat_ok(s) || !bat_ok(g) || !bat_ok(e) || !bat_ok(h) ||
 	    b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(BATgroup, groups, extents, histo, b, s, g, e, h);
-	inarg ab, as, ag, ae, ah;
+	inarg ab = {0}, as = {0}, ag = {0}, ae = {0}, ah = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *rg = NULL, *re = NULL, *rh = NULL;
 	*groups = NULL;
@@ -523,7 +554,7 @@ BATgroup(BAT **groups, BAT **extents, BAT **histo, BAT *b, BAT *s, BAT *g, BAT *
 		*extents = NULL;
 	if (histo)
 		*histo = NULL;
-	if (in_open(&ab, b) && in_open(&as, s) && in_open(&ag, g) && in_open(&ae, e) && in_open(&ah, h)) {
+	if (in_open_any(&ab, b) && in_open(&as, s) && in_open(&ag, g) && in_open(&ae, e) && in_open(&ah, h)) {
 		n_device++;
 		if (b200_BATgroup(&rg, extents ? &re : NULL, histo ? &rh : NULL, ab.d, as.d, ag.d, ae.d, ah.d) == B200_SUCCEED) {
 			*groups = out_bat(rg);
@@ -566,7 +597,7 @@ NAME(BAT *b, BAT *g, BAT *e, BAT *s, int tp, bool skip_nils)						\
 	if (b == NULL || g == NULL || !bat_ok(b) || !bat_ok(g) || !bat_ok(e) || !bat_ok(s) || !type_ok(tp) ||	\
 	    b->ttype == TYPE_void || !enter(BATcount(b)))							\
 		FORWARD(NAME, b, g, e, s, tp, skip_nils);						\
-	inarg ab, ag, ae, as;										\
+	inarg ab = {0}, ag = {0}, ae = {0}, as = {0};										\
 	BAT *bn = NULL;											\
 	if (in_open(&ab, b) && in_open(&ag, g) && in_open(&ae, e) && in_open(&as, s)) {			\
 		b200_bat *r = b200_##NAME(ab.d, ag.d, ae.d, as.d, tp, skip_nils);			\
@@ -593,7 +624,7 @@ BATgroupavg(BAT **bnp, BAT **cntsp, BAT *b, BAT *g, BAT *e, BAT *s, int tp, bool
 	if (b == NULL || g == NULL || bnp == NULL || !bat_ok(b) || !bat_ok(g) || !bat_ok(e) || !bat_ok(s) || tp != TYPE_dbl ||
 	    b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(BATgroupavg, bnp, cntsp, b, g, e, s, tp, skip_nils, scale);
-	inarg ab, ag, ae, as;
+	inarg ab = {0}, ag = {0}, ae = {0}, as = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *ra = NULL, *rc_ = NULL;
 	*bnp = NULL;
@@ -633,7 +664,7 @@ BATsum(void *res, int tp, BAT *b, BAT *s, bool skip_nils, bool nil_if_empty)
 {
 	if (b == NULL || res == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(tp) || b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(BATsum, res, tp, b, s, skip_nils, nil_if_empty);
-	inarg ab, as;
+	inarg ab = {0}, as = {0};
 	gdk_return rc = GDK_FAIL;
 	if (in_open(&ab, b) && in_open(&as, s)) {
 		n_device++;
@@ -657,7 +688,7 @@ BATcalc##OP(BAT *b1, BAT *b2, BAT *s1, BAT *s2, int tp)							\
 	if (b1 == NULL || b2 == NULL || !bat_ok(b1) || !bat_ok(b2) || !bat_ok(s1) || !bat_ok(s2) || !type_ok(tp) ||	\
 	    b1->ttype == TYPE_void || b2->ttype == TYPE_void || !enter(BATcount(b1)))				\
 		FORWARD(BATcalc##OP, b1, b2, s1, s2, tp);						\
-	inarg a1, a2, c1, c2;										\
+	inarg a1 = {0}, a2 = {0}, c1 = {0}, c2 = {0};										\
 	BAT *bn = NULL;											\
 	if (in_open(&a1, b1) && in_open(&a2, b2) && in_open(&c1, s1) && in_open(&c2, s2)) {		\
 		b200_bat *r = b200_BATcalc##OP(a1.d, a2.d, c1.d, c2.d, tp);				\
@@ -678,7 +709,7 @@ BATcalc##OP##cst(BAT *b, const ValRecord *v, BAT *s, int tp)						\
 	if (b == NULL || v == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(tp) || !type_ok(v->vtype) ||	\
 	    v->vtype == TYPE_void || b->ttype == TYPE_void || !enter(BATcount(b)))				\
 		FORWARD(BATcalc##OP##cst, b, v, s, tp);							\
-	inarg ab, as;											\
+	inarg ab = {0}, as = {0};											\
 	BAT *bn = NULL;											\
 	if (in_open(&ab, b) && in_open(&as, s)) {							\
 		b200_bat *r = b200_BATcalc##OP##cst(ab.d, VALptr(v), v->vtype, as.d, tp);		\
@@ -697,7 +728,7 @@ BATcalccst##OP(const ValRecord *v, BAT *b, BAT *s, int tp)						\
 	if (b == NULL || v == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(tp) || !type_ok(v->vtype) ||	\
 	    v->vtype == TYPE_void || b->ttype == TYPE_void || !enter(BATcount(b)))				\
 		FORWARD(BATcalccst##OP, v, b, s, tp);							\
-	inarg ab, as;											\
+	inarg ab = {0}, as = {0};											\
 	BAT *bn = NULL;											\
 	if (in_open(&ab, b) && in_open(&as, s)) {							\
 		b200_bat *r = b200_BATcalccst##OP(VALptr(v), v->vtype, ab.d, as.d, tp);			\
@@ -722,7 +753,7 @@ BATcalc##OP(BAT *b1, BAT *b2, BAT *s1, BAT *s2 EXTRA_DECL)						\
 	if (b1 == NULL || b2 == NULL || !bat_ok(b1) || !bat_ok(b2) || !bat_ok(s1) || !bat_ok(s2) ||	\
 	    b1->ttype == TYPE_void || b2->ttype == TYPE_void || !enter(BATcount(b1)))				\
 		FORWARD(BATcalc##OP, b1, b2, s1, s2 EXTRA_ARG);						\
-	inarg a1, a2, c1, c2;										\
+	inarg a1 = {0}, a2 = {0}, c1 = {0}, c2 = {0};										\
 	BAT *bn = NULL;											\
 	if (in_open(&a1, b1) && in_open(&a2, b2) && in_open(&c1, s1) && in_open(&c2, s2)) {		\
 		b200_bat *r = b200_BATcalc##OP(a1.d, a2.d, c1.d, c2.d EXTRA_ARG);			\
@@ -743,7 +774,7 @@ BATcalc##OP##cst(BAT *b, const ValRecord *v, BAT *s EXTRA_DECL)						\
 	if (b == NULL || v == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(v->vtype) || v->vtype == TYPE_void ||	\
 	    b->ttype == TYPE_void || !enter(BATcount(b)))							\
 		FORWARD(BATcalc##OP##cst, b, v, s EXTRA_ARG);						\
-	inarg ab, as;											\
+	inarg ab = {0}, as = {0};											\
 	BAT *bn = NULL;											\
 	if (in_open(&ab, b) && in_open(&as, s)) {							\
 		b200_bat *r = b200_BATcalc##OP##cst(ab.d, VALptr(v), v->vtype, as.d EXTRA_ARG);		\
@@ -774,7 +805,7 @@ BATjoin(BAT **r1p, BAT **r2p, BAT *l, BAT *r, BAT *sl, BAT *sr, bool nil_matches
 	if (l == NULL || r == NULL || r1p == NULL || !bat_ok(l) || !bat_ok(r) || !bat_ok(sl) || !bat_ok(sr) ||
 	    l->ttype == TYPE_void || r->ttype == TYPE_void || !enter(BATcount(l) + BATcount(r)))
 		FORWARD(BATjoin, r1p, r2p, l, r, sl, sr, nil_matches, estimate);
-	inarg al, ar, asl, asr;
+	inarg al = {0}, ar = {0}, asl = {0}, asr = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *o1 = NULL, *o2 = NULL;
 	*r1p = NULL;
@@ -834,7 +865,7 @@ GDKanalyticaldiff(BAT *r, BAT *b, BAT *p, const bit *restrict npbit, int tpe)
 {
 	if (r == NULL || b == NULL || !bat_ok(b) || !bat_ok(p) || !type_ok(tpe) || b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(GDKanalyticaldiff, r, b, p, npbit, tpe);
-	inarg ab, ap;
+	inarg ab = {0}, ap = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *dr = b200_COLnew(r->hseqbase, TYPE_bit, BATcount(b));
 	if (dr && in_open(&ab, b) && in_open(&ap, p)) {
@@ -861,7 +892,7 @@ GDKanalyticalwindowbounds(BAT *r, BAT *b, BAT *p, BAT *l, const void *restrict b
 	BAT *any = b ? b : p ? p : l;
 	if (r == NULL || any == NULL || !bat_ok(b) || !bat_ok(p) || !bat_ok(l) || !enter(BATcount(any)))
 		FORWARD(GDKanalyticalwindowbounds, r, b, p, l, bound, tp1, tp2, unit, preceding, first_half);
-	inarg ab, ap, al;
+	inarg ab = {0}, ap = {0}, al = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *dr = b200_COLnew(r->hseqbase, TYPE_oid, BATcount(any));
 	if (dr && in_open(&ab, b) && in_open(&ap, p) && in_open(&al, l)) {
@@ -888,7 +919,7 @@ GDKanalyticalsum(BAT *r, BAT *p, BAT *o, BAT *b, BAT *s, BAT *e, int tp1, int tp
 	if (r == NULL || b == NULL || !bat_ok(b) || !bat_ok(p) || !bat_ok(o) || !bat_ok(s) || !bat_ok(e) || !type_ok(tp2) ||
 	    b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(GDKanalyticalsum, r, p, o, b, s, e, tp1, tp2, frame_type);
-	inarg ab, ap, ao, as, ae;
+	inarg ab = {0}, ap = {0}, ao = {0}, as = {0}, ae = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *dr = b200_COLnew(r->hseqbase, tp2, BATcount(b));
 	if (dr && in_open(&ap, p) && in_open(&ao, o) && in_open(&ab, b) && in_open(&as, s) && in_open(&ae, e)) {
@@ -917,7 +948,7 @@ NAME(BAT *r, BAT *p, BAT *o, BAT *b, BAT *s, BAT *e, int tpe, int frame_type)			
 	if (r == NULL || b == NULL || !bat_ok(b) || !bat_ok(p) || !bat_ok(o) || !bat_ok(s) || !bat_ok(e) ||	\
 	    !type_ok(tpe) || b->ttype == TYPE_void || !enter(BATcount(b)))					\
 		FORWARD(NAME, r, p, o, b, s, e, tpe, frame_type);					\
-	inarg ab, ap, ao, as, ae;									\
+	inarg ab = {0}, ap = {0}, ao = {0}, as = {0}, ae = {0};									\
 	gdk_return rc = GDK_FAIL;									\
 	b200_bat *dr = b200_COLnew(r->hseqbase, (RTYPE), BATcount(b));					\
 	if (dr && in_open(&ap, p) && in_open(&ao, o) && in_open(&ab, b) && in_open(&as, s) && in_open(&ae, e)) {	\
@@ -950,7 +981,7 @@ GDKanalyticalcount(BAT *r, BAT *p, BAT *o, BAT *b, BAT *s, BAT *e, bit ignore_ni
 	if (r == NULL || b == NULL || !bat_ok(b) || !bat_ok(p) || !bat_ok(o) || !bat_ok(s) || !bat_ok(e) || !type_ok(tpe) ||
 	    b->ttype == TYPE_void || !enter(BATcount(b)))
 		FORWARD(GDKanalyticalcount, r, p, o, b, s, e, ignore_nils, tpe, frame_type);
-	inarg ab, ap, ao, as, ae;
+	inarg ab = {0}, ap = {0}, ao = {0}, as = {0}, ae = {0};
 	gdk_return rc = GDK_FAIL;
 	b200_bat *dr = b200_COLnew(r->hseqbase, TYPE_lng, BATcount(b));
 	if (dr && in_open(&ap, p) && in_open(&ao, o) && in_open(&ab, b) && in_open(&as, s) && in_open(&ae, e)) {

@@ -81,6 +81,17 @@ def main():
     ws = R.GDKanalyticalsum(R.colnew(T.hge, m), p, None, vl, s, e, T.lng, T.hge, 0)
     wa = R.GDKanalyticalfn("avg", R.colnew(T.dbl, m), p, None, vl, s, e, T.lng, 0)
     out["window"] = {"p": dump(p), "s": dump(s), "e": dump(e), "sum": dump(ws), "avg": dump(wa)}
+    # ---- dictionary strings: GROUP BY two str flags + equality selects on a str column created by the real GDK
+    rng = np.random.default_rng(11)
+    ns = min(n, 200_000)
+    flags = [b"A", b"N", b"R", b"\x80"]
+    rf = R.strbat([flags[i] for i in rng.integers(0, 4, ns)])
+    ls = R.strbat([(b"F", b"O")[i] for i in rng.integers(0, 2, ns)])
+    g, e, hh = R.BATgroup(rf)
+    g, e, hh = R.BATgroup(ls, None, g, e, hh)
+    sel = {op + ":" + v.decode("latin1"): dump(R.BATthetaselect(rf, None, v, op))
+           for op in ("==", "!=", "eq", "ne") for v in (b"N", b"\x80", b"zz")}
+    out["str"] = {"g": dump(g), "e": dump(e), "h": dump(hh), "sel": sel}
     try:
         out["shim_stats"] = list(R.shim_stats())
     except AttributeError:

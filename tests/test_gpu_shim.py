@@ -44,6 +44,9 @@ def test_shim_is_a_drop_in(ref, gdk):
         for name, d in plain[k].items():
             assert shim[k][name] == d, (k, name, d, shim[k][name])
     assert shim["q6"] == plain["q6"]
+    # dictionary strings: BATgroup on str flags, (anti-)equality selects incl. the nil forms
+    assert shim["str"] == plain["str"], (shim["str"], plain["str"])
+    assert dev >= 54, shim["shim_stats"]           # 40 + the two str BATgroup calls and the 12 str selects
     assert shim["join"] == plain["join"]
     assert shim["errors"] == plain["errors"], (shim["errors"], plain["errors"])
     assert "overflow" in plain["errors"]["mul_overflow"] and "division by zero" in plain["errors"]["div_zero"]
