@@ -209,6 +209,9 @@ b200_return b200_BATgroup(b200_bat **groups, b200_bat **extents, b200_bat **hist
 /* ---- grouped / scalar aggregates: gdk_aggr.c:900,1018,1801,3069,3561,3720 ---- */
 b200_bat *b200_BATgroupsum(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+/* gdk_aggr.c:1575 — products in row order with the reference's overflow verdict ("22003!overflow in product aggregate.");
+ * integer results by an exact order-independent form, flt/dbl results by an ordered replay per group */
+b200_bat *b200_BATgroupprod(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_bat *b200_BATgroupmin(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_bat *b200_BATgroupmax(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const b200_bat *b, const b200_bat *g,

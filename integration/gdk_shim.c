@@ -612,6 +612,7 @@ NAME(BAT *b, BAT *g, BAT *e, BAT *s, int tp, bool skip_nils)						\
 	return bn;											\
 }
 GROUPAGGR(BATgroupsum)
+GROUPAGGR(BATgroupprod)
 GROUPAGGR(BATgroupcount)
 GROUPAGGR(BATgroupmin)
 GROUPAGGR(BATgroupmax)

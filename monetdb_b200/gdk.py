@@ -723,7 +723,7 @@ def BATunique(b: BAT, s: BAT | None = None) -> BAT:
 
 
 # ------------------------------------------------------------------ aggregates
-for _n in ("sum", "count", "min", "max"):
+for _n in ("sum", "prod", "count", "min", "max"):
     if hasattr(lib, f"b200_BATgroup{_n}"):
         _sig(f"b200_BATgroup{_n}", _P, _P, _P, _P, _P, C.c_int, C.c_bool)
 _sig("b200_BATgroupavg", C.c_int, _PP, _PP, _P, _P, _P, _P, C.c_int, C.c_bool, C.c_int)
@@ -735,6 +735,11 @@ _sig("b200_BATcalcavg", C.c_int, _P, _P, C.POINTER(C.c_double), C.POINTER(C.c_ui
 
 def BATgroupsum(b, g, e, s, tp, skip_nils=True) -> BAT:
     return BAT(lib.b200_BATgroupsum(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
+
+
+def BATgroupprod(b, g, e, s, tp, skip_nils=True) -> BAT:
+    """BATgroupprod (gdk_aggr.c:1575)"""
+    return BAT(lib.b200_BATgroupprod(b._p, _ptr(g), _ptr(e), _ptr(s), tp, skip_nils))
 
 
 def BATgroupcount(b, g, e, s, tp=TYPE.lng, skip_nils=True) -> BAT:

@@ -141,6 +141,7 @@ def _load(nthreads: int = 0):
         "BATmaskedcands": (P, [C.c_uint64, C.c_uint64, P, B]),
         "BATgroup": (C.c_int, [C.POINTER(P), C.POINTER(P), C.POINTER(P), P, P, P, P, P]),
         "BATgroupsum": (P, [P, P, P, P, C.c_int, B]),
+        "BATgroupprod": (P, [P, P, P, P, C.c_int, B]),
         "BATgroupcount": (P, [P, P, P, P, C.c_int, B]),
         "BATgroupmin": (P, [P, P, P, P, C.c_int, B]),
         "BATgroupmax": (P, [P, P, P, P, C.c_int, B]),
@@ -522,6 +523,10 @@ def _grp(name, b, g, e, s, tp, skip_nils) -> RBAT:
 
 def BATgroupsum(b, g, e, s, tp, skip_nils=True) -> RBAT:
     return _grp("BATgroupsum", b, g, e, s, tp, skip_nils)
+
+
+def BATgroupprod(b, g, e, s, tp, skip_nils=True) -> RBAT:
+    return _grp("BATgroupprod", b, g, e, s, tp, skip_nils)
 
 
 def BATgroupcount(b, g, e, s, tp=T.lng, skip_nils=True) -> RBAT:

@@ -58,7 +58,7 @@ def test_shim_exports_reference_entry_points():
         pytest.skip("shim not built")
     out = subprocess.run(["nm", "-D", "--defined-only", str(SHIM)], capture_output=True, text=True).stdout
     have = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
-    for s in ("BATselect", "BATthetaselect", "BATproject", "BATproject2", "BATgroup", "BATgroupsum", "BATgroupcount", "BATgroupmin",
+    for s in ("BATselect", "BATthetaselect", "BATproject", "BATproject2", "BATgroup", "BATgroupsum", "BATgroupprod", "BATgroupcount", "BATgroupmin",
               "BATgroupmax", "BATgroupavg", "BATsum", "BATjoin", "BATcalcadd", "BATcalcsub", "BATcalcmul", "BATcalcdiv",
               "BATcalcmulcst", "BATcalccstsub", "BATcalclt", "BATcalceq", "GDKanalyticaldiff", "GDKanalyticalwindowbounds",
               "GDKanalyticalsum", "GDKanalyticalavg", "GDKanalyticalcount", "GDKanalyticalmin", "GDKanalyticalmax"):
