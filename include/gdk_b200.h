@@ -278,6 +278,24 @@ b200_bat *b200_BATstrfromhost(const void *offsets, int width, uint64_t cnt, uint
 int b200_BATstrheap_tohost(const b200_bat *b, void *dst);	/* nvheap bytes; the offsets come with b200_BATtohost */
 int b200_BATstrwidth(const b200_bat *b);
 
+/* ---- allocation-free range select.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Selects the rows with lo <= vals[i] <= hi (nil never matches; nil bounds are refused) of a DEVICE-resident lng
+ * column and writes their oids (hseqbase + i, ascending) to oids_out (device, room for n) and their number to
+ * *count_out (device); same result as b200_BATselect(b, NULL, &lo, &hi, true, true, false, false).
+ * The scratch (mask bits, per-chunk counts / offsets) is a file-scope static __device__ array of about 2.1 MiB that
+ * every GPU loading the library holds until exit: n <= B200_NOALLOC_MAX_ROWS, larger inputs are refused (-2).
+ * Calls no cudaMalloc / cudaFree / pool routine and creates no thread context: three launches on `stream`
+ * (a cudaStream_t, NULL = the legacy default stream), no synchronisation — read the outputs in stream order.
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress) and must happen outside stream
+ * capture.  All calls share the array and it keeps the last call's contents (each call overwrites what it reads, so
+ * nothing needs clearing): calls that OVERLAP on the GPU race — serialise them on one stream or with events.
+ * Returns 0, or -1 bad arguments, -2 too many rows, -3 CUDA error; text in b200_errbuf() (stderr if the calling
+ * thread has no context). ---- */
+#define B200_NOALLOC_MAX_ROWS ((uint64_t) 1 << 24)
+int b200_select_lng_noalloc(const int64_t *vals, uint64_t n, uint64_t hseqbase, int64_t lo, int64_t hi, uint64_t *oids_out,
+			    uint64_t *count_out, void *stream);
+
 /* ---- hash + join: gdk_hash.c:989 (BAThash), gdk_join.c:4451 (BATjoin) ---- */
 b200_return b200_BAThash(const b200_bat *b);
 b200_return b200_BATjoin(b200_bat **r1p, b200_bat **r2p, const b200_bat *l, const b200_bat *r,

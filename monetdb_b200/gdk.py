@@ -133,6 +133,9 @@ _sig("b200_BATinvalidate", None, _P)
 _sig("b200_BATstrfromhost", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_bool)
 _sig("b200_BATstrheap_tohost", C.c_int, _P, C.c_void_p)
 _sig("b200_BATstrwidth", C.c_int, _P)
+_sig("b200_select_lng_noalloc", C.c_int, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+     C.c_void_p)
+NOALLOC_MAX_ROWS = 1 << 24
 _sig("b200_BATselect", _P, _P, _P, C.c_void_p, C.c_void_p, C.c_bool, C.c_bool, C.c_bool, C.c_bool)
 _sig("b200_BATthetaselect", _P, _P, _P, C.c_void_p, C.c_char_p)
 for _n in ("b200_BATmergecand", "b200_BATintersectcand", "b200_BATdiffcand", "b200_BATproject"):
