@@ -278,6 +278,23 @@ b200_bat *b200_BATstrfromhost(const void *offsets, int width, uint64_t cnt, uint
 int b200_BATstrheap_tohost(const b200_bat *b, void *dst);	/* nvheap bytes; the offsets come with b200_BATtohost */
 int b200_BATstrwidth(const b200_bat *b);
 
+/* ---- data-format edges of the device tier.
+ * Binary COPY INTO records (sql/backends/monet5/sql_bincopyconvert.c:590-616; layouts common/utils/copybinary.h:15-33):
+ * `src` (host) holds `count` records of `type` — the atom itself for bte/bit/sht/int/lng/hge/flt/dbl, the 4 / 8 / 12-byte
+ * copy_binary_date / _time / _timestamp for the temporal types; byteswap = the file has the other endianness;
+ * width > 0 = DECIMAL(width) range validation (VALIDATE_DECIMAL :45-58); filename only appears in error texts
+ * ("22003!invalid boolean byte value %d in %s", "22003!decimal out of range in %s").  Impossible dates / times decode to
+ * nil as date_create / daytime_create / timestamp_create do (gdk_time.c:62,281,401).  encode is the way back
+ * (dump_binary_column): count * record-size bytes into `dst` (host). */
+b200_bat *b200_bincopy_decode(int type, const void *src, uint64_t count, bool byteswap, int width, const char *filename,
+			      uint64_t hseq);
+int b200_bincopy_encode(const b200_bat *b, void *dst, bool byteswap);
+/* gdk_heap.c:729 (HEAPload) / :860 (HEAPsave -> GDKsave): a tail heap file — the raw array of values — read straight into
+ * / written straight out of device memory through page-locked staging; properties are the BBP directory's business
+ * (b200_BATsetprops).  A file shorter than count * width is refused. */
+b200_bat *b200_HEAPload(const char *path, int type, uint64_t count, uint64_t hseq);
+int b200_HEAPsave(const b200_bat *b, const char *path, bool dosync);
+
 /* ---- allocation-free range select.  NO COUNTERPART IN THE REFERENCE: added for
  * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Selects the rows with lo <= vals[i] <= hi (nil never matches; nil bounds are refused) of a DEVICE-resident lng

@@ -133,6 +133,10 @@ _sig("b200_BATinvalidate", None, _P)
 _sig("b200_BATstrfromhost", _P, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_bool)
 _sig("b200_BATstrheap_tohost", C.c_int, _P, C.c_void_p)
 _sig("b200_BATstrwidth", C.c_int, _P)
+_sig("b200_bincopy_decode", _P, C.c_int, C.c_void_p, C.c_uint64, C.c_bool, C.c_int, C.c_char_p, C.c_uint64)
+_sig("b200_bincopy_encode", C.c_int, _P, C.c_void_p, C.c_bool)
+_sig("b200_HEAPload", _P, C.c_char_p, C.c_int, C.c_uint64, C.c_uint64)
+_sig("b200_HEAPsave", C.c_int, _P, C.c_char_p, C.c_bool)
 _sig("b200_select_lng_noalloc", C.c_int, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
      C.c_void_p)
 NOALLOC_MAX_ROWS = 1 << 24
@@ -381,6 +385,32 @@ def str_decode(offsets: np.ndarray, heap: bytes) -> list:
         o += add
         out.append(heap[o:heap.index(b"\0", o)])
     return out
+
+
+BIN_RECORD = {TYPE.date: 4, TYPE.daytime: 8, TYPE.timestamp: 12}
+
+
+def bincopy_decode(tt: int, raw, count: int, byteswap: bool = False, width: int = 0, filename: str = "<buffer>", hseq: int = 0) -> BAT:
+    """binary COPY INTO records (bytes / numpy buffer) -> device column (sql_bincopyconvert.c)"""
+    buf = np.frombuffer(raw, dtype=np.uint8) if not isinstance(raw, np.ndarray) else np.ascontiguousarray(raw).view(np.uint8)
+    return BAT(lib.b200_bincopy_decode(tt, buf.ctypes.data_as(C.c_void_p), count, byteswap, width, filename.encode(), hseq))
+
+
+def bincopy_encode(b: BAT, byteswap: bool = False) -> bytes:
+    rs = BIN_RECORD.get(b.ttype) or NP_OF[b.ttype].itemsize
+    out = np.empty(len(b) * rs, dtype=np.uint8)
+    if lib.b200_bincopy_encode(b._p, out.ctypes.data_as(C.c_void_p), byteswap) != 0:
+        _fail("bincopy_encode")
+    return out.tobytes()
+
+
+def HEAPload(path: str, tt: int, count: int, hseq: int = 0) -> BAT:
+    return BAT(lib.b200_HEAPload(str(path).encode(), tt, count, hseq))
+
+
+def HEAPsave(b: BAT, path: str, dosync: bool = False) -> None:
+    if lib.b200_HEAPsave(b._p, str(path).encode(), dosync) != 0:
+        _fail("HEAPsave")
 
 
 def BATselect(b: BAT, s: BAT | None, tl, th, li: bool, hi: bool, anti: bool, nil_matches: bool = False) -> BAT:

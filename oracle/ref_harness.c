@@ -132,6 +132,88 @@ refh_str_heap(BAT *b, void *dst)
 	memcpy(dst, b->tvheap->base, b->tvheap->free);
 }
 
+/* the decoders of binary COPY INTO (sql/backends/monet5/sql_bincopyconvert.c:168-280) are loops around the GDK
+ * constructors below; sql/ itself cannot be compiled here (it needs the MAL / SQL headers), so the harness runs the
+ * same loops over the real date_create / daytime_create / timestamp_create of libbat */
+#include "gdk_time.h"
+void
+refh_bincopy_date(int32_t *dst, const uint8_t *src, uint64_t n)
+{
+	for (uint64_t i = 0; i < n; i++, src += 4) {
+		int16_t year;
+		memcpy(&year, src + 2, 2);
+		dst[i] = date_create(year, src[1], src[0]);
+	}
+}
+
+void
+refh_bincopy_time(int64_t *dst, const uint8_t *src, uint64_t n)
+{
+	for (uint64_t i = 0; i < n; i++, src += 8) {
+		uint32_t ms;
+		memcpy(&ms, src, 4);
+		dst[i] = daytime_create(src[6], src[5], src[4], ms);
+	}
+}
+
+void
+refh_bincopy_timestamp(int64_t *dst, const uint8_t *src, uint64_t n)
+{
+	for (uint64_t i = 0; i < n; i++, src += 12) {
+		uint32_t ms;
+		int16_t year;
+		memcpy(&ms, src, 4);
+		memcpy(&year, src + 10, 2);
+		dst[i] = timestamp_create(date_create(year, src[9], src[8]), daytime_create(src[6], src[5], src[4], ms));
+	}
+}
+
+/* encode_date / encode_time / encode_timestamp (:186-330) with the real accessors */
+void
+refh_bincopy_encode(int kind, uint8_t *dst, const void *src, uint64_t n)
+{
+	for (uint64_t i = 0; i < n; i++) {
+		date dt = date_nil;
+		daytime tm = daytime_nil;
+		bool nil;
+		if (kind == 0) {
+			dt = ((const date *) src)[i];
+			nil = is_date_nil(dt);
+		} else if (kind == 1) {
+			tm = ((const daytime *) src)[i];
+			nil = is_daytime_nil(tm);
+		} else {
+			timestamp ts = ((const timestamp *) src)[i];
+			nil = is_timestamp_nil(ts);
+			if (!nil) {
+				dt = timestamp_date(ts);
+				tm = timestamp_daytime(ts);
+			}
+		}
+		const int rs = kind == 0 ? 4 : kind == 1 ? 8 : 12;
+		uint8_t *r = dst + i * rs;
+		if (nil) {
+			memset(r, 0xff, rs);
+			continue;
+		}
+		if (kind != 0) {
+			uint32_t ms = daytime_usec(tm);
+			memcpy(r, &ms, 4);
+			r[4] = daytime_sec(tm);
+			r[5] = daytime_min(tm);
+			r[6] = daytime_hour(tm);
+			r[7] = 0;
+		}
+		if (kind != 1) {
+			uint8_t *d = r + (kind == 0 ? 0 : 8);
+			int16_t year = date_year(dt);
+			d[0] = date_day(dt);
+			d[1] = date_month(dt);
+			memcpy(d + 2, &year, 2);
+		}
+	}
+}
+
 /* a msk BAT from uint32 words holding `nbits` bits */
 BAT *
 refh_msk_new(uint64_t hseq, uint64_t nbits, const uint32_t *words)

@@ -356,6 +356,25 @@ def BATunmask(b) -> RBAT:
     return RBAT(_bat.BATunmask(b.p), "BATunmask")
 
 
+def bincopy_decode(kind: int, raw: bytes, n: int) -> np.ndarray:
+    """kind 0 date / 1 daytime / 2 timestamp records decoded with libbat's date_create / daytime_create /
+    timestamp_create (the loops of sql_bincopyconvert.c:168-280)"""
+    _load()
+    src = np.frombuffer(raw, dtype=np.uint8)
+    out = np.empty(n, dtype=np.int32 if kind == 0 else np.int64)
+    fn = (_h.refh_bincopy_date, _h.refh_bincopy_time, _h.refh_bincopy_timestamp)[kind]
+    fn(out.ctypes.data_as(C.c_void_p), src.ctypes.data_as(C.c_void_p), C.c_uint64(n))
+    return out
+
+
+def bincopy_encode(kind: int, vals: np.ndarray) -> bytes:
+    _load()
+    vals = np.ascontiguousarray(vals)
+    out = np.empty(len(vals) * (4, 8, 12)[kind], dtype=np.uint8)
+    _h.refh_bincopy_encode(C.c_int(kind), out.ctypes.data_as(C.c_void_p), vals.ctypes.data_as(C.c_void_p), C.c_uint64(len(vals)))
+    return out.tobytes()
+
+
 STR = 16
 str_nil = b"\x80"
 _STR_OFF = {1: np.dtype(np.uint8), 2: np.dtype(np.uint16), 4: np.dtype(np.uint32), 8: np.dtype(np.uint64)}
