@@ -191,6 +191,18 @@ template <typename T> struct AvgTreeIntOp {
 	}
 	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
 	{
+		if ((hge) (lng) a.sum == a.sum) {
+			/* the usual case: the sum fits 64 bits — one hardware-sized division instead of __divti3 */
+			const lng s = (lng) a.sum;
+			lng q64 = s / a.n, r64 = s - q64 * a.n;
+			if (r64 < 0) {
+				q64--;
+				r64 += a.n;
+			}
+			q = q64;
+			rr = r64;
+			return;
+		}
 		q = a.sum / (hge) a.n;
 		hge r = a.sum - q * (hge) a.n;
 		if (r < 0) {
@@ -278,6 +290,18 @@ template <typename T, bool EXACT> struct AvgIntegerOp {
 	}
 	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
 	{
+		if ((hge) (lng) a.sum == a.sum) {
+			/* the usual case: the sum fits 64 bits — one hardware-sized division instead of __divti3 */
+			const lng s = (lng) a.sum;
+			lng q64 = s / a.n, r64 = s - q64 * a.n;
+			if (r64 < 0) {
+				q64--;
+				r64 += a.n;
+			}
+			q = q64;
+			rr = r64;
+			return;
+		}
 		q = a.sum / (hge) a.n;
 		hge r = a.sum - q * (hge) a.n;
 		if (r < 0) {

@@ -379,6 +379,12 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		}
 		const T v = bp[k];
 		const bool vnil = !nonil && Atom<T>::is_nil(v);
+		bool olbig = false;
+		unsigned long long ol64 = 0;
+		if constexpr (!Atom<T>::is_float) {
+			olbig = ol > (LT) 0xffffffffffffffffULL;	/* wider than any 64-bit distance */
+			ol64 = (unsigned long long) ol;
+		}
 		/* ok(j): row j is still inside the frame of row k */
 		auto ok = [&](oid j) -> bool {
 			const T w = bp[j];
@@ -390,8 +396,10 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 				const T d = v - w;
 				return (d < 0 ? -d : d) <= ol;
 			} else {
-				const hge d = (hge) v - (hge) w;
-				return (d < 0 ? -d : d) <= ol;
+				/* |v - w| of two values of at most 64 bits is exact in unsigned 64-bit arithmetic */
+				const unsigned long long d = v >= w ? (unsigned long long) v - (unsigned long long) w
+								    : (unsigned long long) w - (unsigned long long) v;
+				return olbig || d <= ol64;
 			}
 		};
 		oid good = k, bad = 0;

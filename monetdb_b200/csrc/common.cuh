@@ -181,6 +181,14 @@ struct Staged {
 bool stage(const b200_bat *in, Staged &out);
 bool stage_sparse(const b200_bat *in, Staged &out, uint64_t touch_rows);	/* zero-copy for sparse gathers */
 
+void launch_iota(uint64_t *dst, uint64_t n, uint64_t start);	/* project.cu: dst[i] = start + i */
+
+// ---------------------------------------------------------------- joins with a dense side (join_void.cu)
+struct Cand;
+bool join_dense_right(b200_bat **r1p, b200_bat **r2p, const b200_bat *lb, const b200_bat *rb, const Cand &lci, const Cand &rci,
+		      unsigned mode);
+b200_bat *join_materialise_dense(const b200_bat *b);
+
 // ---------------------------------------------------------------- dictionary strings (str.cu)
 #define B200_STR_TYPE B200_str
 b200_bat *str_select_entry(const b200_bat *b, const b200_bat *s, const void *tl, const void *th, bool li, bool hi, bool anti,

@@ -631,8 +631,9 @@ static b200_return join_driver(b200_bat **r1p, b200_bat **r2p, const b200_bat *l
 	if (!stage(l, stl) || !stage(r, str_) || !stage(sl, stsl) || !stage(sr, stsr))
 		return B200_FAIL;
 	const b200_bat *lb = stl.b, *rb = str_.b;
-	const int t = basetype(lb->ttype);
-	if (t != basetype(rb->ttype)) {
+	/* ATOMtype: a void column is an oid column */
+	const int t = lb->ttype == B200_void ? B200_lng : basetype(lb->ttype);
+	if (t != (rb->ttype == B200_void ? B200_lng : basetype(rb->ttype))) {
 		/* joinparamcheck: ATOMtype(l->ttype) == ATOMtype(r->ttype) (gdk_join.c:3890) */
 		set_err("%s: inputs not compatible (%s vs %s).\n", func, atomname(lb->ttype), atomname(rb->ttype));
 		return B200_FAIL;
@@ -642,9 +643,33 @@ static b200_return join_driver(b200_bat **r1p, b200_bat **r2p, const b200_bat *l
 		return B200_FAIL;
 	if (lci.ncand == 0 || rci.ncand == 0)
 		return join_nomatch(r1p, r2p, lci, mode);
+	/* dense (void) sides: mergejoin_void when r and its candidates are dense (gdk_join.c:4155-4160, 4556-4560), else
+	 * the dense side becomes a real oid column and joins like any other */
+	struct TmpBat {
+		b200_bat *b = nullptr;
+		~TmpBat() { if (b) b200_BATfree(b); }
+	} lmat, rmat;
 	if (lb->ttype == B200_void || rb->ttype == B200_void) {
-		set_err("%s: void columns are not on the device path\n", func);
-		return B200_FAIL;
+		if (lb->ccand != B200_CAND_NONE || rb->ccand != B200_CAND_NONE ||
+		    (lb->ttype == B200_void && lb->tseqbase == OID_NIL) || (rb->ttype == B200_void && rb->tseqbase == OID_NIL)) {
+			set_err("%s: void-nil columns and candidate-list encodings as join columns are not on the device path\n", func);
+			return B200_FAIL;
+		}
+		if (rb->ttype == B200_void && rci.dense && lb->ttype != B200_msk) {
+			if (!join_dense_right(r1p, r2p, lb, rb, lci, rci, mode & (JM_NIL_ON_MISS | JM_ONLY_MISSES)))
+				return B200_FAIL;
+			return B200_SUCCEED;
+		}
+		if (lb->ttype == B200_void) {
+			if ((lmat.b = join_materialise_dense(lb)) == nullptr)
+				return B200_FAIL;
+			lb = lmat.b;
+		}
+		if (rb->ttype == B200_void) {
+			if ((rmat.b = join_materialise_dense(rb)) == nullptr)
+				return B200_FAIL;
+			rb = rmat.b;
+		}
 	}
 	if (lci.ncand >= JN_END || rci.ncand >= JN_END) {
 		set_err("%s: more than 2^32-1 rows in one device call\n", func);

@@ -324,7 +324,6 @@ extern "C" b200_bat *b200_BATproject2(const b200_bat *l, const b200_bat *r1, con
 			ltmp = (oid *) dev_alloc(lcount * sizeof(oid));
 			if (ltmp == nullptr)
 				return nullptr;
-			extern void launch_iota(oid *dst, uint64_t n, oid start);
 			launch_iota(ltmp, lcount, lc.seq);
 			loids = ltmp;
 			l_sorted_known = true;

@@ -648,7 +648,6 @@ extern "C" b200_return b200_BATsort(b200_bat **sorted, b200_bat **order, b200_ba
 	const oid ohseq = b->hseqbase;
 	/* materialise dense / void o and g (rare: a previous BATsort returns materialised ones) */
 	oid *otmp = nullptr, *gtmp = nullptr, *btmp = nullptr;
-	extern void launch_iota(oid *dst, uint64_t n, oid start);
 	const oid *op = nullptr, *gp = nullptr;
 	b200_return rc = B200_FAIL;
 	SortOut out;

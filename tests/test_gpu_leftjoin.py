@@ -188,3 +188,93 @@ def test_unique(gdk, ref, tt):
     k, rk = both(gdk, ref, np.arange(100, dtype=np.int32), T.int, key=True)
     uk = gdk.BATunique(k)
     assert len(uk) == 100 and np.array_equal(uk.numpy().astype(np.uint64), ref.BATunique(rk).numpy().astype(np.uint64))
+
+
+# ------------------------------------------------------------------ dense right-hand side: mergejoin_void (gdk_join.c:563)
+def _fk(gdk, ref, rng, nl, nr, rhseq, rtseq, lhseq, nilfrac, lkind):
+    """l: an oid column of foreign keys into the dense r (some dangling, some nil), or a dense l"""
+    if lkind == "dense":
+        ltseq = max(0, rtseq - nl // 3)
+        l, rl = gdk.BATdense(lhseq, ltseq, nl), ref.dense(lhseq, ltseq, nl)
+        a = np.arange(ltseq, ltseq + nl, dtype=np.uint64)
+    else:
+        a = rng.integers(max(0, rtseq - nr // 4), rtseq + nr + nr // 4, nl).astype(np.uint64)
+        if nilfrac:
+            a[rng.random(nl) < nilfrac] = NIL
+        if lkind == "sorted":
+            a = np.sort(a)
+        l, rl = both(gdk, ref, a, T.oid, hseq=lhseq, sorted=(lkind == "sorted" and not nilfrac))
+    r, rr = gdk.BATdense(rhseq, rtseq, nr), ref.dense(rhseq, rtseq, nr)
+    return a, l, rl, r, rr
+
+
+def _cand_pairs(gdk, ref, rng, n, hseq):
+    out = [(None, None)]
+    lo, cnt = hseq + n // 5, n // 2
+    out.append((gdk.BATdense(0, lo, cnt), ref.dense(0, lo, cnt)))
+    c = np.sort(rng.choice(n, max(1, n // 3), replace=False)).astype(np.uint64) + hseq
+    out.append((gdk.BATfromhost(c, T.oid, sorted=True, key=True, nonil=True), ref.bat(c, ref.T.oid, sorted=True, key=True, nonil=True)))
+    return out
+
+
+@pytest.mark.parametrize("lkind", ["random", "sorted", "dense"])
+@pytest.mark.parametrize("nilfrac", [0.0, 0.05])
+def test_dense_right_fetch_joins(gdk, ref, lkind, nilfrac):
+    if lkind == "dense" and nilfrac:
+        pytest.skip("a dense column has no nils")
+    rng = np.random.default_rng(len(lkind) * 7 + int(nilfrac * 100))
+    nl, nr, rhseq, rtseq, lhseq = 60_011, 20_003, 9, 1000, 4
+    a, l, rl, r, rr = _fk(gdk, ref, rng, nl, nr, rhseq, rtseq, lhseq, nilfrac, lkind)
+    for sl, rsl in _cand_pairs(gdk, ref, rng, nl, lhseq):
+        for sr, rsr in ((None, None), (gdk.BATdense(0, rhseq + 100, nr // 2), ref.dense(0, rhseq + 100, nr // 2))):
+            _same_pairs(*gdk.BATjoin(l, r, sl, sr, False), *ref.BATjoin(rl, rr, rsl, rsr, False))
+            o1, o2 = gdk.BATleftjoin(l, r, sl, sr, False)
+            e1, e2 = ref.BATleftjoin(rl, rr, rsl, rsr, False)
+            # one partner per row: the result is fully determined, compare it element for element
+            assert np.array_equal(o1.numpy(), e1.numpy()) and np.array_equal(o2.numpy(), e2.numpy())
+            assert_props_true(o1)
+            assert_props_true(o2)
+            o1, o2 = gdk.BATouterjoin(l, r, sl, sr, False)
+            if lkind == "dense" and sl is not None and not sl.is_dense():
+                # the reference crashes here (mergejoin_void's loop for a dense l with a non-dense candidate list,
+                # gdk_join.c:795-860, runs past its buffers): check against the definition instead
+                cl = sl.numpy().astype(np.int64)
+                v = a[cl - lhseq].astype(np.int64)
+                rlo = rtseq + (0 if sr is None else 100)
+                rhi = rlo + (nr if sr is None else nr // 2)
+                want = np.where((v >= rlo) & (v < rhi), (v - rtseq + rhseq).astype(np.uint64), NIL)
+                assert np.array_equal(o1.numpy().astype(np.int64), cl) and np.array_equal(o2.numpy().astype(np.uint64), want)
+            else:
+                e1, e2 = ref.BATouterjoin(rl, rr, rsl, rsr, False)
+                assert np.array_equal(o1.numpy(), e1.numpy()) and np.array_equal(o2.numpy().astype(np.uint64), e2.numpy().astype(np.uint64))
+            miss = o2.numpy().astype(np.uint64) == NIL
+            assert o2.props()["nil"] == bool(miss.any()) and o2.props()["nonil"] == (not miss.any())
+            o1, o2 = gdk.BATsemijoin(l, r, sl, sr, False)
+            e1, e2 = ref.BATsemijoin(rl, rr, rsl, rsr, False)
+            assert np.array_equal(o1.numpy(), e1.numpy()) and np.array_equal(o2.numpy(), e2.numpy())
+            assert np.array_equal(gdk.BATintersect(l, r, sl, sr, False).numpy(), ref.BATintersect(rl, rr, rsl, rsr, False).numpy())
+            for not_in in (False, True):
+                assert np.array_equal(gdk.BATdiff(l, r, sl, sr, False, not_in).numpy(), ref.BATdiff(rl, rr, rsl, rsr, False, not_in).numpy())
+    # the partner really is the row whose (virtual) tail holds the key
+    o1, o2 = gdk.BATleftjoin(l, r, None, None, False)
+    x, y = o1.numpy().astype(np.int64) - lhseq, o2.numpy().astype(np.int64) - rhseq
+    assert np.array_equal(a[x], (y + rtseq).astype(np.uint64))
+
+
+def test_dense_sides_that_need_the_hash_join(gdk, ref):
+    """dense r with NON-dense candidates, and a dense l against a real column: materialised and hash-joined"""
+    rng = np.random.default_rng(77)
+    nl, nr = 30_011, 9_001
+    a, l, rl, r, rr = _fk(gdk, ref, rng, nl, nr, 3, 500, 2, 0.02, "random")
+    c = np.sort(rng.choice(nr, nr // 2, replace=False)).astype(np.uint64) + 3
+    sr, rsr = gdk.BATfromhost(c, T.oid, sorted=True, key=True, nonil=True), ref.bat(c, ref.T.oid, sorted=True, key=True, nonil=True)
+    _same_pairs(*gdk.BATjoin(l, r, None, sr, False), *ref.BATjoin(rl, rr, None, rsr, False))
+    _same_pairs(*gdk.BATleftjoin(l, r, None, sr, False), *ref.BATleftjoin(rl, rr, None, rsr, False))
+    assert np.array_equal(gdk.BATdiff(l, r, None, sr, False, False).numpy(), ref.BATdiff(rl, rr, None, rsr, False, False).numpy())
+    # dense l, real r (values with duplicates)
+    b = rng.integers(0, 12_000, nr).astype(np.uint64)
+    r2, rr2 = both(gdk, ref, b, T.oid, hseq=8)
+    dl, rdl = gdk.BATdense(1, 4000, 10_000), ref.dense(1, 4000, 10_000)
+    _same_pairs(*gdk.BATjoin(dl, r2, None, None, False), *ref.BATjoin(rdl, rr2, None, None, False))
+    _same_pairs(*gdk.BATleftjoin(dl, r2, None, None, False), *ref.BATleftjoin(rdl, rr2, None, None, False))
+    assert np.array_equal(gdk.BATintersect(dl, r2, None, None, False).numpy(), ref.BATintersect(rdl, rr2, None, None, False).numpy())
