@@ -189,6 +189,9 @@ bool join_dense_right(b200_bat **r1p, b200_bat **r2p, const b200_bat *lb, const 
 		      unsigned mode);
 b200_bat *join_materialise_dense(const b200_bat *b);
 
+b200_return firstn_forms(b200_bat **topn, b200_bat **gids, const b200_bat *b, const b200_bat *s, const b200_bat *g, uint64_t n,
+			 bool asc, bool nilslast, bool distinct);	/* firstn.cu */
+
 // ---------------------------------------------------------------- dictionary strings (str.cu)
 #define B200_STR_TYPE B200_str
 b200_bat *str_select_entry(const b200_bat *b, const b200_bat *s, const void *tl, const void *th, bool li, bool hi, bool anti,

@@ -768,8 +768,8 @@ done:
 // ---------------------------------------------------------------- BATfirstn, plain form
 // gdk_firstn.c:1280: the oids of the n smallest (asc) / largest values of b restricted to s, nils first unless
 // nilslast; returned as a candidate list.  Which of several equal boundary values make it is open in the
-// reference (its heap decides); here the earliest rows do.  The grouped / distinct / gids forms are refinements
-// for multi-column top-N and are not on the device path yet.
+// reference (its heap decides); here the earliest rows do.  The grouped / distinct / gids forms — the refinement steps
+// of a multi-column top-N — are in firstn.cu.
 extern "C" b200_return b200_BATfirstn(b200_bat **topn, b200_bat **gids, const b200_bat *b, const b200_bat *s, const b200_bat *g,
 				      uint64_t n, bool asc, bool nilslast, bool distinct)
 {
@@ -782,10 +782,8 @@ extern "C" b200_return b200_BATfirstn(b200_bat **topn, b200_bat **gids, const b2
 		set_err("BATfirstn: b and topn required\n");
 		return B200_FAIL;
 	}
-	if (g != nullptr || gids != nullptr || distinct) {
-		set_err("BATfirstn: the grouped / distinct / gids forms are not on the device path\n");
-		return B200_FAIL;
-	}
+	if (g != nullptr || gids != nullptr || distinct)
+		return firstn_forms(topn, gids, b, s, g, n, asc, nilslast, distinct);	/* firstn.cu */
 	/* values of the candidates, their sort order, the first n oids, as an ascending candidate list */
 	b200_bat *vals = nullptr, *ord = nullptr, *head = nullptr, *picked = nullptr, *cl = nullptr;
 	b200_return rc = B200_FAIL;

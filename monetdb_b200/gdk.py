@@ -662,12 +662,14 @@ def BATsort(b: BAT, o: BAT | None = None, g: BAT | None = None, reverse: bool = 
     return (BAT(ps) if want[0] else None), (BAT(po) if want[1] else None), (BAT(pg) if want[2] else None)
 
 
-def BATfirstn(b: BAT, s: BAT | None, n: int, asc: bool = True, nilslast: bool = False) -> BAT:
-    """BATfirstn, plain form (gdk_firstn.c:1280) -> candidate list of the n smallest / largest values"""
-    p = _P()
-    if lib.b200_BATfirstn(C.byref(p), None, b._p, _ptr(s), None, n, asc, nilslast, False) != 1:
+def BATfirstn(b: BAT, s: BAT | None, n: int, asc: bool = True, nilslast: bool = False, g: BAT | None = None,
+              distinct: bool = False, want_gids: bool = False):
+    """BATfirstn (gdk_firstn.c:1280) -> candidate list of the n smallest / largest values, or (topn, gids) with
+    want_gids; g / distinct / gids are the refinement forms of a multi-column ORDER BY ... LIMIT"""
+    p, q = _P(), _P()
+    if lib.b200_BATfirstn(C.byref(p), C.byref(q) if want_gids else None, b._p, _ptr(s), _ptr(g), n, asc, nilslast, distinct) != 1:
         _fail("BATfirstn")
-    return BAT(p)
+    return (BAT(p), BAT(q)) if want_gids else BAT(p)
 
 
 # ------------------------------------------------------------------ hash + join (gdk_hash.h:36, gdk.h:2266)

@@ -639,13 +639,14 @@ def BATsort(b, o=None, g=None, reverse=False, nilslast=False, stable=False, want
     return (RBAT(ps.value) if want[0] else None), (RBAT(po.value) if want[1] else None), (RBAT(pg.value) if want[2] else None)
 
 
-def BATfirstn(b, s, n, asc=True, nilslast=False) -> RBAT:
-    p = C.c_void_p()
-    if _bat.BATfirstn(C.byref(p), None, b.p, _p(s), None, n, asc, nilslast, False) != 1:
+def BATfirstn(b, s, n, asc=True, nilslast=False, g=None, distinct=False, want_gids=False):
+    """BATfirstn (gdk_firstn.c:1280); returns topn, or (topn, gids) with want_gids"""
+    p, q = C.c_void_p(), C.c_void_p()
+    if _bat.BATfirstn(C.byref(p), C.byref(q) if want_gids else None, b.p, _p(s), _p(g), n, asc, nilslast, distinct) != 1:
         msg = errbuf().strip()
         clrerr()
         raise RefError(msg or "BATfirstn failed")
-    return RBAT(p.value)
+    return (RBAT(p.value), RBAT(q.value)) if want_gids else RBAT(p.value)
 
 
 def BATjoin(l, r, sl=None, sr=None, nil_matches=False, estimate=BUN_NONE):
