@@ -804,7 +804,7 @@ gdk_return
 BATjoin(BAT **r1p, BAT **r2p, BAT *l, BAT *r, BAT *sl, BAT *sr, bool nil_matches, BUN estimate)
 {
 	if (l == NULL || r == NULL || r1p == NULL || !bat_ok(l) || !bat_ok(r) || !bat_ok(sl) || !bat_ok(sr) ||
-	    l->ttype == TYPE_void || r->ttype == TYPE_void || !enter(BATcount(l) + BATcount(r)))
+	    !enter(BATcount(l) + BATcount(r)))
 		FORWARD(BATjoin, r1p, r2p, l, r, sl, sr, nil_matches, estimate);
 	inarg al = {0}, ar = {0}, asl = {0}, asr = {0};
 	gdk_return rc = GDK_FAIL;
@@ -836,6 +836,194 @@ BATjoin(BAT **r1p, BAT **r2p, BAT *l, BAT *r, BAT *sl, BAT *sr, bool nil_matches
 	in_close(&asl);
 	in_close(&ar);
 	in_close(&al);
+	return rc;
+}
+
+/* ------------------------------------------------------------------ the leftjoin family: gdk.h:2254-2265 */
+#define JOIN2(NAME, XDECL, XARG)											\
+static gdk_return (*real_##NAME)(BAT **, BAT **, BAT *, BAT *, BAT *, BAT *, bool XDECL, BUN);				\
+gdk_return													\
+NAME(BAT **r1p, BAT **r2p, BAT *l, BAT *r, BAT *sl, BAT *sr, bool nil_matches XDECL, BUN estimate)			\
+{														\
+	if (l == NULL || r == NULL || r1p == NULL || !bat_ok(l) || !bat_ok(r) || !bat_ok(sl) || !bat_ok(sr) ||		\
+	    !enter(BATcount(l) + BATcount(r)))										\
+		FORWARD(NAME, r1p, r2p, l, r, sl, sr, nil_matches XARG, estimate);					\
+	inarg al = {0}, ar = {0}, asl = {0}, asr = {0};									\
+	gdk_return rc = GDK_FAIL;											\
+	b200_bat *o1 = NULL, *o2 = NULL;										\
+	*r1p = NULL;													\
+	if (r2p)													\
+		*r2p = NULL;												\
+	if (in_open(&al, l) && in_open(&ar, r) && in_open(&asl, sl) && in_open(&asr, sr)) {				\
+		n_device++;												\
+		if (b200_##NAME(&o1, r2p ? &o2 : NULL, al.d, ar.d, asl.d, asr.d, nil_matches XARG, (uint64_t) estimate) == B200_SUCCEED) { \
+			*r1p = out_bat(o1);										\
+			if (r2p)											\
+				*r2p = out_bat(o2);									\
+			if (*r1p && (!r2p || *r2p))									\
+				rc = GDK_SUCCEED;									\
+			else {												\
+				BBPreclaim(*r1p);									\
+				*r1p = NULL;										\
+				if (r2p) {										\
+					BBPreclaim(*r2p);								\
+					*r2p = NULL;									\
+				}											\
+			}												\
+		} else													\
+			fail(__func__);											\
+	} else														\
+		fail(__func__);												\
+	in_close(&asr);													\
+	in_close(&asl);													\
+	in_close(&ar);													\
+	in_close(&al);													\
+	return rc;													\
+}
+#define COMMA_FLAG_DECL(F) , bool F
+#define COMMA_FLAG_ARG(F) , F
+JOIN2(BATleftjoin, NOTHING, NOTHING)
+JOIN2(BATouterjoin, COMMA_FLAG_DECL(match_one), COMMA_FLAG_ARG(match_one))
+JOIN2(BATsemijoin, COMMA_FLAG_DECL(max_one), COMMA_FLAG_ARG(max_one))
+
+#define JOIN1(NAME, FLAG)												\
+static BAT *(*real_##NAME)(BAT *, BAT *, BAT *, BAT *, bool, bool, BUN);						\
+BAT *														\
+NAME(BAT *l, BAT *r, BAT *sl, BAT *sr, bool nil_matches, bool FLAG, BUN estimate)					\
+{														\
+	if (l == NULL || r == NULL || !bat_ok(l) || !bat_ok(r) || !bat_ok(sl) || !bat_ok(sr) ||			\
+	    !enter(BATcount(l) + BATcount(r)))										\
+		FORWARD(NAME, l, r, sl, sr, nil_matches, FLAG, estimate);						\
+	inarg al = {0}, ar = {0}, asl = {0}, asr = {0};									\
+	BAT *bn = NULL;													\
+	if (in_open(&al, l) && in_open(&ar, r) && in_open(&asl, sl) && in_open(&asr, sr)) {				\
+		b200_bat *o = b200_##NAME(al.d, ar.d, asl.d, asr.d, nil_matches, FLAG, (uint64_t) estimate);		\
+		bn = o ? out_bat(o) : fail(__func__);									\
+		n_device++;												\
+	} else														\
+		fail(__func__);												\
+	in_close(&asr);													\
+	in_close(&asl);													\
+	in_close(&ar);													\
+	in_close(&al);													\
+	return bn;													\
+}
+JOIN1(BATintersect, max_one)
+JOIN1(BATdiff, not_in)
+
+/* ------------------------------------------------------------------ BATunique gdk.h:2279, BATconvert gdk_calc.h:123 */
+static BAT *(*real_BATunique)(BAT *, BAT *);
+BAT *
+BATunique(BAT *b, BAT *s)
+{
+	if (b == NULL || !bat_ok(b) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATunique, b, s);
+	inarg ab = {0}, as = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&as, s)) {
+		b200_bat *o = b200_BATunique(ab.d, as.d);
+		bn = o ? out_bat(o) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&as);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATconvert)(BAT *, BAT *, int, uint8_t, uint8_t, uint8_t);
+BAT *
+BATconvert(BAT *b, BAT *s, int tp, uint8_t scale1, uint8_t scale2, uint8_t precision)
+{
+	if (b == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(tp) || tp == TYPE_void || b->ttype == TYPE_void || tp == TYPE_oid ||
+	    b->ttype == TYPE_oid || !enter(BATcount(b)))
+		FORWARD(BATconvert, b, s, tp, scale1, scale2, precision);
+	inarg ab = {0}, as = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&as, s)) {
+		b200_bat *o = b200_BATconvert(ab.d, as.d, tp, scale1, scale2, precision);
+		bn = o ? out_bat(o) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&as);
+	in_close(&ab);
+	return bn;
+}
+
+/* ------------------------------------------------------------------ BATsort gdk.h:1526, BATfirstn gdk.h:2281 */
+static gdk_return (*real_BATsort)(BAT **, BAT **, BAT **, BAT *, BAT *, BAT *, bool, bool, bool);
+gdk_return
+BATsort(BAT **sorted, BAT **order, BAT **groups, BAT *b, BAT *o, BAT *g, bool reverse, bool nilslast, bool stable)
+{
+	if (b == NULL || !bat_ok(b) || !bat_ok(o) || !bat_ok(g) || b->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATsort, sorted, order, groups, b, o, g, reverse, nilslast, stable);
+	inarg ab = {0}, ao = {0}, ag = {0};
+	gdk_return rc = GDK_FAIL;
+	b200_bat *r[3] = {NULL, NULL, NULL};
+	BAT **outs[3] = {sorted, order, groups};
+	for (int i = 0; i < 3; i++)
+		if (outs[i])
+			*outs[i] = NULL;
+	if (in_open(&ab, b) && in_open(&ao, o) && in_open(&ag, g)) {
+		n_device++;
+		if (b200_BATsort(sorted ? &r[0] : NULL, order ? &r[1] : NULL, groups ? &r[2] : NULL, ab.d, ao.d, ag.d, reverse, nilslast,
+				 stable) == B200_SUCCEED) {
+			rc = GDK_SUCCEED;
+			for (int i = 0; i < 3; i++)
+				if (outs[i] && (*outs[i] = out_bat(r[i])) == NULL)
+					rc = GDK_FAIL;
+			if (rc != GDK_SUCCEED)
+				for (int i = 0; i < 3; i++)
+					if (outs[i]) {
+						BBPreclaim(*outs[i]);
+						*outs[i] = NULL;
+					}
+		} else
+			fail(__func__);
+	} else
+		fail(__func__);
+	in_close(&ag);
+	in_close(&ao);
+	in_close(&ab);
+	return rc;
+}
+
+static gdk_return (*real_BATfirstn)(BAT **, BAT **, BAT *, BAT *, BAT *, BUN, bool, bool, bool);
+gdk_return
+BATfirstn(BAT **topn, BAT **gids, BAT *b, BAT *s, BAT *g, BUN n, bool asc, bool nilslast, bool distinct)
+{
+	if (b == NULL || topn == NULL || !bat_ok(b) || !bat_ok(s) || !bat_ok(g) || b->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATfirstn, topn, gids, b, s, g, n, asc, nilslast, distinct);
+	inarg ab = {0}, as = {0}, ag = {0};
+	gdk_return rc = GDK_FAIL;
+	b200_bat *o1 = NULL, *o2 = NULL;
+	*topn = NULL;
+	if (gids)
+		*gids = NULL;
+	if (in_open(&ab, b) && in_open(&as, s) && in_open(&ag, g)) {
+		n_device++;
+		if (b200_BATfirstn(&o1, gids ? &o2 : NULL, ab.d, as.d, ag.d, (uint64_t) n, asc, nilslast, distinct) == B200_SUCCEED) {
+			*topn = out_bat(o1);
+			if (gids)
+				*gids = out_bat(o2);
+			if (*topn && (!gids || *gids))
+				rc = GDK_SUCCEED;
+			else {
+				BBPreclaim(*topn);
+				*topn = NULL;
+				if (gids) {
+					BBPreclaim(*gids);
+					*gids = NULL;
+				}
+			}
+		} else
+			fail(__func__);
+	} else
+		fail(__func__);
+	in_close(&ag);
+	in_close(&as);
+	in_close(&ab);
 	return rc;
 }
 

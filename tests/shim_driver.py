@@ -81,6 +81,26 @@ def main():
     ws = R.GDKanalyticalsum(R.colnew(T.hge, m), p, None, vl, s, e, T.lng, T.hge, 0)
     wa = R.GDKanalyticalfn("avg", R.colnew(T.dbl, m), p, None, vl, s, e, T.lng, 0)
     out["window"] = {"p": dump(p), "s": dump(s), "e": dump(e), "sum": dump(ws), "avg": dump(wa)}
+    # ---- ORDER BY / LIMIT, FK fetch join, DISTINCT, CAST: sort, firstn cascade, leftjoin family, unique, convert
+    rng = np.random.default_rng(13)
+    m = min(n, 300_000)
+    c1 = R.bat(rng.integers(0, 50, m).astype(np.int32), T.int, nonil=True)
+    c2 = R.bat(rng.integers(0, 1000, m).astype(np.int64), T.lng, nonil=True)
+    so, oo, go = R.BATsort(c1, None, None, False, False, True)
+    s2, o2, g2 = R.BATsort(c2, oo, go, True, True, False)
+    s1f, g1f = R.BATfirstn(c1, None, 100, True, False, None, False, True)
+    s2f, g2f = R.BATfirstn(c2, s1f, 100, True, False, g1f, False, True)
+    fk = R.bat(rng.integers(0, m + m // 10, m).astype(np.uint64), T.oid, nonil=True)
+    dim = R.dense(0, 0, m)
+    j1, j2 = R.BATleftjoin(fk, dim, None, None, False)
+    oj1, oj2 = R.BATouterjoin(fk, dim, None, None, False)
+    sj1, sj2 = R.BATsemijoin(c1, R.bat(np.arange(10, 30, dtype=np.int32), T.int, nonil=True), None, None, False)
+    out["order"] = {"sorted": dump(so), "order": dump(oo), "groups": dump(go), "sorted2": dump(s2), "groups2": dump(g2),
+                    "topn1": dump(s1f), "gids1": dump(g1f), "topn2": dump(s2f), "gids2": dump(g2f),
+                    "fk1": dump(j1), "fk2": dump(j2), "outer1": dump(oj1), "outer2": dump(oj2), "semi1": dump(sj1),
+                    "dangling": dump(R.BATdiff(fk, dim, None, None, False, False)),
+                    "unique": dump(R.BATunique(c1, None)),
+                    "convert": dump(R.BATconvert(c2, None, T.int, 0, 0, 0)), "decimal": dump(R.BATconvert(c1, None, T.lng, 0, 2, 0))}
     # ---- dictionary strings: GROUP BY two str flags + equality selects on a str column created by the real GDK
     rng = np.random.default_rng(11)
     ns = min(n, 200_000)
