@@ -31,7 +31,8 @@ enum { AN_ERR_OVERFLOW = 1, AN_ERR_BOUND = 2 };
 struct SegList {
 	oid *S = nullptr;	/* cnt starts + sentinel S[cnt] = n */
 	uint64_t cnt = 0, n = 0;
-	~SegList() { if (S) dev_free(S); }
+	bool cached = false;	/* S belongs to the flag column's SHADOW_SEGLIST twin */
+	~SegList() { if (S && !cached) dev_free(S); }
 };
 
 static __global__ void an_set_u64(oid *p, oid v)

@@ -46,10 +46,33 @@ bool an_check_bit(const b200_bat *x, const char *what, uint64_t n)
 	return true;
 }
 
+// A window plan hands the same partition column to its bounds and to every aggregate (sql_rank.c); the list of
+// partition starts is therefore kept as a twin of that column (a heap this library owns, e.g. GDKanalyticaldiff's
+// result) and rebuilt only when the column is rewritten (every GDKanalytical* entry point drops the twin of its r).
 bool an_partitions(const b200_bat *p, const b200_bat *o, uint64_t n, SegList &out)
 {
+	const bool cacheable = p != nullptr && o == nullptr && n > 0 && p->device >= 0 && p->owns && p->parent == nullptr && shadow_enabled();
+	Shadow sh;
+	if (cacheable && shadow_get(p->base, SHADOW_SEGLIST, n, sh)) {
+		out.S = (oid *) sh.p;
+		out.cnt = sh.a0;
+		out.n = n;
+		out.cached = true;
+		return true;
+	}
 	FlagStart f{p ? (const bte *) p->base : nullptr, o ? (const bte *) o->base : nullptr};
-	return build_seglist(n, f, out);
+	if (!build_seglist(n, f, out))
+		return false;
+	if (cacheable) {
+		Shadow s;
+		s.kind = SHADOW_SEGLIST;
+		s.p = out.S;
+		s.n = n;
+		s.a0 = out.cnt;
+		shadow_put(p->base, s);
+		out.cached = true;
+	}
+	return true;
 }
 
 // ---------------------------------------------------------------- GDKanalyticaldiff
@@ -99,6 +122,7 @@ extern "C" b200_return b200_GDKanalyticaldiff(b200_bat *r, const b200_bat *b, co
 		set_err("GDKanalyticaldiff: result must be a device bit BAT with capacity >= BATcount(b)\n");
 		return B200_FAIL;
 	}
+	shadow_drop(r->base);	/* r is rewritten: what was cached about its old contents goes */
 	if (!an_check_bit(p, "p", n))
 		return B200_FAIL;
 	if (n > 0) {
@@ -921,6 +945,8 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 	p = sp.b;
 	l = sl_.b;
 	const uint64_t n = b->count;
+	if (r->device >= 0)
+		shadow_drop(r->base);
 	if (r->device < 0 || basetype(r->ttype) != B200_lng || r->capacity < n) {
 		set_err("GDKanalyticalwindowbounds: result must be a device oid BAT with capacity >= BATcount(b)\n");
 		return B200_FAIL;

@@ -21,6 +21,8 @@ bool an_frame_prepare(const char *fn, b200_bat *r, const b200_bat *p, const b200
 	fa.frame_type = frame_type;
 	fa.n = fa.b->count;
 	const uint64_t n = fa.n;
+	if (r->device >= 0)
+		shadow_drop(r->base);
 	if (r->device < 0 || atomsize(r->ttype) != atomsize(rtype) || r->capacity < n || (r->base == nullptr && n > 0)) {
 		set_err("%s: result must be a device %s BAT with capacity >= BATcount(b)\n", fn, atomname(rtype));
 		return false;
