@@ -661,6 +661,9 @@ def other_workload(args):
         dev = upload(lambda a, b: workload.window_fast(a, b, threads=max(1, host_threads() // world)), types, lo, hi, chunk=blk * 400)
 
         def step():
+            # one plan = one step: whatever the library cached about the value column in the previous step (its
+            # running totals, shared by the four aggregates of a step) is dropped, so every step pays for it once
+            G.lib.b200_BATinvalidate(dev["val"]._p)
             p = G.GDKanalyticaldiff(G.colnew(T.bit, n), dev["pkey"], None, None, T.lng)
             tot = 0
             for unit, plo, phi, half in ((0, 100, 0, 1), (1, 50, 50, 0)):

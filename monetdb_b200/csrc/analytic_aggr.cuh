@@ -12,6 +12,9 @@
 template <typename Op, typename = void> struct op_checked : std::false_type {};
 template <typename Op> struct op_checked<Op, std::void_t<decltype(Op::checked)>> : std::integral_constant<bool, Op::checked> {};
 
+template <typename Op, typename = void> struct op_prefix_leaves : std::false_type {};
+template <typename Op> struct op_prefix_leaves<Op, std::void_t<decltype(Op::prefix_leaves)>> : std::integral_constant<bool, Op::prefix_leaves> {};
+
 template <typename T1, typename T2> struct SumOp {
 	static constexpr bool checked = true;
 	typedef T1 In;
@@ -189,6 +192,12 @@ template <typename T> struct AvgTreeIntOp {
 			a.n++;
 		}
 	}
+	static constexpr bool prefix_leaves = true;	/* level 0 may come from prefix sums (an_tree_query_p0) */
+	__device__ static __forceinline__ void add_leaves(Acc &a, hge sum, lng cnt)
+	{
+		a.sum += sum;
+		a.n += cnt;
+	}
 	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
 	{
 		if ((hge) (lng) a.sum == a.sum) {
@@ -287,6 +296,12 @@ template <typename T, bool EXACT> struct AvgIntegerOp {
 			a.sum += (hge) v.a;
 			a.n++;
 		}
+	}
+	static constexpr bool prefix_leaves = !EXACT;
+	__device__ static __forceinline__ void add_leaves(Acc &a, hge sum, lng cnt)
+	{
+		a.sum += sum;
+		a.n += cnt;
 	}
 	__device__ static __forceinline__ void floor_div(const Acc &a, hge &q, lng &rr)
 	{
@@ -412,7 +427,8 @@ struct FrameArgs {
 
 // runs Op over every row's frame into rb; st = {error bits, nil count}
 template <typename Op>
-static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long st[2], const char *kname)
+static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long st[2], const char *kname,
+		   const uhge *P = nullptr, const unsigned long long *C = nullptr)
 {
 	Ctx *c = ctx();
 	const uint64_t n = fa.n;
@@ -458,6 +474,15 @@ static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long
 		KTimer kt(kname, n * (sizeof(typename Op::In) + sizeof(typename Op::Out) + (framed ? 16 : 0)));
 		const unsigned grid = (unsigned) ((n + AN_TILE - 1) / AN_TILE);
 		const oid *fs = framed ? (const oid *) fa.s->base : nullptr, *fe = framed ? (const oid *) fa.e->base : nullptr;
+		if constexpr (op_prefix_leaves<Op>::value) {
+			if (P != nullptr && !peers) {
+				an_frame_kernel<Op, false, true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, nullptr, 0, n, (const typename Op::In *) fa.b->base,
+												      fs, fe, fa.frame_type, tree.dev(), rb, state, P, C);
+				COUNT_LAUNCH();
+				kt.stop();
+				return an_read_state(state, st);
+			}
+		}
 		if (peers)
 			an_frame_kernel<Op, true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, O.S, O.cnt, n, (const typename Op::In *) fa.b->base,
 										   fs, fe, fa.frame_type, tree.dev(), rb, state);

@@ -384,13 +384,19 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		       unsigned long long *__restrict__ state)
 {
 	typedef typename std::conditional<Atom<T>::is_float, T, hge>::type LT;
+	constexpr unsigned RPT = AN_TILE / AN_THREADS;	/* consecutive rows per thread */
 	__shared__ TileSegs ts;
 	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
 	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
 	ts.load(S, cnt, base, last);
 	unsigned err = 0;
-	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
-		const uint64_t k = base + i;
+	/* A thread takes RPT CONSECUTIVE rows: on an ascending partition with one static limit the frame edge of row
+	 * k + 1 is never in front of row k's, so after the first row's galloping search the edge only has to be
+	 * advanced — one or two probes per row instead of a dozen. */
+	bool have_prev = false;
+	oid pm = 0, pe = 0, pgood = 0;
+	for (unsigned jrow = 0; jrow < RPT; jrow++) {
+		const uint64_t k = base + (uint64_t) threadIdx.x * RPT + jrow;
 		if (k >= n)
 			break;
 		oid m, e;
@@ -399,6 +405,7 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		if (!an_limit<LT, DT>(lim, (LT) slim, k, ol)) {
 			err |= AN_ERR_BOUND;
 			rb[k] = k;
+			have_prev = false;
 			continue;
 		}
 		const T v = bp[k];
@@ -428,67 +435,92 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		};
 		oid good = k, bad = 0;
 		bool have_bad = false;
+		const bool hint = have_prev && lim == nullptr && !vnil && pm == m && pe == e;
 		if (preceding) {
-			for (oid step = 1;; step <<= 1) {
-				if (good - m < step) {
-					if (good != m) {
-						if (ok(m))
-							good = m;
-						else {
-							bad = m;
-							have_bad = true;
-						}
-					}
-					break;
-				}
-				const oid pos = good - step;
-				if (ok(pos))
-					good = pos;
-				else {
-					bad = pos;
+			if (hint) {
+				/* the start can only move forward: first row from the previous start on that is inside */
+				oid g = pgood;
+				while (g < k && !ok(g))
+					g++;
+				good = g;
+				if (good > m) {
+					bad = good - 1;
 					have_bad = true;
-					break;
 				}
+			} else {
+				for (oid step = 1;; step <<= 1) {
+					if (good - m < step) {
+						if (good != m) {
+							if (ok(m))
+								good = m;
+							else {
+								bad = m;
+								have_bad = true;
+							}
+						}
+						break;
+					}
+					const oid pos = good - step;
+					if (ok(pos))
+						good = pos;
+					else {
+						bad = pos;
+						have_bad = true;
+						break;
+					}
+				}
+				if (have_bad)
+					while (good - bad > 1) {
+						const oid mid = bad + (good - bad) / 2;
+						if (ok(mid))
+							good = mid;
+						else
+							bad = mid;
+					}
 			}
-			if (have_bad)
-				while (good - bad > 1) {
-					const oid mid = bad + (good - bad) / 2;
-					if (ok(mid))
-						good = mid;
-					else
-						bad = mid;
-				}
 			rb[k] = good;
 		} else {
-			for (oid step = 1;; step <<= 1) {
-				if (e - 1 - good < step) {
-					if (good != e - 1) {
-						if (ok(e - 1))
-							good = e - 1;
-						else {
-							bad = e - 1;
-							have_bad = true;
-						}
-					}
-					break;
-				}
-				const oid pos = good + step;
-				if (ok(pos))
-					good = pos;
-				else {
-					bad = pos;
+			if (hint) {
+				/* the end can only move forward: extend from the previous last row (or from k) */
+				oid g = pgood > k ? pgood : k;
+				while (g + 1 < e && ok(g + 1))
+					g++;
+				good = g;
+				if (good + 1 < e) {
+					bad = good + 1;
 					have_bad = true;
-					break;
 				}
+			} else {
+				for (oid step = 1;; step <<= 1) {
+					if (e - 1 - good < step) {
+						if (good != e - 1) {
+							if (ok(e - 1))
+								good = e - 1;
+							else {
+								bad = e - 1;
+								have_bad = true;
+							}
+						}
+						break;
+					}
+					const oid pos = good + step;
+					if (ok(pos))
+						good = pos;
+					else {
+						bad = pos;
+						have_bad = true;
+						break;
+					}
+				}
+				if (have_bad)
+					while (bad - good > 1) {
+						const oid mid = good + (bad - good) / 2;
+						if (ok(mid))
+							good = mid;
+						else
+							bad = mid;
+					}
 			}
-			if (have_bad)
-				while (bad - good > 1) {
-					const oid mid = good + (bad - good) / 2;
-					if (ok(mid))
-						good = mid;
-					else
-						bad = mid;
-				}
 			rb[k] = good + 1;
 		}
 		if (have_bad && !vnil) {
@@ -497,6 +529,10 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 			if (!(!nonil && Atom<T>::is_nil(w)) && !sub_with_check<T>(v, w, calc))
 				err |= AN_ERR_OVERFLOW;
 		}
+		have_prev = !vnil;
+		pm = m;
+		pe = e;
+		pgood = good;
 	}
 	if (err)
 		atomicOr(&state[0], (unsigned long long) err);

@@ -220,4 +220,72 @@ an_frame_prefix_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__res
 	if ((threadIdx.x & 31) == 0 && nils)
 		atomicAdd(&state[1], (unsigned long long) nils);
 }
+
+// ---------------------------------------------------------------- the running totals of a value column
+// Built by the first window aggregate over a column and kept as the column's SHADOW_PREFIX twin (heaps this library
+// owns only; at most AP_CACHE_ROWS rows — 24 bytes per row stay allocated until the column is freed or rewritten):
+// a window plan runs several aggregates over the same column (sum and avg, ROWS and RANGE frames), which then share
+// one build.
+#define AP_CACHE_ROWS ((uint64_t) 256 << 20)
+struct PrefixArrays {
+	uhge *P = nullptr;
+	unsigned long long *C = nullptr;
+	bool cached = false;
+	~PrefixArrays()
+	{
+		if (!cached) {
+			if (P)
+				dev_free(P);
+			if (C)
+				dev_free(C);
+		}
+	}
+};
+
+template <typename T1> static bool an_prefix_get(const b200_bat *b, uint64_t n, PrefixArrays &out)
+{
+	Ctx *c = ctx();
+	const bool want_c = !b->tnonil;
+	const bool cacheable = b->device >= 0 && b->owns && b->parent == nullptr && n <= AP_CACHE_ROWS && shadow_enabled();
+	Shadow sh;
+	if (cacheable && shadow_get(b->base, SHADOW_PREFIX, n, sh) && (sh.p2 != nullptr || !want_c)) {
+		out.P = (uhge *) sh.p;
+		out.C = (unsigned long long *) sh.p2;
+		out.cached = true;
+		return true;
+	}
+	const uint64_t ntiles = (n + AP_TILE - 1) / AP_TILE;
+	uhge *tsum = (uhge *) dev_alloc(ntiles * 16);
+	unsigned long long *tcnt = (unsigned long long *) dev_alloc(ntiles * 8);
+	out.P = (uhge *) dev_alloc((n + 1) * 16);
+	out.C = want_c ? (unsigned long long *) dev_alloc((n + 1) * 8) : nullptr;
+	bool ok = tsum && tcnt && out.P && (!want_c || out.C);
+	if (ok) {
+		const T1 *bp = (const T1 *) b->base;
+		KTimer kt("an_prefix", n * (2 * sizeof(T1) + 16 + (out.C ? 8 : 0)));
+		an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
+		COUNT_LAUNCH();
+		an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
+		COUNT_LAUNCH();
+		an_prefix_write_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt, out.P, out.C);
+		COUNT_LAUNCH();
+		ok = cuda_ok(cudaGetLastError(), "prefix launch");
+	}
+	if (tsum)
+		dev_free(tsum);
+	if (tcnt)
+		dev_free(tcnt);
+	if (!ok)
+		return false;	/* ~PrefixArrays releases P / C */
+	if (cacheable) {
+		Shadow s;
+		s.kind = SHADOW_PREFIX;
+		s.p = out.P;
+		s.p2 = out.C;
+		s.n = n;
+		shadow_put(b->base, s);
+		out.cached = true;
+	}
+	return true;
+}
 #endif

@@ -1,6 +1,7 @@
 // analytic_stat.cu — GDKanalyticalavg (gdk_analytic_statistics.c:364-437),
 // GDKanalyticalcount (gdk_analytic_func.c:1626-1681), GDKanalyticalmin/max (:1263-1323).
 #include "analytic_aggr.cuh"
+#include "analytic_prefix.cuh"
 
 // ---------------------------------------------------------------- avg
 template <typename T> static bool avg_run(const FrameArgs &fa, dbl *rb, unsigned long long st[2])
@@ -13,8 +14,16 @@ template <typename T> static bool avg_run(const FrameArgs &fa, dbl *rb, unsigned
 	ctx()->algo = "analyticalavg: cuda fan-out-16 segment tree";
 	if constexpr (Atom<T>::is_float)
 		return an_run<AvgTreeFltOp<T>>(fa, rb, st, "an_avg");
-	else
+	else {
+		/* level 0 of the tree walk from the column's running totals (shared with GDKanalyticalsum) */
+		PrefixArrays pa;
+		if (sizeof(T) <= 8 && (fa.frame_type < 3 || fa.frame_type > 6) && an_prefix_get<T>(fa.b, fa.n, pa)) {
+			ctx()->algo = "analyticalavg: cuda prefix sums (leaves) + fan-out-16 segment tree";
+			return an_run<AvgTreeIntOp<T>>(fa, rb, st, "an_avg", pa.P, pa.C);
+		}
+		b200_clrerr();
 		return an_run<AvgTreeIntOp<T>>(fa, rb, st, "an_avg");
+	}
 }
 
 extern "C" b200_return b200_GDKanalyticalavg(b200_bat *r, const b200_bat *p, const b200_bat *o, const b200_bat *b,
@@ -58,8 +67,15 @@ template <typename T> static bool avgint_run(const FrameArgs &fa, T *rb, unsigne
 {
 	const bool framed = fa.frame_type < 3 || fa.frame_type > 6;
 	ctx()->algo = framed ? "analyticalavginteger: cuda fan-out-16 segment tree" : "analyticalavginteger: cuda exact sum/count";
-	if (framed)
+	if (framed) {
+		if constexpr (sizeof(T) <= 8) {
+			PrefixArrays pa;
+			if (an_prefix_get<T>(fa.b, fa.n, pa))
+				return an_run<AvgIntegerOp<T, false>>(fa, rb, st, "an_avg", pa.P, pa.C);
+			b200_clrerr();
+		}
 		return an_run<AvgIntegerOp<T, false>>(fa, rb, st, "an_avg");
+	}
 	return an_run<AvgIntegerOp<T, true>>(fa, rb, st, "an_avg");
 }
 

@@ -60,7 +60,6 @@ static bool sum_prefix_run(const FrameArgs &fa, hge *rb, unsigned long long st[2
 {
 	Ctx *c = ctx();
 	const uint64_t n = fa.n;
-	const uint64_t ntiles = (n + AP_TILE - 1) / AP_TILE;
 	const bool peers = fa.frame_type == 3 || fa.frame_type == 4;
 	const bool framed = fa.frame_type < 3 || fa.frame_type > 6;
 	SegList S, O;
@@ -68,39 +67,22 @@ static bool sum_prefix_run(const FrameArgs &fa, hge *rb, unsigned long long st[2
 		return false;
 	if (peers && !an_partitions(fa.p, fa.o, n, O))
 		return false;
+	PrefixArrays pa;
+	if (!an_prefix_get<T1>(fa.b, n, pa))
+		return false;
 	unsigned long long *state = an_state_init();
-	uhge *tsum = (uhge *) dev_alloc(ntiles * 16), *P = (uhge *) dev_alloc((n + 1) * 16);
-	unsigned long long *tcnt = (unsigned long long *) dev_alloc(ntiles * 8);
-	unsigned long long *C = fa.b->tnonil ? nullptr : (unsigned long long *) dev_alloc((n + 1) * 8);
-	bool ok = state && tsum && P && tcnt && (fa.b->tnonil || C);
-	if (ok) {
-		const T1 *bp = (const T1 *) fa.b->base;
-		{
-			KTimer kt("an_prefix", n * (2 * sizeof(T1) + 16 + (C ? 8 : 0)));
-			an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
-			COUNT_LAUNCH();
-			an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
-			COUNT_LAUNCH();
-			an_prefix_write_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt, P, C);
-			COUNT_LAUNCH();
-		}
+	if (state == nullptr)
+		return false;
+	{
 		KTimer kt("an_sum", n * ((framed ? 16 : 0) + 32 + 16));
 		const unsigned grid = (unsigned) ((n + AN_TILE - 1) / AN_TILE);
 		const oid *fs = framed ? (const oid *) fa.s->base : nullptr, *fe = framed ? (const oid *) fa.e->base : nullptr;
 		if (peers)
-			an_frame_prefix_kernel<true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, O.S, O.cnt, n, fs, fe, fa.frame_type, P, C, rb, state);
+			an_frame_prefix_kernel<true><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, O.S, O.cnt, n, fs, fe, fa.frame_type, pa.P, pa.C, rb, state);
 		else
-			an_frame_prefix_kernel<false><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, nullptr, 0, n, fs, fe, fa.frame_type, P, C, rb, state);
+			an_frame_prefix_kernel<false><<<grid, AN_THREADS, 0, c->stream>>>(S.S, S.cnt, nullptr, 0, n, fs, fe, fa.frame_type, pa.P, pa.C, rb, state);
 		COUNT_LAUNCH();
 		ctx()->algo = "analyticalsum: cuda prefix sums";
-	}
-	if (tsum) dev_free(tsum);
-	if (tcnt) dev_free(tcnt);
-	if (P) dev_free(P);
-	if (C) dev_free(C);
-	if (!ok) {
-		if (state) dev_free(state);
-		return false;
 	}
 	return an_read_state(state, st);
 }

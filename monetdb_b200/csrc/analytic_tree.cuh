@@ -129,15 +129,73 @@ __device__ __forceinline__ void an_tree_query(const TreeDev<typename Op::Node> &
 	}
 }
 
+// The same walk with LEVEL 0 TAKEN FROM PREFIX SUMS: the two partial runs of leaves a frame touches (up to 15 rows each,
+// and of different lengths in every lane of a warp) become two differences of running totals.  For ops whose leaf
+// contribution is (sum of the non-nil values, their number) — the integer averages: AVERAGE_ITER keeps a * n + rr equal
+// to the exact sum of what it was fed — this gives the identical accumulator.  P[k] / C[k] = sum / number of the non-nil
+// values of rows [0, k) of the whole column (C == NULL: no nils).
+template <typename Op>
+__device__ __forceinline__ void an_tree_query_p0(const TreeDev<typename Op::Node> &t, const typename Op::In *__restrict__ bp,
+						 const uhge *__restrict__ P, const unsigned long long *__restrict__ C, oid ps, uint64_t q,
+						 uint64_t begin, uint64_t tend, typename Op::Acc &acc, unsigned &err)
+{
+	if (begin >= tend)
+		return;
+	auto leaves = [&](uint64_t a, uint64_t b) {
+		const uint64_t ra = ps + a, rb = ps + b;
+		Op::add_leaves(acc, (hge) (P[rb] - P[ra]), C ? (lng) (C[rb] - C[ra]) : (lng) (b - a));
+	};
+	{
+		uint64_t parent_begin = begin / AN_FANOUT, parent_end = tend / AN_FANOUT;
+		if (parent_begin == parent_end) {
+			leaves(begin, tend);
+			return;
+		}
+		const uint64_t group_begin = parent_begin * AN_FANOUT;
+		if (begin != group_begin) {
+			leaves(begin, group_begin + AN_FANOUT);
+			parent_begin++;
+		}
+		const uint64_t group_end = parent_end * AN_FANOUT;
+		if (tend != group_end)
+			leaves(group_end, tend);
+		begin = parent_begin;
+		tend = parent_end;
+	}
+	for (int level = 1; level <= t.nlev; level++) {
+		uint64_t parent_begin = begin / AN_FANOUT, parent_end = tend / AN_FANOUT;
+		if (parent_begin == parent_end) {
+			for (uint64_t pos = begin; pos < tend; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			break;
+		}
+		const uint64_t group_begin = parent_begin * AN_FANOUT;
+		if (begin != group_begin) {
+			const uint64_t limit = group_begin + AN_FANOUT;
+			for (uint64_t pos = begin; pos < limit; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			parent_begin++;
+		}
+		const uint64_t group_end = parent_end * AN_FANOUT;
+		if (tend != group_end) {
+			for (uint64_t pos = group_end; pos < tend; pos++)
+				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+		}
+		begin = parent_begin;
+		tend = parent_end;
+	}
+}
+
 // frame of row k (sql_catalog.h:104-113): 0-2 explicit start/end columns, 3 unbounded ->
 // current peer group, 4 current peer group -> unbounded, 5 whole partition, 6 current row.
 // DIRECT ops (count(*)) need no tree: the answer is the frame length.
-template <typename Op, bool PEERS>
+template <typename Op, bool PEERS, bool P0 = false>
 __global__ void __launch_bounds__(AN_THREADS)
 an_frame_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__ O, uint64_t ocnt, uint64_t n,
 		const typename Op::In *__restrict__ bp, const oid *__restrict__ fstart, const oid *__restrict__ fend,
 		int frame_type, TreeDev<typename Op::Node> tree, typename Op::Out *__restrict__ rb,
-		unsigned long long *__restrict__ state)
+		unsigned long long *__restrict__ state, const uhge *__restrict__ P = nullptr,
+		const unsigned long long *__restrict__ C = nullptr)
 {
 	__shared__ TileSegs ts;
 	__shared__ TileSegs to;		/* peer groups (frame types 3 and 4 only) */
@@ -179,8 +237,12 @@ an_frame_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__
 				fe = pe;
 			typename Op::Acc acc;
 			Op::init(acc);
-			if (fs < fe)
-				an_tree_query<Op>(tree, bp, ps, q, fs - ps, fe - ps, acc, err);
+			if (fs < fe) {
+				if constexpr (P0)
+					an_tree_query_p0<Op>(tree, bp, P, C, ps, q, fs - ps, fe - ps, acc, err);
+				else
+					an_tree_query<Op>(tree, bp, ps, q, fs - ps, fe - ps, acc, err);
+			}
 			res = Op::result(acc, isnil);
 		}
 		rb[k] = res;

@@ -144,7 +144,8 @@ void hash_cache_drop(const void *base);	/* join.cu: forget a cached BAThash inde
 // in full; a later operator that finds a twin reads it instead of the 8-byte form.
 enum { SHADOW_GID8 = 1 /* group ids < 256 as one byte per row */,
        SHADOW_SELMASK = 2 /* select result: the scan's bitmask + chunk offsets */,
-       SHADOW_SEGLIST = 3 /* a partition-flag column (GDKanalyticaldiff result): the list of partition starts */ };
+       SHADOW_SEGLIST = 3 /* a partition-flag column (GDKanalyticaldiff result): the list of partition starts */,
+       SHADOW_PREFIX = 4 /* an integer value column used by window aggregates: running sums (+ non-nil counts) */ };
 struct Shadow {
 	int kind = 0;
 	void *p = nullptr, *p2 = nullptr;	/* owned device buffers */
