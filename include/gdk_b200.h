@@ -266,6 +266,10 @@ b200_bat *b200_BATunique(const b200_bat *b, const b200_bat *s);
  *      !distinct).  One stable LSD radix sort serves stable and !stable alike. ---- */
 b200_return b200_BATsort(b200_bat **sorted, b200_bat **order, b200_bat **groups, const b200_bat *b, const b200_bat *o,
 			 const b200_bat *g, bool reverse, bool nilslast, bool stable);
+/* order index, gdk_orderidx.c:74 (BATcheckorderidx), :184 (BATorderidx): the stable ascending order of a device column, kept
+ * beside its heap; BATsort (no o / g, ascending, nils first) and selective range selects on large columns use it */
+b200_return b200_BATorderidx(const b200_bat *b, bool stable);
+int b200_BATcheckorderidx(const b200_bat *b);
 b200_return b200_BATfirstn(b200_bat **topn, b200_bat **gids, const b200_bat *b, const b200_bat *s, const b200_bat *g,
 			   uint64_t n, bool asc, bool nilslast, bool distinct);
 

@@ -145,7 +145,9 @@ void hash_cache_drop(const void *base);	/* join.cu: forget a cached BAThash inde
 enum { SHADOW_GID8 = 1 /* group ids < 256 as one byte per row */,
        SHADOW_SELMASK = 2 /* select result: the scan's bitmask + chunk offsets */,
        SHADOW_SEGLIST = 3 /* a partition-flag column (GDKanalyticaldiff result): the list of partition starts */,
-       SHADOW_PREFIX = 4 /* an integer value column used by window aggregates: running sums (+ non-nil counts) */ };
+       SHADOW_PREFIX = 4 /* an integer value column used by window aggregates: running sums (+ non-nil counts) */,
+       SHADOW_ORDERIDX = 5 /* the order index of a column (gdk_orderidx.c): its oids in ascending stable order; a0 = hseqbase
+			      the oids are based on */ };
 struct Shadow {
 	int kind = 0;
 	void *p = nullptr, *p2 = nullptr;	/* owned device buffers */

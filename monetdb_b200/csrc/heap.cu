@@ -538,7 +538,7 @@ extern "C" void b200_BATsetprops(b200_bat *b, bool sorted, bool revsorted, bool 
 
 // ---------------------------------------------------------------- narrow twins (common.cuh)
 static std::mutex g_shadow_mu;
-static std::unordered_map<const void *, Shadow> g_shadows;
+static std::unordered_multimap<const void *, Shadow> g_shadows;	/* one entry per (heap, kind) */
 
 bool shadow_enabled()
 {
@@ -551,9 +551,20 @@ bool shadow_enabled()
 
 void shadow_put(const void *base, const Shadow &s)
 {
-	shadow_drop(base);
-	std::lock_guard<std::mutex> lk(g_shadow_mu);
-	g_shadows[base] = s;
+	Shadow old;
+	{
+		std::lock_guard<std::mutex> lk(g_shadow_mu);
+		auto r = g_shadows.equal_range(base);
+		for (auto it = r.first; it != r.second; ++it)
+			if (it->second.kind == s.kind) {
+				old = it->second;
+				g_shadows.erase(it);
+				break;
+			}
+		g_shadows.emplace(base, s);
+	}
+	dev_free(old.p);
+	dev_free(old.p2);
 }
 
 bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out)
@@ -561,28 +572,32 @@ bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out)
 	if (base == nullptr)
 		return false;
 	std::lock_guard<std::mutex> lk(g_shadow_mu);
-	auto it = g_shadows.find(base);
-	if (it == g_shadows.end() || it->second.kind != kind || it->second.n != n)
-		return false;
-	out = it->second;
-	return true;
+	auto r = g_shadows.equal_range(base);
+	for (auto it = r.first; it != r.second; ++it)
+		if (it->second.kind == kind && it->second.n == n) {
+			out = it->second;
+			return true;
+		}
+	return false;
 }
 
 void shadow_drop(const void *base)
 {
 	if (base == nullptr)
 		return;
-	Shadow s;
+	Shadow gone[8];
+	int k = 0;
 	{
 		std::lock_guard<std::mutex> lk(g_shadow_mu);
-		auto it = g_shadows.find(base);
-		if (it == g_shadows.end())
-			return;
-		s = it->second;
-		g_shadows.erase(it);
+		auto r = g_shadows.equal_range(base);
+		for (auto it = r.first; it != r.second && k < 8; ++it)
+			gone[k++] = it->second;
+		g_shadows.erase(base);
 	}
-	dev_free(s.p);
-	dev_free(s.p2);
+	for (int i = 0; i < k; i++) {
+		dev_free(gone[i].p);
+		dev_free(gone[i].p2);
+	}
 }
 
 // ---------------------------------------------------------------- heap share counts (views)

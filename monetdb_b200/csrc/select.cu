@@ -252,6 +252,100 @@ template <typename T> struct GatherPredF {
 	__device__ __forceinline__ bool test(T v) const { return pred(v); }
 };
 
+// ---------------------------------------------------------------- range select through the order index
+// The index lists the oids in ascending value order, nils first: the rows with vl <= v <= vh are one contiguous run of
+// it.  Two binary searches find the run; its oids, sorted ascending again, are the result.  Worth it only when the run
+// is short against a scan that streams the whole column at HBM speed: the column must hold at least
+// B200_OIDX_SELECT_MIN_BYTES (default 256 MiB) and the run at most 1/64 of the rows, otherwise the scan runs.
+template <typename T>
+__global__ void oidx_bounds_kernel(const oid *__restrict__ idx, oid idx_hseq, const T *__restrict__ vals, uint64_t n, T vl, T vh,
+				   unsigned long long *__restrict__ out)
+{
+	/* thread 0: first position whose value is not below vl; thread 1: first position whose value is above vh */
+	const bool upper = threadIdx.x == 1;
+	uint64_t lo = 0, hi = n;
+	while (lo < hi) {
+		const uint64_t mid = (lo + hi) >> 1;
+		const T v = vals[idx[mid] - idx_hseq];
+		const bool before = Atom<T>::is_nil(v) || (upper ? v <= vh : v < vl);
+		if (before)
+			lo = mid + 1;
+		else
+			hi = mid;
+	}
+	out[threadIdx.x] = lo;
+}
+
+__global__ void oidx_slice_kernel(const oid *__restrict__ idx, oid idx_hseq, oid hseq, uint64_t lo, uint64_t k, oid *__restrict__ dst)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < k; i += (uint64_t) gridDim.x * blockDim.x)
+		dst[i] = idx[lo + i] - idx_hseq + hseq;
+}
+
+// 1: *out holds the result; -1: error; 0: no index / not worth it, scan instead
+template <typename T> static int select_by_orderidx(const b200_bat *b, const RangePred<T> &pred, b200_bat **out)
+{
+	static const uint64_t min_bytes = [] {
+		const char *e = getenv("B200_OIDX_SELECT_MIN_BYTES");
+		return e ? (uint64_t) strtoull(e, nullptr, 10) : (uint64_t) 256 << 20;
+	}();
+	const uint64_t n = b->count;
+	Shadow oix;
+	if (b->device < 0 || n * sizeof(T) < min_bytes || !shadow_get(b->base, SHADOW_ORDERIDX, n, oix))
+		return 0;
+	Ctx *c = ctx();
+	unsigned long long *st = (unsigned long long *) scratch_get(64);
+	if (st == nullptr)
+		return -1;
+	const oid *idx = (const oid *) oix.p;
+	oidx_bounds_kernel<T><<<1, 2, 0, c->stream>>>(idx, (oid) oix.a0, (const T *) b->base, n, pred.vl, pred.vh, st);
+	COUNT_LAUNCH();
+	if (!cuda_ok(cudaGetLastError(), "orderidx bounds") ||
+	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, st, 16, cudaMemcpyDeviceToHost, c->stream), "read") || !stream_sync())
+		return -1;
+	const uint64_t lo = c->slot_h->v[0], hi = c->slot_h->v[1];
+	if (hi <= lo) {
+		*out = bat_dense(0, 0, 0);
+		ctx()->algo = "select: orderidx";
+		return *out ? 1 : -1;
+	}
+	const uint64_t k = hi - lo;
+	if (k > n / 64)
+		return 0;
+	b200_bat *tmp = bat_new(0, B200_oid, k);
+	if (tmp == nullptr)
+		return -1;
+	oidx_slice_kernel<<<grid_for(k, 256, NSM * 16), 256, 0, c->stream>>>(idx, (oid) oix.a0, (oid) b->hseqbase, lo, k, (oid *) tmp->base);
+	COUNT_LAUNCH();
+	tmp->count = k;
+	tmp->tnonil = 1;
+	b200_bat *srt = nullptr;
+	const b200_return rc = b200_BATsort(&srt, nullptr, nullptr, tmp, nullptr, nullptr, false, false, false);	/* "output must be sorted" */
+	b200_BATfree(tmp);
+	if (rc != B200_SUCCEED)
+		return -1;
+	oid ends[2];
+	if (!cuda_ok(cudaMemcpyAsync(&c->slot_h->v[0], srt->base, 8, cudaMemcpyDeviceToHost, c->stream), "first") ||
+	    !cuda_ok(cudaMemcpyAsync(&c->slot_h->v[1], (const oid *) srt->base + (k - 1), 8, cudaMemcpyDeviceToHost, c->stream), "last") ||
+	    !stream_sync()) {
+		b200_BATfree(srt);
+		return -1;
+	}
+	ends[0] = c->slot_h->v[0];
+	ends[1] = c->slot_h->v[1];
+	CompactResult r;
+	r.count = k;
+	r.first = ends[0];
+	r.last = ends[1];
+	oid *dst = (oid *) srt->base;	/* the sorted heap changes hands */
+	srt->base = nullptr;
+	srt->owns = 0;
+	b200_BATfree(srt);
+	*out = oidlist_to_bat(dst, k, r);
+	ctx()->algo = "select: orderidx";
+	return *out ? 1 : -1;
+}
+
 // ---------------------------------------------------------------- typed driver
 struct SelArgs {
 	const b200_bat *b;
@@ -345,6 +439,12 @@ static bool select_typed(const SelArgs &a, b200_bat **out)
 	}
 	ctx()->algo = algo;
 	const Cand &ci = *a.ci;
+	if (!pred.anti && !pred.nilres && ci.dense && ci.ncand == a.b->count && a.b->count > 0) {
+		/* gdk_select.c:1716-1900: a column with an order index answers a range select from the index */
+		int used = select_by_orderidx<T>(a.b, pred, out);
+		if (used != 0)
+			return used > 0;
+	}
 	oid *dst = (oid *) dev_alloc(ci.ncand * sizeof(oid));
 	if (dst == nullptr)
 		return false;

@@ -428,6 +428,17 @@ grp_assign_ids_kernel(const U *__restrict__ keys, const uint32_t *__restrict__ r
 	}
 }
 
+// positions from a cached order index (oids based on idx_hseq)
+__global__ void __launch_bounds__(256)
+oidx_pos_kernel(const oid *__restrict__ idx, oid idx_hseq, uint64_t n, uint32_t *__restrict__ pos)
+{
+	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x)
+		pos[i] = (uint32_t) (idx[i] - idx_hseq);
+}
+/* set by b200_BATsort when the column has an order index that answers the request: the digit passes are skipped */
+static thread_local const oid *tl_sort_index = nullptr;
+static thread_local oid tl_sort_index_hseq = 0;
+
 // ---------------------------------------------------------------- the typed driver
 struct SortOut {
 	b200_bat *sorted = nullptr, *order = nullptr, *groups = nullptr;
@@ -471,6 +482,12 @@ static bool sort_typed(const b200_bat *b, const oid *o, const oid *g, uint64_t n
 		COUNT_LAUNCH();
 		COUNT_LAUNCH();
 		COUNT_LAUNCH();
+	}
+	if (tl_sort_index != nullptr && o == nullptr && g == nullptr && !reverse && !nilslast) {
+		/* the order index IS the answer (gdk_batop.c:2489-2520): no key images, no digit passes */
+		oidx_pos_kernel<<<grid_for(n, 256, NSM * 32), 256, 0, c->stream>>>(tl_sort_index, tl_sort_index_hseq, n, sb.pos[0]);
+		COUNT_LAUNCH();
+		goto passes_done;
 	}
 	sort_keys_kernel<T><<<grid_for(n, 256, NSM * 32), 256, 0, c->stream>>>(vals, o, hseq, n, reverse, nilslast, (U *) sb.keys[0], sb.pos[0]);
 	COUNT_LAUNCH();
@@ -531,6 +548,7 @@ static bool sort_typed(const b200_bat *b, const oid *o, const oid *g, uint64_t n
 			runs_sorted = sb.aux[sb.cur];
 		}
 	}
+passes_done:
 	if (!cuda_ok(cudaGetLastError(), "sort passes"))
 		goto done;
 	/* outputs */
@@ -709,6 +727,17 @@ extern "C" b200_return b200_BATsort(b200_bat **sorted, b200_bat **order, b200_ba
 	{
 		bool ok = false;
 		const bool ws = sorted != nullptr, wo = order != nullptr, wg = groups != nullptr;
+		Shadow oix;
+		tl_sort_index = nullptr;
+		if (op == nullptr && gp == nullptr && !reverse && !nilslast && b->ttype != B200_void && b->device >= 0 &&
+		    shadow_get(b->base, SHADOW_ORDERIDX, n, oix)) {
+			tl_sort_index = (const oid *) oix.p;
+			tl_sort_index_hseq = oix.a0;
+			ctx()->algo = "sort: order index";
+		}
+		struct Reset {
+			~Reset() { tl_sort_index = nullptr; }
+		} reset_index;
 		switch (basetype(bb->ttype)) {
 		case B200_bte: ok = sort_typed<bte>(bb, op, gp, n, reverse, nilslast, ws, wo, wg, ohseq, out); break;
 		case B200_sht: ok = sort_typed<sht>(bb, op, gp, n, reverse, nilslast, ws, wo, wg, ohseq, out); break;
@@ -835,4 +864,52 @@ done:
 	b200_BATfree(picked);
 	b200_BATfree(cl);
 	return rc;
+}
+
+// ---------------------------------------------------------------- order index (gdk_orderidx.c:74 BATcheckorderidx, :184 BATorderidx)
+// The reference keeps a column's stable ascending sort order as a heap beside the tail (b->torderidx) and uses it in
+// BATsort (gdk_batop.c:2489-2520) and in range selects (gdk_select.c:1716-1900).  Here it is a twin of the tail heap
+// (heaps this library owns), built by the radix sort, dropped with the heap or by b200_BATinvalidate.
+extern "C" int b200_BATcheckorderidx(const b200_bat *b)
+{
+	Shadow sh;
+	return b != nullptr && b->device >= 0 && b->base != nullptr && shadow_get(b->base, SHADOW_ORDERIDX, b->count, sh) ? 1 : 0;
+}
+
+extern "C" b200_return b200_BATorderidx(const b200_bat *b, bool stable)
+{
+	b200_clrerr();
+	if (b == nullptr) {
+		set_err("BATorderidx: BAT required\n");
+		return B200_FAIL;
+	}
+	if (b->ttype == B200_void) {
+		set_err("No order index on void type bats\n");	/* gdk_orderidx.c:187 */
+		return B200_FAIL;
+	}
+	if (b200_BATcheckorderidx(b))
+		return B200_SUCCEED;
+	if (b->device < 0 || !b->owns || b->parent != nullptr || b->ccand != B200_CAND_NONE || !shadow_enabled()) {
+		set_err("BATorderidx: an order index can only be kept for a device column whose heap this library owns\n");
+		return B200_FAIL;
+	}
+	b200_bat *on = nullptr;
+	if (b200_BATsort(nullptr, &on, nullptr, b, nullptr, nullptr, false, false, stable) != B200_SUCCEED)
+		return B200_FAIL;
+	if (on->ttype == B200_void || on->base == nullptr || b->count == 0) {
+		b200_BATfree(on);	/* nothing to remember */
+		return B200_SUCCEED;
+	}
+	Shadow s;
+	s.kind = SHADOW_ORDERIDX;
+	s.p = on->base;		/* the order heap changes hands */
+	s.n = b->count;
+	s.a0 = b->hseqbase;
+	s.a1 = 1;		/* always stable: the radix sort is */
+	on->base = nullptr;
+	on->owns = 0;
+	b200_BATfree(on);
+	shadow_put(b->base, s);
+	ctx()->algo = "create order index";
+	return B200_SUCCEED;
 }

@@ -648,6 +648,20 @@ def BATgroup(b: BAT, s: BAT | None = None, g: BAT | None = None, e: BAT | None =
 
 # ------------------------------------------------------------------ sort / top-N (gdk.h BATsort, BATfirstn)
 _sig("b200_BATsort", C.c_int, _PP, _PP, _PP, _P, _P, _P, C.c_bool, C.c_bool, C.c_bool)
+_sig("b200_BATorderidx", C.c_int, _P, C.c_bool)
+_sig("b200_BATcheckorderidx", C.c_int, _P)
+
+
+def BATorderidx(b: BAT, stable: bool = True) -> None:
+    """BATorderidx (gdk_orderidx.c:184): build and keep the column's order index"""
+    if lib.b200_BATorderidx(b._p, stable) != 1:
+        _fail("BATorderidx")
+
+
+def BATcheckorderidx(b: BAT) -> bool:
+    return bool(lib.b200_BATcheckorderidx(b._p))
+
+
 _sig("b200_BATfirstn", C.c_int, _PP, _PP, _P, _P, _P, C.c_uint64, C.c_bool, C.c_bool, C.c_bool)
 
 

@@ -218,3 +218,67 @@ def test_firstn_single_column_forms(gdk, ref, tt):
                     got, want = _firstn_both(gdk, ref, b, rb, cs, rcs, None, None, n, asc, nilslast, True, False)
                     if got is not None:
                         assert np.array_equal(got.numpy(), want.numpy()), (n, asc, nilslast)
+
+
+# ------------------------------------------------------------------ order index (gdk_orderidx.c)
+import os  # noqa: E402
+
+os.environ.setdefault("B200_OIDX_SELECT_MIN_BYTES", "0")     # let small test columns take the index path of BATselect
+
+
+@pytest.mark.parametrize("tt", [T.bte, T.int, T.lng, T.hge, T.flt, T.dbl, T.date])
+def test_order_index(gdk, ref, tt):
+    """BATorderidx + its two users: BATsort (order = the index) and selective range selects (two binary searches in
+    the index); results must be those of the plain paths and of the reference"""
+    rng = np.random.default_rng(tt + 900)
+    n = 120_011
+    a = random_col(rng, tt, n, nilfrac=0.03, lo=-100 if tt == T.bte else -50_000, hi=100 if tt == T.bte else 50_000)
+    # hseqbase 0: the reference's own order-index select returns nothing for columns with another hseqbase (it filters
+    # the index oids against a window computed without it, gdk_select.c:1740-1760,1895) — BASELINE.md §5; a second
+    # column with hseqbase 21 is checked against the definition below
+    b, rb = both(gdk, ref, a, tt, hseq=0)
+    plain = gdk.BATsort(b, None, None, False, False, True)
+    assert not gdk.BATcheckorderidx(b)
+    gdk.BATorderidx(b, True)
+    assert gdk.BATcheckorderidx(b)
+    gdk.BATorderidx(b, True)                      # idempotent
+    via = gdk.BATsort(b, None, None, False, False, True)
+    assert gdk.lib.b200_algorithm() == b"sort: order index"
+    rs, ro, rg = ref.BATsort(rb, None, None, False, False, True)
+    for x, y, z in zip(plain, via, (rs, ro, rg)):
+        assert same_bits(x.numpy(), y.numpy()) and same_bits(y.numpy(), z.numpy())
+    # other orders do not use it
+    check_sort(gdk, ref, b, rb, a, mode=(True, True, False), hseq=0)
+    # selective ranges (<= n/64 rows) through the index, wide ones through the scan; both identical to the reference
+    if tt in (T.flt, T.dbl):
+        ranges = [(10.0, 400.0), (-3.5, -3.5), (49_000.0, 60_000.0), (-40_000.0, 40_000.0)]
+    elif tt == T.bte:
+        ranges = [(5, 5), (99, 120), (-100, 100)]
+    else:
+        ranges = [(10, 400), (-7, -7), (49_500, 60_000), (-40_000, 40_000), (60_001, 70_000)]
+    used = 0
+    for lo, hi in ranges:
+        for li, hi_incl in ((True, True), (False, True), (True, False)):
+            got = gdk.BATselect(b, None, lo, hi, li, hi_incl, False, False)
+            used += gdk.lib.b200_algorithm() == b"select: orderidx"
+            want = ref.BATselect(rb, None, lo, hi, li, hi_incl, False, False)
+            assert same_bits(got.numpy(), want.numpy()), (lo, hi, li, hi_incl)
+            assert got.props()["hseq"] == 0
+    assert used >= 3
+    for op, v in (("==", ranges[0][0]), ("<", -49_000 if tt != T.bte else -99), (">=", 49_900 if tt != T.bte else 100)):
+        got, want = gdk.BATthetaselect(b, None, v, op), ref.BATthetaselect(rb, None, v, op)
+        assert same_bits(got.numpy(), want.numpy()), (op, v)
+    # another hseqbase: against the definition
+    if tt not in (T.hge,):
+        b21 = gdk.BATfromhost(a, tt, hseq=21)
+        gdk.BATorderidx(b21, True)
+        lo, hi = ranges[0]
+        got = gdk.BATselect(b21, None, lo, hi, True, True, False, False).numpy()
+        assert gdk.lib.b200_algorithm() == b"select: orderidx"
+        isnil = np.isnan(a) if tt in (T.flt, T.dbl) else a == np.iinfo(a.dtype).min
+        assert np.array_equal(got, np.flatnonzero(~isnil & (a >= lo) & (a <= hi)).astype(np.uint64) + 21)
+    # rewriting / freeing the column drops the index
+    gdk.lib.b200_BATinvalidate(b._p)
+    assert not gdk.BATcheckorderidx(b)
+    with pytest.raises(G.GDKError, match="No order index on void"):
+        gdk.BATorderidx(gdk.BATdense(0, 0, 10))
