@@ -212,6 +212,9 @@ b200_bat *b200_BATgroupcount(const b200_bat *b, const b200_bat *g, const b200_ba
 /* gdk_aggr.c:1575 — products in row order with the reference's overflow verdict ("22003!overflow in product aggregate.");
  * integer results by an exact order-independent form, flt/dbl results by an ordered replay per group */
 b200_bat *b200_BATgroupprod(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
+/* gdk_aggr.c:1650 — the scalar form; *res is an atom of type tp in host memory; a flt / dbl product of more than 2^24 rows is
+ * refused (order-dependent, one sequential pass) */
+b200_return b200_BATprod(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty);
 b200_bat *b200_BATgroupmin(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_bat *b200_BATgroupmax(const b200_bat *b, const b200_bat *g, const b200_bat *e, const b200_bat *s, int tp, bool skip_nils);
 b200_return b200_BATgroupavg(b200_bat **bnp, b200_bat **cntsp, const b200_bat *b, const b200_bat *g,

@@ -34,10 +34,12 @@ template <typename T> struct PIn {
 	oid gmin, gmax;
 	uint64_t n;
 	bool skip_nils;
+	bool gconst;		/* BATprod: every row in the one group gmin */
+	bool nil_if_empty;	/* false (BATprod only): the product starts at 1 and ANY nil met is final (doprod without `seen`) */
 	__device__ __forceinline__ T value(uint64_t r) const { return cand ? vals[__ldcs(cand + r) - hseq] : ld_stream(vals + r); }
 	__device__ __forceinline__ bool group(uint64_t r, u64 &gi) const
 	{
-		const oid g = gids ? __ldcs(gids + r) : gmin + r;
+		const oid g = gids ? __ldcs(gids + r) : (gconst ? gmin : gmin + r);
 		gi = g - gmin;
 		return g >= gmin && g <= gmax;
 	}
@@ -76,7 +78,7 @@ prod_cut_kernel(PIn<T> in, const u64 *__restrict__ fnn, u64 *__restrict__ fzero,
 		if (Atom<T>::is_nil(v)) {
 			if (!in.skip_nils) {
 				mynils++;
-				if (HGE_RESULT || (fnn != nullptr && r > __ldg(fnn + gi)))
+				if (HGE_RESULT || !in.nil_if_empty || (fnn != nullptr && r > __ldg(fnn + gi)))
 					pr_min(fnil + gi, r);
 			}
 			if (HGE_RESULT && !(__ldcg(seen + (gi >> 5)) & (1u << (gi & 31))))
@@ -126,6 +128,7 @@ prod_mul_kernel(PIn<T> in, const u64 *__restrict__ fzero, const u64 *__restrict_
 		M limit)
 {
 	const M SAT = ~(M) 0;
+	unsigned myneg = 0;	/* one group: counted per thread, one atomic per warp at the end */
 	for (uint64_t r = (uint64_t) blockIdx.x * PR_THREADS + threadIdx.x; r < in.n; r += (uint64_t) gridDim.x * PR_THREADS) {
 		u64 gi;
 		if (!in.group(r, gi))
@@ -136,8 +139,12 @@ prod_mul_kernel(PIn<T> in, const u64 *__restrict__ fzero, const u64 *__restrict_
 		const u64 z = __ldg(fzero + gi), nl = fnil ? __ldg(fnil + gi) : PR_NONE;
 		if (r > (z < nl ? z : nl))
 			continue;	/* behind the first zero / final nil: the running product is 0 or nil there */
-		if (v < 0)
-			atomicAdd(neg + gi, 1u);
+		if (v < 0) {
+			if (in.gconst)
+				myneg++;
+			else
+				atomicAdd(neg + gi, 1u);
+		}
 		const M f = v < 0 ? (M) 0 - (M) v : (M) v;
 		if (f == 1)
 			continue;
@@ -150,13 +157,20 @@ prod_mul_kernel(PIn<T> in, const u64 *__restrict__ fzero, const u64 *__restrict_
 			cur = old;
 		}
 	}
+	if (in.gconst) {
+		for (int o = 16; o > 0; o >>= 1)
+			myneg += __shfl_down_sync(0xffffffffu, myneg, o);
+		if ((threadIdx.x & 31) == 0 && (myneg & 1u))
+			atomicAdd(neg, 1u);	/* only the parity matters */
+	}
 }
 
 // finish: signed results, overflow flag, nil count
 template <typename TR, typename M>
 __global__ void __launch_bounds__(256)
 prod_finish_kernel(u64 ngrp, const u64 *__restrict__ fzero, const u64 *__restrict__ fnil, const unsigned *__restrict__ seen,
-		   const M *__restrict__ mag, const unsigned *__restrict__ neg, TR *__restrict__ out, unsigned long long *__restrict__ state)
+		   const M *__restrict__ mag, const unsigned *__restrict__ neg, TR *__restrict__ out, unsigned long long *__restrict__ state,
+		   bool nil_if_empty = true)
 {
 	unsigned long long nils = 0, unseen = 0;
 	bool ovf = false;
@@ -166,11 +180,11 @@ prod_finish_kernel(u64 ngrp, const u64 *__restrict__ fzero, const u64 *__restric
 		TR res;
 		if (m == ~(M) 0)
 			ovf = true;
-		if (!s) {
-			res = Atom<TR>::nil();
+		if (fnil && fnil[g] != PR_NONE) {
+			res = Atom<TR>::nil();		/* a final nil always belongs to a seen group (see prod_cut_kernel) */
+		} else if (!s) {
+			res = nil_if_empty ? Atom<TR>::nil() : (TR) 1;
 			unseen++;
-		} else if (fnil && fnil[g] != PR_NONE) {
-			res = Atom<TR>::nil();
 		} else if (fzero[g] != PR_NONE) {
 			res = 0;
 		} else {
@@ -206,7 +220,7 @@ prod_float_kernel(PIn<T1> in, const oid *__restrict__ sg, const oid *__restrict_
 	bool ovf = false;
 	for (u64 g = (u64) blockIdx.x * blockDim.x + threadIdx.x; g < ngrp; g += (u64) gridDim.x * blockDim.x) {
 		const oid want = in.gmin + g;
-		uint64_t lo = 0, hi = in.n;
+		uint64_t lo = 0, hi = sg == nullptr ? 0 : in.n;	/* sg == NULL (BATprod): one group, the rows in candidate order */
 		while (lo < hi) {
 			const uint64_t mid = (lo + hi) >> 1;
 			if (sg[mid] == OID_NIL || sg[mid] < want)	/* BATsort puts nil group ids first */
@@ -214,10 +228,10 @@ prod_float_kernel(PIn<T1> in, const oid *__restrict__ sg, const oid *__restrict_
 			else
 				hi = mid;
 		}
-		T2 prod = Atom<T2>::nil();
-		bool seen = false;
-		for (uint64_t i = lo; i < in.n && sg[i] == want && !ovf; i++) {
-			const T1 v = in.value(ord[i] - ghseq);
+		T2 prod = in.nil_if_empty ? Atom<T2>::nil() : (T2) 1;
+		bool seen = !in.nil_if_empty;
+		for (uint64_t i = lo; i < in.n && (sg == nullptr || sg[i] == want) && !ovf; i++) {
+			const T1 v = in.value(sg == nullptr ? i : ord[i] - ghseq);
 			if (Atom<T1>::is_nil(v)) {
 				if (!in.skip_nils) {
 					prod = Atom<T2>::nil();
@@ -254,6 +268,9 @@ prod_float_kernel(PIn<T1> in, const oid *__restrict__ sg, const oid *__restrict_
 }
 
 // ---------------------------------------------------------------- host side
+static thread_local bool tl_prod_nil_if_empty = true;	/* false only inside b200_BATprod(..., nil_if_empty = false) */
+#define PROD_SCALAR_FLOAT_MAX ((uint64_t) 16 << 20)	/* rows one thread may replay for an order-dependent scalar product */
+
 template <typename T> static PIn<T> prod_input(const AggrSetup &a, bool skip_nils)
 {
 	PIn<T> in;
@@ -268,8 +285,10 @@ template <typename T> static PIn<T> prod_input(const AggrSetup &a, bool skip_nil
 	}
 	in.gmin = a.min;
 	in.gmax = a.max;
-	in.gids = bat_is_dense(a.g) ? nullptr : (const oid *) a.g->base;
+	in.gconst = a.g == nullptr;
+	in.gids = (a.g == nullptr || bat_is_dense(a.g)) ? nullptr : (const oid *) a.g->base;
 	in.skip_nils = skip_nils;
+	in.nil_if_empty = tl_prod_nil_if_empty;
 	return in;
 }
 
@@ -283,7 +302,7 @@ static bool prod_int(const AggrSetup &a, bool skip_nils, void *out, unsigned lon
 	const u64 ngrp = a.ngrp;
 	const PIn<T> in = prod_input<T>(a, skip_nils);
 	const bool nilpath = !skip_nils && !a.b->tnonil;
-	const bool need_first = nilpath && !HGE_RESULT;
+	const bool need_first = nilpath && !HGE_RESULT && in.nil_if_empty;
 	const size_t words = (ngrp + 31) / 32;
 	/* [mag: ngrp x M][fzero][fnil][fnn: ngrp x u64 each][neg: ngrp x u32][seen: words x u32][state 4 x u64] */
 	const size_t off_fz = ngrp * sizeof(M), off_fnil = off_fz + ngrp * 8, off_fnn = off_fnil + ngrp * 8, off_neg = off_fnn + ngrp * 8,
@@ -314,7 +333,7 @@ static bool prod_int(const AggrSetup &a, bool skip_nils, void *out, unsigned lon
 		COUNT_LAUNCH();
 	}
 	prod_finish_kernel<TR, M><<<grid_for(ngrp, 256, NSM * 4), 256, 0, c->stream>>>(ngrp, fzero, nilpath ? fnil : nullptr, seen, mag, neg,
-										    (TR *) out, state);
+										    (TR *) out, state, in.nil_if_empty);
 	COUNT_LAUNCH();
 	if (!cuda_ok(cudaGetLastError(), "prod launch") ||
 	    !cuda_ok(cudaMemcpyAsync(c->slot_h->v, state, 32, cudaMemcpyDeviceToHost, c->stream), "read prod state") || !stream_sync())
@@ -334,11 +353,17 @@ static bool prod_float(const AggrSetup &a, bool skip_nils, void *out, unsigned l
 	Ctx *c = ctx();
 	const PIn<T1> in = prod_input<T1>(a, skip_nils);
 	b200_bat *sg = nullptr, *ord = nullptr;
-	if (b200_BATsort(&sg, &ord, nullptr, a.g, nullptr, nullptr, false, false, true) != B200_SUCCEED)
+	if (a.g == nullptr) {
+		if (in.n > PROD_SCALAR_FLOAT_MAX) {
+			set_err("BATprod: a floating-point product is order-dependent (one sequential pass): more than %llu rows are not on the device path\n",
+				(unsigned long long) PROD_SCALAR_FLOAT_MAX);
+			return false;
+		}
+	} else if (b200_BATsort(&sg, &ord, nullptr, a.g, nullptr, nullptr, false, false, true) != B200_SUCCEED)
 		return false;
 	bool ok = false;
 	unsigned long long *state = (unsigned long long *) scratch_get(64);
-	if (sg->ttype == B200_void || ord->ttype == B200_void) {
+	if (sg != nullptr && (sg->ttype == B200_void || ord->ttype == B200_void)) {
 		set_err("BATgroupprod: unexpected dense sort result\n");
 		goto done;
 	}
@@ -346,8 +371,9 @@ static bool prod_float(const AggrSetup &a, bool skip_nils, void *out, unsigned l
 		goto done;
 	{
 		KTimer kt("groupprod_float", in.n * (sizeof(T1) + 16));
-		prod_float_kernel<T1, T2><<<grid_for(a.ngrp, 128, NSM * 16), 128, 0, c->stream>>>(in, (const oid *) sg->base, (const oid *) ord->base,
-												    a.g->hseqbase, a.ngrp, (T2 *) out, state);
+		prod_float_kernel<T1, T2><<<grid_for(a.ngrp, 128, NSM * 16), 128, 0, c->stream>>>(in, sg ? (const oid *) sg->base : nullptr,
+												    ord ? (const oid *) ord->base : nullptr,
+												    a.g ? a.g->hseqbase : 0, a.ngrp, (T2 *) out, state);
 		COUNT_LAUNCH();
 	}
 	if (!cuda_ok(cudaGetLastError(), "prod launch") ||
@@ -466,4 +492,64 @@ extern "C" b200_bat *b200_BATgroupprod(const b200_bat *b, const b200_bat *g, con
 	bn->tnil = nils;
 	bn->tnonil = !nils;
 	return bn;
+}
+
+// BATprod (gdk_aggr.c:1650): the product of all candidates as one value in *res (host memory, atom of type tp)
+extern "C" b200_return b200_BATprod(void *res, int tp, const b200_bat *b, const b200_bat *s, bool skip_nils, bool nil_if_empty)
+{
+	b200_clrerr();
+	if (res == nullptr) {
+		set_err("BATprod: result pointer required\n");
+		return B200_FAIL;
+	}
+	AggrSetup a;
+	if (!aggr_init(a, b, nullptr, nullptr, s))
+		return B200_FAIL;
+	const int t2 = basetype(tp), w = atomsize(t2);
+	if (w <= 0 || t2 == B200_void) {
+		set_err("type combination (prod(%s)->%s) not supported.\n", atomname(a.b->ttype), atomname(tp));
+		return B200_FAIL;
+	}
+	/* *res = nil_if_empty ? nil : 1 (:1666-1694) */
+	unsigned char init[16];
+	atom_nil_bits(t2, init);
+	if (!nil_if_empty) {
+		memset(init, 0, sizeof(init));
+		if (t2 == B200_flt) {
+			const flt one = 1;
+			memcpy(init, &one, 4);
+		} else if (t2 == B200_dbl) {
+			const dbl one = 1;
+			memcpy(init, &one, 8);
+		} else
+			init[0] = 1;
+	}
+	memcpy(res, init, w);
+	if (a.ci.ncand == 0)
+		return B200_SUCCEED;
+	if (a.b->ttype == B200_void) {
+		set_err("BATprod: void columns are not on the device path\n");
+		return B200_FAIL;
+	}
+	Ctx *c = ctx();
+	void *out = dev_alloc(16);
+	if (out == nullptr)
+		return B200_FAIL;
+	unsigned long long st[3] = {0, 0, 0};
+	tl_prod_nil_if_empty = nil_if_empty;
+	c->algo = (t2 == B200_flt || t2 == B200_dbl) ? "prod: cuda ordered replay" : "prod: cuda saturating magnitude product";
+	const int rc = prod_dispatch(a, basetype(a.b->ttype), t2, skip_nils, out, st);
+	tl_prod_nil_if_empty = true;
+	bool ok = rc > 0 && !(st[0] & 1);
+	if (rc < 0)
+		set_err("BATprod: type combination (mul(%s)->%s) not supported.\n", atomname(a.b->ttype), atomname(tp));
+	else if (rc > 0 && (st[0] & 1))
+		set_err("22003!overflow in product aggregate.\n");
+	if (ok)
+		ok = cuda_ok(cudaMemcpyAsync(&c->slot_h->v[8], out, 16, cudaMemcpyDeviceToHost, c->stream), "read product") && stream_sync();
+	dev_free(out);
+	if (!ok)
+		return B200_FAIL;
+	memcpy(res, &c->slot_h->v[8], w);
+	return B200_SUCCEED;
 }

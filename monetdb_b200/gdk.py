@@ -848,6 +848,17 @@ def BATsum(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if
     return out
 
 
+_sig("b200_BATprod", C.c_int, C.c_void_p, C.c_int, _P, _P, C.c_bool, C.c_bool)
+
+
+def BATprod(tp: int, b: BAT, s: BAT | None = None, skip_nils: bool = True, nil_if_empty: bool = True) -> np.ndarray:
+    """BATprod (gdk_aggr.c:1650): 1-element array of the result type"""
+    out = np.zeros(1, dtype=NP_OF[tp])
+    if lib.b200_BATprod(_vp(out), tp, b._p, _ptr(s), skip_nils, nil_if_empty) != 1:
+        _fail("BATprod")
+    return out
+
+
 # ------------------------------------------------------------------ window functions (gdk_analytic.h:21-42)
 _sig("b200_GDKanalyticaldiff", C.c_int, _P, _P, _P, C.c_void_p, C.c_int)
 _sig("b200_GDKanalyticalwindowbounds", C.c_int, _P, _P, _P, _P, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_bool, C.c_uint64)

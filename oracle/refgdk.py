@@ -147,6 +147,7 @@ def _load(nthreads: int = 0):
         "BATgroupmax": (P, [P, P, P, P, C.c_int, B]),
         "BATgroupavg": (C.c_int, [C.POINTER(P), C.POINTER(P), P, P, P, P, C.c_int, B, C.c_int]),
         "BATsum": (C.c_int, [V, C.c_int, P, P, B, B]),
+        "BATprod": (C.c_int, [V, C.c_int, P, P, B, B]),
         "BATgroupavg3": (C.c_int, [C.POINTER(P), C.POINTER(P), C.POINTER(P), P, P, P, P, B]),
         "BATgroupavg3combine": (P, [P, P, P, P, P, B]),
         "BATcalcavg": (C.c_int, [P, P, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
@@ -625,6 +626,16 @@ def BATsum(tp, b, s=None, skip_nils=True, nil_if_empty=True):
         msg = errbuf().strip()
         clrerr()
         raise RefError(msg or "BATsum failed")
+    return out
+
+
+def BATprod(tp, b, s=None, skip_nils=True, nil_if_empty=True):
+    out = np.zeros(1, dtype=NP_OF[tp])
+    rc = _bat.BATprod(_vp(out), tp, b.p, _p(s), skip_nils, nil_if_empty)
+    if rc != 1:
+        msg = errbuf().strip()
+        clrerr()
+        raise RefError(msg or "BATprod failed")
     return out
 
 

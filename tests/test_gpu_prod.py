@@ -173,3 +173,30 @@ def test_trivial_forms(gdk, ref):
     with pytest.raises(ref.RefError) as e2:
         ref.BATgroupprod(rb, rg5, None, None, T.bte, True)
     assert str(e1.value).strip() == str(e2.value).strip()
+
+
+# ------------------------------------------------------------------ BATprod, the scalar form (gdk_aggr.c:1650)
+@pytest.mark.parametrize("t1", [T.bte, T.int, T.lng, T.hge, T.flt, T.dbl])
+def test_batprod(gdk, ref, t1):
+    rng = np.random.default_rng(t1 + 55)
+    for n, small, zf, nf in ((0, 0, 0, 0), (1, 1.0, 0, 0), (300_007, 0.00005, 0.0, 0.0), (300_007, 0.00005, 0.0, 0.00001),
+                             (300_007, 0.0001, 0.00001, 0.0), (5000, 0.05, 0.0, 0.0), (64, 0.3, 0.02, 0.05)):
+        a = column(rng, t1, n, small, zf, nf)
+        b, rb = both(gdk, ref, a, t1, hseq=3)
+        cands = [(None, None)]
+        if n > 10:
+            c = np.sort(rng.choice(n, n // 2, replace=False)).astype(np.uint64) + 3
+            cands.append((gdk.BATfromhost(c, T.oid, sorted=True, key=True, nonil=True), ref.bat(c, ref.T.oid, sorted=True, key=True, nonil=True)))
+        for s, rs in cands:
+            for tp in RESULTS[t1]:
+                for skip in (True, False):
+                    for nie in (True, False):
+                        try:
+                            want = ref.BATprod(tp, rb, rs, skip, nie)
+                        except ref.RefError as ex:
+                            with pytest.raises(G.GDKError) as ei:
+                                gdk.BATprod(tp, b, s, skip, nie)
+                            assert str(ei.value).strip() == str(ex).strip()
+                            continue
+                        got = gdk.BATprod(tp, b, s, skip, nie)
+                        assert same_bits(got, want), (n, tp, skip, nie, got, want)
