@@ -797,6 +797,237 @@ CMP_BINARY(ge, NOTHING, NOTHING)
 CMP_BINARY(eq, COMMA_NILM_DECL, COMMA_NILM_ARG)
 CMP_BINARY(ne, COMMA_NILM_DECL, COMMA_NILM_ARG)
 
+CALC_BINARY(mod)
+
+/* ------------------------------------------------------------------ the rest of the calc surface: gdk_calc.h:12-95 */
+#define CALC_UNARY(OP)												\
+static BAT *(*real_BATcalc##OP)(BAT *, BAT *);									\
+BAT *														\
+BATcalc##OP(BAT *b, BAT *s)											\
+{														\
+	if (b == NULL || !bat_ok(b) || !bat_ok(s) || b->ttype == TYPE_void || !enter(BATcount(b)))			\
+		FORWARD(BATcalc##OP, b, s);										\
+	inarg ab = {0}, as = {0};											\
+	BAT *bn = NULL;													\
+	if (in_open(&ab, b) && in_open(&as, s)) {									\
+		b200_bat *r = b200_BATcalc##OP(ab.d, as.d);								\
+		bn = r ? out_bat(r) : fail(__func__);									\
+		n_device++;												\
+	} else														\
+		fail(__func__);												\
+	in_close(&as);													\
+	in_close(&ab);													\
+	return bn;													\
+}
+CALC_UNARY(not)
+CALC_UNARY(negate)
+CALC_UNARY(absolute)
+CALC_UNARY(iszero)
+CALC_UNARY(sign)
+CALC_UNARY(isnil)
+CALC_UNARY(isnotnil)
+
+/* binary operators without a result-type argument; BB / BC / CB = the names of the bat-bat, bat-cst, cst-bat forms */
+#define CALC_NOTP(BB, BC, CB)											\
+static BAT *(*real_##BB)(BAT *, BAT *, BAT *, BAT *);								\
+BAT *														\
+BB(BAT *b1, BAT *b2, BAT *s1, BAT *s2)										\
+{														\
+	if (b1 == NULL || b2 == NULL || !bat_ok(b1) || !bat_ok(b2) || !bat_ok(s1) || !bat_ok(s2) ||			\
+	    b1->ttype == TYPE_void || b2->ttype == TYPE_void || !enter(BATcount(b1)))					\
+		FORWARD(BB, b1, b2, s1, s2);										\
+	inarg a1 = {0}, a2 = {0}, c1 = {0}, c2 = {0};									\
+	BAT *bn = NULL;													\
+	if (in_open(&a1, b1) && in_open(&a2, b2) && in_open(&c1, s1) && in_open(&c2, s2)) {				\
+		b200_bat *r = b200_##BB(a1.d, a2.d, c1.d, c2.d);							\
+		bn = r ? out_bat(r) : fail(__func__);									\
+		n_device++;												\
+	} else														\
+		fail(__func__);												\
+	in_close(&c2);													\
+	in_close(&c1);													\
+	in_close(&a2);													\
+	in_close(&a1);													\
+	return bn;													\
+}														\
+static BAT *(*real_##BC)(BAT *, const ValRecord *, BAT *);							\
+BAT *														\
+BC(BAT *b, const ValRecord *v, BAT *s)										\
+{														\
+	if (b == NULL || v == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(v->vtype) || v->vtype == TYPE_void ||	\
+	    b->ttype == TYPE_void || !enter(BATcount(b)))								\
+		FORWARD(BC, b, v, s);											\
+	inarg ab = {0}, as = {0};											\
+	BAT *bn = NULL;													\
+	if (in_open(&ab, b) && in_open(&as, s)) {									\
+		b200_bat *r = b200_##BC(ab.d, VALptr(v), v->vtype, as.d);						\
+		bn = r ? out_bat(r) : fail(__func__);									\
+		n_device++;												\
+	} else														\
+		fail(__func__);												\
+	in_close(&as);													\
+	in_close(&ab);													\
+	return bn;													\
+}														\
+static BAT *(*real_##CB)(const ValRecord *, BAT *, BAT *);							\
+BAT *														\
+CB(const ValRecord *v, BAT *b, BAT *s)										\
+{														\
+	if (b == NULL || v == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(v->vtype) || v->vtype == TYPE_void ||	\
+	    b->ttype == TYPE_void || !enter(BATcount(b)))								\
+		FORWARD(CB, v, b, s);											\
+	inarg ab = {0}, as = {0};											\
+	BAT *bn = NULL;													\
+	if (in_open(&ab, b) && in_open(&as, s)) {									\
+		b200_bat *r = b200_##CB(VALptr(v), v->vtype, ab.d, as.d);						\
+		bn = r ? out_bat(r) : fail(__func__);									\
+		n_device++;												\
+	} else														\
+		fail(__func__);												\
+	in_close(&as);													\
+	in_close(&ab);													\
+	return bn;													\
+}
+CALC_NOTP(BATcalcand, BATcalcandcst, BATcalccstand)
+CALC_NOTP(BATcalcor, BATcalcorcst, BATcalccstor)
+CALC_NOTP(BATcalcxor, BATcalcxorcst, BATcalccstxor)
+CALC_NOTP(BATcalclsh, BATcalclshcst, BATcalccstlsh)
+CALC_NOTP(BATcalcrsh, BATcalcrshcst, BATcalccstrsh)
+/* min / max: the cst-first forms are wrappers of the cst-second ones in the reference too (gdk_calc.c:1530,1708,2213,2365) */
+#define b200_BATcalccstmin(v, t, b, s) b200_BATcalcmincst(b, v, t, s)
+#define b200_BATcalccstmin_no_nil(v, t, b, s) b200_BATcalcmincst_no_nil(b, v, t, s)
+#define b200_BATcalccstmax(v, t, b, s) b200_BATcalcmaxcst(b, v, t, s)
+#define b200_BATcalccstmax_no_nil(v, t, b, s) b200_BATcalcmaxcst_no_nil(b, v, t, s)
+CALC_NOTP(BATcalcmin, BATcalcmincst, BATcalccstmin)
+CALC_NOTP(BATcalcmin_no_nil, BATcalcmincst_no_nil, BATcalccstmin_no_nil)
+CALC_NOTP(BATcalcmax, BATcalcmaxcst, BATcalccstmax)
+CALC_NOTP(BATcalcmax_no_nil, BATcalcmaxcst_no_nil, BATcalccstmax_no_nil)
+
+/* between / ifthenelse (gdk_calc.h:87-95) */
+static BAT *(*real_BATcalcbetween)(BAT *, BAT *, BAT *, BAT *, BAT *, BAT *, bool, bool, bool, bool, bool);
+BAT *
+BATcalcbetween(BAT *b, BAT *lo, BAT *hi, BAT *s, BAT *slo, BAT *shi, bool symmetric, bool linc, bool hinc, bool nils_false, bool anti)
+{
+	if (b == NULL || lo == NULL || hi == NULL || !bat_ok(b) || !bat_ok(lo) || !bat_ok(hi) || !bat_ok(s) || !bat_ok(slo) || !bat_ok(shi) ||
+	    b->ttype == TYPE_void || lo->ttype == TYPE_void || hi->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcbetween, b, lo, hi, s, slo, shi, symmetric, linc, hinc, nils_false, anti);
+	inarg ab = {0}, al = {0}, ah = {0}, as = {0}, asl = {0}, ash = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&al, lo) && in_open(&ah, hi) && in_open(&as, s) && in_open(&asl, slo) && in_open(&ash, shi)) {
+		b200_bat *r = b200_BATcalcbetween(ab.d, al.d, ah.d, as.d, asl.d, ash.d, symmetric, linc, hinc, nils_false, anti);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&ash);
+	in_close(&asl);
+	in_close(&as);
+	in_close(&ah);
+	in_close(&al);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATcalcbetweencstcst)(BAT *, const ValRecord *, const ValRecord *, BAT *, bool, bool, bool, bool, bool);
+BAT *
+BATcalcbetweencstcst(BAT *b, const ValRecord *lo, const ValRecord *hi, BAT *s, bool symmetric, bool linc, bool hinc, bool nils_false, bool anti)
+{
+	if (b == NULL || lo == NULL || hi == NULL || !bat_ok(b) || !bat_ok(s) || !type_ok(lo->vtype) || !type_ok(hi->vtype) ||
+	    lo->vtype == TYPE_void || hi->vtype == TYPE_void || b->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcbetweencstcst, b, lo, hi, s, symmetric, linc, hinc, nils_false, anti);
+	inarg ab = {0}, as = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&as, s)) {
+		b200_bat *r = b200_BATcalcbetweencstcst(ab.d, VALptr(lo), lo->vtype, VALptr(hi), hi->vtype, as.d, symmetric, linc, hinc, nils_false, anti);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&as);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATcalcifthenelse)(BAT *, BAT *, BAT *);
+BAT *
+BATcalcifthenelse(BAT *b, BAT *b1, BAT *b2)
+{
+	if (b == NULL || b1 == NULL || b2 == NULL || !bat_ok(b) || !bat_ok(b1) || !bat_ok(b2) || b->ttype == TYPE_void ||
+	    b1->ttype == TYPE_void || b2->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcifthenelse, b, b1, b2);
+	inarg ab = {0}, a1 = {0}, a2 = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&a1, b1) && in_open(&a2, b2)) {
+		b200_bat *r = b200_BATcalcifthenelse(ab.d, a1.d, a2.d);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&a2);
+	in_close(&a1);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATcalcifthenelsecst)(BAT *, BAT *, const ValRecord *);
+BAT *
+BATcalcifthenelsecst(BAT *b, BAT *b1, const ValRecord *c2)
+{
+	if (b == NULL || b1 == NULL || c2 == NULL || !bat_ok(b) || !bat_ok(b1) || !type_ok(c2->vtype) || c2->vtype == TYPE_void ||
+	    b->ttype == TYPE_void || b1->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcifthenelsecst, b, b1, c2);
+	inarg ab = {0}, a1 = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&a1, b1)) {
+		b200_bat *r = b200_BATcalcifthenelsecst(ab.d, a1.d, VALptr(c2), c2->vtype);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&a1);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATcalcifthencstelse)(BAT *, const ValRecord *, BAT *);
+BAT *
+BATcalcifthencstelse(BAT *b, const ValRecord *c1, BAT *b2)
+{
+	if (b == NULL || b2 == NULL || c1 == NULL || !bat_ok(b) || !bat_ok(b2) || !type_ok(c1->vtype) || c1->vtype == TYPE_void ||
+	    b->ttype == TYPE_void || b2->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcifthencstelse, b, c1, b2);
+	inarg ab = {0}, a2 = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b) && in_open(&a2, b2)) {
+		b200_bat *r = b200_BATcalcifthencstelse(ab.d, VALptr(c1), c1->vtype, a2.d);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&a2);
+	in_close(&ab);
+	return bn;
+}
+
+static BAT *(*real_BATcalcifthencstelsecst)(BAT *, const ValRecord *, const ValRecord *);
+BAT *
+BATcalcifthencstelsecst(BAT *b, const ValRecord *c1, const ValRecord *c2)
+{
+	if (b == NULL || c1 == NULL || c2 == NULL || !bat_ok(b) || !type_ok(c1->vtype) || !type_ok(c2->vtype) || c1->vtype == TYPE_void ||
+	    c2->vtype == TYPE_void || b->ttype == TYPE_void || !enter(BATcount(b)))
+		FORWARD(BATcalcifthencstelsecst, b, c1, c2);
+	inarg ab = {0};
+	BAT *bn = NULL;
+	if (in_open(&ab, b)) {
+		b200_bat *r = b200_BATcalcifthencstelsecst(ab.d, VALptr(c1), c1->vtype, VALptr(c2), c2->vtype);
+		bn = r ? out_bat(r) : fail(__func__);
+		n_device++;
+	} else
+		fail(__func__);
+	in_close(&ab);
+	return bn;
+}
+
 /* ------------------------------------------------------------------ join: gdk.h:2266 */
 static gdk_return (*real_BATjoin)(BAT **, BAT **, BAT *, BAT *, BAT *, BAT *, bool, BUN);
 

@@ -101,6 +101,21 @@ def main():
                     "dangling": dump(R.BATdiff(fk, dim, None, None, False, False)),
                     "unique": dump(R.BATunique(c1, None)),
                     "convert": dump(R.BATconvert(c2, None, T.int, 0, 0, 0)), "decimal": dump(R.BATconvert(c1, None, T.lng, 0, 2, 0))}
+    # ---- CASE / BETWEEN / logic / unary / min-max / mod / shifts
+    x = R.bat(rng.integers(-1000, 1000, m).astype(np.int32), T.int, nonil=True)
+    y = R.bat(rng.integers(1, 50, m).astype(np.int32), T.int, nonil=True)
+    lo = R.bat(rng.integers(-500, 0, m).astype(np.int32), T.int, nonil=True)
+    hi = R.bat(rng.integers(0, 500, m).astype(np.int32), T.int, nonil=True)
+    cond = R.BATcalcbetween(x, lo, hi)
+    out["calc"] = {
+        "between": dump(cond), "case": dump(R.BATcalcifthenelse(cond, x, y)),
+        "mod": dump(R.BATcalc("mod", x, y, None, None, T.int)), "modcst": dump(R.BATcalccst("mod", x, 7, T.int, None, T.int)),
+        "and": dump(R.BATcalclogic("and", x, y)), "xorcst": dump(R.BATcalclogiccst("xor", x, 0x55, T.int)),
+        "not": dump(R.BATcalcunary("not", cond)), "neg": dump(R.BATcalcunary("negate", x)), "abs": dump(R.BATcalcunary("absolute", x)),
+        "sign": dump(R.BATcalcunary("sign", x)), "iszero": dump(R.BATcalcunary("iszero", x)),
+        "isnil": dump(R.BATcalcisnil(x)), "min": dump(R.BATcalcminmax("min", x, y)), "maxcst": dump(R.BATcalcminmaxcst("max", x, 3, T.int)),
+        "lsh": dump(R.BATcalcshiftcst("lsh", y, 3, T.int)), "rsh": dump(R.BATcalcshift("rsh", y, R.bat(np.full(m, 2, dtype=np.int32), T.int, nonil=True))),
+    }
     # ---- dictionary strings: GROUP BY two str flags + equality selects on a str column created by the real GDK
     rng = np.random.default_rng(11)
     ns = min(n, 200_000)

@@ -40,13 +40,13 @@ def test_shim_is_a_drop_in(ref, gdk):
     dev, fwd, hits, staged = shim["shim_stats"]
     assert dev >= 40, shim["shim_stats"]           # the plans ran on the device ...
     assert hits >= 25, shim["shim_stats"]          # ... with intermediates taken from the device-twin cache
-    for k in ("config1", "q1", "window", "order"):
+    for k in ("config1", "q1", "window", "order", "calc"):
         for name, d in plain[k].items():
             assert shim[k][name] == d, (k, name, d, shim[k][name])
     assert shim["q6"] == plain["q6"]
     # dictionary strings: BATgroup on str flags, (anti-)equality selects incl. the nil forms
     assert shim["str"] == plain["str"], (shim["str"], plain["str"])
-    assert dev >= 65, shim["shim_stats"]           # + the two str BATgroup calls, 12 str selects, the ORDER BY / join block
+    assert dev >= 80, shim["shim_stats"]           # + the two str BATgroup calls, 12 str selects, the ORDER BY / join block
     assert shim["join"] == plain["join"]
     assert shim["errors"] == plain["errors"], (shim["errors"], plain["errors"])
     assert "overflow" in plain["errors"]["mul_overflow"] and "division by zero" in plain["errors"]["div_zero"]
@@ -60,7 +60,9 @@ def test_shim_exports_reference_entry_points():
     have = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
     for s in ("BATselect", "BATthetaselect", "BATproject", "BATproject2", "BATgroup", "BATgroupsum", "BATgroupprod", "BATgroupcount", "BATgroupmin",
               "BATgroupmax", "BATgroupavg", "BATsum", "BATjoin", "BATleftjoin", "BATouterjoin", "BATsemijoin", "BATintersect", "BATdiff",
-              "BATunique", "BATconvert", "BATsort", "BATfirstn", "BATcalcadd", "BATcalcsub", "BATcalcmul", "BATcalcdiv",
+              "BATunique", "BATconvert", "BATsort", "BATfirstn", "BATcalcmod", "BATcalcand", "BATcalcxorcst", "BATcalcnot", "BATcalcisnil",
+              "BATcalcmin", "BATcalccstmax_no_nil", "BATcalclsh", "BATcalcbetween", "BATcalcbetweencstcst", "BATcalcifthenelse",
+              "BATcalcifthencstelsecst", "BATgroupprod", "BATcalcadd", "BATcalcsub", "BATcalcmul", "BATcalcdiv",
               "BATcalcmulcst", "BATcalccstsub", "BATcalclt", "BATcalceq", "GDKanalyticaldiff", "GDKanalyticalwindowbounds",
               "GDKanalyticalsum", "GDKanalyticalavg", "GDKanalyticalcount", "GDKanalyticalmin", "GDKanalyticalmax"):
         assert s in have, s
