@@ -203,6 +203,18 @@ template <typename T> struct AvgTreeIntOp {
 		if ((hge) (lng) a.sum == a.sum) {
 			/* the usual case: the sum fits 64 bits — one hardware-sized division instead of __divti3 */
 			const lng s = (lng) a.sum;
+			if ((lng) (int) s == s && (lng) (int) a.n == a.n) {
+				/* ... and usually 32: a native-width division */
+				const int s32 = (int) s, n32 = (int) a.n;
+				int q32 = s32 / n32, r32 = s32 - q32 * n32;
+				if (r32 < 0) {
+					q32--;
+					r32 += n32;
+				}
+				q = q32;
+				rr = r32;
+				return;
+			}
 			lng q64 = s / a.n, r64 = s - q64 * a.n;
 			if (r64 < 0) {
 				q64--;
@@ -308,6 +320,18 @@ template <typename T, bool EXACT> struct AvgIntegerOp {
 		if ((hge) (lng) a.sum == a.sum) {
 			/* the usual case: the sum fits 64 bits — one hardware-sized division instead of __divti3 */
 			const lng s = (lng) a.sum;
+			if ((lng) (int) s == s && (lng) (int) a.n == a.n) {
+				/* ... and usually 32: a native-width division */
+				const int s32 = (int) s, n32 = (int) a.n;
+				int q32 = s32 / n32, r32 = s32 - q32 * n32;
+				if (r32 < 0) {
+					q32--;
+					r32 += n32;
+				}
+				q = q32;
+				rr = r32;
+				return;
+			}
 			lng q64 = s / a.n, r64 = s - q64 * a.n;
 			if (r64 < 0) {
 				q64--;
