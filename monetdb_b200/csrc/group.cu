@@ -10,7 +10,9 @@
 //   A  one streaming pass records, per distinct key, the smallest candidate
 //      position holding it ("first row"), in a DIRECT table when the key domain
 //      is small (1-byte values, optionally x <= 256 prior groups; 2-byte values —
-//      the cases the reference serves with GRP_small_values, :607-654,921-939)
+//      the cases the reference serves with GRP_small_values, :607-654,921-939 — and,
+//      beyond the reference, 4- / 8-byte integers whose values span a small RANGE,
+//      found by one min/max pass: entry = value - min)
 //      or in an open-addressing HASH table whose slots hold that first row
 //      itself (keys are compared by reading the column at the slot's row, as the
 //      reference's link-array hash does, so any key width works lock-free);
@@ -28,6 +30,8 @@
 #define GRP_THREADS 256
 #define GRP_SHM_DOMAIN 4096	/* direct tables up to this many entries are privatised per CTA */
 #define GRP_SHM_HISTO 2048
+#define GRP_RANGED_MIN_ROWS ((uint64_t) 1 << 18)	/* below this the hash path is cheap and the extra range pass + sync is not */
+#define GRP_RANGED_MAX_ENTRIES ((u64) 1 << 20)	/* largest ranged direct table (8 MiB of first rows) */
 
 template <typename T> struct GrpSrc {
 	const T *vals;		/* dense: value of candidate position r is vals[r]; else vals[cand[r] - hseq] */
@@ -37,6 +41,9 @@ template <typename T> struct GrpSrc {
 	const oid *g;		/* prior group ids per candidate position, or NULL */
 	const unsigned char *g8;	/* their one-byte twin (SHADOW_GID8) when the prior BATgroup left one */
 	uint64_t n;
+	/* RANGED direct table (4- and 8-byte integers whose values span a small range): entry = value - lo, nil -> span - 1 */
+	unsigned span;		/* 0: not ranged */
+	T lo;
 	__device__ __forceinline__ oid gval(uint64_t r) const { return g8 ? (oid) g8[r] : g[r]; }
 	__device__ __forceinline__ T value(uint64_t r) const { return cand ? vals[cand[r] - hseq] : vals[r]; }
 	__device__ __forceinline__ oid rowoid(uint64_t r) const { return cand ? cand[r] : seq + r; }
@@ -47,10 +54,66 @@ template <typename T> struct GrpSrc {
 template <typename T, bool HASG> __device__ __forceinline__ unsigned direct_index(const GrpSrc<T> &src, uint64_t r)
 {
 	typedef typename KeyBits<T>::type U;
-	unsigned k = (unsigned) (U) src.value(r);
-	if (HASG)
-		k |= (unsigned) src.gval(r) << (8 * sizeof(T));
-	return k;
+	if constexpr (sizeof(T) >= 4) {
+		if constexpr (Atom<T>::is_float || sizeof(T) > 8) {
+			return 0;	/* never direct */
+		} else {
+			const T v = src.value(r);
+			unsigned k = Atom<T>::is_nil(v) ? src.span - 1 : (unsigned) ((u64) v - (u64) src.lo);
+			if (HASG)
+				k += src.span * (unsigned) src.gval(r);
+			return k;
+		}
+	} else {
+		unsigned k = (unsigned) (U) src.value(r);
+		if (HASG)
+			k |= (unsigned) src.gval(r) << (8 * sizeof(T));
+		return k;
+	}
+}
+
+// smallest / largest non-nil value of the candidates as order-preserving unsigned images; out[2] = a nil was seen
+template <typename T>
+__global__ void __launch_bounds__(GRP_THREADS)
+grp_minmax_kernel(GrpSrc<T> src, unsigned long long *__restrict__ out)
+{
+	u64 mn = ~0ULL, mx = 0;
+	bool nil = false;
+	const uint64_t stride = (uint64_t) gridDim.x * GRP_THREADS;
+	constexpr int U8 = 8;	/* independent loads in flight per thread */
+	for (uint64_t r0 = (uint64_t) blockIdx.x * GRP_THREADS + threadIdx.x; r0 < src.n; r0 += stride * U8) {
+		T v[U8];
+#pragma unroll
+		for (int u = 0; u < U8; u++) {
+			const uint64_t r = r0 + u * stride;
+			v[u] = r < src.n ? src.value(r) : Atom<T>::nil();
+		}
+		bool tail = false;
+#pragma unroll
+		for (int u = 0; u < U8; u++) {
+			if (Atom<T>::is_nil(v[u])) {
+				tail |= r0 + u * stride < src.n;
+				continue;
+			}
+			const u64 img = (u64) (long long) v[u] ^ (1ULL << 63);
+			mn = img < mn ? img : mn;
+			mx = img > mx ? img : mx;
+		}
+		nil |= tail;
+	}
+	for (int o = 16; o > 0; o >>= 1) {
+		const u64 a = __shfl_down_sync(0xffffffffu, mn, o), b = __shfl_down_sync(0xffffffffu, mx, o);
+		mn = a < mn ? a : mn;
+		mx = b > mx ? b : mx;
+	}
+	if ((threadIdx.x & 31) == 0) {
+		if (mn != ~0ULL) {
+			atomicMin(&out[0], mn);
+			atomicMax(&out[1], mx);
+		}
+	}
+	if (nil)
+		out[2] = 1;
 }
 
 template <typename T, bool HASG, bool SHM>
@@ -583,14 +646,17 @@ static inline u64 next_pow2(u64 x)
 }
 
 template <typename T, bool HASG>
-static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat **enp, b200_bat **hnp, bool want_e, bool want_h)
+static bool group_run(GrpSrc<T> src, u64 maxgrp, b200_bat *gn, b200_bat **enp, b200_bat **hnp, bool want_e, bool want_h)
 {
 	Ctx *c = ctx();
 	const uint64_t n = src.n;
 	const unsigned sgrid = grid_for(n, GRP_THREADS * 4, NSM * 8);
+	constexpr bool DIRECT_OK = !Atom<T>::is_float && sizeof(T) <= 8;
 	GrpTemps t;
 	int mode;		/* 0 direct/shared, 1 direct/global, 2 hash */
 	u64 nentries;
+	src.span = 0;
+	src.lo = 0;
 	if (sizeof(T) == 1 && (!HASG || maxgrp < 256)) {
 		nentries = HASG ? 256 * (maxgrp + 1) : 256;
 		mode = nentries <= GRP_SHM_DOMAIN ? 0 : 1;
@@ -601,6 +667,35 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 		mode = 2;
 		nentries = 0;
 	}
+	if constexpr (DIRECT_OK && sizeof(T) >= 4) {
+		/* wide integers that only take a small range of values (dimension keys, codes, dates of a few years): one
+		 * pass finds the range; when it — times the prior groups — fits a direct table, no hashing is needed */
+		if (n >= GRP_RANGED_MIN_ROWS && (!HASG || maxgrp < GRP_RANGED_MAX_ENTRIES)) {
+			unsigned long long *mm = (unsigned long long *) scratch_get(64);
+			static const unsigned long long init[3] = {~0ULL, 0, 0};
+			if (mm == nullptr || !cuda_ok(cudaMemcpyAsync(mm, init, 24, cudaMemcpyHostToDevice, c->stream), "init minmax"))
+				return false;
+			{
+				KTimer kt("group_minmax", n * sizeof(T));
+				grp_minmax_kernel<T><<<grid_for(n, GRP_THREADS * 8, NSM * 8), GRP_THREADS, 0, c->stream>>>(src, mm);
+			}
+			COUNT_LAUNCH();
+			if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, mm, 24, cudaMemcpyDeviceToHost, c->stream), "read minmax") || !stream_sync())
+				return false;
+			const u64 imn = c->slot_h->v[0], imx = c->slot_h->v[1];
+			const u64 range = imn == ~0ULL ? 1 : imx - imn + 1;	/* images are order-preserving: their distance is the values' */
+			if (range != 0 && range < GRP_RANGED_MAX_ENTRIES) {
+				const u64 span = range + 1;	/* + the nil entry */
+				const u64 ent = span * (HASG ? maxgrp + 1 : 1);
+				if (ent <= GRP_RANGED_MAX_ENTRIES) {
+					src.span = (unsigned) span;
+					src.lo = imn == ~0ULL ? (T) 0 : (T) (long long) (imn ^ (1ULL << 63));
+					nentries = ent;
+					mode = nentries <= GRP_SHM_DOMAIN ? 0 : 1;
+				}
+			}
+		}
+	}
 	t.state = (unsigned *) dev_alloc(16);
 	if (t.state == nullptr)
 		return false;
@@ -608,7 +703,7 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 		t.table = (u64 *) dev_alloc(nentries * 8);
 		if (t.table == nullptr || !cuda_ok(cudaMemsetAsync(t.table, 0xff, nentries * 8, c->stream), "memset group table"))
 			return false;
-		if constexpr (sizeof(T) <= 2) {
+		if constexpr (DIRECT_OK) {
 			KTimer kt(HASG ? "group_first_g" : "group_first", n * (sizeof(T) + (HASG ? 8 : 0)));
 			bool fastb = false;
 			if constexpr (sizeof(T) == 1)
@@ -719,7 +814,7 @@ static bool group_run(const GrpSrc<T> &src, u64 maxgrp, b200_bat *gn, b200_bat *
 				(const unsigned char *) src.vals, src.g8, n, t.gidtab, (unsigned) nentries, gids, g8out, cnts, (unsigned) ngrp, t.state);
 		} else if (mode == 2) {
 			if (shisto) ASSIGN(2, true); else ASSIGN(2, false);
-		} else if constexpr (sizeof(T) <= 2) {
+		} else if constexpr (DIRECT_OK) {
 			if (mode == 0) {
 				if (shisto) ASSIGN(0, true); else ASSIGN(0, false);
 			} else {
