@@ -308,6 +308,9 @@ static bool aggr_accumulate_typed(const AggrSetup &a, bool skip_nils, int check_
 		}
 #undef REG_CASE
 		ctx()->algo = "aggr: cuda register accumulators";
+	} else if (bytes <= 48 * 1024 && !acc.niltrack) {
+		aggr_tab32_kernel<T1><<<grid, AGGR_THREADS, bytes, c->stream>>>(in, acc.cells, ngrp, flags);
+		ctx()->algo = "aggr: cuda shared-memory table, 32-bit halves";
 	} else if (bytes <= 48 * 1024) {
 		aggr_tab_kernel<T1, true><<<grid, AGGR_THREADS, bytes, c->stream>>>(in, acc.cells, ngrp, acc.niltrack, flags);
 		ctx()->algo = "aggr: cuda shared-memory table";

@@ -505,6 +505,81 @@ aggr_tab_kernel(AggrIn in, u64 *__restrict__ cells, unsigned ngrp, bool niltrack
 	}
 }
 
+// ---------------------------------------------------------------- SHM32: shared table of split cells
+// 64-bit shared-memory atomics compile to a compare-and-swap loop (SASS ATOMS.CAST.SPIN.64);
+// the native shared atomic is 32 bits wide.  Without nil tracking every cell is a plain
+// 64-bit sum, so it is kept as two 32-bit halves in separate arrays: a row adds the low
+// half of its digit with one ATOMS.ADD, and touches the high half only when that add
+// wrapped (the returned old value tells) or the digit is negative.  The number of wraps
+// counted is exactly floor(sum of low halves / 2^32), so lo | hi << 32 at the flush is
+// the same 64-bit sum modulo 2^64 the 64-bit table holds.
+__device__ static inline void shm32_add(unsigned *lo, unsigned *hi, unsigned idx, u64 v)
+{
+	const unsigned vl = (unsigned) v;
+	unsigned vh = (unsigned) (v >> 32);
+	if (vl != 0) {
+		const unsigned old = atomicAdd(&lo[idx], vl);
+		vh += (old + vl) < old;
+	}
+	if (vh != 0)
+		atomicAdd(&hi[idx], vh);
+}
+
+template <typename T1>
+__global__ void __launch_bounds__(AGGR_THREADS)
+aggr_tab32_kernel(AggrIn in, u64 *__restrict__ cells, unsigned ngrp, unsigned *__restrict__ flags)
+{
+	constexpr int ND = Digits<T1>::ND;
+	extern __shared__ u64 sh_cells[];
+	const AggrLayout L(ND, in.check, false);
+	const unsigned ncells = (unsigned) L.ncell * ngrp;
+	unsigned *lo = (unsigned *) sh_cells, *hi = lo + ncells;
+	for (unsigned i = threadIdx.x; i < 2 * ncells; i += AGGR_THREADS)
+		lo[i] = 0;
+	__syncthreads();
+	bool special = false;
+	const uint64_t stride = (uint64_t) gridDim.x * AGGR_THREADS;
+	constexpr int U = 4;	/* rows in flight per thread */
+	for (uint64_t k0 = (uint64_t) blockIdx.x * AGGR_THREADS + threadIdx.x; k0 < in.n; k0 += stride * U) {
+		T1 x[U];
+		oid gid[U];
+		bool ok[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const uint64_t k = k0 + u * stride;
+			ok[u] = k < in.n && aggr_fetch<T1>(in, k, x[u], gid[u]);
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			if (!ok[u] || Atom<T1>::is_nil(x[u]))
+				continue;
+			const unsigned gi = (unsigned) (gid[u] - in.gmin);
+			special |= is_special(x[u]);
+			i64 d[ND];
+			Digits<T1>::split(x[u], in.fexp, d);
+#pragma unroll
+			for (int e = 0; e < ND; e++)
+				if (d[e] != 0)
+					shm32_add(lo, hi, e * ngrp + gi, (u64) d[e]);
+			if (in.check && x[u] > 0) {
+#pragma unroll
+				for (int e = 0; e < ND; e++)
+					if (d[e] != 0)
+						shm32_add(lo, hi, (ND + e) * ngrp + gi, (u64) d[e]);
+			}
+			shm32_add(lo, hi, L.c_cnt * ngrp + gi, 1ULL);
+		}
+	}
+	if (__any_sync(0xffffffffu, special) && (threadIdx.x & 31) == 0)
+		atomicOr(flags, 1u);
+	__syncthreads();
+	for (unsigned i = threadIdx.x; i < ncells; i += AGGR_THREADS) {
+		const u64 v = (u64) lo[i] | (u64) hi[i] << 32;
+		if (v)
+			atomicAdd(&cells[i], v);
+	}
+}
+
 // ---------------------------------------------------------------- wide integers
 struct I192 {		/* two's complement, little endian words */
 	u64 w[3];

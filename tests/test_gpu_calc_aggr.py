@@ -236,6 +236,33 @@ def test_groupsum_avg_count(gdk, ref, ngrp, t1):
                 ref.BATgroupsum(rb, rg, None, None, T.hge if t1 in INT_TYPES else T.dbl, True)) if t1 in INT_TYPES else None
 
 
+@pytest.mark.parametrize("ngrp", [9, 300, 1000])
+@pytest.mark.parametrize("t1,tp,bits", [(T.int, T.lng, 31), (T.lng, T.hge, 62), (T.lng, T.lng, 40), (T.lng, T.lng, 62),
+                                         (T.hge, T.hge, 100), (T.hge, T.hge, 126), (T.int, T.int, 20), (T.int, T.int, 30)])
+def test_groupsum_wide_values_shared_table(gdk, ref, ngrp, t1, tp, bits):
+    """no nils, 9..1000 groups: the shared-memory table of 32-bit halves (aggr_tab32_kernel).  Values span
+    `bits` bits of both signs, so the low halves wrap many times and the high halves see negative digits; the
+    narrow result types run the overflow-checked form and, for the widest values, raise the reference's error"""
+    rng = np.random.default_rng(ngrp * 131 + bits)
+    n = 200003
+    if t1 == T.hge:
+        a = G.hge_from_ints([int(x) * (1 << (bits - 62)) + int(y)
+                             for x, y in zip(rng.integers(-(1 << 62), 1 << 62, n), rng.integers(0, 1 << 30, n))])
+    else:
+        a = rng.integers(-(1 << bits), 1 << bits, n, dtype=np.int64).astype(np.int32 if t1 == T.int else np.int64)
+    gids = rng.integers(0, ngrp, n, dtype=np.uint64)
+    gids[:ngrp] = np.arange(ngrp, dtype=np.uint64)
+    b, rb = both(gdk, ref, a, t1, hseq=0)
+    g, rg = both(gdk, ref, gids, T.oid, hseq=0)
+    e, re_ = gdk.BATdense(0, 0, ngrp), ref.dense(0, 0, ngrp)
+    _cmp_or_err(gdk, ref, lambda: gdk.BATgroupsum(b, g, e, None, tp, True), lambda: ref.BATgroupsum(rb, rg, re_, None, tp, True))
+    if t1 != T.hge:
+        # all-positive values: the sum of positives equals the sum, overflow is reached monotonically
+        b2, rb2 = both(gdk, ref, np.abs(np.asarray(a)), t1, hseq=0)
+        _cmp_or_err(gdk, ref, lambda: gdk.BATgroupsum(b2, g, e, None, tp, True), lambda: ref.BATgroupsum(rb2, rg, re_, None, tp, True))
+    assert_same(gdk.BATgroupcount(b, g, e, None, T.lng, True), ref.BATgroupcount(rb, rg, re_, None, T.lng, True))
+
+
 @pytest.mark.parametrize("ngrp", [1, 4, 9, 500, 7000])
 @pytest.mark.parametrize("t1", [T.bte, T.sht, T.int, T.lng, T.hge])
 def test_groupavg3_and_combine(gdk, ref, ngrp, t1):
