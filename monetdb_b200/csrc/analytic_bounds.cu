@@ -538,6 +538,212 @@ an_range_sorted_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 		atomicOr(&state[0], (unsigned long long) err);
 }
 
+// RANGE with ONE static non-negative integer limit on a nil-free order column that is ascending inside every partition
+// (ORDER BY output, the usual case): the tile's order values plus a halo of AN_HALO rows on the side the frame
+// extends to are staged in shared memory once, with coalesced loads, and every row finds its edge by a binary search in
+// shared memory — uniform trip count across a warp, no dependent global loads.  A row whose edge lies beyond the halo
+// (or beyond the partition part that is staged) continues with the galloping search in global memory.  The kernel
+// also verifies the precondition on the rows it stages — b[k-1] <= b[k] wherever k is not a partition start — and
+// raises state[1] when it does not hold; the caller then discards the result and runs the per-row walk, so the
+// separate an_sorted_check pass (and its host round trip) is not needed on this path.
+#define AN_HALO 1024
+// continuation of the staged search in global memory: row `good` is inside the frame of the row with value v and
+// lies at the edge of the staged rows; returns the outermost inside row of the partition [m, e)
+template <typename T>
+__device__ __noinline__ oid an_gallop_back(const T *__restrict__ bp, oid m, oid good, T v, unsigned long long ol64)
+{
+	auto inside = [&](oid j) -> bool { return (unsigned long long) v - (unsigned long long) bp[j] <= ol64; };
+	oid bad = 0;
+	bool have_bad = false;
+	for (oid step = 1;; step <<= 1) {
+		if (good - m < step) {
+			if (good != m) {
+				if (inside(m))
+					good = m;
+				else {
+					bad = m;
+					have_bad = true;
+				}
+			}
+			break;
+		}
+		const oid pos = good - step;
+		if (inside(pos))
+			good = pos;
+		else {
+			bad = pos;
+			have_bad = true;
+			break;
+		}
+	}
+	if (have_bad)
+		while (good - bad > 1) {
+			const oid mid = bad + (good - bad) / 2;
+			if (inside(mid))
+				good = mid;
+			else
+				bad = mid;
+		}
+	return good;
+}
+template <typename T>
+__device__ __noinline__ oid an_gallop_fwd(const T *__restrict__ bp, oid e, oid good, T v, unsigned long long ol64)
+{
+	auto inside = [&](oid j) -> bool { return (unsigned long long) bp[j] - (unsigned long long) v <= ol64; };
+	oid bad = 0;
+	bool have_bad = false;
+	for (oid step = 1;; step <<= 1) {
+		if (e - 1 - good < step) {
+			if (good != e - 1) {
+				if (inside(e - 1))
+					good = e - 1;
+				else {
+					bad = e - 1;
+					have_bad = true;
+				}
+			}
+			break;
+		}
+		const oid pos = good + step;
+		if (inside(pos))
+			good = pos;
+		else {
+			bad = pos;
+			have_bad = true;
+			break;
+		}
+	}
+	if (have_bad)
+		while (bad - good > 1) {
+			const oid mid = good + (bad - good) / 2;
+			if (inside(mid))
+				good = mid;
+			else
+				bad = mid;
+		}
+	return good;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(AN_THREADS)
+an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__restrict__ bp, unsigned long long ol64,
+		       bool preceding, oid *__restrict__ rb, unsigned long long *__restrict__ state)
+{
+	constexpr unsigned RPT = AN_TILE / AN_THREADS;	/* consecutive rows per thread */
+	const unsigned long long TMAX = (unsigned long long) Atom<T>::maxval();
+	__shared__ TileSegs ts;
+	__shared__ T sh[AN_TILE + AN_HALO + 1];
+	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
+	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
+	ts.load(S, cnt, base, last);
+	/* staged rows [wlo, whi]; always includes row base - 1 for the order check of row base */
+	const uint64_t wlo = preceding ? (base > AN_HALO ? base - AN_HALO : 0) : (base ? base - 1 : 0);
+	const uint64_t whi = preceding ? last : (last + AN_HALO < n ? last + AN_HALO : n - 1);
+	for (unsigned i = threadIdx.x; i <= (unsigned) (whi - wlo); i += AN_THREADS)
+		sh[i] = bp[wlo + i];
+	__syncthreads();
+	bool overflow = false, unsorted = false;
+	const uint64_t k0 = base + (uint64_t) threadIdx.x * RPT;
+	if (k0 <= last) {
+		/* On ascending data the edge of row k + 1 is never in front of row k's: the thread's first row searches
+		 * (binary, 32-bit indices into the staged rows), the others only advance the edge.  With data that is
+		 * not ascending everything below stays inside the staged rows / the partition and the result is void. */
+		oid m, e, out[RPT];
+		ts.locate(k0, m, e);
+		unsigned g = 0;
+		bool have = false;
+#pragma unroll
+		for (unsigned j = 0; j < RPT; j++) {
+			const uint64_t k = k0 + j;
+			out[j] = 0;
+			if (k > last)
+				break;
+			if (k >= e) {
+				ts.locate(k, m, e);
+				have = false;
+			}
+			const unsigned ik = (unsigned) (k - wlo);
+			const T v = sh[ik];
+			if (k > m)
+				unsorted |= sh[ik - 1] > v;
+			if (preceding) {
+				/* inside(w): v - w <= limit, exact in unsigned 64-bit arithmetic for w <= v */
+				const unsigned ilo = m > wlo ? (unsigned) (m - wlo) : 0;
+				unsigned a;
+				if (have) {
+					a = g;
+					while (a < ik && (unsigned long long) v - (unsigned long long) sh[a] > ol64)
+						a++;
+				} else {
+					a = ilo;
+					unsigned b = ik;	/* smallest staged row of [ilo, ik] that is inside; row k is */
+					while (a < b) {
+						const unsigned mid = (a + b) >> 1;
+						if ((unsigned long long) v - (unsigned long long) sh[mid] <= ol64)
+							b = mid;
+						else
+							a = mid + 1;
+					}
+				}
+				g = a;
+				have = true;
+				oid good = wlo + a;
+				if (a == ilo && good > m)	/* the frame reaches in front of the staged rows */
+					good = an_gallop_back<T>(bp, m, good, v, ol64);
+				if (good > m) {
+					/* the reference's walk subtracts the first row outside the frame too, with the
+					 * overflow check: v - w must not exceed the type's maximum */
+					const T w = good - 1 >= wlo ? sh[good - 1 - wlo] : bp[good - 1];
+					overflow |= (unsigned long long) v - (unsigned long long) w > TMAX;
+				}
+				out[j] = good;
+			} else {
+				const oid hi = e - 1 < whi ? e - 1 : whi;
+				const unsigned ihi = (unsigned) (hi - wlo);
+				unsigned a;
+				if (have) {
+					a = g > ik ? g : ik;
+					while (a < ihi && (unsigned long long) sh[a + 1] - (unsigned long long) v <= ol64)
+						a++;
+				} else {
+					a = ik;
+					unsigned b = ihi;	/* largest staged row of [ik, ihi] that is inside */
+					while (a < b) {
+						const unsigned mid = (a + b + 1) >> 1;
+						if ((unsigned long long) sh[mid] - (unsigned long long) v <= ol64)
+							a = mid;
+						else
+							b = mid - 1;
+					}
+				}
+				g = a;
+				have = true;
+				oid good = wlo + a;
+				if (a == ihi && hi < e - 1)
+					good = an_gallop_fwd<T>(bp, e, good, v, ol64);
+				if (good + 1 < e) {
+					const T w = good + 1 <= whi ? sh[good + 1 - wlo] : bp[good + 1];
+					overflow |= (unsigned long long) w - (unsigned long long) v > TMAX;
+				}
+				out[j] = good + 1;
+			}
+		}
+		if (k0 + RPT - 1 <= last) {
+			static_assert(RPT == 4, "two 16-byte stores per thread");
+			ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(rb + k0);	/* k0 is a multiple of 4: 32-byte aligned */
+			dst[0] = make_ulonglong2(out[0], out[1]);
+			dst[1] = make_ulonglong2(out[2], out[3]);
+		} else {
+			for (unsigned j = 0; j < RPT && k0 + j <= last; j++)
+				rb[k0 + j] = out[j];
+		}
+	}
+	if (overflow)
+		atomicOr(&state[0], (unsigned long long) AN_ERR_OVERFLOW);
+	if (__any_sync(0xffffffffu, unsorted) && (threadIdx.x & 31) == 0)
+		atomicOr(&state[1], 1ULL);
+}
+
 // ---------------------------------------------------------------- temporal RANGE frames
 // gdk_analytic_bounds.c:458-611: the order column is a date / daytime / timestamp, the bound an interval in
 // months (int) or milliseconds (lng).  Per row vmin = SUB(v, limit), vmax = ADD(v, limit) with the calendar
@@ -1070,7 +1276,47 @@ extern "C" b200_return b200_GDKanalyticalwindowbounds(b200_bat *r, const b200_ba
 			return B200_FAIL;
 		/* ascending inside every partition?  then search instead of walking */
 		tl_range_sorted = false;
-		if (atomsize(t1) <= 8) {
+		bool known_unsorted = false;
+		if (!temporal && l == nullptr && b->tnonil && (t1 == B200_bte || t1 == B200_sht || t1 == B200_int || t1 == B200_lng)) {
+			/* one static limit, no nils: optimistic staged search that checks the order itself */
+			hge tmax = 0;
+			switch (t1) {
+			case B200_bte: tmax = Atom<bte>::maxval(); break;
+			case B200_sht: tmax = Atom<sht>::maxval(); break;
+			case B200_int: tmax = Atom<int>::maxval(); break;
+			default: tmax = Atom<lng>::maxval(); break;
+			}
+			if (ilim <= tmax) {
+				const unsigned long long ol64 = (unsigned long long) ilim;
+				{
+					KTimer kt("an_range", n * (9 + atomsize(t1)));
+					switch (t1) {
+					case B200_bte: an_range_staged_kernel<bte><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(S.S, S.cnt, n, (const bte *) b->base, ol64, preceding, rb, state); break;
+					case B200_sht: an_range_staged_kernel<sht><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(S.S, S.cnt, n, (const sht *) b->base, ol64, preceding, rb, state); break;
+					case B200_int: an_range_staged_kernel<int><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(S.S, S.cnt, n, (const int *) b->base, ol64, preceding, rb, state); break;
+					default: an_range_staged_kernel<lng><<<an_tiles(n), AN_THREADS, 0, ctx()->stream>>>(S.S, S.cnt, n, (const lng *) b->base, ol64, preceding, rb, state); break;
+					}
+				}
+				COUNT_LAUNCH();
+				unsigned long long st[2];
+				if (!an_read_state(state, st))
+					return B200_FAIL;
+				if (st[1] == 0) {
+					ctx()->algo = "windowbounds: range, cuda shared-memory staged search (sorted partitions)";
+					if (st[0] & AN_ERR_OVERFLOW) {
+						set_err("22003!overflow in calculation.\n");
+						return B200_FAIL;
+					}
+					return bounds_done(r, n, true);
+				}
+				/* not ascending: the result is void, walk row by row */
+				known_unsorted = true;
+				state = an_state_init();
+				if (state == nullptr)
+					return B200_FAIL;
+			}
+		}
+		if (atomsize(t1) <= 8 && !known_unsorted) {
 			const bte *np = p ? (const bte *) p->base : nullptr;
 			const unsigned g = grid_for(n, 256, NSM * 16);
 			switch (t1) {

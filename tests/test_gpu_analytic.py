@@ -359,6 +359,49 @@ def test_config5_shape(gdk, ref):
         close(r.numpy(), rr.numpy(), T.dbl, True)
 
 
+@pytest.mark.parametrize("tt", [T.sht, T.int, T.lng])
+@pytest.mark.parametrize("preceding", [True, False])
+def test_range_bounds_staged_search(gdk, ref, tt, preceding):
+    """static limit, no nils, ascending partitions: the shared-memory staged search (an_range_staged_kernel), with
+    frames inside the halo, longer than the halo (the search continues in global memory), whole partitions, runs of
+    duplicates longer than a tile, and partitions from one row to many tiles"""
+    rng = np.random.default_rng(7 * tt + preceding)
+    for n, nparts, step in ((1, 1, 2), (1024, 1, 2), (1025, 2, 3), (20011, 1, 2), (20011, 7, 2), (20011, 900, 4), (60013, 5, 1)):
+        pkey, o = window(rng, n, nparts, tt, 0, step)
+        p, rp = flags(gdk, ref, pkey, T.int)
+        b, rb = both(gdk, ref, o, tt)
+        for lim in (1, 40, 400, 1500, 30000):
+            r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, p, None, lim, tt, T.lng, 1, preceding, 0)
+            assert "staged" in gdk.algorithm()
+            rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, rp, None, lim, tt, T.lng, 1, preceding, 0)
+            check_oid(r, rr)
+    # without a partition column
+    o = np.cumsum(rng.integers(0, 3, 5000)).astype(G.NP_OF[tt])
+    b, rb = both(gdk, ref, o, tt)
+    r = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, 5000), b, None, None, 9, tt, T.lng, 1, preceding, 0)
+    rr = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, 5000), rb, None, None, 9, tt, T.lng, 1, preceding, 0)
+    check_oid(r, rr)
+
+
+def test_range_bounds_staged_overflow(gdk, ref):
+    """the first row outside a frame is subtracted with the overflow check, also when it sits tiles away"""
+    n = 5000
+    for preceding in (True, False):
+        o = np.arange(n, dtype=np.int64)
+        if preceding:
+            o[0] = -(1 << 63) + 2          # rows whose frame start reaches row 0 subtract it: overflow
+        else:
+            o[-1] = (1 << 63) - 1
+            o[:-1] -= 10000                # negative values: v - max overflows
+        b, rb = both(gdk, ref, o, T.lng)
+        for lim in (3, 3000):
+            with pytest.raises(Exception) as e2:
+                ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), rb, None, None, lim, T.lng, T.lng, 1, preceding, 0)
+            with pytest.raises(G.GDKError) as e1:
+                gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), b, None, None, lim, T.lng, T.lng, 1, preceding, 0)
+            assert str(e1.value).strip() == str(e2.value).strip() == "22003!overflow in calculation."
+
+
 @pytest.mark.parametrize("tt", [T.int, T.lng, T.dbl])
 @pytest.mark.parametrize("preceding", [True, False])
 @pytest.mark.parametrize("order", ["random", "desc"])
