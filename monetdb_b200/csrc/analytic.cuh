@@ -108,6 +108,26 @@ __device__ __forceinline__ uint64_t seg_upper(const oid *__restrict__ S, uint64_
 	return lo;
 }
 
+// the same count found by one whole warp: 32 probes per step narrow [lo, hi] about 33-fold, so a list of 2^14
+// partitions takes 3 dependent loads instead of 14 (every tile kernel starts with two of these searches, with the
+// rest of the CTA waiting).  The answer must lie in [lo, hi]; all 32 lanes call it and get the result.
+__device__ __forceinline__ uint64_t seg_upper_warp(const oid *__restrict__ S, uint64_t lo, uint64_t hi, oid k)
+{
+	const unsigned lane = threadIdx.x & 31;
+	while (lo < hi) {
+		const uint64_t step = (hi - lo) / 33 + 1;
+		const uint64_t pos = lo + step * (lane + 1) - 1;
+		const bool le = pos < hi && S[pos] <= k;	/* monotone over the lanes */
+		const unsigned t = __popc(__ballot_sync(0xffffffffu, le));
+		if (t < 32) {
+			const uint64_t cap = lo + step * (t + 1) - 1;	/* first probe that was > k (or beyond hi) */
+			hi = cap < hi ? cap : hi;
+		}
+		lo += step * t;
+	}
+	return lo;
+}
+
 // The slice of a segment list that intersects one tile, staged in shared memory.
 struct TileSegs {
 	oid sm[AN_TILE + 2];
@@ -117,10 +137,14 @@ struct TileSegs {
 	// all threads of the CTA must call this
 	__device__ __forceinline__ void load(const oid *__restrict__ S, uint64_t cnt, uint64_t first, uint64_t last)
 	{
-		if (threadIdx.x == 0) {
-			uint64_t u0 = seg_upper(S, cnt, first), u1 = seg_upper(S, cnt, last);
-			q0 = u0 ? u0 - 1 : 0;
-			m = (unsigned) (u1 - q0);
+		if (threadIdx.x < 32) {		/* tile kernels run AN_THREADS (>= 32) threads */
+			const uint64_t u0 = seg_upper_warp(S, 0, cnt, first);
+			/* at most last - first starts lie inside the tile, and S is strictly ascending */
+			const uint64_t u1 = seg_upper_warp(S, u0, u0 + (last - first) < cnt ? u0 + (last - first) : cnt, last);
+			if (threadIdx.x == 0) {
+				q0 = u0 ? u0 - 1 : 0;
+				m = (unsigned) (u1 - q0);
+			}
 		}
 		__syncthreads();
 		for (unsigned i = threadIdx.x; i <= m; i += blockDim.x)
