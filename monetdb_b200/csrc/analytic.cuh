@@ -32,6 +32,9 @@ struct SegList {
 	oid *S = nullptr;	/* cnt starts + sentinel S[cnt] = n */
 	uint64_t cnt = 0, n = 0;
 	bool cached = false;	/* S belongs to the flag column's SHADOW_SEGLIST twin */
+	uint64_t token = 0;	/* cached: identity of this list (segment trees built over it are keyed by it) */
+	uint64_t maxlen1 = 0;	/* cached: longest partition + 1 once some aggregate measured it, else 0 */
+	const void *pbase = nullptr;	/* cached: the heap the twin hangs on */
 	~SegList() { if (S && !cached) dev_free(S); }
 };
 

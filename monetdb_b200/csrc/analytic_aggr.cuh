@@ -468,30 +468,60 @@ static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long
 		return false;
 	Tree<typename Op::Node> tree;
 	if (!Op::direct && fa.frame_type != 6) {
-		an_maxlen_kernel<<<grid_for(S.cnt, 256, NSM * 8), 256, 0, c->stream>>>(S.S, S.cnt, state + 1);
-		COUNT_LAUNCH();
-		if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, state + 1, 8, cudaMemcpyDeviceToHost, c->stream), "maxlen") ||
-		    !stream_sync() || !cuda_ok(cudaMemsetAsync(state + 1, 0, 8, c->stream), "state reset")) {
-			dev_free(state);
-			return false;
-		}
-		const uint64_t maxlen = c->slot_h->v[0];
-		for (int level = 1; level < AN_MAXLEV; level++) {
-			const uint64_t below = (maxlen + ((uint64_t) 1 << (4 * (level - 1))) - 1) >> (4 * (level - 1));
-			if (op_checked<Op>::value ? below <= 1 : below < AN_FANOUT)
-				break;
-			const uint64_t nslots = (n >> (4 * level)) + S.cnt + 1;
-			tree.lev[level] = (typename Op::Node *) dev_alloc(nslots * sizeof(typename Op::Node));
-			if (tree.lev[level] == nullptr) {
+		uint64_t maxlen;
+		if (S.maxlen1 != 0) {
+			maxlen = S.maxlen1 - 1;		/* measured by an earlier aggregate over this partition list */
+		} else {
+			an_maxlen_kernel<<<grid_for(S.cnt, 256, NSM * 8), 256, 0, c->stream>>>(S.S, S.cnt, state + 1);
+			COUNT_LAUNCH();
+			if (!cuda_ok(cudaMemcpyAsync(c->slot_h->v, state + 1, 8, cudaMemcpyDeviceToHost, c->stream), "maxlen") ||
+			    !stream_sync() || !cuda_ok(cudaMemsetAsync(state + 1, 0, 8, c->stream), "state reset")) {
 				dev_free(state);
 				return false;
 			}
-			tree.size[level] = nslots;
-			tree.nlev = level;
-			KTimer kt("an_tree_build", level == 1 ? n * sizeof(typename Op::In) : nslots * sizeof(typename Op::Node) * 17);
-			an_tree_build_kernel<Op><<<(unsigned) ((nslots + 255) / 256), 256, 0, c->stream>>>(
-				S.S, S.cnt, (const typename Op::In *) fa.b->base, level, tree.lev[level - 1], tree.lev[level], nslots, state);
-			COUNT_LAUNCH();
+			maxlen = c->slot_h->v[0];
+			if (S.cached)
+				shadow_set_a2(S.pbase, SHADOW_SEGLIST, n, maxlen + 1);
+		}
+		const uint64_t total = tree.plan(n, S.cnt, maxlen, op_checked<Op>::value);
+		/* The inner levels only depend on (value column, partition list, aggregate): a plan that runs the same
+		 * aggregate over several frames of one column (ROWS and RANGE, say) builds them once.  Kept as a twin of the
+		 * value column when this library owns it, keyed by the partition list's token; aggregates whose build can
+		 * fail (the overflow-checked sums) are not kept. */
+		static char op_tag;	/* one per instantiation: identifies the aggregate */
+		const bool keep = !op_checked<Op>::value && S.cached && S.token != 0 && fa.b->device >= 0 && fa.b->owns &&
+				  fa.b->parent == nullptr && shadow_enabled() && n <= ((uint64_t) 1 << 28);
+		Shadow sh;
+		if (total != 0 && keep && shadow_get(fa.b->base, SHADOW_TREE, n, sh) && sh.a0 == S.token &&
+		    sh.a1 == (uint64_t) (uintptr_t) &op_tag && sh.a2 == (uint64_t) tree.nlev && sh.a3 == total) {
+			tree.place((typename Op::Node *) sh.p);
+			tree.cached = true;
+		} else if (total != 0) {
+			typename Op::Node *blk = (typename Op::Node *) dev_alloc(total * sizeof(typename Op::Node));
+			if (blk == nullptr) {
+				dev_free(state);
+				return false;
+			}
+			tree.place(blk);
+			for (int level = 1; level <= tree.nlev; level++) {
+				const uint64_t nslots = tree.size[level];
+				KTimer kt("an_tree_build", level == 1 ? n * sizeof(typename Op::In) : nslots * sizeof(typename Op::Node) * 17);
+				an_tree_build_kernel<Op><<<(unsigned) ((nslots + 255) / 256), 256, 0, c->stream>>>(
+					S.S, S.cnt, (const typename Op::In *) fa.b->base, level, tree.lev[level - 1], tree.lev[level], nslots, state);
+				COUNT_LAUNCH();
+			}
+			if (keep && stream_sync()) {	/* published to other threads' streams only once it is complete */
+				Shadow put;
+				put.kind = SHADOW_TREE;
+				put.p = blk;
+				put.n = n;
+				put.a0 = S.token;
+				put.a1 = (uint64_t) (uintptr_t) &op_tag;
+				put.a2 = (uint64_t) tree.nlev;
+				put.a3 = total;
+				shadow_put(fa.b->base, put);
+				tree.cached = true;
+			}
 		}
 	}
 	{

@@ -5,6 +5,7 @@
 // The reference processes one partition after the other and one row after the other;
 // here every row is independent once it knows its partition [start, end), which it
 // gets from the staged segment list of analytic.cuh.
+#include <atomic>
 #include "analytic.cuh"
 
 // ---------------------------------------------------------------- shared helpers
@@ -58,6 +59,9 @@ bool an_partitions(const b200_bat *p, const b200_bat *o, uint64_t n, SegList &ou
 		out.cnt = sh.a0;
 		out.n = n;
 		out.cached = true;
+		out.token = sh.a1;
+		out.maxlen1 = sh.a2;
+		out.pbase = p->base;
 		return true;
 	}
 	FlagStart f{p ? (const bte *) p->base : nullptr, o ? (const bte *) o->base : nullptr};
@@ -69,8 +73,11 @@ bool an_partitions(const b200_bat *p, const b200_bat *o, uint64_t n, SegList &ou
 		s.p = out.S;
 		s.n = n;
 		s.a0 = out.cnt;
+		static std::atomic<uint64_t> next_token{1};
+		s.a1 = out.token = next_token.fetch_add(1);
 		shadow_put(p->base, s);
 		out.cached = true;
+		out.pbase = p->base;
 	}
 	return true;
 }
@@ -632,7 +639,10 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 	constexpr unsigned RPT = AN_TILE / AN_THREADS;	/* consecutive rows per thread */
 	const unsigned long long TMAX = (unsigned long long) Atom<T>::maxval();
 	__shared__ TileSegs ts;
-	__shared__ T sh[AN_TILE + AN_HALO + 1];
+	/* a thread works on 4 consecutive rows, so a warp reads the staged rows with a stride of 4 elements: one pad
+	 * element after every 16 keeps those reads (and the unit-stride staging writes) free of bank conflicts */
+	__shared__ T shp[AN_TILE + AN_HALO + 1 + (AN_TILE + AN_HALO + 1) / 16 + 1];
+	auto sh = [&](unsigned i) -> T & { return shp[i + (i >> 4)]; };
 	const uint64_t base = (uint64_t) blockIdx.x * AN_TILE;
 	const uint64_t last = (base + AN_TILE < n ? base + AN_TILE : n) - 1;
 	ts.load(S, cnt, base, last);
@@ -640,7 +650,7 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 	const uint64_t wlo = preceding ? (base > AN_HALO ? base - AN_HALO : 0) : (base ? base - 1 : 0);
 	const uint64_t whi = preceding ? last : (last + AN_HALO < n ? last + AN_HALO : n - 1);
 	for (unsigned i = threadIdx.x; i <= (unsigned) (whi - wlo); i += AN_THREADS)
-		sh[i] = bp[wlo + i];
+		sh(i) = bp[wlo + i];
 	__syncthreads();
 	bool overflow = false, unsorted = false;
 	const uint64_t k0 = base + (uint64_t) threadIdx.x * RPT;
@@ -663,23 +673,23 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 				have = false;
 			}
 			const unsigned ik = (unsigned) (k - wlo);
-			const T v = sh[ik];
+			const T v = sh(ik);
 			if (k > m)
-				unsorted |= sh[ik - 1] > v;
+				unsorted |= sh(ik - 1) > v;
 			if (preceding) {
 				/* inside(w): v - w <= limit, exact in unsigned 64-bit arithmetic for w <= v */
 				const unsigned ilo = m > wlo ? (unsigned) (m - wlo) : 0;
 				unsigned a;
 				if (have) {
 					a = g;
-					while (a < ik && (unsigned long long) v - (unsigned long long) sh[a] > ol64)
+					while (a < ik && (unsigned long long) v - (unsigned long long) sh(a) > ol64)
 						a++;
 				} else {
 					a = ilo;
 					unsigned b = ik;	/* smallest staged row of [ilo, ik] that is inside; row k is */
 					while (a < b) {
 						const unsigned mid = (a + b) >> 1;
-						if ((unsigned long long) v - (unsigned long long) sh[mid] <= ol64)
+						if ((unsigned long long) v - (unsigned long long) sh(mid) <= ol64)
 							b = mid;
 						else
 							a = mid + 1;
@@ -693,7 +703,7 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 				if (good > m) {
 					/* the reference's walk subtracts the first row outside the frame too, with the
 					 * overflow check: v - w must not exceed the type's maximum */
-					const T w = good - 1 >= wlo ? sh[good - 1 - wlo] : bp[good - 1];
+					const T w = good - 1 >= wlo ? sh(good - 1 - wlo) : bp[good - 1];
 					overflow |= (unsigned long long) v - (unsigned long long) w > TMAX;
 				}
 				out[j] = good;
@@ -703,14 +713,14 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 				unsigned a;
 				if (have) {
 					a = g > ik ? g : ik;
-					while (a < ihi && (unsigned long long) sh[a + 1] - (unsigned long long) v <= ol64)
+					while (a < ihi && (unsigned long long) sh(a + 1) - (unsigned long long) v <= ol64)
 						a++;
 				} else {
 					a = ik;
 					unsigned b = ihi;	/* largest staged row of [ik, ihi] that is inside */
 					while (a < b) {
 						const unsigned mid = (a + b + 1) >> 1;
-						if ((unsigned long long) sh[mid] - (unsigned long long) v <= ol64)
+						if ((unsigned long long) sh(mid) - (unsigned long long) v <= ol64)
 							a = mid;
 						else
 							b = mid - 1;
@@ -722,7 +732,7 @@ an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, cons
 				if (a == ihi && hi < e - 1)
 					good = an_gallop_fwd<T>(bp, e, good, v, ol64);
 				if (good + 1 < e) {
-					const T w = good + 1 <= whi ? sh[good + 1 - wlo] : bp[good + 1];
+					const T w = good + 1 <= whi ? sh(good + 1 - wlo) : bp[good + 1];
 					overflow |= (unsigned long long) w - (unsigned long long) v > TMAX;
 				}
 				out[j] = good + 1;

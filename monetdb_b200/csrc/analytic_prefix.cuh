@@ -292,7 +292,7 @@ template <typename T1> static bool an_prefix_get(const b200_bat *b, uint64_t n, 
 		dev_free(tcnt);
 	if (!ok)
 		return false;	/* ~PrefixArrays releases P / C */
-	if (cacheable) {
+	if (cacheable && stream_sync()) {	/* published to other threads' streams only once it is complete */
 		Shadow s;
 		s.kind = SHADOW_PREFIX;
 		s.p = out.P;

@@ -23,14 +23,41 @@ template <typename Node> struct TreeDev {
 };
 
 template <typename Node> struct Tree {
-	Node *lev[AN_MAXLEV] = {nullptr};
+	Node *lev[AN_MAXLEV] = {nullptr};	/* all inside block */
 	uint64_t size[AN_MAXLEV] = {0};
 	int nlev = 0;
+	Node *block = nullptr;
+	bool cached = false;	/* block belongs to the value column's SHADOW_TREE twin */
 	~Tree()
 	{
-		for (int i = 1; i <= nlev; i++)
-			if (lev[i])
-				dev_free(lev[i]);
+		if (block && !cached)
+			dev_free(block);
+	}
+	// levels needed for partitions of up to maxlen rows (to_root: build until one node is left, as the checked
+	// sums need; else stop when fewer than a full group is left, like GDKrebuild_segment_tree's callers use it)
+	// and their slot counts; returns the total number of slots (each level's start rounded to 16 slots)
+	uint64_t plan(uint64_t n, uint64_t nparts, uint64_t maxlen, bool to_root)
+	{
+		uint64_t total = 0;
+		nlev = 0;
+		for (int level = 1; level < AN_MAXLEV; level++) {
+			const uint64_t below = (maxlen + ((uint64_t) 1 << (4 * (level - 1))) - 1) >> (4 * (level - 1));
+			if (to_root ? below <= 1 : below < AN_FANOUT)
+				break;
+			size[level] = (n >> (4 * level)) + nparts + 1;
+			total += (size[level] + 15) & ~(uint64_t) 15;
+			nlev = level;
+		}
+		return total;
+	}
+	void place(Node *b)
+	{
+		block = b;
+		uint64_t off = 0;
+		for (int level = 1; level <= nlev; level++) {
+			lev[level] = b + off;
+			off += (size[level] + 15) & ~(uint64_t) 15;
+		}
 	}
 	TreeDev<Node> dev() const
 	{

@@ -147,7 +147,9 @@ enum { SHADOW_GID8 = 1 /* group ids < 256 as one byte per row */,
        SHADOW_SEGLIST = 3 /* a partition-flag column (GDKanalyticaldiff result): the list of partition starts */,
        SHADOW_PREFIX = 4 /* an integer value column used by window aggregates: running sums (+ non-nil counts) */,
        SHADOW_ORDERIDX = 5 /* the order index of a column (gdk_orderidx.c): its oids in ascending stable order; a0 = hseqbase
-			      the oids are based on */ };
+			      the oids are based on */,
+       SHADOW_TREE = 6 /* a value column used by framed window aggregates: the inner levels of the fan-out-16 segment
+			  trees of one aggregate over one partition list (a0 = the list's token, a1 = aggregate, a2 = levels) */ };
 struct Shadow {
 	int kind = 0;
 	void *p = nullptr, *p2 = nullptr;	/* owned device buffers */
@@ -159,6 +161,7 @@ size_t scratch_size();
 void shadow_put(const void *base, const Shadow &s);
 bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out);
 void shadow_drop(const void *base);
+void shadow_set_a2(const void *base, int kind, uint64_t n, uint64_t a2);	/* update one field of an existing twin */
 bool shadow_enabled();
 void *scratch_get(size_t bytes);	/* per-thread reusable device scratch */
 bool stream_sync();			/* sync + error check */

@@ -581,6 +581,15 @@ bool shadow_get(const void *base, int kind, uint64_t n, Shadow &out)
 	return false;
 }
 
+void shadow_set_a2(const void *base, int kind, uint64_t n, uint64_t a2)
+{
+	std::lock_guard<std::mutex> lk(g_shadow_mu);
+	auto r = g_shadows.equal_range(base);
+	for (auto it = r.first; it != r.second; ++it)
+		if (it->second.kind == kind && it->second.n == n)
+			it->second.a2 = a2;
+}
+
 void shadow_drop(const void *base)
 {
 	if (base == nullptr)

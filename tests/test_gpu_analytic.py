@@ -359,6 +359,56 @@ def test_config5_shape(gdk, ref):
         close(r.numpy(), rr.numpy(), T.dbl, True)
 
 
+def test_tree_twin_reuse_and_invalidation(gdk, ref):
+    """the inner tree levels of an aggregate are kept as a twin of the value column, keyed by the partition list:
+    reused for another frame over the same partitions, rebuilt for other partitions, another aggregate, and after the
+    column has been rewritten (here: a window sum written into the same result BAT twice)"""
+    rng = np.random.default_rng(99)
+    n = 120_000
+    pk1 = np.repeat(np.arange(6), n // 6).astype(np.int64)
+    pk2 = np.repeat(np.arange(40), n // 40).astype(np.int64)
+    vals = rng.integers(-10**9, 10**9, n, dtype=np.int64)
+    v, rv = both(gdk, ref, vals, T.lng)
+    o, ro = both(gdk, ref, np.arange(n, dtype=np.int64), T.lng)
+
+    def part(pk):
+        a, ra = both(gdk, ref, pk, T.lng)
+        return (gdk.GDKanalyticaldiff(gdk.colnew(T.bit, n), a, None, None, T.lng),
+                ref.GDKanalyticaldiff(ref.colnew(T.bit, n), ra, None, None, T.lng))
+
+    def bounds(p, rp, lo, hi):
+        s = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, lo, T.lng, T.lng, 0, True, 0)
+        e = gdk.GDKanalyticalwindowbounds(gdk.colnew(T.oid, n), o, p, None, hi, T.lng, T.lng, 0, False, 1)
+        rs = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, lo, T.lng, T.lng, 0, True, 0)
+        re_ = ref.GDKanalyticalwindowbounds(ref.colnew(T.oid, n), ro, rp, None, hi, T.lng, T.lng, 0, False, 1)
+        return s, e, rs, re_
+
+    def check(fn, b, rb, p, rp, fr, out_t=T.dbl):
+        s, e, rs, re_ = fr
+        r = gdk.GDKanalyticalfn(fn, gdk.colnew(out_t, n), p, None, b, s, e, T.lng, 0)
+        rr = ref.GDKanalyticalfn(fn, ref.colnew(out_t, n), rp, None, rb, rs, re_, T.lng, 0)
+        assert same_bits(r.numpy(), rr.numpy()), fn
+
+    p1, rp1 = part(pk1)
+    p2, rp2 = part(pk2)
+    f1a, f1b, f2 = bounds(p1, rp1, 700, 0), bounds(p1, rp1, 40, 5000), bounds(p2, rp2, 700, 300)
+    check("avg", v, rv, p1, rp1, f1a)
+    check("avg", v, rv, p1, rp1, f1b)           # same partitions: the twin is reused
+    check("avg", v, rv, p2, rp2, f2)            # other partitions: rebuilt
+    check("avg", v, rv, p1, rp1, f1a)           # and back
+    check("min", v, rv, p1, rp1, f1b, T.lng)    # another aggregate over the same column
+    check("avg", v, rv, p1, rp1, f1b)
+    # a column this library rewrites in place: the twin must not survive the rewrite
+    small, rsmall = both(gdk, ref, (vals % 1000).astype(np.int64), T.lng)
+    w, rw = gdk.colnew(T.lng, n), ref.colnew(T.lng, n)
+    for src, rsrc in ((small, rsmall), (o, ro)):
+        s, e, rs, re_ = f1a
+        w = gdk.GDKanalyticalsum(w, p1, None, src, s, e, T.lng, T.lng, 0)
+        rw = ref.GDKanalyticalsum(rw, rp1, None, rsrc, rs, re_, T.lng, T.lng, 0)
+        assert same_bits(w.numpy(), rw.numpy())
+        check("avg", w, rw, p1, rp1, f1b)
+
+
 @pytest.mark.parametrize("tt", [T.sht, T.int, T.lng])
 @pytest.mark.parametrize("preceding", [True, False])
 def test_range_bounds_staged_search(gdk, ref, tt, preceding):
