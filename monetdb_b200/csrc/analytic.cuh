@@ -43,6 +43,64 @@ static __global__ void an_set_u64(oid *p, oid v)
 	*p = v;
 }
 
+// partition starts: row 0 and every row whose p (or o) flag is set
+struct FlagStart {
+	const bte *p, *o;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const
+	{
+		return idx == 0 || (p && p[idx]) || (o && o[idx]);
+	}
+	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
+};
+// plain set bits of a bit column (peer-group starts for GROUPS frames)
+struct FlagBits {
+	const bte *b;
+	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const { return b[idx] != 0; }
+	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
+};
+
+#ifdef __CUDACC__
+// the mask pass of the compaction for a plain byte-flag column: a thread turns 32 consecutive flags (two 16-byte
+// loads) into one mask word, instead of one byte load per lane and a ballot
+__device__ __forceinline__ uint32_t flag_nibble(uint32_t x)
+{
+	const uint32_t m = ((((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) & 0x80808080u) >> 7;	/* bit 8k = byte k is non-zero */
+	return (m | m >> 7 | m >> 14 | m >> 21) & 0xfu;
+}
+template <int CHUNK>
+__global__ void __launch_bounds__(CP_THREADS)
+flag_mask_kernel(uint64_t n, const bte *__restrict__ p, uint32_t *__restrict__ words, uint32_t *__restrict__ counts)
+{
+	__shared__ unsigned total;
+	if (threadIdx.x == 0)
+		total = 0;
+	__syncthreads();
+	unsigned cnt = 0;
+	if (threadIdx.x < CHUNK / 32) {
+		const uint64_t idx = (uint64_t) blockIdx.x * CHUNK + (uint64_t) threadIdx.x * 32;
+		uint32_t word = 0;
+		if (idx + 32 <= n) {
+			const uint4 a = reinterpret_cast<const uint4 *>(p + idx)[0], b = reinterpret_cast<const uint4 *>(p + idx)[1];
+			word = flag_nibble(a.x) | flag_nibble(a.y) << 4 | flag_nibble(a.z) << 8 | flag_nibble(a.w) << 12 |
+			       flag_nibble(b.x) << 16 | flag_nibble(b.y) << 20 | flag_nibble(b.z) << 24 | flag_nibble(b.w) << 28;
+		} else {
+			for (unsigned k = 0; idx + k < n; k++)
+				word |= (uint32_t) (p[idx + k] != 0) << k;
+		}
+		if (idx == 0)
+			word |= 1u;	/* row 0 starts a partition */
+		words[idx >> 5] = word;
+		cnt = __popc(word);
+	}
+	cnt = __reduce_add_sync(0xffffffffu, cnt);
+	if ((threadIdx.x & 31) == 0 && cnt)
+		atomicAdd(&total, cnt);
+	__syncthreads();
+	if (threadIdx.x == 0)
+		counts[blockIdx.x] = total;
+}
+#endif
+
 // ordered compaction of the row positions for which f(idx) holds into an exactly
 // sized list (mask -> scan -> read the total -> allocate -> expand)
 template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
@@ -63,7 +121,19 @@ template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
 		return false;
 	{
 		KTimer kt("an_seg_mask", n);
-		compact_launch_mask(s, n, f);
+		bool done = false;
+		if constexpr (std::is_same<F, FlagStart>::value) {
+			if (f.p != nullptr && f.o == nullptr && ((uintptr_t) f.p & 15) == 0) {
+				if (s.chunk == CP_CHUNK)
+					flag_mask_kernel<CP_CHUNK><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f.p, s.words, s.counts);
+				else
+					flag_mask_kernel<CP_CHUNK_SMALL><<<(unsigned) s.nchunks, CP_THREADS, 0, c->stream>>>(n, f.p, s.words, s.counts);
+				COUNT_LAUNCH();
+				done = true;
+			}
+		}
+		if (!done)
+			compact_launch_mask(s, n, f);
 	}
 	compact_launch_scan(s);
 	if (!cuda_ok(cudaGetLastError(), "seglist launch") || !stream_sync())
@@ -79,22 +149,6 @@ template <typename F> static bool build_seglist(uint64_t n, F f, SegList &out)
 	COUNT_LAUNCH();
 	return cuda_ok(cudaGetLastError(), "seglist expand");
 }
-
-// partition starts: row 0 and every row whose p (or o) flag is set
-struct FlagStart {
-	const bte *p, *o;
-	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const
-	{
-		return idx == 0 || (p && p[idx]) || (o && o[idx]);
-	}
-	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
-};
-// plain set bits of a bit column (peer-group starts for GROUPS frames)
-struct FlagBits {
-	const bte *b;
-	__device__ __forceinline__ bool operator()(uint64_t idx, oid &ov) const { return b[idx] != 0; }
-	__device__ __forceinline__ oid at(uint64_t idx) const { return idx; }
-};
 
 #ifdef __CUDACC__
 // number of entries of S[0..cnt) that are <= k
