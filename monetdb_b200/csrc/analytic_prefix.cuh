@@ -63,15 +63,19 @@ __device__ __forceinline__ void ap_block_scan(uhge &sum, unsigned &cnt, uhge &to
 	__syncthreads();
 }
 
+// A CTA takes AP_SUB consecutive tiles (one entry of tsum / tcnt per CTA): the single-CTA scan of those entries is the
+// serial part of the build, and a CTA that only reduces one 16 KB tile spends most of its life in the reduction's barriers.
+#define AP_SUB 4
+#define AP_SUPER (AP_TILE * AP_SUB)
 template <typename T1>
 __global__ void __launch_bounds__(AP_THREADS)
 an_prefix_tile_kernel(const T1 *__restrict__ bp, uint64_t n, uhge *__restrict__ tsum, unsigned long long *__restrict__ tcnt)
 {
-	const uint64_t base = (uint64_t) blockIdx.x * AP_TILE;
+	const uint64_t base = (uint64_t) blockIdx.x * AP_SUPER;
 	uhge s = 0;
 	unsigned c = 0;
 #pragma unroll
-	for (int i = 0; i < AP_ITEMS; i++) {
+	for (int i = 0; i < AP_ITEMS * AP_SUB; i++) {
 		const uint64_t k = base + (uint64_t) i * AP_THREADS + threadIdx.x;
 		if (k < n) {
 			const T1 v = ld_stream(bp + k);
@@ -125,56 +129,65 @@ __global__ void __launch_bounds__(AP_THREADS)
 an_prefix_write_kernel(const T1 *__restrict__ bp, uint64_t n, const uhge *__restrict__ tsum,
 		       const unsigned long long *__restrict__ tcnt, uhge *__restrict__ P, unsigned long long *__restrict__ C)
 {
-	const uint64_t base = (uint64_t) blockIdx.x * AP_TILE + (uint64_t) threadIdx.x * AP_ITEMS;
-	T1 v[AP_ITEMS];
-	uhge s = 0;
-	unsigned c = 0;
-#pragma unroll
-	for (int i = 0; i < AP_ITEMS; i++) {
-		const uint64_t k = base + i;
-		v[i] = k < n ? bp[k] : Atom<T1>::nil();
-		if (!Atom<T1>::is_nil(v[i])) {
-			s += (uhge) (hge) v[i];
-			c++;
-		}
-	}
-	uhge ts;
-	unsigned tc;
-	ap_block_scan(s, c, ts, tc);
-	uhge run = tsum[blockIdx.x] + s;
-	unsigned long long rc = tcnt[blockIdx.x] + c;
-	if (base == 0 && n > 0) {
-		P[0] = 0;
-		if (C)
-			C[0] = 0;
-	}
 	/* a thread's 8 running totals are 128 consecutive bytes: written straight from the registers every store
 	 * instruction touches 32 different lines (ncu: LSU-bound at 39 % of DRAM peak).  They are staged in shared memory
 	 * (one element of padding per thread keeps the 16-byte accesses off each other's banks) and leave the CTA as
 	 * fully coalesced rows. */
 	__shared__ uhge sp[AP_TILE + AP_THREADS];
-	const unsigned sbase = threadIdx.x * (AP_ITEMS + 1);
-#pragma unroll
-	for (int i = 0; i < AP_ITEMS; i++) {
-		const uint64_t k = base + i;
-		if (k < n) {
-			if (!Atom<T1>::is_nil(v[i])) {
-				run += (uhge) (hge) v[i];
-				rc++;
-			}
-			if (C)
-				C[k + 1] = rc;
-		}
-		sp[sbase + i] = run;
+	uhge carry = tsum[blockIdx.x];			/* totals in front of the tile being written */
+	unsigned long long carryc = tcnt[blockIdx.x];
+	if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0) {
+		P[0] = 0;
+		if (C)
+			C[0] = 0;
 	}
-	__syncthreads();
-	const uint64_t tbase = (uint64_t) blockIdx.x * AP_TILE;
+	for (int sub = 0; sub < AP_SUB; sub++) {
+		const uint64_t tbase = (uint64_t) blockIdx.x * AP_SUPER + (uint64_t) sub * AP_TILE;
+		if (tbase >= n)
+			break;
+		const uint64_t base = tbase + (uint64_t) threadIdx.x * AP_ITEMS;
+		T1 v[AP_ITEMS];
+		uhge s = 0;
+		unsigned c = 0;
 #pragma unroll
-	for (int i = 0; i < AP_ITEMS; i++) {
-		const unsigned j = i * AP_THREADS + threadIdx.x;
-		const uint64_t k = tbase + j;
-		if (k < n)
-			P[k + 1] = sp[j + j / AP_ITEMS];
+		for (int i = 0; i < AP_ITEMS; i++) {
+			const uint64_t k = base + i;
+			v[i] = k < n ? bp[k] : Atom<T1>::nil();
+			if (!Atom<T1>::is_nil(v[i])) {
+				s += (uhge) (hge) v[i];
+				c++;
+			}
+		}
+		uhge ts;
+		unsigned tc;
+		ap_block_scan(s, c, ts, tc);
+		uhge run = carry + s;
+		unsigned long long rc = carryc + c;
+		const unsigned sbase = threadIdx.x * (AP_ITEMS + 1);
+#pragma unroll
+		for (int i = 0; i < AP_ITEMS; i++) {
+			const uint64_t k = base + i;
+			if (k < n) {
+				if (!Atom<T1>::is_nil(v[i])) {
+					run += (uhge) (hge) v[i];
+					rc++;
+				}
+				if (C)
+					C[k + 1] = rc;
+			}
+			sp[sbase + i] = run;
+		}
+		__syncthreads();
+#pragma unroll
+		for (int i = 0; i < AP_ITEMS; i++) {
+			const unsigned j = i * AP_THREADS + threadIdx.x;
+			const uint64_t k = tbase + j;
+			if (k < n)
+				P[k + 1] = sp[j + j / AP_ITEMS];
+		}
+		carry += ts;
+		carryc += tc;
+		__syncthreads();	/* sp is rewritten by the next tile */
 	}
 }
 
@@ -269,7 +282,7 @@ template <typename T1> static bool an_prefix_get(const b200_bat *b, uint64_t n, 
 		out.cached = true;
 		return true;
 	}
-	const uint64_t ntiles = (n + AP_TILE - 1) / AP_TILE;
+	const uint64_t ntiles = (n + AP_SUPER - 1) / AP_SUPER;
 	uhge *tsum = (uhge *) dev_alloc(ntiles * 16);
 	unsigned long long *tcnt = (unsigned long long *) dev_alloc(ntiles * 8);
 	out.P = (uhge *) dev_alloc((n + 1) * 16);
@@ -277,11 +290,17 @@ template <typename T1> static bool an_prefix_get(const b200_bat *b, uint64_t n, 
 	bool ok = tsum && tcnt && out.P && (!want_c || out.C);
 	if (ok) {
 		const T1 *bp = (const T1 *) b->base;
-		KTimer kt("an_prefix", n * (2 * sizeof(T1) + 16 + (out.C ? 8 : 0)));
-		an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
-		COUNT_LAUNCH();
-		an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
-		COUNT_LAUNCH();
+		{
+			KTimer kt("an_prefix_tile", n * sizeof(T1));
+			an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
+			COUNT_LAUNCH();
+		}
+		{
+			KTimer kt("an_prefix_scan", ntiles * 48);
+			an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
+			COUNT_LAUNCH();
+		}
+		KTimer kt("an_prefix", n * (sizeof(T1) + 16 + (out.C ? 8 : 0)));
 		an_prefix_write_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt, out.P, out.C);
 		COUNT_LAUNCH();
 		ok = cuda_ok(cudaGetLastError(), "prefix launch");
