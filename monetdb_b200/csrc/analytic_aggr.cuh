@@ -2,6 +2,7 @@
 // driver that builds the per-partition segment trees and runs the frame kernel.
 #pragma once
 #include "analytic_tree.cuh"
+#include "analytic_prefix.cuh"
 #include <type_traits>
 
 // ---- sum (gdk_analytic_func.c:1762-1796)
@@ -493,12 +494,19 @@ static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long
 		 * value column when this library owns it, keyed by the partition list's token; aggregates whose build can
 		 * fail (the overflow-checked sums) are not kept. */
 		static char op_tag;	/* one per instantiation: identifies the aggregate */
+		/* integer averages over a nil-free column: the inner levels get running totals too (an_tree_query_p0) */
+		bool level_totals = false;
+		if constexpr (op_prefix_leaves<Op>::value)
+			level_totals = P != nullptr && C == nullptr && !peers;
 		const bool keep = !op_checked<Op>::value && S.cached && S.token != 0 && fa.b->device >= 0 && fa.b->owns &&
 				  fa.b->parent == nullptr && shadow_enabled() && n <= ((uint64_t) 1 << 28);
 		Shadow sh;
 		if (total != 0 && keep && shadow_get(fa.b->base, SHADOW_TREE, n, sh) && sh.a0 == S.token &&
-		    sh.a1 == (uint64_t) (uintptr_t) &op_tag && sh.a2 == (uint64_t) tree.nlev && sh.a3 == total) {
+		    sh.a1 == (uint64_t) (uintptr_t) &op_tag && sh.a2 == (uint64_t) tree.nlev && sh.a3 == total &&
+		    (sh.p2 != nullptr || !level_totals)) {
 			tree.place((typename Op::Node *) sh.p);
+			if (level_totals)
+				tree.place_prefix((uhge *) sh.p2);
 			tree.cached = true;
 		} else if (total != 0) {
 			typename Op::Node *blk = (typename Op::Node *) dev_alloc(total * sizeof(typename Op::Node));
@@ -514,10 +522,36 @@ static bool an_run(const FrameArgs &fa, typename Op::Out *rb, unsigned long long
 					S.S, S.cnt, (const typename Op::In *) fa.b->base, level, tree.lev[level - 1], tree.lev[level], nslots, state);
 				COUNT_LAUNCH();
 			}
+			if constexpr (op_prefix_leaves<Op>::value) {
+				if (level_totals) {
+					uhge *pb = (uhge *) dev_alloc(tree.prefix_total() * 16);
+					lng *vals = (lng *) dev_alloc(tree.size[1] * 8);	/* level 1 is the largest */
+					if (pb == nullptr || vals == nullptr) {
+						dev_free(pb);
+						dev_free(vals);
+						dev_free(state);
+						return false;
+					}
+					tree.place_prefix(pb);
+					bool ok = true;
+					for (int level = 1; level <= tree.nlev && ok; level++) {
+						const uint64_t nslots = tree.size[level];
+						an_level_vals_kernel<typename Op::Node><<<(unsigned) ((nslots + 255) / 256), 256, 0, c->stream>>>(tree.lev[level], nslots, vals);
+						COUNT_LAUNCH();
+						ok = an_prefix_build_raw<lng>(vals, nslots, tree.plev[level], nullptr, "an_tree_prefix");
+					}
+					dev_free(vals);
+					if (!ok) {
+						dev_free(state);
+						return false;
+					}
+				}
+			}
 			if (keep && stream_sync()) {	/* published to other threads' streams only once it is complete */
 				Shadow put;
 				put.kind = SHADOW_TREE;
 				put.p = blk;
+				put.p2 = tree.pblock;
 				put.n = n;
 				put.a0 = S.token;
 				put.a1 = (uint64_t) (uintptr_t) &op_tag;

@@ -270,6 +270,34 @@ struct PrefixArrays {
 	}
 };
 
+// the three build kernels over a plain device array: P[0..n] (and C when given) must hold n + 1 entries
+template <typename T1> static bool an_prefix_build_raw(const T1 *bp, uint64_t n, uhge *P, unsigned long long *C, const char *kname)
+{
+	Ctx *c = ctx();
+	if (n == 0)
+		return cuda_ok(cudaMemsetAsync(P, 0, 16, c->stream), "prefix zero") &&
+		       (C == nullptr || cuda_ok(cudaMemsetAsync(C, 0, 8, c->stream), "prefix zero"));
+	const uint64_t ntiles = (n + AP_SUPER - 1) / AP_SUPER;
+	uhge *tsum = (uhge *) dev_alloc(ntiles * 16);
+	unsigned long long *tcnt = (unsigned long long *) dev_alloc(ntiles * 8);
+	bool ok = tsum && tcnt;
+	if (ok) {
+		KTimer kt(kname, n * (2 * sizeof(T1) + 16 + (C ? 8 : 0)));
+		an_prefix_tile_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt);
+		COUNT_LAUNCH();
+		an_prefix_scan_kernel<<<1, AP_THREADS, 0, c->stream>>>(tsum, tcnt, ntiles);
+		COUNT_LAUNCH();
+		an_prefix_write_kernel<T1><<<(unsigned) ntiles, AP_THREADS, 0, c->stream>>>(bp, n, tsum, tcnt, P, C);
+		COUNT_LAUNCH();
+		ok = cuda_ok(cudaGetLastError(), "prefix launch");
+	}
+	if (tsum)
+		dev_free(tsum);
+	if (tcnt)
+		dev_free(tcnt);
+	return ok;
+}
+
 template <typename T1> static bool an_prefix_get(const b200_bat *b, uint64_t n, PrefixArrays &out)
 {
 	Ctx *c = ctx();

@@ -19,6 +19,7 @@
 
 template <typename Node> struct TreeDev {
 	const Node *lev[AN_MAXLEV];	/* lev[0] unused */
+	const uhge *pl[AN_MAXLEV];	/* running totals of a level's node values over its slots, or NULL (an_tree_query_p0) */
 	int nlev;			/* highest built level */
 };
 
@@ -27,11 +28,34 @@ template <typename Node> struct Tree {
 	uint64_t size[AN_MAXLEV] = {0};
 	int nlev = 0;
 	Node *block = nullptr;
-	bool cached = false;	/* block belongs to the value column's SHADOW_TREE twin */
+	uhge *plev[AN_MAXLEV] = {nullptr};	/* all inside pblock (optional) */
+	uhge *pblock = nullptr;
+	bool cached = false;	/* block / pblock belong to the value column's SHADOW_TREE twin */
 	~Tree()
 	{
-		if (block && !cached)
-			dev_free(block);
+		if (!cached) {
+			if (block)
+				dev_free(block);
+			if (pblock)
+				dev_free(pblock);
+		}
+	}
+	// entries of the per-level running totals: size[level] + 1 each, every level's start rounded to 16 entries
+	uint64_t prefix_total() const
+	{
+		uint64_t total = 0;
+		for (int level = 1; level <= nlev; level++)
+			total += (size[level] + 1 + 15) & ~(uint64_t) 15;
+		return total;
+	}
+	void place_prefix(uhge *b)
+	{
+		pblock = b;
+		uint64_t off = 0;
+		for (int level = 1; level <= nlev; level++) {
+			plev[level] = b + off;
+			off += (size[level] + 1 + 15) & ~(uint64_t) 15;
+		}
 	}
 	// levels needed for partitions of up to maxlen rows (to_root: build until one node is left, as the checked
 	// sums need; else stop when fewer than a full group is left, like GDKrebuild_segment_tree's callers use it)
@@ -62,8 +86,10 @@ template <typename Node> struct Tree {
 	TreeDev<Node> dev() const
 	{
 		TreeDev<Node> d;
-		for (int i = 0; i < AN_MAXLEV; i++)
+		for (int i = 0; i < AN_MAXLEV; i++) {
 			d.lev[i] = lev[i];
+			d.pl[i] = plev[i];
+		}
 		d.nlev = nlev;
 		return d;
 	}
@@ -90,18 +116,22 @@ an_tree_build_kernel(const oid *__restrict__ S, uint64_t cnt, const typename Op:
 		else
 			hi = mid;
 	}
-	if (lo == 0)
+	typename Op::Acc acc;
+	Op::init(acc);
+	if (lo == 0) {
+		out[c] = Op::node(acc);
 		return;
+	}
 	const uint64_t q = lo - 1;
 	const oid ps = S[q], len = S[q + 1] - ps;
 	const uint64_t t = c - ((ps >> sh) + q);
 	const uint64_t below = (len + ((oid) 1 << (sh - 4)) - 1) >> (sh - 4);	/* nodes of q one level down */
-	if (t * AN_FANOUT >= below)
-		return;		/* gap slot */
+	if (t * AN_FANOUT >= below) {
+		out[c] = Op::node(acc);	/* gap slot: the empty node, so that running totals over the slots are defined */
+		return;
+	}
 	const uint64_t x0 = t * AN_FANOUT;
 	const uint64_t x1 = x0 + AN_FANOUT < below ? x0 + AN_FANOUT : below;
-	typename Op::Acc acc;
-	Op::init(acc);
 	unsigned err = 0;
 	if (level == 1) {
 		for (uint64_t x = x0; x < x1; x++)
@@ -114,6 +144,18 @@ an_tree_build_kernel(const oid *__restrict__ S, uint64_t cnt, const typename Op:
 	out[c] = Op::node(acc);
 	if (err)
 		atomicOr(&state[0], (unsigned long long) err);
+}
+
+// the values of one level's nodes as a lng column (nil = empty node or gap slot), the input of that level's running totals
+template <typename Node>
+__global__ void __launch_bounds__(256)
+an_level_vals_kernel(const Node *__restrict__ lev, uint64_t nslots, lng *__restrict__ out)
+{
+	const uint64_t c = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (c < nslots) {
+		const Node x = lev[c];
+		out[c] = x.has ? (lng) x.a : Atom<lng>::nil();
+	}
 }
 
 template <typename Op>
@@ -190,24 +232,29 @@ __device__ __forceinline__ void an_tree_query_p0(const TreeDev<typename Op::Node
 		tend = parent_end;
 	}
 	for (int level = 1; level <= t.nlev; level++) {
+		/* the inner levels the same way when the column has no nils (every node of a run then counts as one
+		 * value): a run of up to 15 nodes, of a different length in every lane, is one difference */
+		const uhge *__restrict__ PL = t.pl[level] ? t.pl[level] + (ps >> (4 * level)) + q : nullptr;
+		auto nodes = [&](uint64_t a, uint64_t b) {
+			if (PL)
+				Op::add_leaves(acc, (hge) (PL[b] - PL[a]), (lng) (b - a));
+			else
+				for (uint64_t pos = a; pos < b; pos++)
+					Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+		};
 		uint64_t parent_begin = begin / AN_FANOUT, parent_end = tend / AN_FANOUT;
 		if (parent_begin == parent_end) {
-			for (uint64_t pos = begin; pos < tend; pos++)
-				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			nodes(begin, tend);
 			break;
 		}
 		const uint64_t group_begin = parent_begin * AN_FANOUT;
 		if (begin != group_begin) {
-			const uint64_t limit = group_begin + AN_FANOUT;
-			for (uint64_t pos = begin; pos < limit; pos++)
-				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
+			nodes(begin, group_begin + AN_FANOUT);
 			parent_begin++;
 		}
 		const uint64_t group_end = parent_end * AN_FANOUT;
-		if (tend != group_end) {
-			for (uint64_t pos = group_end; pos < tend; pos++)
-				Op::add(acc, an_tree_node<Op>(t, bp, level, ps, q, pos), err);
-		}
+		if (tend != group_end)
+			nodes(group_end, tend);
 		begin = parent_begin;
 		tend = parent_end;
 	}

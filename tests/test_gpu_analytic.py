@@ -489,6 +489,24 @@ def test_avginteger(gdk, ref, tt, frame_type):
         assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
 
 
+@pytest.mark.parametrize("tt", [T.bte, T.sht, T.int, T.lng])
+@pytest.mark.parametrize("fn", ["avg", "avginteger"])
+def test_integer_averages_nil_free_framed(gdk, ref, tt, fn):
+    """framed integer averages over a column without nils: level 0 and the inner tree levels both come from running
+    totals (per-level totals of the node values), bit-exact with the reference's node walk"""
+    rng = np.random.default_rng(tt * 5 + len(fn))
+    for n, nparts, rows in SHAPES:
+        (p, op, s, e), (rp, rop, rs, re_) = frames(gdk, ref, n, nparts, rng, rows)
+        v = random_col(rng, tt, n, nilfrac=0.0)
+        b, rb = both(gdk, ref, v, tt)
+        out_t = T.dbl if fn == "avg" else tt
+        for _ in range(2):          # the second run takes the tree and its totals from the column's twin
+            r = gdk.GDKanalyticalfn(fn, gdk.colnew(out_t, n), p, op, b, s, e, tt, 0)
+            rr = ref.GDKanalyticalfn(fn, ref.colnew(out_t, n), rp, rop, rb, rs, re_, tt, 0)
+            assert same_bits(r.numpy(), rr.numpy())
+            assert (r.props()["nonil"], r.props()["nil"]) == (rr.props()["nonil"], rr.props()["nil"])
+
+
 # ---------------------------------------------------------------------------- temporal RANGE frames (a20)
 def _dates(rng, n, span_days=4000):
     """packed GDK dates (gdk_time.c:17-31) of random days after 1990-01-01, incl. month ends and leap days"""
