@@ -632,7 +632,7 @@ __device__ __noinline__ oid an_gallop_fwd(const T *__restrict__ bp, oid e, oid g
 }
 
 template <typename T>
-__global__ void __launch_bounds__(AN_THREADS)
+__global__ void __launch_bounds__(AN_THREADS, 6)
 an_range_staged_kernel(const oid *__restrict__ S, uint64_t cnt, uint64_t n, const T *__restrict__ bp, unsigned long long ol64,
 		       bool preceding, oid *__restrict__ rb, unsigned long long *__restrict__ state)
 {

@@ -264,7 +264,7 @@ __device__ __forceinline__ void an_tree_query_p0(const TreeDev<typename Op::Node
 // current peer group, 4 current peer group -> unbounded, 5 whole partition, 6 current row.
 // DIRECT ops (count(*)) need no tree: the answer is the frame length.
 template <typename Op, bool PEERS, bool P0 = false>
-__global__ void __launch_bounds__(AN_THREADS)
+__global__ void __launch_bounds__(AN_THREADS, 6)
 an_frame_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__restrict__ O, uint64_t ocnt, uint64_t n,
 		const typename Op::In *__restrict__ bp, const oid *__restrict__ fstart, const oid *__restrict__ fend,
 		int frame_type, TreeDev<typename Op::Node> tree, typename Op::Out *__restrict__ rb,
