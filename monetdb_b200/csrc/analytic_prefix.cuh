@@ -74,14 +74,38 @@ an_prefix_tile_kernel(const T1 *__restrict__ bp, uint64_t n, uhge *__restrict__ 
 	const uint64_t base = (uint64_t) blockIdx.x * AP_SUPER;
 	uhge s = 0;
 	unsigned c = 0;
+	bool done = false;
+	if constexpr (sizeof(T1) == 8) {
+		/* full super-tile of 8-byte values: 16-byte loads (base is a multiple of 8192 rows, so bp + base keeps
+		 * bp's alignment) */
+		if (base + AP_SUPER <= n && ((uintptr_t) bp & 15) == 0) {
+			const ulonglong2 *vp = reinterpret_cast<const ulonglong2 *>(bp + base);
 #pragma unroll
-	for (int i = 0; i < AP_ITEMS * AP_SUB; i++) {
-		const uint64_t k = base + (uint64_t) i * AP_THREADS + threadIdx.x;
-		if (k < n) {
-			const T1 v = ld_stream(bp + k);
-			if (!Atom<T1>::is_nil(v)) {
-				s += (uhge) (hge) v;
-				c++;
+			for (int i = 0; i < AP_ITEMS * AP_SUB / 2; i++) {
+				const ulonglong2 w = __ldcs(vp + i * AP_THREADS + threadIdx.x);
+				const T1 v0 = (T1) w.x, v1 = (T1) w.y;
+				if (!Atom<T1>::is_nil(v0)) {
+					s += (uhge) (hge) v0;
+					c++;
+				}
+				if (!Atom<T1>::is_nil(v1)) {
+					s += (uhge) (hge) v1;
+					c++;
+				}
+			}
+			done = true;
+		}
+	}
+	if (!done) {
+#pragma unroll
+		for (int i = 0; i < AP_ITEMS * AP_SUB; i++) {
+			const uint64_t k = base + (uint64_t) i * AP_THREADS + threadIdx.x;
+			if (k < n) {
+				const T1 v = ld_stream(bp + k);
+				if (!Atom<T1>::is_nil(v)) {
+					s += (uhge) (hge) v;
+					c++;
+				}
 			}
 		}
 	}
