@@ -61,6 +61,38 @@ def test_group_candidates(gdk, ref, tt):
     _check(gdk.BATgroup(b, gdk.BATdense(0, 1100, 5000)), ref.BATgroup(rb, ref.dense(0, 1100, 5000)))
 
 
+@pytest.mark.parametrize("tt", [T.int, T.lng, T.date, T.oid])
+def test_group_ranged_direct_table(gdk, ref, tt):
+    """>= 2^18 rows of a 4- or 8-byte integer key that only spans a small range: one min/max pass, then a direct table
+    indexed by value - min (nil has its own entry) instead of hashing — with nils, negative values, a candidate list,
+    a prior grouping, a misaligned view, and a range too wide for the table (falls back to the hash path)"""
+    rng = np.random.default_rng(int(tt) + 3)
+    n = 300_007
+    base = {T.int: -700, T.lng: -(1 << 40), T.date: 1_000_000, T.oid: 5}[tt]
+    for span, nilfrac in ((900, 0.03), (3, 0.0), (70_000, 0.01), (5_000_000, 0.0)):
+        a = (rng.integers(0, span, n) + base).astype(G.NP_OF[tt])
+        if nilfrac and tt != T.oid:
+            a[rng.random(n) < nilfrac] = np.iinfo(a.dtype).min
+        b, rb = both(gdk, ref, a, tt, hseq=3)
+        o, r = gdk.BATgroup(b), ref.BATgroup(rb)
+        _check(o, r)
+        if span == 900:
+            assert "direct" in gdk.algorithm()
+            # candidates (scalar gather path) and a prior grouping
+            for first in (1003, 1004):      # a 16-byte aligned and a misaligned dense slice
+                s, rs = gdk.BATdense(0, first, 280_001), ref.dense(0, first, 280_001)
+                _check(gdk.BATgroup(b, s), ref.BATgroup(rb, rs))
+            cand = np.sort(rng.choice(n, 270_000, replace=False)).astype(np.uint64) + np.uint64(3)
+            s, rs = both(gdk, ref, cand, T.oid, sorted=True, key=True)
+            _check(gdk.BATgroup(b, s), ref.BATgroup(rb, rs))
+            a1 = rng.integers(0, 5, n).astype(np.int32)
+            b1, r1 = both(gdk, ref, a1, T.int, hseq=3)
+            g1, rg1 = gdk.BATgroup(b1), ref.BATgroup(r1)
+            _check(gdk.BATgroup(b, None, g1[0], g1[1], g1[2]), ref.BATgroup(rb, None, rg1[0], rg1[1], rg1[2]))
+        if span == 5_000_000:
+            assert "hash" in gdk.algorithm()
+
+
 def test_group_trivial_and_sorted(gdk, ref):
     a = np.arange(1000, dtype=np.int32)
     b, rb = both(gdk, ref, a, T.int, key=True, sorted=True)
