@@ -233,11 +233,10 @@ an_frame_prefix_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__res
 	if (PEERS)
 		to.load(O, ocnt, base, last);
 	unsigned nils = 0;
-	for (unsigned i = threadIdx.x; i < AN_TILE; i += AN_THREADS) {
-		const uint64_t k = base + i;
-		if (k >= n)
-			break;
-		oid ps = 0, pe = n, fs, fe;
+	const bool framed = frame_type < 3 || frame_type > 6;
+	/* frame of row k, given its fstart / fend entries (framed types only) -> the sum, or nil */
+	auto row = [&](uint64_t k, oid fs, oid fe) -> hge {
+		oid ps = 0, pe = n;
 		if (need_part)
 			ts.locate(k, ps, pe);
 		switch (frame_type) {
@@ -253,20 +252,39 @@ an_frame_prefix_kernel(const oid *__restrict__ S, uint64_t cnt, const oid *__res
 		case 5: fs = ps; fe = pe; break;
 		case 6: fs = k; fe = k + 1; break;
 		default:
-			fs = fstart[k];
-			fe = fend[k];
 			if (fs < ps)
 				fs = ps;
 			if (fe > pe)
 				fe = pe;
 			break;
 		}
-		hge res = Atom<hge>::nil();
 		if (fs < fe && (C == nullptr || C[fe] != C[fs]))
-			res = (hge) (P[fe] - P[fs]);
-		else
-			nils++;
-		rb[k] = res;
+			return (hge) (P[fe] - P[fs]);
+		nils++;
+		return Atom<hge>::nil();
+	};
+	/* two consecutive rows per thread: 16-byte loads of the frame columns (8-byte loads per lane stream at little
+	 * more than half of that) and 32 contiguous bytes of results */
+	const bool vec = framed && (((uintptr_t) fstart | (uintptr_t) fend) & 15) == 0;
+	for (unsigned i = threadIdx.x * 2; i < AN_TILE; i += AN_THREADS * 2) {
+		const uint64_t k = base + i;
+		if (k >= n)
+			break;
+		if (k + 1 < n) {
+			ulonglong2 fsv = make_ulonglong2(0, 0), fev = make_ulonglong2(0, 0);
+			if (vec) {
+				fsv = *reinterpret_cast<const ulonglong2 *>(fstart + k);	/* k is even */
+				fev = *reinterpret_cast<const ulonglong2 *>(fend + k);
+			} else if (framed) {
+				fsv = make_ulonglong2(fstart[k], fstart[k + 1]);
+				fev = make_ulonglong2(fend[k], fend[k + 1]);
+			}
+			const hge r0 = row(k, fsv.x, fev.x), r1 = row(k + 1, fsv.y, fev.y);
+			rb[k] = r0;
+			rb[k + 1] = r1;
+		} else {
+			rb[k] = row(k, framed ? fstart[k] : 0, framed ? fend[k] : 0);
+		}
 	}
 	nils = __reduce_add_sync(0xffffffffu, nils);
 	if ((threadIdx.x & 31) == 0 && nils)
