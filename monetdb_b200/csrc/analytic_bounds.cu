@@ -96,7 +96,38 @@ __global__ void __launch_bounds__(256)
 an_diff_kernel(const T *__restrict__ b, const bte *__restrict__ np, int mode /* 0 none, 1 np, 2 npbit */, bte npb,
 	       uint64_t n, bte *__restrict__ r)
 {
-	for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
+	uint64_t done = 0;
+	if constexpr (sizeof(T) == 4 || sizeof(T) == 8) {
+		/* four consecutive rows per thread: 16-byte loads of the values (one-row-per-lane loads and byte stores
+		 * reach about half the bandwidth), the four flags leave as one 32-bit store */
+		if ((((uintptr_t) b) & 15) == 0 && (((uintptr_t) r | (uintptr_t) np) & 3) == 0) {
+			const uint64_t nquad = n / 4;
+			for (uint64_t q = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; q < nquad; q += (uint64_t) gridDim.x * blockDim.x) {
+				const uint64_t i0 = q * 4;
+				T v[5];
+				if constexpr (sizeof(T) == 8) {
+					const uint4 w0 = reinterpret_cast<const uint4 *>(b + i0)[0], w1 = reinterpret_cast<const uint4 *>(b + i0)[1];
+					memcpy(&v[1], &w0, 16);
+					memcpy(&v[3], &w1, 16);
+				} else {
+					const uint4 w0 = reinterpret_cast<const uint4 *>(b + i0)[0];
+					memcpy(&v[1], &w0, 16);
+				}
+				v[0] = i0 > 0 ? b[i0 - 1] : v[1];
+				unsigned keep4 = mode == 1 ? *reinterpret_cast<const unsigned *>(np + i0) : mode == 2 ? 0x01010101u * (unsigned) (unsigned char) npb : 0u;
+				unsigned out = 0;
+#pragma unroll
+				for (int j = 0; j < 4; j++) {
+					const bool d = (i0 + j > 0) && an_differs<T>(v[j + 1], v[j]);
+					const unsigned kb = (keep4 >> (8 * j)) & 0xffu;
+					out |= (d ? 1u : kb) << (8 * j);
+				}
+				*reinterpret_cast<unsigned *>(r + i0) = out;
+			}
+			done = nquad * 4;
+		}
+	}
+	for (uint64_t i = done + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
 		const bte keep = mode == 1 ? np[i] : mode == 2 ? npb : 0;
 		r[i] = (i > 0 && an_differs<T>(b[i], b[i - 1])) ? (bte) 1 : keep;
 	}
@@ -107,7 +138,7 @@ static void diff_launch(const b200_bat *b, const b200_bat *p, const int8_t *npbi
 {
 	Ctx *c = ctx();
 	KTimer kt("an_diff", n * (sizeof(T) + 1 + (p ? 1 : 0)));
-	an_diff_kernel<T><<<grid_for(n, 256, NSM * 32), 256, 0, c->stream>>>(
+	an_diff_kernel<T><<<grid_for(sizeof(T) == 4 || sizeof(T) == 8 ? n / 4 + 1 : n, 256, NSM * 32), 256, 0, c->stream>>>(
 		(const T *) b->base, p ? (const bte *) p->base : nullptr, p ? 1 : npbit ? 2 : 0, npbit ? *npbit : 0, n, r);
 	COUNT_LAUNCH();
 }
