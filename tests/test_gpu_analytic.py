@@ -359,6 +359,24 @@ def test_config5_shape(gdk, ref):
         close(r.numpy(), rr.numpy(), T.dbl, True)
 
 
+def test_analytics02_golden(gdk):
+    """the reference's own expected columns for 36 framed window queries (sql/test/analytics/Tests/analytics02.test,
+    fixture tests/golden/analytics02.json; the oracle is pinned to the same fixture in tests/test_cpu_oracle.py), through
+    BATsort -> BATproject -> GDKanalyticaldiff -> GDKanalyticalwindowbounds -> GDKanalytical<fn> on the device"""
+    import json
+    from pathlib import Path
+    from tests.window_sql import run_case
+    d = json.loads((Path(__file__).parent / "golden" / "analytics02.json").read_text())
+    assert len(d["cases"]) == 36
+
+    def mk(arr, tt):
+        hn = bool(has_nil(tt, arr))
+        return gdk.BATfromhost(arr, tt, nonil=not hn, nil=hn)
+
+    for c in d["cases"]:
+        assert run_case(gdk, mk, T, d, c) == c["expected"], c["sql"]
+
+
 def test_tree_twin_reuse_and_invalidation(gdk, ref):
     """the inner tree levels of an aggregate are kept as a twin of the value column, keyed by the partition list:
     reused for another frame over the same partitions, rebuilt for other partitions, another aggregate, and after the
