@@ -359,15 +359,17 @@ def test_config5_shape(gdk, ref):
         close(r.numpy(), rr.numpy(), T.dbl, True)
 
 
-def test_analytics02_golden(gdk):
-    """the reference's own expected columns for 36 framed window queries (sql/test/analytics/Tests/analytics02.test,
-    fixture tests/golden/analytics02.json; the oracle is pinned to the same fixture in tests/test_cpu_oracle.py), through
-    BATsort -> BATproject -> GDKanalyticaldiff -> GDKanalyticalwindowbounds -> GDKanalytical<fn> on the device"""
+@pytest.mark.parametrize("name,ncases", [("analytics00", 50), ("analytics02", 36)])
+def test_analytics_golden(gdk, name, ncases):
+    """the reference's own expected columns for its window queries — sql/test/analytics/Tests/analytics00.test (default
+    frames) and analytics02.test (ROWS BETWEEN n PRECEDING AND m FOLLOWING), fixtures tests/golden/analytics0N.json; the
+    oracle is pinned to the same fixtures in tests/test_cpu_oracle.py — through BATsort -> BATproject ->
+    GDKanalyticaldiff -> GDKanalyticalwindowbounds -> GDKanalytical<fn> on the device"""
     import json
     from pathlib import Path
     from tests.window_sql import run_case
-    d = json.loads((Path(__file__).parent / "golden" / "analytics02.json").read_text())
-    assert len(d["cases"]) == 36
+    d = json.loads((Path(__file__).parent / "golden" / (name + ".json")).read_text())
+    assert len(d["cases"]) == ncases
 
     def mk(arr, tt):
         hn = bool(has_nil(tt, arr))

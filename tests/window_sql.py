@@ -19,34 +19,49 @@ def column(table, name):
 
 def run_case(X, mk, T, table, case):
     """-> the result column as the strings a sqllogictest file holds (NULL, integers, reals with 3 decimals), sorted
-    when the case says rowsort.  X: operator module; mk(array, type) -> BAT of that backend; T: its TYPE table."""
+    when the case says rowsort.  X: operator module; mk(array, type) -> BAT of that backend; T: its TYPE table.
+
+    case["frame"] == "rows":    ROWS BETWEEN preceding PRECEDING AND following FOLLOWING (frame type 0, bounds columns)
+    case["frame"] == "default": no ORDER BY -> the whole partition (frame type 5); ORDER BY -> unbounded preceding to
+                                the current row's last peer (frame type 3, peers = rows with the same order value)"""
     n = len(table["rows"])
     vname = case["col"] if case["col"] != "*" else "aa"
     varr, vt = column(table, vname)
     tp = getattr(T, vt)
     vb = mk(varr, tp)
-    p, ob, otp = None, vb, tp
-    if case["partition"]:
-        parr, pt = column(table, case["partition"])
-        pb = mk(parr, getattr(T, pt))
-        srt, order, _ = X.BATsort(pb, None, None, False, False, True)       # ascending, nils first, stable
+    p, o, ob, otp = None, None, vb, tp
+    key = case["partition"] or case.get("order")
+    if key:
+        karr, kt = column(table, key)
+        ktp = getattr(T, kt)
+        desc = bool(case.get("desc"))
+        # ascending: nils first; descending: nils last (they are the smallest value) — both stable
+        srt, order, _ = X.BATsort(mk(karr, ktp), None, None, desc, desc, True)
         vb = X.BATproject(order, vb)
-        p = X.GDKanalyticaldiff(X.colnew(T.bit, n), srt, None, None, getattr(T, pt))
-        ob, otp = srt, getattr(T, pt)
-    s = X.GDKanalyticalwindowbounds(X.colnew(T.oid, n), ob, p, None, case["preceding"], otp, T.lng, 0, True, 0)
-    e = X.GDKanalyticalwindowbounds(X.colnew(T.oid, n), ob, p, None, case["following"], otp, T.lng, 0, False, 1)
+        if case["partition"]:
+            p = X.GDKanalyticaldiff(X.colnew(T.bit, n), srt, None, None, ktp)
+        if case.get("order") and case["frame"] == "default":
+            o = X.GDKanalyticaldiff(X.colnew(T.bit, n), srt, p, None, ktp)      # peers: a new order value or partition
+        ob, otp = srt, ktp
+    if case["frame"] == "rows":
+        s = X.GDKanalyticalwindowbounds(X.colnew(T.oid, n), ob, p, None, case["preceding"], otp, T.lng, 0, True, 0)
+        e = X.GDKanalyticalwindowbounds(X.colnew(T.oid, n), ob, p, None, case["following"], otp, T.lng, 0, False, 1)
+        ft = 0
+    else:
+        s = e = None
+        ft = 3 if case.get("order") else 5
     fn = case["fn"]
     if fn == "sum":
-        r = X.GDKanalyticalsum(X.colnew(T.lng, n), p, None, vb, s, e, tp, T.lng, 0)
+        r = X.GDKanalyticalsum(X.colnew(T.lng, n), p, o, vb, s, e, tp, T.lng, ft)
         nil = np.iinfo(np.int64).min
     elif fn == "avg":
-        r = X.GDKanalyticalfn("avg", X.colnew(T.dbl, n), p, None, vb, s, e, tp, 0)
+        r = X.GDKanalyticalfn("avg", X.colnew(T.dbl, n), p, o, vb, s, e, tp, ft)
         nil = None
     elif fn in ("min", "max"):
-        r = X.GDKanalyticalfn(fn, X.colnew(tp, n), p, None, vb, s, e, tp, 0)
+        r = X.GDKanalyticalfn(fn, X.colnew(tp, n), p, o, vb, s, e, tp, ft)
         nil = np.iinfo(NP[vt]).min
     else:
-        r = X.GDKanalyticalcount(X.colnew(T.lng, n), p, None, vb, s, e, case["col"] != "*", tp, 0)
+        r = X.GDKanalyticalcount(X.colnew(T.lng, n), p, o, vb, s, e, case["col"] != "*", tp, ft)
         nil = np.iinfo(np.int64).min
     out = []
     for v in r.numpy()[:n]:
